@@ -1,0 +1,165 @@
+/* conga_gpu.h — C-ABI of libconga_gpu.so: CONGA's read-depth genotyping hot path
+ * on one B200 (sm_100a).  Plain C types only; no torch, no C++ in the signatures.
+ *
+ * CONGA (reference tree, commit 58d4fe4) has no plugin/FFI interface: the hot
+ * path sits behind four plain C call sites inside read_bam() (bam_data.c:224-359).
+ * Each entry point below names the reference seam it replaces (file:line under
+ * the reference tree).  One cg_ctx per GPU; calls on one context must come from
+ * one host thread at a time.  Every int-returning function returns CG_OK (0) or a
+ * negative CG_E* code; the text is available from cg_last_error().  There is NO
+ * CPU fallback anywhere behind this interface: if the device or the kernels are
+ * unavailable every call fails.
+ *
+ * Per-chromosome call order (mirrors bam_data.c:304-338):
+ *   cg_chrom_begin      <- init_rd_per_chr            bam_data.c:304, read_distribution.c:12-18
+ *   cg_push_reads  (xN) <- count_reads_bam loop body  bam_data.c:201-217
+ *   cg_chrom_finish     <- calc_mean_per_chr          bam_data.c:322, read_distribution.c:27-84
+ *   cg_set_mappability  <- init_mappability_per_chr + load_mappability_regions
+ *                                                     likelihood.c:352-356, svs.c:317-377
+ *   cg_genotype    (x2) <- find_depths                likelihood.c:290-308 -> :108-169, :96-105
+ */
+#ifndef CONGA_GPU_H
+#define CONGA_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CG_ABI_VERSION 1
+
+enum {
+    CG_OK = 0,
+    CG_EINVAL = -1,   /* bad argument / call order */
+    CG_ECUDA = -2,    /* CUDA runtime or kernel failure */
+    CG_ENOMEM = -3,   /* host or device allocation failed */
+    CG_ERANGE = -4    /* a read or interval lies outside [0, chrom_len) */
+};
+
+/* Where the caller's buffers live (cuBLAS-style pointer mode).
+ * HOST  : every in/out pointer is host memory (pinned from cg_alloc_pinned gives
+ *         asynchronous copies); cg_chrom_finish / cg_genotype block until their
+ *         outputs are valid.  This is the drop-in mode.
+ * DEVICE: every in/out pointer is device memory on the context's GPU and must stay
+ *         valid until cg_sync(); nothing is copied and no call blocks. */
+enum { CG_PTR_HOST = 0, CG_PTR_DEVICE = 1 };
+
+/* One alignment record, 8 bytes.  Only pos and mapq feed the depth path
+ * (bam_data.c:205,213: `if (core.qual > mq_threshold) read_depth[core.pos]++`).
+ * len/fl are carried for the --rp gate (bam_data.c:207): fl bit0 secondary,
+ * bit1 qc-fail, bit2 duplicate, bit3 supplementary, bit4 unmapped, bit5 reverse. */
+typedef struct cg_read {
+    int32_t  pos;    /* bam1_core_t.pos, 0-based leftmost */
+    uint16_t len;    /* bam1_core_t.l_qseq (saturated at 65535) */
+    uint8_t  mapq;   /* bam1_core_t.qual */
+    uint8_t  fl;
+} cg_read;
+
+/* A known CNV, BED coordinates as parsed by atoi (svs.c:49-53); half-open
+ * [start,end) as used by the per-base loop likelihood.c:115. */
+typedef struct cg_cnv { int32_t start, end; } cg_cnv;
+
+/* One mappability BED row of the current chromosome in FILE ORDER (svs.c:350-371):
+ * paints [start, end] INCLUSIVE with val; later rows overwrite earlier ones. */
+typedef struct cg_mapiv { int32_t start, end; float val; uint32_t line; } cg_mapiv;
+
+/* Result per CNV; mirrors the fields of `svs` (svs.h:17-26) that find_depths fills. */
+typedef struct cg_call {
+    int32_t  observed;      /* observed_rd_sv   likelihood.c:120 */
+    float    expected;      /* expected_rd_sv   likelihood.c:119 (ordered fp32 sum) */
+    double   mappability;   /* likelihood.c:128; 0 when no mappability was set */
+    double   lhomo, lhetero, lnone;   /* likelihood.c:133-135 / :155-157 */
+    double   score;         /* likelihood_score likelihood.c:138,160 (int-truncating max) */
+    int32_t  copy_number;   /* likelihood.c:146-149 / :164-167 */
+    uint32_t margin_flags;  /* diagnostics only: bit0 (int) truncation of lhomo/lhetero within
+                               1e-7 of an integer, bit1 |lhomo-lhetero| within 1e-7 relative */
+} cg_call;
+
+#define CG_GC_BINS 101
+/* Per-chromosome integer statistics (read_distribution.c:27-84).  As int64[204]
+ * this is one row of the table a multi-GPU run all-reduces (cg_stats_table). */
+typedef struct cg_chrom_stats {
+    int64_t rd_per_gc[CG_GC_BINS];      /* rd_per_gc_unfiltered  read_distribution.c:71 */
+    int64_t window_per_gc[CG_GC_BINS];  /* window_per_gc         read_distribution.c:72 (positions, not windows) */
+    int64_t rd_cnt;                     /* calc_mu_per_chr       read_distribution.c:35 */
+    int64_t reads_passed;               /* total_read_count_unfiltered  bam_data.c:214 */
+} cg_chrom_stats;
+
+typedef struct cg_ctx cg_ctx;
+
+/* Context on CUDA device `device`.  NULL on failure (cg_last_error(NULL) says why). */
+cg_ctx*     cg_create(int device);
+void        cg_destroy(cg_ctx* ctx);
+const char* cg_last_error(cg_ctx* ctx);
+int         cg_abi_version(void);
+int         cg_set_pointer_mode(cg_ctx* ctx, int mode);
+
+/* Page-locked host memory for read batches / results (library owns it). */
+void* cg_alloc_pinned(cg_ctx* ctx, size_t bytes);
+void  cg_free_pinned(cg_ctx* ctx, void* p);
+
+/* Start a chromosome: depth array of chrom_len zeros, read count 0
+ * (init_rd_per_chr, read_distribution.c:12-18).  gc_profile[w] is SONIC's byte for
+ * positions [100w, 100w+100) (sonic_get_gc_content as called from
+ * read_distribution.c:70 / likelihood.c:117 reduces to gc_profile[pos/100]);
+ * n_windows must be >= ceil(chrom_len/100).  A read passes iff mapq > mq_threshold. */
+int cg_chrom_begin(cg_ctx* ctx, int chr_index, int32_t chrom_len,
+                   const int8_t* gc_profile, int32_t n_windows, int mq_threshold);
+
+/* Append n records (bam_data.c:201-217).  Coordinate-sorted input (README.md:93)
+ * takes the tiled shared-memory path; out-of-order input is detected on the device
+ * and handled by the global-atomic path with identical results. */
+int cg_push_reads(cg_ctx* ctx, const cg_read* reads, size_t n);
+
+/* Close the chromosome: depth (int16, wraps mod 2^16 like the reference's `short`),
+ * int32 inclusive prefix, chromosome sum and the 101 GC-bin sums/counts, and the
+ * expected_read_depth[101] table computed with the reference's exact expression
+ * (read_distribution.c:75-83).  `out` may be NULL. */
+int cg_chrom_finish(cg_ctx* ctx, cg_chrom_stats* out);
+
+/* expected_read_depth[101] of the current chromosome (bam_info.expected_read_depth,
+ * common.h:94).  set overrides what cg_chrom_finish derived (tests, replays). */
+int cg_get_expected(cg_ctx* ctx, float expected[CG_GC_BINS]);
+int cg_set_expected(cg_ctx* ctx, const float expected[CG_GC_BINS]);
+
+/* Mappability rows of the current chromosome; n == 0 clears (no --mappability).
+ * Always a HOST pointer: rows are flattened to disjoint runs on the host (input
+ * preparation, like BED parsing) before upload. */
+int cg_set_mappability(cg_ctx* ctx, const cg_mapiv* rows, size_t n);
+
+/* Genotype n CNVs of the current chromosome (find_depths, likelihood.c:290-308).
+ * is_dup = 0: DELETION hypotheses lambda in {0, 0.5E, E}; 1: DUPLICATION {2E, 1.5E, E}.
+ * Requires 0 <= start and end <= chrom_len (the reference reads unchecked, A23). */
+int cg_genotype(cg_ctx* ctx, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out);
+
+/* Wait for everything queued on the context. */
+int cg_sync(cg_ctx* ctx);
+
+/* Parity/diagnostic downloads of the current chromosome (HOST pointers always). */
+int cg_download_depth(cg_ctx* ctx, int16_t* out /* chrom_len */);
+int cg_download_prefix(cg_ctx* ctx, int32_t* out /* chrom_len */);
+
+/* Device address of the int64[n_rows][204] statistics table, one row per
+ * chr_index seen since cg_stats_reset (layout = cg_chrom_stats).  A multi-GPU
+ * driver all-reduces it (NCCL sum) so every rank holds every chromosome's row. */
+int cg_stats_table(cg_ctx* ctx, void** device_ptr, int32_t* n_rows);
+int cg_stats_reset(cg_ctx* ctx);
+int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
+
+/* Timing of the kernels queued by the last cg_chrom_finish / cg_genotype calls,
+ * from CUDA events on the context's stream.  ms[0]=tile-bounds, ms[1]=fused
+ * depth+GC+prefix pass, ms[2]=genotype (sum of launches since finish).  Only
+ * meaningful after cg_sync() and when enabled with cg_set_profiling(ctx,1). */
+int cg_set_profiling(cg_ctx* ctx, int on);
+int cg_last_kernel_ms(cg_ctx* ctx, float ms[3]);
+/* Number of kernels this context has launched since creation. */
+int64_t cg_launch_count(cg_ctx* ctx);
+/* The CUDA stream (cudaStream_t) all of this context's work is queued on. */
+void* cg_stream(cg_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CONGA_GPU_H */

@@ -1,0 +1,209 @@
+/* conga_oracle.c — CPU restatement of CONGA's read-depth genotyping hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This file is the checker the CUDA path is compared
+ * against; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may build, load or call it.  Nothing under conga_b200/
+ * links or imports it, and the product has no CPU fallback.
+ *
+ * Parity status: CONGA ships no tests, golden vectors or example data
+ * (SURVEY.md §4), so upstream pins nothing.  This restatement is instead pinned
+ * against the UNMODIFIED reference objects compiled from /root/reference
+ * (oracle/Makefile target `ref` -> oracle/_ref/conga_dump, a --wrap shim that
+ * dumps the reference's own intermediates); the resulting vectors are committed
+ * under tests/golden/ and tests/test_oracle_golden.py replays them here.
+ * libm (log, lgamma) comes from the host glibc, exactly as in the reference.
+ *
+ * Written from the behaviour of the reference, one loop per reference loop, with
+ * the same C types so the same integer wrap and fp32/fp64 rounding happen:
+ *   orc_count_reads          bam_data.c:201-217        (count_reads_bam body)
+ *   orc_calc_mu              read_distribution.c:27-46 (calc_mu_per_chr)
+ *   orc_calc_mean_per_chr    read_distribution.c:49-84 (calc_mean_per_chr)
+ *   orc_gc_bin               sonic/sonic_interval.c:245-273 as called with a
+ *                            <=100-wide interval, + (int)round() at the call sites
+ *   orc_paint_mappability    svs.c:317-377 + read_distribution.c:20-24
+ *   orc_lpoisson             likelihood.c:96-105
+ *   orc_imax                 common.c:262-268 (int max(int,int) fed doubles)
+ *   orc_calculate_likelihood likelihood.c:108-169
+ *   orc_compare_start_pos    common.c:199-215
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/conga_gpu.h"
+
+/* bam_data.c:201-217.  `depth` plays in_bam->read_depth (short, zeroed by
+ * init_rd_per_chr, read_distribution.c:12-18).  The increment is done in
+ * unsigned 16-bit arithmetic and stored back, which is what gcc emits for
+ * `short++` (wraps 32767 -> -32768). */
+void orc_count_reads(const cg_read* recs, size_t n, int mq_threshold,
+                     int16_t* depth, int32_t chrom_len, int32_t* total_read_count)
+{
+    int32_t cnt = *total_read_count;
+    for (size_t i = 0; i < n; i++) {
+        if ((int)recs[i].mapq > mq_threshold) {            /* bam_data.c:205 */
+            int32_t p = recs[i].pos;
+            if (p >= 0 && p < chrom_len)                   /* iterator guarantees it, A3 */
+                depth[p] = (int16_t)(uint16_t)((uint16_t)depth[p] + 1u);   /* :213 */
+            cnt++;                                          /* :214 */
+        }
+    }
+    *total_read_count = cnt;
+}
+
+/* read_distribution.c:27-46 */
+void orc_calc_mu(const int16_t* depth, int32_t chrom_len, int64_t* rd_cnt_out, float* mean_out)
+{
+    long rd_cnt = 0, window_total = 0;
+    for (int i = 0; i < chrom_len; i++) {
+        rd_cnt += (long)depth[i];
+        window_total++;
+    }
+    float mean = (double)rd_cnt / (double)window_total;    /* :39, stored to a float field */
+    *rd_cnt_out = rd_cnt;
+    *mean_out = mean;
+}
+
+/* sonic_get_gc_content(sonic, chr, i, end) with end - i <= 100 runs its loop
+ * exactly once (sonic/sonic_interval.c:263-267) and returns
+ * (float)gc_profile[i/100] / 1, or 0.0 when that is 0; the callers apply
+ * (int)round() (read_distribution.c:70, likelihood.c:117). */
+static inline int orc_gc_bin_inl(const int8_t* gc, int pos)
+{
+    float gc_content = 0.0f;
+    gc_content += (float)gc[pos / 100];
+    float r = (gc_content != 0.0f) ? (gc_content / 1) : 0.0f;
+    return (int)round(r);
+}
+int orc_gc_bin(const int8_t* gc, int pos) { return orc_gc_bin_inl(gc, pos); }
+
+/* read_distribution.c:49-84 */
+void orc_calc_mean_per_chr(const int16_t* depth, int32_t chrom_len, const int8_t* gc,
+                           int64_t rd_per_gc[CG_GC_BINS], int64_t window_per_gc_out[CG_GC_BINS],
+                           float expected[CG_GC_BINS])
+{
+    int window_per_gc[CG_GC_BINS];
+    long rd_per_gc_unfiltered[CG_GC_BINS];
+    for (int i = 0; i < CG_GC_BINS; i++) { rd_per_gc_unfiltered[i] = 0; window_per_gc[i] = 0; }
+
+    for (int i = 0; i < chrom_len; i++) {
+        int gc_val = orc_gc_bin_inl(gc, i);                /* :70 */
+        rd_per_gc_unfiltered[gc_val] += (long)depth[i];    /* :71 */
+        window_per_gc[gc_val]++;                           /* :72 */
+    }
+    expected[0] = 0.0;                                     /* :75 */
+    for (int i = 1; i < CG_GC_BINS; i++) {
+        expected[i] = (float)rd_per_gc_unfiltered[i] / (window_per_gc[i]);   /* :78 */
+        if (isnan(expected[i]) || isinf(expected[i]))      /* :80-82 */
+            expected[i] = 0;
+    }
+    for (int i = 0; i < CG_GC_BINS; i++) {
+        rd_per_gc[i] = rd_per_gc_unfiltered[i];
+        window_per_gc_out[i] = window_per_gc[i];
+    }
+}
+
+/* read_distribution.c:20-24 + svs.c:350-371.  Rows are the current chromosome's
+ * rows in file order; inclusive end; later rows overwrite.  The reference paints
+ * unchecked (A10); rows are clipped to the array here so the oracle cannot
+ * corrupt memory — generators never emit out-of-range rows. */
+void orc_paint_mappability(float* mapp, int32_t chrom_len, const cg_mapiv* rows, size_t n)
+{
+    memset(mapp, 0, (size_t)chrom_len * sizeof(float));
+    for (size_t r = 0; r < n; r++) {
+        int s = rows[r].start, e = rows[r].end;
+        if (s < 0) s = 0;
+        if (e > chrom_len - 1) e = chrom_len - 1;
+        for (int i = s; i <= e; i++) mapp[i] = rows[r].val;
+    }
+}
+
+/* likelihood.c:96-105 */
+double orc_lpoisson(int observed, double lambda)
+{
+    double penalty = 0.01;
+    if (lambda == 0.0) lambda = penalty;
+    return observed * log(lambda) - lambda - lgamma(observed + 1);
+}
+
+/* common.c:262-268 — `int max(int,int)`; the call sites pass doubles, which C
+ * converts by truncation toward zero. */
+static int orc_imax_i(int x, int y) { return (x < y) ? y : x; }
+int orc_imax(double x, double y) { return orc_imax_i((int)x, (int)y); }
+
+/* likelihood.c:108-169.  mapp == NULL <=> params->mappability_file == NULL. */
+void orc_calculate_likelihood(const int16_t* depth, const int8_t* gc,
+                              const float expected[CG_GC_BINS], const float* mapp,
+                              int32_t start, int32_t end, int is_dup, cg_call* out)
+{
+    float expected_rd = 0;
+    int observed_rd = 0;
+    double mappability_score = 0;
+
+    for (int i = start; i < end; i++) {                    /* :115 */
+        int gc_val = orc_gc_bin_inl(gc, i);                /* :117 */
+        expected_rd += expected[gc_val];                   /* :119  fp32, in order */
+        observed_rd += depth[i];                           /* :120 */
+        if (mapp != NULL) mappability_score += mapp[i];    /* :122-123 fp64 += fp32 */
+    }
+    memset(out, 0, sizeof(*out));
+    if (mapp != NULL) out->mappability = mappability_score / (double)(end - start);   /* :128 */
+
+    if (!is_dup) {
+        out->lhomo   = orc_lpoisson(observed_rd, 0.0);                 /* :133 */
+        out->lhetero = orc_lpoisson(observed_rd, 0.5 * expected_rd);   /* :134 */
+        out->lnone   = orc_lpoisson(observed_rd, expected_rd);         /* :135 */
+        out->score = orc_imax_i(out->lhomo, out->lhetero) / out->lnone;   /* :138 */
+        out->observed = observed_rd;
+        out->expected = expected_rd;
+        out->copy_number = (observed_rd < (expected_rd / 4)) ? 2 : 1;  /* :146-149 */
+    } else {
+        out->lhomo   = orc_lpoisson(observed_rd, 2 * expected_rd);     /* :155 (float product) */
+        out->lhetero = orc_lpoisson(observed_rd, 1.5 * expected_rd);   /* :156 */
+        out->lnone   = orc_lpoisson(observed_rd, expected_rd);         /* :157 */
+        out->score = orc_imax_i(out->lhomo, out->lhetero) / out->lnone;   /* :160 */
+        out->observed = observed_rd;
+        out->expected = expected_rd;
+        out->copy_number = (out->lhomo > out->lhetero) ? 2 : 1;        /* :164-167 */
+    }
+}
+
+/* find_depths, likelihood.c:290-308: every CNV of one type in array order. */
+void orc_find_depths(const int16_t* depth, const int8_t* gc, const float expected[CG_GC_BINS],
+                     const float* mapp, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out)
+{
+    for (size_t c = 0; c < n; c++)
+        orc_calculate_likelihood(depth, gc, expected, mapp, cnvs[c].start, cnvs[c].end, is_dup, &out[c]);
+}
+
+/* common.c:199-215 on (start,end) pairs; used with qsort like likelihood.c:324-328. */
+int orc_compare_start_pos(const void* a, const void* b)
+{
+    const cg_cnv* x = (const cg_cnv*)a; const cg_cnv* y = (const cg_cnv*)b;
+    if (x->start > y->start) return 1;
+    else if (x->start == y->start) return x->end - y->end;
+    else return -1;
+}
+void orc_sort_cnvs(cg_cnv* cnvs, size_t n) { qsort(cnvs, n, sizeof(cg_cnv), orc_compare_start_pos); }
+
+/* The whole per-chromosome path in one call: the CPU baseline bench.py times
+ * (kind "port").  depth and mapp are caller-provided scratch of chrom_len. */
+void orc_chromosome(const cg_read* recs, size_t n_reads, int mq_threshold,
+                    int32_t chrom_len, const int8_t* gc,
+                    const cg_mapiv* rows, size_t n_rows,
+                    const cg_cnv* dels, size_t n_dels, cg_call* del_out,
+                    const cg_cnv* dups, size_t n_dups, cg_call* dup_out,
+                    int16_t* depth, float* mapp, cg_chrom_stats* stats, float expected[CG_GC_BINS])
+{
+    int32_t cnt = 0; float mean;
+    memset(depth, 0, (size_t)chrom_len * sizeof(int16_t));        /* read_distribution.c:17 */
+    orc_count_reads(recs, n_reads, mq_threshold, depth, chrom_len, &cnt);
+    orc_calc_mu(depth, chrom_len, &stats->rd_cnt, &mean);
+    orc_calc_mean_per_chr(depth, chrom_len, gc, stats->rd_per_gc, stats->window_per_gc, expected);
+    stats->reads_passed = cnt;
+    const float* m = NULL;
+    if (n_rows > 0 && mapp != NULL) { orc_paint_mappability(mapp, chrom_len, rows, n_rows); m = mapp; }
+    orc_find_depths(depth, gc, expected, m, dels, n_dels, 0, del_out);
+    orc_find_depths(depth, gc, expected, m, dups, n_dups, 1, dup_out);
+}
