@@ -1,0 +1,306 @@
+"""ctypes binding of ``libconga_gpu.so`` (``include/conga_gpu.h``).
+
+This is the only way Python code in this repository reaches the hot path: every
+call below goes through the C-ABI a C host would bind.  There is no Python or
+NumPy implementation of any stage here and none is substituted when the library
+or a GPU is missing — ``load_library`` raises, and so does every failed call.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libconga_gpu.so")
+
+CG_OK, CG_EINVAL, CG_ECUDA, CG_ENOMEM, CG_ERANGE = 0, -1, -2, -3, -4
+CG_PTR_HOST, CG_PTR_DEVICE = 0, 1
+CG_GC_BINS = 101
+CG_NSLOTS = 4
+CG_TILE = 16384
+
+# struct layouts of include/conga_gpu.h as NumPy dtypes
+READ_DT = np.dtype([("pos", "<i4"), ("len", "<u2"), ("mapq", "u1"), ("fl", "u1")])
+CNV_DT = np.dtype([("start", "<i4"), ("end", "<i4")])
+MAPIV_DT = np.dtype([("start", "<i4"), ("end", "<i4"), ("val", "<f4"), ("line", "<u4")])
+MAPRUN_DT = np.dtype([("start", "<i4"), ("end", "<i4"), ("val", "<f4"), ("pad", "<i4")])
+CALL_DT = np.dtype([("observed", "<i4"), ("expected", "<f4"), ("mappability", "<f8"),
+                    ("lhomo", "<f8"), ("lhetero", "<f8"), ("lnone", "<f8"), ("score", "<f8"),
+                    ("copy_number", "<i4"), ("margin_flags", "<u4")])
+STATS_DT = np.dtype([("rd_per_gc", "<i8", (CG_GC_BINS,)), ("window_per_gc", "<i8", (CG_GC_BINS,)),
+                     ("rd_cnt", "<i8"), ("reads_passed", "<i8")])
+assert READ_DT.itemsize == 8 and CNV_DT.itemsize == 8 and MAPIV_DT.itemsize == 16
+assert MAPRUN_DT.itemsize == 16 and CALL_DT.itemsize == 56 and STATS_DT.itemsize == 204 * 8
+
+# every symbol include/conga_gpu.h declares: name -> (restype, argtypes)
+_P, _I, _Z = C.c_void_p, C.c_int, C.c_size_t
+SYMBOLS = {
+    "cg_abi_version": (_I, []),
+    "cg_create": (_P, [_I]),
+    "cg_destroy": (None, [_P]),
+    "cg_last_error": (C.c_char_p, [_P]),
+    "cg_set_pointer_mode": (_I, [_P, _I]),
+    "cg_alloc_pinned": (_P, [_P, _Z]),
+    "cg_free_pinned": (None, [_P, _P]),
+    "cg_chrom_begin": (_I, [_P, _I, C.c_int32, _P, C.c_int32, _I]),
+    "cg_push_reads": (_I, [_P, _P, _Z]),
+    "cg_chrom_finish": (_I, [_P, _P]),
+    "cg_get_expected": (_I, [_P, _P]),
+    "cg_set_expected": (_I, [_P, _P]),
+    "cg_set_mappability": (_I, [_P, _P, _Z]),
+    "cg_flatten_mappability": (_I, [_P, _Z, C.c_int32, C.POINTER(_P), C.POINTER(_Z)]),
+    "cg_free_runs": (None, [_P]),
+    "cg_set_mappability_runs": (_I, [_P, _P, _Z, _I]),
+    "cg_genotype": (_I, [_P, _P, _Z, _I, _P]),
+    "cg_sync": (_I, [_P]),
+    "cg_download_depth": (_I, [_P, _P]),
+    "cg_download_prefix": (_I, [_P, _P]),
+    "cg_device_arrays": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
+    "cg_stats_table": (_I, [_P, C.POINTER(_P), C.POINTER(C.c_int32)]),
+    "cg_stats_reset": (_I, [_P]),
+    "cg_stats_row": (_I, [_P, _I, _P]),
+    "cg_set_profiling": (_I, [_P, _I]),
+    "cg_kernel_times": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "cg_launch_count": (C.c_int64, [_P]),
+    "cg_stream": (_P, [_P]),
+}
+
+
+class CongaGpuError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libconga_gpu error {code}: {message}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libconga_gpu.so and type every entry point.  Raises if it is absent:
+    the product has no other implementation to fall back to."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise RuntimeError(f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "or `make -C conga_b200/csrc` (there is no CPU fallback)")
+    lib = C.CDLL(p)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _ptr(x) -> int:
+    """Address of a NumPy array (host), a torch tensor (device or host) or a raw int."""
+    if x is None:
+        return 0
+    if isinstance(x, int):
+        return x
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    if hasattr(x, "data_ptr"):
+        return int(x.data_ptr())
+    raise TypeError(f"cannot take the address of {type(x)}")
+
+
+class Context:
+    """One ``cg_ctx`` (one GPU).  Methods mirror the C entry points one to one; NumPy
+    arrays are passed in HOST pointer mode, torch CUDA tensors / raw device addresses in
+    DEVICE pointer mode."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.h = self.lib.cg_create(device)
+        if not self.h:
+            raise CongaGpuError(CG_ECUDA, self.lib.cg_last_error(None).decode())
+        self.device = device
+        self.mode = CG_PTR_HOST
+        self.chrom_len = 0
+
+    # -- plumbing -----------------------------------------------------------
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _ck(self, rc: int, allow=()):
+        if rc != CG_OK and rc not in allow:
+            raise CongaGpuError(rc, self.lib.cg_last_error(self.h).decode())
+        return rc
+
+    def set_pointer_mode(self, mode: int):
+        self._ck(self.lib.cg_set_pointer_mode(self.h, mode))
+        self.mode = mode
+
+    def sync(self):
+        self._ck(self.lib.cg_sync(self.h))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.cg_stream(self.h) or 0)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.cg_launch_count(self.h))
+
+    def alloc_pinned(self, nbytes: int) -> int:
+        p = self.lib.cg_alloc_pinned(self.h, nbytes)
+        if not p:
+            raise CongaGpuError(CG_ENOMEM, self.lib.cg_last_error(self.h).decode())
+        return int(p)
+
+    def free_pinned(self, p: int):
+        self.lib.cg_free_pinned(self.h, p)
+
+    def pinned_array(self, n: int, dtype) -> np.ndarray:
+        """A NumPy view of n elements of page-locked memory owned by the library."""
+        dt = np.dtype(dtype)
+        p = self.alloc_pinned(max(1, n * dt.itemsize))
+        buf = (C.c_char * (n * dt.itemsize)).from_address(p)
+        arr = np.frombuffer(buf, dtype=dt, count=n)
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(p)
+        return arr
+
+    # -- the per-chromosome path ---------------------------------------------
+    def chrom_begin(self, chr_index: int, chrom_len: int, gc_profile, mq_threshold: int = -1, n_windows=None):
+        if isinstance(gc_profile, np.ndarray):
+            assert gc_profile.dtype == np.int8 and gc_profile.flags.c_contiguous
+            n_windows = len(gc_profile) if n_windows is None else n_windows
+        elif n_windows is None:
+            n_windows = int(gc_profile.numel())
+        self._keep_gc = gc_profile
+        self._ck(self.lib.cg_chrom_begin(self.h, chr_index, chrom_len, _ptr(gc_profile), n_windows, mq_threshold))
+        self.chrom_len = chrom_len
+
+    def push_reads(self, reads, n: Optional[int] = None):
+        if isinstance(reads, np.ndarray):
+            assert reads.dtype == READ_DT and reads.flags.c_contiguous
+            n = len(reads) if n is None else n
+        assert n is not None
+        self._ck(self.lib.cg_push_reads(self.h, _ptr(reads), n))
+
+    def chrom_finish(self, out=None, allow_range: bool = False):
+        """HOST mode: returns the cg_chrom_stats record.  DEVICE mode: `out` is a device address or None."""
+        if self.mode == CG_PTR_HOST:
+            st = np.zeros(1, dtype=STATS_DT)
+            self._ck(self.lib.cg_chrom_finish(self.h, st.ctypes.data), allow=(CG_ERANGE,) if allow_range else ())
+            return st[0]
+        self._ck(self.lib.cg_chrom_finish(self.h, _ptr(out)))
+        return None
+
+    def get_expected(self) -> np.ndarray:
+        assert self.mode == CG_PTR_HOST
+        e = np.zeros(CG_GC_BINS, dtype=np.float32)
+        self._ck(self.lib.cg_get_expected(self.h, e.ctypes.data))
+        return e
+
+    def set_expected(self, expected):
+        if isinstance(expected, np.ndarray):
+            expected = np.ascontiguousarray(expected, dtype=np.float32)
+            assert expected.shape == (CG_GC_BINS,)
+        self._keep_exp = expected
+        self._ck(self.lib.cg_set_expected(self.h, _ptr(expected)))
+        if self.mode == CG_PTR_HOST:
+            self.sync()
+
+    def set_mappability(self, rows: Optional[np.ndarray]):
+        if rows is None or len(rows) == 0:
+            self._ck(self.lib.cg_set_mappability(self.h, None, 0))
+            return
+        assert rows.dtype == MAPIV_DT and rows.flags.c_contiguous
+        self._ck(self.lib.cg_set_mappability(self.h, rows.ctypes.data, len(rows)))
+
+    def set_mappability_runs(self, runs, n: Optional[int] = None, enabled: bool = True):
+        if isinstance(runs, np.ndarray):
+            assert runs.dtype == MAPRUN_DT and runs.flags.c_contiguous
+            n = len(runs)
+        self._keep_runs = runs
+        self._ck(self.lib.cg_set_mappability_runs(self.h, _ptr(runs), n or 0, 1 if enabled else 0))
+        if self.mode == CG_PTR_HOST:
+            self.sync()
+
+    def genotype(self, cnvs, is_dup: bool, out=None, n: Optional[int] = None, allow_range: bool = False):
+        if self.mode == CG_PTR_HOST:
+            assert cnvs.dtype == CNV_DT and cnvs.flags.c_contiguous
+            res = np.zeros(len(cnvs), dtype=CALL_DT)
+            if len(cnvs):
+                self._ck(self.lib.cg_genotype(self.h, cnvs.ctypes.data, len(cnvs), int(is_dup), res.ctypes.data),
+                         allow=(CG_ERANGE,) if allow_range else ())
+            return res
+        assert n is not None
+        self._ck(self.lib.cg_genotype(self.h, _ptr(cnvs), n, int(is_dup), _ptr(out)))
+        return None
+
+    # -- diagnostics -----------------------------------------------------------
+    def download_depth(self) -> np.ndarray:
+        d = np.empty(self.chrom_len, dtype=np.int16)
+        self._ck(self.lib.cg_download_depth(self.h, d.ctypes.data))
+        return d
+
+    def download_prefix(self) -> np.ndarray:
+        d = np.empty(self.chrom_len, dtype=np.int32)
+        self._ck(self.lib.cg_download_prefix(self.h, d.ctypes.data))
+        return d
+
+    def device_arrays(self):
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.cg_device_arrays(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return int(a.value or 0), int(b.value or 0), int(c.value or 0)
+
+    def stats_table(self):
+        p, n = C.c_void_p(), C.c_int32()
+        self._ck(self.lib.cg_stats_table(self.h, C.byref(p), C.byref(n)))
+        return int(p.value or 0), int(n.value)
+
+    def stats_reset(self):
+        self._ck(self.lib.cg_stats_reset(self.h))
+
+    def stats_row(self, chr_index: int):
+        st = np.zeros(1, dtype=STATS_DT)
+        self._ck(self.lib.cg_stats_row(self.h, chr_index, st.ctypes.data))
+        return st[0]
+
+    def set_profiling(self, on: bool):
+        self._ck(self.lib.cg_set_profiling(self.h, int(on)))
+
+    def kernel_times(self):
+        ms = (C.c_double * CG_NSLOTS)()
+        n = (C.c_int64 * CG_NSLOTS)()
+        self._ck(self.lib.cg_kernel_times(self.h, ms, n))
+        return list(ms), list(n)
+
+
+def flatten_mappability(rows: np.ndarray, chrom_len: int) -> np.ndarray:
+    """Host-side cg_flatten_mappability: BED rows (file order, inclusive ends) -> disjoint runs."""
+    lib = load_library()
+    assert rows.dtype == MAPIV_DT and rows.flags.c_contiguous
+    p, n = C.c_void_p(), C.c_size_t()
+    rc = lib.cg_flatten_mappability(rows.ctypes.data if len(rows) else None, len(rows), chrom_len, C.byref(p), C.byref(n))
+    if rc != CG_OK:
+        raise CongaGpuError(rc, lib.cg_last_error(None).decode())
+    try:
+        buf = (C.c_char * (n.value * MAPRUN_DT.itemsize)).from_address(p.value) if n.value else b""
+        return np.frombuffer(buf, dtype=MAPRUN_DT, count=n.value).copy()
+    finally:
+        lib.cg_free_runs(p)

@@ -1,0 +1,62 @@
+/* cg_internal.h — shared between the translation units of libconga_gpu.so.
+ * Not part of the ABI (include/conga_gpu.h is). */
+#ifndef CG_INTERNAL_H
+#define CG_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/conga_gpu.h"
+
+/* ---- geometry of the fused depth pass (K1+K2+K3) ------------------------- */
+#define CG_TILE        16384          /* positions per tile: 64 KB of u32 bins in smem */
+#define CG_PASS_THREADS  256
+#define CG_TILE_SHIFT  14
+#define CG_STATS_WORDS 204            /* int64 words per chromosome row = sizeof(cg_chrom_stats)/8 */
+
+/* Device-side error/condition bits, one u32 word per context. */
+#define CG_FLAG_UNSORTED   1u         /* a pushed record had pos < its predecessor */
+#define CG_FLAG_RANGE      2u         /* a record or CNV outside [0, chrom_len) */
+
+struct cg_pass_args {
+    const cg_read* reads;             /* all records of the chromosome, device */
+    long long      n_reads;
+    const int32_t* tile_lo;           /* [n_tiles+1] first record index of each tile (sorted input) */
+    const int8_t*  gc;                /* SONIC GC byte per 100-position window */
+    int32_t        chrom_len;
+    int32_t        n_tiles;
+    int            mq_threshold;
+    int16_t*       depth;             /* [n_tiles*CG_TILE] */
+    int32_t*       prefix;            /* [n_tiles*CG_TILE] inclusive int32 prefix of depth */
+    unsigned long long* tile_state;   /* [n_tiles] decoupled look-back words */
+    unsigned int*  tile_counter;      /* dynamic tile index */
+    const uint32_t* depth32;          /* unsorted fallback: per-position u32 counts */
+    const unsigned int* flags;        /* CG_FLAG_* word */
+    long long*     stats;             /* this chromosome's int64[204] row */
+};
+
+#ifdef __cplusplus
+extern "C++" {
+/* depth_pass.cu */
+cudaError_t cgk_chrom_init(cudaStream_t s, unsigned long long* tile_state, int n_tiles,
+                           unsigned int* tile_counter, long long* stats_row, unsigned int* flags);
+cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
+                           int32_t* tile_lo, int n_tiles, int32_t chrom_len, unsigned int* flags);
+cudaError_t cgk_seal_bounds(cudaStream_t s, const cg_read* reads, long long n_reads,
+                            int32_t* tile_lo, int n_tiles);
+cudaError_t cgk_unsorted_scatter(cudaStream_t s, const cg_read* reads, long long n_reads,
+                                 uint32_t* depth32, long long n_words, int32_t chrom_len,
+                                 int mq_threshold, const unsigned int* flags, long long* stats_row,
+                                 int n_sms);
+cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms);
+cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
+int         cgk_depth_pass_ctas_per_sm(void);
+
+/* genotype.cu */
+cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
+                         const int32_t* prefix, const int8_t* gc, const float* expected,
+                         const cg_maprun* runs, int n_runs, int has_map,
+                         int32_t chrom_len, unsigned int* flags, cg_call* out, int* work_counter);
+}
+#endif
+
+#endif /* CG_INTERNAL_H */

@@ -65,6 +65,12 @@ typedef struct cg_cnv { int32_t start, end; } cg_cnv;
  * paints [start, end] INCLUSIVE with val; later rows overwrite earlier ones. */
 typedef struct cg_mapiv { int32_t start, end; float val; uint32_t line; } cg_mapiv;
 
+/* One disjoint run of the flattened mappability track: positions [start, end)
+ * (half-open) all carry `val` — what mappability[] holds after svs.c:350-371 has
+ * painted every row.  Runs are sorted by start and never overlap; unpainted (zero)
+ * stretches are simply absent. */
+typedef struct cg_maprun { int32_t start, end; float val; int32_t pad; } cg_maprun;
+
 /* Result per CNV; mirrors the fields of `svs` (svs.h:17-26) that find_depths fills. */
 typedef struct cg_call {
     int32_t  observed;      /* observed_rd_sv   likelihood.c:120 */
@@ -126,8 +132,18 @@ int cg_set_expected(cg_ctx* ctx, const float expected[CG_GC_BINS]);
 
 /* Mappability rows of the current chromosome; n == 0 clears (no --mappability).
  * Always a HOST pointer: rows are flattened to disjoint runs on the host (input
- * preparation, like BED parsing) before upload. */
+ * preparation, like BED parsing) before upload.  Call after cg_chrom_begin. */
 int cg_set_mappability(cg_ctx* ctx, const cg_mapiv* rows, size_t n);
+
+/* The same in two steps, for callers that keep tracks resident across samples
+ * (batch mode): flatten once on the host (result malloc'ed, free with
+ * cg_free_runs), then hand the runs over — a host or device pointer according to
+ * the pointer mode.  enabled != 0 with n == 0 means "--mappability given but no
+ * row on this chromosome" (mappability 0.0 for every CNV). */
+int  cg_flatten_mappability(const cg_mapiv* rows, size_t n, int32_t chrom_len,
+                            cg_maprun** runs_out, size_t* n_out);
+void cg_free_runs(cg_maprun* runs);
+int  cg_set_mappability_runs(cg_ctx* ctx, const cg_maprun* runs, size_t n, int enabled);
 
 /* Genotype n CNVs of the current chromosome (find_depths, likelihood.c:290-308).
  * is_dup = 0: DELETION hypotheses lambda in {0, 0.5E, E}; 1: DUPLICATION {2E, 1.5E, E}.
@@ -140,6 +156,9 @@ int cg_sync(cg_ctx* ctx);
 /* Parity/diagnostic downloads of the current chromosome (HOST pointers always). */
 int cg_download_depth(cg_ctx* ctx, int16_t* out /* chrom_len */);
 int cg_download_prefix(cg_ctx* ctx, int32_t* out /* chrom_len */);
+/* Device addresses of the current chromosome's arrays (valid until the next
+ * cg_chrom_begin): int16 depth, int32 inclusive prefix, float expected[101]. */
+int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const int32_t** prefix, const float** expected);
 
 /* Device address of the int64[n_rows][204] statistics table, one row per
  * chr_index seen since cg_stats_reset (layout = cg_chrom_stats).  A multi-GPU
@@ -148,12 +167,14 @@ int cg_stats_table(cg_ctx* ctx, void** device_ptr, int32_t* n_rows);
 int cg_stats_reset(cg_ctx* ctx);
 int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
 
-/* Timing of the kernels queued by the last cg_chrom_finish / cg_genotype calls,
- * from CUDA events on the context's stream.  ms[0]=tile-bounds, ms[1]=fused
- * depth+GC+prefix pass, ms[2]=genotype (sum of launches since finish).  Only
- * meaningful after cg_sync() and when enabled with cg_set_profiling(ctx,1). */
+/* Device time of this context's kernels, from CUDA events recorded on its stream
+ * around every launch group while profiling is on.  cg_kernel_times waits for the
+ * stream, returns the milliseconds and launch counts accumulated since the last
+ * call, and clears them.  Slots: 0 = chromosome init + batch marking + bounds,
+ * 1 = the fused depth/GC/prefix pass, 2 = CNV sums + likelihoods, 3 = expected table. */
+#define CG_NSLOTS 4
 int cg_set_profiling(cg_ctx* ctx, int on);
-int cg_last_kernel_ms(cg_ctx* ctx, float ms[3]);
+int cg_kernel_times(cg_ctx* ctx, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS]);
 /* Number of kernels this context has launched since creation. */
 int64_t cg_launch_count(cg_ctx* ctx);
 /* The CUDA stream (cudaStream_t) all of this context's work is queued on. */
