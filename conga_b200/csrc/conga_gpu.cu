@@ -47,7 +47,8 @@ struct cg_ctx {
     long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
     float* d_expected = nullptr;              /* [101] */
     unsigned int* d_flags = nullptr;          /* [0] CG_FLAG_*  [1] tile counter */
-    int* d_work = nullptr;
+    unsigned int* d_work = nullptr;      /* monotonic work counter of the genotype kernel */
+    unsigned int work_base = 0;
 
     /* pinned staging */
     cg_chrom_stats* h_stats = nullptr;
@@ -144,6 +145,7 @@ cg_ctx* cg_create(int device)
         && cudaMalloc(&c->d_flags, 16) == cudaSuccess
         && cudaMemset(c->d_flags, 0, 16) == cudaSuccess
         && cudaMalloc(&c->d_work, 16) == cudaSuccess
+        && cudaMemset(c->d_work, 0, 16) == cudaSuccess
         && cudaMallocHost(&c->h_stats, sizeof(cg_chrom_stats)) == cudaSuccess
         && cudaMallocHost(&c->h_flags, 16) == cudaSuccess;
     if (!ok) {
@@ -506,9 +508,9 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
         d_in = c->d_cnvs; d_out = c->d_calls;
     }
     {
-        prof_scope ps(c, 2, 3);
+        prof_scope ps(c, 2, 1);
         CU(c, cgk_genotype(c->stream, d_in, (int)n, is_dup ? 1 : 0, c->d_prefix, c->gc_ptr, c->d_expected,
-                           c->runs_ptr, c->n_runs, c->has_map, c->chrom_len, c->d_flags, d_out, c->d_work));
+                           c->runs_ptr, c->n_runs, c->has_map, c->chrom_len, c->d_flags, d_out, c->d_work, &c->work_base, c->n_sms));
     }
     if (c->ptr_mode == CG_PTR_HOST) {
         CU(c, cudaMemcpyAsync(out, c->d_calls, n * sizeof(cg_call), cudaMemcpyDeviceToHost, c->stream));
@@ -561,7 +563,7 @@ int cg_stats_reset(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)std::max(c->n_rows, 1), c->stream));
+    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)CG_MAX_CHROMS, c->stream));
     c->n_rows = 0;
     return CG_OK;
 }

@@ -101,91 +101,46 @@ __device__ __forceinline__ double add_run_f64(double S, double v, int k)
     return S;
 }
 
-/* ---- per-CNV sums ----------------------------------------------------------- */
-#define WIN_CHUNK 8     /* GC windows a lane advances between refill checks */
-#define RUN_CHUNK 4     /* mappability runs a lane advances between refill checks */
-
-__global__ void __launch_bounds__(128)
-k_cnv_sums(const cg_cnv* __restrict__ cnvs, int n, const int32_t* __restrict__ prefix,
-           const int8_t* __restrict__ gc, const float* __restrict__ expected,
-           const cg_maprun* __restrict__ runs, int n_runs, int has_map, int32_t chrom_len,
-           unsigned int* flags, cg_call* out, int* work_counter)
+/* ---- the common case without any floating-point instruction -----------------
+ * While E sits in the binade with biased exponent e, one rounded addition of v moves
+ * E's bit pattern by d(v, e) = q + (rem > half), where v's 24-bit significand mv is
+ * split at sh = e - exponent(v):  q = mv >> sh, rem = the sh bits shifted out, half =
+ * 2^(sh-1)  (round to nearest; rem == half is the tie, left to add_run_f32).  d does not
+ * depend on E's significand, so a run of k additions is `bits += k*d`, and a whole chunk
+ * of GC windows is a chain of integer multiply-adds.  All d are >= 0, so if the exponent
+ * field is unchanged at the END of the chunk no addition crossed a binade boundary and
+ * every step was exactly the reference's fadd; otherwise the chunk is replayed window by
+ * window through add_run_f32. */
+__device__ __forceinline__ unsigned step_delta_f32(unsigned vb, unsigned e, bool& bad)
 {
-    __shared__ float s_exp[CG_GC_BINS];
-    for (int i = threadIdx.x; i < CG_GC_BINS; i += blockDim.x) s_exp[i] = expected[i];
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
+    if (vb == 0u) return 0u;                         /* + 0.0f changes nothing */
+    const unsigned ev = vb >> 23;                    /* sign bit set -> ev >= 256 */
+    if (ev == 0u || ev >= 255u) { bad = true; return 0u; }
+    const int sh = (int)e - (int)ev;
+    if (sh >= 26) return 0u;                         /* v < ulp/2: absorbed */
+    if (sh < 1) { bad = true; return 0u; }           /* E < 2v: the sum leaves the binade */
+    const unsigned mv = (vb & 0x7fffffu) | 0x800000u;
+    const unsigned rem = mv & ((1u << sh) - 1u), half = 1u << (sh - 1);
+    if (rem == half) bad = true;                     /* exact tie: parity dependent */
+    return (mv >> sh) + (rem > half ? 1u : 0u);
+}
 
-    int c = -1;                 /* CNV this lane is working on */
-    int s = 0, e = 0;           /* clipped interval */
-    int w = 0, w_last = -1;     /* next / last GC window of the fp32 chain */
-    int r = 0;                  /* next mappability run */
-    int phase = 0;              /* 0: expected chain, 1: mappability chain */
-    float E = 0.0f;
-    double M = 0.0;
-    bool more = true;           /* the shared counter may still hold work */
-
-    for (;;) {
-        /* refill idle lanes, one counter bump per warp */
-        const unsigned need = __ballot_sync(FULL, c < 0 && more);
-        if (need) {
-            int first = 0;
-            if (lane == __ffs(need) - 1) first = atomicAdd(work_counter, __popc(need));
-            first = __shfl_sync(FULL, first, __ffs(need) - 1);
-            if (c < 0 && more) {
-                const int mine = first + __popc(need & ((1u << lane) - 1u));
-                if (mine < n) {
-                    c = mine;
-                    const cg_cnv v = cnvs[c];
-                    s = v.start; e = v.end;
-                    if (s < 0 || e > chrom_len) { atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
-                    E = 0.0f; M = 0.0; phase = 0; r = 0;
-                    if (e > s) { w = s / 100; w_last = (e - 1) / 100; } else { w = 0; w_last = -1; }
-                } else more = false;
-            }
-        }
-        if (!__any_sync(FULL, c >= 0)) break;
-        if (c < 0) continue;
-
-        if (phase == 0) {
-            /* likelihood.c:115-119: expected_rd += expected[gc(i)] for i in [s,e), in order */
-#pragma unroll 1
-            for (int j = 0; j < WIN_CHUNK && w <= w_last; j++, w++) {
-                const int k = min(e, 100 * w + 100) - max(s, 100 * w);
-                int bin = (int)__ldg(&gc[w]);
-                if ((unsigned)bin > 100u) bin = 0;
-                E = add_run_f32(E, s_exp[bin], k);
-            }
-            if (w > w_last) {
-                phase = 1;
-                if (has_map && e > s && n_runs > 0) {
-                    /* first run whose end lies beyond s (runs are disjoint and sorted) */
-                    int lo = 0, hi = n_runs;
-                    while (lo < hi) { const int mid = (lo + hi) >> 1; if (runs[mid].end > s) hi = mid; else lo = mid + 1; }
-                    r = lo;
-                } else r = n_runs;
-            }
-        } else {
-            /* likelihood.c:122-123: mappability_score += mappability[i], in order */
-#pragma unroll 1
-            for (int j = 0; j < RUN_CHUNK && r < n_runs; j++, r++) {
-                const cg_maprun q = runs[r];
-                if (q.start >= e) { r = n_runs; break; }
-                const int k = min(e, q.end) - max(s, q.start);
-                M = add_run_f64(M, (double)q.val, k);
-            }
-            if (r >= n_runs) {
-                cg_call* o = &out[c];
-                const cg_cnv v = cnvs[c];
-                int obs = 0;                                   /* likelihood.c:120 */
-                if (e > s) obs = prefix[e - 1] - (s > 0 ? prefix[s - 1] : 0);
-                o->observed = obs;
-                o->expected = E;
-                o->mappability = has_map ? M / (double)(v.end - v.start) : 0.0;   /* likelihood.c:128 */
-                c = -1;
-            }
-        }
-    }
+__device__ __forceinline__ double add_run_f64_fast(double S, double v, int k)
+{
+    if (k <= 0 || v == 0.0) return S;
+    const unsigned long long sb = (unsigned long long)__double_as_longlong(S);
+    const unsigned long long vb = (unsigned long long)__double_as_longlong(v);
+    const unsigned e = (unsigned)(sb >> 52), ev = (unsigned)(vb >> 52);   /* sign set -> >= 2048 */
+    const int sh = (int)e - (int)ev;
+    if (e == 0u || e >= 0x7ffu || ev == 0u || ev >= 0x7ffu || sh < 1) return add_run_f64(S, v, k);
+    if (sh >= 55) return S;
+    const unsigned long long mv = (vb & 0xfffffffffffffull) | 0x10000000000000ull;
+    const unsigned long long rem = mv & ((1ull << sh) - 1ull), half = 1ull << (sh - 1);
+    if (rem == half) return add_run_f64(S, v, k);
+    const unsigned long long d = (mv >> sh) + (rem > half ? 1ull : 0ull);
+    const unsigned long long room = 0xfffffffffffffull - (sb & 0xfffffffffffffull);
+    if (__umul64hi((unsigned long long)k, d) != 0ull || (unsigned long long)k * d > room) return add_run_f64(S, v, k);
+    return __longlong_as_double((long long)(sb + (unsigned long long)k * d));
 }
 
 /* ---- Poisson likelihoods, c-score, copy number ------------------------------ */
@@ -204,61 +159,248 @@ __device__ __forceinline__ bool near_integer(double x)
     return d <= 1e-7 * fmax(1.0, a);
 }
 
-__global__ void __launch_bounds__(128)
-k_cnv_likelihood(cg_call* out, int n, int is_dup)
+
+/* fp64 twin of step_delta_f32: significand increment of one rounded addition of v while the
+ * running sum has biased exponent e. */
+__device__ __forceinline__ unsigned long long step_delta_f64(unsigned long long vb, unsigned e, bool& bad)
 {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31, g = gid & 3, lead = lane & ~3;
-    int c = gid >> 2;
-    const bool live = c < n;
-    if (!live) c = n - 1;
-    const int   obs = out[c].observed;
-    const float E   = out[c].expected;
-
-    double term;
-    if (g == 3) {
-        term = lgamma((double)(obs + 1));                          /* likelihood.c:104 */
-    } else {
-        double lambda;
-        if (g == 2)       lambda = (double)E;                      /* lnone:   :135 / :157 */
-        else if (g == 1)  lambda = (is_dup ? 1.5 : 0.5) * (double)E;   /* lhetero: :134 / :156 */
-        else              lambda = is_dup ? (double)__fmul_rn(2.0f, E) : 0.0;   /* lhomo: :133 / :155 */
-        if (lambda == 0.0) lambda = 0.01;                          /* :100-102 */
-        term = __dsub_rn(__dmul_rn((double)obs, log(lambda)), lambda);
-    }
-    const double lg = __shfl_sync(FULL, term, lead + 3);
-    const double l  = __dsub_rn(term, lg);
-    const double lhomo   = __shfl_sync(FULL, l, lead + 0);
-    const double lhetero = __shfl_sync(FULL, l, lead + 1);
-    const double lnone   = __shfl_sync(FULL, l, lead + 2);
-    if (!live || g != 0) return;
-
-    const int ih = c_double_to_int(lhomo), it = c_double_to_int(lhetero);
-    cg_call* o = &out[c];
-    o->lhomo = lhomo; o->lhetero = lhetero; o->lnone = lnone;
-    o->score = (double)(ih < it ? it : ih) / lnone;                /* :138 / :160 */
-    if (!is_dup) o->copy_number = (__int2float_rn(obs) < __fdiv_rn(E, 4.0f)) ? 2 : 1;   /* :146-149 */
-    else         o->copy_number = (lhomo > lhetero) ? 2 : 1;                           /* :164-167 */
-    unsigned mf = 0;
-    if (near_integer(lhomo) || near_integer(lhetero)) mf |= 1u;
-    if (fabs(lhomo - lhetero) <= 1e-7 * fmax(fabs(lhomo), fabs(lhetero))) mf |= 2u;
-    o->margin_flags = mf;
+    if ((vb << 1) == 0ull) return 0ull;              /* +-0.0 changes nothing */
+    const unsigned ev = (unsigned)(vb >> 52);        /* sign bit set -> ev >= 2048 */
+    if (ev == 0u || ev >= 0x7ffu) { bad = true; return 0ull; }
+    const int sh = (int)e - (int)ev;
+    if (sh >= 55) return 0ull;
+    if (sh < 1) { bad = true; return 0ull; }
+    const unsigned long long mv = (vb & 0xfffffffffffffull) | 0x10000000000000ull;
+    const unsigned long long rem = mv & ((1ull << sh) - 1ull), half = 1ull << (sh - 1);
+    if (rem == half) bad = true;
+    return (mv >> sh) + (rem > half ? 1ull : 0ull);
 }
 
-__global__ void k_reset_counter(int* p) { *p = 0; }
+__device__ __forceinline__ unsigned warp_incl_scan_u32(unsigned v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned o = __shfl_up_sync(FULL, v, d); if (lane >= d) v += o; }
+    return v;
+}
+__device__ __forceinline__ unsigned long long warp_incl_scan_u64(unsigned long long v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned long long o = __shfl_up_sync(FULL, v, d); if (lane >= d) v += o; }
+    return v;
+}
+
+/* four consecutive GC bytes starting at window `idx` (idx is a multiple of 4) */
+__device__ __forceinline__ unsigned load_gc4(const int8_t* __restrict__ gc, int idx, int n_windows)
+{
+    const int8_t* p = gc + idx;
+    if (idx + 3 < n_windows && (reinterpret_cast<uintptr_t>(p) & 3u) == 0u)
+        return __ldg(reinterpret_cast<const unsigned*>(p));
+    unsigned v = 0u;
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (idx + j < n_windows) v |= (unsigned)(unsigned char)__ldg(p + j) << (8 * j);
+    return v;
+}
+
+/* ---- one warp per CNV --------------------------------------------------------
+ * expected_rd: each lane takes 4 consecutive GC windows (one coalesced 32-bit load), turns them
+ * into integer increments under the current exponent, and a warp scan finds how far the chain
+ * runs before anything unusual (binade boundary, tie, E still zero).  Everything before that
+ * point is committed as ONE integer addition to E's bit pattern — bit-identical to the
+ * reference's per-base fadd chain — the offending lane replays its 4 windows through
+ * add_run_f32, and the scan resumes behind it.  mappability_score: the same over 32 runs of
+ * the flattened track per step, in fp64.  The likelihood stage then uses lanes 0..2 for the
+ * three hypotheses and lane 3 for lgamma. */
+#define GENO_WARPS 8
+
+__global__ void __launch_bounds__(GENO_WARPS * 32)
+k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __restrict__ prefix,
+           const int8_t* __restrict__ gc, const float* __restrict__ expected,
+           const cg_maprun* __restrict__ runs, int n_runs, int has_map, int32_t chrom_len,
+           unsigned int* flags, cg_call* out, unsigned int* work_counter, unsigned int work_base, int dynamic)
+{
+    __shared__ unsigned s_expb[CG_GC_BINS];             /* bit patterns of expected_read_depth[] */
+    for (int i = threadIdx.x; i < CG_GC_BINS; i += blockDim.x) s_expb[i] = __float_as_uint(expected[i]);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int n_warps = gridDim.x * GENO_WARPS;
+    const int n_windows = (chrom_len + 99) / 100;
+    int c = blockIdx.x * GENO_WARPS + (threadIdx.x >> 5);
+
+    while (c < n) {
+        const cg_cnv v = cnvs[c];
+        int s = v.start, e = v.end;
+        if (s < 0 || e > chrom_len) { if (lane == 0) atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
+        int pfx = 0;                                    /* lane 0: P[e-1], lane 1: P[s-1] */
+        if (e > s) {
+            if (lane == 0) pfx = __ldg(&prefix[e - 1]);
+            if (lane == 1 && s > 0) pfx = __ldg(&prefix[s - 1]);
+        }
+
+        /* ---- expected_rd (likelihood.c:115-119) ---- */
+        unsigned B = 0u;                                /* bits of the float accumulator, warp-uniform */
+        if (e > s) {
+            const int w_first = s / 100, w_last = (e - 1) / 100;
+            for (int wb = w_first & ~3; wb <= w_last; wb += 128) {
+                const int w4 = wb + 4 * lane;
+                unsigned g4 = 0u;
+                if (w4 <= w_last) g4 = load_gc4(gc, w4, n_windows);
+                unsigned vb[4]; int kk[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int wj = w4 + j;
+                    int bin = (int)(signed char)(g4 >> (8 * j));
+                    if ((unsigned)bin > 100u) bin = 0;
+                    vb[j] = s_expb[bin];
+                    kk[j] = (wj < w_first || wj > w_last) ? 0 : min(e, 100 * wj + 100) - max(s, 100 * wj);
+                }
+                int pos = 0;
+                for (;;) {
+                    const unsigned ee = B >> 23;
+                    bool bad = false;
+                    unsigned t = 0u;
+                    if (lane >= pos) {
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            if (kk[j] > 0) {
+                                const unsigned d = step_delta_f32(vb[j], ee, bad);
+                                t += min((unsigned)kk[j] * d, 0x800000u);
+                            }
+                        }
+                        if (t != 0u || bad) bad = bad || ee == 0u || ee >= 255u;
+                    }
+                    const unsigned incl = warp_incl_scan_u32(t, lane);
+                    const unsigned room = 0x7fffffu - (B & 0x7fffffu);
+                    const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
+                    if (m == 0u) { B += __shfl_sync(FULL, incl, 31); break; }
+                    const int f = __ffs(m) - 1;
+                    B += __shfl_sync(FULL, incl - t, f);            /* everything before lane f, exactly */
+                    unsigned Bf = 0u;
+                    if (lane == f) {
+                        float E = __uint_as_float(B);
+#pragma unroll
+                        for (int j = 0; j < 4; j++) E = add_run_f32(E, __uint_as_float(vb[j]), kk[j]);
+                        Bf = __float_as_uint(E);
+                    }
+                    B = __shfl_sync(FULL, Bf, f);
+                    pos = f + 1;
+                    if (pos >= 32) break;
+                }
+            }
+        }
+
+        /* ---- mappability_score (likelihood.c:122-123) ---- */
+        unsigned long long MB = 0ull;                   /* bits of the double accumulator */
+        if (has_map && e > s && n_runs > 0) {
+            /* first run whose end lies beyond s: 32-ary search, one probe per lane */
+            int lo = 0, hi = n_runs;                    /* answer in [lo, hi] */
+            while (hi - lo > 0) {
+                const int step = (hi - lo + 31) / 32;
+                const int idx = min(lo + (lane + 1) * step - 1, hi - 1);
+                const bool beyond = __ldg(&runs[idx].end) > s;
+                const unsigned bm = __ballot_sync(FULL, beyond);
+                if (bm == 0u) { lo = hi; break; }
+                const int fl = __ffs(bm) - 1;
+                const int nhi = min(lo + (fl + 1) * step - 1, hi - 1);
+                lo = fl == 0 ? lo : min(lo + fl * step, hi - 1);
+                hi = nhi;
+                if (step == 1) { lo = hi; break; }
+            }
+            for (int rb = lo; rb < n_runs; rb += 32) {
+                const int r = rb + lane;
+                cg_maprun q; q.start = 0x7fffffff; q.end = 0x7fffffff; q.val = 0.0f;
+                if (r < n_runs) q = runs[r];
+                const bool past = q.start >= e;
+                const int k = past ? 0 : min(e, q.end) - max(s, q.start);
+                const unsigned long long vbits = (unsigned long long)__double_as_longlong((double)q.val);
+                int pos = 0;
+                for (;;) {
+                    const unsigned ee = (unsigned)(MB >> 52);
+                    bool bad = false;
+                    unsigned long long t = 0ull;
+                    if (lane >= pos && k > 0) {
+                        const unsigned long long d = step_delta_f64(vbits, ee, bad);
+                        t = (__umul64hi((unsigned long long)k, d) != 0ull) ? 0x10000000000000ull
+                                                                          : min((unsigned long long)k * d, 0x10000000000000ull);
+                        if (t != 0ull || bad) bad = bad || ee == 0u || ee >= 0x7ffu;
+                    }
+                    const unsigned long long incl = warp_incl_scan_u64(t, lane);
+                    const unsigned long long room = 0xfffffffffffffull - (MB & 0xfffffffffffffull);
+                    const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
+                    if (m == 0u) { MB += __shfl_sync(FULL, incl, 31); break; }
+                    const int f = __ffs(m) - 1;
+                    MB += __shfl_sync(FULL, incl - t, f);
+                    unsigned long long Mf = 0ull;
+                    if (lane == f) Mf = (unsigned long long)__double_as_longlong(add_run_f64(__longlong_as_double((long long)MB), (double)q.val, k));
+                    MB = __shfl_sync(FULL, Mf, f);
+                    pos = f + 1;
+                    if (pos >= 32) break;
+                }
+                if (__any_sync(FULL, past)) break;
+            }
+        }
+
+        /* ---- observed_rd, likelihoods, c-score, copy number ---- */
+        const int obs = __shfl_sync(FULL, pfx, 0) - __shfl_sync(FULL, pfx, 1);      /* likelihood.c:120 */
+        const float E = __uint_as_float(B);
+        double term = 0.0;
+        if (lane == 3) {
+            term = lgamma((double)(obs + 1));                                      /* likelihood.c:104 */
+        } else if (lane < 3) {
+            double lambda;
+            if (lane == 2)      lambda = (double)E;                                /* lnone:   :135 / :157 */
+            else if (lane == 1) lambda = (is_dup ? 1.5 : 0.5) * (double)E;         /* lhetero: :134 / :156 */
+            else                lambda = is_dup ? (double)__fmul_rn(2.0f, E) : 0.0;   /* lhomo: :133 / :155 */
+            if (lambda == 0.0) lambda = 0.01;                                      /* :100-102 */
+            term = __dsub_rn(__dmul_rn((double)obs, log(lambda)), lambda);
+        }
+        const double lg = __shfl_sync(FULL, term, 3);
+        const double l = __dsub_rn(term, lg);
+        const double lhomo = __shfl_sync(FULL, l, 0), lhetero = __shfl_sync(FULL, l, 1), lnone = __shfl_sync(FULL, l, 2);
+        if (lane == 0) {
+            const int ih = c_double_to_int(lhomo), it = c_double_to_int(lhetero);
+            cg_call o;
+            o.observed = obs;
+            o.expected = E;
+            o.mappability = has_map ? __longlong_as_double((long long)MB) / (double)(v.end - v.start) : 0.0;   /* :128 */
+            o.lhomo = lhomo; o.lhetero = lhetero; o.lnone = lnone;
+            o.score = (double)(ih < it ? it : ih) / lnone;                         /* :138 / :160 */
+            if (!is_dup) o.copy_number = (__int2float_rn(obs) < __fdiv_rn(E, 4.0f)) ? 2 : 1;   /* :146-149 */
+            else         o.copy_number = (lhomo > lhetero) ? 2 : 1;                           /* :164-167 */
+            unsigned mf = 0;
+            if (near_integer(lhomo) || near_integer(lhetero)) mf |= 1u;
+            if (fabs(lhomo - lhetero) <= 1e-7 * fmax(fabs(lhomo), fabs(lhetero))) mf |= 2u;
+            o.margin_flags = mf;
+            out[c] = o;
+        }
+
+        if (!dynamic) break;                            /* n <= warps in the grid: one CNV per warp */
+        unsigned nxt = 0u;
+        if (lane == 0) nxt = atomicAdd(work_counter, 1u) - work_base;
+        c = n_warps + (int)__shfl_sync(FULL, nxt, 0);
+    }
+}
+
+int cgk_genotype_warps(int n, int n_sms)
+{
+    int blocks = (n + GENO_WARPS - 1) / GENO_WARPS;
+    const int cap = n_sms * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return blocks * GENO_WARPS;
+}
 
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
                          const int32_t* prefix, const int8_t* gc, const float* expected,
                          const cg_maprun* runs, int n_runs, int has_map,
-                         int32_t chrom_len, unsigned int* flags, cg_call* out, int* work_counter)
+                         int32_t chrom_len, unsigned int* flags, cg_call* out,
+                         unsigned int* work_counter, unsigned int* work_base, int n_sms)
 {
     if (n <= 0) return cudaSuccess;
-    k_reset_counter<<<1, 1, 0, s>>>(work_counter);
-    int blocks = (n + 127) / 128;
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    k_cnv_sums<<<blocks, 128, 0, s>>>(cnvs, n, prefix, gc, expected, runs, n_runs, has_map,
-                                      chrom_len, flags, out, work_counter);
-    const long long lanes = 4ll * n;
-    k_cnv_likelihood<<<(int)((lanes + 127) / 128), 128, 0, s>>>(out, n, is_dup);
+    const int warps = cgk_genotype_warps(n, n_sms);
+    const int dynamic = n > warps;
+    k_genotype<<<warps / GENO_WARPS, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, prefix, gc, expected, runs, n_runs, has_map,
+                                                             chrom_len, flags, out, work_counter, *work_base, dynamic);
+    /* in dynamic mode every warp draws exactly one index past the end and the n - warps real ones */
+    if (dynamic) *work_base += (unsigned)n;
     return cudaGetLastError();
 }
