@@ -256,17 +256,20 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                 int pos = 0;
                 for (;;) {
                     const unsigned ee = B >> 23;
+                    /* a zero, negative or non-finite accumulator has no binade to replay in:
+                     * any real addend then goes through the literal chain */
+                    const bool acc_odd = ee == 0u || ee >= 255u;
                     bool bad = false;
                     unsigned t = 0u;
                     if (lane >= pos) {
 #pragma unroll
                         for (int j = 0; j < 4; j++) {
-                            if (kk[j] > 0) {
+                            if (kk[j] > 0 && (vb[j] << 1) != 0u) {
+                                if (acc_odd) { bad = true; continue; }
                                 const unsigned d = step_delta_f32(vb[j], ee, bad);
                                 t += min((unsigned)kk[j] * d, 0x800000u);
                             }
                         }
-                        if (t != 0u || bad) bad = bad || ee == 0u || ee >= 255u;
                     }
                     const unsigned incl = warp_incl_scan_u32(t, lane);
                     const unsigned room = 0x7fffffu - (B & 0x7fffffu);
@@ -317,11 +320,14 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                     const unsigned ee = (unsigned)(MB >> 52);
                     bool bad = false;
                     unsigned long long t = 0ull;
-                    if (lane >= pos && k > 0) {
-                        const unsigned long long d = step_delta_f64(vbits, ee, bad);
-                        t = (__umul64hi((unsigned long long)k, d) != 0ull) ? 0x10000000000000ull
-                                                                          : min((unsigned long long)k * d, 0x10000000000000ull);
-                        if (t != 0ull || bad) bad = bad || ee == 0u || ee >= 0x7ffu;
+                    if (lane >= pos && k > 0 && (vbits << 1) != 0ull) {
+                        if (ee == 0u || ee >= 0x7ffu) {
+                            bad = true;                 /* zero / negative / non-finite accumulator */
+                        } else {
+                            const unsigned long long d = step_delta_f64(vbits, ee, bad);
+                            t = (__umul64hi((unsigned long long)k, d) != 0ull) ? 0x10000000000000ull
+                                                                              : min((unsigned long long)k * d, 0x10000000000000ull);
+                        }
                     }
                     const unsigned long long incl = warp_incl_scan_u64(t, lane);
                     const unsigned long long room = 0xfffffffffffffull - (MB & 0xfffffffffffffull);
