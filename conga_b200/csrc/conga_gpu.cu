@@ -38,7 +38,7 @@ struct cg_ctx {
     /* grow-only device buffers */
     cg_read* d_reads = nullptr;       size_t reads_cap = 0;      /* records */
     int8_t* d_gc = nullptr;           size_t gc_cap = 0;
-    int32_t* d_tile_lo = nullptr;     unsigned long long* d_tile_state = nullptr; size_t tiles_cap = 0;
+    int32_t* d_tile_lo = nullptr;     int32_t* d_chunk_cnt = nullptr; uint32_t* d_tile_carry = nullptr; size_t tiles_cap = 0;
     int16_t* d_depth = nullptr;       int32_t* d_prefix = nullptr; uint32_t* d_depth32 = nullptr; size_t pos_cap = 0;
     cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
     cg_cnv* d_cnvs = nullptr;         cg_call* d_calls = nullptr; size_t cnv_cap = 0;
@@ -46,7 +46,7 @@ struct cg_ctx {
 
     long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
     float* d_expected = nullptr;              /* [101] */
-    unsigned int* d_flags = nullptr;          /* [0] CG_FLAG_*  [1] tile counter */
+    unsigned int* d_flags = nullptr;          /* control words CG_W_*: flags, tile counter, done counter */
     unsigned int* d_work = nullptr;      /* monotonic work counter of the genotype kernel */
     unsigned int work_base = 0;
 
@@ -164,7 +164,7 @@ void cg_destroy(cg_ctx* c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
-    cudaFree(c->d_reads); cudaFree(c->d_gc); cudaFree(c->d_tile_lo); cudaFree(c->d_tile_state);
+    cudaFree(c->d_reads); cudaFree(c->d_gc); cudaFree(c->d_tile_lo); cudaFree(c->d_chunk_cnt); cudaFree(c->d_tile_carry);
     cudaFree(c->d_depth); cudaFree(c->d_prefix); cudaFree(c->d_depth32); cudaFree(c->d_runs);
     cudaFree(c->d_cnvs); cudaFree(c->d_calls); cudaFree(c->d_stats); cudaFree(c->d_expected);
     cudaFree(c->d_flags); cudaFree(c->d_work);
@@ -241,9 +241,11 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     const size_t n_pos = (size_t)n_tiles * CG_TILE;
     if ((size_t)n_tiles + 1 > c->tiles_cap) {
         CU(c, cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_tile_lo); cudaFree(c->d_tile_state); c->d_tile_lo = nullptr; c->d_tile_state = nullptr; c->tiles_cap = 0;
+        cudaFree(c->d_tile_lo); cudaFree(c->d_chunk_cnt); cudaFree(c->d_tile_carry);
+        c->d_tile_lo = nullptr; c->d_chunk_cnt = nullptr; c->d_tile_carry = nullptr; c->tiles_cap = 0;
         CU(c, cudaMalloc(&c->d_tile_lo, ((size_t)n_tiles + 1) * sizeof(int32_t)));
-        CU(c, cudaMalloc(&c->d_tile_state, ((size_t)n_tiles + 1) * sizeof(unsigned long long)));
+        CU(c, cudaMalloc(&c->d_chunk_cnt, (size_t)n_tiles * CG_CHUNKS_PER_TILE * sizeof(int32_t)));
+        CU(c, cudaMalloc(&c->d_tile_carry, ((size_t)n_tiles + 1) * sizeof(uint32_t)));
         c->tiles_cap = (size_t)n_tiles + 1;
     }
     if (n_pos > c->pos_cap) {
@@ -253,6 +255,8 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         CU(c, cudaMalloc(&c->d_depth, n_pos * sizeof(int16_t)));
         CU(c, cudaMalloc(&c->d_prefix, n_pos * sizeof(int32_t)));
         CU(c, cudaMalloc(&c->d_depth32, n_pos * sizeof(uint32_t)));
+        /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
+        CU(c, cudaMemsetAsync(c->d_depth32, 0, n_pos * sizeof(uint32_t), c->stream));
         c->pos_cap = n_pos;
     }
     if (c->ptr_mode == CG_PTR_HOST) {
@@ -271,7 +275,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
         prof_scope ps(c, 0, 1);
-        CU(c, cgk_chrom_init(c->stream, c->d_tile_state, n_tiles, c->d_flags + 1,
+        CU(c, cgk_chrom_init(c->stream, c->d_chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
                              c->d_stats + (size_t)chr_index * CG_STATS_WORDS, c->d_flags));
     }
     return CG_OK;
@@ -304,7 +308,9 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     c->n_reads = first + (long long)n;
     {
         prof_scope ps(c, 0, 1);
-        CU(c, cgk_mark_batch(c->stream, c->reads_ptr, first, (long long)n, c->d_tile_lo, c->n_tiles, c->chrom_len, c->d_flags));
+        CU(c, cgk_mark_batch(c->stream, c->reads_ptr, first, (long long)n, c->d_tile_lo, c->d_chunk_cnt, c->n_tiles,
+                             c->chrom_len, c->mq_threshold, c->d_flags,
+                             c->d_stats + (size_t)c->chr_index * CG_STATS_WORDS));
     }
     return CG_OK;
 }
@@ -324,23 +330,20 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     long long* row = c->d_stats + (size_t)c->chr_index * CG_STATS_WORDS;
     {
         prof_scope ps(c, 0, 3);
-        CU(c, cgk_seal_bounds(c->stream, c->reads_ptr, c->n_reads, c->d_tile_lo, c->n_tiles));
-        CU(c, cgk_unsorted_scatter(c->stream, c->reads_ptr, c->n_reads, c->d_depth32,
-                                   (long long)c->n_tiles * CG_TILE, c->chrom_len, c->mq_threshold,
-                                   c->d_flags, row, c->n_sms));
+        CU(c, cgk_rare_paths(c->stream, c->reads_ptr, c->n_reads, c->d_depth32, c->d_chunk_cnt, c->n_tiles,
+                             c->chrom_len, c->mq_threshold, c->d_flags, c->n_sms));
+        CU(c, cgk_tile_scan(c->stream, c->reads_ptr, c->n_reads, c->d_tile_lo, c->d_chunk_cnt, c->d_tile_carry,
+                            c->n_tiles, row));
     }
     {
         prof_scope ps(c, 1, 1);
         cg_pass_args a;
-        a.reads = c->reads_ptr; a.n_reads = c->n_reads; a.tile_lo = c->d_tile_lo; a.gc = c->gc_ptr;
+        a.reads = c->reads_ptr; a.n_reads = c->n_reads; a.tile_lo = c->d_tile_lo; a.chunk_cnt = c->d_chunk_cnt;
+        a.tile_carry = c->d_tile_carry; a.gc = c->gc_ptr;
         a.chrom_len = c->chrom_len; a.n_tiles = c->n_tiles; a.mq_threshold = c->mq_threshold;
-        a.depth = c->d_depth; a.prefix = c->d_prefix; a.tile_state = c->d_tile_state;
-        a.tile_counter = c->d_flags + 1; a.depth32 = c->d_depth32; a.flags = c->d_flags; a.stats = row;
+        a.depth = c->d_depth; a.prefix = c->d_prefix; a.depth32 = c->d_depth32; a.ctl = c->d_flags;
+        a.stats = row; a.expected = c->d_expected;
         CU(c, cgk_depth_pass(c->stream, a, c->n_sms));
-    }
-    {
-        prof_scope ps(c, 3, 1);
-        CU(c, cgk_expected_table(c->stream, row, c->d_expected));
     }
     c->finished = true;
     if (c->ptr_mode == CG_PTR_HOST) {

@@ -9,21 +9,30 @@
  * Data layout in HBM (per context, reused across chromosomes):
  *   reads      cg_read[N]            8 B records, coordinate sorted
  *   tile_lo    int32[n_tiles+1]      first record of every 16384-position tile
+ *   chunk_cnt  int32[n_tiles*8]      sum of the int16 depths of every 2048-position chunk
+ *   tile_carry u32[n_tiles]          prefix in front of every tile (mod 2^32)
  *   depth      int16[n_tiles*16384]  the reference's `short read_depth[]` (wraps mod 2^16)
  *   prefix     int32[n_tiles*16384]  P[i] = sum_{j<=i} depth[j]   (mod 2^32)
- *   tile_state u64[n_tiles]          decoupled look-back: flag<<32 | value
  *   stats      int64[204]            cg_chrom_stats row
+ *
+ * The scan carry never travels between CTAs.  A chunk's depth sum is the number of
+ * passing records that fall in it (every read adds exactly 1) unless a position
+ * collects >= 32768 reads and the int16 wraps; k_mark_batch therefore counts records
+ * per chunk while it checks the pushed batch (the records are read once, 8 B each,
+ * against 6 B per POSITION for the pass), k_rare_paths corrects the count for wrapped
+ * pile-ups, and k_tile_scan turns the counts into per-tile carries.  The pass itself
+ * is then embarrassingly parallel over tiles: no look-back, no spinning.
  *
  * Algorithmic bytes per chromosome: 8·N (records) + 2·L (depth) +
  * 4·L (prefix) + L/100 (GC bytes); the pass is HBM-write bound.
  *
- * Kernel shape: persistent CTAs (3 per SM × 148 SMs), 256 threads, 64 KB of u32
- * bins in shared memory per CTA.  Per tile: warp-aggregated shared-memory
- * histogram of the tile's records -> tile total published for the single-pass
- * look-back -> 8 block-scan iterations that read the bins with conflict-free
- * 16-byte LDS, zero them for the next tile, and write depth (8-byte) and prefix
- * (16-byte) vectors fully coalesced -> per-window sums from prefix differences
- * into 101 shared int64 GC accumulators.
+ * Pass kernel shape: persistent CTAs pulling tiles from a counter, 256 threads,
+ * 32 KB of packed u16 bins in shared memory.  Per tile: warp-aggregated shared
+ * histogram of the tile's records -> barrier -> every warp scans its own 2048
+ * positions in 8 rows (lane = 8 consecutive positions = one 16-byte LDS, which is
+ * also the 16-byte int16 output vector; one warp scan per row; two 16-byte prefix
+ * stores) and zeroes the bins behind it -> barrier -> per-window sums from the
+ * prefixes at window ends into 101 shared int64 GC accumulators.
  */
 #include "cg_internal.h"
 
@@ -31,12 +40,11 @@
 #define TILE CG_TILE
 #define NT   CG_PASS_THREADS
 #define NWARP (NT / 32)
-#define SPAN (NT * 8)                 /* positions per block-scan iteration */
-#define ITERS (TILE / SPAN)
+#define ROWS (CG_CHUNK / 256)         /* rows of 256 positions per warp chunk */
 #define MAXWIN (TILE / 100 + 2)       /* GC windows that can overlap one tile */
 
-static_assert(TILE % SPAN == 0, "tile must be a whole number of scan iterations");
-static_assert((1 << CG_TILE_SHIFT) == TILE, "tile shift");
+static_assert(NWARP == CG_CHUNKS_PER_TILE, "one warp per chunk");
+static_assert((1 << CG_TILE_SHIFT) == TILE && (1 << CG_CHUNK_SHIFT) == CG_CHUNK, "shifts");
 
 __device__ __forceinline__ int sext16(unsigned v) { return (int)(short)(v & 0xffffu); }
 
@@ -50,52 +58,35 @@ __device__ __forceinline__ int warp_incl_scan(int v, int lane)
     return v;
 }
 
-__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p)
-{
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_state(unsigned long long* p, unsigned long long v)
-{
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
-}
 /* streaming stores: depth/prefix are written once and not re-read by this kernel */
-__device__ __forceinline__ void st_cs_v4(int32_t* p, int a, int b, int c, int d)
+__device__ __forceinline__ void st_cs_v4(void* p, unsigned a, unsigned b, unsigned c, unsigned d)
 {
-    asm volatile("st.global.cs.v4.s32 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+    asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-__device__ __forceinline__ void st_cs_v2(int16_t* p, unsigned a, unsigned b)
-{
-    asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(a), "r"(b) : "memory");
-}
-
-#define ST_AGG  1ull
-#define ST_INCL 2ull
 
 /* ------------------------------------------------------------------------- */
-/* chromosome start: clear look-back words, tile counter and the stats row   */
-__global__ void k_chrom_init(unsigned long long* tile_state, int n_tiles, unsigned int* tile_counter,
-                             long long* stats_row, unsigned int* flags)
+/* chromosome start: clear the chunk counts, the stats row and the control words */
+__global__ void k_chrom_init(int4* chunk_cnt4, int n_vec, long long* stats_row, unsigned int* ctl)
 {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    for (int j = i; j < n_tiles; j += gridDim.x * blockDim.x) tile_state[j] = 0ull;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int j = i; j < n_vec; j += gridDim.x * blockDim.x) chunk_cnt4[j] = make_int4(0, 0, 0, 0);
     if (i < CG_STATS_WORDS) stats_row[i] = 0;
-    if (i == 0) { *tile_counter = 0u; *flags = 0u; }
+    if (i < 4) ctl[i] = 0u;
 }
 
-cudaError_t cgk_chrom_init(cudaStream_t s, unsigned long long* tile_state, int n_tiles,
-                           unsigned int* tile_counter, long long* stats_row, unsigned int* flags)
+cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* chunk_cnt, int n_chunks, long long* stats_row, unsigned int* ctl)
 {
-    int blocks = (n_tiles + 255) / 256;
+    const int n_vec = n_chunks / 4;                      /* n_chunks is a multiple of 8 */
+    int blocks = (n_vec + 255) / 256;
     if (blocks < 1) blocks = 1;
     if (blocks > 148) blocks = 148;
-    k_chrom_init<<<blocks, 256, 0, s>>>(tile_state, n_tiles, tile_counter, stats_row, flags);
+    k_chrom_init<<<blocks, 256, 0, s>>>(reinterpret_cast<int4*>(chunk_cnt), n_vec, stats_row, ctl);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
-/* per pushed batch: sortedness check + tile boundaries in one sweep          */
+/* per pushed batch, one sweep over its records: sortedness and range checks,  */
+/* tile boundaries, passing records per chunk, pile-up probe                   */
 __device__ __forceinline__ int tile_of(int pos, int n_tiles)
 {
     int t = pos >> CG_TILE_SHIFT;             /* arithmetic shift: negative pos -> negative tile */
@@ -103,138 +94,264 @@ __device__ __forceinline__ int tile_of(int pos, int n_tiles)
     return t >= n_tiles ? n_tiles - 1 : t;
 }
 
-__global__ void k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n,
-                             int32_t* tile_lo, int n_tiles, int32_t chrom_len, unsigned int* flags)
+__global__ void __launch_bounds__(256)
+k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, int32_t* tile_lo,
+             int32_t* chunk_cnt, int n_tiles, int32_t chrom_len, int mq_threshold,
+             unsigned int* ctl, long long* stats_row)
 {
-    long long stride = (long long)gridDim.x * blockDim.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
     unsigned f = 0;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
-        long long i = first + k;
-        int p = reads[i].pos;
-        int tp = tile_of(p, n_tiles), tq = -1;
-        if (i > 0) {
-            int q = reads[i - 1].pos;
-            if (p < q) f |= CG_FLAG_UNSORTED;
-            tq = tile_of(q, n_tiles);
+    int n_pass = 0;
+    /* whole warps iterate together (k - lane is warp-uniform) so the shuffles below are safe */
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k - lane < n; k += stride) {
+        const bool in = k < n;
+        const long long i = first + k;
+        int p = 0, key = -1 - lane;
+        if (in) {
+            const uint2 r = __ldg(reinterpret_cast<const uint2*>(reads) + i);
+            p = (int)r.x;
+            const int mapq = (int)((r.y >> 16) & 0xffu);
+            const int tp = tile_of(p, n_tiles);
+            int tq = -1;
+            if (i > 0) {
+                const int q = reads[i - 1].pos;
+                if (p < q) f |= CG_FLAG_UNSORTED;
+                tq = tile_of(q, n_tiles);
+            }
+            const bool inside = p >= 0 && p < chrom_len;
+            if (!inside) f |= CG_FLAG_RANGE;
+            for (int t = tq + 1; t <= tp; t++) tile_lo[t] = (int32_t)i;
+            if (mapq > mq_threshold) {                                   /* bam_data.c:205 */
+                n_pass++;                                                /* bam_data.c:214 */
+                if (inside) key = p >> CG_CHUNK_SHIFT;
+            }
+            /* a run of >= 32768 equal positions contains two indices that are multiples of the
+             * probe distance, so the later one sees the earlier one */
+            if ((i & (CG_PILEUP_PROBE - 1)) == 0 && i >= CG_PILEUP_PROBE && reads[i - CG_PILEUP_PROBE].pos == p)
+                f |= CG_FLAG_PILEUP;
         }
-        if (p < 0 || p >= chrom_len) f |= CG_FLAG_RANGE;
-        for (int t = tq + 1; t <= tp; t++) tile_lo[t] = (int32_t)i;
+        /* sorted stream: records of one chunk sit in adjacent lanes -> one atomic per chunk per warp */
+        const int prev = __shfl_up_sync(FULL, key, 1);
+        const bool leader = lane == 0 || key != prev;
+        const unsigned lm = __ballot_sync(FULL, leader);
+        if (leader && key >= 0) {
+            const unsigned above = lane == 31 ? 0u : (lm & ~((2u << lane) - 1u));
+            const int cnt = (above ? __ffs(above) - 1 : 32) - lane;
+            atomicAdd(&chunk_cnt[key], cnt);
+        }
     }
-    if (f) atomicOr(flags, f);
+    if (f) atomicOr(&ctl[CG_W_FLAGS], f);
+    n_pass = __reduce_add_sync(FULL, n_pass);
+    if (lane == 0 && n_pass)
+        atomicAdd((unsigned long long*)&stats_row[2 * CG_GC_BINS + 1], (unsigned long long)n_pass);
 }
 
 cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
-                           int32_t* tile_lo, int n_tiles, int32_t chrom_len, unsigned int* flags)
+                           int32_t* tile_lo, int32_t* chunk_cnt, int n_tiles, int32_t chrom_len,
+                           int mq_threshold, unsigned int* ctl, long long* stats_row)
 {
     if (n <= 0) return cudaSuccess;
     long long blocks = (n + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_mark_batch<<<(int)blocks, 256, 0, s>>>(reads, first, n, tile_lo, n_tiles, chrom_len, flags);
-    return cudaGetLastError();
-}
-
-/* tiles after the last record's tile start at N */
-__global__ void k_seal_bounds(const cg_read* __restrict__ reads, long long n_reads, int32_t* tile_lo, int n_tiles)
-{
-    int last = n_reads > 0 ? tile_of(reads[n_reads - 1].pos, n_tiles) : -1;
-    for (int t = last + 1 + blockIdx.x * blockDim.x + threadIdx.x; t <= n_tiles; t += gridDim.x * blockDim.x)
-        tile_lo[t] = (int32_t)n_reads;
-}
-
-cudaError_t cgk_seal_bounds(cudaStream_t s, const cg_read* reads, long long n_reads, int32_t* tile_lo, int n_tiles)
-{
-    k_seal_bounds<<<8, 256, 0, s>>>(reads, n_reads, tile_lo, n_tiles);
+    k_mark_batch<<<(int)blocks, 256, 0, s>>>(reads, first, n, tile_lo, chunk_cnt, n_tiles, chrom_len,
+                                             mq_threshold, ctl, stats_row);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
-/* out-of-order input: global-atomic histogram into u32 words; both kernels   */
-/* return at once when the batch checks found the stream sorted               */
-__global__ void k_unsorted_zero(uint4* depth32, long long n_vec, const unsigned int* flags)
+/* rare paths; both kernels return at once for a sorted stream without pile-ups */
+
+/* out-of-order input: global-atomic histogram into u32 words (zero at rest: the
+ * pass clears every word it consumes) */
+__global__ void k_rare_scatter(const cg_read* __restrict__ reads, long long n_reads, uint32_t* depth32,
+                               int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
 {
-    if (!(*flags & CG_FLAG_UNSORTED)) return;
-    long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride)
-        depth32[i] = make_uint4(0, 0, 0, 0);
+    if (!(ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED)) return;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_reads; i += stride) {
+        const uint2 r = *reinterpret_cast<const uint2*>(&reads[i]);
+        const int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
+        if (mapq > mq_threshold && pos >= 0 && pos < chrom_len) atomicAdd(&depth32[pos], 1u);
+    }
 }
 
-__global__ void k_unsorted_scatter(const cg_read* __restrict__ reads, long long n_reads, uint32_t* depth32,
-                                   int32_t chrom_len, int mq_threshold, const unsigned int* flags,
-                                   long long* stats_row)
+/* unsorted: chunk sums recomputed from the scattered counts (covers int16 wrap too).
+ * sorted with a pile-up flagged: for every run of equal positions longer than the probe
+ * distance, count its passing records c and replace the chunk's +c by sext16(c). */
+__global__ void __launch_bounds__(256)
+k_rare_totals(const cg_read* __restrict__ reads, long long n_reads, const uint32_t* __restrict__ depth32,
+              int32_t* chunk_cnt, int n_chunks, int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
 {
-    if (!(*flags & CG_FLAG_UNSORTED)) return;
-    long long stride = (long long)gridDim.x * blockDim.x;
-    int pass = 0;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_reads; i += stride) {
-        uint2 r = *reinterpret_cast<const uint2*>(&reads[i]);
-        int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
-        if (mapq > mq_threshold) {
-            pass++;
-            if (pos >= 0 && pos < chrom_len) atomicAdd(&depth32[pos], 1u);
+    const unsigned fl = ctl[CG_W_FLAGS];
+    if (!(fl & (CG_FLAG_UNSORTED | CG_FLAG_PILEUP))) return;
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    if (fl & CG_FLAG_UNSORTED) {
+        for (long long c = warp; c < n_chunks; c += n_warps) {
+            const uint4* src = reinterpret_cast<const uint4*>(depth32 + c * CG_CHUNK);
+            int s = 0;
+            for (int q = lane; q < CG_CHUNK / 4; q += 32) {
+                const uint4 v = src[q];
+                s += sext16(v.x) + sext16(v.y) + sext16(v.z) + sext16(v.w);
+            }
+            s = __reduce_add_sync(FULL, s);
+            if (lane == 0) chunk_cnt[c] = s;
+        }
+        return;
+    }
+    const long long n_groups = (n_reads + 31) >> 5;
+    for (long long g = warp; g < n_groups; g += n_warps) {
+        const long long i = (g << 5) + lane;
+        int p = 0;
+        bool start = false;
+        if (i < n_reads) {
+            p = reads[i].pos;
+            start = (i == 0 || reads[i - 1].pos != p) && i + CG_PILEUP_PROBE < n_reads
+                    && reads[i + CG_PILEUP_PROBE].pos == p;
+        }
+        unsigned m = __ballot_sync(FULL, start);
+        while (m) {
+            const int l = __ffs(m) - 1;
+            m &= m - 1;
+            const long long i0 = __shfl_sync(FULL, i, l);
+            const int p0 = __shfl_sync(FULL, p, l);
+            int c = 0;
+            for (long long j = i0;; j += 32) {
+                const long long jj = j + lane;
+                bool inrun = false;
+                if (jj < n_reads) {
+                    const uint2 r = *reinterpret_cast<const uint2*>(&reads[jj]);
+                    inrun = (int)r.x == p0;
+                    if (inrun && (int)((r.y >> 16) & 0xffu) > mq_threshold) c++;
+                }
+                if (!__all_sync(FULL, inrun)) break;
+            }
+            c = __reduce_add_sync(FULL, c);
+            if (lane == 0 && c >= 32768 && p0 >= 0 && p0 < chrom_len)
+                atomicAdd(&chunk_cnt[p0 >> CG_CHUNK_SHIFT], sext16((unsigned)c) - c);
         }
     }
-    pass = __reduce_add_sync(FULL, pass);
-    if ((threadIdx.x & 31) == 0 && pass)
-        atomicAdd((unsigned long long*)&stats_row[2 * CG_GC_BINS + 1], (unsigned long long)pass);
 }
 
-cudaError_t cgk_unsorted_scatter(cudaStream_t s, const cg_read* reads, long long n_reads,
-                                 uint32_t* depth32, long long n_words, int32_t chrom_len,
-                                 int mq_threshold, const unsigned int* flags, long long* stats_row, int n_sms)
+cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_reads, uint32_t* depth32,
+                           int32_t* chunk_cnt, int n_tiles, int32_t chrom_len, int mq_threshold,
+                           const unsigned int* ctl, int n_sms)
 {
-    k_unsorted_zero<<<n_sms * 4, 256, 0, s>>>(reinterpret_cast<uint4*>(depth32), n_words / 4, flags);
-    k_unsorted_scatter<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chrom_len, mq_threshold, flags, stats_row);
+    k_rare_scatter<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chrom_len, mq_threshold, ctl);
+    k_rare_totals<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
+                                           chrom_len, mq_threshold, ctl);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------------------- */
+/* one CTA: tile bounds behind the last record, per-tile carries, chromosome sum.
+ * |sum of any set of depths| <= number of records < 2^31, so int32 arithmetic is exact. */
+#define SCAN_THREADS 1024
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_tile_scan(const cg_read* __restrict__ reads, long long n_reads, int32_t* tile_lo,
+            const int32_t* __restrict__ chunk_cnt, uint32_t* tile_carry, int n_tiles, long long* stats_row)
+{
+    __shared__ int wsum[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int last = n_reads > 0 ? tile_of(reads[n_reads - 1].pos, n_tiles) : -1;
+    for (int t = last + 1 + tid; t <= n_tiles; t += SCAN_THREADS) tile_lo[t] = (int32_t)n_reads;
+
+    int run = 0;
+    for (int b = 0; b < n_tiles; b += SCAN_THREADS) {
+        const int t = b + tid;
+        int tot = 0;
+        if (t < n_tiles) {
+            const int4 x = __ldg(reinterpret_cast<const int4*>(chunk_cnt) + 2 * t);
+            const int4 y = __ldg(reinterpret_cast<const int4*>(chunk_cnt) + 2 * t + 1);
+            tot = x.x + x.y + x.z + x.w + y.x + y.y + y.z + y.w;
+        }
+        const int incl = warp_incl_scan(tot, lane);
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) wsum[lane] = warp_incl_scan(wsum[lane], lane);
+        __syncthreads();
+        const int woff = warp ? wsum[warp - 1] : 0;
+        if (t < n_tiles) tile_carry[t] = (uint32_t)(run + woff + incl - tot);
+        run += wsum[31];
+        __syncthreads();
+    }
+    if (tid == 0) stats_row[2 * CG_GC_BINS] = (long long)run;          /* calc_mu_per_chr, read_distribution.c:35 */
+}
+
+cudaError_t cgk_tile_scan(cudaStream_t s, const cg_read* reads, long long n_reads, int32_t* tile_lo,
+                          const int32_t* chunk_cnt, uint32_t* tile_carry, int n_tiles, long long* stats_row)
+{
+    k_tile_scan<<<1, SCAN_THREADS, 0, s>>>(reads, n_reads, tile_lo, chunk_cnt, tile_carry, n_tiles, stats_row);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
 /* the fused pass                                                            */
 struct __align__(16) pass_smem {
-    uint4 bins4[TILE / 4];                    /* 64 KB: one u32 count per position of the tile */
-    unsigned long long gc_rd[CG_GC_BINS];     /* per-CTA rd_per_gc (two's complement int64) */
-    unsigned long long gc_cnt[CG_GC_BINS];    /* per-CTA window_per_gc */
+    uint4 bins4[TILE / 8];                    /* 32 KB: eight packed u16 counts per vector */
+    /* per-CTA rd_per_gc / window_per_gc.  32-bit is exact here: a CTA's share of the depth sum is
+     * bounded by the record count (< 2^31) and it sweeps < 2^32 positions; native 32-bit shared
+     * atomics instead of the CAS loop a 64-bit shared add compiles to */
+    int gc_rd[CG_GC_BINS];
+    unsigned gc_cnt[CG_GC_BINS];
     int win_end[MAXWIN];                      /* tile-local inclusive prefix at each window's last position */
-    int wtot[2][NWARP];
-    int tile;
-    int tile_total;
-    unsigned carry;
+    int next_tile;
+    int is_last;
 };
 
-__global__ void __launch_bounds__(NT, 3)
+#define PASS_CTAS_PER_SM 5
+
+/* expected_read_depth[101], read_distribution.c:75-83:
+ *   expected[0] = 0; expected[i] = (float)rd_per_gc[i] / window_per_gc[i]; NaN / Inf -> 0.
+ * long->float and int->float round to nearest like x86's cvtsi2ss, and the quotient is one
+ * IEEE fp32 division. */
+__device__ __forceinline__ float expected_of(long long rd, long long cnt, int i)
+{
+    float e = 0.0f;
+    if (i > 0) {
+        e = __fdiv_rn(__ll2float_rn(rd), __int2float_rn((int)cnt));
+        if (isnan(e) || isinf(e)) e = 0.0f;
+    }
+    return e;
+}
+
+__global__ void __launch_bounds__(NT, PASS_CTAS_PER_SM)
 k_depth_pass(const cg_pass_args a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     pass_smem& sm = *reinterpret_cast<pass_smem*>(smem_raw);
-    unsigned* bins = reinterpret_cast<unsigned*>(sm.bins4);
+    unsigned* bins = reinterpret_cast<unsigned*>(sm.bins4);            /* word = positions 2k (low), 2k+1 (high) */
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool unsorted = (*a.flags & CG_FLAG_UNSORTED) != 0;
+    const bool unsorted = (a.ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED) != 0;
 
-    for (int i = tid; i < TILE / 4; i += NT) sm.bins4[i] = make_uint4(0, 0, 0, 0);
-    for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0ull; sm.gc_cnt[i] = 0ull; }
-    int my_pass = 0;            /* records of this thread that passed the mapq test */
-    long long cta_rd = 0;       /* thread 0: sum of this CTA's tile totals (rd_cnt share) */
+    for (int i = tid; i < TILE / 8; i += NT) sm.bins4[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0; sm.gc_cnt[i] = 0u; }
+    if (tid == 0) sm.next_tile = (int)atomicAdd(&a.ctl[CG_W_TILE], 1u);
+    __syncthreads();
 
     for (;;) {
-        if (tid == 0) { sm.tile = (int)atomicAdd(a.tile_counter, 1u); sm.tile_total = 0; }
-        __syncthreads();
-        const int t = sm.tile;
+        const int t = sm.next_tile;
         if (t >= a.n_tiles) break;
         const int base = t << CG_TILE_SHIFT;
+        /* carry in front of this warp's chunk: tile carry + the chunks before it */
+        const int4 c0 = __ldg(reinterpret_cast<const int4*>(a.chunk_cnt) + 2 * t);
+        const int4 c1 = __ldg(reinterpret_cast<const int4*>(a.chunk_cnt) + 2 * t + 1);
+        const unsigned tile_carry = __ldg(&a.tile_carry[t]);
 
-        /* ---- phase A: the tile's records -> shared-memory histogram ---------- */
-        int contrib = 0;        /* this thread's share of sum(sign-extended int16 depth) */
+        /* ---- phase A: the tile's records -> packed shared-memory histogram ---- */
         if (!unsorted) {
-            const int lo = a.tile_lo[t], hi = a.tile_lo[t + 1];
+            const int lo = __ldg(&a.tile_lo[t]), hi = __ldg(&a.tile_lo[t + 1]);
             for (int i0 = lo + warp * 32; i0 < hi; i0 += NT) {
                 const int i = i0 + lane;
                 const bool in = i < hi;
                 uint2 r = make_uint2(0u, 0u);
                 if (in) r = __ldg(reinterpret_cast<const uint2*>(a.reads) + i);
                 const int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
-                const bool pass = in && mapq > a.mq_threshold;                 /* bam_data.c:205 */
-                my_pass += pass;
                 const unsigned off = (unsigned)(pos - base);
-                const bool ok = pass && off < (unsigned)TILE && pos < a.chrom_len;
+                const bool ok = in && mapq > a.mq_threshold                       /* bam_data.c:205 */
+                                && off < (unsigned)TILE && pos < a.chrom_len;
                 /* warp aggregation: the stream is sorted, so equal positions sit in adjacent lanes */
                 const int key = ok ? (int)off : -1 - lane;
                 const int prev = __shfl_up_sync(FULL, key, 1);
@@ -242,98 +359,77 @@ k_depth_pass(const cg_pass_args a)
                 const unsigned lm = __ballot_sync(FULL, leader);
                 if (ok && leader) {
                     const unsigned above = (lane == 31) ? 0u : (lm & ~((2u << lane) - 1u));
-                    const int cnt = (above ? __ffs(above) - 1 : 32) - lane;
-                    const unsigned old = atomicAdd(&bins[off], (unsigned)cnt);     /* bam_data.c:213 */
-                    contrib += sext16(old + cnt) - sext16(old);
+                    const unsigned cnt = (unsigned)((above ? __ffs(above) - 1 : 32) - lane);
+                    if (off & 1u) {
+                        atomicAdd(&bins[off >> 1], cnt << 16);                    /* bam_data.c:213; carry-out = wrap */
+                    } else {
+                        const unsigned old = atomicAdd(&bins[off >> 1], cnt);
+                        /* the low half wrapped into its neighbour's count: take the carry back out */
+                        if ((old & 0xffffu) + cnt > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
+                    }
                 }
             }
         } else {
-            const uint4* src = reinterpret_cast<const uint4*>(a.depth32 + (size_t)base);
-            for (int q = tid; q < TILE / 4; q += NT) {
-                uint4 v = src[q];
-                sm.bins4[q] = v;
-                contrib += sext16(v.x) + sext16(v.y) + sext16(v.z) + sext16(v.w);
+            uint4* src = reinterpret_cast<uint4*>(a.depth32 + (size_t)base);
+            for (int q = tid; q < TILE / 8; q += NT) {
+                const uint4 x = src[2 * q], y = src[2 * q + 1];
+                sm.bins4[q] = make_uint4((x.x & 0xffffu) | (x.y << 16), (x.z & 0xffffu) | (x.w << 16),
+                                         (y.x & 0xffffu) | (y.y << 16), (y.z & 0xffffu) | (y.w << 16));
+                src[2 * q] = make_uint4(0, 0, 0, 0);                              /* zero at rest */
+                src[2 * q + 1] = make_uint4(0, 0, 0, 0);
             }
         }
-        contrib = __reduce_add_sync(FULL, contrib);
-        if (lane == 0 && contrib) atomicAdd(&sm.tile_total, contrib);
         __syncthreads();
 
-        /* ---- single-pass look-back for the tile's starting prefix ------------ */
-        if (warp == 0) {
-            const unsigned agg = (unsigned)sm.tile_total;
-            unsigned excl = 0;
-            if (t == 0) {
-                if (lane == 0) st_state(&a.tile_state[0], (ST_INCL << 32) | agg);
-            } else {
-                if (lane == 0) st_state(&a.tile_state[t], (ST_AGG << 32) | agg);
-                int idx = t - 1 - lane;
-                for (;;) {
-                    unsigned long long w = (ST_INCL << 32);
-                    if (idx >= 0) {
-                        do { w = ld_state(&a.tile_state[idx]); } while ((w >> 32) == 0ull);
-                    }
-                    const unsigned incl = __ballot_sync(FULL, (w >> 32) == ST_INCL);
-                    unsigned v = (unsigned)w;
-                    if (incl) {
-                        const int first = __ffs(incl) - 1;       /* nearest tile with a full prefix */
-                        if (lane > first) v = 0;
-                        excl += __reduce_add_sync(FULL, v);
-                        break;
-                    }
-                    excl += __reduce_add_sync(FULL, v);
-                    idx -= 32;
-                }
-                if (lane == 0) st_state(&a.tile_state[t], (ST_INCL << 32) | (unsigned)(excl + agg));
-            }
-            if (lane == 0) { sm.carry = excl; cta_rd += (long long)(int)agg; }
-        }
+        /* everyone has read sm.next_tile; fetch the tile after this one while the scan runs */
+        unsigned nxt = 0u;
+        if (tid == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], 1u);
 
-        /* ---- block-scan iterations: bins -> depth + prefix -------------------- */
-        const int w0 = base / 100;                 /* first GC window overlapping the tile */
-        unsigned run = 0;                          /* prefix at the start of this iteration's span */
-        unsigned carry0 = 0;
-#pragma unroll 1
-        for (int it = 0; it < ITERS; it++) {
-            /* warp `warp` owns 256 positions; lane owns quad A (4 positions) and quad B 128 further on */
-            const int sp = it * SPAN + warp * 256;
-            const int qa = (sp >> 2) + lane, qb = qa + 32;
-            const uint4 va = sm.bins4[qa], vb = sm.bins4[qb];
-            sm.bins4[qa] = make_uint4(0, 0, 0, 0);             /* clean bins for the next tile */
-            sm.bins4[qb] = make_uint4(0, 0, 0, 0);
-            const int a0 = sext16(va.x), a1 = sext16(va.y), a2 = sext16(va.z), a3 = sext16(va.w);
-            const int b0 = sext16(vb.x), b1 = sext16(vb.y), b2 = sext16(vb.z), b3 = sext16(vb.w);
-            const int sa = a0 + a1 + a2 + a3, sb = b0 + b1 + b2 + b3;
-            const int ia = warp_incl_scan(sa, lane), ib = warp_incl_scan(sb, lane);
-            const int ta = __shfl_sync(FULL, ia, 31), tb = __shfl_sync(FULL, ib, 31);
-            if (lane == 31) sm.wtot[it & 1][warp] = ta + tb;
-            __syncthreads();
-            if (it == 0) { carry0 = sm.carry; run = carry0; }
-            int woff = 0, btot = 0;
+        /* ---- scan: bins -> depth + prefix, one warp per chunk, 8 rows of 256 positions ---- */
+        const int w0 = base / 100;                     /* first GC window overlapping the tile */
+        {
+            const int cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+            int woff = 0;
 #pragma unroll
-            for (int j = 0; j < NWARP; j++) {
-                const int v = sm.wtot[it & 1][j];
-                btot += v;
-                if (j < warp) woff += v;
+            for (int j = 0; j < 7; j++) woff += (j < warp) ? cc[j] : 0;
+            unsigned run = tile_carry + (unsigned)woff;
+            const int cpos = base + warp * CG_CHUNK + lane * 8;       /* this lane's first position in row 0 */
+            int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
+            int vi = warp * (CG_CHUNK / 8) + lane;                    /* uint4 index into the bins */
+            char* dp = reinterpret_cast<char*>(a.depth) + (size_t)cpos * 2;
+            char* pp = reinterpret_cast<char*>(a.prefix) + (size_t)cpos * 4;
+#pragma unroll 2
+            for (int r = 0; r < ROWS; r++) {
+                const uint4 v = sm.bins4[vi];
+                sm.bins4[vi] = make_uint4(0, 0, 0, 0);                /* clean bins for the next tile */
+                const int s0 = sext16(v.x), s1 = s0 + ((int)v.x >> 16);
+                const int s2 = s1 + sext16(v.y), s3 = s2 + ((int)v.y >> 16);
+                const int s4 = s3 + sext16(v.z), s5 = s4 + ((int)v.z >> 16);
+                const int s6 = s5 + sext16(v.w), s7 = s6 + ((int)v.w >> 16);
+                const int incl = warp_incl_scan(s7, lane);
+                const unsigned b = run + (unsigned)(incl - s7);
+                st_cs_v4(dp, v.x, v.y, v.z, v.w);
+                st_cs_v4(pp, b + s0, b + s1, b + s2, b + s3);
+                st_cs_v4(pp + 16, b + s4, b + s5, b + s6, b + s7);
+                /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
+                if (wm >= 92) {
+                    const int k = 99 - wm;
+                    const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
+                                 : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
+                    sm.win_end[wq - w0] = (int)(b - tile_carry) + sk;
+                }
+                if (r == ROWS - 1 && tid == NT - 1)                   /* the tile's last position closes a partial window */
+                    sm.win_end[(base + TILE - 1) / 100 - w0] = (int)(b - tile_carry) + s7;
+                run += (unsigned)__shfl_sync(FULL, incl, 31);
+                vi += 32; dp += 512; pp += 1024;
+                wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
+                if (wm >= 100) { wm -= 100; wq++; }
             }
-            const int pa0 = (int)run + woff + (ia - sa) + a0, pa1 = pa0 + a1, pa2 = pa1 + a2, pa3 = pa2 + a3;
-            const int pb0 = (int)run + woff + ta + (ib - sb) + b0, pb1 = pb0 + b1, pb2 = pb1 + b2, pb3 = pb2 + b3;
-            const size_t ga = (size_t)base + (size_t)(qa << 2), gb = ga + 128;
-            st_cs_v2(a.depth + ga, (va.x & 0xffffu) | (va.y << 16), (va.z & 0xffffu) | (va.w << 16));
-            st_cs_v2(a.depth + gb, (vb.x & 0xffffu) | (vb.y << 16), (vb.z & 0xffffu) | (vb.w << 16));
-            st_cs_v4(a.prefix + ga, pa0, pa1, pa2, pa3);
-            st_cs_v4(a.prefix + gb, pb0, pb1, pb2, pb3);
-            /* a quad starting at global position == 96 (mod 100) ends a GC window */
-            const unsigned pga = (unsigned)ga, pgb = (unsigned)gb;
-            if (pga % 100u == 96u) sm.win_end[pga / 100u - w0] = pa3 - (int)carry0;
-            if (pgb % 100u == 96u) sm.win_end[pgb / 100u - w0] = pb3 - (int)carry0;
-            if (it == ITERS - 1 && tid == NT - 1)
-                sm.win_end[(unsigned)(base + TILE - 1) / 100u - w0] = pb3 - (int)carry0;
-            run += (unsigned)btot;
         }
+        if (tid == 0) sm.next_tile = (int)nxt;
         __syncthreads();
 
-        /* ---- GC-bin sums from window-end prefixes (read_distribution.c:63-73) -- */
+        /* ---- GC-bin sums from window-end prefixes (read_distribution.c:63-73) ---- */
         {
             const int nwin = (base + TILE - 1) / 100 - w0 + 1;
             const int tile_end = min(base + TILE, a.chrom_len);
@@ -341,29 +437,35 @@ k_depth_pass(const cg_pass_args a)
                 const int w = w0 + tid;
                 const int ws = max(base, 100 * w), we = min(tile_end, 100 * w + 100);
                 if (we > ws) {
-                    int bin = (int)a.gc[w];                       /* sonic_interval.c:263-272 */
+                    int bin = (int)a.gc[w];                           /* sonic_interval.c:263-272 */
                     if ((unsigned)bin > 100u) bin = 0;
                     const int sum = sm.win_end[tid] - (tid ? sm.win_end[tid - 1] : 0);
-                    if (sum) atomicAdd(&sm.gc_rd[bin], (unsigned long long)(long long)sum);
-                    atomicAdd(&sm.gc_cnt[bin], (unsigned long long)(we - ws));
+                    if (sum) atomicAdd(&sm.gc_rd[bin], sum);
+                    atomicAdd(&sm.gc_cnt[bin], (unsigned)(we - ws));
                 }
             }
         }
-        /* the loop-top barrier orders these reads before the next tile's writes */
+        /* win_end is next written after the next tile's first barrier, bins after this loop-top read */
     }
 
-    /* ---- CTA epilogue: flush the per-CTA statistics ---------------------------- */
+    /* ---- CTA epilogue: flush the per-CTA statistics; the last CTA derives the table ---- */
+    __syncthreads();
     for (int b = tid; b < CG_GC_BINS; b += NT) {
-        if (sm.gc_rd[b])  atomicAdd((unsigned long long*)&a.stats[b], sm.gc_rd[b]);
-        if (sm.gc_cnt[b]) atomicAdd((unsigned long long*)&a.stats[CG_GC_BINS + b], sm.gc_cnt[b]);
+        if (sm.gc_rd[b])  atomicAdd((unsigned long long*)&a.stats[b], (unsigned long long)(long long)sm.gc_rd[b]);
+        if (sm.gc_cnt[b]) atomicAdd((unsigned long long*)&a.stats[CG_GC_BINS + b], (unsigned long long)sm.gc_cnt[b]);
     }
-    if (tid == 0 && cta_rd) atomicAdd((unsigned long long*)&a.stats[2 * CG_GC_BINS], (unsigned long long)cta_rd);
-    my_pass = __reduce_add_sync(FULL, my_pass);
-    if (lane == 0 && my_pass)
-        atomicAdd((unsigned long long*)&a.stats[2 * CG_GC_BINS + 1], (unsigned long long)my_pass);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) sm.is_last = atomicAdd(&a.ctl[CG_W_DONE], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (sm.is_last && tid < CG_GC_BINS) {
+        __threadfence();
+        const long long rd = __ldcg(&a.stats[tid]), cnt = __ldcg(&a.stats[CG_GC_BINS + tid]);
+        a.expected[tid] = expected_of(rd, cnt, tid);
+    }
 }
 
-int cgk_depth_pass_ctas_per_sm(void) { return 3; }
+int cgk_depth_pass_ctas_per_sm(void) { return PASS_CTAS_PER_SM; }
 
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
 {
@@ -374,7 +476,7 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    int grid = n_sms * cgk_depth_pass_ctas_per_sm();
+    int grid = n_sms * PASS_CTAS_PER_SM;
     if (grid > a.n_tiles) grid = a.n_tiles;
     if (grid < 1) grid = 1;
     k_depth_pass<<<grid, NT, smem, s>>>(a);
@@ -382,22 +484,11 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
 }
 
 /* ------------------------------------------------------------------------- */
-/* expected_read_depth[101], read_distribution.c:75-83:                       */
-/*   expected[0] = 0; expected[i] = (float)rd_per_gc[i] / window_per_gc[i];    */
-/*   NaN / Inf -> 0.  long->float and int->float round to nearest like x86's   */
-/*   cvtsi2ss, and the quotient is one IEEE fp32 division.                     */
+/* the table alone (cg_set_expected replays, tests) */
 __global__ void k_expected_table(const long long* __restrict__ stats_row, float* expected)
 {
-    int i = threadIdx.x;
-    if (i >= CG_GC_BINS) return;
-    float e = 0.0f;
-    if (i > 0) {
-        const float num = __ll2float_rn(stats_row[i]);
-        const float den = __int2float_rn((int)stats_row[CG_GC_BINS + i]);
-        e = __fdiv_rn(num, den);
-        if (isnan(e) || isinf(e)) e = 0.0f;
-    }
-    expected[i] = e;
+    const int i = threadIdx.x;
+    if (i < CG_GC_BINS) expected[i] = expected_of(stats_row[i], stats_row[CG_GC_BINS + i], i);
 }
 
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected)

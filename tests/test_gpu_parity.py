@@ -135,6 +135,27 @@ def test_int16_wrap_pileup(ctx, oracle):
     assert d[777] == np.int16(70000 - 65536) and d[778] == -32768 and d[40_000] == 0
 
 
+def test_pileup_with_mapq_filter_and_packed_neighbours(ctx, oracle):
+    # pile-ups on even positions (low half of a packed bin word, carry must not leak into the odd
+    # neighbour), across a chunk edge (2047|2048) and a tile edge, half of the records failing mapq
+    rng = np.random.default_rng(9)
+    reads = [(1000, int(q)) for q in rng.choice([10, 30], size=90_000)]          # ~45k pass at mq=20 -> wraps once
+    reads += [(1001, 60)] * 5 + [(999, 60)] * 3
+    reads += [(5000, 60)] * 140_000 + [(5001, 60)] * 7                           # low half overflows twice
+    reads += [(2047, 60)] * 40_000 + [(2048, 60)] * 40_000
+    reads += [(CG_TILE - 1, 60)] * 33_000 + [(CG_TILE, 30)] * 33_000 + [(CG_TILE, 10)] * 33_000
+    reads += [(int(p), 60) for p in rng.integers(0, 40_000, size=3000) if p not in (1001, 5000, 5001)]
+    cnvs = [(0, 1500), (900, 2500), (2047, 3047), (2048, 5001), (4000, 6000), (CG_TILE - 500, CG_TILE + 500), (0, 40_000)]
+    ch = tiny_chrom(40_000, sorted(reads), dels=sorted(cnvs), dups=sorted(cnvs))
+    for mq, batch in ((20, 1 << 22), (-1, 77_777), (20, 16_384)):
+        check_chromosome_against_oracle(ctx, oracle, ch, mq=mq, batch=batch)
+    d = ctx.download_depth()
+    assert d[5000] == np.int16(140_000 - 131_072) and d[5001] == 7 and d[1001] == 5
+    # the same records out of order: the global-atomic path must wrap the same way
+    ch.reads = np.ascontiguousarray(ch.reads[rng.permutation(len(ch.reads))])
+    check_chromosome_against_oracle(ctx, oracle, ch, mq=20, batch=100_000)
+
+
 def test_multi_batch_equals_single_batch(ctx, oracle):
     wl = synth.config1(length=2_000_000)
     ch = wl.chroms[0]
