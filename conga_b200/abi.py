@@ -43,6 +43,8 @@ SYMBOLS = {
     "cg_destroy": (None, [_P]),
     "cg_last_error": (C.c_char_p, [_P]),
     "cg_set_pointer_mode": (_I, [_P, _I]),
+    "cg_set_async": (_I, [_P, _I]),
+    "cg_join": (_I, [_P]),
     "cg_alloc_pinned": (_P, [_P, _Z]),
     "cg_free_pinned": (None, [_P, _P]),
     "cg_chrom_begin": (_I, [_P, _I, C.c_int32, _P, C.c_int32, _I]),
@@ -151,6 +153,13 @@ class Context:
     def set_pointer_mode(self, mode: int):
         self._ck(self.lib.cg_set_pointer_mode(self.h, mode))
         self.mode = mode
+
+    def set_async(self, on: bool):
+        self._ck(self.lib.cg_set_async(self.h, int(on)))
+        self.is_async = bool(on)
+
+    def join(self):
+        self._ck(self.lib.cg_join(self.h))
 
     def sync(self):
         self._ck(self.lib.cg_sync(self.h))

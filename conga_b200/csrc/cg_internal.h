@@ -42,10 +42,15 @@ struct cg_pass_args {
     unsigned int*  ctl;               /* CG_W_* control words */
     long long*     stats;             /* this chromosome's int64[204] row */
     float*         expected;          /* [101] written by the last CTA to finish */
+    unsigned int*  sticky;            /* context-wide word: CG_FLAG_RANGE is copied here */
 };
 
 #ifdef __cplusplus
+#include <vector>
 extern "C++" {
+/* conga_gpu.cu / flatten.cu */
+int  cg_fail(cg_ctx* c, int code, const char* fmt, ...);
+void cg_flatten_rows(const cg_mapiv* rows, size_t n, int32_t chrom_len, std::vector<cg_maprun>& out);
 /* depth_pass.cu */
 cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* chunk_cnt, int n_chunks, long long* stats_row, unsigned int* ctl);
 cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,

@@ -1,7 +1,19 @@
 /* conga_gpu.cu — context management and the C-ABI of libconga_gpu.so
  * (include/conga_gpu.h).  Host code only; the kernels live in depth_pass.cu and
  * genotype.cu.  There is no CPU implementation of any stage in this library:
- * without a CUDA device cg_create fails and nothing else can be called. */
+ * without a CUDA device cg_create fails and nothing else can be called.
+ *
+ * Execution model.  A context owns three streams and two chromosome slots:
+ *   s_copy  host->device copies of GC bytes and read batches (HOST pointer mode)
+ *   s_depth chromosome init, batch marking, tile scan, the fused depth pass
+ *   s_geno  mappability / CNV uploads, the genotype kernel, result downloads
+ * Chromosome k lives in slot k&1 (its own depth, prefix, GC, expected-table,
+ * control-word and staging buffers), so the latency-bound genotype kernel of
+ * chromosome k runs underneath the bandwidth-bound depth pass of chromosome k+1
+ * and the copies of k+1 run underneath the pass of k.  Events order the three
+ * streams per slot; nothing ever waits on the host unless the caller asked for
+ * blocking HOST-mode semantics.
+ */
 #include "cg_internal.h"
 
 #include <algorithm>
@@ -9,45 +21,62 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <queue>
 #include <vector>
 
 #define CG_MAX_CHROMS 4096            /* rows of the statistics table */
-
+#define CG_NSLOT 2
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
+
+/* everything one chromosome needs from cg_chrom_begin to its last cg_genotype */
+struct cg_slot {
+    /* geometry */
+    int chr_index = -1;
+    int32_t chrom_len = 0;
+    int n_tiles = 0;
+    /* depth side */
+    cg_read* d_reads = nullptr;       size_t reads_cap = 0;
+    int8_t* d_gc = nullptr;           size_t gc_cap = 0;
+    int32_t* d_tile_lo = nullptr;     int32_t* d_chunk_cnt = nullptr; uint32_t* d_tile_carry = nullptr; size_t tiles_cap = 0;
+    int16_t* d_depth = nullptr;       int32_t* d_prefix = nullptr; size_t pos_cap = 0;
+    float* d_expected = nullptr;              /* [101] (128 allocated) */
+    unsigned int* d_ctl = nullptr;            /* CG_W_* control words */
+    const cg_read* reads_ptr = nullptr;       /* own buffer or the caller's (DEVICE mode) */
+    const int8_t* gc_ptr = nullptr;
+    /* genotype side */
+    cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
+    const cg_maprun* runs_ptr = nullptr; int n_runs = 0; int has_map = 0;
+    char* d_arena = nullptr;          size_t arena_cap = 0, arena_used = 0;   /* CNV + call staging, HOST mode */
+    /* ordering */
+    cudaEvent_t ev_copy = nullptr;            /* s_copy: last upload for this slot */
+    cudaEvent_t ev_pass = nullptr;            /* s_depth: the pass (and the table) of this slot is done */
+    cudaEvent_t ev_geno = nullptr;            /* s_geno: last genotype work queued for this slot */
+    bool used = false, geno_queued = false;
+};
 
 struct cg_ctx {
     int device = 0;
     int n_sms = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t s_copy = nullptr, s_depth = nullptr, s_geno = nullptr;
+    cudaEvent_t ev_join = nullptr;
     int ptr_mode = CG_PTR_HOST;
+    bool async = false;
     char err[512] = {0};
+
+    cg_slot slot[CG_NSLOT];
+    int cur = 0;                              /* slot of the current chromosome */
+    long long n_begun = 0;
 
     /* current chromosome */
     bool in_chrom = false, finished = false;
-    int chr_index = -1;
-    int32_t chrom_len = 0;
-    int n_tiles = 0;
     int mq_threshold = -1;
     long long n_reads = 0;
-    const cg_read* reads_ptr = nullptr;       /* device: own buffer or the caller's (DEVICE mode) */
-    const int8_t* gc_ptr = nullptr;
     int n_rows = 0;
 
-    /* grow-only device buffers */
-    cg_read* d_reads = nullptr;       size_t reads_cap = 0;      /* records */
-    int8_t* d_gc = nullptr;           size_t gc_cap = 0;
-    int32_t* d_tile_lo = nullptr;     int32_t* d_chunk_cnt = nullptr; uint32_t* d_tile_carry = nullptr; size_t tiles_cap = 0;
-    int16_t* d_depth = nullptr;       int32_t* d_prefix = nullptr; uint32_t* d_depth32 = nullptr; size_t pos_cap = 0;
-    cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
-    cg_cnv* d_cnvs = nullptr;         cg_call* d_calls = nullptr; size_t cnv_cap = 0;
-    const cg_maprun* runs_ptr = nullptr; int n_runs = 0; int has_map = 0;
-
+    uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;    /* out-of-order path only; zero at rest */
     long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
-    float* d_expected = nullptr;              /* [101] */
-    unsigned int* d_flags = nullptr;          /* control words CG_W_*: flags, tile counter, done counter */
-    unsigned int* d_work = nullptr;      /* monotonic work counter of the genotype kernel */
+    unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
+    unsigned int* d_work = nullptr;           /* monotonic work counter of the genotype kernel */
     unsigned int work_base = 0;
 
     /* pinned staging */
@@ -64,7 +93,7 @@ struct cg_ctx {
 
 static char g_err[512] = "no error";
 
-static int fail(cg_ctx* c, int code, const char* fmt, ...)
+int cg_fail(cg_ctx* c, int code, const char* fmt, ...)
 {
     char* dst = c ? c->err : g_err;
     va_list ap; va_start(ap, fmt);
@@ -73,36 +102,51 @@ static int fail(cg_ctx* c, int code, const char* fmt, ...)
     if (c) memcpy(g_err, c->err, 512);
     return code;
 }
+#define fail cg_fail
 
 #define CU(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
     return fail((c), e_ == cudaErrorMemoryAllocation ? CG_ENOMEM : CG_ECUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
 
+static inline bool blocking(const cg_ctx* c) { return c->ptr_mode == CG_PTR_HOST && !c->async; }
+
+static int sync_all(cg_ctx* c)
+{
+    CU(c, cudaStreamSynchronize(c->s_copy));
+    CU(c, cudaStreamSynchronize(c->s_depth));
+    CU(c, cudaStreamSynchronize(c->s_geno));
+    return CG_OK;
+}
+
+/* Replace a device buffer by a larger one.  Everything queued is drained first (the old
+ * buffer may still be read by any stream); growth is rare and amortised. */
 template <typename T>
 static int grow(cg_ctx* c, T** p, size_t* cap, size_t need, size_t keep_elems = 0)
 {
     if (need <= *cap) return CG_OK;
-    size_t ncap = std::max(need, *cap + *cap / 2);
+    const size_t ncap = std::max(need, *cap + *cap / 2);
+    int rc = sync_all(c);
+    if (rc) return rc;
     T* np = nullptr;
     CU(c, cudaMalloc(&np, ncap * sizeof(T)));
-    if (keep_elems && *p) CU(c, cudaMemcpyAsync(np, *p, keep_elems * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
-    if (*p) { CU(c, cudaStreamSynchronize(c->stream)); cudaFree(*p); }
+    if (keep_elems && *p) CU(c, cudaMemcpy(np, *p, keep_elems * sizeof(T), cudaMemcpyDeviceToDevice));
+    if (*p) cudaFree(*p);
     *p = np; *cap = ncap;
     return CG_OK;
 }
 
 /* profiling brackets */
 struct prof_scope {
-    cg_ctx* c; cg_evpair ev; bool on; int n;
-    prof_scope(cg_ctx* c_, int slot, int n_launches) : c(c_), on(c_->profiling), n(n_launches) {
+    cg_ctx* c; cudaStream_t s; cg_evpair ev; bool on;
+    prof_scope(cg_ctx* c_, cudaStream_t s_, int slot, int n_launches) : c(c_), s(s_), on(c_->profiling) {
         c->launch_count += n_launches;
         if (!on) return;
         if (!c->ev_free.empty()) { ev = c->ev_free.back(); c->ev_free.pop_back(); }
         else { cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); }
         ev.slot = slot;
         c->launches_acc[slot] += n_launches;
-        cudaEventRecord(ev.a, c->stream);
+        cudaEventRecord(ev.a, s);
     }
-    ~prof_scope() { if (on) { cudaEventRecord(ev.b, c->stream); c->ev_live.push_back(ev); } }
+    ~prof_scope() { if (on) { cudaEventRecord(ev.b, s); c->ev_live.push_back(ev); } }
 };
 
 static void prof_collect(cg_ctx* c)
@@ -113,6 +157,19 @@ static void prof_collect(cg_ctx* c)
         c->ev_free.push_back(ev);
     }
     c->ev_live.clear();
+}
+
+/* CG_FLAG_RANGE raised on the device since the last report -> CG_ERANGE (caller has synchronised) */
+static int report_sticky(cg_ctx* c, const char* what)
+{
+    CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_geno));
+    CU(c, cudaStreamSynchronize(c->s_geno));
+    if (c->h_flags[0] & CG_FLAG_RANGE) {
+        CU(c, cudaMemsetAsync(c->d_sticky, 0, 4, c->s_geno));
+        CU(c, cudaStreamSynchronize(c->s_geno));
+        return fail(c, CG_ERANGE, "%s: a record or interval lies outside [0, chrom_len); it was clipped", what);
+    }
+    return CG_OK;
 }
 
 extern "C" {
@@ -137,17 +194,31 @@ cg_ctx* cg_create(int device)
     cg_ctx* c = new cg_ctx();
     c->device = device;
     c->n_sms = prop.multiProcessorCount;
-    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
+    bool ok = cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        && cudaStreamCreateWithPriority(&c->s_depth, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        /* the genotype kernel is small and latency-bound: let its CTAs be placed first */
+        && cudaStreamCreateWithPriority(&c->s_geno, cudaStreamNonBlocking, prio_hi) == cudaSuccess
+        && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
         && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
         && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
-        && cudaMalloc(&c->d_expected, sizeof(float) * 128) == cudaSuccess
-        && cudaMemset(c->d_expected, 0, sizeof(float) * 128) == cudaSuccess
-        && cudaMalloc(&c->d_flags, 16) == cudaSuccess
-        && cudaMemset(c->d_flags, 0, 16) == cudaSuccess
+        && cudaMalloc(&c->d_sticky, 16) == cudaSuccess
+        && cudaMemset(c->d_sticky, 0, 16) == cudaSuccess
         && cudaMalloc(&c->d_work, 16) == cudaSuccess
         && cudaMemset(c->d_work, 0, 16) == cudaSuccess
         && cudaMallocHost(&c->h_stats, sizeof(cg_chrom_stats)) == cudaSuccess
         && cudaMallocHost(&c->h_flags, 16) == cudaSuccess;
+    for (int i = 0; ok && i < CG_NSLOT; i++) {
+        cg_slot& s = c->slot[i];
+        ok = cudaMalloc(&s.d_expected, sizeof(float) * 128) == cudaSuccess
+            && cudaMemset(s.d_expected, 0, sizeof(float) * 128) == cudaSuccess
+            && cudaMalloc(&s.d_ctl, 16) == cudaSuccess
+            && cudaMemset(s.d_ctl, 0, 16) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_copy, cudaEventDisableTiming) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_pass, cudaEventDisableTiming) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_geno, cudaEventDisableTiming) == cudaSuccess;
+    }
     if (!ok) {
         fail(nullptr, CG_ECUDA, "context allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
         cg_destroy(c);
@@ -161,16 +232,27 @@ void cg_destroy(cg_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->s_copy) cudaStreamSynchronize(c->s_copy);
+    if (c->s_depth) cudaStreamSynchronize(c->s_depth);
+    if (c->s_geno) cudaStreamSynchronize(c->s_geno);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
-    cudaFree(c->d_reads); cudaFree(c->d_gc); cudaFree(c->d_tile_lo); cudaFree(c->d_chunk_cnt); cudaFree(c->d_tile_carry);
-    cudaFree(c->d_depth); cudaFree(c->d_prefix); cudaFree(c->d_depth32); cudaFree(c->d_runs);
-    cudaFree(c->d_cnvs); cudaFree(c->d_calls); cudaFree(c->d_stats); cudaFree(c->d_expected);
-    cudaFree(c->d_flags); cudaFree(c->d_work);
+    for (int i = 0; i < CG_NSLOT; i++) {
+        cg_slot& s = c->slot[i];
+        cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_tile_lo); cudaFree(s.d_chunk_cnt); cudaFree(s.d_tile_carry);
+        cudaFree(s.d_depth); cudaFree(s.d_prefix); cudaFree(s.d_expected); cudaFree(s.d_ctl);
+        cudaFree(s.d_runs); cudaFree(s.d_arena);
+        if (s.ev_copy) cudaEventDestroy(s.ev_copy);
+        if (s.ev_pass) cudaEventDestroy(s.ev_pass);
+        if (s.ev_geno) cudaEventDestroy(s.ev_geno);
+    }
+    cudaFree(c->d_depth32); cudaFree(c->d_stats); cudaFree(c->d_sticky); cudaFree(c->d_work);
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    if (c->s_depth) cudaStreamDestroy(c->s_depth);
+    if (c->s_geno) cudaStreamDestroy(c->s_geno);
     delete c;
 }
 
@@ -179,6 +261,13 @@ int cg_set_pointer_mode(cg_ctx* c, int mode)
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (mode != CG_PTR_HOST && mode != CG_PTR_DEVICE) return fail(c, CG_EINVAL, "bad pointer mode %d", mode);
     c->ptr_mode = mode;
+    return CG_OK;
+}
+
+int cg_set_async(cg_ctx* c, int on)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    c->async = on != 0;
     return CG_OK;
 }
 
@@ -193,14 +282,29 @@ void* cg_alloc_pinned(cg_ctx* c, size_t bytes)
 
 void cg_free_pinned(cg_ctx* c, void* p) { (void)c; if (p) cudaFreeHost(p); }
 
-void* cg_stream(cg_ctx* c) { return c ? (void*)c->stream : nullptr; }
+void* cg_stream(cg_ctx* c) { return c ? (void*)c->s_depth : nullptr; }
 int64_t cg_launch_count(cg_ctx* c) { return c ? c->launch_count : 0; }
+
+/* make the depth stream (cg_stream) wait for everything queued on the other two */
+int cg_join(cg_ctx* c)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaEventRecord(c->ev_join, c->s_geno));
+    CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
+    CU(c, cudaEventRecord(c->ev_join, c->s_copy));
+    CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
+    return CG_OK;
+}
 
 int cg_sync(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaSetDevice(c->device));
+    int rc = sync_all(c);
+    if (rc) return rc;
     prof_collect(c);
+    if (c->ptr_mode == CG_PTR_HOST) return report_sticky(c, "cg_sync");
     return CG_OK;
 }
 
@@ -214,7 +318,8 @@ int cg_set_profiling(cg_ctx* c, int on)
 int cg_kernel_times(cg_ctx* c, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS])
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    CU(c, cudaStreamSynchronize(c->stream));
+    int rc = sync_all(c);
+    if (rc) return rc;
     prof_collect(c);
     for (int i = 0; i < CG_NSLOTS; i++) {
         if (ms) ms[i] = c->ms_acc[i];
@@ -237,46 +342,69 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         return fail(c, CG_EINVAL, "gc_profile needs >= %d windows for length %d (got %d)", need_windows, chrom_len, n_windows);
     CU(c, cudaSetDevice(c->device));
 
+    const int si = (int)(c->n_begun & 1);
+    cg_slot& s = c->slot[si];
     const int n_tiles = (chrom_len + CG_TILE - 1) / CG_TILE;
     const size_t n_pos = (size_t)n_tiles * CG_TILE;
-    if ((size_t)n_tiles + 1 > c->tiles_cap) {
-        CU(c, cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_tile_lo); cudaFree(c->d_chunk_cnt); cudaFree(c->d_tile_carry);
-        c->d_tile_lo = nullptr; c->d_chunk_cnt = nullptr; c->d_tile_carry = nullptr; c->tiles_cap = 0;
-        CU(c, cudaMalloc(&c->d_tile_lo, ((size_t)n_tiles + 1) * sizeof(int32_t)));
-        CU(c, cudaMalloc(&c->d_chunk_cnt, (size_t)n_tiles * CG_CHUNKS_PER_TILE * sizeof(int32_t)));
-        CU(c, cudaMalloc(&c->d_tile_carry, ((size_t)n_tiles + 1) * sizeof(uint32_t)));
-        c->tiles_cap = (size_t)n_tiles + 1;
+    if ((size_t)n_tiles + 1 > s.tiles_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_tile_lo); cudaFree(s.d_chunk_cnt); cudaFree(s.d_tile_carry);
+        s.d_tile_lo = nullptr; s.d_chunk_cnt = nullptr; s.d_tile_carry = nullptr; s.tiles_cap = 0;
+        CU(c, cudaMalloc(&s.d_tile_lo, ((size_t)n_tiles + 1) * sizeof(int32_t)));
+        CU(c, cudaMalloc(&s.d_chunk_cnt, (size_t)n_tiles * CG_CHUNKS_PER_TILE * sizeof(int32_t)));
+        CU(c, cudaMalloc(&s.d_tile_carry, ((size_t)n_tiles + 1) * sizeof(uint32_t)));
+        s.tiles_cap = (size_t)n_tiles + 1;
     }
-    if (n_pos > c->pos_cap) {
-        CU(c, cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_depth); cudaFree(c->d_prefix); cudaFree(c->d_depth32);
-        c->d_depth = nullptr; c->d_prefix = nullptr; c->d_depth32 = nullptr; c->pos_cap = 0;
-        CU(c, cudaMalloc(&c->d_depth, n_pos * sizeof(int16_t)));
-        CU(c, cudaMalloc(&c->d_prefix, n_pos * sizeof(int32_t)));
+    if (n_pos > s.pos_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_depth); cudaFree(s.d_prefix);
+        s.d_depth = nullptr; s.d_prefix = nullptr; s.pos_cap = 0;
+        CU(c, cudaMalloc(&s.d_depth, n_pos * sizeof(int16_t)));
+        CU(c, cudaMalloc(&s.d_prefix, n_pos * sizeof(int32_t)));
+        s.pos_cap = n_pos;
+    }
+    if (n_pos > c->depth32_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(c->d_depth32); c->d_depth32 = nullptr; c->depth32_cap = 0;
         CU(c, cudaMalloc(&c->d_depth32, n_pos * sizeof(uint32_t)));
         /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
-        CU(c, cudaMemsetAsync(c->d_depth32, 0, n_pos * sizeof(uint32_t), c->stream));
-        c->pos_cap = n_pos;
+        CU(c, cudaMemsetAsync(c->d_depth32, 0, n_pos * sizeof(uint32_t), c->s_depth));
+        c->depth32_cap = n_pos;
     }
     if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &c->d_gc, &c->gc_cap, (size_t)need_windows);
+        int rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows);
         if (rc) return rc;
-        CU(c, cudaMemcpyAsync(c->d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->stream));
-        c->gc_ptr = c->d_gc;
-    } else {
-        c->gc_ptr = gc_profile;
     }
-    c->chr_index = chr_index; c->chrom_len = chrom_len; c->n_tiles = n_tiles;
+    /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
+    if (s.used) CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_pass, 0));            /* d_reads */
+    if (s.geno_queued) {
+        CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno, 0));                     /* d_gc */
+        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_geno, 0));                    /* d_prefix, d_expected */
+    }
+    if (c->ptr_mode == CG_PTR_HOST) {
+        CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy));
+        CU(c, cudaEventRecord(s.ev_copy, c->s_copy));
+        s.gc_ptr = s.d_gc;
+    } else {
+        s.gc_ptr = gc_profile;
+    }
+    s.chr_index = chr_index; s.chrom_len = chrom_len; s.n_tiles = n_tiles;
+    s.reads_ptr = s.d_reads;
+    s.n_runs = 0; s.has_map = 0; s.runs_ptr = nullptr;
+    s.arena_used = 0;
+    s.used = true; s.geno_queued = false;
+    c->cur = si; c->n_begun++;
     c->mq_threshold = mq_threshold;
-    c->n_reads = 0; c->reads_ptr = c->d_reads;
+    c->n_reads = 0;
     c->in_chrom = true; c->finished = false;
-    c->n_runs = 0; c->has_map = 0; c->runs_ptr = nullptr;
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
-        prof_scope ps(c, 0, 1);
-        CU(c, cgk_chrom_init(c->stream, c->d_chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
-                             c->d_stats + (size_t)chr_index * CG_STATS_WORDS, c->d_flags));
+        prof_scope ps(c, c->s_depth, 0, 1);
+        CU(c, cgk_chrom_init(c->s_depth, s.d_chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
+                             c->d_stats + (size_t)chr_index * CG_STATS_WORDS, s.d_ctl));
     }
     return CG_OK;
 }
@@ -289,36 +417,32 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     if (!reads) return fail(c, CG_EINVAL, "null reads");
     if ((unsigned long long)c->n_reads + n >= 0x7fffffffull) return fail(c, CG_EINVAL, "more than 2^31-1 records on one chromosome");
     CU(c, cudaSetDevice(c->device));
+    cg_slot& s = c->slot[c->cur];
     const long long first = c->n_reads;
     if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &c->d_reads, &c->reads_cap, (size_t)first + n, (size_t)first);
+        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, (size_t)first);
         if (rc) return rc;
-        CU(c, cudaMemcpyAsync(c->d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->stream));
-        c->reads_ptr = c->d_reads;
+        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy));
+        CU(c, cudaEventRecord(s.ev_copy, c->s_copy));
+        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_copy, 0));
+        s.reads_ptr = s.d_reads;
     } else if (first == 0) {
-        c->reads_ptr = reads;                 /* single device batch: used in place */
+        s.reads_ptr = reads;                  /* single device batch: used in place */
     } else {
-        const bool external = c->reads_ptr != c->d_reads;
-        int rc = grow(c, &c->d_reads, &c->reads_cap, (size_t)first + n, external ? 0 : (size_t)first);
+        const bool external = s.reads_ptr != s.d_reads;
+        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, external ? 0 : (size_t)first);
         if (rc) return rc;
-        if (external) CU(c, cudaMemcpyAsync(c->d_reads, c->reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->stream));
-        CU(c, cudaMemcpyAsync(c->d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->stream));
-        c->reads_ptr = c->d_reads;
+        if (external) CU(c, cudaMemcpyAsync(s.d_reads, s.reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_depth));
+        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_depth));
+        s.reads_ptr = s.d_reads;
     }
     c->n_reads = first + (long long)n;
     {
-        prof_scope ps(c, 0, 1);
-        CU(c, cgk_mark_batch(c->stream, c->reads_ptr, first, (long long)n, c->d_tile_lo, c->d_chunk_cnt, c->n_tiles,
-                             c->chrom_len, c->mq_threshold, c->d_flags,
-                             c->d_stats + (size_t)c->chr_index * CG_STATS_WORDS));
+        prof_scope ps(c, c->s_depth, 0, 1);
+        CU(c, cgk_mark_batch(c->s_depth, s.reads_ptr, first, (long long)n, s.d_tile_lo, s.d_chunk_cnt, s.n_tiles,
+                             s.chrom_len, c->mq_threshold, s.d_ctl,
+                             c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS));
     }
-    return CG_OK;
-}
-
-static int check_flags_host(cg_ctx* c, const char* what)
-{
-    const unsigned f = c->h_flags[0];
-    if (f & CG_FLAG_RANGE) return fail(c, CG_ERANGE, "%s: a record or interval lies outside [0, %d); it was clipped", what, c->chrom_len);
     return CG_OK;
 }
 
@@ -327,34 +451,40 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (!c->in_chrom || c->finished) return fail(c, CG_EINVAL, "cg_chrom_finish without cg_chrom_begin");
     CU(c, cudaSetDevice(c->device));
-    long long* row = c->d_stats + (size_t)c->chr_index * CG_STATS_WORDS;
+    cg_slot& s = c->slot[c->cur];
+    long long* row = c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS;
+    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_copy, 0));   /* GC bytes */
     {
-        prof_scope ps(c, 0, 3);
-        CU(c, cgk_rare_paths(c->stream, c->reads_ptr, c->n_reads, c->d_depth32, c->d_chunk_cnt, c->n_tiles,
-                             c->chrom_len, c->mq_threshold, c->d_flags, c->n_sms));
-        CU(c, cgk_tile_scan(c->stream, c->reads_ptr, c->n_reads, c->d_tile_lo, c->d_chunk_cnt, c->d_tile_carry,
-                            c->n_tiles, row));
+        prof_scope ps(c, c->s_depth, 0, 3);
+        CU(c, cgk_rare_paths(c->s_depth, s.reads_ptr, c->n_reads, c->d_depth32, s.d_chunk_cnt, s.n_tiles,
+                             s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
+        CU(c, cgk_tile_scan(c->s_depth, s.reads_ptr, c->n_reads, s.d_tile_lo, s.d_chunk_cnt, s.d_tile_carry,
+                            s.n_tiles, row));
     }
     {
-        prof_scope ps(c, 1, 1);
+        prof_scope ps(c, c->s_depth, 1, 1);
         cg_pass_args a;
-        a.reads = c->reads_ptr; a.n_reads = c->n_reads; a.tile_lo = c->d_tile_lo; a.chunk_cnt = c->d_chunk_cnt;
-        a.tile_carry = c->d_tile_carry; a.gc = c->gc_ptr;
-        a.chrom_len = c->chrom_len; a.n_tiles = c->n_tiles; a.mq_threshold = c->mq_threshold;
-        a.depth = c->d_depth; a.prefix = c->d_prefix; a.depth32 = c->d_depth32; a.ctl = c->d_flags;
-        a.stats = row; a.expected = c->d_expected;
-        CU(c, cgk_depth_pass(c->stream, a, c->n_sms));
+        a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.tile_lo = s.d_tile_lo; a.chunk_cnt = s.d_chunk_cnt;
+        a.tile_carry = s.d_tile_carry; a.gc = s.gc_ptr;
+        a.chrom_len = s.chrom_len; a.n_tiles = s.n_tiles; a.mq_threshold = c->mq_threshold;
+        a.depth = s.d_depth; a.prefix = s.d_prefix; a.depth32 = c->d_depth32; a.ctl = s.d_ctl;
+        a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
+        CU(c, cgk_depth_pass(c->s_depth, a, c->n_sms));
     }
+    CU(c, cudaEventRecord(s.ev_pass, c->s_depth));
     c->finished = true;
-    if (c->ptr_mode == CG_PTR_HOST) {
-        CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaMemcpyAsync(c->h_flags, c->d_flags, 4, cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
-        if (out) memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
-        return check_flags_host(c, "cg_chrom_finish");
+    if (c->ptr_mode == CG_PTR_DEVICE) {
+        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->s_depth));
+        return CG_OK;
     }
-    if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->stream));
-    return CG_OK;
+    if (c->async) {                       /* `out` is page-locked and is valid after cg_sync */
+        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_depth));
+        return CG_OK;
+    }
+    CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_depth));
+    CU(c, cudaStreamSynchronize(c->s_depth));
+    if (out) memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
+    return report_sticky(c, "cg_chrom_finish");
 }
 
 int cg_get_expected(cg_ctx* c, float expected[CG_GC_BINS])
@@ -362,9 +492,10 @@ int cg_get_expected(cg_ctx* c, float expected[CG_GC_BINS])
     if (!c || !expected) return fail(c, CG_EINVAL, "null argument");
     if (!c->finished) return fail(c, CG_EINVAL, "cg_get_expected before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemcpyAsync(expected, c->d_expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c->stream));
-    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamSynchronize(c->stream));
+    cg_slot& s = c->slot[c->cur];
+    CU(c, cudaMemcpyAsync(expected, s.d_expected, sizeof(float) * CG_GC_BINS,
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c->s_depth));
+    if (blocking(c)) CU(c, cudaStreamSynchronize(c->s_depth));
     return CG_OK;
 }
 
@@ -373,101 +504,31 @@ int cg_set_expected(cg_ctx* c, const float expected[CG_GC_BINS])
     if (!c || !expected) return fail(c, CG_EINVAL, "null argument");
     if (!c->finished) return fail(c, CG_EINVAL, "cg_set_expected before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemcpyAsync(c->d_expected, expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, c->stream));
+    cg_slot& s = c->slot[c->cur];
+    CU(c, cudaMemcpyAsync(s.d_expected, expected, sizeof(float) * CG_GC_BINS,
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, c->s_depth));
+    CU(c, cudaEventRecord(s.ev_pass, c->s_depth));        /* the genotype stream waits for this */
     return CG_OK;
 }
 
 /* ------------------------------------------------------------------------- */
-/* Mappability rows -> disjoint runs.  svs.c:350-371 paints rows in file order,
- * [start, end] inclusive, later rows overwriting earlier ones; the run list is
- * what mappability[] would hold afterwards (zero gaps omitted), clipped to the
- * chromosome.  Input preparation, like BED parsing: done on the host once. */
-static void flatten_rows(const cg_mapiv* rows, size_t n, int32_t chrom_len, std::vector<cg_maprun>& out)
-{
-    out.clear();
-    if (n == 0) return;
-    auto emit = [&](int32_t s, int32_t e, float v) {           /* [s,e) */
-        if (s < 0) s = 0;
-        if (e > chrom_len) e = chrom_len;
-        if (e <= s) return;
-        if (!out.empty() && out.back().end == s && memcmp(&out.back().val, &v, 4) == 0) { out.back().end = e; return; }
-        out.push_back(cg_maprun{s, e, v, 0});
-    };
-    /* fast path: bedGraph order (starts strictly increasing, ends non-decreasing) */
-    bool ordered = true;
-    for (size_t i = 1; i < n && ordered; i++)
-        ordered = rows[i].start > rows[i - 1].start && rows[i].end >= rows[i - 1].end;
-    if (ordered) {
-        for (size_t i = 0; i < n; i++) {
-            if (rows[i].end < rows[i].start) { ordered = false; break; }
-        }
-    }
-    if (ordered) {
-        out.reserve(n);
-        for (size_t i = 0; i < n; i++) {
-            long long e = (long long)rows[i].end + 1;
-            if (i + 1 < n && rows[i + 1].start < e) e = rows[i + 1].start;
-            emit(rows[i].start, (int32_t)std::min<long long>(e, chrom_len), rows[i].val);
-        }
-        return;
-    }
-    /* general case: sweep over elementary segments; the winner is the latest row covering it */
-    std::vector<uint32_t> order;
-    order.reserve(n);
-    std::vector<long long> cuts;
-    cuts.reserve(2 * n);
-    for (size_t i = 0; i < n; i++) {
-        if (rows[i].end < rows[i].start) continue;
-        order.push_back((uint32_t)i);
-        cuts.push_back(rows[i].start);
-        cuts.push_back((long long)rows[i].end + 1);
-    }
-    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-        return rows[a].start != rows[b].start ? rows[a].start < rows[b].start : a < b; });
-    std::sort(cuts.begin(), cuts.end());
-    cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
-    std::priority_queue<uint32_t> active;                      /* largest file index on top */
-    size_t next = 0;
-    for (size_t k = 0; k + 1 < cuts.size(); k++) {
-        const long long a = cuts[k], b = cuts[k + 1];
-        while (next < order.size() && rows[order[next]].start <= a) active.push(order[next++]);
-        while (!active.empty() && (long long)rows[active.top()].end < a) active.pop();
-        if (active.empty()) continue;
-        const long long lo = std::max<long long>(a, 0), hi = std::min<long long>(b, chrom_len);
-        if (hi > lo) emit((int32_t)lo, (int32_t)hi, rows[active.top()].val);
-    }
-}
-
-int cg_flatten_mappability(const cg_mapiv* rows, size_t n, int32_t chrom_len, cg_maprun** runs_out, size_t* n_out)
-{
-    if ((!rows && n) || !runs_out || !n_out) return fail(nullptr, CG_EINVAL, "null argument");
-    std::vector<cg_maprun> v;
-    flatten_rows(rows, n, chrom_len, v);
-    cg_maprun* p = (cg_maprun*)malloc((v.size() ? v.size() : 1) * sizeof(cg_maprun));
-    if (!p) return fail(nullptr, CG_ENOMEM, "out of host memory");
-    if (!v.empty()) memcpy(p, v.data(), v.size() * sizeof(cg_maprun));
-    *runs_out = p; *n_out = v.size();
-    return CG_OK;
-}
-
-void cg_free_runs(cg_maprun* runs) { free(runs); }
-
 int cg_set_mappability_runs(cg_ctx* c, const cg_maprun* runs, size_t n, int enabled)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (!c->in_chrom) return fail(c, CG_EINVAL, "cg_set_mappability outside a chromosome");
     if (n > 0x7fffffffull) return fail(c, CG_EINVAL, "too many mappability runs");
     CU(c, cudaSetDevice(c->device));
-    c->has_map = enabled ? 1 : 0;
-    c->n_runs = (int)n;
-    if (n == 0) { c->runs_ptr = nullptr; return CG_OK; }
+    cg_slot& s = c->slot[c->cur];
+    s.has_map = enabled ? 1 : 0;
+    s.n_runs = (int)n;
+    if (n == 0) { s.runs_ptr = nullptr; return CG_OK; }
     if (!runs) return fail(c, CG_EINVAL, "null runs");
-    if (c->ptr_mode == CG_PTR_DEVICE) { c->runs_ptr = runs; return CG_OK; }
-    int rc = grow(c, &c->d_runs, &c->runs_cap, n);
+    if (c->ptr_mode == CG_PTR_DEVICE) { s.runs_ptr = runs; return CG_OK; }
+    int rc = grow(c, &s.d_runs, &s.runs_cap, n);
     if (rc) return rc;
-    CU(c, cudaMemcpyAsync(c->d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, c->stream));
-    c->runs_ptr = c->d_runs;
+    /* on the genotype stream: behind the slot's previous tenant, which may still read d_runs */
+    CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, c->s_geno));
+    s.runs_ptr = s.d_runs;
     return CG_OK;
 }
 
@@ -477,16 +538,36 @@ int cg_set_mappability(cg_ctx* c, const cg_mapiv* rows, size_t n)
     if (!c->in_chrom) return fail(c, CG_EINVAL, "cg_set_mappability outside a chromosome");
     if (n && !rows) return fail(c, CG_EINVAL, "null rows");
     std::vector<cg_maprun> v;
-    flatten_rows(rows, n, c->chrom_len, v);
+    cg_flatten_rows(rows, n, c->slot[c->cur].chrom_len, v);
     const int saved = c->ptr_mode;
     c->ptr_mode = CG_PTR_HOST;                                 /* rows are always host memory */
     int rc = cg_set_mappability_runs(c, v.data(), v.size(), n > 0);
     if (rc == CG_OK && !v.empty()) {
-        cudaError_t e = cudaStreamSynchronize(c->stream);      /* v dies at return */
+        cudaError_t e = cudaStreamSynchronize(c->s_geno);      /* v dies at return */
         if (e != cudaSuccess) rc = fail(c, CG_ECUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
     }
     c->ptr_mode = saved;
     return rc;
+}
+
+/* HOST-mode staging for one cg_genotype call: room for n CNVs and n calls in the slot's arena.
+ * The arena is rewound by cg_chrom_begin; when it has to grow, everything queued is drained
+ * first, so earlier calls of this chromosome have already delivered their results. */
+static int arena_take(cg_ctx* c, cg_slot& s, size_t n, cg_cnv** d_in, cg_call** d_out)
+{
+    const size_t in_b = (n * sizeof(cg_cnv) + 255) & ~(size_t)255, out_b = (n * sizeof(cg_call) + 255) & ~(size_t)255;
+    if (s.arena_used + in_b + out_b > s.arena_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_arena); s.d_arena = nullptr; s.arena_cap = 0; s.arena_used = 0;
+        const size_t cap = std::max<size_t>(2 * (in_b + out_b), (size_t)1 << 20);
+        CU(c, cudaMalloc(&s.d_arena, cap));
+        s.arena_cap = cap;
+    }
+    *d_in = reinterpret_cast<cg_cnv*>(s.d_arena + s.arena_used);
+    *d_out = reinterpret_cast<cg_call*>(s.d_arena + s.arena_used + in_b);
+    s.arena_used += in_b + out_b;
+    return CG_OK;
 }
 
 int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out)
@@ -497,29 +578,28 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     if (!cnvs || !out) return fail(c, CG_EINVAL, "null argument");
     if (n > 0x3fffffffull) return fail(c, CG_EINVAL, "too many CNVs in one call");
     CU(c, cudaSetDevice(c->device));
+    cg_slot& s = c->slot[c->cur];
     const cg_cnv* d_in = cnvs; cg_call* d_out = out;
     if (c->ptr_mode == CG_PTR_HOST) {
-        if (n > c->cnv_cap) {
-            CU(c, cudaStreamSynchronize(c->stream));
-            cudaFree(c->d_cnvs); cudaFree(c->d_calls); c->d_cnvs = nullptr; c->d_calls = nullptr; c->cnv_cap = 0;
-            const size_t cap = std::max<size_t>(n, 4096);
-            CU(c, cudaMalloc(&c->d_cnvs, cap * sizeof(cg_cnv)));
-            CU(c, cudaMalloc(&c->d_calls, cap * sizeof(cg_call)));
-            c->cnv_cap = cap;
-        }
-        CU(c, cudaMemcpyAsync(c->d_cnvs, cnvs, n * sizeof(cg_cnv), cudaMemcpyHostToDevice, c->stream));
-        d_in = c->d_cnvs; d_out = c->d_calls;
+        cg_cnv* a_in = nullptr;
+        int rc = arena_take(c, s, n, &a_in, &d_out);
+        if (rc) return rc;
+        CU(c, cudaMemcpyAsync(a_in, cnvs, n * sizeof(cg_cnv), cudaMemcpyHostToDevice, c->s_geno));
+        d_in = a_in;
     }
+    CU(c, cudaStreamWaitEvent(c->s_geno, s.ev_pass, 0));       /* prefix + expected table of this slot */
     {
-        prof_scope ps(c, 2, 1);
-        CU(c, cgk_genotype(c->stream, d_in, (int)n, is_dup ? 1 : 0, c->d_prefix, c->gc_ptr, c->d_expected,
-                           c->runs_ptr, c->n_runs, c->has_map, c->chrom_len, c->d_flags, d_out, c->d_work, &c->work_base, c->n_sms));
+        prof_scope ps(c, c->s_geno, 2, 1);
+        CU(c, cgk_genotype(c->s_geno, d_in, (int)n, is_dup ? 1 : 0, s.d_prefix, s.gc_ptr, s.d_expected,
+                           s.runs_ptr, s.n_runs, s.has_map, s.chrom_len, c->d_sticky, d_out, c->d_work, &c->work_base, c->n_sms));
     }
-    if (c->ptr_mode == CG_PTR_HOST) {
-        CU(c, cudaMemcpyAsync(out, c->d_calls, n * sizeof(cg_call), cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaMemcpyAsync(c->h_flags, c->d_flags, 4, cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
-        return check_flags_host(c, "cg_genotype");
+    if (c->ptr_mode == CG_PTR_HOST)
+        CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, c->s_geno));
+    CU(c, cudaEventRecord(s.ev_geno, c->s_geno));
+    s.geno_queued = true;
+    if (blocking(c)) {
+        CU(c, cudaStreamSynchronize(c->s_geno));
+        return report_sticky(c, "cg_genotype");
     }
     return CG_OK;
 }
@@ -530,8 +610,9 @@ int cg_download_depth(cg_ctx* c, int16_t* out)
     if (!c || !out) return fail(c, CG_EINVAL, "null argument");
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_depth before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemcpyAsync(out, c->d_depth, (size_t)c->chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    cg_slot& s = c->slot[c->cur];
+    CU(c, cudaMemcpyAsync(out, s.d_depth, (size_t)s.chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, c->s_depth));
+    CU(c, cudaStreamSynchronize(c->s_depth));
     return CG_OK;
 }
 
@@ -540,17 +621,19 @@ int cg_download_prefix(cg_ctx* c, int32_t* out)
     if (!c || !out) return fail(c, CG_EINVAL, "null argument");
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_prefix before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemcpyAsync(out, c->d_prefix, (size_t)c->chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    cg_slot& s = c->slot[c->cur];
+    CU(c, cudaMemcpyAsync(out, s.d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, c->s_depth));
+    CU(c, cudaStreamSynchronize(c->s_depth));
     return CG_OK;
 }
 
 int cg_device_arrays(cg_ctx* c, const int16_t** depth, const int32_t** prefix, const float** expected)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (depth) *depth = c->d_depth;
-    if (prefix) *prefix = c->d_prefix;
-    if (expected) *expected = c->d_expected;
+    cg_slot& s = c->slot[c->cur];
+    if (depth) *depth = s.d_depth;
+    if (prefix) *prefix = s.d_prefix;
+    if (expected) *expected = s.d_expected;
     return CG_OK;
 }
 
@@ -566,7 +649,7 @@ int cg_stats_reset(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)CG_MAX_CHROMS, c->stream));
+    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)(c->n_rows > 0 ? c->n_rows : 1), c->s_depth));
     c->n_rows = 0;
     return CG_OK;
 }
@@ -577,8 +660,8 @@ int cg_stats_row(cg_ctx* c, int chr_index, cg_chrom_stats* out)
     if (chr_index < 0 || chr_index >= CG_MAX_CHROMS) return fail(c, CG_EINVAL, "chr_index %d out of range", chr_index);
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMemcpyAsync(c->h_stats, c->d_stats + (size_t)chr_index * CG_STATS_WORDS, sizeof(cg_chrom_stats),
-                          cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+                          cudaMemcpyDeviceToHost, c->s_depth));
+    CU(c, cudaStreamSynchronize(c->s_depth));
     memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
     return CG_OK;
 }

@@ -462,6 +462,7 @@ k_depth_pass(const cg_pass_args a)
         __threadfence();
         const long long rd = __ldcg(&a.stats[tid]), cnt = __ldcg(&a.stats[CG_GC_BINS + tid]);
         a.expected[tid] = expected_of(rd, cnt, tid);
+        if (tid == 0 && (a.ctl[CG_W_FLAGS] & CG_FLAG_RANGE)) atomicOr(a.sticky, CG_FLAG_RANGE);
     }
 }
 

@@ -101,6 +101,12 @@ void        cg_destroy(cg_ctx* ctx);
 const char* cg_last_error(cg_ctx* ctx);
 int         cg_abi_version(void);
 int         cg_set_pointer_mode(cg_ctx* ctx, int mode);
+/* HOST pointer mode only.  on != 0: no call blocks any more — every host pointer handed to
+ * cg_chrom_begin / cg_push_reads / cg_chrom_finish / cg_set_mappability_runs / cg_genotype must
+ * be page-locked (cg_alloc_pinned) and stay untouched until cg_sync(), which is also when the
+ * outputs become valid and when CG_ERANGE is reported.  This is how a host that decodes the
+ * next chromosome while the GPU works on the current one drives the library. */
+int         cg_set_async(cg_ctx* ctx, int on);
 
 /* Page-locked host memory for read batches / results (library owns it). */
 void* cg_alloc_pinned(cg_ctx* ctx, size_t bytes);
@@ -150,8 +156,13 @@ int  cg_set_mappability_runs(cg_ctx* ctx, const cg_maprun* runs, size_t n, int e
  * Requires 0 <= start and end <= chrom_len (the reference reads unchecked, A23). */
 int cg_genotype(cg_ctx* ctx, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out);
 
-/* Wait for everything queued on the context. */
+/* Wait for everything queued on the context (all of its streams).  In HOST pointer mode it
+ * returns CG_ERANGE if a record or interval was clipped since the last report. */
 int cg_sync(cg_ctx* ctx);
+/* Order the context's main stream (cg_stream) behind everything queued so far on its
+ * internal copy and genotype streams, without blocking the host: work or events queued on
+ * cg_stream afterwards (a collective, a timing event) see all results. */
+int cg_join(cg_ctx* ctx);
 
 /* Parity/diagnostic downloads of the current chromosome (HOST pointers always). */
 int cg_download_depth(cg_ctx* ctx, int16_t* out /* chrom_len */);
@@ -170,14 +181,16 @@ int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
 /* Device time of this context's kernels, from CUDA events recorded on its stream
  * around every launch group while profiling is on.  cg_kernel_times waits for the
  * stream, returns the milliseconds and launch counts accumulated since the last
- * call, and clears them.  Slots: 0 = chromosome init + batch marking + bounds,
- * 1 = the fused depth/GC/prefix pass, 2 = CNV sums + likelihoods, 3 = expected table. */
+ * call, and clears them.  Slots: 0 = chromosome init + batch marking + rare paths
+ * + tile scan, 1 = the fused depth/GC/prefix pass (it also derives the expected table),
+ * 2 = CNV sums + likelihoods (runs on the genotype stream, overlapping slot 1 of the next
+ * chromosome), 3 = unused. */
 #define CG_NSLOTS 4
 int cg_set_profiling(cg_ctx* ctx, int on);
 int cg_kernel_times(cg_ctx* ctx, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS]);
 /* Number of kernels this context has launched since creation. */
 int64_t cg_launch_count(cg_ctx* ctx);
-/* The CUDA stream (cudaStream_t) all of this context's work is queued on. */
+/* The context's main CUDA stream (cudaStream_t): the depth pass runs on it; see cg_join. */
 void* cg_stream(cg_ctx* ctx);
 
 #ifdef __cplusplus

@@ -341,3 +341,44 @@ def test_full_size_chromosome_properties(ctx):
     idx = rng.integers(0, L, size=1000)
     cnt = np.searchsorted(passing, idx, side="right") - np.searchsorted(passing, idx, side="left")
     assert np.array_equal(depth[idx], cnt.astype(np.int16))
+
+
+def test_async_host_mode_pipelines_chromosomes_without_mixing_them_up(ctx, oracle):
+    """cg_set_async: page-locked buffers, no call blocks, results valid after cg_sync.  Five
+    chromosomes of very different sizes go through back to back, so chromosome k's genotype kernel
+    runs under chromosome k+1's depth pass and the two slots are reused twice."""
+    from conga_b200 import CALL_DT, CG_PTR_HOST, STATS_DT, flatten_mappability
+    rng = np.random.default_rng(11)
+    lens = [1_500_000, 40_000, 700_000, 16_384, 2_100_000]
+    chroms = [synth._chrom("c%d" % i, i, L, rng, max(10, L // 40), 30 + i, 12 + i, True, cnv_hi=max(2000, L // 8))
+              for i, L in enumerate(lens)]
+    ctx.set_pointer_mode(CG_PTR_HOST)
+    ctx.set_async(True)
+    keep = []
+    try:
+        for ch in chroms:
+            runs = flatten_mappability(np.ascontiguousarray(ch.maprows), ch.length)
+            pin = lambda a, dt: (lambda p: (p.__setitem__(slice(None), a), p)[1])(ctx.pinned_array(len(a), dt))
+            pr, pg = pin(ch.reads, READ_DT), pin(ch.gc, np.int8)
+            pd, pu, prn = pin(ch.dels, CNV_DT), pin(ch.dups, CNV_DT), pin(runs, runs.dtype)
+            od, ou = ctx.pinned_array(len(ch.dels), CALL_DT), ctx.pinned_array(len(ch.dups), CALL_DT)
+            st = ctx.pinned_array(1, STATS_DT)
+            lib, h = ctx.lib, ctx.h
+            ctx._ck(lib.cg_chrom_begin(h, ch.index, ch.length, pg.ctypes.data, len(pg), 10))
+            half = len(pr) // 2
+            ctx._ck(lib.cg_push_reads(h, pr.ctypes.data, half))
+            ctx._ck(lib.cg_push_reads(h, pr.ctypes.data + half * READ_DT.itemsize, len(pr) - half))
+            ctx._ck(lib.cg_chrom_finish(h, st.ctypes.data))
+            ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data, len(prn), 1))
+            ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od.ctypes.data))
+            ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou.ctypes.data))
+            keep.append((ch, st, od, ou, (pr, pg, pd, pu, prn)))
+        ctx.sync()
+        for ch, st, od, ou, _ in keep:
+            depth, st_ref, exp, d_ref, u_ref = oracle.chromosome(ch, 10, True)
+            assert int(st[0]["rd_cnt"]) == int(st_ref["rd_cnt"]) and int(st[0]["reads_passed"]) == int(st_ref["reads_passed"])
+            assert np.array_equal(st[0]["rd_per_gc"], st_ref["rd_per_gc"])
+            assert_calls_equal(od, d_ref, True)
+            assert_calls_equal(ou, u_ref, True)
+    finally:
+        ctx.set_async(False)
