@@ -7,13 +7,15 @@
 #include <stdint.h>
 #include "../../include/conga_gpu.h"
 
-/* ---- geometry of the fused depth pass (K1+K2+K3) ------------------------- */
-#define CG_TILE        16384          /* positions per tile: 32 KB of packed u16 bins in smem */
-#define CG_PASS_THREADS  256
-#define CG_TILE_SHIFT  14
-#define CG_CHUNK       2048           /* positions one warp scans; unit of the record pre-count */
-#define CG_CHUNK_SHIFT 11
-#define CG_CHUNKS_PER_TILE (CG_TILE / CG_CHUNK)
+/* ---- geometry of the fused depth pass (K1+K2+K3) -------------------------
+ * The unit of work is a CHUNK of 2048 positions, owned by one warp (4 KB of packed u16 bins
+ * in shared memory).  Record counts are kept at three levels so that a chunk's scan carry is
+ * three short coalesced loads: per chunk, per GROUP of 32 chunks, per SUPER of 32 groups. */
+#define CG_CHUNK        2048
+#define CG_CHUNK_SHIFT  11
+#define CG_GROUP_SHIFT  16            /* 32 chunks  = 65,536 positions   */
+#define CG_SUPER_SHIFT  21            /* 32 groups  = 2,097,152 positions */
+#define CG_PASS_THREADS 256
 #define CG_PILEUP_PROBE 16384         /* k_mark_batch looks this many records back for an equal pos */
 #define CG_STATS_WORDS 204            /* int64 words per chromosome row = sizeof(cg_chrom_stats)/8 */
 
@@ -23,21 +25,26 @@
 #define CG_FLAG_PILEUP     4u         /* > CG_PILEUP_PROBE records share one pos: int16 wrap possible */
 /* words of the per-context u32 control block (d_flags) */
 #define CG_W_FLAGS   0
-#define CG_W_TILE    1                /* dynamic tile counter of the depth pass */
+#define CG_W_TILE    1                /* dynamic chunk counter of the depth pass */
 #define CG_W_DONE    2                /* CTAs of the depth pass that have flushed their statistics */
+
+struct cg_counts {                    /* one allocation per slot, see cgk_counts_layout */
+    int32_t* chunk_lo;                /* [n_chunks+1] first record index of each chunk (sorted input) */
+    int32_t* cnt1;                    /* [n_chunks]   sum of the (int16) depths of each chunk */
+    int32_t* cnt2;                    /* [n_groups]   ... of each group of 32 chunks */
+    int32_t* cnt3;                    /* [n_supers]   ... of each super of 32 groups */
+};
 
 struct cg_pass_args {
     const cg_read* reads;             /* all records of the chromosome, device */
     long long      n_reads;
-    const int32_t* tile_lo;           /* [n_tiles+1] first record index of each tile (sorted input) */
-    const int32_t* chunk_cnt;         /* [n_tiles*8] sum of the (int16) depths of each 2048-position chunk */
-    const uint32_t* tile_carry;       /* [n_tiles] prefix (mod 2^32) in front of each tile */
+    cg_counts      k;
     const int8_t*  gc;                /* SONIC GC byte per 100-position window */
     int32_t        chrom_len;
-    int32_t        n_tiles;
+    int32_t        n_chunks;
     int            mq_threshold;
-    int16_t*       depth;             /* [n_tiles*CG_TILE] */
-    int32_t*       prefix;            /* [n_tiles*CG_TILE] inclusive int32 prefix of depth */
+    int16_t*       depth;             /* [n_chunks*CG_CHUNK] */
+    int32_t*       prefix;            /* [n_chunks*CG_CHUNK] inclusive int32 prefix of depth */
     uint32_t*      depth32;           /* unsorted fallback: per-position u32 counts (zero at rest) */
     unsigned int*  ctl;               /* CG_W_* control words */
     long long*     stats;             /* this chromosome's int64[204] row */
@@ -52,15 +59,15 @@ extern "C++" {
 int  cg_fail(cg_ctx* c, int code, const char* fmt, ...);
 void cg_flatten_rows(const cg_mapiv* rows, size_t n, int32_t chrom_len, std::vector<cg_maprun>& out);
 /* depth_pass.cu */
-cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* chunk_cnt, int n_chunks, long long* stats_row, unsigned int* ctl);
+size_t      cgk_counts_words(int n_chunks);                       /* int32 words one slot's counts need */
+cg_counts   cgk_counts_layout(int32_t* base, int n_chunks);
+cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* counts_base, int n_chunks, long long* stats_row, unsigned int* ctl);
 cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
-                           int32_t* tile_lo, int32_t* chunk_cnt, int n_tiles, int32_t chrom_len,
-                           int mq_threshold, unsigned int* ctl, long long* stats_row);
+                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
+                           unsigned int* ctl, long long* stats_row);
 cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_reads, uint32_t* depth32,
-                           int32_t* chunk_cnt, int n_tiles, int32_t chrom_len, int mq_threshold,
+                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
                            const unsigned int* ctl, int n_sms);
-cudaError_t cgk_tile_scan(cudaStream_t s, const cg_read* reads, long long n_reads, int32_t* tile_lo,
-                          const int32_t* chunk_cnt, uint32_t* tile_carry, int n_tiles, long long* stats_row);
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms);
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
 int         cgk_depth_pass_ctas_per_sm(void);

@@ -5,7 +5,7 @@
  *
  * Execution model.  A context owns three streams and two chromosome slots:
  *   s_copy  host->device copies of GC bytes and read batches (HOST pointer mode)
- *   s_depth chromosome init, batch marking, tile scan, the fused depth pass
+ *   s_depth chromosome init, batch marking, the fused depth pass
  *   s_geno  mappability / CNV uploads, the genotype kernel, result downloads
  * Chromosome k lives in slot k&1 (its own depth, prefix, GC, expected-table,
  * control-word and staging buffers), so the latency-bound genotype kernel of
@@ -33,11 +33,11 @@ struct cg_slot {
     /* geometry */
     int chr_index = -1;
     int32_t chrom_len = 0;
-    int n_tiles = 0;
+    int n_chunks = 0;
     /* depth side */
     cg_read* d_reads = nullptr;       size_t reads_cap = 0;
     int8_t* d_gc = nullptr;           size_t gc_cap = 0;
-    int32_t* d_tile_lo = nullptr;     int32_t* d_chunk_cnt = nullptr; uint32_t* d_tile_carry = nullptr; size_t tiles_cap = 0;
+    int32_t* d_counts = nullptr;      size_t counts_cap = 0;      /* chunk bounds + three count levels (cg_counts) */
     int16_t* d_depth = nullptr;       int32_t* d_prefix = nullptr; size_t pos_cap = 0;
     float* d_expected = nullptr;              /* [101] (128 allocated) */
     unsigned int* d_ctl = nullptr;            /* CG_W_* control words */
@@ -50,14 +50,16 @@ struct cg_slot {
     /* ordering */
     cudaEvent_t ev_copy = nullptr;            /* s_copy: last upload for this slot */
     cudaEvent_t ev_pass = nullptr;            /* s_depth: the pass (and the table) of this slot is done */
-    cudaEvent_t ev_geno = nullptr;            /* s_geno: last genotype work queued for this slot */
-    bool used = false, geno_queued = false;
+    cudaEvent_t ev_geno[2] = {nullptr, nullptr};   /* s_geno[t]: last genotype work queued for this slot */
+    cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded */
+    bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false;
 };
 
 struct cg_ctx {
     int device = 0;
     int n_sms = 148;
-    cudaStream_t s_copy = nullptr, s_depth = nullptr, s_geno = nullptr;
+    cudaStream_t s_copy = nullptr, s_depth = nullptr;
+    cudaStream_t s_geno[2] = {nullptr, nullptr};  /* [0] deletions (and uploads), [1] duplications */
     cudaEvent_t ev_join = nullptr;
     int ptr_mode = CG_PTR_HOST;
     bool async = false;
@@ -76,8 +78,8 @@ struct cg_ctx {
     uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;    /* out-of-order path only; zero at rest */
     long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
     unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
-    unsigned int* d_work = nullptr;           /* monotonic work counter of the genotype kernel */
-    unsigned int work_base = 0;
+    unsigned int* d_work = nullptr;           /* [2] monotonic work counters of the genotype kernel, one per stream */
+    unsigned int work_base[2] = {0, 0};
 
     /* pinned staging */
     cg_chrom_stats* h_stats = nullptr;
@@ -113,7 +115,8 @@ static int sync_all(cg_ctx* c)
 {
     CU(c, cudaStreamSynchronize(c->s_copy));
     CU(c, cudaStreamSynchronize(c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_geno));
+    CU(c, cudaStreamSynchronize(c->s_geno[0]));
+    CU(c, cudaStreamSynchronize(c->s_geno[1]));
     return CG_OK;
 }
 
@@ -162,11 +165,11 @@ static void prof_collect(cg_ctx* c)
 /* CG_FLAG_RANGE raised on the device since the last report -> CG_ERANGE (caller has synchronised) */
 static int report_sticky(cg_ctx* c, const char* what)
 {
-    CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_geno));
-    CU(c, cudaStreamSynchronize(c->s_geno));
+    CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_geno[0]));
+    CU(c, cudaStreamSynchronize(c->s_geno[0]));
     if (c->h_flags[0] & CG_FLAG_RANGE) {
-        CU(c, cudaMemsetAsync(c->d_sticky, 0, 4, c->s_geno));
-        CU(c, cudaStreamSynchronize(c->s_geno));
+        CU(c, cudaMemsetAsync(c->d_sticky, 0, 4, c->s_geno[0]));
+        CU(c, cudaStreamSynchronize(c->s_geno[0]));
         return fail(c, CG_ERANGE, "%s: a record or interval lies outside [0, chrom_len); it was clipped", what);
     }
     return CG_OK;
@@ -199,7 +202,8 @@ cg_ctx* cg_create(int device)
     bool ok = cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaStreamCreateWithPriority(&c->s_depth, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         /* the genotype kernel is small and latency-bound: let its CTAs be placed first */
-        && cudaStreamCreateWithPriority(&c->s_geno, cudaStreamNonBlocking, prio_hi) == cudaSuccess
+        && cudaStreamCreateWithPriority(&c->s_geno[0], cudaStreamNonBlocking, prio_hi) == cudaSuccess
+        && cudaStreamCreateWithPriority(&c->s_geno[1], cudaStreamNonBlocking, prio_hi) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
         && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
         && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
@@ -217,7 +221,9 @@ cg_ctx* cg_create(int device)
             && cudaMemset(s.d_ctl, 0, 16) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_copy, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_pass, cudaEventDisableTiming) == cudaSuccess
-            && cudaEventCreateWithFlags(&s.ev_geno, cudaEventDisableTiming) == cudaSuccess;
+            && cudaEventCreateWithFlags(&s.ev_geno[0], cudaEventDisableTiming) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_geno[1], cudaEventDisableTiming) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_runs, cudaEventDisableTiming) == cudaSuccess;
     }
     if (!ok) {
         fail(nullptr, CG_ECUDA, "context allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -234,17 +240,18 @@ void cg_destroy(cg_ctx* c)
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     if (c->s_depth) cudaStreamSynchronize(c->s_depth);
-    if (c->s_geno) cudaStreamSynchronize(c->s_geno);
+    for (int t = 0; t < 2; t++) if (c->s_geno[t]) cudaStreamSynchronize(c->s_geno[t]);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (int i = 0; i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
-        cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_tile_lo); cudaFree(s.d_chunk_cnt); cudaFree(s.d_tile_carry);
+        cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_counts);
         cudaFree(s.d_depth); cudaFree(s.d_prefix); cudaFree(s.d_expected); cudaFree(s.d_ctl);
         cudaFree(s.d_runs); cudaFree(s.d_arena);
         if (s.ev_copy) cudaEventDestroy(s.ev_copy);
         if (s.ev_pass) cudaEventDestroy(s.ev_pass);
-        if (s.ev_geno) cudaEventDestroy(s.ev_geno);
+        for (int t = 0; t < 2; t++) if (s.ev_geno[t]) cudaEventDestroy(s.ev_geno[t]);
+        if (s.ev_runs) cudaEventDestroy(s.ev_runs);
     }
     cudaFree(c->d_depth32); cudaFree(c->d_stats); cudaFree(c->d_sticky); cudaFree(c->d_work);
     if (c->h_stats) cudaFreeHost(c->h_stats);
@@ -252,7 +259,7 @@ void cg_destroy(cg_ctx* c)
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     if (c->s_depth) cudaStreamDestroy(c->s_depth);
-    if (c->s_geno) cudaStreamDestroy(c->s_geno);
+    for (int t = 0; t < 2; t++) if (c->s_geno[t]) cudaStreamDestroy(c->s_geno[t]);
     delete c;
 }
 
@@ -290,8 +297,10 @@ int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaEventRecord(c->ev_join, c->s_geno));
-    CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
+    for (int t = 0; t < 2; t++) {
+        CU(c, cudaEventRecord(c->ev_join, c->s_geno[t]));
+        CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
+    }
     CU(c, cudaEventRecord(c->ev_join, c->s_copy));
     CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
     return CG_OK;
@@ -336,7 +345,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (chr_index < 0 || chr_index >= CG_MAX_CHROMS) return fail(c, CG_EINVAL, "chr_index %d outside 0..%d", chr_index, CG_MAX_CHROMS - 1);
     if (chrom_len <= 0) return fail(c, CG_EINVAL, "chrom_len %d must be positive", chrom_len);
-    if (chrom_len > INT32_MAX - CG_TILE) return fail(c, CG_EINVAL, "chrom_len %d too large", chrom_len);
+    if (chrom_len > INT32_MAX - CG_CHUNK) return fail(c, CG_EINVAL, "chrom_len %d too large", chrom_len);
     const int need_windows = (chrom_len + 99) / 100;
     if (!gc_profile || n_windows < need_windows)
         return fail(c, CG_EINVAL, "gc_profile needs >= %d windows for length %d (got %d)", need_windows, chrom_len, n_windows);
@@ -344,17 +353,14 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
 
     const int si = (int)(c->n_begun & 1);
     cg_slot& s = c->slot[si];
-    const int n_tiles = (chrom_len + CG_TILE - 1) / CG_TILE;
-    const size_t n_pos = (size_t)n_tiles * CG_TILE;
-    if ((size_t)n_tiles + 1 > s.tiles_cap) {
+    const int n_chunks = (chrom_len + CG_CHUNK - 1) / CG_CHUNK;
+    const size_t n_pos = (size_t)n_chunks * CG_CHUNK;
+    if (cgk_counts_words(n_chunks) > s.counts_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
-        cudaFree(s.d_tile_lo); cudaFree(s.d_chunk_cnt); cudaFree(s.d_tile_carry);
-        s.d_tile_lo = nullptr; s.d_chunk_cnt = nullptr; s.d_tile_carry = nullptr; s.tiles_cap = 0;
-        CU(c, cudaMalloc(&s.d_tile_lo, ((size_t)n_tiles + 1) * sizeof(int32_t)));
-        CU(c, cudaMalloc(&s.d_chunk_cnt, (size_t)n_tiles * CG_CHUNKS_PER_TILE * sizeof(int32_t)));
-        CU(c, cudaMalloc(&s.d_tile_carry, ((size_t)n_tiles + 1) * sizeof(uint32_t)));
-        s.tiles_cap = (size_t)n_tiles + 1;
+        cudaFree(s.d_counts); s.d_counts = nullptr; s.counts_cap = 0;
+        CU(c, cudaMalloc(&s.d_counts, cgk_counts_words(n_chunks) * sizeof(int32_t)));
+        s.counts_cap = cgk_counts_words(n_chunks);
     }
     if (n_pos > s.pos_cap) {
         int rc = sync_all(c);
@@ -380,9 +386,11 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     }
     /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
     if (s.used) CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_pass, 0));            /* d_reads */
-    if (s.geno_queued) {
-        CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno, 0));                     /* d_gc */
-        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_geno, 0));                    /* d_prefix, d_expected */
+    for (int t = 0; t < 2; t++) {
+        if (!s.geno_queued[t]) continue;
+        CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno[t], 0));                  /* d_gc */
+        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_geno[t], 0));                 /* d_prefix, d_expected */
+        if (t == 1) CU(c, cudaStreamWaitEvent(c->s_geno[0], s.ev_geno[1], 0));   /* d_runs is uploaded on s_geno[0] */
     }
     if (c->ptr_mode == CG_PTR_HOST) {
         CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy));
@@ -391,11 +399,11 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     } else {
         s.gc_ptr = gc_profile;
     }
-    s.chr_index = chr_index; s.chrom_len = chrom_len; s.n_tiles = n_tiles;
+    s.chr_index = chr_index; s.chrom_len = chrom_len; s.n_chunks = n_chunks;
     s.reads_ptr = s.d_reads;
     s.n_runs = 0; s.has_map = 0; s.runs_ptr = nullptr;
     s.arena_used = 0;
-    s.used = true; s.geno_queued = false;
+    s.used = true; s.geno_queued[0] = s.geno_queued[1] = false; s.runs_uploaded = false;
     c->cur = si; c->n_begun++;
     c->mq_threshold = mq_threshold;
     c->n_reads = 0;
@@ -403,7 +411,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
         prof_scope ps(c, c->s_depth, 0, 1);
-        CU(c, cgk_chrom_init(c->s_depth, s.d_chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
+        CU(c, cgk_chrom_init(c->s_depth, s.d_counts, n_chunks,
                              c->d_stats + (size_t)chr_index * CG_STATS_WORDS, s.d_ctl));
     }
     return CG_OK;
@@ -439,8 +447,8 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     c->n_reads = first + (long long)n;
     {
         prof_scope ps(c, c->s_depth, 0, 1);
-        CU(c, cgk_mark_batch(c->s_depth, s.reads_ptr, first, (long long)n, s.d_tile_lo, s.d_chunk_cnt, s.n_tiles,
-                             s.chrom_len, c->mq_threshold, s.d_ctl,
+        CU(c, cgk_mark_batch(c->s_depth, s.reads_ptr, first, (long long)n, cgk_counts_layout(s.d_counts, s.n_chunks),
+                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl,
                              c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS));
     }
     return CG_OK;
@@ -455,18 +463,16 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     long long* row = c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS;
     if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_copy, 0));   /* GC bytes */
     {
-        prof_scope ps(c, c->s_depth, 0, 3);
-        CU(c, cgk_rare_paths(c->s_depth, s.reads_ptr, c->n_reads, c->d_depth32, s.d_chunk_cnt, s.n_tiles,
-                             s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
-        CU(c, cgk_tile_scan(c->s_depth, s.reads_ptr, c->n_reads, s.d_tile_lo, s.d_chunk_cnt, s.d_tile_carry,
-                            s.n_tiles, row));
+        prof_scope ps(c, c->s_depth, 0, 2);
+        CU(c, cgk_rare_paths(c->s_depth, s.reads_ptr, c->n_reads, c->d_depth32, cgk_counts_layout(s.d_counts, s.n_chunks),
+                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
     }
     {
         prof_scope ps(c, c->s_depth, 1, 1);
         cg_pass_args a;
-        a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.tile_lo = s.d_tile_lo; a.chunk_cnt = s.d_chunk_cnt;
-        a.tile_carry = s.d_tile_carry; a.gc = s.gc_ptr;
-        a.chrom_len = s.chrom_len; a.n_tiles = s.n_tiles; a.mq_threshold = c->mq_threshold;
+        a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.k = cgk_counts_layout(s.d_counts, s.n_chunks);
+        a.gc = s.gc_ptr;
+        a.chrom_len = s.chrom_len; a.n_chunks = s.n_chunks; a.mq_threshold = c->mq_threshold;
         a.depth = s.d_depth; a.prefix = s.d_prefix; a.depth32 = c->d_depth32; a.ctl = s.d_ctl;
         a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
         CU(c, cgk_depth_pass(c->s_depth, a, c->n_sms));
@@ -526,8 +532,10 @@ int cg_set_mappability_runs(cg_ctx* c, const cg_maprun* runs, size_t n, int enab
     if (c->ptr_mode == CG_PTR_DEVICE) { s.runs_ptr = runs; return CG_OK; }
     int rc = grow(c, &s.d_runs, &s.runs_cap, n);
     if (rc) return rc;
-    /* on the genotype stream: behind the slot's previous tenant, which may still read d_runs */
-    CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, c->s_geno));
+    /* on a genotype stream: behind the slot's previous tenant, which may still read d_runs */
+    CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, c->s_geno[0]));
+    CU(c, cudaEventRecord(s.ev_runs, c->s_geno[0]));
+    s.runs_uploaded = true;
     s.runs_ptr = s.d_runs;
     return CG_OK;
 }
@@ -543,7 +551,7 @@ int cg_set_mappability(cg_ctx* c, const cg_mapiv* rows, size_t n)
     c->ptr_mode = CG_PTR_HOST;                                 /* rows are always host memory */
     int rc = cg_set_mappability_runs(c, v.data(), v.size(), n > 0);
     if (rc == CG_OK && !v.empty()) {
-        cudaError_t e = cudaStreamSynchronize(c->s_geno);      /* v dies at return */
+        cudaError_t e = cudaStreamSynchronize(c->s_geno[0]);   /* v dies at return */
         if (e != cudaSuccess) rc = fail(c, CG_ECUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
     }
     c->ptr_mode = saved;
@@ -579,26 +587,29 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     if (n > 0x3fffffffull) return fail(c, CG_EINVAL, "too many CNVs in one call");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
+    const int t = is_dup ? 1 : 0;
+    cudaStream_t st = c->s_geno[t];           /* deletions and duplications of one chromosome run side by side */
     const cg_cnv* d_in = cnvs; cg_call* d_out = out;
     if (c->ptr_mode == CG_PTR_HOST) {
         cg_cnv* a_in = nullptr;
         int rc = arena_take(c, s, n, &a_in, &d_out);
         if (rc) return rc;
-        CU(c, cudaMemcpyAsync(a_in, cnvs, n * sizeof(cg_cnv), cudaMemcpyHostToDevice, c->s_geno));
+        CU(c, cudaMemcpyAsync(a_in, cnvs, n * sizeof(cg_cnv), cudaMemcpyHostToDevice, st));
         d_in = a_in;
     }
-    CU(c, cudaStreamWaitEvent(c->s_geno, s.ev_pass, 0));       /* prefix + expected table of this slot */
+    CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));              /* prefix + expected table of this slot */
+    if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
     {
-        prof_scope ps(c, c->s_geno, 2, 1);
-        CU(c, cgk_genotype(c->s_geno, d_in, (int)n, is_dup ? 1 : 0, s.d_prefix, s.gc_ptr, s.d_expected,
-                           s.runs_ptr, s.n_runs, s.has_map, s.chrom_len, c->d_sticky, d_out, c->d_work, &c->work_base, c->n_sms));
+        prof_scope ps(c, st, 2, 1);
+        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_prefix, s.gc_ptr, s.d_expected, s.runs_ptr, s.n_runs, s.has_map,
+                           s.chrom_len, c->d_sticky, d_out, c->d_work + t, &c->work_base[t], c->n_sms));
     }
     if (c->ptr_mode == CG_PTR_HOST)
-        CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, c->s_geno));
-    CU(c, cudaEventRecord(s.ev_geno, c->s_geno));
-    s.geno_queued = true;
+        CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaEventRecord(s.ev_geno[t], st));
+    s.geno_queued[t] = true;
     if (blocking(c)) {
-        CU(c, cudaStreamSynchronize(c->s_geno));
+        CU(c, cudaStreamSynchronize(st));
         return report_sticky(c, "cg_genotype");
     }
     return CG_OK;

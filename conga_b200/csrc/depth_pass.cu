@@ -6,45 +6,46 @@
  *   K2  chromosome sum + 101 GC-bin sums/counts     read_distribution.c:27-46, :49-73
  *   K3  int32 inclusive prefix of the depth array   (serves likelihood.c:115-121 as O(1) queries)
  *
- * Data layout in HBM (per context, reused across chromosomes):
+ * Data layout in HBM (per chromosome slot, reused across chromosomes):
  *   reads      cg_read[N]            8 B records, coordinate sorted
- *   tile_lo    int32[n_tiles+1]      first record of every 16384-position tile
- *   chunk_cnt  int32[n_tiles*8]      sum of the int16 depths of every 2048-position chunk
- *   tile_carry u32[n_tiles]          prefix in front of every tile (mod 2^32)
- *   depth      int16[n_tiles*16384]  the reference's `short read_depth[]` (wraps mod 2^16)
- *   prefix     int32[n_tiles*16384]  P[i] = sum_{j<=i} depth[j]   (mod 2^32)
+ *   chunk_lo   int32[n_chunks+1]     first record of every 2048-position chunk
+ *   cnt1/2/3   int32[...]            sum of the int16 depths per chunk / 32 chunks / 1024 chunks
+ *   depth      int16[n_chunks*2048]  the reference's `short read_depth[]` (wraps mod 2^16)
+ *   prefix     int32[n_chunks*2048]  P[i] = sum_{j<=i} depth[j]   (mod 2^32)
  *   stats      int64[204]            cg_chrom_stats row
  *
- * The scan carry never travels between CTAs.  A chunk's depth sum is the number of
+ * The scan carry never travels between warps.  A chunk's depth sum is the number of
  * passing records that fall in it (every read adds exactly 1) unless a position
  * collects >= 32768 reads and the int16 wraps; k_mark_batch therefore counts records
- * per chunk while it checks the pushed batch (the records are read once, 8 B each,
- * against 6 B per POSITION for the pass), k_rare_paths corrects the count for wrapped
- * pile-ups, and k_tile_scan turns the counts into per-tile carries.  The pass itself
- * is then embarrassingly parallel over tiles: no look-back, no spinning.
+ * per chunk / group / super while it checks the pushed batch (the records are read
+ * once, 8 B each, against 6 B per POSITION for the pass) and k_rare_paths corrects the
+ * counts for wrapped pile-ups.  A chunk's carry is then three short coalesced loads:
+ * the supers in front of its super, the groups in front of its group inside the super,
+ * the chunks in front of it inside the group.  The pass is embarrassingly parallel
+ * over chunks: no look-back, no spinning, no block barrier, no separate scan kernel.
  *
  * Algorithmic bytes per chromosome: 8·N (records) + 2·L (depth) +
  * 4·L (prefix) + L/100 (GC bytes); the pass is HBM-write bound.
  *
- * Pass kernel shape: persistent CTAs pulling tiles from a counter, 256 threads,
- * 32 KB of packed u16 bins in shared memory.  Per tile: warp-aggregated shared
- * histogram of the tile's records -> barrier -> every warp scans its own 2048
- * positions in 8 rows (lane = 8 consecutive positions = one 16-byte LDS, which is
- * also the 16-byte int16 output vector; one warp scan per row; two 16-byte prefix
- * stores) and zeroes the bins behind it -> barrier -> per-window sums from the
- * prefixes at window ends into 101 shared int64 GC accumulators.
+ * Pass kernel shape: persistent warps pulling chunks from a counter; a warp owns 4 KB of
+ * packed u16 bins in shared memory.  Per chunk: warp-aggregated shared histogram of the
+ * chunk's records -> the eight 256-position rows are summed per lane and their eight
+ * warp scans run interleaved (eight independent shuffle chains) -> per row one 16-byte
+ * LDS (which is also the 16-byte int16 output vector) and two 16-byte prefix stores,
+ * bins zeroed behind -> per-window sums from the prefixes at window ends into 101
+ * shared GC accumulators.
  */
 #include "cg_internal.h"
 
 #define FULL 0xffffffffu
-#define TILE CG_TILE
 #define NT   CG_PASS_THREADS
 #define NWARP (NT / 32)
-#define ROWS (CG_CHUNK / 256)         /* rows of 256 positions per warp chunk */
-#define MAXWIN (TILE / 100 + 2)       /* GC windows that can overlap one tile */
+#define ROWS (CG_CHUNK / 256)         /* rows of 256 positions per chunk */
+#define MAXWIN 24                     /* GC windows that can overlap one chunk: 2048/100 + 2 */
+#define LVL (CG_GROUP_SHIFT - CG_CHUNK_SHIFT)      /* 5: 32 children per level */
 
-static_assert(NWARP == CG_CHUNKS_PER_TILE, "one warp per chunk");
-static_assert((1 << CG_TILE_SHIFT) == TILE && (1 << CG_CHUNK_SHIFT) == CG_CHUNK, "shifts");
+static_assert(CG_SUPER_SHIFT - CG_GROUP_SHIFT == LVL && LVL == 5, "32 children per level, one per lane");
+static_assert((1 << CG_CHUNK_SHIFT) == CG_CHUNK && ROWS == 8, "chunk geometry");
 
 __device__ __forceinline__ int sext16(unsigned v) { return (int)(short)(v & 0xffffu); }
 
@@ -65,39 +66,72 @@ __device__ __forceinline__ void st_cs_v4(void* p, unsigned a, unsigned b, unsign
 }
 
 /* ------------------------------------------------------------------------- */
-/* chromosome start: clear the chunk counts, the stats row and the control words */
-__global__ void k_chrom_init(int4* chunk_cnt4, int n_vec, long long* stats_row, unsigned int* ctl)
+static inline int n_groups_of(int n_chunks) { return (n_chunks + 31) >> LVL; }
+static inline int n_supers_of(int n_chunks) { return (n_chunks + 1023) >> (2 * LVL); }
+static inline size_t pad4(size_t n) { return (n + 3) & ~(size_t)3; }
+
+size_t cgk_counts_words(int n_chunks)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    for (int j = i; j < n_vec; j += gridDim.x * blockDim.x) chunk_cnt4[j] = make_int4(0, 0, 0, 0);
+    return pad4((size_t)n_chunks + 1) + pad4((size_t)n_chunks) + pad4((size_t)n_groups_of(n_chunks)) + pad4((size_t)n_supers_of(n_chunks));
+}
+
+cg_counts cgk_counts_layout(int32_t* base, int n_chunks)
+{
+    cg_counts k;
+    k.cnt1 = base;                                            /* the three zeroed arrays first, chunk_lo last */
+    k.cnt2 = k.cnt1 + pad4((size_t)n_chunks);
+    k.cnt3 = k.cnt2 + pad4((size_t)n_groups_of(n_chunks));
+    k.chunk_lo = k.cnt3 + pad4((size_t)n_supers_of(n_chunks));
+    return k;
+}
+
+/* chromosome start: clear the counts, the stats row and the control words; every chunk
+ * bound starts "behind the last record" (the pass clamps it to the record count) */
+__global__ void k_chrom_init(int4* base4, int n_zero_vec, int n_vec, long long* stats_row, unsigned int* ctl)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    for (int j = i; j < n_vec; j += stride)
+        base4[j] = j < n_zero_vec ? make_int4(0, 0, 0, 0) : make_int4(0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff);
     if (i < CG_STATS_WORDS) stats_row[i] = 0;
     if (i < 4) ctl[i] = 0u;
 }
 
-cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* chunk_cnt, int n_chunks, long long* stats_row, unsigned int* ctl)
+cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* counts_base, int n_chunks, long long* stats_row, unsigned int* ctl)
 {
-    const int n_vec = n_chunks / 4;                      /* n_chunks is a multiple of 8 */
+    const cg_counts k = cgk_counts_layout(counts_base, n_chunks);
+    const int n_zero_vec = (int)((k.chunk_lo - counts_base) / 4);
+    const int n_vec = (int)(cgk_counts_words(n_chunks) / 4);
     int blocks = (n_vec + 255) / 256;
     if (blocks < 1) blocks = 1;
-    if (blocks > 148) blocks = 148;
-    k_chrom_init<<<blocks, 256, 0, s>>>(reinterpret_cast<int4*>(chunk_cnt), n_vec, stats_row, ctl);
+    if (blocks > 148 * 2) blocks = 148 * 2;
+    k_chrom_init<<<blocks, 256, 0, s>>>(reinterpret_cast<int4*>(counts_base), n_zero_vec, n_vec, stats_row, ctl);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
 /* per pushed batch, one sweep over its records: sortedness and range checks,  */
-/* tile boundaries, passing records per chunk, pile-up probe                   */
-__device__ __forceinline__ int tile_of(int pos, int n_tiles)
+/* chunk boundaries, passing records per chunk/group/super, pile-up probe      */
+__device__ __forceinline__ int chunk_of(int pos, int n_chunks)
 {
-    int t = pos >> CG_TILE_SHIFT;             /* arithmetic shift: negative pos -> negative tile */
+    int t = pos >> CG_CHUNK_SHIFT;            /* arithmetic shift: negative pos -> negative chunk */
     t = t < 0 ? 0 : t;
-    return t >= n_tiles ? n_tiles - 1 : t;
+    return t >= n_chunks ? n_chunks - 1 : t;
+}
+
+/* first lane of a run of equal keys in the warp, and the run's length */
+__device__ __forceinline__ bool run_leader(int key, int lane, int& cnt)
+{
+    const int prev = __shfl_up_sync(FULL, key, 1);
+    const bool leader = lane == 0 || key != prev;
+    const unsigned lm = __ballot_sync(FULL, leader);
+    const unsigned above = lane == 31 ? 0u : (lm & ~((2u << lane) - 1u));
+    cnt = (above ? __ffs(above) - 1 : 32) - lane;
+    return leader;
 }
 
 __global__ void __launch_bounds__(256)
-k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, int32_t* tile_lo,
-             int32_t* chunk_cnt, int n_tiles, int32_t chrom_len, int mq_threshold,
-             unsigned int* ctl, long long* stats_row)
+k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, cg_counts kk,
+             int n_chunks, int32_t chrom_len, int mq_threshold, unsigned int* ctl, long long* stats_row)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31;
@@ -112,34 +146,33 @@ k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, in
             const uint2 r = __ldg(reinterpret_cast<const uint2*>(reads) + i);
             p = (int)r.x;
             const int mapq = (int)((r.y >> 16) & 0xffu);
-            const int tp = tile_of(p, n_tiles);
-            int tq = -1;
+            const int cp = chunk_of(p, n_chunks);
+            int cq = -1;
             if (i > 0) {
                 const int q = reads[i - 1].pos;
                 if (p < q) f |= CG_FLAG_UNSORTED;
-                tq = tile_of(q, n_tiles);
+                cq = chunk_of(q, n_chunks);
             }
             const bool inside = p >= 0 && p < chrom_len;
             if (!inside) f |= CG_FLAG_RANGE;
-            for (int t = tq + 1; t <= tp; t++) tile_lo[t] = (int32_t)i;
+            for (int t = cq + 1; t <= cp; t++) kk.chunk_lo[t] = (int32_t)i;
             if (mapq > mq_threshold) {                                   /* bam_data.c:205 */
                 n_pass++;                                                /* bam_data.c:214 */
-                if (inside) key = p >> CG_CHUNK_SHIFT;
+                if (inside) key = cp;
             }
             /* a run of >= 32768 equal positions contains two indices that are multiples of the
              * probe distance, so the later one sees the earlier one */
             if ((i & (CG_PILEUP_PROBE - 1)) == 0 && i >= CG_PILEUP_PROBE && reads[i - CG_PILEUP_PROBE].pos == p)
                 f |= CG_FLAG_PILEUP;
         }
-        /* sorted stream: records of one chunk sit in adjacent lanes -> one atomic per chunk per warp */
-        const int prev = __shfl_up_sync(FULL, key, 1);
-        const bool leader = lane == 0 || key != prev;
-        const unsigned lm = __ballot_sync(FULL, leader);
-        if (leader && key >= 0) {
-            const unsigned above = lane == 31 ? 0u : (lm & ~((2u << lane) - 1u));
-            const int cnt = (above ? __ffs(above) - 1 : 32) - lane;
-            atomicAdd(&chunk_cnt[key], cnt);
-        }
+        /* sorted stream: records of one chunk sit in adjacent lanes -> one atomic per chunk per warp,
+         * and the same for the two coarser levels */
+        int cnt;
+        if (run_leader(key, lane, cnt) && key >= 0) atomicAdd(&kk.cnt1[key], cnt);
+        const int gkey = key >= 0 ? key >> LVL : key;
+        if (run_leader(gkey, lane, cnt) && gkey >= 0) atomicAdd(&kk.cnt2[gkey], cnt);
+        const int skey = key >= 0 ? key >> (2 * LVL) : key;
+        if (run_leader(skey, lane, cnt) && skey >= 0) atomicAdd(&kk.cnt3[skey], cnt);
     }
     if (f) atomicOr(&ctl[CG_W_FLAGS], f);
     n_pass = __reduce_add_sync(FULL, n_pass);
@@ -148,14 +181,13 @@ k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, in
 }
 
 cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
-                           int32_t* tile_lo, int32_t* chunk_cnt, int n_tiles, int32_t chrom_len,
-                           int mq_threshold, unsigned int* ctl, long long* stats_row)
+                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
+                           unsigned int* ctl, long long* stats_row)
 {
     if (n <= 0) return cudaSuccess;
     long long blocks = (n + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_mark_batch<<<(int)blocks, 256, 0, s>>>(reads, first, n, tile_lo, chunk_cnt, n_tiles, chrom_len,
-                                             mq_threshold, ctl, stats_row);
+    k_mark_batch<<<(int)blocks, 256, 0, s>>>(reads, first, n, k, n_chunks, chrom_len, mq_threshold, ctl, stats_row);
     return cudaGetLastError();
 }
 
@@ -176,12 +208,19 @@ __global__ void k_rare_scatter(const cg_read* __restrict__ reads, long long n_re
     }
 }
 
+__device__ __forceinline__ void counts_add(const cg_counts& k, int chunk, int delta)
+{
+    atomicAdd(&k.cnt1[chunk], delta);
+    atomicAdd(&k.cnt2[chunk >> LVL], delta);
+    atomicAdd(&k.cnt3[chunk >> (2 * LVL)], delta);
+}
+
 /* unsorted: chunk sums recomputed from the scattered counts (covers int16 wrap too).
  * sorted with a pile-up flagged: for every run of equal positions longer than the probe
- * distance, count its passing records c and replace the chunk's +c by sext16(c). */
+ * distance, count its passing records c and replace the +c by sext16(c). */
 __global__ void __launch_bounds__(256)
 k_rare_totals(const cg_read* __restrict__ reads, long long n_reads, const uint32_t* __restrict__ depth32,
-              int32_t* chunk_cnt, int n_chunks, int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
+              cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
 {
     const unsigned fl = ctl[CG_W_FLAGS];
     if (!(fl & (CG_FLAG_UNSORTED | CG_FLAG_PILEUP))) return;
@@ -197,7 +236,11 @@ k_rare_totals(const cg_read* __restrict__ reads, long long n_reads, const uint32
                 s += sext16(v.x) + sext16(v.y) + sext16(v.z) + sext16(v.w);
             }
             s = __reduce_add_sync(FULL, s);
-            if (lane == 0) chunk_cnt[c] = s;
+            /* the record count of the chunk is order independent; only a wrap changes it */
+            if (lane == 0) {
+                const int old = k.cnt1[c];
+                if (s != old) counts_add(k, (int)c, s - old);
+            }
         }
         return;
     }
@@ -230,74 +273,30 @@ k_rare_totals(const cg_read* __restrict__ reads, long long n_reads, const uint32
             }
             c = __reduce_add_sync(FULL, c);
             if (lane == 0 && c >= 32768 && p0 >= 0 && p0 < chrom_len)
-                atomicAdd(&chunk_cnt[p0 >> CG_CHUNK_SHIFT], sext16((unsigned)c) - c);
+                counts_add(k, p0 >> CG_CHUNK_SHIFT, sext16((unsigned)c) - c);
         }
     }
 }
 
 cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_reads, uint32_t* depth32,
-                           int32_t* chunk_cnt, int n_tiles, int32_t chrom_len, int mq_threshold,
+                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
                            const unsigned int* ctl, int n_sms)
 {
     k_rare_scatter<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chrom_len, mq_threshold, ctl);
-    k_rare_totals<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chunk_cnt, n_tiles * CG_CHUNKS_PER_TILE,
-                                           chrom_len, mq_threshold, ctl);
-    return cudaGetLastError();
-}
-
-/* ------------------------------------------------------------------------- */
-/* one CTA: tile bounds behind the last record, per-tile carries, chromosome sum.
- * |sum of any set of depths| <= number of records < 2^31, so int32 arithmetic is exact. */
-#define SCAN_THREADS 1024
-__global__ void __launch_bounds__(SCAN_THREADS)
-k_tile_scan(const cg_read* __restrict__ reads, long long n_reads, int32_t* tile_lo,
-            const int32_t* __restrict__ chunk_cnt, uint32_t* tile_carry, int n_tiles, long long* stats_row)
-{
-    __shared__ int wsum[32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int last = n_reads > 0 ? tile_of(reads[n_reads - 1].pos, n_tiles) : -1;
-    for (int t = last + 1 + tid; t <= n_tiles; t += SCAN_THREADS) tile_lo[t] = (int32_t)n_reads;
-
-    int run = 0;
-    for (int b = 0; b < n_tiles; b += SCAN_THREADS) {
-        const int t = b + tid;
-        int tot = 0;
-        if (t < n_tiles) {
-            const int4 x = __ldg(reinterpret_cast<const int4*>(chunk_cnt) + 2 * t);
-            const int4 y = __ldg(reinterpret_cast<const int4*>(chunk_cnt) + 2 * t + 1);
-            tot = x.x + x.y + x.z + x.w + y.x + y.y + y.z + y.w;
-        }
-        const int incl = warp_incl_scan(tot, lane);
-        if (lane == 31) wsum[warp] = incl;
-        __syncthreads();
-        if (warp == 0) wsum[lane] = warp_incl_scan(wsum[lane], lane);
-        __syncthreads();
-        const int woff = warp ? wsum[warp - 1] : 0;
-        if (t < n_tiles) tile_carry[t] = (uint32_t)(run + woff + incl - tot);
-        run += wsum[31];
-        __syncthreads();
-    }
-    if (tid == 0) stats_row[2 * CG_GC_BINS] = (long long)run;          /* calc_mu_per_chr, read_distribution.c:35 */
-}
-
-cudaError_t cgk_tile_scan(cudaStream_t s, const cg_read* reads, long long n_reads, int32_t* tile_lo,
-                          const int32_t* chunk_cnt, uint32_t* tile_carry, int n_tiles, long long* stats_row)
-{
-    k_tile_scan<<<1, SCAN_THREADS, 0, s>>>(reads, n_reads, tile_lo, chunk_cnt, tile_carry, n_tiles, stats_row);
+    k_rare_totals<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, k, n_chunks, chrom_len, mq_threshold, ctl);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
 /* the fused pass                                                            */
 struct __align__(16) pass_smem {
-    uint4 bins4[TILE / 8];                    /* 32 KB: eight packed u16 counts per vector */
+    uint4 bins4[NWARP][CG_CHUNK / 8];         /* 8 x 4 KB: eight packed u16 counts per vector, one region per warp */
+    int win_end[NWARP][MAXWIN];               /* chunk-local inclusive prefix at each window's last position */
     /* per-CTA rd_per_gc / window_per_gc.  32-bit is exact here: a CTA's share of the depth sum is
      * bounded by the record count (< 2^31) and it sweeps < 2^32 positions; native 32-bit shared
      * atomics instead of the CAS loop a 64-bit shared add compiles to */
     int gc_rd[CG_GC_BINS];
     unsigned gc_cnt[CG_GC_BINS];
-    int win_end[MAXWIN];                      /* tile-local inclusive prefix at each window's last position */
-    int next_tile;
     int is_last;
 };
 
@@ -317,33 +316,50 @@ __device__ __forceinline__ float expected_of(long long rd, long long cnt, int i)
     return e;
 }
 
+/* sum of the two sign-extended 16-bit halves of w, added to acc (one IDP.2A) */
+__device__ __forceinline__ int add_halves(unsigned w, int acc) { return __dp2a_lo((int)w, 0x0101, acc); }
+
 __global__ void __launch_bounds__(NT, PASS_CTAS_PER_SM)
 k_depth_pass(const cg_pass_args a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     pass_smem& sm = *reinterpret_cast<pass_smem*>(smem_raw);
-    unsigned* bins = reinterpret_cast<unsigned*>(sm.bins4);            /* word = positions 2k (low), 2k+1 (high) */
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint4* my4 = sm.bins4[warp];
+    unsigned* bins = reinterpret_cast<unsigned*>(my4);                 /* word = positions 2k (low), 2k+1 (high) */
+    int* wend = sm.win_end[warp];
     const bool unsorted = (a.ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED) != 0;
+    const int n_reads = (int)a.n_reads;
 
-    for (int i = tid; i < TILE / 8; i += NT) sm.bins4[i] = make_uint4(0, 0, 0, 0);
+    for (int i = lane; i < CG_CHUNK / 8; i += 32) my4[i] = make_uint4(0, 0, 0, 0);
     for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0; sm.gc_cnt[i] = 0u; }
-    if (tid == 0) sm.next_tile = (int)atomicAdd(&a.ctl[CG_W_TILE], 1u);
     __syncthreads();
 
-    for (;;) {
-        const int t = sm.next_tile;
-        if (t >= a.n_tiles) break;
-        const int base = t << CG_TILE_SHIFT;
-        /* carry in front of this warp's chunk: tile carry + the chunks before it */
-        const int4 c0 = __ldg(reinterpret_cast<const int4*>(a.chunk_cnt) + 2 * t);
-        const int4 c1 = __ldg(reinterpret_cast<const int4*>(a.chunk_cnt) + 2 * t + 1);
-        const unsigned tile_carry = __ldg(&a.tile_carry[t]);
+    unsigned cur = 0u;
+    if (lane == 0) cur = atomicAdd(&a.ctl[CG_W_TILE], 1u);
+    int c = (int)__shfl_sync(FULL, cur, 0);
 
-        /* ---- phase A: the tile's records -> packed shared-memory histogram ---- */
+    while (c < a.n_chunks) {
+        /* the chunk after this one: asked for now, looked at after the stores */
+        unsigned nxt = 0u;
+        if (lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], 1u);
+        const int base = c << CG_CHUNK_SHIFT;
+
+        /* ---- carry in front of the chunk: supers before its super, groups before its group,
+         *      chunks before it (one lane each), summed across the warp ---- */
+        int part = 0;
+        {
+            const int g = c >> LVL, s = c >> (2 * LVL);
+            const int i1 = (g << LVL) + lane, i2 = (s << LVL) + lane;
+            if (i1 < c) part += __ldg(&a.k.cnt1[i1]);
+            if (i2 < g) part += __ldg(&a.k.cnt2[i2]);
+            for (int j = lane; j < s; j += 32) part += __ldg(&a.k.cnt3[j]);
+        }
+
+        /* ---- phase A: the chunk's records -> packed shared-memory histogram ---- */
         if (!unsorted) {
-            const int lo = __ldg(&a.tile_lo[t]), hi = __ldg(&a.tile_lo[t + 1]);
-            for (int i0 = lo + warp * 32; i0 < hi; i0 += NT) {
+            const int lo = min(__ldg(&a.k.chunk_lo[c]), n_reads), hi = min(__ldg(&a.k.chunk_lo[c + 1]), n_reads);
+            for (int i0 = lo; i0 < hi; i0 += 32) {
                 const int i = i0 + lane;
                 const bool in = i < hi;
                 uint2 r = make_uint2(0u, 0u);
@@ -351,101 +367,112 @@ k_depth_pass(const cg_pass_args a)
                 const int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
                 const unsigned off = (unsigned)(pos - base);
                 const bool ok = in && mapq > a.mq_threshold                       /* bam_data.c:205 */
-                                && off < (unsigned)TILE && pos < a.chrom_len;
+                                && off < (unsigned)CG_CHUNK && pos < a.chrom_len;
                 /* warp aggregation: the stream is sorted, so equal positions sit in adjacent lanes */
-                const int key = ok ? (int)off : -1 - lane;
-                const int prev = __shfl_up_sync(FULL, key, 1);
-                const bool leader = (lane == 0) || key != prev;
-                const unsigned lm = __ballot_sync(FULL, leader);
+                int cnt;
+                const bool leader = run_leader(ok ? (int)off : -1 - lane, lane, cnt);
                 if (ok && leader) {
-                    const unsigned above = (lane == 31) ? 0u : (lm & ~((2u << lane) - 1u));
-                    const unsigned cnt = (unsigned)((above ? __ffs(above) - 1 : 32) - lane);
                     if (off & 1u) {
-                        atomicAdd(&bins[off >> 1], cnt << 16);                    /* bam_data.c:213; carry-out = wrap */
+                        atomicAdd(&bins[off >> 1], (unsigned)cnt << 16);          /* bam_data.c:213; carry-out = wrap */
                     } else {
-                        const unsigned old = atomicAdd(&bins[off >> 1], cnt);
+                        const unsigned old = atomicAdd(&bins[off >> 1], (unsigned)cnt);
                         /* the low half wrapped into its neighbour's count: take the carry back out */
-                        if ((old & 0xffffu) + cnt > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
+                        if ((old & 0xffffu) + (unsigned)cnt > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
                     }
                 }
             }
         } else {
             uint4* src = reinterpret_cast<uint4*>(a.depth32 + (size_t)base);
-            for (int q = tid; q < TILE / 8; q += NT) {
+            for (int q = lane; q < CG_CHUNK / 8; q += 32) {
                 const uint4 x = src[2 * q], y = src[2 * q + 1];
-                sm.bins4[q] = make_uint4((x.x & 0xffffu) | (x.y << 16), (x.z & 0xffffu) | (x.w << 16),
-                                         (y.x & 0xffffu) | (y.y << 16), (y.z & 0xffffu) | (y.w << 16));
+                my4[q] = make_uint4((x.x & 0xffffu) | (x.y << 16), (x.z & 0xffffu) | (x.w << 16),
+                                    (y.x & 0xffffu) | (y.y << 16), (y.z & 0xffffu) | (y.w << 16));
                 src[2 * q] = make_uint4(0, 0, 0, 0);                              /* zero at rest */
                 src[2 * q + 1] = make_uint4(0, 0, 0, 0);
             }
         }
-        __syncthreads();
+        const unsigned carry = (unsigned)__reduce_add_sync(FULL, part);
+        __syncwarp();
 
-        /* everyone has read sm.next_tile; fetch the tile after this one while the scan runs */
-        unsigned nxt = 0u;
-        if (tid == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], 1u);
-
-        /* ---- scan: bins -> depth + prefix, one warp per chunk, 8 rows of 256 positions ---- */
-        const int w0 = base / 100;                     /* first GC window overlapping the tile */
+        /* ---- eight row scans at once: lane sums, then eight independent shuffle chains ---- */
+        int ex[ROWS];                                 /* -> prefix in front of this lane's 8 positions, per row */
         {
-            const int cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-            int woff = 0;
+            int tot[ROWS];
 #pragma unroll
-            for (int j = 0; j < 7; j++) woff += (j < warp) ? cc[j] : 0;
-            unsigned run = tile_carry + (unsigned)woff;
-            const int cpos = base + warp * CG_CHUNK + lane * 8;       /* this lane's first position in row 0 */
+            for (int r = 0; r < ROWS; r++) {
+                const uint4 v = my4[r * 32 + lane];
+                tot[r] = add_halves(v.w, add_halves(v.z, add_halves(v.y, add_halves(v.x, 0))));
+                ex[r] = tot[r];
+            }
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+                for (int r = 0; r < ROWS; r++) {
+                    const int o = __shfl_up_sync(FULL, ex[r], d);
+                    if (lane >= d) ex[r] += o;
+                }
+            }
+            unsigned run = carry;
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                const int row_total = __shfl_sync(FULL, ex[r], 31);
+                ex[r] = (int)run + ex[r] - tot[r];
+                run += (unsigned)row_total;
+            }
+        }
+
+        /* ---- rows -> depth + prefix stores ---- */
+        const int w0 = base / 100;                    /* first GC window overlapping the chunk */
+        {
+            const int cpos = base + lane * 8;         /* this lane's first position in row 0 */
             int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
-            int vi = warp * (CG_CHUNK / 8) + lane;                    /* uint4 index into the bins */
             char* dp = reinterpret_cast<char*>(a.depth) + (size_t)cpos * 2;
             char* pp = reinterpret_cast<char*>(a.prefix) + (size_t)cpos * 4;
-#pragma unroll 2
+#pragma unroll
             for (int r = 0; r < ROWS; r++) {
-                const uint4 v = sm.bins4[vi];
-                sm.bins4[vi] = make_uint4(0, 0, 0, 0);                /* clean bins for the next tile */
-                const int s0 = sext16(v.x), s1 = s0 + ((int)v.x >> 16);
-                const int s2 = s1 + sext16(v.y), s3 = s2 + ((int)v.y >> 16);
-                const int s4 = s3 + sext16(v.z), s5 = s4 + ((int)v.z >> 16);
-                const int s6 = s5 + sext16(v.w), s7 = s6 + ((int)v.w >> 16);
-                const int incl = warp_incl_scan(s7, lane);
-                const unsigned b = run + (unsigned)(incl - s7);
-                st_cs_v4(dp, v.x, v.y, v.z, v.w);
-                st_cs_v4(pp, b + s0, b + s1, b + s2, b + s3);
-                st_cs_v4(pp + 16, b + s4, b + s5, b + s6, b + s7);
+                const uint4 v = my4[r * 32 + lane];
+                my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
+                const unsigned b = (unsigned)ex[r];
+                const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
+                const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
+                const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
+                const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
+                st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
+                st_cs_v4(pp + r * 1024, b + s0, b + s1, b + s2, b + s3);
+                st_cs_v4(pp + r * 1024 + 16, b + s4, b + s5, b + s6, b + s7);
                 /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
                 if (wm >= 92) {
                     const int k = 99 - wm;
                     const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
                                  : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
-                    sm.win_end[wq - w0] = (int)(b - tile_carry) + sk;
+                    wend[wq - w0] = (int)(b - carry) + sk;
                 }
-                if (r == ROWS - 1 && tid == NT - 1)                   /* the tile's last position closes a partial window */
-                    sm.win_end[(base + TILE - 1) / 100 - w0] = (int)(b - tile_carry) + s7;
-                run += (unsigned)__shfl_sync(FULL, incl, 31);
-                vi += 32; dp += 512; pp += 1024;
+                if (r == ROWS - 1 && lane == 31)                      /* the chunk's last position closes a partial window */
+                    wend[(base + CG_CHUNK - 1) / 100 - w0] = (int)(b - carry) + s7;
                 wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
                 if (wm >= 100) { wm -= 100; wq++; }
             }
         }
-        if (tid == 0) sm.next_tile = (int)nxt;
-        __syncthreads();
+        __syncwarp();
 
         /* ---- GC-bin sums from window-end prefixes (read_distribution.c:63-73) ---- */
         {
-            const int nwin = (base + TILE - 1) / 100 - w0 + 1;
-            const int tile_end = min(base + TILE, a.chrom_len);
-            if (tid < nwin) {
-                const int w = w0 + tid;
-                const int ws = max(base, 100 * w), we = min(tile_end, 100 * w + 100);
+            const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
+            const int chunk_end = min(base + CG_CHUNK, a.chrom_len);
+            if (lane < nwin) {
+                const int w = w0 + lane;
+                const int ws = max(base, 100 * w), we = min(chunk_end, 100 * w + 100);
                 if (we > ws) {
                     int bin = (int)a.gc[w];                           /* sonic_interval.c:263-272 */
                     if ((unsigned)bin > 100u) bin = 0;
-                    const int sum = sm.win_end[tid] - (tid ? sm.win_end[tid - 1] : 0);
+                    const int sum = wend[lane] - (lane ? wend[lane - 1] : 0);
                     if (sum) atomicAdd(&sm.gc_rd[bin], sum);
                     atomicAdd(&sm.gc_cnt[bin], (unsigned)(we - ws));
                 }
             }
         }
-        /* win_end is next written after the next tile's first barrier, bins after this loop-top read */
+        __syncwarp();
+        c = (int)__shfl_sync(FULL, nxt, 0);
     }
 
     /* ---- CTA epilogue: flush the per-CTA statistics; the last CTA derives the table ---- */
@@ -458,11 +485,23 @@ k_depth_pass(const cg_pass_args a)
     __syncthreads();
     if (tid == 0) sm.is_last = atomicAdd(&a.ctl[CG_W_DONE], 1u) == gridDim.x - 1;
     __syncthreads();
-    if (sm.is_last && tid < CG_GC_BINS) {
+    if (sm.is_last) {
         __threadfence();
-        const long long rd = __ldcg(&a.stats[tid]), cnt = __ldcg(&a.stats[CG_GC_BINS + tid]);
-        a.expected[tid] = expected_of(rd, cnt, tid);
-        if (tid == 0 && (a.ctl[CG_W_FLAGS] & CG_FLAG_RANGE)) atomicOr(a.sticky, CG_FLAG_RANGE);
+        if (tid < CG_GC_BINS) {
+            const long long rd = __ldcg(&a.stats[tid]), cnt = __ldcg(&a.stats[CG_GC_BINS + tid]);
+            a.expected[tid] = expected_of(rd, cnt, tid);
+        }
+        if (warp == NWARP - 1) {
+            /* calc_mu_per_chr, read_distribution.c:35: |sum| <= number of records < 2^31 */
+            int tot = 0;
+            const int n_supers = (a.n_chunks + 1023) >> (2 * LVL);
+            for (int j = lane; j < n_supers; j += 32) tot += a.k.cnt3[j];
+            tot = __reduce_add_sync(FULL, tot);
+            if (lane == 0) {
+                a.stats[2 * CG_GC_BINS] = (long long)tot;
+                if (a.ctl[CG_W_FLAGS] & CG_FLAG_RANGE) atomicOr(a.sticky, CG_FLAG_RANGE);
+            }
+        }
     }
 }
 
@@ -478,7 +517,8 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
         configured = true;
     }
     int grid = n_sms * PASS_CTAS_PER_SM;
-    if (grid > a.n_tiles) grid = a.n_tiles;
+    const int want = (a.n_chunks + NWARP - 1) / NWARP;
+    if (grid > want) grid = want;
     if (grid < 1) grid = 1;
     k_depth_pass<<<grid, NT, smem, s>>>(a);
     return cudaGetLastError();
