@@ -175,6 +175,7 @@ def own_arm(args):
             e0.record()
         for _ in range(k):
             step_fn()
+        ctx.join()                            # cg_stream() now waits for every other stream of the context
         with torch.cuda.stream(ext):
             e1.record()
         ctx.sync()

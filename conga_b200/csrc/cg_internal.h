@@ -75,9 +75,10 @@ int         cgk_depth_pass_ctas_per_sm(void);
 /* genotype.cu */
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
                          const int32_t* prefix, const int8_t* gc, const float* expected,
-                         const cg_maprun* runs, int n_runs, int has_map,
-                         int32_t chrom_len, unsigned int* flags, cg_call* out,
-                         unsigned int* work_counter, unsigned int* work_base, int n_sms);
+                         const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
+                         int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms);
+int         cgk_run_index_words(int32_t chrom_len);
+cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len);
 }
 #endif
 

@@ -3,16 +3,22 @@
  * genotype.cu.  There is no CPU implementation of any stage in this library:
  * without a CUDA device cg_create fails and nothing else can be called.
  *
- * Execution model.  A context owns three streams and two chromosome slots:
- *   s_copy  host->device copies of GC bytes and read batches (HOST pointer mode)
- *   s_depth chromosome init, batch marking, the fused depth pass
- *   s_geno  mappability / CNV uploads, the genotype kernel, result downloads
- * Chromosome k lives in slot k&1 (its own depth, prefix, GC, expected-table,
- * control-word and staging buffers), so the latency-bound genotype kernel of
- * chromosome k runs underneath the bandwidth-bound depth pass of chromosome k+1
- * and the copies of k+1 run underneath the pass of k.  Events order the three
- * streams per slot; nothing ever waits on the host unless the caller asked for
- * blocking HOST-mode semantics.
+ * Execution model.  A context owns two chromosome slots and six streams:
+ *   s_copy     host->device copies of GC bytes and read batches (HOST pointer mode)
+ *   s_slot[2]  one per slot: chromosome init, batch marking, rare paths, the fused depth pass
+ *   s_geno[2]  per slot, deletions / duplications: mappability + CNV uploads, the genotype kernel,
+ *              downloads.  The genotype kernel is a chain of dependent loads whose latency grows
+ *              several-fold under a depth pass that saturates HBM, so the genotype kernels of
+ *              up to CG_NSLOT chromosomes are allowed to run side by side.
+ *   s_main     cg_stream(): statistics reset, and what cg_join() orders behind everything else
+ * Chromosome k lives in slot k&1 (its own records, depth, prefix, GC, expected-table, count and
+ * staging buffers) and nothing of slot 0 depends on slot 1.  So the preparation kernels and the
+ * ramp-up of chromosome k+1's depth pass fill the SMs that chromosome k's pass is draining from,
+ * the latency-bound genotype kernels of k run underneath the bandwidth-bound pass of k+1, and the
+ * copies of k+1 run underneath the pass of k.  Events order the streams per slot; nothing ever
+ * waits on the host unless the caller asked for blocking HOST-mode semantics.  With profiling on
+ * (cg_set_profiling) the slots are chained one behind the other so that the event brackets time
+ * each kernel alone.
  */
 #include "cg_internal.h"
 
@@ -24,7 +30,7 @@
 #include <vector>
 
 #define CG_MAX_CHROMS 4096            /* rows of the statistics table */
-#define CG_NSLOT 2
+#define CG_NSLOT 4
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
 
@@ -45,21 +51,25 @@ struct cg_slot {
     const int8_t* gc_ptr = nullptr;
     /* genotype side */
     cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
+    int32_t* d_run_idx = nullptr;     size_t run_idx_cap = 0;    /* first run per 16384 positions */
     const cg_maprun* runs_ptr = nullptr; int n_runs = 0; int has_map = 0;
     char* d_arena = nullptr;          size_t arena_cap = 0, arena_used = 0;   /* CNV + call staging, HOST mode */
     /* ordering */
     cudaEvent_t ev_copy = nullptr;            /* s_copy: last upload for this slot */
-    cudaEvent_t ev_pass = nullptr;            /* s_depth: the pass (and the table) of this slot is done */
+    cudaEvent_t ev_pass = nullptr;            /* slot stream: the pass (and the table) of this slot is done */
+    cudaStream_t s_geno[2] = {nullptr, nullptr};   /* [0] deletions (and uploads), [1] duplications */
     cudaEvent_t ev_geno[2] = {nullptr, nullptr};   /* s_geno[t]: last genotype work queued for this slot */
     cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded */
-    bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false;
+    bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false, wait_reset = false;
+    uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;    /* out-of-order path only; zero at rest */
 };
 
 struct cg_ctx {
     int device = 0;
     int n_sms = 148;
-    cudaStream_t s_copy = nullptr, s_depth = nullptr;
-    cudaStream_t s_geno[2] = {nullptr, nullptr};  /* [0] deletions (and uploads), [1] duplications */
+    cudaStream_t s_copy = nullptr, s_main = nullptr;
+    cudaStream_t s_slot[CG_NSLOT] = {};
+    cudaEvent_t ev_reset = nullptr;           /* s_main: statistics table cleared */
     cudaEvent_t ev_join = nullptr;
     int ptr_mode = CG_PTR_HOST;
     bool async = false;
@@ -75,11 +85,8 @@ struct cg_ctx {
     long long n_reads = 0;
     int n_rows = 0;
 
-    uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;    /* out-of-order path only; zero at rest */
     long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
     unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
-    unsigned int* d_work = nullptr;           /* [2] monotonic work counters of the genotype kernel, one per stream */
-    unsigned int work_base[2] = {0, 0};
 
     /* pinned staging */
     cg_chrom_stats* h_stats = nullptr;
@@ -114,9 +121,9 @@ static inline bool blocking(const cg_ctx* c) { return c->ptr_mode == CG_PTR_HOST
 static int sync_all(cg_ctx* c)
 {
     CU(c, cudaStreamSynchronize(c->s_copy));
-    CU(c, cudaStreamSynchronize(c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_geno[0]));
-    CU(c, cudaStreamSynchronize(c->s_geno[1]));
+    CU(c, cudaStreamSynchronize(c->s_main));
+    for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_slot[i]));
+    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(c->slot[i].s_geno[t]));
     return CG_OK;
 }
 
@@ -165,11 +172,11 @@ static void prof_collect(cg_ctx* c)
 /* CG_FLAG_RANGE raised on the device since the last report -> CG_ERANGE (caller has synchronised) */
 static int report_sticky(cg_ctx* c, const char* what)
 {
-    CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_geno[0]));
-    CU(c, cudaStreamSynchronize(c->s_geno[0]));
+    CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_main));
     if (c->h_flags[0] & CG_FLAG_RANGE) {
-        CU(c, cudaMemsetAsync(c->d_sticky, 0, 4, c->s_geno[0]));
-        CU(c, cudaStreamSynchronize(c->s_geno[0]));
+        CU(c, cudaMemsetAsync(c->d_sticky, 0, 4, c->s_main));
+        CU(c, cudaStreamSynchronize(c->s_main));
         return fail(c, CG_ERANGE, "%s: a record or interval lies outside [0, chrom_len); it was clipped", what);
     }
     return CG_OK;
@@ -200,22 +207,23 @@ cg_ctx* cg_create(int device)
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
     bool ok = cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
-        && cudaStreamCreateWithPriority(&c->s_depth, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        && cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        && cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming) == cudaSuccess
         /* the genotype kernel is small and latency-bound: let its CTAs be placed first */
-        && cudaStreamCreateWithPriority(&c->s_geno[0], cudaStreamNonBlocking, prio_hi) == cudaSuccess
-        && cudaStreamCreateWithPriority(&c->s_geno[1], cudaStreamNonBlocking, prio_hi) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
         && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
         && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
         && cudaMalloc(&c->d_sticky, 16) == cudaSuccess
         && cudaMemset(c->d_sticky, 0, 16) == cudaSuccess
-        && cudaMalloc(&c->d_work, 16) == cudaSuccess
-        && cudaMemset(c->d_work, 0, 16) == cudaSuccess
         && cudaMallocHost(&c->h_stats, sizeof(cg_chrom_stats)) == cudaSuccess
         && cudaMallocHost(&c->h_flags, 16) == cudaSuccess;
     for (int i = 0; ok && i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
-        ok = cudaMalloc(&s.d_expected, sizeof(float) * 128) == cudaSuccess
+        ok = cudaStreamCreateWithPriority(&c->s_slot[i], cudaStreamNonBlocking, prio_lo) == cudaSuccess
+            /* the genotype kernels are small and latency-bound: let their CTAs be placed first */
+            && cudaStreamCreateWithPriority(&s.s_geno[0], cudaStreamNonBlocking, prio_hi) == cudaSuccess
+            && cudaStreamCreateWithPriority(&s.s_geno[1], cudaStreamNonBlocking, prio_hi) == cudaSuccess
+            && cudaMalloc(&s.d_expected, sizeof(float) * 128) == cudaSuccess
             && cudaMemset(s.d_expected, 0, sizeof(float) * 128) == cudaSuccess
             && cudaMalloc(&s.d_ctl, 16) == cudaSuccess
             && cudaMemset(s.d_ctl, 0, 16) == cudaSuccess
@@ -239,27 +247,30 @@ void cg_destroy(cg_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
-    if (c->s_depth) cudaStreamSynchronize(c->s_depth);
-    for (int t = 0; t < 2; t++) if (c->s_geno[t]) cudaStreamSynchronize(c->s_geno[t]);
+    if (c->s_main) cudaStreamSynchronize(c->s_main);
+    for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamSynchronize(c->s_slot[t]);
+    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamSynchronize(c->slot[i].s_geno[t]);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (int i = 0; i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
         cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_counts);
         cudaFree(s.d_depth); cudaFree(s.d_prefix); cudaFree(s.d_expected); cudaFree(s.d_ctl);
-        cudaFree(s.d_runs); cudaFree(s.d_arena);
+        cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32);
         if (s.ev_copy) cudaEventDestroy(s.ev_copy);
         if (s.ev_pass) cudaEventDestroy(s.ev_pass);
         for (int t = 0; t < 2; t++) if (s.ev_geno[t]) cudaEventDestroy(s.ev_geno[t]);
         if (s.ev_runs) cudaEventDestroy(s.ev_runs);
     }
-    cudaFree(c->d_depth32); cudaFree(c->d_stats); cudaFree(c->d_sticky); cudaFree(c->d_work);
+    cudaFree(c->d_stats); cudaFree(c->d_sticky);
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
-    if (c->s_depth) cudaStreamDestroy(c->s_depth);
-    for (int t = 0; t < 2; t++) if (c->s_geno[t]) cudaStreamDestroy(c->s_geno[t]);
+    if (c->s_main) cudaStreamDestroy(c->s_main);
+    for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamDestroy(c->s_slot[t]);
+    if (c->ev_reset) cudaEventDestroy(c->ev_reset);
+    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamDestroy(c->slot[i].s_geno[t]);
     delete c;
 }
 
@@ -289,20 +300,20 @@ void* cg_alloc_pinned(cg_ctx* c, size_t bytes)
 
 void cg_free_pinned(cg_ctx* c, void* p) { (void)c; if (p) cudaFreeHost(p); }
 
-void* cg_stream(cg_ctx* c) { return c ? (void*)c->s_depth : nullptr; }
+void* cg_stream(cg_ctx* c) { return c ? (void*)c->s_main : nullptr; }
 int64_t cg_launch_count(cg_ctx* c) { return c ? c->launch_count : 0; }
 
-/* make the depth stream (cg_stream) wait for everything queued on the other two */
+/* make the main stream (cg_stream) wait for everything queued on the others */
 int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    for (int t = 0; t < 2; t++) {
-        CU(c, cudaEventRecord(c->ev_join, c->s_geno[t]));
-        CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
+    cudaStream_t all[1 + 3 * CG_NSLOT] = {c->s_copy};
+    for (int i = 0; i < CG_NSLOT; i++) { all[1 + 3 * i] = c->s_slot[i]; all[2 + 3 * i] = c->slot[i].s_geno[0]; all[3 + 3 * i] = c->slot[i].s_geno[1]; }
+    for (int t = 0; t < 1 + 3 * CG_NSLOT; t++) {
+        CU(c, cudaEventRecord(c->ev_join, all[t]));
+        CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
     }
-    CU(c, cudaEventRecord(c->ev_join, c->s_copy));
-    CU(c, cudaStreamWaitEvent(c->s_depth, c->ev_join, 0));
     return CG_OK;
 }
 
@@ -351,7 +362,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         return fail(c, CG_EINVAL, "gc_profile needs >= %d windows for length %d (got %d)", need_windows, chrom_len, n_windows);
     CU(c, cudaSetDevice(c->device));
 
-    const int si = (int)(c->n_begun & 1);
+    const int si = (int)(c->n_begun % CG_NSLOT);
     cg_slot& s = c->slot[si];
     const int n_chunks = (chrom_len + CG_CHUNK - 1) / CG_CHUNK;
     const size_t n_pos = (size_t)n_chunks * CG_CHUNK;
@@ -371,14 +382,15 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         CU(c, cudaMalloc(&s.d_prefix, n_pos * sizeof(int32_t)));
         s.pos_cap = n_pos;
     }
-    if (n_pos > c->depth32_cap) {
+    cudaStream_t ss = c->s_slot[si];
+    if (n_pos > s.depth32_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
-        cudaFree(c->d_depth32); c->d_depth32 = nullptr; c->depth32_cap = 0;
-        CU(c, cudaMalloc(&c->d_depth32, n_pos * sizeof(uint32_t)));
+        cudaFree(s.d_depth32); s.d_depth32 = nullptr; s.depth32_cap = 0;
+        CU(c, cudaMalloc(&s.d_depth32, n_pos * sizeof(uint32_t)));
         /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
-        CU(c, cudaMemsetAsync(c->d_depth32, 0, n_pos * sizeof(uint32_t), c->s_depth));
-        c->depth32_cap = n_pos;
+        CU(c, cudaMemsetAsync(s.d_depth32, 0, n_pos * sizeof(uint32_t), ss));
+        s.depth32_cap = n_pos;
     }
     if (c->ptr_mode == CG_PTR_HOST) {
         int rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows);
@@ -389,8 +401,15 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     for (int t = 0; t < 2; t++) {
         if (!s.geno_queued[t]) continue;
         CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno[t], 0));                  /* d_gc */
-        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_geno[t], 0));                 /* d_prefix, d_expected */
-        if (t == 1) CU(c, cudaStreamWaitEvent(c->s_geno[0], s.ev_geno[1], 0));   /* d_runs is uploaded on s_geno[0] */
+        CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_prefix, d_expected */
+        /* d_runs and the staging arena are written from both genotype streams */
+        CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
+    }
+    if (s.wait_reset) { CU(c, cudaStreamWaitEvent(ss, c->ev_reset, 0)); s.wait_reset = false; }
+    if (c->profiling && !getenv("CG_PROF_NOCHAIN")) {   /* time kernels alone: chain this slot behind the other one */
+        cg_slot& o = c->slot[(si + CG_NSLOT - 1) % CG_NSLOT];
+        if (o.used) CU(c, cudaStreamWaitEvent(ss, o.ev_pass, 0));
+        for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(ss, o.ev_geno[t], 0));
     }
     if (c->ptr_mode == CG_PTR_HOST) {
         CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy));
@@ -410,8 +429,8 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     c->in_chrom = true; c->finished = false;
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
-        prof_scope ps(c, c->s_depth, 0, 1);
-        CU(c, cgk_chrom_init(c->s_depth, s.d_counts, n_chunks,
+        prof_scope ps(c, c->s_slot[c->cur], 0, 1);
+        CU(c, cgk_chrom_init(c->s_slot[c->cur], s.d_counts, n_chunks,
                              c->d_stats + (size_t)chr_index * CG_STATS_WORDS, s.d_ctl));
     }
     return CG_OK;
@@ -432,7 +451,7 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
         if (rc) return rc;
         CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy));
         CU(c, cudaEventRecord(s.ev_copy, c->s_copy));
-        CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_copy, 0));
+        CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));
         s.reads_ptr = s.d_reads;
     } else if (first == 0) {
         s.reads_ptr = reads;                  /* single device batch: used in place */
@@ -440,14 +459,14 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
         const bool external = s.reads_ptr != s.d_reads;
         int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, external ? 0 : (size_t)first);
         if (rc) return rc;
-        if (external) CU(c, cudaMemcpyAsync(s.d_reads, s.reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_depth));
-        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_depth));
+        if (external) CU(c, cudaMemcpyAsync(s.d_reads, s.reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
+        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
         s.reads_ptr = s.d_reads;
     }
     c->n_reads = first + (long long)n;
     {
-        prof_scope ps(c, c->s_depth, 0, 1);
-        CU(c, cgk_mark_batch(c->s_depth, s.reads_ptr, first, (long long)n, cgk_counts_layout(s.d_counts, s.n_chunks),
+        prof_scope ps(c, c->s_slot[c->cur], 0, 1);
+        CU(c, cgk_mark_batch(c->s_slot[c->cur], s.reads_ptr, first, (long long)n, cgk_counts_layout(s.d_counts, s.n_chunks),
                              s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl,
                              c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS));
     }
@@ -461,34 +480,41 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
     long long* row = c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS;
-    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_depth, s.ev_copy, 0));   /* GC bytes */
+    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));   /* GC bytes */
     {
-        prof_scope ps(c, c->s_depth, 0, 2);
-        CU(c, cgk_rare_paths(c->s_depth, s.reads_ptr, c->n_reads, c->d_depth32, cgk_counts_layout(s.d_counts, s.n_chunks),
+        prof_scope ps(c, c->s_slot[c->cur], 0, 2);
+        CU(c, cgk_rare_paths(c->s_slot[c->cur], s.reads_ptr, c->n_reads, s.d_depth32, cgk_counts_layout(s.d_counts, s.n_chunks),
                              s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
     }
     {
-        prof_scope ps(c, c->s_depth, 1, 1);
+        /* One depth pass at a time: two passes side by side double the number of concurrent write
+         * streams and cost HBM efficiency (measured).  Everything else of this chromosome — init,
+         * batch marking, copies — has already overlapped the previous chromosome's pass. */
+        cg_slot& o = c->slot[(c->cur + CG_NSLOT - 1) % CG_NSLOT];
+        if (o.used) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
+    }
+    {
+        prof_scope ps(c, c->s_slot[c->cur], 1, 1);
         cg_pass_args a;
         a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.k = cgk_counts_layout(s.d_counts, s.n_chunks);
         a.gc = s.gc_ptr;
         a.chrom_len = s.chrom_len; a.n_chunks = s.n_chunks; a.mq_threshold = c->mq_threshold;
-        a.depth = s.d_depth; a.prefix = s.d_prefix; a.depth32 = c->d_depth32; a.ctl = s.d_ctl;
+        a.depth = s.d_depth; a.prefix = s.d_prefix; a.depth32 = s.d_depth32; a.ctl = s.d_ctl;
         a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
-        CU(c, cgk_depth_pass(c->s_depth, a, c->n_sms));
+        CU(c, cgk_depth_pass(c->s_slot[c->cur], a, c->n_sms));
     }
-    CU(c, cudaEventRecord(s.ev_pass, c->s_depth));
+    CU(c, cudaEventRecord(s.ev_pass, c->s_slot[c->cur]));
     c->finished = true;
     if (c->ptr_mode == CG_PTR_DEVICE) {
-        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->s_depth));
+        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
         return CG_OK;
     }
     if (c->async) {                       /* `out` is page-locked and is valid after cg_sync */
-        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_depth));
+        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
         return CG_OK;
     }
-    CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_depth));
+    CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
+    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
     if (out) memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
     return report_sticky(c, "cg_chrom_finish");
 }
@@ -500,8 +526,8 @@ int cg_get_expected(cg_ctx* c, float expected[CG_GC_BINS])
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
     CU(c, cudaMemcpyAsync(expected, s.d_expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c->s_depth));
-    if (blocking(c)) CU(c, cudaStreamSynchronize(c->s_depth));
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
+    if (blocking(c)) CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
     return CG_OK;
 }
 
@@ -512,8 +538,8 @@ int cg_set_expected(cg_ctx* c, const float expected[CG_GC_BINS])
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
     CU(c, cudaMemcpyAsync(s.d_expected, expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, c->s_depth));
-    CU(c, cudaEventRecord(s.ev_pass, c->s_depth));        /* the genotype stream waits for this */
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
+    CU(c, cudaEventRecord(s.ev_pass, c->s_slot[c->cur]));        /* the genotype stream waits for this */
     return CG_OK;
 }
 
@@ -529,14 +555,23 @@ int cg_set_mappability_runs(cg_ctx* c, const cg_maprun* runs, size_t n, int enab
     s.n_runs = (int)n;
     if (n == 0) { s.runs_ptr = nullptr; return CG_OK; }
     if (!runs) return fail(c, CG_EINVAL, "null runs");
-    if (c->ptr_mode == CG_PTR_DEVICE) { s.runs_ptr = runs; return CG_OK; }
-    int rc = grow(c, &s.d_runs, &s.runs_cap, n);
+    int rc = grow(c, &s.d_run_idx, &s.run_idx_cap, (size_t)cgk_run_index_words(s.chrom_len));
     if (rc) return rc;
-    /* on a genotype stream: behind the slot's previous tenant, which may still read d_runs */
-    CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, c->s_geno[0]));
-    CU(c, cudaEventRecord(s.ev_runs, c->s_geno[0]));
+    if (c->ptr_mode == CG_PTR_DEVICE) {
+        s.runs_ptr = runs;
+    } else {
+        rc = grow(c, &s.d_runs, &s.runs_cap, n);
+        if (rc) return rc;
+        /* on a genotype stream: behind the slot's previous tenant, which may still read d_runs */
+        CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, s.s_geno[0]));
+        s.runs_ptr = s.d_runs;
+    }
+    {
+        prof_scope ps(c, s.s_geno[0], 2, 1);
+        CU(c, cgk_run_index(s.s_geno[0], s.runs_ptr, (int)n, s.d_run_idx, s.chrom_len));
+    }
+    CU(c, cudaEventRecord(s.ev_runs, s.s_geno[0]));
     s.runs_uploaded = true;
-    s.runs_ptr = s.d_runs;
     return CG_OK;
 }
 
@@ -551,7 +586,7 @@ int cg_set_mappability(cg_ctx* c, const cg_mapiv* rows, size_t n)
     c->ptr_mode = CG_PTR_HOST;                                 /* rows are always host memory */
     int rc = cg_set_mappability_runs(c, v.data(), v.size(), n > 0);
     if (rc == CG_OK && !v.empty()) {
-        cudaError_t e = cudaStreamSynchronize(c->s_geno[0]);   /* v dies at return */
+        cudaError_t e = cudaStreamSynchronize(c->slot[c->cur].s_geno[0]);   /* v dies at return */
         if (e != cudaSuccess) rc = fail(c, CG_ECUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e));
     }
     c->ptr_mode = saved;
@@ -588,7 +623,7 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
     const int t = is_dup ? 1 : 0;
-    cudaStream_t st = c->s_geno[t];           /* deletions and duplications of one chromosome run side by side */
+    cudaStream_t st = s.s_geno[t];            /* deletions and duplications of one chromosome run side by side */
     const cg_cnv* d_in = cnvs; cg_call* d_out = out;
     if (c->ptr_mode == CG_PTR_HOST) {
         cg_cnv* a_in = nullptr;
@@ -601,8 +636,8 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
     {
         prof_scope ps(c, st, 2, 1);
-        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_prefix, s.gc_ptr, s.d_expected, s.runs_ptr, s.n_runs, s.has_map,
-                           s.chrom_len, c->d_sticky, d_out, c->d_work + t, &c->work_base[t], c->n_sms));
+        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_prefix, s.gc_ptr, s.d_expected, s.runs_ptr, s.d_run_idx, s.n_runs, s.has_map,
+                           s.chrom_len, c->d_sticky, d_out, c->n_sms));
     }
     if (c->ptr_mode == CG_PTR_HOST)
         CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, st));
@@ -622,8 +657,8 @@ int cg_download_depth(cg_ctx* c, int16_t* out)
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_depth before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(out, s.d_depth, (size_t)s.chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_depth));
+    CU(c, cudaMemcpyAsync(out, s.d_depth, (size_t)s.chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
+    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
     return CG_OK;
 }
 
@@ -633,8 +668,8 @@ int cg_download_prefix(cg_ctx* c, int32_t* out)
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_prefix before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(out, s.d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_depth));
+    CU(c, cudaMemcpyAsync(out, s.d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
+    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
     return CG_OK;
 }
 
@@ -660,7 +695,11 @@ int cg_stats_reset(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)(c->n_rows > 0 ? c->n_rows : 1), c->s_depth));
+    int rc = cg_join(c);                      /* rows may still be written or copied by queued work */
+    if (rc) return rc;
+    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)(c->n_rows > 0 ? c->n_rows : 1), c->s_main));
+    CU(c, cudaEventRecord(c->ev_reset, c->s_main));
+    for (int i = 0; i < CG_NSLOT; i++) c->slot[i].wait_reset = true;
     c->n_rows = 0;
     return CG_OK;
 }
@@ -670,9 +709,11 @@ int cg_stats_row(cg_ctx* c, int chr_index, cg_chrom_stats* out)
     if (!c || !out) return fail(c, CG_EINVAL, "null argument");
     if (chr_index < 0 || chr_index >= CG_MAX_CHROMS) return fail(c, CG_EINVAL, "chr_index %d out of range", chr_index);
     CU(c, cudaSetDevice(c->device));
+    int rc = sync_all(c);
+    if (rc) return rc;
     CU(c, cudaMemcpyAsync(c->h_stats, c->d_stats + (size_t)chr_index * CG_STATS_WORDS, sizeof(cg_chrom_stats),
-                          cudaMemcpyDeviceToHost, c->s_depth));
-    CU(c, cudaStreamSynchronize(c->s_depth));
+                          cudaMemcpyDeviceToHost, c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_main));
     memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
     return CG_OK;
 }

@@ -36,6 +36,7 @@
  * shared GC accumulators.
  */
 #include "cg_internal.h"
+#include <cstdlib>
 
 #define FULL 0xffffffffu
 #define NT   CG_PASS_THREADS
@@ -300,7 +301,11 @@ struct __align__(16) pass_smem {
     int is_last;
 };
 
-#define PASS_CTAS_PER_SM 5
+#define PASS_CTAS_PER_SM 5            /* register/shared-memory budget the kernel is compiled for */
+/* CTAs per SM one launch asks for.  Measured on B200 (C2 chromosomes, pass alone): 1 -> 4.9, 2 -> 6.1,
+ * 3 -> 5.6, 4 -> 5.2, 5 -> 5.1 TB/s: more resident warps mean more concurrent write streams and
+ * worse HBM efficiency; the rest of the SM stays free for the genotype and preparation kernels. */
+#define PASS_GRID_CTAS_PER_SM 2
 
 /* expected_read_depth[101], read_distribution.c:75-83:
  *   expected[0] = 0; expected[i] = (float)rd_per_gc[i] / window_per_gc[i]; NaN / Inf -> 0.
@@ -516,7 +521,13 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    int grid = n_sms * PASS_CTAS_PER_SM;
+    static int ctas_per_sm = 0;               /* CG_PASS_CTAS: CTAs per SM one launch asks for (tuning) */
+    if (!ctas_per_sm) {
+        const char* e = getenv("CG_PASS_CTAS");
+        ctas_per_sm = e ? atoi(e) : PASS_GRID_CTAS_PER_SM;
+        if (ctas_per_sm < 1 || ctas_per_sm > PASS_CTAS_PER_SM) ctas_per_sm = PASS_CTAS_PER_SM;
+    }
+    int grid = n_sms * ctas_per_sm;
     const int want = (a.n_chunks + NWARP - 1) / NWARP;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;

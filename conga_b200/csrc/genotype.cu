@@ -24,6 +24,7 @@
  */
 #include "cg_internal.h"
 #include <math.h>
+#include <stdlib.h>
 
 #define FULL 0xffffffffu
 
@@ -201,22 +202,59 @@ __device__ __forceinline__ unsigned load_gc4(const int8_t* __restrict__ gc, int 
     return v;
 }
 
-/* ---- one warp per CNV --------------------------------------------------------
- * expected_rd: each lane takes 4 consecutive GC windows (one coalesced 32-bit load), turns them
- * into integer increments under the current exponent, and a warp scan finds how far the chain
- * runs before anything unusual (binade boundary, tie, E still zero).  Everything before that
- * point is committed as ONE integer addition to E's bit pattern — bit-identical to the
- * reference's per-base fadd chain — the offending lane replays its 4 windows through
- * add_run_f32, and the scan resumes behind it.  mappability_score: the same over 32 runs of
- * the flattened track per step, in fp64.  The likelihood stage then uses lanes 0..2 for the
- * three hypotheses and lane 3 for lgamma. */
-#define GENO_WARPS 8
+__device__ __forceinline__ cg_cnv make_cnv(int a, int b) { cg_cnv v; v.start = a; v.end = b; return v; }
 
+/* ---- G CNVs per warp ---------------------------------------------------------
+ * The work per CNV is irregular (a few windows to several thousand) and the exact fp32 chain
+ * has a serial, branchy ramp-up: while E is small every addition changes its exponent.  A warp
+ * therefore owns G consecutive CNVs, one per lane, and works in four phases:
+ *   0  lane = CNV: record, the two prefix words -> observed_rd
+ *   1  lane = CNV: the first RAMP windows of the expected chain and the whole mappability chain,
+ *      literally / run by run (add_run_f32, add_run_f64_fast): every lane busy with its own CNV
+ *   2  warp = one CNV at a time, for the CNVs longer than RAMP windows: each lane takes 4
+ *      consecutive GC windows (one coalesced 32-bit load), turns them into integer increments
+ *      under the current exponent, and a warp scan finds how far the chain runs before anything
+ *      unusual (binade boundary, tie).  Everything before that point is committed as ONE integer
+ *      addition to E's bit pattern — bit-identical to the reference's per-base fadd chain — the
+ *      offending lane replays its 4 windows through add_run_f32, and the scan resumes behind it
+ *   3  lane = CNV: lgamma, three log-likelihoods, c-score, copy number
+ * Phases 0, 1 and 3 run at full SIMT width; only the long, regular part of a long CNV uses the
+ * warp cooperatively.  A launch needs n/G warps, which leaves the SMs to the depth pass it runs
+ * underneath. */
+#define GENO_WARPS 4                        /* warps per CTA */
+#define GENO_RAMP 32                        /* windows of the expected chain walked lane-serially */
+#define RUN_BUCKET_SHIFT 14                 /* run_idx[b] = first run whose end lies beyond position b << 14 */
+
+/* index of the flattened mappability track: one entry per 16384 positions */
+__global__ void k_run_index(const cg_maprun* __restrict__ runs, int n_runs, int32_t* run_idx, int n_buckets)
+{
+    const int stride = gridDim.x * blockDim.x;
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= n_runs; r += stride) {
+        const long long prev_end = r ? runs[r - 1].end : 0;
+        const long long end = r < n_runs ? runs[r].end : ((long long)n_buckets << RUN_BUCKET_SHIFT) + 1;
+        /* buckets whose first position p satisfies prev_end <= p < end: run r is the first one ending beyond p */
+        for (long long b = (prev_end + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT; b <= n_buckets && (b << RUN_BUCKET_SHIFT) < end; b++)
+            run_idx[b] = r;
+    }
+}
+
+int cgk_run_index_words(int32_t chrom_len) { return ((chrom_len + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT) + 2; }
+
+cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len)
+{
+    const int n_buckets = cgk_run_index_words(chrom_len) - 1;
+    int blocks = (n_runs + 256) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    k_run_index<<<blocks, 256, 0, s>>>(runs, n_runs, run_idx, n_buckets);
+    return cudaGetLastError();
+}
+
+template <int G>
 __global__ void __launch_bounds__(GENO_WARPS * 32)
 k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __restrict__ prefix,
            const int8_t* __restrict__ gc, const float* __restrict__ expected,
-           const cg_maprun* __restrict__ runs, int n_runs, int has_map, int32_t chrom_len,
-           unsigned int* flags, cg_call* out, unsigned int* work_counter, unsigned int work_base, int dynamic)
+           const cg_maprun* __restrict__ runs, const int32_t* __restrict__ run_idx, int n_runs, int has_map,
+           int32_t chrom_len, unsigned int* flags, cg_call* out)
 {
     __shared__ unsigned s_expb[CG_GC_BINS];             /* bit patterns of expected_read_depth[] */
     for (int i = threadIdx.x; i < CG_GC_BINS; i += blockDim.x) s_expb[i] = __float_as_uint(expected[i]);
@@ -224,26 +262,125 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
     const int lane = threadIdx.x & 31;
     const int n_warps = gridDim.x * GENO_WARPS;
     const int n_windows = (chrom_len + 99) / 100;
-    int c = blockIdx.x * GENO_WARPS + (threadIdx.x >> 5);
+    const bool use_map = has_map && n_runs > 0;
+    const int n_groups = (n + G - 1) / G;
 
-    while (c < n) {
-        const cg_cnv v = cnvs[c];
+    for (int grp = blockIdx.x * GENO_WARPS + (threadIdx.x >> 5); grp < n_groups; grp += n_warps) {
+        /* ---- phase 0: lane = CNV ---- */
+        const int c = grp * G + lane;
+        const bool valid = lane < G && c < n;
+        cg_cnv v = make_cnv(0, 0);
+        if (valid) v = cnvs[c];
         int s = v.start, e = v.end;
-        if (s < 0 || e > chrom_len) { if (lane == 0) atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
-        int pfx = 0;                                    /* lane 0: P[e-1], lane 1: P[s-1] */
-        if (e > s) {
-            if (lane == 0) pfx = __ldg(&prefix[e - 1]);
-            if (lane == 1 && s > 0) pfx = __ldg(&prefix[s - 1]);
+        if (valid && (s < 0 || e > chrom_len)) { atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
+        const bool any = valid && e > s;
+        int p_hi = 0, p_lo = 0;
+        if (any) {
+            p_hi = __ldg(&prefix[e - 1]);
+            if (s > 0) p_lo = __ldg(&prefix[s - 1]);
+        }
+        const int w_last = any ? (e - 1) / 100 : -1;
+        int w = any ? s / 100 : 0;                      /* next window of the expected chain */
+        int r_lo = 0, r_hi = 0;                         /* the first run ending beyond s lies in [r_lo, r_hi] */
+        if (use_map && any) {
+            r_lo = __ldg(&run_idx[s >> RUN_BUCKET_SHIFT]);
+            r_hi = __ldg(&run_idx[(s >> RUN_BUCKET_SHIFT) + 1]);
         }
 
-        /* ---- expected_rd (likelihood.c:115-119) ---- */
-        unsigned B = 0u;                                /* bits of the float accumulator, warp-uniform */
-        if (e > s) {
-            const int w_first = s / 100, w_last = (e - 1) / 100;
-            for (int wb = w_first & ~3; wb <= w_last; wb += 128) {
+        /* ---- phase 1: expected_rd ramp-up (likelihood.c:115-119), window by window ---- */
+        float E = 0.0f;
+        for (int i = 0; i < GENO_RAMP && w <= w_last; i++, w++) {
+            int bin = (int)__ldg(&gc[w]);                                          /* sonic_interval.c:263-272 */
+            if ((unsigned)bin > 100u) bin = 0;
+            E = add_run_f32(E, __uint_as_float(s_expb[bin]), min(e, 100 * w + 100) - max(s, 100 * w));
+        }
+
+        /* ---- phase 1: first mappability run of the CNV (a crowded index bucket is bisected) ---- */
+        if (use_map && any) {
+            while (r_hi - r_lo > 8) {
+                const int mid = (r_lo + r_hi) >> 1;
+                if (__ldg(&runs[mid].end) > s) r_hi = mid; else r_lo = mid + 1;
+            }
+        }
+
+        /* ---- phase 2: mappability_score (likelihood.c:122-123), one CNV at a time: 32 runs of the
+         *      flattened track per step, fp64 twin of the expected chain below; the first block of
+         *      the next CNV and the next block of this one are asked for ahead of use ---- */
+        double S = 0.0;
+        {
+            unsigned todo = __ballot_sync(FULL, use_map && any);
+            const cg_maprun none = {0x7fffffff, 0x7fffffff, 0.0f, 0};
+            cg_maprun q_first = none;
+            if (todo) {
+                const int r0 = __shfl_sync(FULL, r_lo, __ffs(todo) - 1);
+                if (r0 + lane < n_runs) q_first = runs[r0 + lane];
+            }
+            while (todo) {
+                const int L = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const int cs = __shfl_sync(FULL, s, L), ce = __shfl_sync(FULL, e, L), r0 = __shfl_sync(FULL, r_lo, L);
+                cg_maprun q = q_first;
+                q_first = none;
+                if (todo) {
+                    const int rn = __shfl_sync(FULL, r_lo, __ffs(todo) - 1);
+                    if (rn + lane < n_runs) q_first = runs[rn + lane];
+                }
+                unsigned long long MB = 0ull;           /* bits of the double accumulator */
+                for (int rb = r0; rb < n_runs; rb += 32) {
+                    const bool past = q.start >= ce;
+                    const bool more = !__any_sync(FULL, past);
+                    cg_maprun qn = none;
+                    if (more && rb + 32 + lane < n_runs) qn = runs[rb + 32 + lane];
+                    const int k = past ? 0 : max(0, min(ce, q.end) - max(cs, q.start));   /* runs ending before s add nothing */
+                    const unsigned long long vbits = (unsigned long long)__double_as_longlong((double)q.val);
+                    int pos = 0;
+                    for (;;) {
+                        const unsigned ee = (unsigned)(MB >> 52);
+                        bool bad = false;
+                        unsigned long long t = 0ull;
+                        if (lane >= pos && k > 0 && (vbits << 1) != 0ull) {
+                            if (ee == 0u || ee >= 0x7ffu) {
+                                bad = true;             /* zero / negative / non-finite accumulator */
+                            } else {
+                                const unsigned long long d = step_delta_f64(vbits, ee, bad);
+                                t = (__umul64hi((unsigned long long)k, d) != 0ull) ? 0x10000000000000ull
+                                                                                  : min((unsigned long long)k * d, 0x10000000000000ull);
+                            }
+                        }
+                        const unsigned long long incl = warp_incl_scan_u64(t, lane);
+                        const unsigned long long room = 0xfffffffffffffull - (MB & 0xfffffffffffffull);
+                        const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
+                        if (m == 0u) { MB += __shfl_sync(FULL, incl, 31); break; }
+                        const int f = __ffs(m) - 1;
+                        MB += __shfl_sync(FULL, incl - t, f);
+                        unsigned long long Mf = 0ull;
+                        if (lane == f) Mf = (unsigned long long)__double_as_longlong(add_run_f64(__longlong_as_double((long long)MB), (double)q.val, k));
+                        MB = __shfl_sync(FULL, Mf, f);
+                        pos = f + 1;
+                        if (pos >= 32) break;
+                    }
+                    if (!more) break;
+                    q = qn;
+                }
+                if (lane == L) S = __longlong_as_double((long long)MB);
+            }
+        }
+
+        /* ---- phase 2: the rest of the long expected chains, one CNV at a time across the warp ---- */
+        unsigned todo = __ballot_sync(FULL, any && w <= w_last);
+        while (todo) {
+            const int L = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int cs = __shfl_sync(FULL, s, L), ce = __shfl_sync(FULL, e, L);
+            const int w_from = __shfl_sync(FULL, w, L), cw_last = (ce - 1) / 100;
+            unsigned B = __shfl_sync(FULL, __float_as_uint(E), L);                 /* bits of the accumulator, warp-uniform */
+            int wb = w_from & ~3;
+            unsigned g4 = 0u;
+            if (wb + 4 * lane <= cw_last) g4 = load_gc4(gc, wb + 4 * lane, n_windows);
+            for (; wb <= cw_last; wb += 128) {
                 const int w4 = wb + 4 * lane;
-                unsigned g4 = 0u;
-                if (w4 <= w_last) g4 = load_gc4(gc, w4, n_windows);
+                unsigned g4n = 0u;                      /* the block after this one */
+                if (w4 + 128 <= cw_last) g4n = load_gc4(gc, w4 + 128, n_windows);
                 unsigned vb[4]; int kk[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -251,7 +388,7 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                     int bin = (int)(signed char)(g4 >> (8 * j));
                     if ((unsigned)bin > 100u) bin = 0;
                     vb[j] = s_expb[bin];
-                    kk[j] = (wj < w_first || wj > w_last) ? 0 : min(e, 100 * wj + 100) - max(s, 100 * wj);
+                    kk[j] = (wj < w_from || wj > cw_last) ? 0 : min(ce, 100 * wj + 100) - max(cs, 100 * wj);
                 }
                 int pos = 0;
                 for (;;) {
@@ -279,95 +416,39 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                     B += __shfl_sync(FULL, incl - t, f);            /* everything before lane f, exactly */
                     unsigned Bf = 0u;
                     if (lane == f) {
-                        float E = __uint_as_float(B);
+                        float Ef = __uint_as_float(B);
 #pragma unroll
-                        for (int j = 0; j < 4; j++) E = add_run_f32(E, __uint_as_float(vb[j]), kk[j]);
-                        Bf = __float_as_uint(E);
+                        for (int j = 0; j < 4; j++) Ef = add_run_f32(Ef, __uint_as_float(vb[j]), kk[j]);
+                        Bf = __float_as_uint(Ef);
                     }
                     B = __shfl_sync(FULL, Bf, f);
                     pos = f + 1;
                     if (pos >= 32) break;
                 }
+                g4 = g4n;
             }
+            if (lane == L) E = __uint_as_float(B);
         }
 
-        /* ---- mappability_score (likelihood.c:122-123) ---- */
-        unsigned long long MB = 0ull;                   /* bits of the double accumulator */
-        if (has_map && e > s && n_runs > 0) {
-            /* first run whose end lies beyond s: 32-ary search, one probe per lane */
-            int lo = 0, hi = n_runs;                    /* answer in [lo, hi] */
-            while (hi - lo > 0) {
-                const int step = (hi - lo + 31) / 32;
-                const int idx = min(lo + (lane + 1) * step - 1, hi - 1);
-                const bool beyond = __ldg(&runs[idx].end) > s;
-                const unsigned bm = __ballot_sync(FULL, beyond);
-                if (bm == 0u) { lo = hi; break; }
-                const int fl = __ffs(bm) - 1;
-                const int nhi = min(lo + (fl + 1) * step - 1, hi - 1);
-                lo = fl == 0 ? lo : min(lo + fl * step, hi - 1);
-                hi = nhi;
-                if (step == 1) { lo = hi; break; }
-            }
-            for (int rb = lo; rb < n_runs; rb += 32) {
-                const int r = rb + lane;
-                cg_maprun q; q.start = 0x7fffffff; q.end = 0x7fffffff; q.val = 0.0f;
-                if (r < n_runs) q = runs[r];
-                const bool past = q.start >= e;
-                const int k = past ? 0 : min(e, q.end) - max(s, q.start);
-                const unsigned long long vbits = (unsigned long long)__double_as_longlong((double)q.val);
-                int pos = 0;
-                for (;;) {
-                    const unsigned ee = (unsigned)(MB >> 52);
-                    bool bad = false;
-                    unsigned long long t = 0ull;
-                    if (lane >= pos && k > 0 && (vbits << 1) != 0ull) {
-                        if (ee == 0u || ee >= 0x7ffu) {
-                            bad = true;                 /* zero / negative / non-finite accumulator */
-                        } else {
-                            const unsigned long long d = step_delta_f64(vbits, ee, bad);
-                            t = (__umul64hi((unsigned long long)k, d) != 0ull) ? 0x10000000000000ull
-                                                                              : min((unsigned long long)k * d, 0x10000000000000ull);
-                        }
-                    }
-                    const unsigned long long incl = warp_incl_scan_u64(t, lane);
-                    const unsigned long long room = 0xfffffffffffffull - (MB & 0xfffffffffffffull);
-                    const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
-                    if (m == 0u) { MB += __shfl_sync(FULL, incl, 31); break; }
-                    const int f = __ffs(m) - 1;
-                    MB += __shfl_sync(FULL, incl - t, f);
-                    unsigned long long Mf = 0ull;
-                    if (lane == f) Mf = (unsigned long long)__double_as_longlong(add_run_f64(__longlong_as_double((long long)MB), (double)q.val, k));
-                    MB = __shfl_sync(FULL, Mf, f);
-                    pos = f + 1;
-                    if (pos >= 32) break;
-                }
-                if (__any_sync(FULL, past)) break;
-            }
-        }
-
-        /* ---- observed_rd, likelihoods, c-score, copy number ---- */
-        const int obs = __shfl_sync(FULL, pfx, 0) - __shfl_sync(FULL, pfx, 1);      /* likelihood.c:120 */
-        const float E = __uint_as_float(B);
-        double term = 0.0;
-        if (lane == 3) {
-            term = lgamma((double)(obs + 1));                                      /* likelihood.c:104 */
-        } else if (lane < 3) {
-            double lambda;
-            if (lane == 2)      lambda = (double)E;                                /* lnone:   :135 / :157 */
-            else if (lane == 1) lambda = (is_dup ? 1.5 : 0.5) * (double)E;         /* lhetero: :134 / :156 */
-            else                lambda = is_dup ? (double)__fmul_rn(2.0f, E) : 0.0;   /* lhomo: :133 / :155 */
-            if (lambda == 0.0) lambda = 0.01;                                      /* :100-102 */
-            term = __dsub_rn(__dmul_rn((double)obs, log(lambda)), lambda);
-        }
-        const double lg = __shfl_sync(FULL, term, 3);
-        const double l = __dsub_rn(term, lg);
-        const double lhomo = __shfl_sync(FULL, l, 0), lhetero = __shfl_sync(FULL, l, 1), lnone = __shfl_sync(FULL, l, 2);
-        if (lane == 0) {
+        /* ---- phase 3: observed_rd, likelihoods, c-score, copy number; lane = CNV ---- */
+        if (valid) {
+            const int obs = p_hi - p_lo;                                           /* likelihood.c:120 */
+            const double k = (double)obs;
+            const double lg = lgamma((double)(obs + 1));                           /* likelihood.c:104 */
+            double lam_homo = is_dup ? (double)__fmul_rn(2.0f, E) : 0.0;           /* :133 / :155 (float product) */
+            double lam_het = (is_dup ? 1.5 : 0.5) * (double)E;                     /* :134 / :156 */
+            double lam_none = (double)E;                                           /* :135 / :157 */
+            if (lam_homo == 0.0) lam_homo = 0.01;                                  /* :100-102 */
+            if (lam_het == 0.0) lam_het = 0.01;
+            if (lam_none == 0.0) lam_none = 0.01;
+            const double lhomo = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_homo)), lam_homo), lg);
+            const double lhetero = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_het)), lam_het), lg);
+            const double lnone = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_none)), lam_none), lg);
             const int ih = c_double_to_int(lhomo), it = c_double_to_int(lhetero);
             cg_call o;
             o.observed = obs;
             o.expected = E;
-            o.mappability = has_map ? __longlong_as_double((long long)MB) / (double)(v.end - v.start) : 0.0;   /* :128 */
+            o.mappability = has_map ? S / (double)(v.end - v.start) : 0.0;         /* :128 */
             o.lhomo = lhomo; o.lhetero = lhetero; o.lnone = lnone;
             o.score = (double)(ih < it ? it : ih) / lnone;                         /* :138 / :160 */
             if (!is_dup) o.copy_number = (__int2float_rn(obs) < __fdiv_rn(E, 4.0f)) ? 2 : 1;   /* :146-149 */
@@ -378,35 +459,23 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
             o.margin_flags = mf;
             out[c] = o;
         }
-
-        if (!dynamic) break;                            /* n <= warps in the grid: one CNV per warp */
-        unsigned nxt = 0u;
-        if (lane == 0) nxt = atomicAdd(work_counter, 1u) - work_base;
-        c = n_warps + (int)__shfl_sync(FULL, nxt, 0);
     }
 }
 
-int cgk_genotype_warps(int n, int n_sms)
-{
-    int blocks = (n + GENO_WARPS - 1) / GENO_WARPS;
-    const int cap = n_sms * 4;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return blocks * GENO_WARPS;
-}
+#ifndef GENO_G
+#define GENO_G 16                           /* CNVs per warp */
+#endif
 
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
                          const int32_t* prefix, const int8_t* gc, const float* expected,
-                         const cg_maprun* runs, int n_runs, int has_map,
-                         int32_t chrom_len, unsigned int* flags, cg_call* out,
-                         unsigned int* work_counter, unsigned int* work_base, int n_sms)
+                         const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
+                         int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms)
 {
     if (n <= 0) return cudaSuccess;
-    const int warps = cgk_genotype_warps(n, n_sms);
-    const int dynamic = n > warps;
-    k_genotype<<<warps / GENO_WARPS, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, prefix, gc, expected, runs, n_runs, has_map,
-                                                             chrom_len, flags, out, work_counter, *work_base, dynamic);
-    /* in dynamic mode every warp draws exactly one index past the end and the n - warps real ones */
-    if (dynamic) *work_base += (unsigned)n;
+    const int n_groups = (n + GENO_G - 1) / GENO_G;
+    int blocks = (n_groups + GENO_WARPS - 1) / GENO_WARPS;
+    if (blocks > n_sms * 2) blocks = n_sms * 2;
+    k_genotype<GENO_G><<<blocks, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, prefix, gc, expected, runs, run_idx, n_runs,
+                                                          has_map, chrom_len, flags, out);
     return cudaGetLastError();
 }
