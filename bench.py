@@ -152,7 +152,8 @@ def own_arm(args):
     torch.cuda.synchronize()
 
     def step_device():
-        ctx.stats_reset()
+        if world > 1:
+            ctx.stats_reset()                 # rows of the other ranks' chromosomes must be zero again before the all-reduce
         for r in res:
             c = r["c"]
             ctx.chrom_begin(c.index, c.length, r["gc"], mq, n_windows=len(c.gc))
@@ -162,8 +163,8 @@ def own_arm(args):
                 ctx.set_mappability_runs(r["runs"], r["n_runs"], True)
             ctx.genotype(r["dels"], False, r["out_del"], n=len(c.dels))
             ctx.genotype(r["dups"], True, r["out_dup"], n=len(c.dups))
-        ctx.join()                            # main stream now waits for the genotype stream
         if world > 1:
+            ctx.join()                        # main stream now waits for every stream of the context
             with torch.cuda.stream(ext):
                 dist.all_reduce(table)
 
@@ -228,7 +229,8 @@ def own_arm(args):
     BATCH = 1 << 22
 
     def step_host():
-        ctx.stats_reset()
+        if world > 1:
+            ctx.stats_reset()
         for (c, pr, pg, pd, pu, od, ou, st, prn) in host:
             ctx._ck(lib.cg_chrom_begin(h, c.index, c.length, pg.ctypes.data, len(pg), mq))
             for i in range(0, len(pr), BATCH):

@@ -14,7 +14,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libconga_gpu.so")
+LIB_PATH = os.environ.get("CG_LIB") or os.path.join(_HERE, "libconga_gpu.so")   # CG_LIB: tuning builds only
 
 CG_OK, CG_EINVAL, CG_ECUDA, CG_ENOMEM, CG_ERANGE = 0, -1, -2, -3, -4
 CG_PTR_HOST, CG_PTR_DEVICE = 0, 1

@@ -28,6 +28,18 @@
 
 #define FULL 0xffffffffu
 
+#ifdef CG_DEBUG_COUNTERS                     /* tuning builds only (scripts/build_variant.sh ... -DCG_DEBUG_COUNTERS) */
+__device__ unsigned long long g_dbg[16];
+#define DBG(i) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_dbg[i], 1ull); } while (0)
+extern "C" void cg_debug_counters(unsigned long long* out, int reset)
+{
+    cudaMemcpyFromSymbol(out, g_dbg, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_dbg, z, sizeof z); }
+}
+#else
+#define DBG(i) do { } while (0)
+#endif
+
 /* ---- k repeated additions of one value, exactly ---------------------------
  * For E > 0 and v > 0 in fp32: while E stays inside one binade [2^e, 2^(e+1)) every
  * rounded addition moves the significand by the same integer d (v = q*ulp + r adds q
@@ -142,6 +154,69 @@ __device__ __forceinline__ double add_run_f64_fast(double S, double v, int k)
     const unsigned long long room = 0xfffffffffffffull - (sb & 0xfffffffffffffull);
     if (__umul64hi((unsigned long long)k, d) != 0ull || (unsigned long long)k * d > room) return add_run_f64(S, v, k);
     return __longlong_as_double((long long)(sb + (unsigned long long)k * d));
+}
+
+
+/* ---- a block of mappability runs without rounding --------------------------------------
+ * Every addend of the block is a positive multiple of 2^u, u = the lowest set bit over the
+ * accumulator and the block's values.  If accumulator + sum(k_i * v_i) stays below 2^53 * 2^u,
+ * every partial sum of the reference's sequential loop is a multiple of 2^u below that bound,
+ * hence exactly representable: no addition ever rounds, the order does not matter, and the
+ * result is the integer sum scaled by 2^u.  (Mappability values are fp32 in [0,1] and the sums
+ * stay far below 2^53 units, so this is the path real tracks take.)  Returns false — nothing
+ * changed — when the bound or a precondition fails; the caller then replays the block through
+ * the rounding-aware scan. */
+__device__ __forceinline__ bool map_block_exact(unsigned long long& MB, int k, double v, int lane)
+{
+    const unsigned long long vb = (unsigned long long)__double_as_longlong(v);
+    const unsigned ev = (unsigned)(vb >> 52);                    /* sign bit set -> >= 2048 */
+    const bool active = k > 0 && (vb << 1) != 0ull;
+    bool ok = !active || (ev >= 1u && ev <= 2046u);
+    int low = 0x7fffffff;                                         /* exponent of the lowest set bit */
+    unsigned long long odd = 0ull;
+    if (active && ok) {
+        const unsigned long long m = (vb & 0xfffffffffffffull) | 0x10000000000000ull;
+        const int tz = __ffsll((long long)m) - 1;
+        odd = m >> tz;
+        low = (int)ev - 1075 + tz;
+    }
+    const unsigned es = (unsigned)(MB >> 52);
+    int low_s = 0x7fffffff;
+    unsigned long long odd_s = 0ull;
+    if (MB != 0ull) {
+        if (es < 1u || es > 2046u) ok = false;                    /* negative, subnormal, inf, nan */
+        const unsigned long long m = (MB & 0xfffffffffffffull) | 0x10000000000000ull;
+        const int tz = __ffsll((long long)m) - 1;
+        odd_s = m >> tz;
+        low_s = (int)es - 1075 + tz;
+    }
+    const int u = min(__reduce_min_sync(FULL, low), low_s);
+    unsigned long long units = 0ull;
+    if (active && ok) {
+        const int sh = low - u;                                   /* >= 0 */
+        const unsigned long long prod = (unsigned long long)k * odd;              /* < 2^55 for an fp32 value */
+        if ((odd >> 24) != 0ull || sh > 52 || (prod >> (53 - sh)) != 0ull) ok = false;
+        else units = prod << sh;                                  /* < 2^53 */
+    }
+    unsigned long long acc = 0ull;
+    if (MB != 0ull && ok) {
+        const int sh = low_s - u;
+        if (sh > 52 || (odd_s >> (53 - sh)) != 0ull) ok = false;
+        else acc = odd_s << sh;                                   /* < 2^53 */
+    }
+    if (!__all_sync(FULL, ok)) return false;
+    if (u == 0x7fffffff) return true;                             /* nothing to add, accumulator zero */
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) units += __shfl_xor_sync(FULL, units, d);     /* 33 terms below 2^53: no overflow */
+    const unsigned long long total = acc + units;
+    if (total >= (1ull << 53)) return false;
+    if (total == 0ull) return true;
+    const double t = __ll2double_rn((long long)total);            /* exact: < 2^53 */
+    const long long tb = __double_as_longlong(t) + ((long long)u << 52);
+    const unsigned et = (unsigned)((unsigned long long)tb >> 52);
+    if (et < 1u || et > 2046u) return false;
+    MB = (unsigned long long)tb;
+    return true;
 }
 
 /* ---- Poisson likelihoods, c-score, copy number ------------------------------ */
@@ -327,14 +402,15 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                 }
                 unsigned long long MB = 0ull;           /* bits of the double accumulator */
                 for (int rb = r0; rb < n_runs; rb += 32) {
+                    DBG(6);
                     const bool past = q.start >= ce;
                     const bool more = !__any_sync(FULL, past);
                     cg_maprun qn = none;
                     if (more && rb + 32 + lane < n_runs) qn = runs[rb + 32 + lane];
                     const int k = past ? 0 : max(0, min(ce, q.end) - max(cs, q.start));   /* runs ending before s add nothing */
                     const unsigned long long vbits = (unsigned long long)__double_as_longlong((double)q.val);
-                    int pos = 0;
-                    for (;;) {
+                    int pos = map_block_exact(MB, k, (double)q.val, lane) ? 32 : 0;
+                    while (pos < 32) {
                         const unsigned ee = (unsigned)(MB >> 52);
                         bool bad = false;
                         unsigned long long t = 0ull;
@@ -350,6 +426,7 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                         const unsigned long long incl = warp_incl_scan_u64(t, lane);
                         const unsigned long long room = 0xfffffffffffffull - (MB & 0xfffffffffffffull);
                         const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
+                        DBG(4); if (__ballot_sync(FULL, lane >= pos && bad)) DBG(5);
                         if (m == 0u) { MB += __shfl_sync(FULL, incl, 31); break; }
                         const int f = __ffs(m) - 1;
                         MB += __shfl_sync(FULL, incl - t, f);
@@ -381,6 +458,7 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                 const int w4 = wb + 4 * lane;
                 unsigned g4n = 0u;                      /* the block after this one */
                 if (w4 + 128 <= cw_last) g4n = load_gc4(gc, w4 + 128, n_windows);
+                DBG(0);
                 unsigned vb[4]; int kk[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -411,6 +489,7 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
                     const unsigned incl = warp_incl_scan_u32(t, lane);
                     const unsigned room = 0x7fffffu - (B & 0x7fffffu);
                     const unsigned m = __ballot_sync(FULL, lane >= pos && (bad || incl > room));
+                    DBG(1); if (acc_odd) DBG(2); if (__ballot_sync(FULL, lane >= pos && bad)) DBG(3);
                     if (m == 0u) { B += __shfl_sync(FULL, incl, 31); break; }
                     const int f = __ffs(m) - 1;
                     B += __shfl_sync(FULL, incl - t, f);            /* everything before lane f, exactly */
@@ -463,7 +542,7 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
 }
 
 #ifndef GENO_G
-#define GENO_G 16                           /* CNVs per warp */
+#define GENO_G 8                            /* CNVs per warp (measured on C2: 4 -> 3.93, 8 -> 3.80, 16 -> 4.12 ms per step) */
 #endif
 
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
