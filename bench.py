@@ -45,8 +45,58 @@ def build_workload(name, scale):
     return synth.config2(scale=scale)
 
 
+class NvmlSampler:
+    """SM clock and throttle reasons polled through NVML every few milliseconds from a thread while
+    the timed regions run (the nvidia-smi loop of B200_PROFILING.md cannot sample faster than its
+    own start-up time, and a timed region here lasts tens of milliseconds)."""
+
+    def __init__(self, gpu_index, period_s=0.004):
+        import threading
+        import pynvml
+        self.nv = pynvml
+        pynvml.nvmlInit()
+        self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        self.period = period_s
+        self.sm, self.reasons, self.busy = [], set(), []
+        self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        self._stop = threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        nv = self.nv
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for nm, b in bits.items():
+                    if r & b:
+                        self.reasons.add(nm)
+            except Exception:           # a failed query is a missing sample, nothing more
+                pass
+            self._stop.wait(self.period)
+
+    def start(self):
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        self._t.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx,
+                "samples": len(self.sm), "reasons": sorted(self.reasons), "source": "nvml, %d ms period" % round(self.period * 1e3)}
+
+
+def make_sampler(gpu_index):
+    try:
+        return NvmlSampler(gpu_index)
+    except Exception:
+        return ClockSampler(gpu_index)
+
+
 class ClockSampler:
-    """nvidia-smi sampled every 200 ms while the timed region runs (B200_PROFILING.md)."""
+    """Fallback: nvidia-smi sampled every 200 ms while the timed region runs (B200_PROFILING.md)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -124,8 +174,13 @@ def own_arm(args):
 
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
-    table_ptr, _ = ctx.stats_table()
-    table = torch.as_tensor(DevArr(table_ptr, (n_chrom, 204), "<i8"), device=dev)
+    # the statistics table of each of the two banks (cg_stats_bank): consecutive samples alternate, so
+    # the all-reduce of sample k is in flight while sample k+1's chromosomes run
+    tables = []
+    for b in (1, 0):
+        ctx.stats_bank(b)
+        tables.insert(0, torch.as_tensor(DevArr(ctx.stats_table()[0], (n_chrom, 204), "<i8"), device=dev))
+    sample_no = [0]
 
     def barrier():
         if world > 1:
@@ -152,8 +207,10 @@ def own_arm(args):
     torch.cuda.synchronize()
 
     def step_device():
+        bank = sample_no[0] & 1
+        sample_no[0] += 1
         if world > 1:
-            ctx.stats_reset()                 # rows of the other ranks' chromosomes must be zero again before the all-reduce
+            ctx.stats_bank(bank)              # cleared on the device behind the all-reduce that last read it
         for r in res:
             c = r["c"]
             ctx.chrom_begin(c.index, c.length, r["gc"], mq, n_windows=len(c.gc))
@@ -166,7 +223,7 @@ def own_arm(args):
         if world > 1:
             ctx.join()                        # main stream now waits for every stream of the context
             with torch.cuda.stream(ext):
-                dist.all_reduce(table)
+                dist.all_reduce(tables[bank])
 
     def timed(step_fn, k):
         barrier()
@@ -188,7 +245,7 @@ def own_arm(args):
     for _ in range(args.warmup):
         step_device()
     ctx.sync()
-    sampler = ClockSampler(local)
+    sampler = make_sampler(local)
     if rank == 0:
         sampler.start()
     launches0 = ctx.launch_count
@@ -214,9 +271,10 @@ def own_arm(args):
         pg = ctx.pinned_array(len(c.gc), np.int8); pg[:] = c.gc
         pd = ctx.pinned_array(len(c.dels), CNV_DT); pd[:] = c.dels
         pu = ctx.pinned_array(len(c.dups), CNV_DT); pu[:] = c.dups
-        od = ctx.pinned_array(len(c.dels), CALL_DT)
-        ou = ctx.pinned_array(len(c.dups), CALL_DT)
-        st = ctx.pinned_array(1, STATS_DT)
+        # results are double-buffered: sample k's calls stay intact while sample k+1 is being issued
+        od = [ctx.pinned_array(len(c.dels), CALL_DT) for _ in range(2)]
+        ou = [ctx.pinned_array(len(c.dups), CALL_DT) for _ in range(2)]
+        st = [ctx.pinned_array(1, STATS_DT) for _ in range(2)]
         rows = np.ascontiguousarray(c.maprows) if (has_map and c.maprows is not None) else np.zeros(0, dtype=MAPIV_DT)
         # the track is flattened once per BED file (input parsing, like the reference's per-chromosome
         # re-parse of the BED, svs.c:329-374); its upload is part of every step
@@ -224,39 +282,56 @@ def own_arm(args):
         prn = ctx.pinned_array(len(fr), MAPRUN_DT); prn[:] = fr
         host.append((c, pr, pg, pd, pu, od, ou, st, prn))
         h2d += pr.nbytes + pg.nbytes + pd.nbytes + pu.nbytes + prn.nbytes
-        d2h += od.nbytes + ou.nbytes + st.nbytes
+        d2h += od[0].nbytes + ou[0].nbytes + st[0].nbytes
     lib, h = ctx.lib, ctx.h
     BATCH = 1 << 22
 
     def step_host():
+        bank = sample_no[0] & 1
+        sample_no[0] += 1
         if world > 1:
-            ctx.stats_reset()
+            ctx.stats_bank(bank)
         for (c, pr, pg, pd, pu, od, ou, st, prn) in host:
             ctx._ck(lib.cg_chrom_begin(h, c.index, c.length, pg.ctypes.data, len(pg), mq))
             for i in range(0, len(pr), BATCH):
                 n = min(BATCH, len(pr) - i)
                 ctx._ck(lib.cg_push_reads(h, pr.ctypes.data + i * READ_DT.itemsize, n))
-            ctx._ck(lib.cg_chrom_finish(h, st.ctypes.data))
+            ctx._ck(lib.cg_chrom_finish(h, st[bank].ctypes.data))
             if has_map:
                 ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data if len(prn) else None, len(prn), 1))
             if len(pd):
-                ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od.ctypes.data))
+                ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od[bank].ctypes.data))
             if len(pu):
-                ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou.ctypes.data))
+                ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou[bank].ctypes.data))
         if world > 1:
             ctx.join()
             with torch.cuda.stream(ext):
-                dist.all_reduce(table)
-        ctx.sync()                            # statistics rows and calls of this step are now in host memory
+                dist.all_reduce(tables[bank])
+        # one sample in flight behind the one being issued: its statistics rows and calls are complete in
+        # host memory when its event has passed (a pipelined host waits here, not on the whole device)
+        ev = torch.cuda.Event()
+        ctx.join()
+        with torch.cuda.stream(ext):
+            ev.record()
+        if pending[0] is not None:
+            pending[0].synchronize()
+        pending[0] = ev
 
+    pending = [None]
     for _ in range(max(1, min(args.warmup, 2))):
         step_host()
-    ms_e2e = timed(step_host, args.steps)
+    ms_e2e = timed(step_host, args.steps)     # timed() ends with cg_sync: the last sample is complete as well
+    if world > 1:                             # every rank holds every chromosome's row after the all-reduce
+        for tb in tables:
+            t_host = tb.cpu().numpy()
+            for c in wl.chroms:
+                assert int(t_host[c.index, 101:202].sum()) == c.length, "statistics table row %d wrong after the all-reduce" % c.index
 
     # sanity: the e2e leg and the device leg produced the same bits for the last chromosome
     if res:
         got = res[-1]["out_del"].cpu().numpy()[: len(mine[-1].dels) * CALL_DT.itemsize]
-        assert got.tobytes() == host[-1][5].tobytes(), "device-mode and host-mode results differ"
+        for b in range(2):
+            assert got.tobytes() == host[-1][5][b].tobytes(), "device-mode and host-mode results differ"
 
     n_reads, n_cnvs = wl.n_reads, wl.n_cnvs
     value = n_reads * args.steps / (ms_dev / 1e3)
@@ -413,8 +488,8 @@ def _port_one(a):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (debugging only; 1.0 = the named config)")

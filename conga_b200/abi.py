@@ -63,6 +63,7 @@ SYMBOLS = {
     "cg_device_arrays": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
     "cg_stats_table": (_I, [_P, C.POINTER(_P), C.POINTER(C.c_int32)]),
     "cg_stats_reset": (_I, [_P]),
+    "cg_stats_bank": (_I, [_P, _I]),
     "cg_stats_row": (_I, [_P, _I, _P]),
     "cg_set_profiling": (_I, [_P, _I]),
     "cg_kernel_times": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
@@ -284,6 +285,9 @@ class Context:
 
     def stats_reset(self):
         self._ck(self.lib.cg_stats_reset(self.h))
+
+    def stats_bank(self, bank: int):
+        self._ck(self.lib.cg_stats_bank(self.h, int(bank)))
 
     def stats_row(self, chr_index: int):
         st = np.zeros(1, dtype=STATS_DT)

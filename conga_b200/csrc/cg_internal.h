@@ -71,6 +71,9 @@ cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_rea
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms);
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
 int         cgk_depth_pass_ctas_per_sm(void);
+int         cgk_carveout(void);                                   /* shared-memory carve-out (percent) every kernel asks for */
+cudaError_t cgk_configure_depth(void);                            /* once per process, after the device is selected */
+cudaError_t cgk_configure_genotype(void);
 
 /* genotype.cu */
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,

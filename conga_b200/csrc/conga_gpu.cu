@@ -40,6 +40,7 @@ struct cg_slot {
     int chr_index = -1;
     int32_t chrom_len = 0;
     int n_chunks = 0;
+    long long* d_row = nullptr;               /* this chromosome's int64[204] row in the statistics bank it was begun under */
     /* depth side */
     cg_read* d_reads = nullptr;       size_t reads_cap = 0;
     int8_t* d_gc = nullptr;           size_t gc_cap = 0;
@@ -69,7 +70,12 @@ struct cg_ctx {
     int n_sms = 148;
     cudaStream_t s_copy = nullptr, s_main = nullptr;
     cudaStream_t s_slot[CG_NSLOT] = {};
-    cudaEvent_t ev_reset = nullptr;           /* s_main: statistics table cleared */
+    cudaStream_t s_bank = nullptr;            /* clears a statistics bank that is selected again */
+    cudaEvent_t ev_reset = nullptr;           /* the current statistics bank has been cleared */
+    cudaEvent_t ev_left[2] = {nullptr, nullptr};   /* s_main: everything queued when the bank was left (its collective) */
+    bool bank_left[2] = {false, false};
+    int bank = 0;
+    bool dirty = false;                       /* work queued since the last cg_join */
     cudaEvent_t ev_join = nullptr;
     int ptr_mode = CG_PTR_HOST;
     bool async = false;
@@ -85,7 +91,7 @@ struct cg_ctx {
     long long n_reads = 0;
     int n_rows = 0;
 
-    long long* d_stats = nullptr;             /* [CG_MAX_CHROMS][204] */
+    long long* d_stats = nullptr;             /* [2 banks][CG_MAX_CHROMS][204] */
     unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
 
     /* pinned staging */
@@ -122,6 +128,7 @@ static int sync_all(cg_ctx* c)
 {
     CU(c, cudaStreamSynchronize(c->s_copy));
     CU(c, cudaStreamSynchronize(c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_bank));
     for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_slot[i]));
     for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(c->slot[i].s_geno[t]));
     return CG_OK;
@@ -149,6 +156,7 @@ struct prof_scope {
     cg_ctx* c; cudaStream_t s; cg_evpair ev; bool on;
     prof_scope(cg_ctx* c_, cudaStream_t s_, int slot, int n_launches) : c(c_), s(s_), on(c_->profiling) {
         c->launch_count += n_launches;
+        c->dirty = true;
         if (!on) return;
         if (!c->ev_free.empty()) { ev = c->ev_free.back(); c->ev_free.pop_back(); }
         else { cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); }
@@ -201,6 +209,10 @@ cg_ctx* cg_create(int device)
         fail(nullptr, CG_ECUDA, "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
         return nullptr;
     }
+    if ((e = cgk_configure_depth()) != cudaSuccess || (e = cgk_configure_genotype()) != cudaSuccess) {
+        fail(nullptr, CG_ECUDA, "kernel configuration failed (no sm_100a image for this device?): %s", cudaGetErrorString(e));
+        return nullptr;
+    }
     cg_ctx* c = new cg_ctx();
     c->device = device;
     c->n_sms = prop.multiProcessorCount;
@@ -208,11 +220,14 @@ cg_ctx* cg_create(int device)
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
     bool ok = cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        && cudaStreamCreateWithPriority(&c->s_bank, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming) == cudaSuccess
+        && cudaEventCreateWithFlags(&c->ev_left[0], cudaEventDisableTiming) == cudaSuccess
+        && cudaEventCreateWithFlags(&c->ev_left[1], cudaEventDisableTiming) == cudaSuccess
         /* the genotype kernel is small and latency-bound: let its CTAs be placed first */
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
-        && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
-        && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS) == cudaSuccess
+        && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
+        && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
         && cudaMalloc(&c->d_sticky, 16) == cudaSuccess
         && cudaMemset(c->d_sticky, 0, 16) == cudaSuccess
         && cudaMallocHost(&c->h_stats, sizeof(cg_chrom_stats)) == cudaSuccess
@@ -248,6 +263,7 @@ void cg_destroy(cg_ctx* c)
     cudaSetDevice(c->device);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
+    if (c->s_bank) cudaStreamSynchronize(c->s_bank);
     for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamSynchronize(c->s_slot[t]);
     for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamSynchronize(c->slot[i].s_geno[t]);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
@@ -268,6 +284,8 @@ void cg_destroy(cg_ctx* c)
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     if (c->s_main) cudaStreamDestroy(c->s_main);
+    if (c->s_bank) cudaStreamDestroy(c->s_bank);
+    for (int b = 0; b < 2; b++) if (c->ev_left[b]) cudaEventDestroy(c->ev_left[b]);
     for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamDestroy(c->s_slot[t]);
     if (c->ev_reset) cudaEventDestroy(c->ev_reset);
     for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamDestroy(c->slot[i].s_geno[t]);
@@ -314,6 +332,7 @@ int cg_join(cg_ctx* c)
         CU(c, cudaEventRecord(c->ev_join, all[t]));
         CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
     }
+    c->dirty = false;
     return CG_OK;
 }
 
@@ -419,6 +438,8 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         s.gc_ptr = gc_profile;
     }
     s.chr_index = chr_index; s.chrom_len = chrom_len; s.n_chunks = n_chunks;
+    s.d_row = c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS;
+    c->dirty = true;
     s.reads_ptr = s.d_reads;
     s.n_runs = 0; s.has_map = 0; s.runs_ptr = nullptr;
     s.arena_used = 0;
@@ -430,8 +451,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
         prof_scope ps(c, c->s_slot[c->cur], 0, 1);
-        CU(c, cgk_chrom_init(c->s_slot[c->cur], s.d_counts, n_chunks,
-                             c->d_stats + (size_t)chr_index * CG_STATS_WORDS, s.d_ctl));
+        CU(c, cgk_chrom_init(c->s_slot[c->cur], s.d_counts, n_chunks, s.d_row, s.d_ctl));
     }
     return CG_OK;
 }
@@ -467,8 +487,7 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     {
         prof_scope ps(c, c->s_slot[c->cur], 0, 1);
         CU(c, cgk_mark_batch(c->s_slot[c->cur], s.reads_ptr, first, (long long)n, cgk_counts_layout(s.d_counts, s.n_chunks),
-                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl,
-                             c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS));
+                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, s.d_row));
     }
     return CG_OK;
 }
@@ -479,7 +498,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     if (!c->in_chrom || c->finished) return fail(c, CG_EINVAL, "cg_chrom_finish without cg_chrom_begin");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    long long* row = c->d_stats + (size_t)s.chr_index * CG_STATS_WORDS;
+    long long* row = s.d_row;
     if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));   /* GC bytes */
     {
         prof_scope ps(c, c->s_slot[c->cur], 0, 2);
@@ -686,7 +705,7 @@ int cg_device_arrays(cg_ctx* c, const int16_t** depth, const int32_t** prefix, c
 int cg_stats_table(cg_ctx* c, void** device_ptr, int32_t* n_rows)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (device_ptr) *device_ptr = c->d_stats;
+    if (device_ptr) *device_ptr = c->d_stats + (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
     if (n_rows) *n_rows = c->n_rows;
     return CG_OK;
 }
@@ -697,10 +716,37 @@ int cg_stats_reset(cg_ctx* c)
     CU(c, cudaSetDevice(c->device));
     int rc = cg_join(c);                      /* rows may still be written or copied by queued work */
     if (rc) return rc;
-    CU(c, cudaMemsetAsync(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * (size_t)(c->n_rows > 0 ? c->n_rows : 1), c->s_main));
+    /* the whole bank: an in-place collective also fills the rows of chromosomes this context never saw */
+    CU(c, cudaMemsetAsync(c->d_stats + (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS, 0,
+                          sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS, c->s_main));
     CU(c, cudaEventRecord(c->ev_reset, c->s_main));
     for (int i = 0; i < CG_NSLOT; i++) c->slot[i].wait_reset = true;
     c->n_rows = 0;
+    return CG_OK;
+}
+
+/* Two statistics tables so that the collective over sample k's table (queued on cg_stream after
+ * cg_join) can be in flight while the chromosomes of sample k+1 fill the other one.  Selecting a
+ * bank clears it on a side stream, ordered behind everything that was queued on cg_stream when the
+ * bank was left (the collective that read it); the chromosomes begun afterwards wait for that
+ * clear only, never for the other bank's collective. */
+int cg_stats_bank(cg_ctx* c, int bank)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (bank != 0 && bank != 1) return fail(c, CG_EINVAL, "bank %d must be 0 or 1", bank);
+    if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_stats_bank inside a chromosome");
+    if (bank == c->bank) return CG_OK;
+    CU(c, cudaSetDevice(c->device));
+    if (c->dirty) { int rc = cg_join(c); if (rc) return rc; }      /* the table being left is complete behind this point */
+    CU(c, cudaEventRecord(c->ev_left[c->bank], c->s_main));
+    c->bank_left[c->bank] = true;
+    if (c->bank_left[bank]) CU(c, cudaStreamWaitEvent(c->s_bank, c->ev_left[bank], 0));
+    if (c->bank_left[bank])
+        CU(c, cudaMemsetAsync(c->d_stats + (size_t)bank * CG_MAX_CHROMS * CG_STATS_WORDS, 0,
+                              sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS, c->s_bank));
+    CU(c, cudaEventRecord(c->ev_reset, c->s_bank));
+    for (int i = 0; i < CG_NSLOT; i++) c->slot[i].wait_reset = true;
+    c->bank = bank; c->n_rows = 0;
     return CG_OK;
 }
 
@@ -711,7 +757,7 @@ int cg_stats_row(cg_ctx* c, int chr_index, cg_chrom_stats* out)
     CU(c, cudaSetDevice(c->device));
     int rc = sync_all(c);
     if (rc) return rc;
-    CU(c, cudaMemcpyAsync(c->h_stats, c->d_stats + (size_t)chr_index * CG_STATS_WORDS, sizeof(cg_chrom_stats),
+    CU(c, cudaMemcpyAsync(c->h_stats, c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS, sizeof(cg_chrom_stats),
                           cudaMemcpyDeviceToHost, c->s_main));
     CU(c, cudaStreamSynchronize(c->s_main));
     memcpy(out, c->h_stats, sizeof(cg_chrom_stats));

@@ -512,15 +512,37 @@ k_depth_pass(const cg_pass_args a)
 
 int cgk_depth_pass_ctas_per_sm(void) { return PASS_CTAS_PER_SM; }
 
+/* Two kernels share an SM only if they ask for the same L1/shared-memory split; otherwise the
+ * CTAs of the second wait until the SM has drained.  Every kernel of the library therefore
+ * states the same carve-out, so that the preparation and genotype kernels of one chromosome
+ * really run on the SMs a neighbour's depth pass occupies. */
+int cgk_carveout(void)
+{
+    static int pct = -1;
+    if (pct < 0) {
+        const char* e = getenv("CG_CARVEOUT");            /* tuning only */
+        pct = e ? atoi(e) : 100;
+        if (pct < 0 || pct > 100) pct = 100;
+    }
+    return pct;
+}
+
+cudaError_t cgk_configure_depth(void)
+{
+    const int pct = cgk_carveout();
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pass_smem))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_chrom_init, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_mark_batch, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_rare_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_rare_totals, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
 {
-    static bool configured = false;
-    const int smem = (int)sizeof(pass_smem);
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    const int smem = (int)sizeof(pass_smem);           /* opted in by cgk_configure_depth */
     static int ctas_per_sm = 0;               /* CG_PASS_CTAS: CTAs per SM one launch asks for (tuning) */
     if (!ctas_per_sm) {
         const char* e = getenv("CG_PASS_CTAS");

@@ -542,8 +542,20 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
 }
 
 #ifndef GENO_G
-#define GENO_G 8                            /* CNVs per warp (measured on C2: 4 -> 3.93, 8 -> 3.80, 16 -> 4.12 ms per step) */
+/* CNVs per warp.  Measured on B200, C2, all kernels with one shared-memory carve-out (so that they
+ * really share SMs with the depth pass): genotype kernels alone 8 -> 7.7, 4 -> 5.4, 2 -> 4.1,
+ * 1 -> 2.9 ms per sample; whole step 8 -> 3.14, 4 -> 3.05, 2 -> 3.02, 1 -> 3.01 ms.  The GPU is
+ * otherwise idle under the bandwidth-bound pass, so latency wins over lane efficiency. */
+#define GENO_G 1
 #endif
+
+cudaError_t cgk_configure_genotype(void)
+{
+    const int pct = cgk_carveout();                       /* see cgk_configure_depth */
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_genotype<GENO_G>, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_run_index, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+}
 
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
                          const int32_t* prefix, const int8_t* gc, const float* expected,
@@ -553,7 +565,7 @@ cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
     if (n <= 0) return cudaSuccess;
     const int n_groups = (n + GENO_G - 1) / GENO_G;
     int blocks = (n_groups + GENO_WARPS - 1) / GENO_WARPS;
-    if (blocks > n_sms * 2) blocks = n_sms * 2;
+    if (blocks > n_sms * 8) blocks = n_sms * 8;
     k_genotype<GENO_G><<<blocks, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, prefix, gc, expected, runs, run_idx, n_runs,
                                                           has_map, chrom_len, flags, out);
     return cudaGetLastError();

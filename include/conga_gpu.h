@@ -176,6 +176,13 @@ int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const int32_t** prefix,
  * driver all-reduces it (NCCL sum) so every rank holds every chromosome's row. */
 int cg_stats_table(cg_ctx* ctx, void** device_ptr, int32_t* n_rows);
 int cg_stats_reset(cg_ctx* ctx);
+/* Two tables ("banks", 0 and 1; 0 at creation).  The chromosomes begun after cg_stats_bank write
+ * their rows to `bank`, and cg_stats_table / cg_stats_row refer to it.  A driver that processes
+ * sample after sample alternates banks: the collective over sample k's table — queued on cg_stream
+ * after cg_join — is then in flight while sample k+1's chromosomes already fill the other bank.
+ * A bank that is selected again is cleared first (all rows, so an in-place all-reduce is fine),
+ * ordered behind whatever was queued on cg_stream when it was left; nothing waits on the host. */
+int cg_stats_bank(cg_ctx* ctx, int bank);
 int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
 
 /* Device time of this context's kernels, from CUDA events recorded on its stream

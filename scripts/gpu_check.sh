@@ -23,4 +23,4 @@ if [ "${NCU:-1}" = "1" ]; then
       -o gpurun_out/prof_genotype -f $CMD > gpurun_out/ncu_full_geno.log 2>&1
   echo "ncu geno rc=$?"
 fi
-tail -5 gpurun_out/pytest_gpu.log gpurun_out/smoke.log
+tail -n 5 gpurun_out/pytest_gpu.log; tail -n 5 gpurun_out/smoke.log

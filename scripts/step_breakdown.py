@@ -1,0 +1,86 @@
+"""Where a step's time goes on ONE GPU when it owns the chromosomes rank 0 of a WORLD-rank job would own
+(no collective): host issue time, pipelined device time per step, and the same with stages removed.
+
+  python scripts/step_breakdown.py [--world W] [--steps K] [lib.so ...]
+"""
+import argparse, json, os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from conga_b200 import abi, synth, CG_PTR_DEVICE, CALL_DT, flatten_mappability
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--world", type=int, default=1)
+ap.add_argument("--rank", type=int, default=0)
+ap.add_argument("--steps", type=int, default=20)
+ap.add_argument("--workload", default="c2")
+ap.add_argument("libs", nargs="*")
+args = ap.parse_args()
+
+wl = synth.config3() if args.workload == "c3" else synth.config2()
+parts = synth.lpt_partition([c.length for c in wl.chroms], args.world)
+mine = [wl.chroms[i] for i in parts[args.rank]]
+dev = torch.device("cuda:0")
+to_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+res = []
+for c in mine:
+    runs = flatten_mappability(c.maprows, c.length) if (wl.has_mappability and c.maprows is not None) else None
+    res.append(dict(c=c, gc=to_dev(c.gc), reads=to_dev(c.reads), dels=to_dev(c.dels), dups=to_dev(c.dups),
+                    runs=to_dev(runs) if runs is not None and len(runs) else None, n_runs=0 if runs is None else len(runs),
+                    od=torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev),
+                    ou=torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)))
+alg = sum(8 * len(c.reads) + 6 * c.length + (c.length + 99) // 100 for c in mine)
+n_reads = sum(len(c.reads) for c in mine)
+
+for path in (args.libs or [abi.LIB_PATH]):
+    abi._lib = abi.load_library(path)
+    ctx = abi.Context(0)
+    ctx.set_pointer_mode(CG_PTR_DEVICE)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+    def step(geno=True, mapp=True, dups=True):
+        for r in res:
+            c = r["c"]
+            ctx.chrom_begin(c.index, c.length, r["gc"], wl.mq_threshold, n_windows=len(c.gc))
+            ctx.push_reads(r["reads"], len(c.reads))
+            ctx.chrom_finish(None)
+            if mapp and wl.has_mappability:
+                ctx.set_mappability_runs(r["runs"], r["n_runs"], True)
+            if geno:
+                ctx.genotype(r["dels"], False, r["od"], n=len(c.dels))
+                if dups:
+                    ctx.genotype(r["dups"], True, r["ou"], n=len(c.dups))
+
+    def run(K, **kw):
+        for _ in range(3):
+            step(**kw)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext):
+            e0.record()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            step(**kw)
+        t_issue = (time.perf_counter() - t0) / K * 1e3
+        ctx.join()
+        with torch.cuda.stream(ext):
+            e1.record()
+        ctx.sync()
+        return round(e0.elapsed_time(e1) / K, 4), round(t_issue, 4)
+
+    out = {"lib": os.path.basename(path), "world": args.world, "chroms": len(mine), "pass_floor_ms": round(alg / 6536e6, 4)}
+    out["full"] = run(args.steps)
+    out["one_step_serial"] = run(1)
+    out["no_dups"] = run(args.steps, dups=False)
+    out["no_map"] = run(args.steps, mapp=False)
+    out["no_geno"] = run(args.steps, geno=False, mapp=False)
+    ctx.set_profiling(True); ctx.kernel_times()
+    for _ in range(args.steps):
+        step()
+    ms, n = ctx.kernel_times()
+    ctx.set_profiling(False)
+    out["kernels_alone_ms"] = {"prep": round(ms[0] / args.steps, 4), "pass": round(ms[1] / args.steps, 4), "geno": round(ms[2] / args.steps, 4)}
+    out["reads_per_s_full"] = round(n_reads / (out["full"][0] / 1e3))
+    print(json.dumps(out), flush=True)
+    ctx.close()

@@ -382,3 +382,34 @@ def test_async_host_mode_pipelines_chromosomes_without_mixing_them_up(ctx, oracl
             assert_calls_equal(ou, u_ref, True)
     finally:
         ctx.set_async(False)
+
+
+def test_statistics_banks(ctx, oracle):
+    """cg_stats_bank: rows go to the selected bank; a bank that is selected again starts cleared (all rows,
+    including ones an in-place all-reduce would have filled for other ranks' chromosomes)."""
+    rng = np.random.default_rng(5)
+    a = synth._chrom("a", 3, 300_000, rng, 5000, 4, 2, False, cnv_hi=20_000)
+    b = synth._chrom("b", 7, 200_000, rng, 3000, 4, 2, False, cnv_hi=20_000)
+    st_a = oracle.chromosome(a, -1, False)[1]
+    st_b = oracle.chromosome(b, -1, False)[1]
+    same = lambda got, want: all(np.array_equal(got[f], want[f]) for f in ("rd_per_gc", "window_per_gc", "rd_cnt", "reads_passed"))
+    ctx.stats_bank(0)
+    ctx.stats_reset()
+    try:
+        hotpath.run_chromosome(ctx, a)
+        assert same(ctx.stats_row(3), st_a)
+        ctx.stats_bank(1)
+        hotpath.run_chromosome(ctx, b)
+        assert same(ctx.stats_row(7), st_b)
+        assert int(ctx.stats_row(3)["window_per_gc"].sum()) == 0          # bank 1 never saw chromosome a
+        p0 = ctx.stats_table()[0]
+        ctx.stats_bank(0)                                                  # selected again: cleared
+        assert ctx.stats_table()[0] != p0
+        assert int(ctx.stats_row(3)["window_per_gc"].sum()) == 0
+        hotpath.run_chromosome(ctx, b)
+        assert same(ctx.stats_row(7), st_b)
+        ctx.stats_bank(1)
+        assert int(ctx.stats_row(7)["window_per_gc"].sum()) == 0
+    finally:
+        ctx.stats_bank(0)
+        ctx.stats_reset()
