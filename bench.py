@@ -153,10 +153,16 @@ class DevArr:
 def own_arm(args):
     import torch
     import torch.distributed as dist
+    from conga_b200 import multi
     from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CNV_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, Context,
                             flatten_mappability, synth)
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    # stdout carries the JSON line and nothing else: libraries that print there (NCCL's version banner)
+    # are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
@@ -168,7 +174,7 @@ def own_arm(args):
 
     wl = build_workload(args.workload, args.scale)
     n_chrom = len(wl.chroms)
-    parts = synth.lpt_partition([c.length for c in wl.chroms], world)
+    parts = multi.lpt_partition([c.length for c in wl.chroms], world)
     mine = [wl.chroms[i] for i in parts[rank]]
     has_map, mq = wl.has_mappability, wl.mq_threshold
 
@@ -223,7 +229,7 @@ def own_arm(args):
         if world > 1:
             ctx.join()                        # main stream now waits for every stream of the context
             with torch.cuda.stream(ext):
-                dist.all_reduce(tables[bank])
+                multi.allreduce_stats(tables[bank])
 
     def timed(step_fn, k):
         barrier()
@@ -306,7 +312,7 @@ def own_arm(args):
         if world > 1:
             ctx.join()
             with torch.cuda.stream(ext):
-                dist.all_reduce(tables[bank])
+                multi.allreduce_stats(tables[bank])
         # one sample in flight behind the one being issued: its statistics rows and calls are complete in
         # host memory when its event has passed (a pipelined host waits here, not on the whole device)
         ev = torch.cuda.Event()
@@ -372,7 +378,7 @@ def own_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_port(wl, budget_s=args.cpu_budget)
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

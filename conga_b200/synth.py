@@ -220,14 +220,6 @@ def config3(scale: float = 1.0, seed: int = SEED0 + 3) -> Workload:
 
 
 def lpt_partition(lengths: List[int], n_parts: int) -> List[List[int]]:
-    """Longest-processing-time assignment of chromosomes to GPUs."""
-    order = sorted(range(len(lengths)), key=lambda i: -lengths[i])
-    loads = [0] * n_parts
-    parts: List[List[int]] = [[] for _ in range(n_parts)]
-    for i in order:
-        k = min(range(n_parts), key=lambda j: loads[j])
-        parts[k].append(i)
-        loads[k] += lengths[i]
-    for p in parts:
-        p.sort()
-    return parts
+    """Longest-processing-time assignment of chromosomes to GPUs; see multi.lpt_partition."""
+    from .multi import lpt_partition as _lpt
+    return _lpt(lengths, n_parts)
