@@ -1,0 +1,590 @@
+/* conga_host.cpp — `conga-b200`: CONGA's command line over libconga_gpu.so.
+ *
+ * Same flags, same input files, byte-identical <out>_svs.bed / _dels.bed / _dups.bed and
+ * conga.log as the reference program (asylvz/CONGA @58d4fe4), with the four numeric stages of
+ * read_bam() routed through the C-ABI (include/conga_gpu.h) to the sm_100a kernels:
+ *
+ *   reference                                   here
+ *   main                  svdepth.c:16-74       main()
+ *   parse_cmd_line        cmdline.c:12-207      parse_cmd_line()        same option table and defaults
+ *   read_bam              bam_data.c:224-359    run()                   chromosome loop in SONIC order
+ *   init_rd_per_chr       bam_data.c:304        cg_chrom_begin
+ *   count_reads_bam       bam_data.c:316        decode threads -> cg_push_reads
+ *   calc_mean_per_chr     bam_data.c:322        cg_chrom_finish (+ the conga.log line)
+ *   find_SVs              bam_data.c:338        CNV selection/sort, cg_set_mappability, cg_genotype x2
+ *   output_SVs            likelihood.c:172-288  write_rows()            same printf formats
+ *
+ * What the host does differently — none of it visible in the outputs:
+ *   * every BED is parsed once (the reference re-reads the del/dup BEDs twice and the mappability
+ *     BED once PER CHROMOSOME, svs.c:7-240, :317-377);
+ *   * htslib decoding runs in worker threads, one chromosome per task with its own htsFile and
+ *     iterator (the index makes chromosomes independently seekable), ahead of the GPU;
+ *   * there is no short read_depth[L] and no float mappability[L] on the host at all.
+ *
+ * There is no CPU implementation of the numeric stages in this program: without the library and
+ * a B200 it stops with an error.  --rp (split-read support, split_read.c) is not built yet and is
+ * refused rather than silently ignored.
+ *
+ * htslib and libsonic are third-party inputs (the same two libraries the reference links).
+ */
+#include <getopt.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cctype>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include <htslib/hts.h>
+#include <htslib/sam.h>
+#include "sonic.h"
+
+#include "conga_gpu.h"
+
+#ifndef CONGA_VERSION
+#define CONGA_VERSION "1.0-b200"
+#endif
+#ifndef CONGA_UPDATE
+#define CONGA_UPDATE "November 24, 2022"
+#endif
+#ifndef BUILD_DATE
+#define BUILD_DATE __DATE__
+#endif
+
+namespace {
+
+/* parameters, common.h:62-86 (only what the genotyping path reads) */
+struct Params {
+    std::string ref_genome, outdir, outprefix, low_map_regions, dup_file, del_file, bam_file, sonic_file,
+                mappability_file, sonic_info;
+    bool has_ref = false, has_out = false, has_dup = false, has_del = false, has_map = false, has_sonic = false,
+         has_lowmap = false;
+    int min_sv_size = 0, min_read_length = 0, first_chrom = 0, last_chrom = -1;
+    float c_score = 0.5f;
+    int mq_threshold = -1, rp_support = 10, no_sr = 1;
+    sonic* this_sonic = nullptr;
+};
+
+FILE* g_log = nullptr;
+
+[[noreturn]] void die(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vfprintf(stderr, fmt, ap);
+    va_end(ap);
+    fputc('\n', stderr);
+    exit(1);
+}
+
+FILE* open_or_die(const std::string& path, const char* mode)
+{
+    FILE* f = fopen(path.c_str(), mode);
+    if (!f) {   /* common.c:102-119: message + exit(1) */
+        fprintf(stderr, "\n[CONGA INPUT ERROR] Unable to open file %s in %s mode.\n", path.c_str(), mode[0] == 'w' ? "write" : "read");
+        fprintf(stderr, "Invoke parameter -h for help.\n");
+        exit(1);
+    }
+    return f;
+}
+
+void print_help()
+{
+    fprintf(stdout, "\n\t... CONGA (COpy Number variation Genotyping in Ancient genomes) — B200 host ...\n\n");
+    fprintf(stdout, "\tVersion %s\n\tLast update: %s, build date: %s\n\n", CONGA_VERSION, CONGA_UPDATE, BUILD_DATE);
+    fprintf(stdout, "\tParameters (identical to conga):\n");
+    fprintf(stdout, "\t--input [BAM file]        : Input file in sorted and indexed BAM format (required).\n");
+    fprintf(stdout, "\t--out [output prefix]     : Prefix for the output file names (required).\n");
+    fprintf(stdout, "\t--ref [reference genome]  : Reference genome in FASTA format (required).\n");
+    fprintf(stdout, "\t--sonic [sonic file]      : SONIC file that contains assembly annotations (required).\n");
+    fprintf(stdout, "\t--dels [BED file]         : Known deletion SVs in BED format\n");
+    fprintf(stdout, "\t--dups [BED file]         : Known duplication SVs in BED format\n");
+    fprintf(stdout, "\t--first-chr [chr index]   : The index of the first chromosome for genotyping in your BAM\n");
+    fprintf(stdout, "\t--last-chr [chr index]    : The index of the last chromosome for genotyping in your BAM\n");
+    fprintf(stdout, "\t--mappability [BED file]  : Mappability file in BED format\n");
+    fprintf(stdout, "\t--min-read-length [INT]   : Minimum length of a read to be processed for RP (default: 60 bps)\n");
+    fprintf(stdout, "\t--min-sv-size [INT]       : Minimum length of a CNV (default: 1000 bps)\n");
+    fprintf(stdout, "\t--min-mapq [INT]          : Minimum mapping quality filter for reads (default: no-filter)\n");
+    fprintf(stdout, "\t--c-score [FLOAT]         : Minimum c-score to filter variants (default: 0.5).\n");
+    fprintf(stdout, "\t--rp [INT]                : Split-read support for duplications (not available in this build).\n");
+    fprintf(stdout, "\n\tEnvironment: CONGA_GPU_DEVICE (CUDA device, default 0), CONGA_DECODE_THREADS (default: cores, at most 16)\n");
+    fprintf(stdout, "\n\tInformation:\n\t--version                 : Print version and exit.\n\t--help                    : Print this help screen and exit.\n\n");
+}
+
+/* cmdline.c:12-207.  Returns 3 = parameter error (exit 1), 0 = help/version shown (exit 0), 1 = go on. */
+int parse_cmd_line(int argc, char** argv, Params& p)
+{
+    enum { FIRST_CHROM = 10001, LAST_CHROM = 10002 };
+    static int no_sr_flag = 1;
+    static struct option long_options[] = {
+        {"c-score", required_argument, 0, 'a'},      {"min-read-length", required_argument, 0, 'b'},
+        {"dels", required_argument, 0, 'd'},         {"min-mapq", required_argument, 0, 'e'},
+        {"ref", required_argument, 0, 'f'},          {"help", no_argument, 0, 'h'},
+        {"input", required_argument, 0, 'i'},        {"rp", required_argument, 0, 'j'},
+        {"min-sv-size", required_argument, 0, 'l'},  {"mappability", required_argument, 0, 'm'},
+        {"sonic-info", required_argument, 0, 'n'},   {"out", required_argument, 0, 'o'},
+        {"sonic", required_argument, 0, 's'},        {"dups", required_argument, 0, 'u'},
+        {"version", no_argument, 0, 'v'},            {"exclude", required_argument, 0, 'x'},
+        {"no-sr", no_argument, &no_sr_flag, 1},      {"first-chr", required_argument, 0, FIRST_CHROM},
+        {"last-chr", required_argument, 0, LAST_CHROM}, {0, 0, 0, 0}};
+    if (argc == 1) { print_help(); return 0; }
+    bool load_sonic = false, has_c = false, has_mq = false, has_rp = false;
+    std::string c_score, min_mapq, min_rp;
+    int o, index;
+    /* the reference's short-option string, cmdline.c:54 (note: "x" takes no argument there) */
+    while ((o = getopt_long(argc, argv, "hvb:i:f:g:d:r:o:m:c:s:a:e:n:j:k:u:x", long_options, &index)) != -1) {
+        switch (o) {
+        case 'a': c_score = optarg; has_c = true; break;
+        case 'b': p.min_read_length = atoi(optarg); break;
+        case 'd': p.del_file = optarg; p.has_del = true; break;
+        case 'e': min_mapq = optarg; has_mq = true; break;
+        case 'f': p.ref_genome = optarg; p.has_ref = true; break;
+        case 'h': print_help(); return 0;
+        case 'i': p.bam_file = optarg; break;
+        case 'j': min_rp = optarg; has_rp = true; break;
+        case 'l': p.min_sv_size = atoi(optarg); break;
+        case 'm': p.mappability_file = optarg; p.has_map = true; break;
+        case 'n': p.sonic_info = optarg; break;
+        case 'o': p.outprefix = optarg; p.has_out = true; break;
+        case 's': p.sonic_file = optarg; p.has_sonic = true; load_sonic = true; break;
+        case 'u': p.dup_file = optarg; p.has_dup = true; break;
+        case 'v':
+            fprintf(stderr, "\n\tCONGA Version %s\n\tLast update: %s, build date: %s\n", CONGA_VERSION, CONGA_UPDATE, BUILD_DATE);
+            fprintf(stderr, "\tFor more information, check https://github.com/asylvz/CONGA\n\n");
+            return 0;
+        case 'x': if (optarg) { p.low_map_regions = optarg; p.has_lowmap = true; } break;
+        case FIRST_CHROM: p.first_chrom = atoi(optarg); break;
+        case LAST_CHROM: p.last_chrom = atoi(optarg); break;
+        default: break;
+        }
+    }
+    if (!p.has_out) { fprintf(stderr, "[CONGA CMDLINE ERROR] Please enter the output file name prefix using the --out option.\n"); return 3; }
+    if (!p.has_ref) { fprintf(stderr, "[CONGA CMDLINE ERROR] Please enter reference genome file (FASTA) using the --ref option.\n"); return 3; }
+    if (!p.has_sonic && load_sonic) { fprintf(stderr, "[CONGA CMDLINE ERROR] Please enter the SONIC file (BED) using the --sonic option.\n"); return 3; }
+    if (p.min_sv_size <= 0) { p.min_sv_size = 1000; fprintf(stderr, "Minimum size of an SV is set to %d\n", p.min_sv_size); }
+    if (p.min_read_length <= 0) { p.min_read_length = 60; fprintf(stderr, "Minimum size of a read is set to %d\n", p.min_read_length); }
+    p.c_score = has_c ? (float)atof(c_score.c_str()) : 0.5f;                 /* float c_score, common.h:74 */
+    if (has_rp) { p.rp_support = atoi(min_rp.c_str()); p.no_sr = 0; } else { p.rp_support = 10; p.no_sr = 1; }
+    p.mq_threshold = has_mq ? atoi(min_mapq.c_str()) : -1;
+    if (p.sonic_info.empty()) p.sonic_info = p.ref_genome;
+    /* get_working_directory, common.c:45-83: --out dir/pre splits at the last '/' */
+    const size_t slash = p.outprefix.rfind('/');
+    if (slash == std::string::npos) {
+        p.outdir = "";
+    } else {
+        const std::string prefix = p.outprefix.substr(slash + 1);
+        fprintf(stderr, "prefix: %s\n", prefix.c_str());
+        p.outdir = p.outprefix.substr(0, slash) + "/";
+        fprintf(stderr, "prefix2: %s\n", prefix.c_str());
+        p.outprefix = prefix;
+    }
+    fprintf(stderr, "[CONGA INFO] Working directory: %s\n", p.outdir.c_str());
+    return 1;
+}
+
+/* print_params, common.c:86-99 */
+void print_params(const Params& p)
+{
+    printf("\n");
+    printf("%-30s%s\n", "BAM input:", p.bam_file.c_str());
+    fprintf(g_log, "%-30s%s\n", "BAM input:", p.bam_file.c_str());
+    printf("%-30s%s\n", "Reference genome:", p.ref_genome.c_str());
+    printf("%-30s%s\n", "SONIC file:", p.has_sonic ? p.sonic_file.c_str() : "(null)");
+    fprintf(g_log, "%-30s%s\n", "Reference genome:", p.ref_genome.c_str());
+    fprintf(g_log, "%-30s%s\n", "SONIC file:", p.has_sonic ? p.sonic_file.c_str() : "(null)");
+    fprintf(g_log, "%-30s%d\n", "First chrom:", p.first_chrom);
+    fprintf(g_log, "%-30s%d\n", "Last chrom:", p.last_chrom);
+}
+
+/* ---- BED files, each read once --------------------------------------------------------- */
+struct BedRow { int start, end; };
+
+/* One pass with the reference's line discipline (svs.c:26-65): fgets into 512 bytes, lines of
+ * white space skipped, tokens split on " \t\r\n", atoi.  Rows are grouped by column 1; the
+ * per-chromosome filter (name == BAM target name, end-start >= min_sv_size; svs.c:55) is applied
+ * when the chromosome comes up. */
+std::map<std::string, std::vector<BedRow>> read_cnv_bed(const std::string& path)
+{
+    std::map<std::string, std::vector<BedRow>> out;
+    FILE* f = open_or_die(path, "r");
+    char line[512];
+    while (fgets(line, sizeof line, f)) {
+        bool blank = true;
+        for (const char* c = line; *c; c++) if (!isspace((unsigned char)*c)) { blank = false; break; }
+        if (blank) continue;
+        char* save = nullptr;
+        const char* chr = strtok_r(line, " \t\r\n", &save);
+        const char* a = strtok_r(nullptr, " \t\r\n", &save);
+        const char* b = strtok_r(nullptr, " \t\r\n", &save);
+        if (!chr || !a || !b) die("[CONGA INPUT ERROR] %s: a row needs at least three columns", path.c_str());
+        out[chr].push_back(BedRow{atoi(a), atoi(b)});
+    }
+    fclose(f);
+    return out;
+}
+
+/* Mappability BED (svs.c:329-374): chr start end value, rows of one chromosome kept in FILE ORDER
+ * because the reference paints them in that order and later rows win. */
+std::map<std::string, std::vector<cg_mapiv>> read_mappability_bed(const std::string& path)
+{
+    std::map<std::string, std::vector<cg_mapiv>> out;
+    FILE* f = open_or_die(path, "r");
+    char line[512];
+    uint32_t line_no = 0;
+    while (fgets(line, sizeof line, f)) {
+        bool blank = true;
+        for (const char* c = line; *c; c++) if (!isspace((unsigned char)*c)) { blank = false; break; }
+        if (blank) continue;
+        char* save = nullptr;
+        const char* chr = strtok_r(line, " \t\r\n", &save);
+        const char* a = strtok_r(nullptr, " \t\r\n", &save);
+        const char* b = strtok_r(nullptr, " \t\r\n", &save);
+        const char* v = strtok_r(nullptr, " \t\r\n", &save);
+        if (!chr || !a || !b || !v) die("[CONGA INPUT ERROR] %s: a mappability row needs four columns", path.c_str());
+        cg_mapiv r;
+        r.start = atoi(a); r.end = atoi(b);
+        r.val = (float)atof(v);                                    /* float mappability = atof(...), svs.c:365 */
+        r.line = line_no++;
+        out[chr].push_back(r);
+    }
+    fclose(f);
+    return out;
+}
+
+/* ---- decoding ahead of the GPU ---------------------------------------------------------- */
+struct ChromTask {
+    int chr_index = -1, tid = -1;
+    int32_t length = 0;
+    std::vector<cg_read> reads;
+    long n_records = 0;
+    bool done = false, failed = false;
+};
+
+struct Decoder {
+    const Params& p;
+    std::vector<ChromTask>& tasks;
+    hts_idx_t* idx;                       /* shared, read-only */
+    std::atomic<size_t> next{0};
+    std::mutex mu;
+    std::condition_variable cv;
+    size_t consumed = 0;                  /* tasks the main thread is done with */
+    size_t window;                        /* decode at most this many tasks ahead of the consumer */
+    std::vector<std::thread> threads;
+
+    Decoder(const Params& p_, std::vector<ChromTask>& t, hts_idx_t* i, int n_threads, size_t win)
+        : p(p_), tasks(t), idx(i), window(win)
+    {
+        for (int k = 0; k < n_threads; k++) threads.emplace_back([this] { work(); });
+    }
+    ~Decoder() { for (auto& t : threads) t.join(); }
+
+    void work()
+    {
+        htsFile* fp = hts_open(p.bam_file.c_str(), "r");
+        bam_hdr_t* hdr = fp ? sam_hdr_read(fp) : nullptr;
+        bam1_t* b = bam_init1();
+        for (;;) {
+            const size_t k = next.fetch_add(1);
+            if (k >= tasks.size()) break;
+            {   /* bounded look-ahead: the reads of a whole chromosome are held in memory */
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return k < consumed + window; });
+            }
+            ChromTask& t = tasks[k];
+            bool ok = fp && hdr;
+            if (ok) {
+                /* bam_data.c:293: every record overlapping [0, SONIC length) of this target */
+                hts_itr_t* it = sam_itr_queryi(idx, t.tid, 0, t.length);
+                if (!it) ok = false;
+                else {
+                    while (sam_itr_next(fp, it, b) > 0) {
+                        const bam1_core_t& c = b->core;
+                        cg_read r;
+                        r.pos = (int32_t)c.pos;
+                        r.len = c.l_qseq > 65535 ? 65535 : (uint16_t)c.l_qseq;
+                        r.mapq = c.qual;
+                        r.fl = (uint8_t)(((c.flag & BAM_FSECONDARY) ? 1 : 0) | ((c.flag & BAM_FQCFAIL) ? 2 : 0) | ((c.flag & BAM_FDUP) ? 4 : 0)
+                             | ((c.flag & BAM_FSUPPLEMENTARY) ? 8 : 0) | ((c.flag & BAM_FUNMAP) ? 16 : 0) | ((c.flag & BAM_FREVERSE) ? 32 : 0));
+                        t.reads.push_back(r);
+                    }
+                    sam_itr_destroy(it);
+                }
+            }
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                t.failed = !ok;
+                t.done = true;
+            }
+            cv.notify_all();
+        }
+        bam_destroy1(b);
+        if (hdr) bam_hdr_destroy(hdr);
+        if (fp) hts_close(fp);
+    }
+
+    ChromTask& wait_for(size_t k)
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return tasks[k].done; });
+        return tasks[k];
+    }
+    void release(size_t k)
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            std::vector<cg_read>().swap(tasks[k].reads);
+            consumed = k + 1;
+        }
+        cv.notify_all();
+    }
+};
+
+/* ---- output_SVs, likelihood.c:172-288 ---------------------------------------------------- */
+struct Totals { int dels = 0, dups = 0; };
+
+void write_rows(const Params& p, const char* chr, const std::vector<cg_cnv>& dels, const std::vector<cg_call>& dcall,
+                const std::vector<cg_cnv>& dups, const std::vector<cg_call>& ucall, FILE* fp_svs, FILE* fp_del, FILE* fp_dup, Totals& tot)
+{
+    int n_del = 0, n_dup = 0;
+    const float c_score = p.c_score;
+    const float inv_c = 1 / c_score;                               /* `1 / params->c_score`: a float quotient */
+    if (p.has_del) {
+        for (size_t i = 0; i < dels.size(); i++) {
+            const cg_call& r = dcall[i];
+            const char* gt = r.score < c_score ? (r.copy_number == 2 ? "1/1" : "0/1") : (r.score <= inv_c ? "N/A" : "0/0");
+            const int border_rp = 0;                               /* split reads are not built (A19: 0 without --rp and --dups) */
+            if (p.has_map) {
+                fprintf(fp_del, "%s\t%d\t%d\t%s\t%.2f\t%d\t%.2lf\t%d\t%.1f\n", chr, dels[i].start, dels[i].end, gt, r.score, border_rp,
+                        r.mappability, r.observed, r.expected);
+                if (r.score < c_score && r.mappability > 0.5) {
+                    fprintf(fp_svs, "%s\t%d\t%d\tDEL\t%s\t%.2f\t%d\t%.2lf\n", chr, dels[i].start, dels[i].end,
+                            r.copy_number == 2 ? "1/1" : "0/1", r.score, border_rp, r.mappability);
+                    n_del++;
+                }
+            } else {
+                fprintf(fp_del, "%s\t%d\t%d\t%s\t%.2f\t%d\tN/A\t%d\t%.1f\n", chr, dels[i].start, dels[i].end, gt, r.score, border_rp,
+                        r.observed, r.expected);
+                if (r.score < c_score) {
+                    fprintf(fp_svs, "%s\t%d\t%d\tDEL\t%s\t%.2f\t%d\n", chr, dels[i].start, dels[i].end,
+                            r.copy_number == 2 ? "1/1" : "0/1", r.score, border_rp);
+                    n_del++;
+                }
+            }
+        }
+    }
+    if (p.has_dup) {
+        for (size_t i = 0; i < dups.size(); i++) {
+            const cg_call& r = ucall[i];
+            const char* gt = r.copy_number == 2 ? "1/1" : "0/1";
+            const int rp = 0;
+            if (p.has_map) {
+                fprintf(fp_dup, "%s\t%d\t%d\t%s\t%.2lf\t%d\t%.2lf\t%d\t%.1f\n", chr, dups[i].start, dups[i].end, gt, r.score, rp,
+                        r.mappability, r.observed, r.expected);
+                if (r.score < c_score && r.mappability > 0.5) {
+                    fprintf(fp_svs, "%s\t%d\t%d\tDUP\t%s\t%.2lf\t%d\t%.2lf\n", chr, dups[i].start, dups[i].end, gt, r.score, rp, r.mappability);
+                    n_dup++;
+                }
+            } else {
+                fprintf(fp_dup, "%s\t%d\t%d\t%s\t%.2lf\t%d\tN/A\t%d\t%.1f\n", chr, dups[i].start, dups[i].end, gt, r.score, rp,
+                        r.observed, r.expected);
+                if (r.score < c_score) {
+                    fprintf(fp_svs, "%s\t%d\t%d\tDUP\t%s\t%.2lf\t%d\tN/A\n", chr, dups[i].start, dups[i].end, gt, r.score, rp);
+                    n_dup++;
+                }
+            }
+        }
+    }
+    fprintf(stderr, "\nFound %d DELs - %d DUPs\n\n", n_del, n_dup);
+    tot.dels += n_del;
+    tot.dups += n_dup;
+}
+
+/* CNVs of one chromosome as find_SVs sees them: rows whose column 1 equals the BAM target name and whose
+ * length reaches min_sv_size (svs.c:55), sorted by start then end (common.c:199-215; stable, like glibc's
+ * merge-sorting qsort, for rows that compare equal). */
+std::vector<cg_cnv> select_cnvs(const std::map<std::string, std::vector<BedRow>>& bed, const char* chr, int min_sv_size)
+{
+    std::vector<cg_cnv> v;
+    auto it = bed.find(chr);
+    if (it == bed.end()) return v;
+    for (const BedRow& r : it->second)
+        if (r.end - r.start >= min_sv_size) { cg_cnv c; c.start = r.start; c.end = r.end; v.push_back(c); }
+    std::stable_sort(v.begin(), v.end(), [](const cg_cnv& a, const cg_cnv& b) { return a.start != b.start ? a.start < b.start : a.end < b.end; });
+    return v;
+}
+
+#define CG(ctx, call) do { if ((call) != CG_OK) die("Error: %s: %s", #call, cg_last_error(ctx)); } while (0)
+
+/* read_bam, bam_data.c:224-359 */
+void run(Params& p, Totals& tot)
+{
+    const std::string f_svs = p.outdir + p.outprefix + "_svs.bed";
+    fprintf(stderr, "\nOutput SV file: %s\n", f_svs.c_str());
+    FILE* fp_svs = open_or_die(f_svs, "w");
+    fprintf(fp_svs, "#CHR\tSTART_SV\tEND_SV\tSV_TYPE\tCOPY_NUMBER\tLIKELIHOOD\tREAD_PAIR\tMAPPABILITY\n");
+    FILE *fp_del = nullptr, *fp_dup = nullptr;
+    if (p.has_del) {
+        const std::string f = p.outdir + p.outprefix + "_dels.bed";
+        fprintf(stderr, "Output Del file: %s\n", f.c_str());
+        fp_del = open_or_die(f, "w");
+        fprintf(fp_del, "#CHR\tSTART_SV\tEND_SV\tCOPY_NUMBER\tLIKELIHOOD\tREAD_PAIR\tMAPPABILITY\tOBSERVED_READS\tEXPECTED_READS\n");
+    }
+    if (p.has_dup) {
+        const std::string f = p.outdir + p.outprefix + "_dups.bed";
+        fprintf(stderr, "Output DUP file: %s\n", f.c_str());
+        fp_dup = open_or_die(f, "w");
+        fprintf(fp_dup, "#CHR\tSTART_SV\tEND_SV\tCOPY_NUMBER\tLIKELIHOOD\tREAD_PAIR\tMAPPABILITY\tOBSERVED_READS\tEXPECTED_READS\n");
+    }
+
+    htsFile* fp = hts_open(p.bam_file.c_str(), "r");
+    if (!fp) die("Error opening BAM file %s", p.bam_file.c_str());
+    bam_hdr_t* hdr = sam_hdr_read(fp);
+    if (!hdr) die("Error: cannot read the BAM header of %s", p.bam_file.c_str());
+    hts_idx_t* idx = sam_index_load(fp, p.bam_file.c_str());
+    if (!idx) die("Error: Sam Index cannot be loaded (sam_index_load)");
+
+    /* get_sample_name, common.c:325-352: first header token that starts with "SM" */
+    std::string sample = "";
+    {
+        std::string text(hdr->text ? hdr->text : "");
+        size_t i = 0;
+        while (i < text.size()) {
+            size_t j = text.find_first_of("\t\n", i);
+            if (j == std::string::npos) j = text.size();
+            if (j - i >= 2 && text[i] == 'S' && text[i + 1] == 'M') { sample = j - i > 3 ? text.substr(i + 3, j - i - 3) : ""; break; }
+            i = j + 1;
+        }
+    }
+
+    sonic* sn = p.this_sonic;
+    std::vector<ChromTask> tasks;
+    /* the chromosome loop's selection logic, bam_data.c:269-291 */
+    for (int ci = 0; ci < sn->number_of_chromosomes; ci++) {
+        if (ci < p.first_chrom) ci = p.first_chrom;
+        if (ci > p.last_chrom || ci >= sn->number_of_chromosomes) break;
+        const char* name = sn->chromosome_names[ci];
+        if (strstr(name, "X") || strstr(name, "Y")) continue;
+        int tid = -1;
+        for (int t = 0; t < hdr->n_targets; t++) if (strcmp(name, hdr->target_name[t]) == 0) { tid = t; break; }
+        ChromTask t;
+        t.chr_index = ci; t.tid = tid; t.length = sn->chromosome_lengths[ci];
+        tasks.push_back(std::move(t));
+    }
+
+    std::map<std::string, std::vector<BedRow>> del_bed, dup_bed;
+    std::map<std::string, std::vector<cg_mapiv>> map_bed;
+    if (p.has_del) del_bed = read_cnv_bed(p.del_file);
+    if (p.has_dup) dup_bed = read_cnv_bed(p.dup_file);
+    if (p.has_map) map_bed = read_mappability_bed(p.mappability_file);
+
+    const char* dev_env = getenv("CONGA_GPU_DEVICE");
+    cg_ctx* ctx = cg_create(dev_env ? atoi(dev_env) : 0);
+    if (!ctx) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
+
+    /* tasks for targets missing from the BAM are never decoded */
+    std::vector<ChromTask> todo;
+    std::vector<size_t> todo_of(tasks.size(), (size_t)-1);
+    for (size_t k = 0; k < tasks.size(); k++) if (tasks[k].tid >= 0) { todo_of[k] = todo.size(); todo.push_back(tasks[k]); }
+    int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
+    if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
+    n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
+    Decoder dec(p, todo, idx, n_threads, (size_t)n_threads + 2);
+
+    for (size_t k = 0; k < tasks.size(); k++) {
+        const int ci = tasks[k].chr_index;
+        if (tasks[k].tid < 0) {
+            fprintf(stderr, "\nCannot find chromosome name %s in BAM/CRAM %s", sn->chromosome_names[ci], sample.c_str());
+            continue;
+        }
+        ChromTask& t = dec.wait_for(todo_of[k]);
+        if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
+        const char* chr = hdr->target_name[t.tid];
+        fprintf(stderr, "\nReading BAM [%s] - Chromosome: %s", sample.c_str(), chr);
+        fprintf(stderr, "\n-->counting reads");
+
+        /* seams 1-3 */
+        CG(ctx, cg_chrom_begin(ctx, ci, t.length, (const int8_t*)sn->chromosome_gc_profile[ci], t.length / 100 + 1, p.mq_threshold));
+        const size_t BATCH = (size_t)1 << 22;
+        for (size_t i = 0; i < t.reads.size(); i += BATCH)
+            CG(ctx, cg_push_reads(ctx, t.reads.data() + i, std::min(BATCH, t.reads.size() - i)));
+        cg_chrom_stats st;
+        CG(ctx, cg_chrom_finish(ctx, &st));
+        fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)st.reads_passed, 0L);
+        dec.release(todo_of[k]);
+        {   /* calc_mu_per_chr, read_distribution.c:39-41 */
+            const float mean = (float)((double)st.rd_cnt / (double)(long)t.length);
+            fprintf(g_log, "Read Count:%li  Window count:%li mean=%f\n", (long)st.rd_cnt, (long)t.length, mean);
+        }
+
+        /* find_SVs, likelihood.c:311-371 */
+        fprintf(stderr, "\nLoading known SVs");
+        std::vector<cg_cnv> dels, dups;
+        if (p.has_del) dels = select_cnvs(del_bed, chr, p.min_sv_size);
+        if (p.has_dup) dups = select_cnvs(dup_bed, chr, p.min_sv_size);
+        fprintf(stderr, "(%d DELS, %d DUPS in chromosome %s - larger than the threshold %d)\n", (int)dels.size(), (int)dups.size(), chr, p.min_sv_size);
+        if (dels.empty() && dups.empty()) continue;                 /* likelihood.c:332-336 */
+        fprintf(stderr, "Finding mappability for each region\n");
+        if (p.has_map) {
+            auto it = map_bed.find(chr);
+            if (it != map_bed.end() && !it->second.empty()) CG(ctx, cg_set_mappability(ctx, it->second.data(), it->second.size()));
+            else CG(ctx, cg_set_mappability_runs(ctx, nullptr, 0, 1));   /* --mappability given, no row here: 0.0 everywhere */
+        }
+        fprintf(stderr, "\nCalculating Likelihoods\n");
+        std::vector<cg_call> dcall(dels.size()), ucall(dups.size());
+        if (!dels.empty()) CG(ctx, cg_genotype(ctx, dels.data(), dels.size(), 0, dcall.data()));
+        if (!dups.empty()) CG(ctx, cg_genotype(ctx, dups.data(), dups.size(), 1, ucall.data()));
+        write_rows(p, chr, dels, dcall, dups, ucall, fp_svs, fp_del, fp_dup, tot);
+    }
+
+    cg_destroy(ctx);
+    if (hts_close(fp) != 0) die("Error closing BAM file");
+    bam_hdr_destroy(hdr);
+    hts_idx_destroy(idx);
+    fprintf(stderr, "\n");
+    if (fp_del) fclose(fp_del);
+    if (fp_dup) fclose(fp_dup);
+    fclose(fp_svs);
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    time_t raw;
+    time(&raw);
+    const struct tm* ti = localtime(&raw);
+    g_log = open_or_die("conga.log", "w");                          /* svdepth.c:30: always in the CWD */
+    fprintf(g_log, "#CreationDate=%d.%d.%d\n\n", ti->tm_year + 1900, ti->tm_mon + 1, ti->tm_mday);
+
+    Params p;
+    const int rc = parse_cmd_line(argc, argv, p);
+    if (rc == 3) return EXIT_FAILURE;
+    if (rc == 0) return EXIT_SUCCESS;
+    print_params(p);
+    if (!p.no_sr && p.has_dup)
+        die("[CONGA-B200] --rp (split-read support) together with --dups is not built yet; run without --rp");
+    if (!p.has_sonic) die("[CONGA CMDLINE ERROR] Please enter the SONIC file using the --sonic option.");
+
+    p.this_sonic = sonic_load(const_cast<char*>(p.sonic_file.c_str()));
+    if (!p.this_sonic) die("Error: cannot load SONIC file %s", p.sonic_file.c_str());
+    if (p.last_chrom < p.first_chrom) p.last_chrom = p.this_sonic->number_of_chromosomes - 1;   /* svdepth.c:49-50 */
+
+    Totals tot;
+    run(p, tot);
+
+    char user[256] = "";
+    if (getlogin_r(user, sizeof user - 1) != 0) snprintf(user, sizeof user, "you");
+    fprintf(stderr, "\nThank you %s. I found %d DELs and %d DUPs. Hope to see you again...\n", user, tot.dels, tot.dups);
+    fclose(g_log);
+    return EXIT_SUCCESS;
+}

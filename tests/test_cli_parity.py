@@ -1,0 +1,110 @@
+"""Drop-in check at the command line: `conga-b200` (conga_b200/host, the four seams routed through
+libconga_gpu.so) against the UNMODIFIED reference program (oracle/_ref/conga) on the same BAM, SONIC and
+BED files.  <out>_svs.bed, <out>_dels.bed, <out>_dups.bed and the conga.log chromosome lines must be
+byte-identical."""
+import os
+import shutil
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import cli_inputs
+
+pytestmark = pytest.mark.gpu
+ROOT = cli_inputs.ROOT
+HOST = os.path.join(ROOT, "conga_b200", "host", "conga-b200")
+REF_CONGA = os.path.join(cli_inputs.REF, "conga")
+
+
+def run_both(tmp, paths, flags):
+    outs = {}
+    for tag, exe in (("ref", REF_CONGA), ("b200", HOST)):
+        wd = os.path.join(tmp, tag)
+        os.makedirs(os.path.join(wd, "o"), exist_ok=True)
+        cmd = [exe, "-i", paths["bam"], "--ref", paths["ref"], "--sonic", paths["sonic"], "--out", os.path.join(wd, "o", "s")] + flags
+        p = subprocess.run(cmd, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+        assert p.returncode == 0, "%s failed:\n%s" % (tag, p.stderr.decode()[-2000:])
+        files = {}
+        for nm in ("s_svs.bed", "s_dels.bed", "s_dups.bed"):
+            f = os.path.join(wd, "o", nm)
+            files[nm] = open(f, "rb").read() if os.path.exists(f) else None
+        log = open(os.path.join(wd, "conga.log"), "rb").read().split(b"\n")
+        # line 0 is the creation date; the BAM/ref/SONIC/first/last lines and one line per chromosome follow
+        files["log"] = b"\n".join(log[1:])
+        outs[tag] = files
+    return outs
+
+
+def assert_same(outs, expect_rows=True):
+    for nm in outs["ref"]:
+        assert outs["ref"][nm] == outs["b200"][nm], "%s differs from the reference's" % nm
+    if expect_rows:
+        assert outs["ref"]["s_svs.bed"].count(b"\n") > 1, "the case genotypes nothing: not a test"
+
+
+@pytest.fixture(scope="module")
+def tools():
+    if not cli_inputs.have_reference_binaries():
+        pytest.fail("oracle/_ref binaries missing: run `make -C oracle ref` where /root/reference exists")
+    if not os.path.exists(HOST):
+        pytest.fail("conga_b200/host/conga-b200 missing: run `make -C conga_b200/host`")
+
+
+def test_plain_dels_and_dups(tools):
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(101)
+        paths = cli_inputs.build_inputs(tmp, [("1", 400_000), ("2", 250_000), ("X", 100_000), ("MT", 16_500)], rng)
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"]])
+        assert_same(outs)
+        assert b"DEL" in outs["ref"]["s_svs.bed"] and b"X\t" not in outs["ref"]["s_dels.bed"]
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_mappability_min_mapq_c_score(tools):
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(102)
+        paths = cli_inputs.build_inputs(tmp, [("1", 300_000), ("chr2", 200_000)], rng, reads_per_mb=60000, with_map=True)
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"], "--mappability", paths["map"],
+                                     "--min-mapq", "20", "--c-score", "0.3", "--min-sv-size", "1200"])
+        assert_same(outs)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_chromosome_range_missing_target_and_dels_only(tools):
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(103)
+        chroms = [("1", 200_000), ("2", 150_000), ("3", 120_000), ("4", 100_000)]
+        paths = cli_inputs.build_inputs(tmp, chroms, rng, bam_chroms={"1", "2", "4"})        # "3" is not in the BAM
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--first-chr", "1", "--last-chr", "3"])
+        assert_same(outs)
+        assert outs["ref"]["s_dups.bed"] is None and b"\n1\t" not in outs["ref"]["s_dels.bed"]
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_int16_wrap_pileup_through_the_cli(tools):
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(104)
+        paths = cli_inputs.build_inputs(tmp, [("1", 200_000)], rng, reads_per_mb=3000, pileup=True)
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"]])
+        assert_same(outs)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_rp_is_refused_not_ignored(tools):
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        p = subprocess.run([HOST, "-i", "x.bam", "--ref", "r.fa", "--sonic", "s.sonic", "--out", "o", "--dups", "d.bed", "--rp", "5"],
+                           cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert p.returncode == 1 and b"--rp" in p.stderr
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
