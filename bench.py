@@ -356,8 +356,15 @@ def own_arm(args):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     pass_ms, pass_n = k_ms[1], max(1, k_n[1])
     achieved = alg * args.steps / (pass_ms / 1e3) / 1e9 if pass_ms > 0 else 0.0
+    # DRAM bytes per launch from the committed ncu capture of this command (profiles/traffic.json, written by
+    # scripts/traffic_summary.py from scripts/gpu_traffic.sh); only meaningful for the workload it was taken on
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath) and args.workload == "c2" and args.scale == 1.0 and world == 1:
+        tj = json.load(open(tpath))
+        traffic, traffic_src = int(tj["traffic_bytes_per_launch"]), tj["source"]
     roofline = {"kernel": "k_depth_pass", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg // max(1, len(mine)), "launches": int(pass_n),
                 "avg_launch_ms": round(pass_ms / pass_n, 4),
                 "kernel_ms_per_step": {"prep": round(k_ms[0] / args.steps, 4), "depth_pass": round(k_ms[1] / args.steps, 4),

@@ -19,7 +19,11 @@
  *     BED once PER CHROMOSOME, svs.c:7-240, :317-377);
  *   * htslib decoding runs in worker threads, one chromosome per task with its own htsFile and
  *     iterator (the index makes chromosomes independently seekable), ahead of the GPU;
- *   * there is no short read_depth[L] and no float mappability[L] on the host at all.
+ *   * there is no short read_depth[L] and no float mappability[L] on the host at all;
+ *   * CONGA_GPUS=N spreads the chromosomes over N GPUs of the box (longest-processing-time by
+ *     length, one host thread per GPU) and ends with the path's one collective, an NCCL all-reduce
+ *     of the per-chromosome statistics table over NVLink; the outputs are written in SONIC order
+ *     and do not depend on N.
  *
  * There is no CPU implementation of the numeric stages in this program: without the library and
  * a B200 it stops with an error.  --rp (split-read support, split_read.c) is not built yet and is
@@ -35,6 +39,7 @@
 #include <cctype>
 #include <chrono>
 #include <condition_variable>
+#include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -48,6 +53,9 @@
 #include <htslib/hts.h>
 #include <htslib/sam.h>
 #include "sonic.h"
+
+#include <cuda_runtime.h>
+#include <nccl.h>
 
 #include "conga_gpu.h"
 
@@ -117,7 +125,8 @@ void print_help()
     fprintf(stdout, "\t--min-mapq [INT]          : Minimum mapping quality filter for reads (default: no-filter)\n");
     fprintf(stdout, "\t--c-score [FLOAT]         : Minimum c-score to filter variants (default: 0.5).\n");
     fprintf(stdout, "\t--rp [INT]                : Split-read support for duplications (not available in this build).\n");
-    fprintf(stdout, "\n\tEnvironment: CONGA_GPU_DEVICE (CUDA device, default 0), CONGA_DECODE_THREADS (default: cores, at most 16)\n");
+    fprintf(stdout, "\n\tEnvironment: CONGA_GPUS (GPUs to spread the chromosomes over, default 1), CONGA_GPU_DEVICE (first CUDA device,\n"
+                    "\tdefault 0), CONGA_DECODE_THREADS (default: cores, at most 16)\n");
     fprintf(stdout, "\n\tInformation:\n\t--version                 : Print version and exit.\n\t--help                    : Print this help screen and exit.\n\n");
 }
 
@@ -277,7 +286,7 @@ struct Decoder {
     std::atomic<size_t> next{0};
     std::mutex mu;
     std::condition_variable cv;
-    size_t consumed = 0;                  /* tasks the main thread is done with */
+    size_t consumed = 0;                  /* tasks the consumers are done with (any order) */
     size_t window;                        /* decode at most this many tasks ahead of the consumer */
     std::vector<std::thread> threads;
 
@@ -296,7 +305,9 @@ struct Decoder {
         for (;;) {
             const size_t k = next.fetch_add(1);
             if (k >= tasks.size()) break;
-            {   /* bounded look-ahead: the reads of a whole chromosome are held in memory */
+            {   /* bounded look-ahead: the reads of a whole chromosome are held in memory.  Every consumer
+                 * takes its tasks in increasing order, so the smallest unreleased task is always
+                 * inside the window and progress is guaranteed. */
                 std::unique_lock<std::mutex> lk(mu);
                 cv.wait(lk, [&] { return k < consumed + window; });
             }
@@ -343,7 +354,7 @@ struct Decoder {
         {
             std::lock_guard<std::mutex> lk(mu);
             std::vector<cg_read>().swap(tasks[k].reads);
-            consumed = k + 1;
+            consumed++;
         }
         cv.notify_all();
     }
@@ -423,7 +434,116 @@ std::vector<cg_cnv> select_cnvs(const std::map<std::string, std::vector<BedRow>>
     return v;
 }
 
+/* ncclAllReduce(int64, sum) of the statistics tables, one communicator per GPU of this process */
+void allreduce_stats_tables(std::vector<cg_ctx*>& ctx, int first_dev, int n_rows)
+{
+    const int n = (int)ctx.size();
+    std::vector<int> devs(n);
+    for (int g = 0; g < n; g++) devs[g] = first_dev + g;
+    std::vector<ncclComm_t> comms(n);
+    ncclResult_t rc = ncclCommInitAll(comms.data(), n, devs.data());
+    if (rc != ncclSuccess) die("Error: ncclCommInitAll: %s", ncclGetErrorString(rc));
+    std::vector<void*> tables(n);
+    for (int g = 0; g < n; g++) {
+        int32_t rows = 0;
+        if (cg_stats_table(ctx[g], &tables[g], &rows) != CG_OK || cg_join(ctx[g]) != CG_OK) die("Error: %s", cg_last_error(ctx[g]));
+    }
+    ncclGroupStart();
+    for (int g = 0; g < n; g++) {
+        rc = ncclAllReduce(tables[g], tables[g], (size_t)n_rows * 204, ncclInt64, ncclSum, comms[g], (cudaStream_t)cg_stream(ctx[g]));
+        if (rc != ncclSuccess) die("Error: ncclAllReduce: %s", ncclGetErrorString(rc));
+    }
+    rc = ncclGroupEnd();
+    if (rc != ncclSuccess) die("Error: ncclGroupEnd: %s", ncclGetErrorString(rc));
+    for (int g = 0; g < n; g++) if (cg_sync(ctx[g]) != CG_OK) die("Error: cg_sync: %s", cg_last_error(ctx[g]));
+    for (int g = 0; g < n; g++) ncclCommDestroy(comms[g]);
+}
+
 #define CG(ctx, call) do { if ((call) != CG_OK) die("Error: %s: %s", #call, cg_last_error(ctx)); } while (0)
+
+/* everything one chromosome contributes to the outputs */
+struct ChromResult {
+    bool in_bam = false, has_cnvs = false;
+    std::string chr;                      /* BAM target name: what column 1 of the BEDs is compared with */
+    int32_t length = 0;
+    cg_chrom_stats st;
+    std::vector<cg_cnv> dels, dups;
+    std::vector<cg_call> dcall, ucall;
+    bool done = false;
+};
+
+struct Inputs {
+    std::map<std::string, std::vector<BedRow>> del_bed, dup_bed;
+    std::map<std::string, std::vector<cg_mapiv>> map_bed;
+};
+
+/* The body of the reference's chromosome loop (bam_data.c:304-338) for one chromosome on one context. */
+void process_chromosome(const Params& p, const Inputs& in, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
+{
+    sonic* sn = p.this_sonic;
+    /* seams 1-3 */
+    CG(ctx, cg_chrom_begin(ctx, t.chr_index, t.length, (const int8_t*)sn->chromosome_gc_profile[t.chr_index], t.length / 100 + 1, p.mq_threshold));
+    const size_t BATCH = (size_t)1 << 22;
+    for (size_t i = 0; i < t.reads.size(); i += BATCH)
+        CG(ctx, cg_push_reads(ctx, t.reads.data() + i, std::min(BATCH, t.reads.size() - i)));
+    CG(ctx, cg_chrom_finish(ctx, &r.st));
+    /* find_SVs, likelihood.c:311-371 */
+    if (p.has_del) r.dels = select_cnvs(in.del_bed, r.chr.c_str(), p.min_sv_size);
+    if (p.has_dup) r.dups = select_cnvs(in.dup_bed, r.chr.c_str(), p.min_sv_size);
+    r.has_cnvs = !(r.dels.empty() && r.dups.empty());
+    if (!r.has_cnvs) return;                                        /* likelihood.c:332-336 */
+    if (p.has_map) {
+        auto it = in.map_bed.find(r.chr);
+        if (it != in.map_bed.end() && !it->second.empty()) CG(ctx, cg_set_mappability(ctx, it->second.data(), it->second.size()));
+        else CG(ctx, cg_set_mappability_runs(ctx, nullptr, 0, 1));   /* --mappability given, no row here: 0.0 everywhere */
+    }
+    r.dcall.resize(r.dels.size());
+    r.ucall.resize(r.dups.size());
+    if (!r.dels.empty()) CG(ctx, cg_genotype(ctx, r.dels.data(), r.dels.size(), 0, r.dcall.data()));
+    if (!r.dups.empty()) CG(ctx, cg_genotype(ctx, r.dups.data(), r.dups.size(), 1, r.ucall.data()));
+}
+
+/* What the reference prints and writes for one chromosome, in its order. */
+void emit_chromosome(const Params& p, const std::string& sample, const char* sonic_name, const ChromResult& r,
+                     FILE* fp_svs, FILE* fp_del, FILE* fp_dup, Totals& tot)
+{
+    if (!r.in_bam) {
+        fprintf(stderr, "\nCannot find chromosome name %s in BAM/CRAM %s", sonic_name, sample.c_str());
+        return;
+    }
+    const char* chr = r.chr.c_str();
+    fprintf(stderr, "\nReading BAM [%s] - Chromosome: %s", sample.c_str(), chr);
+    fprintf(stderr, "\n-->counting reads");
+    fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)r.st.reads_passed, 0L);
+    {   /* calc_mu_per_chr, read_distribution.c:39-41 */
+        const float mean = (float)((double)r.st.rd_cnt / (double)(long)r.length);
+        fprintf(g_log, "Read Count:%li  Window count:%li mean=%f\n", (long)r.st.rd_cnt, (long)r.length, mean);
+    }
+    fprintf(stderr, "\nLoading known SVs");
+    fprintf(stderr, "(%d DELS, %d DUPS in chromosome %s - larger than the threshold %d)\n", (int)r.dels.size(), (int)r.dups.size(), chr, p.min_sv_size);
+    if (!r.has_cnvs) return;
+    fprintf(stderr, "Finding mappability for each region\n");
+    fprintf(stderr, "\nCalculating Likelihoods\n");
+    write_rows(p, chr, r.dels, r.dcall, r.dups, r.ucall, fp_svs, fp_del, fp_dup, tot);
+}
+
+/* Longest-processing-time assignment by chromosome length: the depth pass streams
+ * 6 bytes per position, so length is the cost.  Same rule as conga_b200/multi.py. */
+std::vector<int> lpt_assign(const std::vector<ChromTask>& todo, int n_gpus)
+{
+    std::vector<size_t> order(todo.size());
+    for (size_t i = 0; i < order.size(); i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return todo[a].length > todo[b].length; });
+    std::vector<long long> load(n_gpus, 0);
+    std::vector<int> gpu_of(todo.size(), 0);
+    for (size_t i : order) {
+        int g = 0;
+        for (int k = 1; k < n_gpus; k++) if (load[k] < load[g]) g = k;
+        gpu_of[i] = g;
+        load[g] += todo[i].length;
+    }
+    return gpu_of;
+}
 
 /* read_bam, bam_data.c:224-359 */
 void run(Params& p, Totals& tot)
@@ -481,72 +601,83 @@ void run(Params& p, Totals& tot)
         tasks.push_back(std::move(t));
     }
 
-    std::map<std::string, std::vector<BedRow>> del_bed, dup_bed;
-    std::map<std::string, std::vector<cg_mapiv>> map_bed;
-    if (p.has_del) del_bed = read_cnv_bed(p.del_file);
-    if (p.has_dup) dup_bed = read_cnv_bed(p.dup_file);
-    if (p.has_map) map_bed = read_mappability_bed(p.mappability_file);
-
-    const char* dev_env = getenv("CONGA_GPU_DEVICE");
-    cg_ctx* ctx = cg_create(dev_env ? atoi(dev_env) : 0);
-    if (!ctx) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
+    Inputs in;
+    if (p.has_del) in.del_bed = read_cnv_bed(p.del_file);
+    if (p.has_dup) in.dup_bed = read_cnv_bed(p.dup_file);
+    if (p.has_map) in.map_bed = read_mappability_bed(p.mappability_file);
 
     /* tasks for targets missing from the BAM are never decoded */
     std::vector<ChromTask> todo;
     std::vector<size_t> todo_of(tasks.size(), (size_t)-1);
-    for (size_t k = 0; k < tasks.size(); k++) if (tasks[k].tid >= 0) { todo_of[k] = todo.size(); todo.push_back(tasks[k]); }
+    std::vector<ChromResult> results(tasks.size());
+    for (size_t k = 0; k < tasks.size(); k++) {
+        if (tasks[k].tid < 0) continue;
+        todo_of[k] = todo.size();
+        todo.push_back(tasks[k]);
+        results[k].in_bam = true;
+        results[k].chr = hdr->target_name[tasks[k].tid];
+        results[k].length = tasks[k].length;
+    }
+    std::vector<size_t> task_of_todo(todo.size());
+    for (size_t k = 0; k < tasks.size(); k++) if (todo_of[k] != (size_t)-1) task_of_todo[todo_of[k]] = k;
+
+    /* GPUs: CONGA_GPUS=N uses devices first..first+N-1 (first = CONGA_GPU_DEVICE, default 0) */
+    const int first_dev = getenv("CONGA_GPU_DEVICE") ? atoi(getenv("CONGA_GPU_DEVICE")) : 0;
+    int n_gpus = getenv("CONGA_GPUS") ? std::max(1, atoi(getenv("CONGA_GPUS"))) : 1;
+    n_gpus = (int)std::min<size_t>((size_t)n_gpus, std::max<size_t>(1, todo.size()));
+    std::vector<cg_ctx*> ctx(n_gpus, nullptr);
+    for (int g = 0; g < n_gpus; g++) {
+        ctx[g] = cg_create(first_dev + g);
+        if (!ctx[g]) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
+    }
+    const std::vector<int> gpu_of = lpt_assign(todo, n_gpus);
+
     int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
     if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
     n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
-    Decoder dec(p, todo, idx, n_threads, (size_t)n_threads + 2);
+    Decoder dec(p, todo, idx, n_threads, (size_t)n_threads + 2 * (size_t)n_gpus);
 
-    for (size_t k = 0; k < tasks.size(); k++) {
-        const int ci = tasks[k].chr_index;
-        if (tasks[k].tid < 0) {
-            fprintf(stderr, "\nCannot find chromosome name %s in BAM/CRAM %s", sn->chromosome_names[ci], sample.c_str());
-            continue;
+    if (n_gpus == 1) {
+        /* streaming, like the reference: each chromosome is written as soon as it is genotyped */
+        for (size_t k = 0; k < tasks.size(); k++) {
+            if (results[k].in_bam) {
+                ChromTask& t = dec.wait_for(todo_of[k]);
+                if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
+                process_chromosome(p, in, ctx[0], t, results[k]);
+                dec.release(todo_of[k]);
+            }
+            emit_chromosome(p, sample, sn->chromosome_names[tasks[k].chr_index], results[k], fp_svs, fp_del, fp_dup, tot);
         }
-        ChromTask& t = dec.wait_for(todo_of[k]);
-        if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
-        const char* chr = hdr->target_name[t.tid];
-        fprintf(stderr, "\nReading BAM [%s] - Chromosome: %s", sample.c_str(), chr);
-        fprintf(stderr, "\n-->counting reads");
-
-        /* seams 1-3 */
-        CG(ctx, cg_chrom_begin(ctx, ci, t.length, (const int8_t*)sn->chromosome_gc_profile[ci], t.length / 100 + 1, p.mq_threshold));
-        const size_t BATCH = (size_t)1 << 22;
-        for (size_t i = 0; i < t.reads.size(); i += BATCH)
-            CG(ctx, cg_push_reads(ctx, t.reads.data() + i, std::min(BATCH, t.reads.size() - i)));
-        cg_chrom_stats st;
-        CG(ctx, cg_chrom_finish(ctx, &st));
-        fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)st.reads_passed, 0L);
-        dec.release(todo_of[k]);
-        {   /* calc_mu_per_chr, read_distribution.c:39-41 */
-            const float mean = (float)((double)st.rd_cnt / (double)(long)t.length);
-            fprintf(g_log, "Read Count:%li  Window count:%li mean=%f\n", (long)st.rd_cnt, (long)t.length, mean);
+    } else {
+        /* one host thread per GPU, each walking its own chromosomes in SONIC order */
+        std::vector<std::thread> workers;
+        for (int g = 0; g < n_gpus; g++)
+            workers.emplace_back([&, g] {
+                for (size_t j = 0; j < todo.size(); j++) {
+                    if (gpu_of[j] != g) continue;
+                    ChromTask& t = dec.wait_for(j);
+                    if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
+                    process_chromosome(p, in, ctx[g], t, results[task_of_todo[j]]);
+                    dec.release(j);
+                }
+            });
+        for (auto& w : workers) w.join();
+        /* the path's one collective: every GPU's int64[n_chrom][204] statistics table summed over NVLink, so
+         * that the writer of conga.log (GPU 0's host side) holds every chromosome's row; a chromosome's row is
+         * zero everywhere but on the GPU that processed it */
+        allreduce_stats_tables(ctx, first_dev, sn->number_of_chromosomes);
+        for (size_t k = 0; k < tasks.size(); k++) {
+            if (results[k].in_bam) {
+                cg_chrom_stats st;
+                CG(ctx[0], cg_stats_row(ctx[0], tasks[k].chr_index, &st));
+                if (memcmp(&st, &results[k].st, sizeof st) != 0) die("Error: statistics row %d differs after the all-reduce", tasks[k].chr_index);
+                results[k].st = st;
+            }
+            emit_chromosome(p, sample, sn->chromosome_names[tasks[k].chr_index], results[k], fp_svs, fp_del, fp_dup, tot);
         }
-
-        /* find_SVs, likelihood.c:311-371 */
-        fprintf(stderr, "\nLoading known SVs");
-        std::vector<cg_cnv> dels, dups;
-        if (p.has_del) dels = select_cnvs(del_bed, chr, p.min_sv_size);
-        if (p.has_dup) dups = select_cnvs(dup_bed, chr, p.min_sv_size);
-        fprintf(stderr, "(%d DELS, %d DUPS in chromosome %s - larger than the threshold %d)\n", (int)dels.size(), (int)dups.size(), chr, p.min_sv_size);
-        if (dels.empty() && dups.empty()) continue;                 /* likelihood.c:332-336 */
-        fprintf(stderr, "Finding mappability for each region\n");
-        if (p.has_map) {
-            auto it = map_bed.find(chr);
-            if (it != map_bed.end() && !it->second.empty()) CG(ctx, cg_set_mappability(ctx, it->second.data(), it->second.size()));
-            else CG(ctx, cg_set_mappability_runs(ctx, nullptr, 0, 1));   /* --mappability given, no row here: 0.0 everywhere */
-        }
-        fprintf(stderr, "\nCalculating Likelihoods\n");
-        std::vector<cg_call> dcall(dels.size()), ucall(dups.size());
-        if (!dels.empty()) CG(ctx, cg_genotype(ctx, dels.data(), dels.size(), 0, dcall.data()));
-        if (!dups.empty()) CG(ctx, cg_genotype(ctx, dups.data(), dups.size(), 1, ucall.data()));
-        write_rows(p, chr, dels, dcall, dups, ucall, fp_svs, fp_del, fp_dup, tot);
     }
 
-    cg_destroy(ctx);
+    for (cg_ctx* c : ctx) cg_destroy(c);
     if (hts_close(fp) != 0) die("Error closing BAM file");
     bam_hdr_destroy(hdr);
     hts_idx_destroy(idx);

@@ -18,13 +18,14 @@ HOST = os.path.join(ROOT, "conga_b200", "host", "conga-b200")
 REF_CONGA = os.path.join(cli_inputs.REF, "conga")
 
 
-def run_both(tmp, paths, flags):
+def run_both(tmp, paths, flags, env=None):
     outs = {}
     for tag, exe in (("ref", REF_CONGA), ("b200", HOST)):
         wd = os.path.join(tmp, tag)
         os.makedirs(os.path.join(wd, "o"), exist_ok=True)
         cmd = [exe, "-i", paths["bam"], "--ref", paths["ref"], "--sonic", paths["sonic"], "--out", os.path.join(wd, "o", "s")] + flags
-        p = subprocess.run(cmd, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+        p = subprocess.run(cmd, cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600,
+                           env=dict(os.environ, **(env or {})) if tag == "b200" else None)
         assert p.returncode == 0, "%s failed:\n%s" % (tag, p.stderr.decode()[-2000:])
         files = {}
         for nm in ("s_svs.bed", "s_dels.bed", "s_dups.bed"):
@@ -95,6 +96,24 @@ def test_int16_wrap_pileup_through_the_cli(tools):
         rng = np.random.default_rng(104)
         paths = cli_inputs.build_inputs(tmp, [("1", 200_000)], rng, reads_per_mb=3000, pileup=True)
         outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"]])
+        assert_same(outs)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_two_gpus_write_the_same_bytes(tools):
+    """CONGA_GPUS=2: chromosomes spread over two GPUs (LPT), NCCL all-reduce of the statistics table, outputs
+    in SONIC order — still byte-identical to the single-threaded reference."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(105)
+        chroms = [("1", 300_000), ("2", 260_000), ("3", 200_000), ("4", 150_000), ("5", 90_000), ("X", 50_000)]
+        paths = cli_inputs.build_inputs(tmp, chroms, rng, with_map=True, bam_chroms={"1", "2", "3", "5", "X"})
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"], "--mappability", paths["map"]],
+                        env={"CONGA_GPUS": "2"})
         assert_same(outs)
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
