@@ -85,6 +85,14 @@ struct Params {
 
 FILE* g_log = nullptr;
 
+/* CONGA_TIMING=1: phase times on stderr */
+const auto g_t0 = std::chrono::steady_clock::now();
+void tick(const char* what)
+{
+    static const bool on = getenv("CONGA_TIMING") != nullptr;
+    if (on) fprintf(stderr, "[timing] %8.3f s  %s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - g_t0).count(), what);
+}
+
 [[noreturn]] void die(const char* fmt, ...)
 {
     va_list ap;
@@ -545,8 +553,23 @@ std::vector<int> lpt_assign(const std::vector<ChromTask>& todo, int n_gpus)
     return gpu_of;
 }
 
+/* CUDA contexts brought up on side threads from the moment the command line is known */
+struct Gpus {
+    int first_dev = 0;
+    std::vector<cg_ctx*> ctx;
+    std::vector<std::thread> threads;
+    void start()
+    {
+        first_dev = getenv("CONGA_GPU_DEVICE") ? atoi(getenv("CONGA_GPU_DEVICE")) : 0;
+        const int n = getenv("CONGA_GPUS") ? std::max(1, atoi(getenv("CONGA_GPUS"))) : 1;
+        ctx.assign(n, nullptr);
+        for (int g = 0; g < n; g++) threads.emplace_back([this, g] { ctx[g] = cg_create(first_dev + g); });
+    }
+    void wait() { for (auto& t : threads) t.join(); threads.clear(); }
+};
+
 /* read_bam, bam_data.c:224-359 */
-void run(Params& p, Totals& tot)
+void run(Params& p, Totals& tot, Gpus& gpus)
 {
     const std::string f_svs = p.outdir + p.outprefix + "_svs.bed";
     fprintf(stderr, "\nOutput SV file: %s\n", f_svs.c_str());
@@ -601,11 +624,6 @@ void run(Params& p, Totals& tot)
         tasks.push_back(std::move(t));
     }
 
-    Inputs in;
-    if (p.has_del) in.del_bed = read_cnv_bed(p.del_file);
-    if (p.has_dup) in.dup_bed = read_cnv_bed(p.dup_file);
-    if (p.has_map) in.map_bed = read_mappability_bed(p.mappability_file);
-
     /* tasks for targets missing from the BAM are never decoded */
     std::vector<ChromTask> todo;
     std::vector<size_t> todo_of(tasks.size(), (size_t)-1);
@@ -621,21 +639,29 @@ void run(Params& p, Totals& tot)
     std::vector<size_t> task_of_todo(todo.size());
     for (size_t k = 0; k < tasks.size(); k++) if (todo_of[k] != (size_t)-1) task_of_todo[todo_of[k]] = k;
 
-    /* GPUs: CONGA_GPUS=N uses devices first..first+N-1 (first = CONGA_GPU_DEVICE, default 0) */
-    const int first_dev = getenv("CONGA_GPU_DEVICE") ? atoi(getenv("CONGA_GPU_DEVICE")) : 0;
-    int n_gpus = getenv("CONGA_GPUS") ? std::max(1, atoi(getenv("CONGA_GPUS"))) : 1;
-    n_gpus = (int)std::min<size_t>((size_t)n_gpus, std::max<size_t>(1, todo.size()));
-    std::vector<cg_ctx*> ctx(n_gpus, nullptr);
-    for (int g = 0; g < n_gpus; g++) {
-        ctx[g] = cg_create(first_dev + g);
-        if (!ctx[g]) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
-    }
+    /* GPUs: CONGA_GPUS=N uses devices first..first+N-1 (first = CONGA_GPU_DEVICE, default 0).  Bringing up a
+     * CUDA context takes from a few hundred milliseconds to more than a second; it happens on side threads
+     * while the BEDs are parsed and the first chromosomes are decoded. */
+    const int first_dev = gpus.first_dev;
+    const int n_gpus = (int)std::min<size_t>(gpus.ctx.size(), std::max<size_t>(1, todo.size()));
+    std::vector<cg_ctx*>& ctx = gpus.ctx;
     const std::vector<int> gpu_of = lpt_assign(todo, n_gpus);
 
     int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
     if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
     n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
     Decoder dec(p, todo, idx, n_threads, (size_t)n_threads + 2 * (size_t)n_gpus);
+    tick("decoders started");
+
+    Inputs in;
+    if (p.has_del) in.del_bed = read_cnv_bed(p.del_file);
+    if (p.has_dup) in.dup_bed = read_cnv_bed(p.dup_file);
+    if (p.has_map) in.map_bed = read_mappability_bed(p.mappability_file);
+    tick("BEDs parsed");
+    gpus.wait();
+    for (size_t g = 0; g < ctx.size(); g++)
+        if (!ctx[g]) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
+    tick("CUDA contexts up");
 
     if (n_gpus == 1) {
         /* streaming, like the reference: each chromosome is written as soon as it is genotyped */
@@ -677,7 +703,9 @@ void run(Params& p, Totals& tot)
         }
     }
 
+    tick("chromosomes done");
     for (cg_ctx* c : ctx) cg_destroy(c);
+    tick("contexts destroyed");
     if (hts_close(fp) != 0) die("Error closing BAM file");
     bam_hdr_destroy(hdr);
     hts_idx_destroy(idx);
@@ -706,12 +734,16 @@ int main(int argc, char** argv)
         die("[CONGA-B200] --rp (split-read support) together with --dups is not built yet; run without --rp");
     if (!p.has_sonic) die("[CONGA CMDLINE ERROR] Please enter the SONIC file using the --sonic option.");
 
+    tick("start");
+    Gpus gpus;
+    gpus.start();
     p.this_sonic = sonic_load(const_cast<char*>(p.sonic_file.c_str()));
+    tick("SONIC loaded");
     if (!p.this_sonic) die("Error: cannot load SONIC file %s", p.sonic_file.c_str());
     if (p.last_chrom < p.first_chrom) p.last_chrom = p.this_sonic->number_of_chromosomes - 1;   /* svdepth.c:49-50 */
 
     Totals tot;
-    run(p, tot);
+    run(p, tot, gpus);
 
     char user[256] = "";
     if (getlogin_r(user, sizeof user - 1) != 0) snprintf(user, sizeof user, "you");
