@@ -442,31 +442,6 @@ std::vector<cg_cnv> select_cnvs(const std::map<std::string, std::vector<BedRow>>
     return v;
 }
 
-/* ncclAllReduce(int64, sum) of the statistics tables, one communicator per GPU of this process */
-void allreduce_stats_tables(std::vector<cg_ctx*>& ctx, int first_dev, int n_rows)
-{
-    const int n = (int)ctx.size();
-    std::vector<int> devs(n);
-    for (int g = 0; g < n; g++) devs[g] = first_dev + g;
-    std::vector<ncclComm_t> comms(n);
-    ncclResult_t rc = ncclCommInitAll(comms.data(), n, devs.data());
-    if (rc != ncclSuccess) die("Error: ncclCommInitAll: %s", ncclGetErrorString(rc));
-    std::vector<void*> tables(n);
-    for (int g = 0; g < n; g++) {
-        int32_t rows = 0;
-        if (cg_stats_table(ctx[g], &tables[g], &rows) != CG_OK || cg_join(ctx[g]) != CG_OK) die("Error: %s", cg_last_error(ctx[g]));
-    }
-    ncclGroupStart();
-    for (int g = 0; g < n; g++) {
-        rc = ncclAllReduce(tables[g], tables[g], (size_t)n_rows * 204, ncclInt64, ncclSum, comms[g], (cudaStream_t)cg_stream(ctx[g]));
-        if (rc != ncclSuccess) die("Error: ncclAllReduce: %s", ncclGetErrorString(rc));
-    }
-    rc = ncclGroupEnd();
-    if (rc != ncclSuccess) die("Error: ncclGroupEnd: %s", ncclGetErrorString(rc));
-    for (int g = 0; g < n; g++) if (cg_sync(ctx[g]) != CG_OK) die("Error: cg_sync: %s", cg_last_error(ctx[g]));
-    for (int g = 0; g < n; g++) ncclCommDestroy(comms[g]);
-}
-
 #define CG(ctx, call) do { if ((call) != CG_OK) die("Error: %s: %s", #call, cg_last_error(ctx)); } while (0)
 
 /* everything one chromosome contributes to the outputs */
@@ -483,10 +458,27 @@ struct ChromResult {
 struct Inputs {
     std::map<std::string, std::vector<BedRow>> del_bed, dup_bed;
     std::map<std::string, std::vector<cg_mapiv>> map_bed;
+    /* the painted mappability track of a chromosome as disjoint runs (cg_flatten_mappability), made on first
+     * use and kept: in batch mode every sample reuses it */
+    std::mutex mu;
+    std::map<std::string, std::pair<cg_maprun*, size_t>> runs;
+
+    const std::pair<cg_maprun*, size_t>& runs_of(const std::string& chr, int32_t chrom_len)
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = runs.find(chr);
+        if (it != runs.end()) return it->second;
+        std::pair<cg_maprun*, size_t> r(nullptr, 0);
+        auto rows = map_bed.find(chr);
+        if (rows != map_bed.end() && !rows->second.empty()
+            && cg_flatten_mappability(rows->second.data(), rows->second.size(), chrom_len, &r.first, &r.second) != CG_OK)
+            die("Error: cg_flatten_mappability: %s", cg_last_error(nullptr));
+        return runs.emplace(chr, r).first->second;
+    }
 };
 
 /* The body of the reference's chromosome loop (bam_data.c:304-338) for one chromosome on one context. */
-void process_chromosome(const Params& p, const Inputs& in, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
+void process_chromosome(const Params& p, Inputs& in, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
 {
     sonic* sn = p.this_sonic;
     /* seams 1-3 */
@@ -501,9 +493,9 @@ void process_chromosome(const Params& p, const Inputs& in, cg_ctx* ctx, const Ch
     r.has_cnvs = !(r.dels.empty() && r.dups.empty());
     if (!r.has_cnvs) return;                                        /* likelihood.c:332-336 */
     if (p.has_map) {
-        auto it = in.map_bed.find(r.chr);
-        if (it != in.map_bed.end() && !it->second.empty()) CG(ctx, cg_set_mappability(ctx, it->second.data(), it->second.size()));
-        else CG(ctx, cg_set_mappability_runs(ctx, nullptr, 0, 1));   /* --mappability given, no row here: 0.0 everywhere */
+        /* no run at all (no row on this chromosome, or only zeros): mappability 0.0 for every CNV */
+        const auto& runs = in.runs_of(r.chr, t.length);
+        CG(ctx, cg_set_mappability_runs(ctx, runs.first, runs.second, 1));
     }
     r.dcall.resize(r.dels.size());
     r.ucall.resize(r.dups.size());
@@ -553,11 +545,13 @@ std::vector<int> lpt_assign(const std::vector<ChromTask>& todo, int n_gpus)
     return gpu_of;
 }
 
-/* CUDA contexts brought up on side threads from the moment the command line is known */
+/* CUDA contexts brought up on side threads from the moment the command line is known, and the NCCL
+ * communicators over them (created on first use, kept for the following samples of a batch) */
 struct Gpus {
     int first_dev = 0;
     std::vector<cg_ctx*> ctx;
     std::vector<std::thread> threads;
+    std::vector<ncclComm_t> comms;
     void start()
     {
         first_dev = getenv("CONGA_GPU_DEVICE") ? atoi(getenv("CONGA_GPU_DEVICE")) : 0;
@@ -565,12 +559,116 @@ struct Gpus {
         ctx.assign(n, nullptr);
         for (int g = 0; g < n; g++) threads.emplace_back([this, g] { ctx[g] = cg_create(first_dev + g); });
     }
-    void wait() { for (auto& t : threads) t.join(); threads.clear(); }
+    void wait()
+    {
+        for (auto& t : threads) t.join();
+        threads.clear();
+        for (cg_ctx* c : ctx)
+            if (!c) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
+    }
+    /* ncclAllReduce(int64, sum) of the statistics tables, one communicator per GPU of this process */
+    void allreduce(int n_rows)
+    {
+        const int n = (int)ctx.size();
+        ncclResult_t rc;
+        if (comms.empty()) {
+            std::vector<int> devs(n);
+            for (int g = 0; g < n; g++) devs[g] = first_dev + g;
+            comms.resize(n);
+            if ((rc = ncclCommInitAll(comms.data(), n, devs.data())) != ncclSuccess) die("Error: ncclCommInitAll: %s", ncclGetErrorString(rc));
+        }
+        std::vector<void*> tables(n);
+        for (int g = 0; g < n; g++) {
+            int32_t rows = 0;
+            if (cg_stats_table(ctx[g], &tables[g], &rows) != CG_OK || cg_join(ctx[g]) != CG_OK) die("Error: %s", cg_last_error(ctx[g]));
+        }
+        ncclGroupStart();
+        for (int g = 0; g < n; g++)
+            if ((rc = ncclAllReduce(tables[g], tables[g], (size_t)n_rows * 204, ncclInt64, ncclSum, comms[g], (cudaStream_t)cg_stream(ctx[g]))) != ncclSuccess)
+                die("Error: ncclAllReduce: %s", ncclGetErrorString(rc));
+        if ((rc = ncclGroupEnd()) != ncclSuccess) die("Error: ncclGroupEnd: %s", ncclGetErrorString(rc));
+        for (int g = 0; g < n; g++) if (cg_sync(ctx[g]) != CG_OK) die("Error: cg_sync: %s", cg_last_error(ctx[g]));
+    }
+    void shutdown()
+    {
+        for (ncclComm_t c : comms) ncclCommDestroy(c);
+        comms.clear();
+        for (cg_ctx* c : ctx) cg_destroy(c);
+        ctx.clear();
+    }
 };
 
-/* read_bam, bam_data.c:224-359 */
-void run(Params& p, Totals& tot, Gpus& gpus)
+/* One BAM being worked on: its header and index, the chromosomes to visit, and the threads decoding them. */
+struct Sample {
+    Params p;                             /* the run's parameters with this sample's BAM and output prefix */
+    htsFile* fp = nullptr;
+    bam_hdr_t* hdr = nullptr;
+    hts_idx_t* idx = nullptr;
+    std::string name;
+    std::vector<ChromTask> tasks, todo;
+    std::vector<size_t> todo_of, task_of_todo;
+    std::vector<ChromResult> results;
+    Decoder* dec = nullptr;
+
+    Sample(const Params& p_, int n_gpus) : p(p_)
+    {
+        fp = hts_open(p.bam_file.c_str(), "r");
+        if (!fp) die("Error opening BAM file %s", p.bam_file.c_str());
+        hdr = sam_hdr_read(fp);
+        if (!hdr) die("Error: cannot read the BAM header of %s", p.bam_file.c_str());
+        idx = sam_index_load(fp, p.bam_file.c_str());
+        if (!idx) die("Error: Sam Index cannot be loaded (sam_index_load)");
+        /* get_sample_name, common.c:325-352: first header token that starts with "SM" */
+        std::string text(hdr->text ? hdr->text : "");
+        for (size_t i = 0; i < text.size();) {
+            size_t j = text.find_first_of("\t\n", i);
+            if (j == std::string::npos) j = text.size();
+            if (j - i >= 2 && text[i] == 'S' && text[i + 1] == 'M') { name = j - i > 3 ? text.substr(i + 3, j - i - 3) : ""; break; }
+            i = j + 1;
+        }
+        /* the chromosome loop's selection logic, bam_data.c:269-291 */
+        sonic* sn = p.this_sonic;
+        for (int ci = 0; ci < sn->number_of_chromosomes; ci++) {
+            if (ci < p.first_chrom) ci = p.first_chrom;
+            if (ci > p.last_chrom || ci >= sn->number_of_chromosomes) break;
+            const char* cname = sn->chromosome_names[ci];
+            if (strstr(cname, "X") || strstr(cname, "Y")) continue;
+            int tid = -1;
+            for (int t = 0; t < hdr->n_targets; t++) if (strcmp(cname, hdr->target_name[t]) == 0) { tid = t; break; }
+            ChromTask t;
+            t.chr_index = ci; t.tid = tid; t.length = sn->chromosome_lengths[ci];
+            tasks.push_back(std::move(t));
+        }
+        /* tasks for targets missing from the BAM are never decoded */
+        todo_of.assign(tasks.size(), (size_t)-1);
+        results.resize(tasks.size());
+        for (size_t k = 0; k < tasks.size(); k++) {
+            if (tasks[k].tid < 0) continue;
+            todo_of[k] = todo.size();
+            task_of_todo.push_back(k);
+            todo.push_back(tasks[k]);
+            results[k].in_bam = true;
+            results[k].chr = hdr->target_name[tasks[k].tid];
+            results[k].length = tasks[k].length;
+        }
+        int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
+        if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
+        n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
+        dec = new Decoder(p, todo, idx, n_threads, (size_t)n_threads + 2 * (size_t)n_gpus);
+    }
+    ~Sample()
+    {
+        delete dec;
+        if (fp && hts_close(fp) != 0) die("Error closing BAM file");
+        if (hdr) bam_hdr_destroy(hdr);
+        if (idx) hts_idx_destroy(idx);
+    }
+};
+
+/* read_bam, bam_data.c:224-359, for one sample whose decoding is already under way */
+void run_sample(Sample& sm, Inputs& in, Gpus& gpus, Totals& tot)
 {
+    const Params& p = sm.p;
     const std::string f_svs = p.outdir + p.outprefix + "_svs.bed";
     fprintf(stderr, "\nOutput SV file: %s\n", f_svs.c_str());
     FILE* fp_svs = open_or_die(f_svs, "w");
@@ -589,101 +687,33 @@ void run(Params& p, Totals& tot, Gpus& gpus)
         fprintf(fp_dup, "#CHR\tSTART_SV\tEND_SV\tCOPY_NUMBER\tLIKELIHOOD\tREAD_PAIR\tMAPPABILITY\tOBSERVED_READS\tEXPECTED_READS\n");
     }
 
-    htsFile* fp = hts_open(p.bam_file.c_str(), "r");
-    if (!fp) die("Error opening BAM file %s", p.bam_file.c_str());
-    bam_hdr_t* hdr = sam_hdr_read(fp);
-    if (!hdr) die("Error: cannot read the BAM header of %s", p.bam_file.c_str());
-    hts_idx_t* idx = sam_index_load(fp, p.bam_file.c_str());
-    if (!idx) die("Error: Sam Index cannot be loaded (sam_index_load)");
-
-    /* get_sample_name, common.c:325-352: first header token that starts with "SM" */
-    std::string sample = "";
-    {
-        std::string text(hdr->text ? hdr->text : "");
-        size_t i = 0;
-        while (i < text.size()) {
-            size_t j = text.find_first_of("\t\n", i);
-            if (j == std::string::npos) j = text.size();
-            if (j - i >= 2 && text[i] == 'S' && text[i + 1] == 'M') { sample = j - i > 3 ? text.substr(i + 3, j - i - 3) : ""; break; }
-            i = j + 1;
-        }
-    }
-
     sonic* sn = p.this_sonic;
-    std::vector<ChromTask> tasks;
-    /* the chromosome loop's selection logic, bam_data.c:269-291 */
-    for (int ci = 0; ci < sn->number_of_chromosomes; ci++) {
-        if (ci < p.first_chrom) ci = p.first_chrom;
-        if (ci > p.last_chrom || ci >= sn->number_of_chromosomes) break;
-        const char* name = sn->chromosome_names[ci];
-        if (strstr(name, "X") || strstr(name, "Y")) continue;
-        int tid = -1;
-        for (int t = 0; t < hdr->n_targets; t++) if (strcmp(name, hdr->target_name[t]) == 0) { tid = t; break; }
-        ChromTask t;
-        t.chr_index = ci; t.tid = tid; t.length = sn->chromosome_lengths[ci];
-        tasks.push_back(std::move(t));
-    }
-
-    /* tasks for targets missing from the BAM are never decoded */
-    std::vector<ChromTask> todo;
-    std::vector<size_t> todo_of(tasks.size(), (size_t)-1);
-    std::vector<ChromResult> results(tasks.size());
-    for (size_t k = 0; k < tasks.size(); k++) {
-        if (tasks[k].tid < 0) continue;
-        todo_of[k] = todo.size();
-        todo.push_back(tasks[k]);
-        results[k].in_bam = true;
-        results[k].chr = hdr->target_name[tasks[k].tid];
-        results[k].length = tasks[k].length;
-    }
-    std::vector<size_t> task_of_todo(todo.size());
-    for (size_t k = 0; k < tasks.size(); k++) if (todo_of[k] != (size_t)-1) task_of_todo[todo_of[k]] = k;
-
-    /* GPUs: CONGA_GPUS=N uses devices first..first+N-1 (first = CONGA_GPU_DEVICE, default 0).  Bringing up a
-     * CUDA context takes from a few hundred milliseconds to more than a second; it happens on side threads
-     * while the BEDs are parsed and the first chromosomes are decoded. */
-    const int first_dev = gpus.first_dev;
-    const int n_gpus = (int)std::min<size_t>(gpus.ctx.size(), std::max<size_t>(1, todo.size()));
     std::vector<cg_ctx*>& ctx = gpus.ctx;
-    const std::vector<int> gpu_of = lpt_assign(todo, n_gpus);
-
-    int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
-    if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
-    n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
-    Decoder dec(p, todo, idx, n_threads, (size_t)n_threads + 2 * (size_t)n_gpus);
-    tick("decoders started");
-
-    Inputs in;
-    if (p.has_del) in.del_bed = read_cnv_bed(p.del_file);
-    if (p.has_dup) in.dup_bed = read_cnv_bed(p.dup_file);
-    if (p.has_map) in.map_bed = read_mappability_bed(p.mappability_file);
-    tick("BEDs parsed");
-    gpus.wait();
-    for (size_t g = 0; g < ctx.size(); g++)
-        if (!ctx[g]) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
-    tick("CUDA contexts up");
-
+    const int n_gpus = (int)std::min<size_t>(ctx.size(), std::max<size_t>(1, sm.todo.size()));
+    Decoder& dec = *sm.dec;
     if (n_gpus == 1) {
         /* streaming, like the reference: each chromosome is written as soon as it is genotyped */
-        for (size_t k = 0; k < tasks.size(); k++) {
-            if (results[k].in_bam) {
-                ChromTask& t = dec.wait_for(todo_of[k]);
+        for (size_t k = 0; k < sm.tasks.size(); k++) {
+            if (sm.results[k].in_bam) {
+                ChromTask& t = dec.wait_for(sm.todo_of[k]);
                 if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
-                process_chromosome(p, in, ctx[0], t, results[k]);
-                dec.release(todo_of[k]);
+                process_chromosome(p, in, ctx[0], t, sm.results[k]);
+                dec.release(sm.todo_of[k]);
             }
-            emit_chromosome(p, sample, sn->chromosome_names[tasks[k].chr_index], results[k], fp_svs, fp_del, fp_dup, tot);
+            emit_chromosome(p, sm.name, sn->chromosome_names[sm.tasks[k].chr_index], sm.results[k], fp_svs, fp_del, fp_dup, tot);
         }
     } else {
         /* one host thread per GPU, each walking its own chromosomes in SONIC order */
+        const std::vector<int> gpu_of = lpt_assign(sm.todo, n_gpus);
+        for (int g = 0; g < (int)ctx.size(); g++) CG(ctx[g], cg_stats_reset(ctx[g]));      /* batch mode: the previous sample's rows */
         std::vector<std::thread> workers;
         for (int g = 0; g < n_gpus; g++)
             workers.emplace_back([&, g] {
-                for (size_t j = 0; j < todo.size(); j++) {
+                for (size_t j = 0; j < sm.todo.size(); j++) {
                     if (gpu_of[j] != g) continue;
                     ChromTask& t = dec.wait_for(j);
                     if (t.failed) die("Error: Iterator cannot be loaded (bam_itr_queryi)");
-                    process_chromosome(p, in, ctx[g], t, results[task_of_todo[j]]);
+                    process_chromosome(p, in, ctx[g], t, sm.results[sm.task_of_todo[j]]);
                     dec.release(j);
                 }
             });
@@ -691,39 +721,71 @@ void run(Params& p, Totals& tot, Gpus& gpus)
         /* the path's one collective: every GPU's int64[n_chrom][204] statistics table summed over NVLink, so
          * that the writer of conga.log (GPU 0's host side) holds every chromosome's row; a chromosome's row is
          * zero everywhere but on the GPU that processed it */
-        allreduce_stats_tables(ctx, first_dev, sn->number_of_chromosomes);
-        for (size_t k = 0; k < tasks.size(); k++) {
-            if (results[k].in_bam) {
+        gpus.allreduce(sn->number_of_chromosomes);
+        for (size_t k = 0; k < sm.tasks.size(); k++) {
+            if (sm.results[k].in_bam) {
                 cg_chrom_stats st;
-                CG(ctx[0], cg_stats_row(ctx[0], tasks[k].chr_index, &st));
-                if (memcmp(&st, &results[k].st, sizeof st) != 0) die("Error: statistics row %d differs after the all-reduce", tasks[k].chr_index);
-                results[k].st = st;
+                CG(ctx[0], cg_stats_row(ctx[0], sm.tasks[k].chr_index, &st));
+                if (memcmp(&st, &sm.results[k].st, sizeof st) != 0) die("Error: statistics row %d differs after the all-reduce", sm.tasks[k].chr_index);
+                sm.results[k].st = st;
             }
-            emit_chromosome(p, sample, sn->chromosome_names[tasks[k].chr_index], results[k], fp_svs, fp_del, fp_dup, tot);
+            emit_chromosome(p, sm.name, sn->chromosome_names[sm.tasks[k].chr_index], sm.results[k], fp_svs, fp_del, fp_dup, tot);
         }
     }
-
-    tick("chromosomes done");
-    for (cg_ctx* c : ctx) cg_destroy(c);
-    tick("contexts destroyed");
-    if (hts_close(fp) != 0) die("Error closing BAM file");
-    bam_hdr_destroy(hdr);
-    hts_idx_destroy(idx);
     fprintf(stderr, "\n");
     if (fp_del) fclose(fp_del);
     if (fp_dup) fclose(fp_dup);
     fclose(fp_svs);
 }
 
+/* CONGA_BATCH=<file>: one "BAM <white space> output prefix" per line.  Every sample is genotyped against the
+ * same --dels/--dups/--mappability/--sonic with the same flags and gets its own three BED files plus
+ * <prefix>_conga.log — the files separate runs would write — while the CUDA contexts, the SONIC tables, the
+ * parsed BEDs and the flattened mappability tracks are set up once, and sample k+1 is decoded while k is on
+ * the GPUs (BASELINE.json configs[4]). */
+std::vector<std::pair<std::string, std::string>> read_batch_list(const char* path)
+{
+    std::vector<std::pair<std::string, std::string>> v;
+    FILE* f = open_or_die(path, "r");
+    char line[8192];
+    while (fgets(line, sizeof line, f)) {
+        char* save = nullptr;
+        const char* bam = strtok_r(line, " \t\r\n", &save);
+        const char* out = bam ? strtok_r(nullptr, " \t\r\n", &save) : nullptr;
+        if (!bam || bam[0] == '#') continue;
+        if (!out) die("[CONGA INPUT ERROR] %s: a batch row needs a BAM and an output prefix", path);
+        v.emplace_back(bam, out);
+    }
+    fclose(f);
+    return v;
+}
+
 }  // namespace
 
-int main(int argc, char** argv)
+/* --out dir/pre -> outdir "dir/", outprefix "pre" (get_working_directory, common.c:45-83) */
+void split_outprefix(Params& p, bool chatty)
+{
+    const size_t slash = p.outprefix.rfind('/');
+    if (slash == std::string::npos) { p.outdir = ""; return; }
+    const std::string prefix = p.outprefix.substr(slash + 1);
+    if (chatty) fprintf(stderr, "prefix: %s\n", prefix.c_str());
+    p.outdir = p.outprefix.substr(0, slash) + "/";
+    if (chatty) fprintf(stderr, "prefix2: %s\n", prefix.c_str());
+    p.outprefix = prefix;
+}
+
+void log_header(FILE* f)
 {
     time_t raw;
     time(&raw);
     const struct tm* ti = localtime(&raw);
+    fprintf(f, "#CreationDate=%d.%d.%d\n\n", ti->tm_year + 1900, ti->tm_mon + 1, ti->tm_mday);   /* svdepth.c:31 */
+}
+
+int main(int argc, char** argv)
+{
     g_log = open_or_die("conga.log", "w");                          /* svdepth.c:30: always in the CWD */
-    fprintf(g_log, "#CreationDate=%d.%d.%d\n\n", ti->tm_year + 1900, ti->tm_mon + 1, ti->tm_mday);
+    log_header(g_log);
 
     Params p;
     const int rc = parse_cmd_line(argc, argv, p);
@@ -740,10 +802,58 @@ int main(int argc, char** argv)
     p.this_sonic = sonic_load(const_cast<char*>(p.sonic_file.c_str()));
     tick("SONIC loaded");
     if (!p.this_sonic) die("Error: cannot load SONIC file %s", p.sonic_file.c_str());
+    const int first_as_given = p.first_chrom, last_as_given = p.last_chrom;
     if (p.last_chrom < p.first_chrom) p.last_chrom = p.this_sonic->number_of_chromosomes - 1;   /* svdepth.c:49-50 */
 
+    /* the samples: the command line's one BAM, or the rows of CONGA_BATCH */
+    std::vector<Params> samples;
+    const char* batch = getenv("CONGA_BATCH");
+    if (batch) {
+        for (const auto& row : read_batch_list(batch)) {
+            Params q = p;
+            q.bam_file = row.first;
+            q.outprefix = row.second;
+            split_outprefix(q, false);
+            samples.push_back(q);
+        }
+        if (samples.empty()) die("[CONGA INPUT ERROR] %s lists no sample", batch);
+    } else {
+        samples.push_back(p);
+    }
+
     Totals tot;
-    run(p, tot, gpus);
+    Inputs in;
+    Sample* cur = new Sample(samples[0], (int)gpus.ctx.size());       /* decoding starts here */
+    tick("decoders started");
+    if (p.has_del) in.del_bed = read_cnv_bed(p.del_file);
+    if (p.has_dup) in.dup_bed = read_cnv_bed(p.dup_file);
+    if (p.has_map) in.map_bed = read_mappability_bed(p.mappability_file);
+    tick("BEDs parsed");
+    gpus.wait();
+    tick("CUDA contexts up");
+    FILE* main_log = g_log;
+    for (size_t i = 0; i < samples.size(); i++) {
+        Sample* next = i + 1 < samples.size() ? new Sample(samples[i + 1], (int)gpus.ctx.size()) : nullptr;   /* decoded under sample i */
+        if (batch) {   /* what a separate run would have left in ./conga.log */
+            g_log = open_or_die(cur->p.outdir + cur->p.outprefix + "_conga.log", "w");
+            log_header(g_log);
+            Params shown = cur->p;
+            shown.first_chrom = first_as_given; shown.last_chrom = last_as_given;
+            fprintf(g_log, "%-30s%s\n", "BAM input:", shown.bam_file.c_str());
+            fprintf(g_log, "%-30s%s\n", "Reference genome:", shown.ref_genome.c_str());
+            fprintf(g_log, "%-30s%s\n", "SONIC file:", shown.sonic_file.c_str());
+            fprintf(g_log, "%-30s%d\n", "First chrom:", shown.first_chrom);
+            fprintf(g_log, "%-30s%d\n", "Last chrom:", shown.last_chrom);
+        }
+        run_sample(*cur, in, gpus, tot);
+        if (batch) { fclose(g_log); g_log = main_log; fprintf(g_log, "sample %zu: %s -> %s%s\n", i, cur->p.bam_file.c_str(), cur->p.outdir.c_str(), cur->p.outprefix.c_str()); }
+        delete cur;
+        cur = next;
+        tick("sample done");
+    }
+    gpus.shutdown();
+    tick("contexts destroyed");
+    for (auto& kv : in.runs) cg_free_runs(kv.second.first);
 
     char user[256] = "";
     if (getlogin_r(user, sizeof user - 1) != 0) snprintf(user, sizeof user, "you");

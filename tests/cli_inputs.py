@@ -97,3 +97,22 @@ def build_inputs(tmp, chroms, rng, reads_per_mb=20000, with_map=False, bam_chrom
         with open(paths["map"], "w") as f:
             f.writelines(map_rows)
     return paths
+
+
+def extra_bam(tmp, chroms, rng, tag, reads_per_mb=20000):
+    """Another sample over the same chromosomes: reads only (uniform starts, random mapq), BAM + index."""
+    tsv = []
+    for k, (name, L) in enumerate(chroms):
+        n = int(L / 1e6 * reads_per_mb)
+        r = np.zeros(n, dtype=READ_DT)
+        r["pos"] = np.sort(rng.integers(0, L - 100, size=n)).astype(np.int32)
+        r["len"] = rng.integers(30, 101, size=n)
+        r["mapq"] = rng.choice(np.array([0, 10, 20, 21, 30, 37, 60], dtype=np.uint8), size=n)
+        path = os.path.join(tmp, "reads_%s.%d.bin" % (tag, k))
+        r.tofile(path)
+        tsv.append("%s\t%d\t%s\n" % (name, L, path))
+    with open(os.path.join(tmp, "chroms_%s.tsv" % tag), "w") as f:
+        f.writelines(tsv)
+    bam = os.path.join(tmp, "in_%s.bam" % tag)
+    subprocess.run([os.path.join(REF, "mkbam"), bam, os.path.join(tmp, "chroms_%s.tsv" % tag)], check=True, stdout=subprocess.DEVNULL)
+    return bam

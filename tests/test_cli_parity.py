@@ -119,6 +119,46 @@ def test_two_gpus_write_the_same_bytes(tools):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+def test_batch_of_samples_equals_separate_runs(tools):
+    """CONGA_BATCH: three BAMs against one CNV set / mappability track in ONE process (contexts, SONIC, BEDs and
+    flattened tracks set up once, sample k+1 decoded under sample k) — each sample's files must be the bytes a
+    separate run of the reference writes for it."""
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(106)
+        chroms = [("1", 300_000), ("2", 200_000), ("3", 120_000)]
+        paths = cli_inputs.build_inputs(tmp, chroms, rng, with_map=True)
+        bams = [paths["bam"], cli_inputs.extra_bam(tmp, chroms, rng, "b", 30000), cli_inputs.extra_bam(tmp, chroms, rng, "c", 8000)]
+        flags = ["--dels", paths["dels"], "--dups", paths["dups"], "--mappability", paths["map"], "--min-mapq", "10"]
+        want = []
+        for i, bam in enumerate(bams):
+            wd = os.path.join(tmp, "ref%d" % i)
+            os.makedirs(os.path.join(wd, "o"))
+            p = subprocess.run([REF_CONGA, "-i", bam, "--ref", paths["ref"], "--sonic", paths["sonic"], "--out", os.path.join(wd, "o", "s")] + flags,
+                               cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+            assert p.returncode == 0
+            files = {nm: open(os.path.join(wd, "o", "s_" + nm), "rb").read() for nm in ("svs.bed", "dels.bed", "dups.bed")}
+            files["log"] = [l for l in open(os.path.join(wd, "conga.log"), "rb").read().split(b"\n") if l.startswith(b"Read Count")]
+            want.append(files)
+        wd = os.path.join(tmp, "batch")
+        os.makedirs(wd)
+        with open(os.path.join(wd, "batch.tsv"), "w") as f:
+            for i, bam in enumerate(bams):
+                f.write("%s\t%s\n" % (bam, os.path.join(wd, "s%d" % i)))
+        p = subprocess.run([HOST, "-i", bams[0], "--ref", paths["ref"], "--sonic", paths["sonic"], "--out", os.path.join(wd, "unused")] + flags,
+                           cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600,
+                           env=dict(os.environ, CONGA_BATCH=os.path.join(wd, "batch.tsv")))
+        assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+        for i in range(3):
+            for nm in ("svs.bed", "dels.bed", "dups.bed"):
+                assert open(os.path.join(wd, "s%d_%s" % (i, nm)), "rb").read() == want[i][nm], "sample %d %s" % (i, nm)
+            log = [l for l in open(os.path.join(wd, "s%d_conga.log" % i), "rb").read().split(b"\n") if l.startswith(b"Read Count")]
+            assert log == want[i]["log"]
+        assert want[0]["dels.bed"] != want[1]["dels.bed"]
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def test_rp_is_refused_not_ignored(tools):
     tmp = tempfile.mkdtemp(prefix="cli_")
     try:
@@ -127,3 +167,18 @@ def test_rp_is_refused_not_ignored(tools):
         assert p.returncode == 1 and b"--rp" in p.stderr
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
+
+
+@pytest.mark.parametrize("workload", ["c1", "c2"])
+def test_baseline_configs_at_full_size_whole_program(tools, workload):
+    """BASELINE.json configs[0] and configs[1] at their full sizes (C2: 22 GRCh37-length chromosomes, 4.8 M reads,
+    10 k deletions + 5 k duplications, mappability BED): every byte of the three BED files and every conga.log
+    chromosome line equals what the unmodified reference program writes from the same BAM."""
+    import json
+    import sys
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "cli_bench.py"), "--workload", workload, "--runs", "1"],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=900)
+    assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
+    res = json.loads(p.stdout.decode().strip().splitlines()[-1])
+    assert res["identical_outputs"] is True
+    assert res["rows"]["s_dels.bed"] > 100 and res["rows"]["s_svs.bed"] > 10
