@@ -7,8 +7,10 @@
  * it contains no reference code.
  *
  * usage: mkbam OUT.bam CHROMS.tsv
- *   CHROMS.tsv: one line per @SQ in BAM header order:  name <TAB> length <TAB> records.bin|-
+ *   CHROMS.tsv: one line per @SQ in BAM header order:  name <TAB> length <TAB> records.bin|- [<TAB> seq.bin]
  *   records.bin holds cg_read records (include/conga_gpu.h) sorted by pos.
+ *   seq.bin (optional, for the --rp split-read path): per record, in order, `len` ASCII bases (ACGTN)
+ *   followed by `len` raw phred bytes; without it SEQ is all N and QUAL absent.
  * Each record becomes one single-end alignment: QNAME r<n>, FLAG from cg_read.fl
  * (bit0 secondary 0x100, bit1 qc-fail 0x200, bit2 duplicate 0x400, bit3
  * supplementary 0x800, bit4 unmapped 0x4, bit5 reverse 0x10), POS, MAPQ, CIGAR
@@ -32,7 +34,7 @@ static void die(const char* m, const char* a) { fprintf(stderr, "mkbam: %s %s\n"
 int main(int argc, char** argv)
 {
     if (argc != 3) die("usage: mkbam OUT.bam CHROMS.tsv", NULL);
-    static char names[MAXCHR][256], paths[MAXCHR][2048];
+    static char names[MAXCHR][256], paths[MAXCHR][2048], seqs[MAXCHR][2048];
     static long lens[MAXCHR];
     int n_chr = 0;
     FILE* f = fopen(argv[2], "r");
@@ -41,7 +43,8 @@ int main(int argc, char** argv)
     while (fgets(line, sizeof line, f)) {
         if (line[0] == '\n' || line[0] == '#') continue;
         if (n_chr >= MAXCHR) die("too many chromosomes", NULL);
-        if (sscanf(line, "%255s %ld %2047s", names[n_chr], &lens[n_chr], paths[n_chr]) != 3) die("bad line", line);
+        seqs[n_chr][0] = 0;
+        if (sscanf(line, "%255s %ld %2047s %2047s", names[n_chr], &lens[n_chr], paths[n_chr], seqs[n_chr]) < 3) die("bad line", line);
         n_chr++;
     }
     fclose(f);
@@ -64,6 +67,9 @@ int main(int argc, char** argv)
         if (!strcmp(paths[tid], "-")) continue;
         FILE* r = fopen(paths[tid], "rb");
         if (!r) die("cannot open", paths[tid]);
+        FILE* sq = seqs[tid][0] ? fopen(seqs[tid], "rb") : NULL;
+        if (seqs[tid][0] && !sq) die("cannot open", seqs[tid]);
+        static unsigned char bases[65536], quals[65536];
         cg_read q; int32_t last = -1;
         while (fread(&q, sizeof q, 1, r) == 1) {
             if (q.pos < last) die("records not sorted in", paths[tid]);
@@ -83,8 +89,19 @@ int main(int argc, char** argv)
             memcpy(p, qname, lq); p += lq;
             memset(p, 0, extranul); p += extranul;
             if (n_cigar) { uint32_t c = ((uint32_t)l_qseq << BAM_CIGAR_SHIFT) | BAM_CMATCH; memcpy(p, &c, 4); p += 4; }
-            memset(p, 0xff, (l_qseq + 1) / 2); p += (l_qseq + 1) / 2;      /* 'N' = nibble 15 */
-            memset(p, 0xff, l_qseq); p += l_qseq;                          /* QUAL absent */
+            if (sq) {
+                if (fread(bases, 1, l_qseq, sq) != (size_t)l_qseq || fread(quals, 1, l_qseq, sq) != (size_t)l_qseq) die("short read from", seqs[tid]);
+                memset(p, 0, (l_qseq + 1) / 2);
+                for (int i = 0; i < l_qseq; i++) {
+                    int c = bases[i] == 'A' ? 1 : bases[i] == 'C' ? 2 : bases[i] == 'G' ? 4 : bases[i] == 'T' ? 8 : 15;
+                    p[i >> 1] |= (uint8_t)(c << ((~i & 1) << 2));
+                }
+                p += (l_qseq + 1) / 2;
+                memcpy(p, quals, l_qseq); p += l_qseq;
+            } else {
+                memset(p, 0xff, (l_qseq + 1) / 2); p += (l_qseq + 1) / 2;  /* 'N' = nibble 15 */
+                memset(p, 0xff, l_qseq); p += l_qseq;                      /* QUAL absent */
+            }
             b->l_data = (int)(p - b->data);
             uint16_t flag = 0;
             if (q.fl & 1)  flag |= BAM_FSECONDARY;
@@ -102,6 +119,7 @@ int main(int argc, char** argv)
             if (sam_write1(out, h, b) < 0) die("sam_write1 failed", NULL);
         }
         fclose(r);
+        if (sq) fclose(sq);
     }
     bam_destroy1(b);
     if (sam_close(out) < 0) die("sam_close failed", NULL);

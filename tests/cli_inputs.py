@@ -116,3 +116,104 @@ def extra_bam(tmp, chroms, rng, tag, reads_per_mb=20000):
     bam = os.path.join(tmp, "in_%s.bam" % tag)
     subprocess.run([os.path.join(REF, "mkbam"), bam, os.path.join(tmp, "chroms_%s.tsv" % tag)], check=True, stdout=subprocess.DEVNULL)
     return bam
+
+
+def read_fasta_upper(path):
+    """{name: uppercase bases as a uint8 array} of a FASTA written by write_fasta."""
+    out, name, chunks = {}, None, []
+    for line in open(path, "rb"):
+        if line.startswith(b">"):
+            if name is not None:
+                out[name] = np.frombuffer(b"".join(chunks).upper(), dtype=np.uint8)
+            name, chunks = line[1:].strip().decode(), []
+        else:
+            chunks.append(line.strip())
+    if name is not None:
+        out[name] = np.frombuffer(b"".join(chunks).upper(), dtype=np.uint8)
+    return out
+
+
+def build_inputs_rp(tmp, chroms, rng, reads_per_mb=15000, n_dels=12, n_dups=10, junction_reads=25, with_map=False,
+                    satellites=True):
+    """Inputs for the split-read path (--rp with --dups): reads carry real bases copied from the reference
+    (0.5 % substitutions) and phred bytes; every CNV gets `junction_reads` chimeric reads whose two halves
+    sit on either side of its breakpoints, so READ_PAIR columns are non-zero.
+    RepeatMasker rows of class Satellite gate some reads out (bam_data.c:207)."""
+    fa = os.path.join(tmp, "ref.fa")
+    write_fasta(fa, chroms, rng)
+    seqs = read_fasta_upper(fa)
+    for nm in ("gaps.bed", "dups_sonic.bed"):
+        open(os.path.join(tmp, nm), "w").close()
+    with open(os.path.join(tmp, "rm.out"), "w") as f:
+        f.write("   SW   perc perc perc  query     position in query    matching  repeat       position in repeat\n"
+                "score   div. del. ins.  sequence  begin end   (left)   repeat    class/family begin end (left) ID\n\n")
+        rid = 1
+        for name, L in chroms:
+            if not satellites:
+                break
+            for s in sorted(rng.integers(1000, L - 3000, size=4).tolist()):
+                cls = "Satellite/centr" if rid % 2 else "LINE/L1"
+                f.write("  900  10.0  0.5  0.5  %s  %d  %d  (%d)  +  REP%d  %s  1  %d  (0)  %d\n" % (name, s, s + 1500, L - s - 1500, rid, cls, 1500, rid))
+                rid += 1
+    sonic = os.path.join(tmp, "ref.sonic")
+    subprocess.run([os.path.join(REF, "sonic"), "--ref", fa, "--gaps", os.path.join(tmp, "gaps.bed"), "--dups",
+                    os.path.join(tmp, "dups_sonic.bed"), "--reps", os.path.join(tmp, "rm.out"), "--make-sonic", sonic],
+                   check=True, cwd=tmp, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    sub = np.frombuffer(b"ACGT", dtype=np.uint8)
+    tsv, del_rows, dup_rows, map_rows = [], [], [], []
+    for k, (name, L) in enumerate(chroms):
+        ref = seqs[name]
+        assert len(ref) == L
+        n = int(L / 1e6 * reads_per_mb)
+        pos = rng.integers(1, L - 200, size=n)
+        ln = rng.integers(50, 101, size=n)                       # some at or below --min-read-length 60: not split
+        recs = [(int(p), ref[p:p + l].copy()) for p, l in zip(pos, ln)]
+        cn = {}
+        for key, rows, cnt in (("del", del_rows, n_dels), ("dup", dup_rows, n_dups)):
+            size = np.exp(rng.uniform(np.log(1200), np.log(min(60000, L // 6)), size=cnt)).astype(np.int64)
+            st = rng.integers(2000, L - size - 2000)
+            c = np.unique(np.array(list(zip(st, st + size)), dtype=CNV_DT))
+            cn[key] = c
+            rows += ["%s\t%d\t%d\n" % (name, a, b) for a, b in zip(c["start"], c["end"])]
+        for a, b in zip(cn["del"]["start"], cn["del"]["end"]):   # junction exactly at len/2, a few bases of slack in some
+            for _ in range(junction_reads):
+                l = int(rng.integers(62, 101)); h = l // 2; j = int(rng.integers(-3, 4))
+                recs.append((int(a - h + j), np.concatenate([ref[a - h + j:a + j], ref[b + j:b + j + (l - h)]])))
+        for a, b in zip(cn["dup"]["start"], cn["dup"]["end"]):
+            for _ in range(junction_reads):
+                l = int(rng.integers(62, 101)); h = l // 2; j = int(rng.integers(-3, 4))
+                recs.append((int(b - h + j), np.concatenate([ref[b - h + j:b + j], ref[a + j:a + j + (l - h)]])))
+        recs.sort(key=lambda t: t[0])
+        r = np.zeros(len(recs), dtype=READ_DT)
+        r["pos"] = [t[0] for t in recs]
+        r["len"] = [len(t[1]) for t in recs]
+        r["mapq"] = rng.choice(np.array([0, 10, 21, 30, 37, 60], dtype=np.uint8), size=len(recs), p=[.05, .05, .1, .2, .3, .3])
+        r["fl"] = np.where(rng.random(len(recs)) < 0.04, 4, 0) | np.where(rng.random(len(recs)) < 0.02, 1, 0)
+        path, spath = os.path.join(tmp, "reads.%d.bin" % k), os.path.join(tmp, "seq.%d.bin" % k)
+        r.tofile(path)
+        with open(spath, "wb") as f:
+            for _p, b in recs:
+                b = b.copy()
+                m = rng.random(len(b)) < 0.005
+                b[m] = rng.choice(sub, size=int(m.sum()))
+                q = rng.integers(2, 41, size=len(b)).astype(np.uint8)
+                if rng.random() < 0.1:
+                    q[:] = rng.integers(2, 25)                    # low-quality reads: the average-phred test bites
+                f.write(b.tobytes() + q.tobytes())
+        tsv.append("%s\t%d\t%s\t%s\n" % (name, L, path, spath))
+        if with_map:
+            bnd = np.concatenate([[0], np.cumsum(rng.integers(1, 3000, size=L // 1000))])
+            bnd = bnd[bnd < L - 1]
+            v = rng.choice(MAP_VALUES, size=len(bnd) - 1, p=[.6, .1, .05, .05, .04, .03, .03, .02, .03, .03, .02])
+            map_rows += ["%s\t%d\t%d\t%.9g\n" % (name, s, e, float(x)) for s, e, x in zip(bnd[:-1], bnd[1:], v)]
+    with open(os.path.join(tmp, "chroms.tsv"), "w") as f:
+        f.writelines(tsv)
+    bam = os.path.join(tmp, "in.bam")
+    subprocess.run([os.path.join(REF, "mkbam"), bam, os.path.join(tmp, "chroms.tsv")], check=True, stdout=subprocess.DEVNULL)
+    paths = {"ref": fa, "sonic": sonic, "bam": bam, "dels": os.path.join(tmp, "dels.bed"), "dups": os.path.join(tmp, "dups.bed")}
+    open(paths["dels"], "w").writelines(del_rows)
+    open(paths["dups"], "w").writelines(dup_rows)
+    if with_map:
+        paths["map"] = os.path.join(tmp, "map.bed")
+        open(paths["map"], "w").writelines(map_rows)
+    return paths
