@@ -32,6 +32,10 @@ CALL_DT = np.dtype([("observed", "<i4"), ("expected", "<f4"), ("mappability", "<
                     ("copy_number", "<i4"), ("margin_flags", "<u4")])
 STATS_DT = np.dtype([("rd_per_gc", "<i8", (CG_GC_BINS,)), ("window_per_gc", "<i8", (CG_GC_BINS,)),
                      ("rd_cnt", "<i8"), ("reads_passed", "<i8")])
+HALF_DT = np.dtype([("pos", "<i4"), ("seq_off", "<u4"), ("len", "<u2"), ("read_len", "<u2"), ("mapq", "u1"), ("is_read2", "u1"), ("pad", "<u2")])
+SPLITROW_DT = np.dtype([("pos", "<i4"), ("pos_map", "<i4"), ("left_start", "<i4"), ("left_end", "<i4"), ("right_start", "<i4"),
+                        ("right_end", "<i4"), ("sv_type", "u1"), ("pad", "u1", (7,))])
+assert HALF_DT.itemsize == 16 and SPLITROW_DT.itemsize == 32
 assert READ_DT.itemsize == 8 and CNV_DT.itemsize == 8 and MAPIV_DT.itemsize == 16
 assert MAPRUN_DT.itemsize == 16 and CALL_DT.itemsize == 56 and STATS_DT.itemsize == 204 * 8
 
@@ -57,6 +61,10 @@ SYMBOLS = {
     "cg_free_runs": (None, [_P]),
     "cg_set_mappability_runs": (_I, [_P, _P, _Z, _I]),
     "cg_genotype": (_I, [_P, _P, _Z, _I, _P]),
+    "cg_sr_reference": (_I, [_P, _P, C.c_int32]),
+    "cg_sr_push": (_I, [_P, _P, _Z, _P, _Z]),
+    "cg_sr_rows": (_I, [_P, _P, _Z, C.POINTER(_Z), C.POINTER(C.c_uint64)]),
+    "cg_sr_count": (_I, [_P, _P, _Z, _P, _Z, _P, _Z, _P, _P]),
     "cg_sync": (_I, [_P]),
     "cg_download_depth": (_I, [_P, _P]),
     "cg_download_prefix": (_I, [_P, _P]),

@@ -80,6 +80,16 @@ cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
                          const int32_t* prefix, const int8_t* gc, const float* expected,
                          const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
                          int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms);
+/* split_read.cu */
+size_t      cgk_sr_sort_temp_bytes(int n);
+cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, unsigned* keys_a, unsigned* keys_b, int* vals_a, int* vals_b,
+                         void* temp, size_t temp_bytes, int* lo, int* hi, int n_sms);
+cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len, const int* pos_sorted, const int* lo, const int* hi,
+                          const cg_half* halves, long long n_halves, const unsigned char* bases, int chrom_len, int mq_threshold,
+                          cg_splitrow* rows, unsigned* n_rows, unsigned cap, unsigned long long* n_mappings, int n_sms);
+cudaError_t cgk_sr_count(cudaStream_t s, const cg_splitrow* rows, int n_rows, const cg_cnv* dels, int n_del, const cg_cnv* dups, int n_dup,
+                         int* border_rp, int* rp, int n_sms);
+cudaError_t cgk_configure_split(void);
 int         cgk_run_index_words(int32_t chrom_len);
 cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len);
 }

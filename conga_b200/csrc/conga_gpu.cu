@@ -98,6 +98,22 @@ struct cg_ctx {
     cg_chrom_stats* h_stats = nullptr;
     unsigned int* h_flags = nullptr;
 
+    /* split reads (--rp): one chromosome at a time on its own stream */
+    struct {
+        cudaStream_t st = nullptr;
+        unsigned char* d_ref = nullptr; size_t ref_cap = 0; int ref_len = 0;
+        unsigned *d_keys_a = nullptr, *d_keys_b = nullptr; int *d_vals_a = nullptr, *d_vals_b = nullptr; size_t idx_cap = 0;
+        void* d_temp = nullptr; size_t temp_cap = 0;
+        int *d_lo = nullptr, *d_hi = nullptr;
+        cg_half* d_halves = nullptr; size_t halves_cap = 0;
+        unsigned char* d_bases = nullptr; size_t bases_cap = 0;
+        cg_splitrow* d_rows = nullptr; unsigned rows_cap = 0;
+        unsigned* d_n_rows = nullptr; unsigned long long* d_n_map = nullptr;     /* one 16-byte block */
+        char* d_count = nullptr; size_t count_cap = 0;
+        bool have_ref = false;
+        int chrom_len = 0, mq_threshold = -1;
+    } sr;
+
     /* profiling */
     bool profiling = false;
     std::vector<cg_evpair> ev_live, ev_free;
@@ -129,6 +145,7 @@ static int sync_all(cg_ctx* c)
     CU(c, cudaStreamSynchronize(c->s_copy));
     CU(c, cudaStreamSynchronize(c->s_main));
     CU(c, cudaStreamSynchronize(c->s_bank));
+    if (c->sr.st) CU(c, cudaStreamSynchronize(c->sr.st));
     for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_slot[i]));
     for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(c->slot[i].s_geno[t]));
     return CG_OK;
@@ -190,6 +207,21 @@ static int report_sticky(cg_ctx* c, const char* what)
     return CG_OK;
 }
 
+#define SR_ROWS_CAP (8u << 20)
+
+template <typename T>
+static int sr_grow(cg_ctx* c, T** p, size_t* cap, size_t need)
+{
+    if (need <= *cap) return CG_OK;
+    CU(c, cudaStreamSynchronize(c->sr.st));
+    if (*p) cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    const size_t ncap = need + need / 4 + 1024;
+    CU(c, cudaMalloc(p, ncap * sizeof(T)));
+    *cap = ncap;
+    return CG_OK;
+}
+
 extern "C" {
 
 int cg_abi_version(void) { return CG_ABI_VERSION; }
@@ -209,7 +241,8 @@ cg_ctx* cg_create(int device)
         fail(nullptr, CG_ECUDA, "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
         return nullptr;
     }
-    if ((e = cgk_configure_depth()) != cudaSuccess || (e = cgk_configure_genotype()) != cudaSuccess) {
+    if ((e = cgk_configure_depth()) != cudaSuccess || (e = cgk_configure_genotype()) != cudaSuccess
+        || (e = cgk_configure_split()) != cudaSuccess) {
         fail(nullptr, CG_ECUDA, "kernel configuration failed (no sm_100a image for this device?): %s", cudaGetErrorString(e));
         return nullptr;
     }
@@ -279,6 +312,10 @@ void cg_destroy(cg_ctx* c)
         if (s.ev_runs) cudaEventDestroy(s.ev_runs);
     }
     cudaFree(c->d_stats); cudaFree(c->d_sticky);
+    if (c->sr.st) { cudaStreamSynchronize(c->sr.st); cudaStreamDestroy(c->sr.st); }
+    cudaFree(c->sr.d_ref); cudaFree(c->sr.d_keys_a); cudaFree(c->sr.d_keys_b); cudaFree(c->sr.d_vals_a); cudaFree(c->sr.d_vals_b);
+    cudaFree(c->sr.d_temp); cudaFree(c->sr.d_lo); cudaFree(c->sr.d_hi); cudaFree(c->sr.d_halves); cudaFree(c->sr.d_bases);
+    cudaFree(c->sr.d_rows); cudaFree(c->sr.d_n_rows); cudaFree(c->sr.d_count);
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
@@ -761,6 +798,134 @@ int cg_stats_row(cg_ctx* c, int chr_index, cg_chrom_stats* out)
                           cudaMemcpyDeviceToHost, c->s_main));
     CU(c, cudaStreamSynchronize(c->s_main));
     memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
+    return CG_OK;
+}
+
+/* ---- split reads (--rp) ----------------------------------------------------------------- */
+int cg_sr_reference(cg_ctx* c, const char* ref_seq, int32_t ref_len)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (!c->in_chrom) return fail(c, CG_EINVAL, "cg_sr_reference outside a chromosome");
+    if (!ref_seq || ref_len < 0) return fail(c, CG_EINVAL, "bad reference sequence");
+    CU(c, cudaSetDevice(c->device));
+    auto& r = c->sr;
+    if (!r.st) {
+        CU(c, cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+        CU(c, cudaMalloc(&r.d_lo, sizeof(int) << 20));
+        CU(c, cudaMalloc(&r.d_hi, sizeof(int) << 20));
+        CU(c, cudaMalloc(&r.d_n_rows, 16));
+        r.d_n_map = reinterpret_cast<unsigned long long*>(r.d_n_rows + 2);
+        CU(c, cudaMalloc(&r.d_rows, sizeof(cg_splitrow) * (size_t)SR_ROWS_CAP));
+        r.rows_cap = SR_ROWS_CAP;
+    }
+    int rc;
+    if ((rc = sr_grow(c, &r.d_ref, &r.ref_cap, (size_t)ref_len + 1))) return rc;
+    if ((size_t)ref_len > r.idx_cap) {
+        CU(c, cudaStreamSynchronize(r.st));
+        cudaFree(r.d_keys_a); cudaFree(r.d_keys_b); cudaFree(r.d_vals_a); cudaFree(r.d_vals_b);
+        r.d_keys_a = r.d_keys_b = nullptr; r.d_vals_a = r.d_vals_b = nullptr; r.idx_cap = 0;
+        const size_t n = (size_t)ref_len + 1024;
+        CU(c, cudaMalloc(&r.d_keys_a, n * 4)); CU(c, cudaMalloc(&r.d_keys_b, n * 4));
+        CU(c, cudaMalloc(&r.d_vals_a, n * 4)); CU(c, cudaMalloc(&r.d_vals_b, n * 4));
+        r.idx_cap = n;
+    }
+    const size_t temp = cgk_sr_sort_temp_bytes(ref_len > 0 ? ref_len : 1);
+    if (temp > r.temp_cap) {
+        CU(c, cudaStreamSynchronize(r.st));
+        cudaFree(r.d_temp); r.d_temp = nullptr; r.temp_cap = 0;
+        CU(c, cudaMalloc(&r.d_temp, temp + 1024));
+        r.temp_cap = temp + 1024;
+    }
+    CU(c, cudaMemcpyAsync(r.d_ref, ref_seq, (size_t)ref_len, cudaMemcpyHostToDevice, r.st));
+    CU(c, cudaMemsetAsync(r.d_ref + ref_len, 0, 1, r.st));
+    CU(c, cudaMemsetAsync(r.d_n_rows, 0, 16, r.st));
+    {
+        prof_scope ps(c, r.st, 3, 2);
+        CU(c, cgk_sr_index(r.st, r.d_ref, ref_len, r.d_keys_a, r.d_keys_b, r.d_vals_a, r.d_vals_b, r.d_temp, r.temp_cap, r.d_lo, r.d_hi, c->n_sms));
+    }
+    CU(c, cudaStreamSynchronize(r.st));            /* ref_seq may be pageable and may die at return */
+    r.ref_len = ref_len;
+    r.have_ref = true;
+    r.chrom_len = c->slot[c->cur].chrom_len;
+    r.mq_threshold = c->mq_threshold;
+    return CG_OK;
+}
+
+int cg_sr_push(cg_ctx* c, const cg_half* halves, size_t n, const char* bases, size_t n_bases)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (!c->sr.have_ref) return fail(c, CG_EINVAL, "cg_sr_push before cg_sr_reference");
+    if (n == 0) return CG_OK;
+    if (!halves || !bases) return fail(c, CG_EINVAL, "null argument");
+    if (n_bases > 0xffffffffull) return fail(c, CG_EINVAL, "more than 2^32 bases in one cg_sr_push");
+    CU(c, cudaSetDevice(c->device));
+    auto& r = c->sr;
+    int rc;
+    if ((rc = sr_grow(c, &r.d_halves, &r.halves_cap, n))) return rc;
+    if ((rc = sr_grow(c, &r.d_bases, &r.bases_cap, n_bases + 1))) return rc;
+    CU(c, cudaMemcpyAsync(r.d_halves, halves, n * sizeof(cg_half), cudaMemcpyHostToDevice, r.st));
+    CU(c, cudaMemcpyAsync(r.d_bases, bases, n_bases, cudaMemcpyHostToDevice, r.st));
+    {
+        prof_scope ps(c, r.st, 3, 1);
+        CU(c, cgk_sr_search(r.st, r.d_ref, r.ref_len, r.d_vals_b, r.d_lo, r.d_hi, r.d_halves, (long long)n, r.d_bases, r.chrom_len,
+                            r.mq_threshold, r.d_rows, r.d_n_rows, r.rows_cap, r.d_n_map, c->n_sms));
+    }
+    CU(c, cudaStreamSynchronize(r.st));            /* the staging buffers are reused by the next batch */
+    return CG_OK;
+}
+
+int cg_sr_rows(cg_ctx* c, cg_splitrow* out, size_t cap, size_t* n_rows, uint64_t* n_mappings)
+{
+    if (!c || !n_rows) return fail(c, CG_EINVAL, "null argument");
+    if (!c->sr.have_ref) return fail(c, CG_EINVAL, "cg_sr_rows before cg_sr_reference");
+    CU(c, cudaSetDevice(c->device));
+    auto& r = c->sr;
+    unsigned long long head[2] = {0, 0};
+    CU(c, cudaMemcpyAsync(head, r.d_n_rows, 16, cudaMemcpyDeviceToHost, r.st));
+    CU(c, cudaStreamSynchronize(r.st));
+    const unsigned n = (unsigned)(head[0] & 0xffffffffull);
+    if (n > r.rows_cap) return fail(c, CG_ENOMEM, "%u split-read rows exceed the device buffer (%u)", n, r.rows_cap);
+    *n_rows = n;
+    if (n_mappings) *n_mappings = head[1];
+    const size_t take = n < cap ? n : cap;
+    if (take && !out) return fail(c, CG_EINVAL, "null rows buffer");
+    if (take) {
+        CU(c, cudaMemcpyAsync(out, r.d_rows, take * sizeof(cg_splitrow), cudaMemcpyDeviceToHost, r.st));
+        CU(c, cudaStreamSynchronize(r.st));
+    }
+    return CG_OK;
+}
+
+int cg_sr_count(cg_ctx* c, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
+                const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if ((n && !rows) || (n_del && (!dels || !border_rp)) || (n_dup && (!dups || !rp))) return fail(c, CG_EINVAL, "null argument");
+    if (n > 0x7fffffffull || n_del > 0x3fffffffull || n_dup > 0x3fffffffull) return fail(c, CG_EINVAL, "too many rows or CNVs");
+    CU(c, cudaSetDevice(c->device));
+    auto& r = c->sr;
+    if (!r.st) CU(c, cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+    const size_t b_rows = (n * sizeof(cg_splitrow) + 255) & ~(size_t)255, b_del = (n_del * sizeof(cg_cnv) + 255) & ~(size_t)255,
+                 b_dup = (n_dup * sizeof(cg_cnv) + 255) & ~(size_t)255, b_cd = (n_del * 4 + 255) & ~(size_t)255, b_cu = (n_dup * 4 + 255) & ~(size_t)255;
+    int rc;
+    if ((rc = sr_grow(c, &r.d_count, &r.count_cap, b_rows + b_del + b_dup + b_cd + b_cu + 256))) return rc;
+    char* p = r.d_count;
+    cg_splitrow* d_rows = reinterpret_cast<cg_splitrow*>(p); p += b_rows;
+    cg_cnv* d_del = reinterpret_cast<cg_cnv*>(p); p += b_del;
+    cg_cnv* d_dup = reinterpret_cast<cg_cnv*>(p); p += b_dup;
+    int* d_cd = reinterpret_cast<int*>(p); p += b_cd;
+    int* d_cu = reinterpret_cast<int*>(p);
+    if (n) CU(c, cudaMemcpyAsync(d_rows, rows, n * sizeof(cg_splitrow), cudaMemcpyHostToDevice, r.st));
+    if (n_del) CU(c, cudaMemcpyAsync(d_del, dels, n_del * sizeof(cg_cnv), cudaMemcpyHostToDevice, r.st));
+    if (n_dup) CU(c, cudaMemcpyAsync(d_dup, dups, n_dup * sizeof(cg_cnv), cudaMemcpyHostToDevice, r.st));
+    CU(c, cudaMemsetAsync(d_cd, 0, b_cd + b_cu, r.st));
+    {
+        prof_scope ps(c, r.st, 3, 1);
+        CU(c, cgk_sr_count(r.st, d_rows, (int)n, d_del, (int)n_del, d_dup, (int)n_dup, d_cd, d_cu, c->n_sms));
+    }
+    if (n_del) CU(c, cudaMemcpyAsync(border_rp, d_cd, n_del * 4, cudaMemcpyDeviceToHost, r.st));
+    if (n_dup) CU(c, cudaMemcpyAsync(rp, d_cu, n_dup * 4, cudaMemcpyDeviceToHost, r.st));
+    CU(c, cudaStreamSynchronize(r.st));
     return CG_OK;
 }
 

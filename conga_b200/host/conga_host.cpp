@@ -26,8 +26,9 @@
  *     and do not depend on N.
  *
  * There is no CPU implementation of the numeric stages in this program: without the library and
- * a B200 it stops with an error.  --rp (split-read support, split_read.c) is not built yet and is
- * refused rather than silently ignored.
+ * a B200 it stops with an error.  With --rp and --dups the split-read side path (split_read.c) runs too:
+ * the gate and the average-phred tests here (they need the BAM record and SONIC), the k-mer index, the
+ * re-mapping of the read halves and the overlap counts on the GPU.
  *
  * htslib and libsonic are third-party inputs (the same two libraries the reference links).
  */
@@ -37,6 +38,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cctype>
+#include <cmath>
 #include <chrono>
 #include <condition_variable>
 #include <cstdarg>
@@ -50,6 +52,7 @@
 #include <thread>
 #include <vector>
 
+#include <htslib/faidx.h>
 #include <htslib/hts.h>
 #include <htslib/sam.h>
 #include "sonic.h"
@@ -132,7 +135,7 @@ void print_help()
     fprintf(stdout, "\t--min-sv-size [INT]       : Minimum length of a CNV (default: 1000 bps)\n");
     fprintf(stdout, "\t--min-mapq [INT]          : Minimum mapping quality filter for reads (default: no-filter)\n");
     fprintf(stdout, "\t--c-score [FLOAT]         : Minimum c-score to filter variants (default: 0.5).\n");
-    fprintf(stdout, "\t--rp [INT]                : Split-read support for duplications (not available in this build).\n");
+    fprintf(stdout, "\t--rp [INT]                : Enable split-read and set minimum read-pair support for a duplication (Suggested for >5x only).\n");
     fprintf(stdout, "\n\tEnvironment: CONGA_GPUS (GPUs to spread the chromosomes over, default 1), CONGA_GPU_DEVICE (first CUDA device,\n"
                     "\tdefault 0), CONGA_DECODE_THREADS (default: cores, at most 16)\n");
     fprintf(stdout, "\n\tInformation:\n\t--version                 : Print version and exit.\n\t--help                    : Print this help screen and exit.\n\n");
@@ -283,6 +286,9 @@ struct ChromTask {
     int chr_index = -1, tid = -1;
     int32_t length = 0;
     std::vector<cg_read> reads;
+    std::vector<cg_half> halves;          /* --rp: the read halves find_split_reads would list, and their bases */
+    std::vector<char> bases;
+    std::vector<size_t> half_off;         /* offset of each half's bases */
     long n_records = 0;
     bool done = false, failed = false;
 };
@@ -297,9 +303,47 @@ struct Decoder {
     size_t consumed = 0;                  /* tasks the consumers are done with (any order) */
     size_t window;                        /* decode at most this many tasks ahead of the consumer */
     std::vector<std::thread> threads;
+    const bool sr_on;                     /* split-read machinery: --rp together with --dups (bam_data.c:207) */
+
+    /* The gate of bam_data.c:207 and the part of find_split_reads (split_read.c:205-336) that needs the
+     * BAM record: which halves exist (average-phred tests) and their bases.  The re-mapping itself
+     * (almostPerfect_match_seq_ref) is the GPU's. */
+    void split_halves(ChromTask& t, const bam1_t* b) const
+    {
+        const bam1_core_t& c = b->core;
+        const int l = c.l_qseq;
+        if (!(l > p.min_read_length)) return;
+        if ((c.flag & (BAM_FSECONDARY | BAM_FSUPPLEMENTARY | BAM_FDUP | BAM_FQCFAIL)) != 0) return;         /* is_proper, common.c:317-323 */
+        if (sonic_is_satellite(p.this_sonic, p.this_sonic->chromosome_names[t.chr_index], (int)c.pos, (int)c.pos + 20) != 0) return;
+        if (c.pos == 0) return;                                                                               /* split_read.c:215-216 */
+        const uint8_t* q = bam_get_qual(b);
+        const uint8_t* sq = bam_get_seq(b);
+        const int h = l / 2;
+        auto emit = [&](int from, int to, int32_t pos, uint8_t read2) {
+            cg_half hf;
+            hf.pos = pos; hf.seq_off = (uint32_t)0; hf.len = (uint16_t)(to - from); hf.read_len = (uint16_t)l;
+            hf.mapq = c.qual; hf.is_read2 = read2; hf.pad = 0;
+            t.half_off.push_back(t.bases.size());
+            for (int i = from; i < to; i++) {
+                const int code = bam_seqi(sq, i);
+                t.bases.push_back(code == 1 ? 'A' : code == 2 ? 'C' : code == 4 ? 'G' : code == 8 ? 'T' : 'N');
+            }
+            t.halves.push_back(hf);
+        };
+        /* the running average is NOT reset between the two halves (split_read.c:212, :236-239, :301-304) */
+        float avg = 0;
+        for (int i = h; i < l; i++) avg = avg + q[i];
+        avg = (float)avg / (float)(l - h);
+        if ((int)floorf(avg) < p.mq_threshold) return;
+        emit(h, l, (int32_t)c.pos, 0);
+        for (int i = 0; i < h; i++) avg = avg + q[i];
+        avg = (float)avg / (float)h;
+        if ((int)floorf(avg) < p.mq_threshold) return;
+        emit(0, h, (int32_t)(c.pos + h), 1);
+    }
 
     Decoder(const Params& p_, std::vector<ChromTask>& t, hts_idx_t* i, int n_threads, size_t win)
-        : p(p_), tasks(t), idx(i), window(win)
+        : p(p_), tasks(t), idx(i), window(win), sr_on(!p_.no_sr && p_.has_dup)
     {
         for (int k = 0; k < n_threads; k++) threads.emplace_back([this] { work(); });
     }
@@ -335,6 +379,7 @@ struct Decoder {
                         r.fl = (uint8_t)(((c.flag & BAM_FSECONDARY) ? 1 : 0) | ((c.flag & BAM_FQCFAIL) ? 2 : 0) | ((c.flag & BAM_FDUP) ? 4 : 0)
                              | ((c.flag & BAM_FSUPPLEMENTARY) ? 8 : 0) | ((c.flag & BAM_FUNMAP) ? 16 : 0) | ((c.flag & BAM_FREVERSE) ? 32 : 0));
                         t.reads.push_back(r);
+                        if (sr_on && (int)c.qual > p.mq_threshold) split_halves(t, b);
                     }
                     sam_itr_destroy(it);
                 }
@@ -362,6 +407,9 @@ struct Decoder {
         {
             std::lock_guard<std::mutex> lk(mu);
             std::vector<cg_read>().swap(tasks[k].reads);
+            std::vector<cg_half>().swap(tasks[k].halves);
+            std::vector<char>().swap(tasks[k].bases);
+            std::vector<size_t>().swap(tasks[k].half_off);
             consumed++;
         }
         cv.notify_all();
@@ -372,7 +420,8 @@ struct Decoder {
 struct Totals { int dels = 0, dups = 0; };
 
 void write_rows(const Params& p, const char* chr, const std::vector<cg_cnv>& dels, const std::vector<cg_call>& dcall,
-                const std::vector<cg_cnv>& dups, const std::vector<cg_call>& ucall, FILE* fp_svs, FILE* fp_del, FILE* fp_dup, Totals& tot)
+                const std::vector<cg_cnv>& dups, const std::vector<cg_call>& ucall, const std::vector<int32_t>& del_border_rp,
+                const std::vector<int32_t>& dup_rp, FILE* fp_svs, FILE* fp_del, FILE* fp_dup, Totals& tot)
 {
     int n_del = 0, n_dup = 0;
     const float c_score = p.c_score;
@@ -381,7 +430,7 @@ void write_rows(const Params& p, const char* chr, const std::vector<cg_cnv>& del
         for (size_t i = 0; i < dels.size(); i++) {
             const cg_call& r = dcall[i];
             const char* gt = r.score < c_score ? (r.copy_number == 2 ? "1/1" : "0/1") : (r.score <= inv_c ? "N/A" : "0/0");
-            const int border_rp = 0;                               /* split reads are not built (A19: 0 without --rp and --dups) */
+            const int border_rp = del_border_rp[i];                /* 0 unless --rp and --dups are both given (A19) */
             if (p.has_map) {
                 fprintf(fp_del, "%s\t%d\t%d\t%s\t%.2f\t%d\t%.2lf\t%d\t%.1f\n", chr, dels[i].start, dels[i].end, gt, r.score, border_rp,
                         r.mappability, r.observed, r.expected);
@@ -405,18 +454,20 @@ void write_rows(const Params& p, const char* chr, const std::vector<cg_cnv>& del
         for (size_t i = 0; i < dups.size(); i++) {
             const cg_call& r = ucall[i];
             const char* gt = r.copy_number == 2 ? "1/1" : "0/1";
-            const int rp = 0;
+            const int rp = dup_rp[i];
+            /* with --rp a duplication also qualifies through its read pairs (likelihood.c:245,265) */
+            const bool take = !p.no_sr ? (rp > p.rp_support || r.score < c_score) : (r.score < c_score);
             if (p.has_map) {
                 fprintf(fp_dup, "%s\t%d\t%d\t%s\t%.2lf\t%d\t%.2lf\t%d\t%.1f\n", chr, dups[i].start, dups[i].end, gt, r.score, rp,
                         r.mappability, r.observed, r.expected);
-                if (r.score < c_score && r.mappability > 0.5) {
+                if (take && r.mappability > 0.5) {
                     fprintf(fp_svs, "%s\t%d\t%d\tDUP\t%s\t%.2lf\t%d\t%.2lf\n", chr, dups[i].start, dups[i].end, gt, r.score, rp, r.mappability);
                     n_dup++;
                 }
             } else {
                 fprintf(fp_dup, "%s\t%d\t%d\t%s\t%.2lf\t%d\tN/A\t%d\t%.1f\n", chr, dups[i].start, dups[i].end, gt, r.score, rp,
                         r.observed, r.expected);
-                if (r.score < c_score) {
+                if (take) {
                     fprintf(fp_svs, "%s\t%d\t%d\tDUP\t%s\t%.2lf\t%d\tN/A\n", chr, dups[i].start, dups[i].end, gt, r.score, rp);
                     n_dup++;
                 }
@@ -452,6 +503,8 @@ struct ChromResult {
     cg_chrom_stats st;
     std::vector<cg_cnv> dels, dups;
     std::vector<cg_call> dcall, ucall;
+    std::vector<int32_t> border_rp, rp;   /* svs.border_rp of the deletions, svs.rp of the duplications */
+    long n_split = 0, n_paired = 0;
     bool done = false;
 };
 
@@ -477,6 +530,82 @@ struct Inputs {
     }
 };
 
+/* readReferenceSeq, common.c:421-458: the chromosome in upper case, fetched in 1000-base steps while
+ * `max < length` — so a tail shorter than the last step is never loaded and the sequence the k-mer index
+ * sees can be shorter than the SONIC length. */
+std::vector<char> read_reference(const Params& p, int chr_index)
+{
+    sonic* sn = p.this_sonic;
+    const char* name = sn->chromosome_names[chr_index];
+    const int L = sn->chromosome_lengths[chr_index];
+    faidx_t* fai = fai_load(p.ref_genome.c_str());
+    if (!fai) die("Error: cannot load the FASTA index of %s", p.ref_genome.c_str());
+    const int fa_len = faidx_seq_len(fai, name);
+    if (fa_len < 0) die("Error: chromosome %s is not in %s", name, p.ref_genome.c_str());
+    long bp = 0;
+    for (long mn = 0, mx = 999; mx < L;) {
+        const long e = std::min<long>(mx, fa_len - 1);
+        const long loc = e >= mn ? e - mn + 1 : 0;
+        if (loc <= 0) break;
+        bp += loc;
+        if (bp >= L) break;
+        mn += loc; mx += loc;
+    }
+    const int n = (int)std::min<long>(bp, L);
+    std::vector<char> seq((size_t)n);
+    if (n > 0) {
+        int got = 0;
+        char* raw = faidx_fetch_seq(fai, name, 0, n - 1, &got);
+        if (!raw || got < n) die("Error: cannot fetch %s:1-%d from %s", name, n, p.ref_genome.c_str());
+        for (int i = 0; i < n; i++) seq[i] = (char)toupper((unsigned char)raw[i]);
+        free(raw);
+    }
+    fai_destroy(fai);
+    return seq;
+}
+
+/* The split-read side path of one chromosome (bam_data.c:306-335): reference k-mer index and re-mapping
+ * of every half on the GPU, then read_SplitReads' satellite test and +-50 widening on the rows. */
+std::vector<cg_splitrow> split_read_rows(const Params& p, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
+{
+    sonic* sn = p.this_sonic;
+    const char* name = sn->chromosome_names[t.chr_index];
+    const std::vector<char> ref = read_reference(p, t.chr_index);
+    CG(ctx, cg_sr_reference(ctx, ref.data(), (int32_t)ref.size()));
+    const size_t MAX_BASES = (size_t)1 << 28;
+    std::vector<cg_half> batch;
+    for (size_t i = 0; i < t.halves.size();) {
+        const size_t base0 = t.half_off[i];
+        size_t j = i;
+        batch.clear();
+        while (j < t.halves.size() && t.half_off[j] + t.halves[j].len - base0 <= MAX_BASES) {
+            cg_half hf = t.halves[j];
+            hf.seq_off = (uint32_t)(t.half_off[j] - base0);
+            batch.push_back(hf);
+            j++;
+        }
+        const size_t nb = (j < t.halves.size() ? t.half_off[j] : t.bases.size()) - base0;
+        CG(ctx, cg_sr_push(ctx, batch.data(), batch.size(), t.bases.data() + base0, nb));
+        i = j;
+    }
+    r.n_split = (long)t.halves.size();
+    size_t n = 0;
+    std::vector<cg_splitrow> rows((size_t)1 << 16);
+    CG(ctx, cg_sr_rows(ctx, rows.data(), rows.size(), &n, nullptr));
+    if (n > rows.size()) { rows.resize(n); CG(ctx, cg_sr_rows(ctx, rows.data(), rows.size(), &n, nullptr)); }
+    rows.resize(n);
+    std::vector<cg_splitrow> kept;
+    for (cg_splitrow row : rows) {
+        /* bam_data.c:101-104: both ends outside satellites */
+        const float sat = sonic_is_satellite(sn, name, row.pos, row.pos + 1) + sonic_is_satellite(sn, name, row.pos_map, row.pos_map + 1);
+        if (sat != 0) continue;
+        row.left_start -= 50; row.left_end -= 50; row.right_start += 50; row.right_end += 50;   /* SOFTCLIP_WRONGMAP_WINDOW, :112-125 */
+        kept.push_back(row);
+    }
+    r.n_paired = (long)kept.size();
+    return kept;
+}
+
 /* The body of the reference's chromosome loop (bam_data.c:304-338) for one chromosome on one context. */
 void process_chromosome(const Params& p, Inputs& in, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
 {
@@ -487,6 +616,8 @@ void process_chromosome(const Params& p, Inputs& in, cg_ctx* ctx, const ChromTas
     for (size_t i = 0; i < t.reads.size(); i += BATCH)
         CG(ctx, cg_push_reads(ctx, t.reads.data() + i, std::min(BATCH, t.reads.size() - i)));
     CG(ctx, cg_chrom_finish(ctx, &r.st));
+    std::vector<cg_splitrow> rows;
+    if (!p.no_sr && p.has_dup) rows = split_read_rows(p, ctx, t, r);
     /* find_SVs, likelihood.c:311-371 */
     if (p.has_del) r.dels = select_cnvs(in.del_bed, r.chr.c_str(), p.min_sv_size);
     if (p.has_dup) r.dups = select_cnvs(in.dup_bed, r.chr.c_str(), p.min_sv_size);
@@ -499,6 +630,11 @@ void process_chromosome(const Params& p, Inputs& in, cg_ctx* ctx, const ChromTas
     }
     r.dcall.resize(r.dels.size());
     r.ucall.resize(r.dups.size());
+    r.border_rp.assign(r.dels.size(), 0);
+    r.rp.assign(r.dups.size(), 0);
+    if (!p.no_sr && p.has_dup)                                       /* count_ReadPairs, likelihood.c:344-348 */
+        CG(ctx, cg_sr_count(ctx, rows.data(), rows.size(), r.dels.data(), r.dels.size(), r.dups.data(), r.dups.size(),
+                            r.border_rp.data(), r.rp.data()));
     if (!r.dels.empty()) CG(ctx, cg_genotype(ctx, r.dels.data(), r.dels.size(), 0, r.dcall.data()));
     if (!r.dups.empty()) CG(ctx, cg_genotype(ctx, r.dups.data(), r.dups.size(), 1, r.ucall.data()));
 }
@@ -514,7 +650,8 @@ void emit_chromosome(const Params& p, const std::string& sample, const char* son
     const char* chr = r.chr.c_str();
     fprintf(stderr, "\nReading BAM [%s] - Chromosome: %s", sample.c_str(), chr);
     fprintf(stderr, "\n-->counting reads");
-    fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)r.st.reads_passed, 0L);
+    fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)r.st.reads_passed, r.n_split);
+    if (!p.no_sr && p.has_dup) fprintf(stderr, "Loading Split-Reads\n\nCONGA paired %ld single-end reads\n", r.n_paired);
     {   /* calc_mu_per_chr, read_distribution.c:39-41 */
         const float mean = (float)((double)r.st.rd_cnt / (double)(long)r.length);
         fprintf(g_log, "Read Count:%li  Window count:%li mean=%f\n", (long)r.st.rd_cnt, (long)r.length, mean);
@@ -524,7 +661,7 @@ void emit_chromosome(const Params& p, const std::string& sample, const char* son
     if (!r.has_cnvs) return;
     fprintf(stderr, "Finding mappability for each region\n");
     fprintf(stderr, "\nCalculating Likelihoods\n");
-    write_rows(p, chr, r.dels, r.dcall, r.dups, r.ucall, fp_svs, fp_del, fp_dup, tot);
+    write_rows(p, chr, r.dels, r.dcall, r.dups, r.ucall, r.border_rp, r.rp, fp_svs, fp_del, fp_dup, tot);
 }
 
 /* Longest-processing-time assignment by chromosome length: the depth pass streams
@@ -792,8 +929,6 @@ int main(int argc, char** argv)
     if (rc == 3) return EXIT_FAILURE;
     if (rc == 0) return EXIT_SUCCESS;
     print_params(p);
-    if (!p.no_sr && p.has_dup)
-        die("[CONGA-B200] --rp (split-read support) together with --dups is not built yet; run without --rp");
     if (!p.has_sonic) die("[CONGA CMDLINE ERROR] Please enter the SONIC file using the --sonic option.");
 
     tick("start");

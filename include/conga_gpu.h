@@ -156,6 +156,51 @@ int  cg_set_mappability_runs(cg_ctx* ctx, const cg_maprun* runs, size_t n, int e
  * Requires 0 <= start and end <= chrom_len (the reference reads unchecked, A23). */
 int cg_genotype(cg_ctx* ctx, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out);
 
+/* ---- read-pair support from split reads: `--rp` together with `--dups` (split_read.c, bam_data.c:10-154,
+ * likelihood.c:41-94).  Per chromosome, after cg_chrom_begin:
+ *   cg_sr_reference  <- readReferenceSeq + build_hash_table + create_hash_table   bam_data.c:306-312
+ *   cg_sr_push  (xN) <- find_split_reads -> almostPerfect_match_seq_ref           bam_data.c:207-210
+ *   cg_sr_rows       <- read_SplitReads + determine_SvType                         bam_data.c:331-335
+ *   cg_sr_count      <- count_ReadPairs                                            likelihood.c:344-348
+ * All pointers of these four calls are HOST pointers in either pointer mode; cg_sr_rows and cg_sr_count
+ * block.  The caller keeps what needs htslib or SONIC: the gate of bam_data.c:207, the average-phred
+ * tests of split_read.c:236-246 / :301-311 (which decide whether a half exists at all), and the
+ * sonic_is_satellite term of bam_data.c:101-102 on the rows that come back. */
+
+/* One half of a read that passed the gate and its average-phred test (a `splitRead`, 16 bytes). */
+typedef struct cg_half {
+    int32_t  pos;        /* splitRead.pos: core.pos for the second half of the read (split_read.c:228),
+                            core.pos + l_qseq/2 for the first half, the "_read2" element (:291) */
+    uint32_t seq_off;    /* offset of the half's bases in the `bases` buffer of the same cg_sr_push call */
+    uint16_t len;        /* bases in the half: strlen(str) in almostPerfect_match_seq_ref */
+    uint16_t read_len;   /* splitRead.read_length = core.l_qseq */
+    uint8_t  mapq;       /* splitRead.qual = core.qual */
+    uint8_t  is_read2;   /* readName ends in "_read2" (bam_data.c:40-41) */
+    uint16_t pad;
+} cg_half;
+
+/* A (half, mapping) pair that passed read_SplitReads' tests other than the satellite one and that
+ * determine_SvType classified; coordinates BEFORE the +-SOFTCLIP_WRONGMAP_WINDOW widening of
+ * bam_data.c:112-125. */
+typedef struct cg_splitrow {
+    int32_t pos, pos_map;                                    /* splitRead.pos, posMapSplitRead.posMap */
+    int32_t left_start, left_end, right_start, right_end;    /* locMapLeftStart/End, locMapRightStart/End */
+    uint8_t sv_type;                                         /* 'D' DELETION, 'E' DUPLICATION (common.h:12-13) */
+    uint8_t pad[7];
+} cg_splitrow;
+
+/* ref_seq[0..ref_len) is the chromosome as readReferenceSeq leaves it (upper case; common.c:421-458). */
+int cg_sr_reference(cg_ctx* ctx, const char* ref_seq, int32_t ref_len);
+/* n halves and their bases (one ASCII character per base: A C G T N). */
+int cg_sr_push(cg_ctx* ctx, const cg_half* halves, size_t n, const char* bases, size_t n_bases);
+/* Rows found since cg_sr_reference, in no particular order.  Copies min(*n_rows, cap) rows; *n_rows is the
+ * total.  n_mappings (may be NULL): (half, mapping) pairs listed, reverse-strand ones included. */
+int cg_sr_rows(cg_ctx* ctx, cg_splitrow* out, size_t cap, size_t* n_rows, uint64_t* n_mappings);
+/* rows: the caller's surviving rows with widened coordinates.  border_rp[n_del], rp[n_dup]: the counts
+ * count_ReadPairs adds to svs.border_rp / svs.rp (both start at 0, svs.c:164-167). */
+int cg_sr_count(cg_ctx* ctx, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
+                const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp);
+
 /* Wait for everything queued on the context (all of its streams).  In HOST pointer mode it
  * returns CG_ERANGE if a record or interval was clipped since the last report. */
 int cg_sync(cg_ctx* ctx);

@@ -159,12 +159,42 @@ def test_batch_of_samples_equals_separate_runs(tools):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
-def test_rp_is_refused_not_ignored(tools):
+@pytest.mark.parametrize("case", ["mq20", "map_default_mq", "ragged_length"])
+def test_split_read_support(tools, case):
+    """--rp with --dups (BASELINE.json configs[3]): the split-read side path — gate, average-phred tests, 10-mer
+    index of the chromosome, re-mapping of both read halves within +-100 kb at <= 5 % mismatches, FORWARD/FORWARD
+    pairing, satellite filter, +-50 widening, overlap counts — must reproduce the reference's READ_PAIR columns
+    and the read-pair rule for duplications in _svs.bed, byte for byte."""
     tmp = tempfile.mkdtemp(prefix="cli_")
     try:
-        p = subprocess.run([HOST, "-i", "x.bam", "--ref", "r.fa", "--sonic", "s.sonic", "--out", "o", "--dups", "d.bed", "--rp", "5"],
-                           cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-        assert p.returncode == 1 and b"--rp" in p.stderr
+        rng = np.random.default_rng({"mq20": 201, "map_default_mq": 202, "ragged_length": 203}[case])
+        if case == "mq20":
+            paths = cli_inputs.build_inputs_rp(tmp, [("1", 400_000), ("2", 250_000)], rng)
+            flags = ["--rp", "5", "--min-mapq", "20"]
+        elif case == "map_default_mq":
+            paths = cli_inputs.build_inputs_rp(tmp, [("1", 300_000), ("chr2", 200_000), ("X", 60_000)], rng, with_map=True)
+            flags = ["--rp", "12", "--mappability", paths["map"], "--min-read-length", "70"]
+        else:                                                    # lengths that are not multiples of 1000: the tail is never indexed
+            paths = cli_inputs.build_inputs_rp(tmp, [("1", 300_700), ("2", 150_300)], rng, junction_reads=8)
+            flags = ["--rp", "3", "--min-mapq", "9", "--c-score", "0.4"]
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"]] + flags)
+        assert_same(outs)
+        read_pair = [int(l.split(b"\t")[5]) for l in outs["ref"]["s_dups.bed"].split(b"\n")[1:] if l]
+        border = [int(l.split(b"\t")[5]) for l in outs["ref"]["s_dels.bed"].split(b"\n")[1:] if l]
+        assert max(read_pair) > 0 and max(border) > 0, "no read-pair support in the case: not a test"
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def test_rp_without_dups_changes_nothing(tools):
+    """--rp with only --dels leaves the split-read machinery off (bam_data.c:207: `!no_sr && dup_file`)."""
+    tmp = tempfile.mkdtemp(prefix="cli_")
+    try:
+        rng = np.random.default_rng(204)
+        paths = cli_inputs.build_inputs_rp(tmp, [("1", 200_000)], rng, junction_reads=5)
+        outs = run_both(tmp, paths, ["--dels", paths["dels"], "--rp", "5"])
+        assert_same(outs, expect_rows=False)
+        assert outs["ref"]["s_dels.bed"].count(b"\n") > 5
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
