@@ -133,8 +133,25 @@ def read_fasta_upper(path):
     return out
 
 
+def write_fasta_from(path, named_seqs, rng, width=60):
+    """FASTA + .fai from uppercase base arrays; a tenth of the bases are written in lower case (soft-masked)."""
+    fai = []
+    with open(path, "wb") as f:
+        for name, seq in named_seqs:
+            out = seq.copy()
+            lower = (rng.random(len(out)) < 0.1) & (out != ord("N"))
+            out[lower] += 32
+            f.write((">%s\n" % name).encode())
+            off = f.tell()
+            for i in range(0, len(out), width):
+                f.write(out[i:i + width].tobytes() + b"\n")
+            fai.append("%s\t%d\t%d\t%d\t%d\n" % (name, len(out), off, width, width + 1))
+    with open(path + ".fai", "w") as f:
+        f.writelines(fai)
+
+
 def build_inputs_rp(tmp, chroms, rng, reads_per_mb=15000, n_dels=12, n_dups=10, junction_reads=25, with_map=False,
-                    satellites=True):
+                    satellites=True, repeats=False):
     """Inputs for the split-read path (--rp with --dups): reads carry real bases copied from the reference
     (0.5 % substitutions) and phred bytes; every CNV gets `junction_reads` chimeric reads whose two halves
     sit on either side of its breakpoints, so READ_PAIR columns are non-zero.
@@ -142,6 +159,22 @@ def build_inputs_rp(tmp, chroms, rng, reads_per_mb=15000, n_dels=12, n_dups=10, 
     fa = os.path.join(tmp, "ref.fa")
     write_fasta(fa, chroms, rng)
     seqs = read_fasta_upper(fa)
+    if repeats:
+        seqs = {k: v.copy() for k, v in seqs.items()}
+        comp = np.zeros(256, dtype=np.uint8)
+        for x, y in zip(b"ACGTN", b"TGCAN"):
+            comp[x] = y
+        for name, L in chroms:
+            g = seqs[name]
+            p0 = int(L * 0.15)                               # tandem repeat: 6 copies of 200 bases -> several forward hits per half
+            for c in range(1, 6):
+                g[p0 + 200 * c:p0 + 200 * (c + 1)] = g[p0:p0 + 200]
+            p1 = int(L * 0.55)                               # 150 copies of 60 bases -> >= MAX_MAPPING hits: all dropped
+            for c in range(1, 150):
+                g[p1 + 60 * c:p1 + 60 * (c + 1)] = g[p1:p1 + 60]
+            p2 = int(L * 0.8)                                # inverted repeat 5 kb away -> reverse-strand hits
+            g[p2 + 5000:p2 + 5400] = comp[g[p2:p2 + 400]][::-1]
+        write_fasta_from(fa, [(name, seqs[name]) for name, _L in chroms], rng)
     for nm in ("gaps.bed", "dups_sonic.bed"):
         open(os.path.join(tmp, nm), "w").close()
     with open(os.path.join(tmp, "rm.out"), "w") as f:
@@ -168,6 +201,16 @@ def build_inputs_rp(tmp, chroms, rng, reads_per_mb=15000, n_dels=12, n_dups=10, 
         pos = rng.integers(1, L - 200, size=n)
         ln = rng.integers(50, 101, size=n)                       # some at or below --min-read-length 60: not split
         recs = [(int(p), ref[p:p + l].copy()) for p, l in zip(pos, ln)]
+        if repeats:
+            for frac, span in ((0.15, 1200), (0.55, 9000), (0.8, 5400)):      # dense coverage of the repeat structures
+                for p in rng.integers(int(L * frac) - 100, int(L * frac) + span, size=150):
+                    l = int(rng.integers(62, 101))
+                    recs.append((int(p), ref[p:p + l].copy()))
+            for p in rng.integers(L - 140, L - 100, size=20):                 # reads that end at the chromosome end
+                recs.append((int(p), ref[p:p + 100].copy()))
+            for p in (1, 2, 3):                                                # and at its start (pos 0 is skipped by the reference)
+                recs.append((p, ref[p:p + 80].copy()))
+            recs.append((0, ref[0:80].copy()))
         cn = {}
         for key, rows, cnt in (("del", del_rows, n_dels), ("dup", dup_rows, n_dups)):
             size = np.exp(rng.uniform(np.log(1200), np.log(min(60000, L // 6)), size=cnt)).astype(np.int64)
@@ -196,6 +239,8 @@ def build_inputs_rp(tmp, chroms, rng, reads_per_mb=15000, n_dels=12, n_dups=10, 
                 b = b.copy()
                 m = rng.random(len(b)) < 0.005
                 b[m] = rng.choice(sub, size=int(m.sum()))
+                if repeats and rng.random() < 0.05:
+                    b[rng.random(len(b)) < 0.03] = ord("N")
                 q = rng.integers(2, 41, size=len(b)).astype(np.uint8)
                 if rng.random() < 0.1:
                     q[:] = rng.integers(2, 25)                    # low-quality reads: the average-phred test bites

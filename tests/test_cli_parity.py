@@ -159,7 +159,7 @@ def test_batch_of_samples_equals_separate_runs(tools):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
-@pytest.mark.parametrize("case", ["mq20", "map_default_mq", "ragged_length"])
+@pytest.mark.parametrize("case", ["mq20", "map_default_mq", "ragged_length", "repeats_mq20", "repeats_mq_default"])
 def test_split_read_support(tools, case):
     """--rp with --dups (BASELINE.json configs[3]): the split-read side path — gate, average-phred tests, 10-mer
     index of the chromosome, re-mapping of both read halves within +-100 kb at <= 5 % mismatches, FORWARD/FORWARD
@@ -167,13 +167,16 @@ def test_split_read_support(tools, case):
     and the read-pair rule for duplications in _svs.bed, byte for byte."""
     tmp = tempfile.mkdtemp(prefix="cli_")
     try:
-        rng = np.random.default_rng({"mq20": 201, "map_default_mq": 202, "ragged_length": 203}[case])
+        rng = np.random.default_rng({"mq20": 201, "map_default_mq": 202, "ragged_length": 203, "repeats_mq20": 205, "repeats_mq_default": 206}[case])
         if case == "mq20":
             paths = cli_inputs.build_inputs_rp(tmp, [("1", 400_000), ("2", 250_000)], rng)
             flags = ["--rp", "5", "--min-mapq", "20"]
         elif case == "map_default_mq":
             paths = cli_inputs.build_inputs_rp(tmp, [("1", 300_000), ("chr2", 200_000), ("X", 60_000)], rng, with_map=True)
             flags = ["--rp", "12", "--mappability", paths["map"], "--min-read-length", "70"]
+        elif case.startswith("repeats"):                         # tandem repeats (mapq = 60 / n), >= 100 hits, inverted repeats, Ns, chromosome ends
+            paths = cli_inputs.build_inputs_rp(tmp, [("1", 350_000), ("2", 220_000)], rng, repeats=True)
+            flags = ["--rp", "4"] + (["--min-mapq", "20"] if case == "repeats_mq20" else [])
         else:                                                    # lengths that are not multiples of 1000: the tail is never indexed
             paths = cli_inputs.build_inputs_rp(tmp, [("1", 300_700), ("2", 150_300)], rng, junction_reads=8)
             flags = ["--rp", "3", "--min-mapq", "9", "--c-score", "0.4"]
