@@ -571,7 +571,9 @@ std::vector<cg_splitrow> split_read_rows(const Params& p, cg_ctx* ctx, const Chr
     sonic* sn = p.this_sonic;
     const char* name = sn->chromosome_names[t.chr_index];
     const std::vector<char> ref = read_reference(p, t.chr_index);
+    tick("split reads: reference sequence read");
     CG(ctx, cg_sr_reference(ctx, ref.data(), (int32_t)ref.size()));
+    tick("split reads: k-mer index built");
     const size_t MAX_BASES = (size_t)1 << 28;
     std::vector<cg_half> batch;
     for (size_t i = 0; i < t.halves.size();) {
@@ -589,6 +591,7 @@ std::vector<cg_splitrow> split_read_rows(const Params& p, cg_ctx* ctx, const Chr
         i = j;
     }
     r.n_split = (long)t.halves.size();
+    tick("split reads: halves re-mapped");
     size_t n = 0;
     std::vector<cg_splitrow> rows((size_t)1 << 16);
     CG(ctx, cg_sr_rows(ctx, rows.data(), rows.size(), &n, nullptr));
@@ -966,6 +969,7 @@ int main(int argc, char** argv)
     tick("BEDs parsed");
     gpus.wait();
     tick("CUDA contexts up");
+    if (getenv("CONGA_TIMING")) for (cg_ctx* c : gpus.ctx) cg_set_profiling(c, 1);
     FILE* main_log = g_log;
     for (size_t i = 0; i < samples.size(); i++) {
         Sample* next = i + 1 < samples.size() ? new Sample(samples[i + 1], (int)gpus.ctx.size()) : nullptr;   /* decoded under sample i */
@@ -986,6 +990,13 @@ int main(int argc, char** argv)
         cur = next;
         tick("sample done");
     }
+    if (getenv("CONGA_TIMING"))
+        for (cg_ctx* c : gpus.ctx) {
+            double ms[CG_NSLOTS]; int64_t n[CG_NSLOTS];
+            if (cg_kernel_times(c, ms, n) == CG_OK)
+                fprintf(stderr, "[timing] kernels: prep %.3f ms (%ld), depth pass %.3f ms (%ld), genotype %.3f ms (%ld), split reads %.3f ms (%ld)\n",
+                        ms[0], (long)n[0], ms[1], (long)n[1], ms[2], (long)n[2], ms[3], (long)n[3]);
+        }
     gpus.shutdown();
     tick("contexts destroyed");
     for (auto& kv : in.runs) cg_free_runs(kv.second.first);
