@@ -282,15 +282,42 @@ std::map<std::string, std::vector<cg_mapiv>> read_mappability_bed(const std::str
 }
 
 /* ---- decoding ahead of the GPU ---------------------------------------------------------- */
-struct ChromTask {
-    int chr_index = -1, tid = -1;
-    int32_t length = 0;
+/* readReferenceSeq, common.c:421-458, fetches the chromosome in 1000-base steps while `max < length` — so a tail
+ * shorter than the last step is never loaded and the sequence the k-mer index sees can be shorter than the
+ * SONIC length.  Returns bp_cnt, the number of bases it ends up with. */
+long reference_loaded_length(int L, int fa_len)
+{
+    long bp = 0;
+    for (long mn = 0, mx = 999; mx < L;) {
+        const long e = std::min<long>(mx, (long)fa_len - 1);
+        const long loc = e >= mn ? e - mn + 1 : 0;
+        if (loc <= 0) break;
+        bp += loc;
+        if (bp >= L) break;
+        mn += loc; mx += loc;
+    }
+    return std::min<long>(bp, L);
+}
+
+/* A chromosome is decoded in PARTS of CHROM_PART positions, each by whichever thread is free (the index
+ * makes any region seekable): part [beg, end) keeps the records whose pos lies inside it, so the parts in
+ * order are exactly the records the reference's iterator over [0, length) returns (bam_data.c:293). */
+#define CHROM_PART (4 << 20)
+struct Part {
+    int32_t beg = 0, end = 0;
     std::vector<cg_read> reads;
     std::vector<cg_half> halves;          /* --rp: the read halves find_split_reads would list, and their bases */
     std::vector<char> bases;
     std::vector<size_t> half_off;         /* offset of each half's bases */
-    long n_records = 0;
+};
+struct ChromTask {
+    int chr_index = -1, tid = -1;
+    int32_t length = 0;
+    std::vector<Part> parts;
+    std::vector<char> ref;                /* --rp: the chromosome as readReferenceSeq leaves it, filled part by part */
+    int parts_left = 0;
     bool done = false, failed = false;
+    size_t n_halves() const { size_t n = 0; for (const Part& q : parts) n += q.halves.size(); return n; }
 };
 
 struct Decoder {
@@ -303,18 +330,19 @@ struct Decoder {
     size_t consumed = 0;                  /* tasks the consumers are done with (any order) */
     size_t window;                        /* decode at most this many tasks ahead of the consumer */
     std::vector<std::thread> threads;
+    std::vector<std::pair<size_t, size_t>> items;   /* (task, part) in decoding order */
     const bool sr_on;                     /* split-read machinery: --rp together with --dups (bam_data.c:207) */
 
     /* The gate of bam_data.c:207 and the part of find_split_reads (split_read.c:205-336) that needs the
      * BAM record: which halves exist (average-phred tests) and their bases.  The re-mapping itself
      * (almostPerfect_match_seq_ref) is the GPU's. */
-    void split_halves(ChromTask& t, const bam1_t* b) const
+    void split_halves(const ChromTask& ct, Part& t, const bam1_t* b) const
     {
         const bam1_core_t& c = b->core;
         const int l = c.l_qseq;
         if (!(l > p.min_read_length)) return;
         if ((c.flag & (BAM_FSECONDARY | BAM_FSUPPLEMENTARY | BAM_FDUP | BAM_FQCFAIL)) != 0) return;         /* is_proper, common.c:317-323 */
-        if (sonic_is_satellite(p.this_sonic, p.this_sonic->chromosome_names[t.chr_index], (int)c.pos, (int)c.pos + 20) != 0) return;
+        if (sonic_is_satellite(p.this_sonic, p.this_sonic->chromosome_names[ct.chr_index], (int)c.pos, (int)c.pos + 20) != 0) return;
         if (c.pos == 0) return;                                                                               /* split_read.c:215-216 */
         const uint8_t* q = bam_get_qual(b);
         const uint8_t* sq = bam_get_seq(b);
@@ -345,6 +373,25 @@ struct Decoder {
     Decoder(const Params& p_, std::vector<ChromTask>& t, hts_idx_t* i, int n_threads, size_t win)
         : p(p_), tasks(t), idx(i), window(win), sr_on(!p_.no_sr && p_.has_dup)
     {
+        faidx_t* fai = nullptr;
+        if (sr_on && !(fai = fai_load(p.ref_genome.c_str()))) die("Error: cannot load the FASTA index of %s", p.ref_genome.c_str());
+        for (size_t k = 0; k < tasks.size(); k++) {
+            ChromTask& ct = tasks[k];
+            if (sr_on) {
+                const char* name = p.this_sonic->chromosome_names[ct.chr_index];
+                const int fa_len = faidx_seq_len(fai, name);
+                if (fa_len < 0) die("Error: chromosome %s is not in %s", name, p.ref_genome.c_str());
+                ct.ref.resize((size_t)reference_loaded_length(ct.length, fa_len));
+            }
+            for (int64_t beg = 0; beg < std::max<int64_t>(1, ct.length); beg += CHROM_PART) {
+                Part q;
+                q.beg = (int32_t)beg; q.end = (int32_t)std::min<int64_t>(beg + CHROM_PART, ct.length);
+                ct.parts.push_back(std::move(q));
+            }
+            ct.parts_left = (int)ct.parts.size();
+            for (size_t j = 0; j < ct.parts.size(); j++) items.emplace_back(k, j);
+        }
+        if (fai) fai_destroy(fai);
         for (int k = 0; k < n_threads; k++) threads.emplace_back([this] { work(); });
     }
     ~Decoder() { for (auto& t : threads) t.join(); }
@@ -354,44 +401,58 @@ struct Decoder {
         htsFile* fp = hts_open(p.bam_file.c_str(), "r");
         bam_hdr_t* hdr = fp ? sam_hdr_read(fp) : nullptr;
         bam1_t* b = bam_init1();
+        faidx_t* fai = sr_on ? fai_load(p.ref_genome.c_str()) : nullptr;     /* one handle per thread: fetching seeks */
         for (;;) {
-            const size_t k = next.fetch_add(1);
-            if (k >= tasks.size()) break;
-            {   /* bounded look-ahead: the reads of a whole chromosome are held in memory.  Every consumer
+            const size_t w = next.fetch_add(1);
+            if (w >= items.size()) break;
+            const size_t k = items[w].first;
+            {   /* bounded look-ahead: the reads of whole chromosomes are held in memory.  Every consumer
                  * takes its tasks in increasing order, so the smallest unreleased task is always
                  * inside the window and progress is guaranteed. */
                 std::unique_lock<std::mutex> lk(mu);
                 cv.wait(lk, [&] { return k < consumed + window; });
             }
             ChromTask& t = tasks[k];
+            Part& q = t.parts[items[w].second];
             bool ok = fp && hdr;
             if (ok) {
-                /* bam_data.c:293: every record overlapping [0, SONIC length) of this target */
-                hts_itr_t* it = sam_itr_queryi(idx, t.tid, 0, t.length);
+                hts_itr_t* it = sam_itr_queryi(idx, t.tid, q.beg, q.end);
                 if (!it) ok = false;
                 else {
                     while (sam_itr_next(fp, it, b) > 0) {
                         const bam1_core_t& c = b->core;
+                        if (c.pos < q.beg || c.pos >= q.end) continue;     /* starts in a neighbouring part */
                         cg_read r;
                         r.pos = (int32_t)c.pos;
                         r.len = c.l_qseq > 65535 ? 65535 : (uint16_t)c.l_qseq;
                         r.mapq = c.qual;
                         r.fl = (uint8_t)(((c.flag & BAM_FSECONDARY) ? 1 : 0) | ((c.flag & BAM_FQCFAIL) ? 2 : 0) | ((c.flag & BAM_FDUP) ? 4 : 0)
                              | ((c.flag & BAM_FSUPPLEMENTARY) ? 8 : 0) | ((c.flag & BAM_FUNMAP) ? 16 : 0) | ((c.flag & BAM_FREVERSE) ? 32 : 0));
-                        t.reads.push_back(r);
-                        if (sr_on && (int)c.qual > p.mq_threshold) split_halves(t, b);
+                        q.reads.push_back(r);
+                        if (sr_on && (int)c.qual > p.mq_threshold) split_halves(t, q, b);
                     }
                     sam_itr_destroy(it);
                 }
             }
+            if (ok && sr_on) {   /* this part's slice of the reference sequence, upper case (common.c:441-446) */
+                const int64_t e = std::min<int64_t>(q.end, (int64_t)t.ref.size());
+                if (e > q.beg) {
+                    int got = 0;
+                    char* raw = fai ? faidx_fetch_seq(fai, p.this_sonic->chromosome_names[t.chr_index], q.beg, (int)e - 1, &got) : nullptr;
+                    if (!raw || got < e - q.beg) ok = false;
+                    else for (int64_t i = 0; i < e - q.beg; i++) t.ref[(size_t)(q.beg + i)] = (char)toupper((unsigned char)raw[i]);
+                    free(raw);
+                }
+            }
             {
                 std::lock_guard<std::mutex> lk(mu);
-                t.failed = !ok;
-                t.done = true;
+                if (!ok) t.failed = true;
+                if (--t.parts_left == 0) t.done = true;
             }
             cv.notify_all();
         }
         bam_destroy1(b);
+        if (fai) fai_destroy(fai);
         if (hdr) bam_hdr_destroy(hdr);
         if (fp) hts_close(fp);
     }
@@ -406,10 +467,8 @@ struct Decoder {
     {
         {
             std::lock_guard<std::mutex> lk(mu);
-            std::vector<cg_read>().swap(tasks[k].reads);
-            std::vector<cg_half>().swap(tasks[k].halves);
-            std::vector<char>().swap(tasks[k].bases);
-            std::vector<size_t>().swap(tasks[k].half_off);
+            std::vector<Part>().swap(tasks[k].parts);
+            std::vector<char>().swap(tasks[k].ref);
             consumed++;
         }
         cv.notify_all();
@@ -530,67 +589,34 @@ struct Inputs {
     }
 };
 
-/* readReferenceSeq, common.c:421-458: the chromosome in upper case, fetched in 1000-base steps while
- * `max < length` — so a tail shorter than the last step is never loaded and the sequence the k-mer index
- * sees can be shorter than the SONIC length. */
-std::vector<char> read_reference(const Params& p, int chr_index)
-{
-    sonic* sn = p.this_sonic;
-    const char* name = sn->chromosome_names[chr_index];
-    const int L = sn->chromosome_lengths[chr_index];
-    faidx_t* fai = fai_load(p.ref_genome.c_str());
-    if (!fai) die("Error: cannot load the FASTA index of %s", p.ref_genome.c_str());
-    const int fa_len = faidx_seq_len(fai, name);
-    if (fa_len < 0) die("Error: chromosome %s is not in %s", name, p.ref_genome.c_str());
-    long bp = 0;
-    for (long mn = 0, mx = 999; mx < L;) {
-        const long e = std::min<long>(mx, fa_len - 1);
-        const long loc = e >= mn ? e - mn + 1 : 0;
-        if (loc <= 0) break;
-        bp += loc;
-        if (bp >= L) break;
-        mn += loc; mx += loc;
-    }
-    const int n = (int)std::min<long>(bp, L);
-    std::vector<char> seq((size_t)n);
-    if (n > 0) {
-        int got = 0;
-        char* raw = faidx_fetch_seq(fai, name, 0, n - 1, &got);
-        if (!raw || got < n) die("Error: cannot fetch %s:1-%d from %s", name, n, p.ref_genome.c_str());
-        for (int i = 0; i < n; i++) seq[i] = (char)toupper((unsigned char)raw[i]);
-        free(raw);
-    }
-    fai_destroy(fai);
-    return seq;
-}
-
 /* The split-read side path of one chromosome (bam_data.c:306-335): reference k-mer index and re-mapping
  * of every half on the GPU, then read_SplitReads' satellite test and +-50 widening on the rows. */
 std::vector<cg_splitrow> split_read_rows(const Params& p, cg_ctx* ctx, const ChromTask& t, ChromResult& r)
 {
     sonic* sn = p.this_sonic;
     const char* name = sn->chromosome_names[t.chr_index];
-    const std::vector<char> ref = read_reference(p, t.chr_index);
-    tick("split reads: reference sequence read");
-    CG(ctx, cg_sr_reference(ctx, ref.data(), (int32_t)ref.size()));
+    const std::vector<char>& ref = t.ref;                       /* fetched by the decode threads, part by part */
+    CG(ctx, cg_sr_reference(ctx, ref.empty() ? "" : ref.data(), (int32_t)ref.size()));
     tick("split reads: k-mer index built");
     const size_t MAX_BASES = (size_t)1 << 28;
     std::vector<cg_half> batch;
-    for (size_t i = 0; i < t.halves.size();) {
-        const size_t base0 = t.half_off[i];
-        size_t j = i;
-        batch.clear();
-        while (j < t.halves.size() && t.half_off[j] + t.halves[j].len - base0 <= MAX_BASES) {
-            cg_half hf = t.halves[j];
-            hf.seq_off = (uint32_t)(t.half_off[j] - base0);
-            batch.push_back(hf);
-            j++;
+    for (const Part& q : t.parts) {
+        for (size_t i = 0; i < q.halves.size();) {
+            const size_t base0 = q.half_off[i];
+            size_t j = i;
+            batch.clear();
+            while (j < q.halves.size() && q.half_off[j] + q.halves[j].len - base0 <= MAX_BASES) {
+                cg_half hf = q.halves[j];
+                hf.seq_off = (uint32_t)(q.half_off[j] - base0);
+                batch.push_back(hf);
+                j++;
+            }
+            const size_t nb = (j < q.halves.size() ? q.half_off[j] : q.bases.size()) - base0;
+            CG(ctx, cg_sr_push(ctx, batch.data(), batch.size(), q.bases.data() + base0, nb));
+            i = j;
         }
-        const size_t nb = (j < t.halves.size() ? t.half_off[j] : t.bases.size()) - base0;
-        CG(ctx, cg_sr_push(ctx, batch.data(), batch.size(), t.bases.data() + base0, nb));
-        i = j;
     }
-    r.n_split = (long)t.halves.size();
+    r.n_split = (long)t.n_halves();
     tick("split reads: halves re-mapped");
     size_t n = 0;
     std::vector<cg_splitrow> rows((size_t)1 << 16);
@@ -616,8 +642,9 @@ void process_chromosome(const Params& p, Inputs& in, cg_ctx* ctx, const ChromTas
     /* seams 1-3 */
     CG(ctx, cg_chrom_begin(ctx, t.chr_index, t.length, (const int8_t*)sn->chromosome_gc_profile[t.chr_index], t.length / 100 + 1, p.mq_threshold));
     const size_t BATCH = (size_t)1 << 22;
-    for (size_t i = 0; i < t.reads.size(); i += BATCH)
-        CG(ctx, cg_push_reads(ctx, t.reads.data() + i, std::min(BATCH, t.reads.size() - i)));
+    for (const Part& q : t.parts)
+        for (size_t i = 0; i < q.reads.size(); i += BATCH)
+            CG(ctx, cg_push_reads(ctx, q.reads.data() + i, std::min(BATCH, q.reads.size() - i)));
     CG(ctx, cg_chrom_finish(ctx, &r.st));
     std::vector<cg_splitrow> rows;
     if (!p.no_sr && p.has_dup) rows = split_read_rows(p, ctx, t, r);
@@ -793,7 +820,9 @@ struct Sample {
         }
         int n_threads = (int)std::min<size_t>(std::max<unsigned>(1u, std::thread::hardware_concurrency()), 16);
         if (const char* e = getenv("CONGA_DECODE_THREADS")) n_threads = std::max(1, atoi(e));
-        n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, todo.size()));
+        size_t n_parts = 0;
+        for (const ChromTask& t : todo) n_parts += ((size_t)std::max<int32_t>(1, t.length) + CHROM_PART - 1) / CHROM_PART;
+        n_threads = (int)std::min<size_t>((size_t)n_threads, std::max<size_t>(1, n_parts));
         dec = new Decoder(p, todo, idx, n_threads, (size_t)n_threads + 2 * (size_t)n_gpus);
     }
     ~Sample()
