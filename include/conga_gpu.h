@@ -236,7 +236,7 @@ int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
  * call, and clears them.  Slots: 0 = chromosome init + batch marking + rare paths
  * + tile scan, 1 = the fused depth/GC/prefix pass (it also derives the expected table),
  * 2 = CNV sums + likelihoods (runs on the genotype stream, overlapping slot 1 of the next
- * chromosome), 3 = unused. */
+ * chromosome), 3 = the split-read kernels (k-mer index, re-mapping, overlap counts). */
 #define CG_NSLOTS 4
 int cg_set_profiling(cg_ctx* ctx, int on);
 int cg_kernel_times(cg_ctx* ctx, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS]);
