@@ -294,6 +294,35 @@ class Context:
     def stats_reset(self):
         self._ck(self.lib.cg_stats_reset(self.h))
 
+    # -- split reads (--rp) ---------------------------------------------------
+    def sr_reference(self, ref: np.ndarray):
+        ref = np.ascontiguousarray(ref, dtype=np.uint8)
+        self._keep_ref = ref
+        self._ck(self.lib.cg_sr_reference(self.h, ref.ctypes.data if len(ref) else C.cast(C.c_char_p(b""), C.c_void_p).value, len(ref)))
+
+    def sr_push(self, halves: np.ndarray, bases: np.ndarray):
+        halves = np.ascontiguousarray(halves, dtype=HALF_DT)
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        if len(halves):
+            self._ck(self.lib.cg_sr_push(self.h, halves.ctypes.data, len(halves), bases.ctypes.data, len(bases)))
+
+    def sr_rows(self):
+        n, nm = C.c_size_t(0), C.c_uint64(0)
+        self._ck(self.lib.cg_sr_rows(self.h, None, 0, C.byref(n), C.byref(nm)))
+        out = np.zeros(n.value, dtype=SPLITROW_DT)
+        if n.value:
+            self._ck(self.lib.cg_sr_rows(self.h, out.ctypes.data, len(out), C.byref(n), C.byref(nm)))
+        return out, int(nm.value)
+
+    def sr_count(self, rows: np.ndarray, dels: np.ndarray, dups: np.ndarray):
+        rows = np.ascontiguousarray(rows, dtype=SPLITROW_DT)
+        dels = np.ascontiguousarray(dels, dtype=CNV_DT)
+        dups = np.ascontiguousarray(dups, dtype=CNV_DT)
+        b, r = np.zeros(len(dels), dtype=np.int32), np.zeros(len(dups), dtype=np.int32)
+        self._ck(self.lib.cg_sr_count(self.h, rows.ctypes.data if len(rows) else None, len(rows), dels.ctypes.data if len(dels) else None, len(dels),
+                                      dups.ctypes.data if len(dups) else None, len(dups), b.ctypes.data if len(b) else None, r.ctypes.data if len(r) else None))
+        return b, r
+
     def stats_bank(self, bank: int):
         self._ck(self.lib.cg_stats_bank(self.h, int(bank)))
 

@@ -207,3 +207,185 @@ void orc_chromosome(const cg_read* recs, size_t n_reads, int mq_threshold,
     orc_find_depths(depth, gc, expected, m, dels, n_dels, 0, del_out);
     orc_find_depths(depth, gc, expected, m, dups, n_dups, 1, dup_out);
 }
+
+/* ======================================================================================
+ * Split-read support (--rp with --dups): restatement of the part of split_read.c /
+ * bam_data.c / likelihood.c that the CUDA path replaces.  Same caveat as above: TEST
+ * INFRASTRUCTURE ONLY.  Pinned against the reference binary through the per-CNV rp /
+ * border_rp values its --wrap dump holds (tests/golden/rp/ref_rp.npz) and, on the GPU box,
+ * through the command-line parity tests.
+ *   orc_sr_rows    build_hash_table x2 + init_hash_table     split_read.c:338-455
+ *                  almostPerfect_match_seq_ref               split_read.c:76-204
+ *                  read_SplitReads' tests (satellite term excluded) + determine_SvType
+ *                                                            bam_data.c:29-154
+ *   orc_sr_count   count_ReadPairs                           likelihood.c:41-94
+ * ====================================================================================== */
+#include <stdio.h>
+
+#define ORC_K 10                 /* HASHKMERLEN   split_read.h:18 */
+#define ORC_MAX_SR_HIT 50000     /* split_read.h:13 */
+#define ORC_MAX_MAPPING 100      /* split_read.h:14 */
+#define ORC_LOOKAHEAD 100000     /* split_read.c:5 */
+
+static int orc_is_dna(char c) { return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }       /* common.c:303-314 */
+static int orc_kmer_valid(const char* s)                                                       /* split_read.c:60-74 */
+{
+    for (int i = 0; i < ORC_K; i++) { if (s[i] == 0) return 0; if (!orc_is_dna(s[i])) return 0; }
+    return 1;
+}
+static unsigned orc_hash_ref(const char* s)                                                    /* split_read.c:36-50 */
+{
+    unsigned val = 0;
+    for (int i = 0; i < ORC_K; i++) val = (val << 2) | (unsigned)((s[i] & 0x6) >> 1);
+    return val;
+}
+
+/* one scan of build_hash_table: mode 0 counts, mode 1 fills (split_read.c:338-421); the rolling
+ * update is hash_function_next (split_read.c:29-34) */
+static void orc_build(const char* ref, int len, int hash_size, int mode, int* count, int* iter, int** array)
+{
+    int i = 0, j;
+    const unsigned mask = (unsigned)(hash_size - 1) >> 2;
+    const int len_limit = len - ORC_K + 1;
+    unsigned h;
+    if (len < ORC_K) return;
+    while (i < len && !orc_is_dna(ref[i])) i++;
+    while (i < len_limit && !orc_kmer_valid(ref + i)) i++;
+    if (i >= len_limit) return;
+    h = orc_hash_ref(ref + i);
+#define ORC_ADD(pos) do { if (mode == 0) count[h]++; else if (count[h] != 0) { array[h][iter[h]] = (pos); iter[h]++; } } while (0)
+    ORC_ADD(i);
+    j = i + ORC_K;
+    while (i < len_limit) {
+        i++;
+        if (orc_is_dna(ref[j])) {
+            h = ((h & mask) << 2) | (unsigned)((ref[j++] & 0x6) >> 1);
+            ORC_ADD(i);
+        } else {
+            while (!orc_is_dna(ref[j]) && i < len_limit) { i++; j++; }
+            if (i >= len_limit) break;
+            while (i < len_limit && !orc_kmer_valid(ref + i)) i++;
+            if (i >= len_limit) break;             /* the reference would run off the sequence here */
+            j = i + ORC_K;
+            h = orc_hash_ref(ref + i);
+            ORC_ADD(i);
+        }
+    }
+#undef ORC_ADD
+}
+
+/* rows in the order the reference's lists would yield them is not reproduced: callers compare multisets */
+long orc_sr_rows(const char* ref, int ref_len, const cg_half* halves, size_t n_halves, const char* bases,
+                 int chrom_len, int mq_threshold, cg_splitrow* out, size_t cap, uint64_t* n_mappings)
+{
+    const int hash_size = 1 << (2 * ORC_K);
+    int* count = (int*)calloc((size_t)hash_size, sizeof(int));
+    int* iter = (int*)calloc((size_t)hash_size, sizeof(int));
+    int** array = (int**)calloc((size_t)hash_size, sizeof(int*));
+    char* refz = (char*)malloc((size_t)ref_len + 2048);
+    long n_rows = 0;
+    uint64_t n_map = 0;
+    memcpy(refz, ref, (size_t)ref_len);
+    memset(refz + ref_len, 0, 2048);                /* the terminator; what lies behind it is not a base */
+    orc_build(refz, ref_len, hash_size, 0, count, iter, array);
+    for (int i = 0; i < hash_size; i++) {           /* init_hash_table, split_read.c:431-449 */
+        if (count[i] != 0 && count[i] < ORC_MAX_SR_HIT) array[i] = (int*)malloc(sizeof(int) * (size_t)count[i]);
+        else count[i] = 0;
+    }
+    orc_build(refz, ref_len, hash_size, 1, count, iter, array);
+
+    int* posMap = (int*)malloc(sizeof(int) * 400000);
+    char* orient = (char*)malloc(400000);
+    for (size_t k = 0; k < n_halves; k++) {
+        const cg_half* hf = &halves[k];
+        char str[2048], rev[2048];
+        const int len = hf->len < 2047 ? hf->len : 2047;
+        memcpy(str, bases + hf->seq_off, (size_t)len);
+        str[len] = 0;
+        const int dist_max = (int)(0.05 * len);
+        int size = 0;
+        if (len < ORC_K) continue;
+        if (orc_kmer_valid(str)) {
+            const unsigned idx = orc_hash_ref(str);
+            for (int c = 0; c < count[idx]; c++) {
+                const int hit = array[idx][c];
+                if (abs(hit - hf->pos) < ORC_LOOKAHEAD) {
+                    int d = 0;
+                    for (int i = 0; i < len; i++) if (refz[hit + i] != str[i]) d++;          /* hammingDistance, common.c:277-287 */
+                    if (d <= dist_max && size < 400000) { posMap[size] = hit; orient[size] = 'F'; size++; }
+                }
+            }
+        }
+        if (size < ORC_MAX_MAPPING) {
+            for (int i = 0; i < len; i++) {
+                const char c = str[i];
+                rev[len - i - 1] = c == 'A' ? 'T' : c == 'T' ? 'A' : c == 'G' ? 'C' : c == 'C' ? 'G' : c;
+            }
+            rev[len] = 0;
+            if (orc_kmer_valid(rev)) {
+                const unsigned idx = orc_hash_ref(rev);
+                for (int c = 0; c < count[idx]; c++) {
+                    const int hit = array[idx][c];
+                    if (abs(hit - hf->pos) < ORC_LOOKAHEAD) {
+                        int d = 0;
+                        for (int i = 0; i < len; i++) if (refz[hit + i] != rev[i]) d++;
+                        if (d <= dist_max) { posMap[size] = hit; orient[size] = 'R'; size++; }
+                    }
+                    if (size > ORC_MAX_MAPPING) break;
+                }
+            }
+        }
+        if (!(size > 0 && size < ORC_MAX_MAPPING)) continue;
+        n_map += (uint64_t)size;
+        const int mapq = 60 / size;
+        for (int m = 0; m < size; m++) {
+            const int pos = hf->pos, pm = posMap[m];
+            /* read_SplitReads, bam_data.c:104-106, without the satellite term */
+            if (!((int)hf->mapq > mq_threshold && mapq > mq_threshold && pos > 0 && pm > 0 && pos < chrom_len && pm < chrom_len)) continue;
+            /* determine_SvType, bam_data.c:29-78 */
+            const int lengthSplit = hf->read_len / 2, lengthRead = hf->read_len - lengthSplit;
+            int p11, p12, p21, p22;
+            if (pos < pm) { p11 = pos; p12 = pos + lengthRead; p21 = pm; p22 = pm + lengthSplit; }
+            else if (pm < pos) { p11 = pm; p12 = pm + lengthSplit; p21 = pos; p22 = pos + lengthRead; }
+            else continue;
+            if (p12 >= p21) continue;
+            if (orient[m] != 'F') continue;                      /* splitRead.orient is always FORWARD */
+            char type;
+            if ((pos < pm && !hf->is_read2) || (pos > pm && hf->is_read2)) type = 'D';
+            else if ((pm < pos && !hf->is_read2) || (pm > pos && hf->is_read2)) type = 'E';
+            else continue;
+            if ((size_t)n_rows < cap) {
+                cg_splitrow r;
+                memset(&r, 0, sizeof r);
+                r.pos = pos; r.pos_map = pm; r.left_start = p11; r.left_end = p12; r.right_start = p21; r.right_end = p22;
+                r.sv_type = (uint8_t)type;
+                out[n_rows] = r;
+            }
+            n_rows++;
+        }
+    }
+    for (int i = 0; i < hash_size; i++) free(array[i]);
+    free(count); free(iter); free(array); free(refz); free(posMap); free(orient);
+    if (n_mappings) *n_mappings = n_map;
+    return n_rows;
+}
+
+/* count_ReadPairs, likelihood.c:41-94; rows carry the widened coordinates */
+void orc_sr_count(const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del, const cg_cnv* dups, size_t n_dup,
+                  int32_t* border_rp, int32_t* rp)
+{
+    for (size_t i = 0; i < n_del; i++) border_rp[i] = 0;
+    for (size_t i = 0; i < n_dup; i++) rp[i] = 0;
+    for (size_t k = 0; k < n; k++) {
+        const cg_splitrow* r = &rows[k];
+        if (r->sv_type == 'E') {
+            for (size_t i = 0; i < n_dup; i++)
+                if (r->left_end >= dups[i].start - 5000 && r->left_end <= dups[i].end + 5000
+                    && r->right_start <= dups[i].end + 5000 && r->right_start >= dups[i].start - 5000) rp[i]++;
+        } else if (r->sv_type == 'D') {
+            for (size_t i = 0; i < n_del; i++)
+                if (r->left_end <= dels[i].start + 100 && r->left_end >= dels[i].start - 5000
+                    && r->right_start >= dels[i].end - 100 && r->right_start <= dels[i].end + 5000) border_rp[i]++;
+        }
+    }
+}

@@ -12,7 +12,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "oracle", "liboracle.so")
 
-from conga_b200.abi import CALL_DT, CNV_DT, MAPIV_DT, READ_DT, STATS_DT  # noqa: E402  (struct layouts only)
+from conga_b200.abi import CALL_DT, CNV_DT, HALF_DT, MAPIV_DT, READ_DT, SPLITROW_DT, STATS_DT  # noqa: E402  (struct layouts only)
 
 
 class Oracle:
@@ -33,6 +33,32 @@ class Oracle:
         lib.orc_gc_bin.restype = C.c_int
         lib.orc_chromosome.argtypes = [P, C.c_size_t, C.c_int, C.c_int32, P, P, C.c_size_t,
                                        P, C.c_size_t, P, P, C.c_size_t, P, P, P, P, P]
+
+    def sr_rows(self, ref, halves, bases, chrom_len, mq_threshold):
+        """split_read.c / bam_data.c:29-154 minus the satellite term -> (SPLITROW_DT rows, n_mappings)"""
+        P = C.c_void_p
+        self.lib.orc_sr_rows.argtypes = [P, C.c_int, P, C.c_size_t, P, C.c_int, C.c_int, P, C.c_size_t, C.POINTER(C.c_uint64)]
+        self.lib.orc_sr_rows.restype = C.c_long
+        ref = np.ascontiguousarray(ref, dtype=np.uint8)
+        halves = np.ascontiguousarray(halves, dtype=HALF_DT)
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        cap = max(1024, 64 * len(halves))
+        out = np.zeros(cap, dtype=SPLITROW_DT)
+        nm = C.c_uint64(0)
+        n = self.lib.orc_sr_rows(ref.ctypes.data, len(ref), halves.ctypes.data, len(halves), bases.ctypes.data, chrom_len, mq_threshold,
+                                 out.ctypes.data, cap, C.byref(nm))
+        assert n <= cap
+        return out[:n], int(nm.value)
+
+    def sr_count(self, rows, dels, dups):
+        P = C.c_void_p
+        self.lib.orc_sr_count.argtypes = [P, C.c_size_t, P, C.c_size_t, P, C.c_size_t, P, P]
+        rows = np.ascontiguousarray(rows, dtype=SPLITROW_DT)
+        dels = np.ascontiguousarray(dels, dtype=CNV_DT)
+        dups = np.ascontiguousarray(dups, dtype=CNV_DT)
+        b, r = np.zeros(len(dels), dtype=np.int32), np.zeros(len(dups), dtype=np.int32)
+        self.lib.orc_sr_count(rows.ctypes.data, len(rows), dels.ctypes.data, len(dels), dups.ctypes.data, len(dups), b.ctypes.data, r.ctypes.data)
+        return b, r
 
     def count_reads(self, reads, mq_threshold, chrom_len, depth=None):
         """bam_data.c:201-217 -> (int16 depth, total_read_count)"""
