@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--skip-reference", action="store_true")
     ap.add_argument("--keep", action="store_true")
+    ap.add_argument("--batch", type=int, default=0, help="also run K copies of the sample through CONGA_BATCH in one process")
     args = ap.parse_args()
     wl = {"c1": synth.config1, "c2": lambda: synth.config2(scale=args.scale), "c3": lambda: synth.config3(scale=args.scale)}[args.workload]()
     tmp = tempfile.mkdtemp(prefix="clibench_")
@@ -86,6 +87,26 @@ def main():
         res["b200_median_s"] = round(float(np.median(tb)), 3)
         res["b200_gpus"] = args.gpus
         res["b200_reads_per_s"] = round(wl.n_reads / float(np.median(tb)), 1)
+        if args.batch > 0:
+            # configs[4] shape: many samples against one CNV set, one process (contexts, SONIC, BEDs, tracks resident)
+            wd = os.path.join(tmp, "batch")
+            os.makedirs(wd, exist_ok=True)
+            with open(os.path.join(wd, "batch.tsv"), "w") as f:
+                for i in range(args.batch):
+                    f.write("%s\t%s\n" % (bam, os.path.join(wd, "s%d" % i)))
+            cmd = [HOST, "-i", bam, "--ref", os.path.join(tmp, "ref.fa"), "--out", os.path.join(wd, "unused")] + flags
+            t = time.perf_counter()
+            p = subprocess.run(cmd, cwd=wd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE,
+                               env=dict(os.environ, CONGA_BATCH=os.path.join(wd, "batch.tsv"), CONGA_GPUS=str(args.gpus), CONGA_TIMING="1"))
+            dt = time.perf_counter() - t
+            if p.returncode != 0:
+                sys.exit("batch failed: %s" % p.stderr.decode(errors="replace")[-1500:])
+            marks = [float(l.split()[1]) for l in p.stderr.decode(errors="replace").split("\n") if l.startswith("[timing]") and "sample done" in l]
+            same = all(open(os.path.join(wd, "s%d_%s" % (i, nm)), "rb").read() == ob["s_" + nm]
+                       for i in range(args.batch) for nm in ("svs.bed", "dels.bed", "dups.bed") if ob["s_" + nm] is not None)
+            res["batch"] = {"samples": args.batch, "total_s": round(dt, 3), "first_sample_done_s": marks[0] if marks else None,
+                            "s_per_sample_after_first": round((marks[-1] - marks[0]) / max(1, len(marks) - 1), 4) if len(marks) > 1 else None,
+                            "identical_to_single_runs": same}
         if not args.skip_reference:
             dt, orf = run(os.path.join(REF, "conga"), "ref")
             res["reference_s"] = round(dt, 3)
