@@ -119,10 +119,15 @@ def test_two_gpus_write_the_same_bytes(tools):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
-def test_batch_of_samples_equals_separate_runs(tools):
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_batch_of_samples_equals_separate_runs(tools, gpus):
     """CONGA_BATCH: three BAMs against one CNV set / mappability track in ONE process (contexts, SONIC, BEDs and
     flattened tracks set up once, sample k+1 decoded under sample k) — each sample's files must be the bytes a
     separate run of the reference writes for it."""
+    if gpus > 1:
+        import torch
+        if torch.cuda.device_count() < gpus:
+            pytest.skip("needs %d GPUs" % gpus)
     tmp = tempfile.mkdtemp(prefix="cli_")
     try:
         rng = np.random.default_rng(106)
@@ -147,7 +152,7 @@ def test_batch_of_samples_equals_separate_runs(tools):
                 f.write("%s\t%s\n" % (bam, os.path.join(wd, "s%d" % i)))
         p = subprocess.run([HOST, "-i", bams[0], "--ref", paths["ref"], "--sonic", paths["sonic"], "--out", os.path.join(wd, "unused")] + flags,
                            cwd=wd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600,
-                           env=dict(os.environ, CONGA_BATCH=os.path.join(wd, "batch.tsv")))
+                           env=dict(os.environ, CONGA_BATCH=os.path.join(wd, "batch.tsv"), CONGA_GPUS=str(gpus)))
         assert p.returncode == 0, p.stderr.decode(errors="replace")[-2000:]
         for i in range(3):
             for nm in ("svs.bed", "dels.bed", "dups.bed"):
