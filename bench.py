@@ -270,6 +270,7 @@ def own_arm(args):
     # results (statistics rows, genotype calls) are valid on the host.
     ctx.set_pointer_mode(CG_PTR_HOST)
     ctx.set_async(True)
+    DEPTH = max(1, env_int("BENCH_E2E_DEPTH", 2))      # samples in flight behind the one being issued
     host = []
     h2d = d2h = 0
     for c in mine:
@@ -277,10 +278,10 @@ def own_arm(args):
         pg = ctx.pinned_array(len(c.gc), np.int8); pg[:] = c.gc
         pd = ctx.pinned_array(len(c.dels), CNV_DT); pd[:] = c.dels
         pu = ctx.pinned_array(len(c.dups), CNV_DT); pu[:] = c.dups
-        # results are double-buffered: sample k's calls stay intact while sample k+1 is being issued
-        od = [ctx.pinned_array(len(c.dels), CALL_DT) for _ in range(2)]
-        ou = [ctx.pinned_array(len(c.dups), CALL_DT) for _ in range(2)]
-        st = [ctx.pinned_array(1, STATS_DT) for _ in range(2)]
+        # results are multi-buffered: sample k's calls stay intact while the next DEPTH samples are being issued
+        od = [ctx.pinned_array(len(c.dels), CALL_DT) for _ in range(DEPTH + 1)]
+        ou = [ctx.pinned_array(len(c.dups), CALL_DT) for _ in range(DEPTH + 1)]
+        st = [ctx.pinned_array(1, STATS_DT) for _ in range(DEPTH + 1)]
         rows = np.ascontiguousarray(c.maprows) if (has_map and c.maprows is not None) else np.zeros(0, dtype=MAPIV_DT)
         # the track is flattened once per BED file (input parsing, like the reference's per-chromosome
         # re-parse of the BED, svs.c:329-374); its upload is part of every step
@@ -294,6 +295,7 @@ def own_arm(args):
 
     def step_host():
         bank = sample_no[0] & 1
+        buf = sample_no[0] % (DEPTH + 1)
         sample_no[0] += 1
         if world > 1:
             ctx.stats_bank(bank)
@@ -302,28 +304,28 @@ def own_arm(args):
             for i in range(0, len(pr), BATCH):
                 n = min(BATCH, len(pr) - i)
                 ctx._ck(lib.cg_push_reads(h, pr.ctypes.data + i * READ_DT.itemsize, n))
-            ctx._ck(lib.cg_chrom_finish(h, st[bank].ctypes.data))
+            ctx._ck(lib.cg_chrom_finish(h, st[buf].ctypes.data))
             if has_map:
                 ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data if len(prn) else None, len(prn), 1))
             if len(pd):
-                ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od[bank].ctypes.data))
+                ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od[buf].ctypes.data))
             if len(pu):
-                ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou[bank].ctypes.data))
+                ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou[buf].ctypes.data))
         if world > 1:
             ctx.join()
             with torch.cuda.stream(ext):
                 multi.allreduce_stats(tables[bank])
-        # one sample in flight behind the one being issued: its statistics rows and calls are complete in
-        # host memory when its event has passed (a pipelined host waits here, not on the whole device)
+        # DEPTH samples in flight behind the one being issued: a sample's statistics rows and calls are complete
+        # in host memory when its event has passed (a pipelined host waits there, not on the whole device)
         ev = torch.cuda.Event()
         ctx.join()
         with torch.cuda.stream(ext):
             ev.record()
-        if pending[0] is not None:
-            pending[0].synchronize()
-        pending[0] = ev
+        pending.append(ev)
+        if len(pending) > DEPTH:
+            pending.pop(0).synchronize()
 
-    pending = [None]
+    pending = []
     for _ in range(max(1, min(args.warmup, 2))):
         step_host()
     ms_e2e = timed(step_host, args.steps)     # timed() ends with cg_sync: the last sample is complete as well
@@ -336,7 +338,7 @@ def own_arm(args):
     # sanity: the e2e leg and the device leg produced the same bits for the last chromosome
     if res:
         got = res[-1]["out_del"].cpu().numpy()[: len(mine[-1].dels) * CALL_DT.itemsize]
-        for b in range(2):
+        for b in range(DEPTH + 1):
             assert got.tobytes() == host[-1][5][b].tobytes(), "device-mode and host-mode results differ"
 
     n_reads, n_cnvs = wl.n_reads, wl.n_cnvs
@@ -380,7 +382,7 @@ def own_arm(args):
            "cnvs_per_s": round(n_cnvs * args.steps / (ms_dev / 1e3), 1),
            "cnvs_per_s_genotype_kernels_rank0": round(sum(len(c.dels) + len(c.dups) for c in mine) / (cnv_ms / 1e3), 1) if cnv_ms > 0 else None,
            "e2e": {"value": round(e2e, 1), "unit": "reads/s", "ms_per_step": round(ms_e2e / args.steps, 4),
-                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "samples_in_flight": DEPTH},
            "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_port(wl, budget_s=args.cpu_budget)

@@ -75,6 +75,55 @@ for path in (args.libs or [abi.LIB_PATH]):
     out["no_dups"] = run(args.steps, dups=False)
     out["no_map"] = run(args.steps, mapp=False)
     out["no_geno"] = run(args.steps, geno=False, mapp=False)
+    # HOST pointer mode from pinned buffers (bench.py's e2e leg), one sample in flight behind the one being issued
+    from conga_b200 import CG_PTR_HOST, READ_DT, CNV_DT, MAPRUN_DT, STATS_DT
+    ctx.set_pointer_mode(CG_PTR_HOST); ctx.set_async(True)
+    host = []
+    for c in mine:
+        pin = lambda a, dt: (lambda q: (q.__setitem__(slice(None), a), q)[1])(ctx.pinned_array(len(a), dt))
+        runs = flatten_mappability(np.ascontiguousarray(c.maprows), c.length) if (wl.has_mappability and c.maprows is not None) else np.zeros(0, dtype=MAPRUN_DT)
+        host.append((c, pin(c.reads, READ_DT), pin(c.gc, np.int8), pin(c.dels, CNV_DT), pin(c.dups, CNV_DT), pin(runs, MAPRUN_DT),
+                     [ctx.pinned_array(len(c.dels), CALL_DT) for _ in range(2)], [ctx.pinned_array(len(c.dups), CALL_DT) for _ in range(2)],
+                     [ctx.pinned_array(1, STATS_DT) for _ in range(2)]))
+    lib, h = ctx.lib, ctx.h
+    state = {"n": 0, "pending": None}
+
+    def step_host(depth=1, geno=True, mapp=True):
+        b = state["n"] & 1; state["n"] += 1
+        for (c, pr, pg, pd, pu, prn, od, ou, st) in host:
+            ctx._ck(lib.cg_chrom_begin(h, c.index, c.length, pg.ctypes.data, len(pg), wl.mq_threshold))
+            ctx._ck(lib.cg_push_reads(h, pr.ctypes.data, len(pr)))
+            ctx._ck(lib.cg_chrom_finish(h, st[b].ctypes.data))
+            if mapp and wl.has_mappability:
+                ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data if len(prn) else None, len(prn), 1))
+            if geno:
+                if len(pd): ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od[b].ctypes.data))
+                if len(pu): ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou[b].ctypes.data))
+        if depth == 0:
+            ctx.sync(); return
+        ev = torch.cuda.Event(); ctx.join()
+        with torch.cuda.stream(ext): ev.record()
+        if state["pending"] is not None: state["pending"].synchronize()
+        state["pending"] = ev
+
+    def run_host(K, **kw):
+        for _ in range(3): step_host(**kw)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext): e0.record()
+        t0 = time.perf_counter()
+        for _ in range(K): step_host(**kw)
+        t_issue = (time.perf_counter() - t0) / K * 1e3
+        ctx.join()
+        with torch.cuda.stream(ext): e1.record()
+        ctx.sync()
+        return round(e0.elapsed_time(e1) / K, 4), round(t_issue, 4)
+    out["host_pipelined"] = run_host(args.steps)
+    out["host_sync_each"] = run_host(args.steps, depth=0)
+    out["host_no_geno"] = run_host(args.steps, geno=False, mapp=False)
+    out["host_no_map"] = run_host(args.steps, mapp=False)
+    out["h2d_MB"] = round(sum(x[1].nbytes + x[2].nbytes + x[3].nbytes + x[4].nbytes + x[5].nbytes for x in host) / 1e6, 2)
+    ctx.set_async(False); ctx.set_pointer_mode(CG_PTR_DEVICE)
     ctx.set_profiling(True); ctx.kernel_times()
     for _ in range(args.steps):
         step()
