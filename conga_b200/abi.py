@@ -65,6 +65,7 @@ SYMBOLS = {
     "cg_sr_push": (_I, [_P, _P, _Z, _P, _Z]),
     "cg_sr_rows": (_I, [_P, _P, _Z, C.POINTER(_Z), C.POINTER(C.c_uint64)]),
     "cg_sr_count": (_I, [_P, _P, _Z, _P, _Z, _P, _Z, _P, _P]),
+    "cg_gc_profile": (_I, [_P, _P, C.c_int64, _P, C.c_int32]),
     "cg_sync": (_I, [_P]),
     "cg_download_depth": (_I, [_P, _P]),
     "cg_download_prefix": (_I, [_P, _P]),
@@ -322,6 +323,18 @@ class Context:
         self._ck(self.lib.cg_sr_count(self.h, rows.ctypes.data if len(rows) else None, len(rows), dels.ctypes.data if len(dels) else None, len(dels),
                                       dups.ctypes.data if len(dups) else None, len(dups), b.ctypes.data if len(b) else None, r.ctypes.data if len(r) else None))
         return b, r
+
+    def gc_profile(self, bases, n_bases=None, out=None):
+        """SONIC's GC bytes of one chromosome from its bases (cg_gc_profile).  HOST mode: bytes / uint8
+        array in, int8 array out.  DEVICE mode: uint8 tensor in, `out` an int8 tensor of (n + 1) // 100."""
+        if isinstance(bases, (bytes, bytearray)):
+            bases = np.frombuffer(bases, dtype=np.uint8)
+        n = len(bases) if n_bases is None else int(n_bases)
+        need = (n + 1) // 100
+        if out is None:
+            out = np.empty(need, dtype=np.int8)
+        self._ck(self.lib.cg_gc_profile(self.h, _ptr(bases) if n else None, n, _ptr(out) if need else None, need))
+        return out
 
     def stats_bank(self, bank: int):
         self._ck(self.lib.cg_stats_bank(self.h, int(bank)))

@@ -90,6 +90,10 @@ cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len,
 cudaError_t cgk_sr_count(cudaStream_t s, const cg_splitrow* rows, int n_rows, const cg_cnv* dels, int n_del, const cg_cnv* dups, int n_dup,
                          int* border_rp, int* rp, int n_sms);
 cudaError_t cgk_configure_split(void);
+
+/* gc_profile.cu — SONIC's GC bytes from the bases of one chromosome (sonic/sonic_reference.c:30-106) */
+cudaError_t cgk_gc_profile(cudaStream_t s, const char* bases, long long n_bases, int8_t* out, int n_windows, int n_sms);
+cudaError_t cgk_configure_gc_profile(void);
 int         cgk_run_index_words(int32_t chrom_len);
 cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len);
 }

@@ -114,6 +114,10 @@ struct cg_ctx {
         int chrom_len = 0, mq_threshold = -1;
     } sr;
 
+    /* cg_gc_profile staging (HOST pointer mode) */
+    char* d_gc_bases = nullptr; size_t gc_bases_cap = 0;
+    int8_t* d_gc_out = nullptr; size_t gc_out_cap = 0;
+
     /* profiling */
     bool profiling = false;
     std::vector<cg_evpair> ev_live, ev_free;
@@ -242,7 +246,7 @@ cg_ctx* cg_create(int device)
         return nullptr;
     }
     if ((e = cgk_configure_depth()) != cudaSuccess || (e = cgk_configure_genotype()) != cudaSuccess
-        || (e = cgk_configure_split()) != cudaSuccess) {
+        || (e = cgk_configure_split()) != cudaSuccess || (e = cgk_configure_gc_profile()) != cudaSuccess) {
         fail(nullptr, CG_ECUDA, "kernel configuration failed (no sm_100a image for this device?): %s", cudaGetErrorString(e));
         return nullptr;
     }
@@ -316,6 +320,7 @@ void cg_destroy(cg_ctx* c)
     cudaFree(c->sr.d_ref); cudaFree(c->sr.d_keys_a); cudaFree(c->sr.d_keys_b); cudaFree(c->sr.d_vals_a); cudaFree(c->sr.d_vals_b);
     cudaFree(c->sr.d_temp); cudaFree(c->sr.d_lo); cudaFree(c->sr.d_hi); cudaFree(c->sr.d_halves); cudaFree(c->sr.d_bases);
     cudaFree(c->sr.d_rows); cudaFree(c->sr.d_n_rows); cudaFree(c->sr.d_count);
+    cudaFree(c->d_gc_bases); cudaFree(c->d_gc_out);
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
@@ -926,6 +931,45 @@ int cg_sr_count(cg_ctx* c, const cg_splitrow* rows, size_t n, const cg_cnv* dels
     if (n_del) CU(c, cudaMemcpyAsync(border_rp, d_cd, n_del * 4, cudaMemcpyDeviceToHost, r.st));
     if (n_dup) CU(c, cudaMemcpyAsync(rp, d_cu, n_dup * 4, cudaMemcpyDeviceToHost, r.st));
     CU(c, cudaStreamSynchronize(r.st));
+    return CG_OK;
+}
+
+int cg_gc_profile(cg_ctx* c, const char* bases, int64_t n_bases, int8_t* out_gc, int32_t n_windows)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (n_bases < 0 || n_bases > 0x7fffffffll) return fail(c, CG_EINVAL, "chromosome of %lld bases", (long long)n_bases);
+    const int32_t need = (int32_t)((n_bases + 1) / 100);           /* complete windows only: sonic_reference.c:95 */
+    if (n_windows < need) return fail(c, CG_EINVAL, "out_gc holds %d bytes, %d needed", n_windows, need);
+    if (need == 0) return CG_OK;
+    if (!bases || !out_gc) return fail(c, CG_EINVAL, "null argument");
+    CU(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->s_main;
+    if (c->ptr_mode == CG_PTR_DEVICE) {
+        prof_scope ps(c, st, 0, 1);
+        CU(c, cgk_gc_profile(st, bases, n_bases, out_gc, need, c->n_sms));
+        return CG_OK;
+    }
+    if ((size_t)n_bases + 16 > c->gc_bases_cap) {
+        CU(c, cudaStreamSynchronize(st));
+        cudaFree(c->d_gc_bases); c->d_gc_bases = nullptr; c->gc_bases_cap = 0;
+        const size_t cap = (size_t)n_bases + (size_t)n_bases / 8 + 4096;
+        CU(c, cudaMalloc(&c->d_gc_bases, cap));
+        c->gc_bases_cap = cap;
+    }
+    if ((size_t)need > c->gc_out_cap) {
+        CU(c, cudaStreamSynchronize(st));
+        cudaFree(c->d_gc_out); c->d_gc_out = nullptr; c->gc_out_cap = 0;
+        const size_t cap = (size_t)need + (size_t)need / 8 + 4096;
+        CU(c, cudaMalloc(&c->d_gc_out, cap));
+        c->gc_out_cap = cap;
+    }
+    CU(c, cudaMemcpyAsync(c->d_gc_bases, bases, (size_t)n_bases, cudaMemcpyHostToDevice, st));
+    {
+        prof_scope ps(c, st, 0, 1);
+        CU(c, cgk_gc_profile(st, c->d_gc_bases, n_bases, c->d_gc_out, need, c->n_sms));
+    }
+    CU(c, cudaMemcpyAsync(out_gc, c->d_gc_out, (size_t)need, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));                  /* bases / out_gc may be pageable */
     return CG_OK;
 }
 

@@ -201,6 +201,16 @@ int cg_sr_rows(cg_ctx* ctx, cg_splitrow* out, size_t cap, size_t* n_rows, uint64
 int cg_sr_count(cg_ctx* ctx, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
                 const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp);
 
+/* ---- SONIC's GC profile from the bases of a chromosome ----
+ * Replaces the character loop of sonic_write_gc_profile (sonic/sonic_reference.c:30-106) for ONE FASTA
+ * record.  bases: the record's n_bases characters with white space removed (what faidx_fetch_seq returns),
+ * either case.  out_gc: floor((n_bases + 1) / 100) bytes, byte w = the number of G/C/g/c among bases
+ * [100w - 1, 100w + 99) (window 0: [0, 99) — char_count starts at 1, :82), the value the builder writes
+ * as (char)(100.0 * gc / 100) (:96) and sonic_read_gc_profile (:139-159) hands to CONGA.  n_windows: capacity
+ * of out_gc.  Pointers follow the pointer mode; in HOST mode the call blocks, in DEVICE mode it is queued
+ * on cg_stream.  Needs no chromosome to be open. */
+int cg_gc_profile(cg_ctx* ctx, const char* bases, int64_t n_bases, int8_t* out_gc, int32_t n_windows);
+
 /* Wait for everything queued on the context (all of its streams).  In HOST pointer mode it
  * returns CG_ERANGE if a record or interval was clipped since the last report. */
 int cg_sync(cg_ctx* ctx);

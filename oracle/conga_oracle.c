@@ -25,6 +25,7 @@
  *   orc_imax                 common.c:262-268 (int max(int,int) fed doubles)
  *   orc_calculate_likelihood likelihood.c:108-169
  *   orc_compare_start_pos    common.c:199-215
+ *   orc_gc_profile           sonic/sonic_reference.c:57-104 (the SONIC builder's GC bytes of one record)
  */
 #include <math.h>
 #include <stdint.h>
@@ -388,4 +389,32 @@ void orc_sr_count(const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t 
                     && r->right_start >= dels[i].end - 100 && r->right_start <= dels[i].end + 5000) border_rp[i]++;
         }
     }
+}
+
+/* ---- SONIC's GC profile of one FASTA record ----
+ * sonic/sonic_reference.c:57-104, the body of sonic_write_gc_profile's character loop for the text between one
+ * '>' line and the next: white space skipped (:86), everything else is a base (:88), only G/C after
+ * toupper count (:87,:90), char_count starts at 1 (:82) so the first byte closes after 99 bases, a byte is
+ * written per complete window as (char)(100.0 * gc / SONIC_GC_WINDOW) (:93-99; SONIC_GC_WINDOW = 100,
+ * sonic/sonic.h).  text: n characters (line feeds allowed); out: capacity `cap`.  Returns the number of
+ * bytes the builder writes for the record (all of them stored when cap allows). */
+#include <ctype.h>
+long orc_gc_profile(const char* text, long n, signed char* out, long cap)
+{
+    int char_count = 1, gc = 0;
+    long written = 0;
+    for (long i = 0; i < n; i++) {
+        char ch = text[i];
+        if (isspace((unsigned char)ch)) continue;
+        ch = (char)toupper((unsigned char)ch);
+        char_count++;
+        if (ch == 'G' || ch == 'C') gc++;
+        if (char_count % 100 == 0) {
+            const char gc_content = (char)(100.0 * gc / 100);
+            if (written < cap) out[written] = gc_content;
+            written++;
+            gc = 0;
+        }
+    }
+    return written;
 }

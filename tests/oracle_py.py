@@ -60,6 +60,16 @@ class Oracle:
         self.lib.orc_sr_count(rows.ctypes.data, len(rows), dels.ctypes.data, len(dels), dups.ctypes.data, len(dups), b.ctypes.data, r.ctypes.data)
         return b, r
 
+    def gc_profile(self, text):
+        """sonic/sonic_reference.c:57-104 for the text of one FASTA record (line feeds allowed) -> int8 bytes"""
+        buf = np.frombuffer(bytes(text), dtype=np.uint8)
+        out = np.zeros(len(buf) // 99 + 2, dtype=np.int8)
+        self.lib.orc_gc_profile.restype = C.c_long
+        self.lib.orc_gc_profile.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_long]
+        n = self.lib.orc_gc_profile(buf.ctypes.data if len(buf) else None, len(buf), out.ctypes.data, len(out))
+        assert n <= len(out)
+        return out[:n].copy()
+
     def count_reads(self, reads, mq_threshold, chrom_len, depth=None):
         """bam_data.c:201-217 -> (int16 depth, total_read_count)"""
         assert reads.dtype == READ_DT
