@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <future>
 #include <string>
 #include <thread>
 #include <vector>
@@ -81,6 +82,17 @@ static size_t strip_space(const unsigned char* text, size_t a, size_t b, char* o
     return cnt[threads];
 }
 
+// The CUDA context (about a second to bring up) is created on a side thread from main(), behind
+// sonic_build's parsing of the .fai, the BED files and the RepeatMasker file.
+// The thread is detached and hands the context over through a future, so an exit() inside libsonic
+// (missing file, malformed RepeatMasker line) ends the program the way it ends the original.
+static std::shared_future<cg_ctx*> g_ctx_ready;
+static cg_ctx* create_context()
+{
+    const char* dev_env = getenv("CONGA_GPU_DEVICE");
+    return cg_create(dev_env ? atoi(dev_env) : 0);
+}
+
 static void die(const char* msg)
 {
     fprintf(stderr, "[sonic-b200] %s\n", msg);
@@ -105,8 +117,7 @@ extern "C" void __wrap_sonic_write_gc_profile(gzFile sonic_file, FILE* ref_file,
         if (const void* ff = memchr(text, 0xFF, size)) size = (size_t)(static_cast<const unsigned char*>(ff) - text);
     }
 
-    const char* dev_env = getenv("CONGA_GPU_DEVICE");
-    cg_ctx* ctx = cg_create(dev_env ? atoi(dev_env) : 0);
+    cg_ctx* ctx = g_ctx_ready.valid() ? g_ctx_ready.get() : create_context();
     if (!ctx) { fprintf(stderr, "[sonic-b200] %s\n", cg_last_error(nullptr)); exit(1); }
     mark("gc profile: GPU context ready");
     int threads = (int)std::thread::hardware_concurrency();
@@ -240,6 +251,11 @@ int main(int argc, char** argv)
         a_dups(dups.begin(), dups.end()), a_info(info.begin(), info.end()), a_sonic(sonic_path.begin(), sonic_path.end());
     for (auto* v : {&a_ref, &a_gaps, &a_reps, &a_dups, &a_info, &a_sonic}) v->push_back(0);
     mark("start");
+    {
+        std::packaged_task<cg_ctx*()> task(create_context);
+        g_ctx_ready = task.get_future().share();
+        std::thread(std::move(task)).detach();
+    }
     sonic_build(a_ref.data(), a_gaps.data(), a_reps.data(), a_dups.data(), have_info ? a_info.data() : nullptr, a_sonic.data());
     mark("done");
     return 0;

@@ -16,11 +16,15 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--mb", type=float, default=600.0)
 ap.add_argument("--records", type=int, default=3)
 ap.add_argument("--skip-reference", action="store_true")
+ap.add_argument("--kernel-only", action="store_true")
+ap.add_argument("--kernel-bases", type=int, default=249_250_621)
 args = ap.parse_args()
 rng = np.random.default_rng(20221124 + 9)
 tmp = tempfile.mkdtemp(prefix="sonicbench_")
 res = {"fasta_mb": args.mb, "records": args.records, "host_cores": len(os.sched_getaffinity(0))}
 try:
+    if args.kernel_only:
+        raise StopIteration
     alpha = np.frombuffer(b"ACGTacgtNN", dtype=np.uint8)
     fa = os.path.join(tmp, "ref.fa")
     total = 0
@@ -66,6 +70,8 @@ try:
     if "reference" in outs:
         res["identical_containers"] = outs["reference"] == outs["b200"]
         res["speedup_whole_program"] = round(res["reference_s"][0] / float(np.median(res["b200_s"])), 1)
+except StopIteration:
+    pass
 finally:
     shutil.rmtree(tmp, ignore_errors=True)
 
@@ -73,7 +79,7 @@ finally:
 import torch
 from conga_b200 import abi, CG_PTR_DEVICE
 dev = torch.device("cuda:0")
-n = 249_250_621
+n = args.kernel_bases
 codes = torch.randint(0, 8, (n,), device=dev, dtype=torch.uint8)
 bases = torch.take(torch.tensor(list(b"ACGTgcNn"), dtype=torch.uint8, device=dev), codes.to(torch.int64)); del codes
 out = torch.empty((n + 1) // 100, dtype=torch.int8, device=dev)
