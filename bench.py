@@ -271,7 +271,7 @@ def own_arm(args):
     ctx.set_pointer_mode(CG_PTR_HOST)
     ctx.set_async(True)
     DEPTH = max(1, env_int("BENCH_E2E_DEPTH", 2))      # samples in flight behind the one being issued
-    host = []
+    host, addr = [], []
     h2d = d2h = 0
     for c in mine:
         pr = ctx.pinned_array(len(c.reads), READ_DT); pr[:] = c.reads
@@ -288,10 +288,16 @@ def own_arm(args):
         fr = flatten_mappability(rows, c.length) if len(rows) else np.zeros(0, dtype=MAPRUN_DT)
         prn = ctx.pinned_array(len(fr), MAPRUN_DT); prn[:] = fr
         host.append((c, pr, pg, pd, pu, od, ou, st, prn))
+        # addresses taken once: ndarray.ctypes builds an object per access, microseconds that the issue loop of a
+        # 0.4 ms sample would pay thirty times
+        addr.append(dict(gc=pg.ctypes.data, n_gc=len(pg), runs=prn.ctypes.data if len(prn) else None, n_runs=len(prn),
+                         dels=pd.ctypes.data, n_del=len(pd), dups=pu.ctypes.data, n_dup=len(pu),
+                         batches=[(pr.ctypes.data + i * READ_DT.itemsize, min(1 << 22, len(pr) - i)) for i in range(0, len(pr), 1 << 22)],
+                         od=[x.ctypes.data for x in od], ou=[x.ctypes.data for x in ou], st=[x.ctypes.data for x in st],
+                         index=c.index, length=c.length))
         h2d += pr.nbytes + pg.nbytes + pd.nbytes + pu.nbytes + prn.nbytes
         d2h += od[0].nbytes + ou[0].nbytes + st[0].nbytes
-    lib, h = ctx.lib, ctx.h
-    BATCH = 1 << 22
+    lib, h, ck = ctx.lib, ctx.h, ctx._ck
 
     def step_host():
         bank = sample_no[0] & 1
@@ -299,26 +305,25 @@ def own_arm(args):
         sample_no[0] += 1
         if world > 1:
             ctx.stats_bank(bank)
-        for (c, pr, pg, pd, pu, od, ou, st, prn) in host:
-            ctx._ck(lib.cg_chrom_begin(h, c.index, c.length, pg.ctypes.data, len(pg), mq))
-            for i in range(0, len(pr), BATCH):
-                n = min(BATCH, len(pr) - i)
-                ctx._ck(lib.cg_push_reads(h, pr.ctypes.data + i * READ_DT.itemsize, n))
-            ctx._ck(lib.cg_chrom_finish(h, st[buf].ctypes.data))
+        for a in addr:
+            ck(lib.cg_chrom_begin(h, a["index"], a["length"], a["gc"], a["n_gc"], mq))
+            for p, n in a["batches"]:
+                ck(lib.cg_push_reads(h, p, n))
+            ck(lib.cg_chrom_finish(h, a["st"][buf]))
             if has_map:
-                ctx._ck(lib.cg_set_mappability_runs(h, prn.ctypes.data if len(prn) else None, len(prn), 1))
-            if len(pd):
-                ctx._ck(lib.cg_genotype(h, pd.ctypes.data, len(pd), 0, od[buf].ctypes.data))
-            if len(pu):
-                ctx._ck(lib.cg_genotype(h, pu.ctypes.data, len(pu), 1, ou[buf].ctypes.data))
+                ck(lib.cg_set_mappability_runs(h, a["runs"], a["n_runs"], 1))
+            if a["n_del"]:
+                ck(lib.cg_genotype(h, a["dels"], a["n_del"], 0, a["od"][buf]))
+            if a["n_dup"]:
+                ck(lib.cg_genotype(h, a["dups"], a["n_dup"], 1, a["ou"][buf]))
+        # cg_join orders cg_stream behind everything queued so far; the all-reduce and the event go on cg_stream
+        ctx.join()
         if world > 1:
-            ctx.join()
             with torch.cuda.stream(ext):
                 multi.allreduce_stats(tables[bank])
         # DEPTH samples in flight behind the one being issued: a sample's statistics rows and calls are complete
         # in host memory when its event has passed (a pipelined host waits there, not on the whole device)
         ev = torch.cuda.Event()
-        ctx.join()
         with torch.cuda.stream(ext):
             ev.record()
         pending.append(ev)
