@@ -355,7 +355,7 @@ def own_arm(args):
         h2d, d2h, launches = int(t[0].item()), int(t[1].item()), int(t[2].item())
 
     # roofline of the dominant kernel (fused depth pass), this rank's chromosomes
-    alg = sum(8 * len(c.reads) + 6 * c.length + (c.length + 99) // 100 for c in mine)
+    alg = sum(8 * len(c.reads) + 2 * c.length + (c.length + 99) // 100 for c in mine)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"

@@ -69,7 +69,7 @@ SYMBOLS = {
     "cg_sync": (_I, [_P]),
     "cg_download_depth": (_I, [_P, _P]),
     "cg_download_prefix": (_I, [_P, _P]),
-    "cg_device_arrays": (_I, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)]),
+    "cg_device_arrays": (_I, [_P, C.POINTER(_P), C.POINTER(_P)]),
     "cg_stats_table": (_I, [_P, C.POINTER(_P), C.POINTER(C.c_int32)]),
     "cg_stats_reset": (_I, [_P]),
     "cg_stats_bank": (_I, [_P, _I]),
@@ -283,9 +283,10 @@ class Context:
         return d
 
     def device_arrays(self):
-        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
-        self._ck(self.lib.cg_device_arrays(self.h, C.byref(a), C.byref(b), C.byref(c)))
-        return int(a.value or 0), int(b.value or 0), int(c.value or 0)
+        """Device addresses of the current chromosome's int16 depth array and float expected[101] table."""
+        a, b = C.c_void_p(), C.c_void_p()
+        self._ck(self.lib.cg_device_arrays(self.h, C.byref(a), C.byref(b)))
+        return int(a.value or 0), int(b.value or 0)
 
     def stats_table(self):
         p, n = C.c_void_p(), C.c_int32()

@@ -44,7 +44,6 @@ struct cg_pass_args {
     int32_t        n_chunks;
     int            mq_threshold;
     int16_t*       depth;             /* [n_chunks*CG_CHUNK] */
-    int32_t*       prefix;            /* [n_chunks*CG_CHUNK] inclusive int32 prefix of depth */
     uint32_t*      depth32;           /* unsorted fallback: per-position u32 counts (zero at rest) */
     unsigned int*  ctl;               /* CG_W_* control words */
     long long*     stats;             /* this chromosome's int64[204] row */
@@ -69,6 +68,7 @@ cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_rea
                            cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
                            const unsigned int* ctl, int n_sms);
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms);
+cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int n_chunks, int32_t* prefix);
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
 int         cgk_depth_pass_ctas_per_sm(void);
 int         cgk_carveout(void);                                   /* shared-memory carve-out (percent) every kernel asks for */
@@ -77,7 +77,7 @@ cudaError_t cgk_configure_genotype(void);
 
 /* genotype.cu */
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
-                         const int32_t* prefix, const int8_t* gc, const float* expected,
+                         const int16_t* depth, const cg_counts& counts, const int8_t* gc, const float* expected,
                          const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
                          int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms);
 /* split_read.cu */

@@ -11,7 +11,7 @@
  *              several-fold under a depth pass that saturates HBM, so the genotype kernels of
  *              up to CG_NSLOT chromosomes are allowed to run side by side.
  *   s_main     cg_stream(): statistics reset, and what cg_join() orders behind everything else
- * Chromosome k lives in slot k&1 (its own records, depth, prefix, GC, expected-table, count and
+ * Chromosome k lives in slot k&1 (its own records, depth, GC, expected-table, count and
  * staging buffers) and nothing of slot 0 depends on slot 1.  So the preparation kernels and the
  * ramp-up of chromosome k+1's depth pass fill the SMs that chromosome k's pass is draining from,
  * the latency-bound genotype kernels of k run underneath the bandwidth-bound pass of k+1, and the
@@ -45,7 +45,7 @@ struct cg_slot {
     cg_read* d_reads = nullptr;       size_t reads_cap = 0;
     int8_t* d_gc = nullptr;           size_t gc_cap = 0;
     int32_t* d_counts = nullptr;      size_t counts_cap = 0;      /* chunk bounds + three count levels (cg_counts) */
-    int16_t* d_depth = nullptr;       int32_t* d_prefix = nullptr; size_t pos_cap = 0;
+    int16_t* d_depth = nullptr;       size_t pos_cap = 0;
     float* d_expected = nullptr;              /* [101] (128 allocated) */
     unsigned int* d_ctl = nullptr;            /* CG_W_* control words */
     const cg_read* reads_ptr = nullptr;       /* own buffer or the caller's (DEVICE mode) */
@@ -308,7 +308,7 @@ void cg_destroy(cg_ctx* c)
     for (int i = 0; i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
         cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_counts);
-        cudaFree(s.d_depth); cudaFree(s.d_prefix); cudaFree(s.d_expected); cudaFree(s.d_ctl);
+        cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl);
         cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32);
         if (s.ev_copy) cudaEventDestroy(s.ev_copy);
         if (s.ev_pass) cudaEventDestroy(s.ev_pass);
@@ -437,10 +437,9 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (n_pos > s.pos_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
-        cudaFree(s.d_depth); cudaFree(s.d_prefix);
-        s.d_depth = nullptr; s.d_prefix = nullptr; s.pos_cap = 0;
+        cudaFree(s.d_depth);
+        s.d_depth = nullptr; s.pos_cap = 0;
         CU(c, cudaMalloc(&s.d_depth, n_pos * sizeof(int16_t)));
-        CU(c, cudaMalloc(&s.d_prefix, n_pos * sizeof(int32_t)));
         s.pos_cap = n_pos;
     }
     cudaStream_t ss = c->s_slot[si];
@@ -462,7 +461,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     for (int t = 0; t < 2; t++) {
         if (!s.geno_queued[t]) continue;
         CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno[t], 0));                  /* d_gc */
-        CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_prefix, d_expected */
+        CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_depth, d_counts, d_expected */
         /* d_runs and the staging arena are written from both genotype streams */
         CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
     }
@@ -560,7 +559,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
         a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.k = cgk_counts_layout(s.d_counts, s.n_chunks);
         a.gc = s.gc_ptr;
         a.chrom_len = s.chrom_len; a.n_chunks = s.n_chunks; a.mq_threshold = c->mq_threshold;
-        a.depth = s.d_depth; a.prefix = s.d_prefix; a.depth32 = s.d_depth32; a.ctl = s.d_ctl;
+        a.depth = s.d_depth; a.depth32 = s.d_depth32; a.ctl = s.d_ctl;
         a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
         CU(c, cgk_depth_pass(c->s_slot[c->cur], a, c->n_sms));
     }
@@ -693,11 +692,11 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
         CU(c, cudaMemcpyAsync(a_in, cnvs, n * sizeof(cg_cnv), cudaMemcpyHostToDevice, st));
         d_in = a_in;
     }
-    CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));              /* prefix + expected table of this slot */
+    CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));              /* depth, chunk sums and expected table of this slot */
     if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
     {
         prof_scope ps(c, st, 2, 1);
-        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_prefix, s.gc_ptr, s.d_expected, s.runs_ptr, s.d_run_idx, s.n_runs, s.has_map,
+        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_depth, cgk_counts_layout(s.d_counts, s.n_chunks), s.gc_ptr, s.d_expected, s.runs_ptr, s.d_run_idx, s.n_runs, s.has_map,
                            s.chrom_len, c->d_sticky, d_out, c->n_sms));
     }
     if (c->ptr_mode == CG_PTR_HOST)
@@ -729,17 +728,23 @@ int cg_download_prefix(cg_ctx* c, int32_t* out)
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_prefix before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(out, s.d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
-    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
+    cudaStream_t st = c->s_slot[c->cur];
+    /* no prefix array exists on the product path: rebuilt here from the depth array and the chunk sums */
+    int32_t* d_prefix = nullptr;
+    CU(c, cudaMalloc(&d_prefix, (size_t)s.n_chunks * CG_CHUNK * sizeof(int32_t)));
+    cudaError_t e = cgk_prefix_from_depth(st, s.d_depth, cgk_counts_layout(s.d_counts, s.n_chunks), s.n_chunks, d_prefix);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_prefix);
+    CU(c, e);
     return CG_OK;
 }
 
-int cg_device_arrays(cg_ctx* c, const int16_t** depth, const int32_t** prefix, const float** expected)
+int cg_device_arrays(cg_ctx* c, const int16_t** depth, const float** expected)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     cg_slot& s = c->slot[c->cur];
     if (depth) *depth = s.d_depth;
-    if (prefix) *prefix = s.d_prefix;
     if (expected) *expected = s.d_expected;
     return CG_OK;
 }

@@ -4,14 +4,14 @@
  * round trip):
  *   K1  read_depth[pos]++ per passing record        bam_data.c:201-217, read_distribution.c:12-18
  *   K2  chromosome sum + 101 GC-bin sums/counts     read_distribution.c:27-46, :49-73
- *   K3  int32 inclusive prefix of the depth array   (serves likelihood.c:115-121 as O(1) queries)
+ *   K3  per-CNV depth sums in O(1): NOT a prefix array — the chunk / group / super depth sums left by the
+ *       record sweep plus the depth array itself serve likelihood.c:115-121 (genotype.cu, depth_sum_before)
  *
  * Data layout in HBM (per chromosome slot, reused across chromosomes):
  *   reads      cg_read[N]            8 B records, coordinate sorted
  *   chunk_lo   int32[n_chunks+1]     first record of every 2048-position chunk
  *   cnt1/2/3   int32[...]            sum of the int16 depths per chunk / 32 chunks / 1024 chunks
  *   depth      int16[n_chunks*2048]  the reference's `short read_depth[]` (wraps mod 2^16)
- *   prefix     int32[n_chunks*2048]  P[i] = sum_{j<=i} depth[j]   (mod 2^32)
  *   stats      int64[204]            cg_chrom_stats row
  *
  * The scan carry never travels between warps.  A chunk's depth sum is the number of
@@ -24,8 +24,9 @@
  * the chunks in front of it inside the group.  The pass is embarrassingly parallel
  * over chunks: no look-back, no spinning, no block barrier, no separate scan kernel.
  *
- * Algorithmic bytes per chromosome: 8·N (records) + 2·L (depth) +
- * 4·L (prefix) + L/100 (GC bytes); the pass is HBM-write bound.
+ * Algorithmic bytes per chromosome: 8·N (records) + 2·L (depth, written once) + L/100 (GC bytes); the
+ * pass is HBM-write bound.  (SURVEY §8d's plan also wrote a 4·L int32 prefix; rounds r01a-r01g did, at
+ * 6 B per position.  It was only ever read at two positions per CNV, see genotype.cu.)
  *
  * Pass kernel shape: persistent warps pulling chunks from a counter; a warp owns 4 KB of
  * packed u16 bins in shared memory.  Per chunk: warp-aggregated shared histogram of the
@@ -337,6 +338,7 @@ k_depth_pass(const cg_pass_args a)
     const int n_reads = (int)a.n_reads;
 
     for (int i = lane; i < CG_CHUNK / 8; i += 32) my4[i] = make_uint4(0, 0, 0, 0);
+    if (lane < MAXWIN) wend[lane] = 0;
     for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0; sm.gc_cnt[i] = 0u; }
     __syncthreads();
 
@@ -349,19 +351,13 @@ k_depth_pass(const cg_pass_args a)
         unsigned nxt = 0u;
         if (lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], 1u);
         const int base = c << CG_CHUNK_SHIFT;
+        const int w0 = base / 100;                    /* first GC window overlapping the chunk */
+        /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
+         * went negative (32768 or more records on one position): counted while the records are binned.
+         * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
+        bool big = false;
 
-        /* ---- carry in front of the chunk: supers before its super, groups before its group,
-         *      chunks before it (one lane each), summed across the warp ---- */
-        int part = 0;
-        {
-            const int g = c >> LVL, s = c >> (2 * LVL);
-            const int i1 = (g << LVL) + lane, i2 = (s << LVL) + lane;
-            if (i1 < c) part += __ldg(&a.k.cnt1[i1]);
-            if (i2 < g) part += __ldg(&a.k.cnt2[i2]);
-            for (int j = lane; j < s; j += 32) part += __ldg(&a.k.cnt3[j]);
-        }
-
-        /* ---- phase A: the chunk's records -> packed shared-memory histogram ---- */
+        /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
         if (!unsorted) {
             const int lo = min(__ldg(&a.k.chunk_lo[c]), n_reads), hi = min(__ldg(&a.k.chunk_lo[c + 1]), n_reads);
             for (int i0 = lo; i0 < hi; i0 += 32) {
@@ -377,13 +373,16 @@ k_depth_pass(const cg_pass_args a)
                 int cnt;
                 const bool leader = run_leader(ok ? (int)off : -1 - lane, lane, cnt);
                 if (ok && leader) {
+                    unsigned now;                                                 /* the position's count so far, unwrapped */
                     if (off & 1u) {
-                        atomicAdd(&bins[off >> 1], (unsigned)cnt << 16);          /* bam_data.c:213; carry-out = wrap */
+                        now = (atomicAdd(&bins[off >> 1], (unsigned)cnt << 16) >> 16) + (unsigned)cnt;   /* bam_data.c:213; carry-out = wrap */
                     } else {
-                        const unsigned old = atomicAdd(&bins[off >> 1], (unsigned)cnt);
+                        now = (atomicAdd(&bins[off >> 1], (unsigned)cnt) & 0xffffu) + (unsigned)cnt;
                         /* the low half wrapped into its neighbour's count: take the carry back out */
-                        if ((old & 0xffffu) + (unsigned)cnt > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
+                        if (now > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
                     }
+                    big |= now >= 0x8000u;
+                    atomicAdd(&wend[pos / 100 - w0], cnt);
                 }
             }
         } else {
@@ -395,72 +394,89 @@ k_depth_pass(const cg_pass_args a)
                 src[2 * q] = make_uint4(0, 0, 0, 0);                              /* zero at rest */
                 src[2 * q + 1] = make_uint4(0, 0, 0, 0);
             }
+            big = true;
         }
-        const unsigned carry = (unsigned)__reduce_add_sync(FULL, part);
+        const bool wrapped = __any_sync(FULL, big);
         __syncwarp();
 
-        /* ---- eight row scans at once: lane sums, then eight independent shuffle chains ---- */
-        int ex[ROWS];                                 /* -> prefix in front of this lane's 8 positions, per row */
-        {
-            int tot[ROWS];
-#pragma unroll
-            for (int r = 0; r < ROWS; r++) {
-                const uint4 v = my4[r * 32 + lane];
-                tot[r] = add_halves(v.w, add_halves(v.z, add_halves(v.y, add_halves(v.x, 0))));
-                ex[r] = tot[r];
-            }
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-#pragma unroll
-                for (int r = 0; r < ROWS; r++) {
-                    const int o = __shfl_up_sync(FULL, ex[r], d);
-                    if (lane >= d) ex[r] += o;
-                }
-            }
-            unsigned run = carry;
-#pragma unroll
-            for (int r = 0; r < ROWS; r++) {
-                const int row_total = __shfl_sync(FULL, ex[r], 31);
-                ex[r] = (int)run + ex[r] - tot[r];
-                run += (unsigned)row_total;
-            }
-        }
-
-        /* ---- rows -> depth + prefix stores ---- */
-        const int w0 = base / 100;                    /* first GC window overlapping the chunk */
-        {
-            const int cpos = base + lane * 8;         /* this lane's first position in row 0 */
-            int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
-            char* dp = reinterpret_cast<char*>(a.depth) + (size_t)cpos * 2;
-            char* pp = reinterpret_cast<char*>(a.prefix) + (size_t)cpos * 4;
+        if (!wrapped) {
+            /* ---- rows -> depth stores: the packed bins ARE the int16 output vectors ---- */
+            char* dp = reinterpret_cast<char*>(a.depth) + ((size_t)base + lane * 8) * 2;
 #pragma unroll
             for (int r = 0; r < ROWS; r++) {
                 const uint4 v = my4[r * 32 + lane];
                 my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
-                const unsigned b = (unsigned)ex[r];
-                const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
-                const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
-                const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
-                const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
                 st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
-                st_cs_v4(pp + r * 1024, b + s0, b + s1, b + s2, b + s3);
-                st_cs_v4(pp + r * 1024 + 16, b + s4, b + s5, b + s6, b + s7);
-                /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
-                if (wm >= 92) {
-                    const int k = 99 - wm;
-                    const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
-                                 : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
-                    wend[wq - w0] = (int)(b - carry) + sk;
-                }
-                if (r == ROWS - 1 && lane == 31)                      /* the chunk's last position closes a partial window */
-                    wend[(base + CG_CHUNK - 1) / 100 - w0] = (int)(b - carry) + s7;
-                wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
-                if (wm >= 100) { wm -= 100; wq++; }
             }
+        } else {
+            if (lane < MAXWIN) wend[lane] = 0;                        /* the scan below writes window-END sums */
+            __syncwarp();
+            /* ---- eight row scans at once: lane sums, then eight independent shuffle chains ---- */
+            int ex[ROWS];                                 /* -> prefix in front of this lane's 8 positions, per row */
+            {
+                int tot[ROWS];
+    #pragma unroll
+                for (int r = 0; r < ROWS; r++) {
+                    const uint4 v = my4[r * 32 + lane];
+                    tot[r] = add_halves(v.w, add_halves(v.z, add_halves(v.y, add_halves(v.x, 0))));
+                    ex[r] = tot[r];
+                }
+    #pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+    #pragma unroll
+                    for (int r = 0; r < ROWS; r++) {
+                        const int o = __shfl_up_sync(FULL, ex[r], d);
+                        if (lane >= d) ex[r] += o;
+                    }
+                }
+                int run = 0;                                /* sums are relative to the chunk's first position */
+    #pragma unroll
+                for (int r = 0; r < ROWS; r++) {
+                    const int row_total = __shfl_sync(FULL, ex[r], 31);
+                    ex[r] = run + ex[r] - tot[r];
+                    run += row_total;
+                }
+            }
+
+            /* ---- rows -> depth stores, window-end sums ---- */
+            {
+                const int cpos = base + lane * 8;         /* this lane's first position in row 0 */
+                int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
+                char* dp = reinterpret_cast<char*>(a.depth) + (size_t)cpos * 2;
+    #pragma unroll
+                for (int r = 0; r < ROWS; r++) {
+                    const uint4 v = my4[r * 32 + lane];
+                    my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
+                    const int b = ex[r];
+                    const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
+                    const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
+                    const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
+                    const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
+                    st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
+                    /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
+                    if (wm >= 92) {
+                        const int k = 99 - wm;
+                        const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
+                                     : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
+                        wend[wq - w0] = b + sk;
+                    }
+                    if (r == ROWS - 1 && lane == 31)                      /* the chunk's last position closes a partial window */
+                        wend[(base + CG_CHUNK - 1) / 100 - w0] = b + s7;
+                    wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
+                    if (wm >= 100) { wm -= 100; wq++; }
+                }
+            }
+            __syncwarp();
+
+            /* window-end sums -> per-window sums */
+            const int nw = (base + CG_CHUNK - 1) / 100 - w0 + 1;
+            const int d = lane < nw ? wend[lane] - (lane ? wend[lane - 1] : 0) : 0;
+            __syncwarp();
+            if (lane < nw) wend[lane] = d;
         }
         __syncwarp();
 
-        /* ---- GC-bin sums from window-end prefixes (read_distribution.c:63-73) ---- */
+        /* ---- GC-bin sums from the per-window depth sums (read_distribution.c:63-73) ---- */
         {
             const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
             const int chunk_end = min(base + CG_CHUNK, a.chrom_len);
@@ -470,11 +486,12 @@ k_depth_pass(const cg_pass_args a)
                 if (we > ws) {
                     int bin = (int)a.gc[w];                           /* sonic_interval.c:263-272 */
                     if ((unsigned)bin > 100u) bin = 0;
-                    const int sum = wend[lane] - (lane ? wend[lane - 1] : 0);
+                    const int sum = wend[lane];
                     if (sum) atomicAdd(&sm.gc_rd[bin], sum);
                     atomicAdd(&sm.gc_cnt[bin], (unsigned)(we - ws));
                 }
             }
+            if (lane < MAXWIN) wend[lane] = 0;                        /* clean for the next chunk */
         }
         __syncwarp();
         c = (int)__shfl_sync(FULL, nxt, 0);
@@ -538,6 +555,48 @@ cudaError_t cgk_configure_depth(void)
     if ((e = cudaFuncSetAttribute(k_rare_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_rare_totals, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     return cudaSuccess;
+}
+
+/* Diagnostic (cg_download_prefix): the int32 inclusive prefix of the depth array, P[i] = sum of depth[0..i]
+ * mod 2^32, rebuilt from the depth array and the chunk / group / super sums.  One warp per chunk. */
+__global__ void __launch_bounds__(256)
+k_prefix_from_depth(const int16_t* __restrict__ depth, cg_counts k, int n_chunks, int32_t* __restrict__ prefix)
+{
+    const int lane = threadIdx.x & 31;
+    const int n_warps = gridDim.x * (blockDim.x >> 5);
+    for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < n_chunks; c += n_warps) {
+        int part = 0;
+        const int g = c >> LVL, sp = c >> (2 * LVL);
+        const int i1 = (g << LVL) + lane, i2 = (sp << LVL) + lane;
+        if (i1 < c) part += k.cnt1[i1];
+        if (i2 < g) part += k.cnt2[i2];
+        for (int j = lane; j < sp; j += 32) part += k.cnt3[j];
+        int run = __reduce_add_sync(FULL, part);
+        const size_t base = (size_t)c << CG_CHUNK_SHIFT;
+        const uint4* src = reinterpret_cast<const uint4*>(depth + base);
+        for (int r = 0; r < ROWS; r++) {
+            const uint4 v = src[r * 32 + lane];
+            const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
+            const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
+            const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
+            const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
+            const int incl = warp_incl_scan(s7, lane);
+            const int b = run + incl - s7;
+            int4* dst = reinterpret_cast<int4*>(prefix + base + (size_t)(r * 32 + lane) * 8);
+            dst[0] = make_int4(b + s0, b + s1, b + s2, b + s3);
+            dst[1] = make_int4(b + s4, b + s5, b + s6, b + s7);
+            run += __shfl_sync(FULL, incl, 31);
+        }
+    }
+}
+
+cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int n_chunks, int32_t* prefix)
+{
+    if (n_chunks <= 0) return cudaSuccess;
+    int blocks = (n_chunks + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_prefix_from_depth<<<blocks, 256, 0, s>>>(depth, k, n_chunks, prefix);
+    return cudaGetLastError();
 }
 
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)

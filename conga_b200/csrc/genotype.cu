@@ -5,8 +5,11 @@
  *
  * The reference walks every base of every CNV with three accumulators
  * (likelihood.c:115-124).  Here:
- *   observed_rd  (int)    = P[end-1] - P[start-1] from the int32 prefix the depth
- *                           pass wrote: two loads per CNV.
+ *   observed_rd  (int)    = D(end) - D(start), D(p) = sum of depth[0, p): the per-chunk /
+ *                           per-group / per-super depth sums the record sweep left behind
+ *                           (cg_counts) give D at the chunk boundary in three short loads,
+ *                           the warp sums the < 2048 int16 depths from there to p.  No
+ *                           per-position prefix array exists.
  *   expected_rd  (float)  = the SAME ordered fp32 sum, evaluated window by window:
  *                           inside one 100-position GC window the addend is constant,
  *                           and k repeated fp32 additions of one value are replayed
@@ -283,7 +286,7 @@ __device__ __forceinline__ cg_cnv make_cnv(int a, int b) { cg_cnv v; v.start = a
  * The work per CNV is irregular (a few windows to several thousand) and the exact fp32 chain
  * has a serial, branchy ramp-up: while E is small every addition changes its exponent.  A warp
  * therefore owns G consecutive CNVs, one per lane, and works in four phases:
- *   0  lane = CNV: record, the two prefix words -> observed_rd
+ *   0  lane = CNV: record; warp = one CNV at a time: observed_rd from the chunk sums and the depth array
  *   1  lane = CNV: the first RAMP windows of the expected chain and the whole mappability chain,
  *      literally / run by run (add_run_f32, add_run_f64_fast): every lane busy with its own CNV
  *   2  warp = one CNV at a time, for the CNVs longer than RAMP windows: each lane takes 4
@@ -324,9 +327,45 @@ cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int
     return cudaGetLastError();
 }
 
+/* D(p) = sum of depth[0, p) mod 2^32, by one warp (every lane gets the result).  Chunk boundary: the supers
+ * in front of p's super, the groups in front of its group, the chunks in front of its chunk (one lane each,
+ * the carry of the depth pass's first version).  Inside the chunk: 16-byte loads of eight int16 depths. */
+__device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ depth, const cg_counts& k, int p, int lane)
+{
+    const int c = p >> CG_CHUNK_SHIFT;
+    const int g = c >> 5, sp = c >> 10;
+    int part = 0;
+    {
+        const int i1 = (g << 5) + lane, i2 = (sp << 5) + lane;
+        if (i1 < c) part += __ldg(&k.cnt1[i1]);
+        if (i2 < g) part += __ldg(&k.cnt2[i2]);
+        for (int j = lane; j < sp; j += 32) part += __ldg(&k.cnt3[j]);
+    }
+    const int base = c << CG_CHUNK_SHIFT;
+    const uint4* row = reinterpret_cast<const uint4*>(depth + base);
+    for (int q0 = 0; base + q0 * 8 < p; q0 += 32) {
+        const int q = q0 + lane, first = base + q * 8;                 /* this lane's eight positions */
+        if (first < p) {
+            uint4 v = __ldg(row + q);
+            const int keep = p - first;                                /* 1..8 of them lie in front of p */
+            if (keep < 8) {
+                unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int left = keep - 2 * j;                     /* halves of word j in front of p */
+                    w[j] = left >= 2 ? w[j] : left == 1 ? (w[j] & 0xffffu) : 0u;
+                }
+                v = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            part = __dp2a_lo((int)v.w, 0x0101, __dp2a_lo((int)v.z, 0x0101, __dp2a_lo((int)v.y, 0x0101, __dp2a_lo((int)v.x, 0x0101, part))));
+        }
+    }
+    return __reduce_add_sync(FULL, part);
+}
+
 template <int G>
 __global__ void __launch_bounds__(GENO_WARPS * 32)
-k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __restrict__ prefix,
+k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int16_t* __restrict__ depth, const cg_counts counts,
            const int8_t* __restrict__ gc, const float* __restrict__ expected,
            const cg_maprun* __restrict__ runs, const int32_t* __restrict__ run_idx, int n_runs, int has_map,
            int32_t chrom_len, unsigned int* flags, cg_call* out)
@@ -349,10 +388,12 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
         int s = v.start, e = v.end;
         if (valid && (s < 0 || e > chrom_len)) { atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
         const bool any = valid && e > s;
-        int p_hi = 0, p_lo = 0;
-        if (any) {
-            p_hi = __ldg(&prefix[e - 1]);
-            if (s > 0) p_lo = __ldg(&prefix[s - 1]);
+        int obs = 0;                                    /* likelihood.c:120, the warp sums for one CNV at a time */
+        for (unsigned todo = __ballot_sync(FULL, any); todo; todo &= todo - 1) {
+            const int L = __ffs(todo) - 1;
+            const int cs = __shfl_sync(FULL, s, L), ce = __shfl_sync(FULL, e, L);
+            const int d = depth_sum_before(depth, counts, ce, lane) - depth_sum_before(depth, counts, cs, lane);
+            if (lane == L) obs = d;
         }
         const int w_last = any ? (e - 1) / 100 : -1;
         int w = any ? s / 100 : 0;                      /* next window of the expected chain */
@@ -511,7 +552,6 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int32_t* __
 
         /* ---- phase 3: observed_rd, likelihoods, c-score, copy number; lane = CNV ---- */
         if (valid) {
-            const int obs = p_hi - p_lo;                                           /* likelihood.c:120 */
             const double k = (double)obs;
             const double lg = lgamma((double)(obs + 1));                           /* likelihood.c:104 */
             double lam_homo = is_dup ? (double)__fmul_rn(2.0f, E) : 0.0;           /* :133 / :155 (float product) */
@@ -558,7 +598,7 @@ cudaError_t cgk_configure_genotype(void)
 }
 
 cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
-                         const int32_t* prefix, const int8_t* gc, const float* expected,
+                         const int16_t* depth, const cg_counts& counts, const int8_t* gc, const float* expected,
                          const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
                          int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms)
 {
@@ -566,7 +606,7 @@ cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
     const int n_groups = (n + GENO_G - 1) / GENO_G;
     int blocks = (n_groups + GENO_WARPS - 1) / GENO_WARPS;
     if (blocks > n_sms * 8) blocks = n_sms * 8;
-    k_genotype<GENO_G><<<blocks, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, prefix, gc, expected, runs, run_idx, n_runs,
+    k_genotype<GENO_G><<<blocks, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, depth, counts, gc, expected, runs, run_idx, n_runs,
                                                           has_map, chrom_len, flags, out);
     return cudaGetLastError();
 }

@@ -57,8 +57,9 @@ class Workload:
         return int(sum(c.length for c in self.chroms))
 
     def algorithmic_bytes_depth_pass(self) -> int:
-        """8·N + 2·L + 4·L + ceil(L/100) summed over chromosomes (fused K1+K2+K3)."""
-        return int(sum(8 * len(c.reads) + 6 * c.length + (c.length + 99) // 100 for c in self.chroms))
+        """8·N + 2·L + ceil(L/100) summed over chromosomes: records read, int16 depth written once, GC bytes
+        (SURVEY §8d's fused figure less the 4·L prefix array, which is not materialised)."""
+        return int(sum(8 * len(c.reads) + 2 * c.length + (c.length + 99) // 100 for c in self.chroms))
 
 
 def make_gc(length: int, rng: np.random.Generator, n_frac: float = 0.0) -> np.ndarray:

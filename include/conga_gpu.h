@@ -126,7 +126,7 @@ int cg_chrom_begin(cg_ctx* ctx, int chr_index, int32_t chrom_len,
 int cg_push_reads(cg_ctx* ctx, const cg_read* reads, size_t n);
 
 /* Close the chromosome: depth (int16, wraps mod 2^16 like the reference's `short`),
- * int32 inclusive prefix, chromosome sum and the 101 GC-bin sums/counts, and the
+ * chromosome sum and the 101 GC-bin sums/counts, and the
  * expected_read_depth[101] table computed with the reference's exact expression
  * (read_distribution.c:75-83).  `out` may be NULL. */
 int cg_chrom_finish(cg_ctx* ctx, cg_chrom_stats* out);
@@ -221,10 +221,12 @@ int cg_join(cg_ctx* ctx);
 
 /* Parity/diagnostic downloads of the current chromosome (HOST pointers always). */
 int cg_download_depth(cg_ctx* ctx, int16_t* out /* chrom_len */);
+/* P[i] = sum of depth[0..i] mod 2^32.  No such array exists on the product path (cg_genotype sums a CNV
+ * from per-2048-position depth sums and the depth array); this call rebuilds it on the device for tests. */
 int cg_download_prefix(cg_ctx* ctx, int32_t* out /* chrom_len */);
 /* Device addresses of the current chromosome's arrays (valid until the next
- * cg_chrom_begin): int16 depth, int32 inclusive prefix, float expected[101]. */
-int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const int32_t** prefix, const float** expected);
+ * cg_chrom_begin): int16 depth, float expected[101]. */
+int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const float** expected);
 
 /* Device address of the int64[n_rows][204] statistics table, one row per
  * chr_index seen since cg_stats_reset (layout = cg_chrom_stats).  A multi-GPU
@@ -244,7 +246,7 @@ int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
  * around every launch group while profiling is on.  cg_kernel_times waits for the
  * stream, returns the milliseconds and launch counts accumulated since the last
  * call, and clears them.  Slots: 0 = chromosome init + batch marking + rare paths
- * + tile scan, 1 = the fused depth/GC/prefix pass (it also derives the expected table),
+ * + tile scan, 1 = the fused depth/GC pass (it also derives the expected table),
  * 2 = CNV sums + likelihoods (runs on the genotype stream, overlapping slot 1 of the next
  * chromosome), 3 = the split-read kernels (k-mer index, re-mapping, overlap counts). */
 #define CG_NSLOTS 4

@@ -12,7 +12,7 @@ wl = synth.config2()
 dev = torch.device("cuda:0")
 to_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
 res = [(c, to_dev(c.gc), to_dev(c.reads)) for c in wl.chroms]
-alg = sum(8 * len(c.reads) + 6 * c.length + (c.length + 99) // 100 for c in wl.chroms)
+alg = sum(8 * len(c.reads) + 2 * c.length + (c.length + 99) // 100 for c in wl.chroms)
 for path in libs:
     abi._lib = abi.load_library(path)
     ctx = abi.Context(0)

@@ -30,7 +30,7 @@ for c in mine:
                     runs=to_dev(runs) if runs is not None and len(runs) else None, n_runs=0 if runs is None else len(runs),
                     od=torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev),
                     ou=torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)))
-alg = sum(8 * len(c.reads) + 6 * c.length + (c.length + 99) // 100 for c in mine)
+alg = sum(8 * len(c.reads) + 2 * c.length + (c.length + 99) // 100 for c in mine)
 n_reads = sum(len(c.reads) for c in mine)
 
 for path in (args.libs or [abi.LIB_PATH]):

@@ -334,8 +334,8 @@ def test_full_size_chromosome_properties(ctx):
     assert np.array_equal(calls["observed"], want)
     whole = ctx.genotype(np.array([(0, L)], dtype=CNV_DT), True)
     assert int(whole["observed"][0]) == n_pass
-    d_ptr, p_ptr, _ = ctx.device_arrays()
-    assert d_ptr and p_ptr
+    d_ptr, e_ptr = ctx.device_arrays()
+    assert d_ptr and e_ptr
     depth = ctx.download_depth()
     assert int(depth.astype(np.int64).sum()) == n_pass
     idx = rng.integers(0, L, size=1000)
