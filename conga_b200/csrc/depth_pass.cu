@@ -307,6 +307,9 @@ struct __align__(16) pass_smem {
  * 3 -> 5.6, 4 -> 5.2, 5 -> 5.1 TB/s: more resident warps mean more concurrent write streams and
  * worse HBM efficiency; the rest of the SM stays free for the genotype and preparation kernels. */
 #define PASS_GRID_CTAS_PER_SM 2
+#ifndef PASS_BATCH
+#define PASS_BATCH 4                  /* chunks per visit to the work counter */
+#endif
 
 /* expected_read_depth[101], read_distribution.c:75-83:
  *   expected[0] = 0; expected[i] = (float)rd_per_gc[i] / window_per_gc[i]; NaN / Inf -> 0.
@@ -342,14 +345,17 @@ k_depth_pass(const cg_pass_args a)
     for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0; sm.gc_cnt[i] = 0u; }
     __syncthreads();
 
+    /* Chunks are handed out PASS_BATCH at a time from one counter: at 2 B per position the pass needs
+     * 1.5 G chunks/s to saturate HBM, more than one address takes atomics (measured 0.9 G/s, r01g) */
     unsigned cur = 0u;
-    if (lane == 0) cur = atomicAdd(&a.ctl[CG_W_TILE], 1u);
+    if (lane == 0) cur = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
     int c = (int)__shfl_sync(FULL, cur, 0);
+    int left = PASS_BATCH;                            /* chunks of the current batch not yet done, this one included */
+    unsigned nxt = 0u;
 
     while (c < a.n_chunks) {
-        /* the chunk after this one: asked for now, looked at after the stores */
-        unsigned nxt = 0u;
-        if (lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], 1u);
+        /* the batch after this one: asked for at the batch's first chunk, looked at after its last */
+        if (left == PASS_BATCH && lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
         const int base = c << CG_CHUNK_SHIFT;
         const int w0 = base / 100;                    /* first GC window overlapping the chunk */
         /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
@@ -494,7 +500,8 @@ k_depth_pass(const cg_pass_args a)
             if (lane < MAXWIN) wend[lane] = 0;                        /* clean for the next chunk */
         }
         __syncwarp();
-        c = (int)__shfl_sync(FULL, nxt, 0);
+        if (--left) c++;
+        else { c = (int)__shfl_sync(FULL, nxt, 0); left = PASS_BATCH; }
     }
 
     /* ---- CTA epilogue: flush the per-CTA statistics; the last CTA derives the table ---- */
