@@ -551,7 +551,8 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
          * streams and cost HBM efficiency (measured).  Everything else of this chromosome — init,
          * batch marking, copies — has already overlapped the previous chromosome's pass. */
         cg_slot& o = c->slot[(c->cur + CG_NSLOT - 1) % CG_NSLOT];
-        if (o.used) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
+        static const bool overlap = getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP"));   /* tuning only */
+        if (o.used && !overlap) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
     }
     {
         prof_scope ps(c, c->s_slot[c->cur], 1, 1);

@@ -352,20 +352,31 @@ k_depth_pass(const cg_pass_args a)
     int c = (int)__shfl_sync(FULL, cur, 0);
     int left = PASS_BATCH;                            /* chunks of the current batch not yet done, this one included */
     unsigned nxt = 0u;
+    int blo = 0;
 
     while (c < a.n_chunks) {
         /* the batch after this one: asked for at the batch's first chunk, looked at after its last */
-        if (left == PASS_BATCH && lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
+        if (left == PASS_BATCH) {
+            if (lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
+            /* record bounds of the whole batch in one coalesced load: lane j holds chunk_lo[c + j] */
+            blo = lane <= PASS_BATCH ? min(__ldg(&a.k.chunk_lo[min(c + lane, a.n_chunks)]), n_reads) : 0;
+        }
         const int base = c << CG_CHUNK_SHIFT;
         const int w0 = base / 100;                    /* first GC window overlapping the chunk */
         /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
          * went negative (32768 or more records on one position): counted while the records are binned.
          * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
         bool big = false;
+        /* the GC byte of this lane's window: asked for now, used after the stores */
+        const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
+        const int chunk_end = min(base + CG_CHUNK, a.chrom_len);
+        const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(chunk_end, 100 * (w0 + lane) + 100);
+        int gbin = 0;
+        if (lane < nwin && gw_e > gw_s) gbin = (int)a.gc[w0 + lane];              /* sonic_interval.c:263-272 */
 
         /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
         if (!unsorted) {
-            const int lo = min(__ldg(&a.k.chunk_lo[c]), n_reads), hi = min(__ldg(&a.k.chunk_lo[c + 1]), n_reads);
+            const int lo = __shfl_sync(FULL, blo, PASS_BATCH - left), hi = __shfl_sync(FULL, blo, PASS_BATCH - left + 1);
             for (int i0 = lo; i0 < hi; i0 += 32) {
                 const int i = i0 + lane;
                 const bool in = i < hi;
@@ -483,22 +494,13 @@ k_depth_pass(const cg_pass_args a)
         __syncwarp();
 
         /* ---- GC-bin sums from the per-window depth sums (read_distribution.c:63-73) ---- */
-        {
-            const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
-            const int chunk_end = min(base + CG_CHUNK, a.chrom_len);
-            if (lane < nwin) {
-                const int w = w0 + lane;
-                const int ws = max(base, 100 * w), we = min(chunk_end, 100 * w + 100);
-                if (we > ws) {
-                    int bin = (int)a.gc[w];                           /* sonic_interval.c:263-272 */
-                    if ((unsigned)bin > 100u) bin = 0;
-                    const int sum = wend[lane];
-                    if (sum) atomicAdd(&sm.gc_rd[bin], sum);
-                    atomicAdd(&sm.gc_cnt[bin], (unsigned)(we - ws));
-                }
-            }
-            if (lane < MAXWIN) wend[lane] = 0;                        /* clean for the next chunk */
+        if (lane < nwin && gw_e > gw_s) {
+            const int bin = (unsigned)gbin > 100u ? 0 : gbin;
+            const int sum = wend[lane];
+            if (sum) atomicAdd(&sm.gc_rd[bin], sum);
+            atomicAdd(&sm.gc_cnt[bin], (unsigned)(gw_e - gw_s));
         }
+        if (lane < MAXWIN) wend[lane] = 0;                            /* clean for the next chunk */
         __syncwarp();
         if (--left) c++;
         else { c = (int)__shfl_sync(FULL, nxt, 0); left = PASS_BATCH; }
