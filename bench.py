@@ -22,6 +22,7 @@ import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 import numpy as np
@@ -154,8 +155,8 @@ def own_arm(args):
     import torch
     import torch.distributed as dist
     from conga_b200 import multi
-    from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CNV_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, Context,
-                            flatten_mappability, synth)
+    from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CHROM_JOB_DT, CNV_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, Context,
+                            chrom_job, flatten_mappability, synth)
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     # stdout carries the JSON line and nothing else: libraries that print there (NCCL's version banner)
@@ -212,20 +213,18 @@ def own_arm(args):
                         out_dup=torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)))
     torch.cuda.synchronize()
 
+    # one cg_run_chromosomes per sample = cg_chrom_begin / cg_push_reads / cg_chrom_finish / cg_set_mappability_runs /
+    # cg_genotype x2 for each chromosome, in one foreign call
+    jobs_dev = np.concatenate([chrom_job(r["c"].index, r["c"].length, r["gc"], len(r["c"].gc), mq, r["reads"], len(r["c"].reads),
+                                         r["runs"], r["n_runs"], has_map, r["dels"], len(r["c"].dels), r["out_del"],
+                                         r["dups"], len(r["c"].dups), r["out_dup"], None) for r in res]) if res else np.zeros(0, dtype=CHROM_JOB_DT)
+
     def step_device():
         bank = sample_no[0] & 1
         sample_no[0] += 1
         if world > 1:
             ctx.stats_bank(bank)              # cleared on the device behind the all-reduce that last read it
-        for r in res:
-            c = r["c"]
-            ctx.chrom_begin(c.index, c.length, r["gc"], mq, n_windows=len(c.gc))
-            ctx.push_reads(r["reads"], len(c.reads))
-            ctx.chrom_finish(None)
-            if has_map:
-                ctx.set_mappability_runs(r["runs"], r["n_runs"], True)
-            ctx.genotype(r["dels"], False, r["out_del"], n=len(c.dels))
-            ctx.genotype(r["dups"], True, r["out_dup"], n=len(c.dups))
+        ctx.run_chromosomes(jobs_dev)
         if world > 1:
             ctx.join()                        # main stream now waits for every stream of the context
             with torch.cuda.stream(ext):
@@ -268,83 +267,127 @@ def own_arm(args):
     # ---- leg 2: end to end through the C-ABI from pinned host buffers (CG_PTR_HOST) -------
     # A pipelined host: page-locked buffers, asynchronous calls, one cg_sync per step — that is when the
     # results (statistics rows, genotype calls) are valid on the host.
-    ctx.set_pointer_mode(CG_PTR_HOST)
-    ctx.set_async(True)
-    DEPTH = max(1, env_int("BENCH_E2E_DEPTH", 2))      # samples in flight behind the one being issued
-    host, addr = [], []
+    DEPTH = max(1, env_int("BENCH_E2E_DEPTH", 2))      # samples in flight behind the one being issued, per lane
+    # Issuing a sample costs the host about as much time as the device needs to run it, so a single-GPU host
+    # issues from LANES threads, one context each (a context is driven by one thread at a time; the foreign call
+    # releases the interpreter lock).  Multi-GPU ranks keep one lane: their collective must be issued in one
+    # order on every rank.
+    LANES = max(1, env_int("BENCH_E2E_LANES", 2)) if world == 1 else 1
+    lanes = [dict(ctx=ctx, ext=ext)]
+    for _ in range(LANES - 1):
+        cx = Context(local)
+        lanes.append(dict(ctx=cx, ext=torch.cuda.ExternalStream(cx.stream, device=dev)))
+    for ln in lanes:
+        ln["ctx"].set_pointer_mode(CG_PTR_HOST)
+        ln["ctx"].set_async(True)
+    # inputs: one page-locked copy shared by the lanes; results: DEPTH + 1 buffers per lane, so that sample k's
+    # calls stay intact while the next DEPTH samples of the lane are being issued
+    inputs = []
     h2d = d2h = 0
     for c in mine:
         pr = ctx.pinned_array(len(c.reads), READ_DT); pr[:] = c.reads
         pg = ctx.pinned_array(len(c.gc), np.int8); pg[:] = c.gc
         pd = ctx.pinned_array(len(c.dels), CNV_DT); pd[:] = c.dels
         pu = ctx.pinned_array(len(c.dups), CNV_DT); pu[:] = c.dups
-        # results are multi-buffered: sample k's calls stay intact while the next DEPTH samples are being issued
-        od = [ctx.pinned_array(len(c.dels), CALL_DT) for _ in range(DEPTH + 1)]
-        ou = [ctx.pinned_array(len(c.dups), CALL_DT) for _ in range(DEPTH + 1)]
-        st = [ctx.pinned_array(1, STATS_DT) for _ in range(DEPTH + 1)]
         rows = np.ascontiguousarray(c.maprows) if (has_map and c.maprows is not None) else np.zeros(0, dtype=MAPIV_DT)
         # the track is flattened once per BED file (input parsing, like the reference's per-chromosome
         # re-parse of the BED, svs.c:329-374); its upload is part of every step
         fr = flatten_mappability(rows, c.length) if len(rows) else np.zeros(0, dtype=MAPRUN_DT)
         prn = ctx.pinned_array(len(fr), MAPRUN_DT); prn[:] = fr
-        host.append((c, pr, pg, pd, pu, od, ou, st, prn))
-        # addresses taken once: ndarray.ctypes builds an object per access, microseconds that the issue loop of a
-        # 0.4 ms sample would pay thirty times
-        addr.append(dict(gc=pg.ctypes.data, n_gc=len(pg), runs=prn.ctypes.data if len(prn) else None, n_runs=len(prn),
-                         dels=pd.ctypes.data, n_del=len(pd), dups=pu.ctypes.data, n_dup=len(pu),
-                         batches=[(pr.ctypes.data + i * READ_DT.itemsize, min(1 << 22, len(pr) - i)) for i in range(0, len(pr), 1 << 22)],
-                         od=[x.ctypes.data for x in od], ou=[x.ctypes.data for x in ou], st=[x.ctypes.data for x in st],
-                         index=c.index, length=c.length))
+        inputs.append((c, pr, pg, pd, pu, prn))
         h2d += pr.nbytes + pg.nbytes + pd.nbytes + pu.nbytes + prn.nbytes
-        d2h += od[0].nbytes + ou[0].nbytes + st[0].nbytes
-    lib, h, ck = ctx.lib, ctx.h, ctx._ck
+        d2h += len(c.dels) * CALL_DT.itemsize + len(c.dups) * CALL_DT.itemsize + STATS_DT.itemsize
+    for ln in lanes:
+        cx = ln["ctx"]
+        ln["out"] = [[(cx.pinned_array(len(c.dels), CALL_DT), cx.pinned_array(len(c.dups), CALL_DT), cx.pinned_array(1, STATS_DT))
+                      for (c, *_rest) in inputs] for _ in range(DEPTH + 1)]
+        ln["jobs"] = [np.concatenate([chrom_job(c.index, c.length, pg, len(pg), mq, pr, len(pr), prn, len(prn), has_map,
+                                                pd, len(pd), od, pu, len(pu), ou, st)
+                                      for (c, pr, pg, pd, pu, prn), (od, ou, st) in zip(inputs, outs)]) if inputs else np.zeros(0, dtype=CHROM_JOB_DT)
+                      for outs in ln["out"]]
+        ln["pending"], ln["n"] = [], 0
 
-    def step_host():
-        bank = sample_no[0] & 1
-        buf = sample_no[0] % (DEPTH + 1)
-        sample_no[0] += 1
+    def lane_step(ln):
+        cx = ln["ctx"]
+        buf = ln["n"] % (DEPTH + 1)
+        ln["n"] += 1
         if world > 1:
-            ctx.stats_bank(bank)
-        for a in addr:
-            ck(lib.cg_chrom_begin(h, a["index"], a["length"], a["gc"], a["n_gc"], mq))
-            for p, n in a["batches"]:
-                ck(lib.cg_push_reads(h, p, n))
-            ck(lib.cg_chrom_finish(h, a["st"][buf]))
-            if has_map:
-                ck(lib.cg_set_mappability_runs(h, a["runs"], a["n_runs"], 1))
-            if a["n_del"]:
-                ck(lib.cg_genotype(h, a["dels"], a["n_del"], 0, a["od"][buf]))
-            if a["n_dup"]:
-                ck(lib.cg_genotype(h, a["dups"], a["n_dup"], 1, a["ou"][buf]))
+            bank = sample_no[0] & 1
+            sample_no[0] += 1
+            cx.stats_bank(bank)
+        cx.run_chromosomes(ln["jobs"][buf])
         # cg_join orders cg_stream behind everything queued so far; the all-reduce and the event go on cg_stream
-        ctx.join()
+        cx.join()
         if world > 1:
-            with torch.cuda.stream(ext):
+            with torch.cuda.stream(ln["ext"]):
                 multi.allreduce_stats(tables[bank])
         # DEPTH samples in flight behind the one being issued: a sample's statistics rows and calls are complete
         # in host memory when its event has passed (a pipelined host waits there, not on the whole device)
         ev = torch.cuda.Event()
-        with torch.cuda.stream(ext):
+        with torch.cuda.stream(ln["ext"]):
             ev.record()
-        pending.append(ev)
-        if len(pending) > DEPTH:
-            pending.pop(0).synchronize()
+        ln["pending"].append(ev)
+        if len(ln["pending"]) > DEPTH:
+            ln["pending"].pop(0).synchronize()
 
-    pending = []
-    for _ in range(max(1, min(args.warmup, 2))):
-        step_host()
-    ms_e2e = timed(step_host, args.steps)     # timed() ends with cg_sync: the last sample is complete as well
+    def run_lanes(k):
+        """k samples, dealt round-robin to the lanes; returns when every one of them has been issued."""
+        if len(lanes) == 1:
+            for _ in range(k):
+                lane_step(lanes[0])
+            return
+        def work(ln, n):
+            torch.cuda.set_device(local)
+            for _ in range(n):
+                lane_step(ln)
+        ts = [threading.Thread(target=work, args=(ln, (k + len(lanes) - 1 - i) // len(lanes))) for i, ln in enumerate(lanes)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+
+    def timed_e2e(k):
+        barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext):
+            e0.record()
+        for ln in lanes[1:]:
+            ln["ext"].wait_event(e0)          # no lane starts before the clock does
+        run_lanes(k)
+        for ln in lanes[1:]:                  # ... and the clock stops behind the last sample of every lane
+            ln["ctx"].join()
+            done = torch.cuda.Event()
+            with torch.cuda.stream(ln["ext"]):
+                done.record()
+            ext.wait_event(done)
+        ctx.join()
+        with torch.cuda.stream(ext):
+            e1.record()
+        for ln in lanes:
+            ln["ctx"].sync()
+        torch.cuda.synchronize()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    run_lanes(max(1, min(args.warmup, 2)) * len(lanes))
+    for ln in lanes:
+        ln["ctx"].sync()
+    ms_e2e = timed_e2e(args.steps)
     if world > 1:                             # every rank holds every chromosome's row after the all-reduce
         for tb in tables:
             t_host = tb.cpu().numpy()
             for c in wl.chroms:
                 assert int(t_host[c.index, 101:202].sum()) == c.length, "statistics table row %d wrong after the all-reduce" % c.index
 
-    # sanity: the e2e leg and the device leg produced the same bits for the last chromosome
+    # sanity: the e2e leg and the device leg produced the same bits for the last chromosome, in every result buffer
     if res:
         got = res[-1]["out_del"].cpu().numpy()[: len(mine[-1].dels) * CALL_DT.itemsize]
-        for b in range(DEPTH + 1):
-            assert got.tobytes() == host[-1][5][b].tobytes(), "device-mode and host-mode results differ"
+        for ln in lanes:
+            for outs in ln["out"][: min(DEPTH + 1, ln["n"])]:
+                assert got.tobytes() == outs[-1][0].tobytes(), "device-mode and host-mode results differ"
+    for ln in lanes[1:]:
+        ln["ctx"].close()
 
     n_reads, n_cnvs = wl.n_reads, wl.n_cnvs
     value = n_reads * args.steps / (ms_dev / 1e3)
@@ -387,7 +430,7 @@ def own_arm(args):
            "cnvs_per_s": round(n_cnvs * args.steps / (ms_dev / 1e3), 1),
            "cnvs_per_s_genotype_kernels_rank0": round(sum(len(c.dels) + len(c.dups) for c in mine) / (cnv_ms / 1e3), 1) if cnv_ms > 0 else None,
            "e2e": {"value": round(e2e, 1), "unit": "reads/s", "ms_per_step": round(ms_e2e / args.steps, 4),
-                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "samples_in_flight": DEPTH},
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "samples_in_flight": DEPTH * LANES, "host_threads": LANES},
            "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline_port(wl, budget_s=args.cpu_budget)

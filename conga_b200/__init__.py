@@ -5,8 +5,8 @@ The product is ``libconga_gpu.so`` (C-ABI in ``include/conga_gpu.h``, CUDA sourc
 of the reference's call seams (`hotpath`) and the synthetic-input generator (`synth`).
 Nothing here computes any stage of the path on the CPU.
 """
-from .abi import (CALL_DT, CNV_DT, HALF_DT, SPLITROW_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, CG_PTR_DEVICE, CG_PTR_HOST,
+from .abi import (CALL_DT, CHROM_JOB_DT, chrom_job, CNV_DT, HALF_DT, SPLITROW_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, CG_PTR_DEVICE, CG_PTR_HOST,
                   CongaGpuError, Context, flatten_mappability, load_library)
 
-__all__ = ["CALL_DT", "CNV_DT", "HALF_DT", "SPLITROW_DT", "MAPIV_DT", "MAPRUN_DT", "READ_DT", "STATS_DT", "CG_PTR_DEVICE",
+__all__ = ["CALL_DT", "CHROM_JOB_DT", "chrom_job", "CNV_DT", "HALF_DT", "SPLITROW_DT", "MAPIV_DT", "MAPRUN_DT", "READ_DT", "STATS_DT", "CG_PTR_DEVICE",
            "CG_PTR_HOST", "CongaGpuError", "Context", "flatten_mappability", "load_library"]

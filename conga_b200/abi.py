@@ -35,6 +35,12 @@ STATS_DT = np.dtype([("rd_per_gc", "<i8", (CG_GC_BINS,)), ("window_per_gc", "<i8
 HALF_DT = np.dtype([("pos", "<i4"), ("seq_off", "<u4"), ("len", "<u2"), ("read_len", "<u2"), ("mapq", "u1"), ("is_read2", "u1"), ("pad", "<u2")])
 SPLITROW_DT = np.dtype([("pos", "<i4"), ("pos_map", "<i4"), ("left_start", "<i4"), ("left_end", "<i4"), ("right_start", "<i4"),
                         ("right_end", "<i4"), ("sv_type", "u1"), ("pad", "u1", (7,))])
+# cg_chrom_job: pointers as integers (host or device addresses, whatever the pointer mode says)
+CHROM_JOB_DT = np.dtype([("chr_index", "<i4"), ("chrom_len", "<i4"), ("gc", "<u8"), ("n_windows", "<i4"), ("mq_threshold", "<i4"),
+                         ("reads", "<u8"), ("n_reads", "<u8"), ("runs", "<u8"), ("n_runs", "<u8"), ("use_mappability", "<i4"), ("pad", "<i4"),
+                         ("dels", "<u8"), ("n_del", "<u8"), ("del_calls", "<u8"), ("dups", "<u8"), ("n_dup", "<u8"), ("dup_calls", "<u8"),
+                         ("stats", "<u8")])
+assert CHROM_JOB_DT.itemsize == 120
 assert HALF_DT.itemsize == 16 and SPLITROW_DT.itemsize == 32
 assert READ_DT.itemsize == 8 and CNV_DT.itemsize == 8 and MAPIV_DT.itemsize == 16
 assert MAPRUN_DT.itemsize == 16 and CALL_DT.itemsize == 56 and STATS_DT.itemsize == 204 * 8
@@ -66,6 +72,7 @@ SYMBOLS = {
     "cg_sr_rows": (_I, [_P, _P, _Z, C.POINTER(_Z), C.POINTER(C.c_uint64)]),
     "cg_sr_count": (_I, [_P, _P, _Z, _P, _Z, _P, _Z, _P, _P]),
     "cg_gc_profile": (_I, [_P, _P, C.c_int64, _P, C.c_int32]),
+    "cg_run_chromosomes": (_I, [_P, _P, _Z]),
     "cg_sync": (_I, [_P]),
     "cg_download_depth": (_I, [_P, _P]),
     "cg_download_prefix": (_I, [_P, _P]),
@@ -325,6 +332,11 @@ class Context:
                                       dups.ctypes.data if len(dups) else None, len(dups), b.ctypes.data if len(b) else None, r.ctypes.data if len(r) else None))
         return b, r
 
+    def run_chromosomes(self, jobs: np.ndarray):
+        """cg_run_chromosomes: `jobs` is a CHROM_JOB_DT array (see chrom_job); one foreign call for all of them."""
+        assert jobs.dtype == CHROM_JOB_DT and jobs.flags.c_contiguous
+        self._ck(self.lib.cg_run_chromosomes(self.h, jobs.ctypes.data, len(jobs)))
+
     def gc_profile(self, bases, n_bases=None, out=None):
         """SONIC's GC bytes of one chromosome from its bases (cg_gc_profile).  HOST mode: bytes / uint8
         array in, int8 array out.  DEVICE mode: uint8 tensor in, `out` an int8 tensor of (n + 1) // 100."""
@@ -353,6 +365,19 @@ class Context:
         n = (C.c_int64 * CG_NSLOTS)()
         self._ck(self.lib.cg_kernel_times(self.h, ms, n))
         return list(ms), list(n)
+
+
+def chrom_job(chr_index, chrom_len, gc, n_windows, mq_threshold, reads, n_reads, runs=None, n_runs=0, use_mappability=False,
+              dels=None, n_del=0, del_calls=None, dups=None, n_dup=0, dup_calls=None, stats=None) -> np.ndarray:
+    """One cg_chrom_job record; array arguments may be NumPy arrays, torch tensors or raw addresses."""
+    j = np.zeros(1, dtype=CHROM_JOB_DT)
+    j["chr_index"], j["chrom_len"], j["gc"], j["n_windows"], j["mq_threshold"] = chr_index, chrom_len, _ptr(gc), n_windows, mq_threshold
+    j["reads"], j["n_reads"] = _ptr(reads), n_reads
+    j["runs"], j["n_runs"], j["use_mappability"] = _ptr(runs) if n_runs else 0, n_runs, int(bool(use_mappability))
+    j["dels"], j["n_del"], j["del_calls"] = _ptr(dels) if n_del else 0, n_del, _ptr(del_calls) if n_del else 0
+    j["dups"], j["n_dup"], j["dup_calls"] = _ptr(dups) if n_dup else 0, n_dup, _ptr(dup_calls) if n_dup else 0
+    j["stats"] = _ptr(stats)
+    return j
 
 
 def flatten_mappability(rows: np.ndarray, chrom_len: int) -> np.ndarray:

@@ -47,6 +47,7 @@ struct cg_pass_args {
     uint32_t*      depth32;           /* unsorted fallback: per-position u32 counts (zero at rest) */
     unsigned int*  ctl;               /* CG_W_* control words */
     long long*     stats;             /* this chromosome's int64[204] row */
+    long long*     host_row;          /* NULL, or page-locked host memory the last CTA copies the finished row to */
     float*         expected;          /* [101] written by the last CTA to finish */
     unsigned int*  sticky;            /* context-wide word: CG_FLAG_RANGE is copied here */
 };

@@ -4,7 +4,8 @@
  * without a CUDA device cg_create fails and nothing else can be called.
  *
  * Execution model.  A context owns two chromosome slots and six streams:
- *   s_copy     host->device copies of GC bytes and read batches (HOST pointer mode)
+ *   s_copy[k]  host->device copies of GC bytes and read batches of slot k (HOST pointer mode); one stream per slot,
+ *              so that the few-megabyte copies of consecutive chromosomes overlap their start-up gaps on the copy engines
  *   s_slot[2]  one per slot: chromosome init, batch marking, rare paths, the fused depth pass
  *   s_geno[2]  per slot, deletions / duplications: mappability + CNV uploads, the genotype kernel,
  *              downloads.  The genotype kernel is a chain of dependent loads whose latency grows
@@ -30,7 +31,9 @@
 #include <vector>
 
 #define CG_MAX_CHROMS 4096            /* rows of the statistics table */
+#ifndef CG_NSLOT
 #define CG_NSLOT 4
+#endif
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
 
@@ -68,7 +71,7 @@ struct cg_slot {
 struct cg_ctx {
     int device = 0;
     int n_sms = 148;
-    cudaStream_t s_copy = nullptr, s_main = nullptr;
+    cudaStream_t s_copy[CG_NSLOT] = {}, s_main = nullptr;
     cudaStream_t s_slot[CG_NSLOT] = {};
     cudaStream_t s_bank = nullptr;            /* clears a statistics bank that is selected again */
     cudaEvent_t ev_reset = nullptr;           /* the current statistics bank has been cleared */
@@ -146,7 +149,7 @@ static inline bool blocking(const cg_ctx* c) { return c->ptr_mode == CG_PTR_HOST
 
 static int sync_all(cg_ctx* c)
 {
-    CU(c, cudaStreamSynchronize(c->s_copy));
+    for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_copy[i]));
     CU(c, cudaStreamSynchronize(c->s_main));
     CU(c, cudaStreamSynchronize(c->s_bank));
     if (c->sr.st) CU(c, cudaStreamSynchronize(c->sr.st));
@@ -255,8 +258,9 @@ cg_ctx* cg_create(int device)
     c->n_sms = prop.multiProcessorCount;
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
-    bool ok = cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
-        && cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+    bool ok = true;
+    for (int i = 0; ok && i < CG_NSLOT; i++) ok = cudaStreamCreateWithPriority(&c->s_copy[i], cudaStreamNonBlocking, prio_lo) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaStreamCreateWithPriority(&c->s_bank, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_left[0], cudaEventDisableTiming) == cudaSuccess
@@ -298,7 +302,7 @@ void cg_destroy(cg_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    if (c->s_copy) cudaStreamSynchronize(c->s_copy);
+    for (int i = 0; i < CG_NSLOT; i++) if (c->s_copy[i]) cudaStreamSynchronize(c->s_copy[i]);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     if (c->s_bank) cudaStreamSynchronize(c->s_bank);
     for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamSynchronize(c->s_slot[t]);
@@ -324,7 +328,7 @@ void cg_destroy(cg_ctx* c)
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
-    if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    for (int i = 0; i < CG_NSLOT; i++) if (c->s_copy[i]) cudaStreamDestroy(c->s_copy[i]);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_bank) cudaStreamDestroy(c->s_bank);
     for (int b = 0; b < 2; b++) if (c->ev_left[b]) cudaEventDestroy(c->ev_left[b]);
@@ -368,9 +372,11 @@ int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    cudaStream_t all[1 + 3 * CG_NSLOT] = {c->s_copy};
-    for (int i = 0; i < CG_NSLOT; i++) { all[1 + 3 * i] = c->s_slot[i]; all[2 + 3 * i] = c->slot[i].s_geno[0]; all[3 + 3 * i] = c->slot[i].s_geno[1]; }
-    for (int t = 0; t < 1 + 3 * CG_NSLOT; t++) {
+    /* every upload on a copy stream is waited for by a kernel on its slot's stream (cg_push_reads, cg_chrom_finish),
+     * so the slot and genotype streams cover the copy streams */
+    cudaStream_t all[3 * CG_NSLOT];
+    for (int i = 0; i < CG_NSLOT; i++) { all[3 * i] = c->s_slot[i]; all[1 + 3 * i] = c->slot[i].s_geno[0]; all[2 + 3 * i] = c->slot[i].s_geno[1]; }
+    for (int t = 0; t < 3 * CG_NSLOT; t++) {
         CU(c, cudaEventRecord(c->ev_join, all[t]));
         CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
     }
@@ -457,10 +463,10 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         if (rc) return rc;
     }
     /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
-    if (s.used) CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_pass, 0));            /* d_reads */
+    if (s.used) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_pass, 0));        /* d_reads */
     for (int t = 0; t < 2; t++) {
         if (!s.geno_queued[t]) continue;
-        CU(c, cudaStreamWaitEvent(c->s_copy, s.ev_geno[t], 0));                  /* d_gc */
+        CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_geno[t], 0));              /* d_gc */
         CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_depth, d_counts, d_expected */
         /* d_runs and the staging arena are written from both genotype streams */
         CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
@@ -472,8 +478,8 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(ss, o.ev_geno[t], 0));
     }
     if (c->ptr_mode == CG_PTR_HOST) {
-        CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy));
-        CU(c, cudaEventRecord(s.ev_copy, c->s_copy));
+        CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy[si]));
+        CU(c, cudaEventRecord(s.ev_copy, c->s_copy[si]));
         s.gc_ptr = s.d_gc;
     } else {
         s.gc_ptr = gc_profile;
@@ -510,8 +516,8 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     if (c->ptr_mode == CG_PTR_HOST) {
         int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, (size_t)first);
         if (rc) return rc;
-        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy));
-        CU(c, cudaEventRecord(s.ev_copy, c->s_copy));
+        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy[c->cur]));
+        CU(c, cudaEventRecord(s.ev_copy, c->s_copy[c->cur]));
         CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));
         s.reads_ptr = s.d_reads;
     } else if (first == 0) {
@@ -547,11 +553,12 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
                              s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
     }
     {
-        /* One depth pass at a time: two passes side by side double the number of concurrent write
-         * streams and cost HBM efficiency (measured).  Everything else of this chromosome — init,
-         * batch marking, copies — has already overlapped the previous chromosome's pass. */
+        /* Passes of consecutive chromosomes may run side by side (CG_PASS_OVERLAP=0 chains them).  At 6 bytes per
+         * position (rounds r01a-g) two passes doubled the concurrent write streams and cost HBM efficiency, so
+         * they were chained; at 2 bytes per position the overlap hides each launch's ramp and tail instead:
+         * C2 sample 1.25 -> 1.20 ms (measured r01h). */
         cg_slot& o = c->slot[(c->cur + CG_NSLOT - 1) % CG_NSLOT];
-        static const bool overlap = getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP"));   /* tuning only */
+        static const bool overlap = !(getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP")) == 0);
         if (o.used && !overlap) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
     }
     {
@@ -562,6 +569,8 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
         a.chrom_len = s.chrom_len; a.n_chunks = s.n_chunks; a.mq_threshold = c->mq_threshold;
         a.depth = s.d_depth; a.depth32 = s.d_depth32; a.ctl = s.d_ctl;
         a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
+        /* asynchronous HOST mode hands over page-locked pointers: the kernel writes the row there itself */
+        a.host_row = (c->ptr_mode == CG_PTR_HOST && c->async && out) ? reinterpret_cast<long long*>(out) : nullptr;
         CU(c, cgk_depth_pass(c->s_slot[c->cur], a, c->n_sms));
     }
     CU(c, cudaEventRecord(s.ev_pass, c->s_slot[c->cur]));
@@ -570,10 +579,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
         if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
         return CG_OK;
     }
-    if (c->async) {                       /* `out` is page-locked and is valid after cg_sync */
-        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
-        return CG_OK;
-    }
+    if (c->async) return CG_OK;           /* `out` is page-locked, written by the pass, valid after cg_sync */
     CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
     CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
     if (out) memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
@@ -686,7 +692,11 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     const int t = is_dup ? 1 : 0;
     cudaStream_t st = s.s_geno[t];            /* deletions and duplications of one chromosome run side by side */
     const cg_cnv* d_in = cnvs; cg_call* d_out = out;
-    if (c->ptr_mode == CG_PTR_HOST) {
+    /* Asynchronous HOST mode: both arrays are page-locked (cg_set_async), i.e. addressable from the device; the
+     * kernel reads 8 bytes and writes 56 per CNV across PCIe itself, which is cheaper than two copy calls per
+     * launch on a host that issues a chromosome every 50 us. */
+    const bool staged = c->ptr_mode == CG_PTR_HOST && !c->async;
+    if (staged) {
         cg_cnv* a_in = nullptr;
         int rc = arena_take(c, s, n, &a_in, &d_out);
         if (rc) return rc;
@@ -700,13 +710,31 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
         CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_depth, cgk_counts_layout(s.d_counts, s.n_chunks), s.gc_ptr, s.d_expected, s.runs_ptr, s.d_run_idx, s.n_runs, s.has_map,
                            s.chrom_len, c->d_sticky, d_out, c->n_sms));
     }
-    if (c->ptr_mode == CG_PTR_HOST)
-        CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, st));
+    if (staged) CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, st));
     CU(c, cudaEventRecord(s.ev_geno[t], st));
     s.geno_queued[t] = true;
     if (blocking(c)) {
         CU(c, cudaStreamSynchronize(st));
         return report_sticky(c, "cg_genotype");
+    }
+    return CG_OK;
+}
+
+int cg_run_chromosomes(cg_ctx* c, const cg_chrom_job* jobs, size_t n_jobs)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (n_jobs && !jobs) return fail(c, CG_EINVAL, "null jobs");
+    const size_t BATCH = (size_t)1 << 22;
+    int rc;
+    for (size_t k = 0; k < n_jobs; k++) {
+        const cg_chrom_job& j = jobs[k];
+        if ((rc = cg_chrom_begin(c, j.chr_index, j.chrom_len, j.gc, j.n_windows, j.mq_threshold)) != CG_OK) return rc;
+        for (size_t i = 0; i < j.n_reads; i += BATCH)
+            if ((rc = cg_push_reads(c, j.reads + i, j.n_reads - i < BATCH ? (size_t)(j.n_reads - i) : BATCH)) != CG_OK) return rc;
+        if ((rc = cg_chrom_finish(c, j.stats)) != CG_OK) return rc;
+        if (j.use_mappability && (rc = cg_set_mappability_runs(c, j.runs, (size_t)j.n_runs, 1)) != CG_OK) return rc;
+        if (j.n_del && (rc = cg_genotype(c, j.dels, (size_t)j.n_del, 0, j.del_calls)) != CG_OK) return rc;
+        if (j.n_dup && (rc = cg_genotype(c, j.dups, (size_t)j.n_dup, 1, j.dup_calls)) != CG_OK) return rc;
     }
     return CG_OK;
 }

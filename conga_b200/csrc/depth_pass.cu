@@ -533,6 +533,10 @@ k_depth_pass(const cg_pass_args a)
                 if (a.ctl[CG_W_FLAGS] & CG_FLAG_RANGE) atomicOr(a.sticky, CG_FLAG_RANGE);
             }
         }
+        if (a.host_row) {                     /* asynchronous HOST mode: the row goes straight to page-locked host memory */
+            __syncthreads();
+            if (tid < CG_STATS_WORDS) a.host_row[tid] = __ldcg(&a.stats[tid]);
+        }
     }
 }
 

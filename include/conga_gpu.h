@@ -105,7 +105,9 @@ int         cg_set_pointer_mode(cg_ctx* ctx, int mode);
  * cg_chrom_begin / cg_push_reads / cg_chrom_finish / cg_set_mappability_runs / cg_genotype must
  * be page-locked (cg_alloc_pinned) and stay untouched until cg_sync(), which is also when the
  * outputs become valid and when CG_ERANGE is reported.  This is how a host that decodes the
- * next chromosome while the GPU works on the current one drives the library. */
+ * next chromosome while the GPU works on the current one drives the library.  The small arrays
+ * (the statistics row of cg_chrom_finish, the CNVs and calls of cg_genotype) are then read and
+ * written by the kernels directly in that page-locked memory, without a copy call. */
 int         cg_set_async(cg_ctx* ctx, int on);
 
 /* Page-locked host memory for read batches / results (library owns it). */
@@ -200,6 +202,25 @@ int cg_sr_rows(cg_ctx* ctx, cg_splitrow* out, size_t cap, size_t* n_rows, uint64
  * count_ReadPairs adds to svs.border_rp / svs.rp (both start at 0, svs.c:164-167). */
 int cg_sr_count(cg_ctx* ctx, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
                 const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp);
+
+/* ---- One call for the loop body of read_bam (bam_data.c:304-338) over several chromosomes ----
+ * Job k is exactly: cg_chrom_begin(chr_index, chrom_len, gc, n_windows, mq_threshold);
+ * cg_push_reads(reads, n_reads) in batches of 2^22 records; cg_chrom_finish(stats);
+ * cg_set_mappability_runs(runs, n_runs, 1) when use_mappability != 0; cg_genotype(dels, n_del, 0, del_calls)
+ * when n_del > 0; cg_genotype(dups, n_dup, 1, dup_calls) when n_dup > 0 — same pointer mode, same
+ * blocking / asynchronous behaviour, same errors (the first failing call's code is returned and the jobs
+ * after it are not started).  It exists for callers that drive the library through a foreign-function
+ * interface with a per-call cost (ctypes, cgo, JNI): one crossing per sample instead of six per chromosome. */
+typedef struct cg_chrom_job {
+    int32_t chr_index, chrom_len;
+    const int8_t* gc;          int32_t n_windows; int32_t mq_threshold;
+    const cg_read* reads;      uint64_t n_reads;
+    const cg_maprun* runs;     uint64_t n_runs;   int32_t use_mappability; int32_t pad;
+    const cg_cnv* dels;        uint64_t n_del;    cg_call* del_calls;
+    const cg_cnv* dups;        uint64_t n_dup;    cg_call* dup_calls;
+    cg_chrom_stats* stats;     /* may be NULL */
+} cg_chrom_job;
+int cg_run_chromosomes(cg_ctx* ctx, const cg_chrom_job* jobs, size_t n_jobs);
 
 /* ---- SONIC's GC profile from the bases of a chromosome ----
  * Replaces the character loop of sonic_write_gc_profile (sonic/sonic_reference.c:30-106) for ONE FASTA

@@ -8,7 +8,7 @@ expected sums, mappability and copy numbers BIT-EXACT; likelihoods and c-scores 
 import numpy as np
 import pytest
 
-from conga_b200 import CNV_DT, MAPIV_DT, READ_DT, CongaGpuError, hotpath, synth
+from conga_b200 import CNV_DT, MAPIV_DT, MAPRUN_DT, READ_DT, CongaGpuError, hotpath, synth
 from conga_b200.abi import CG_ERANGE, CG_TILE
 from golden_util import GoldenCase, golden_files
 
@@ -413,3 +413,66 @@ def test_statistics_banks(ctx, oracle):
     finally:
         ctx.stats_bank(0)
         ctx.stats_reset()
+
+
+def test_run_chromosomes_one_call_per_sample(ctx, oracle):
+    """cg_run_chromosomes: one foreign call for the loop body of read_bam over several chromosomes, pinned
+    host buffers in asynchronous HOST mode, then the same jobs again with device buffers in DEVICE mode."""
+    import torch
+    from conga_b200 import CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, STATS_DT, chrom_job, flatten_mappability
+    rng = np.random.default_rng(12)
+    lens = [900_000, 30_000, 1_300_000]
+    chroms = [synth._chrom("r%d" % i, i, L, rng, max(10, L // 30), 25 + i, (10 + i) if i != 1 else 0, i != 2, cnv_hi=max(2000, L // 8))
+              for i, L in enumerate(lens)]
+    want = [oracle.chromosome(ch, 10, ch.maprows is not None) for ch in chroms]
+
+    def check(stats, dels, dups):
+        for ch, (depth, st_ref, exp, d_ref, u_ref), st, od, ou in zip(chroms, want, stats, dels, dups):
+            assert int(st[0]["rd_cnt"]) == int(st_ref["rd_cnt"]) and np.array_equal(st[0]["rd_per_gc"], st_ref["rd_per_gc"])
+            assert_calls_equal(od, d_ref, ch.maprows is not None)
+            if len(ch.dups):
+                assert_calls_equal(ou, u_ref, ch.maprows is not None)
+
+    # HOST mode, nothing blocks
+    ctx.set_pointer_mode(CG_PTR_HOST)
+    ctx.set_async(True)
+    try:
+        keep, jobs, outs = [], [], ([], [], [])
+        for ch in chroms:
+            pin = lambda a, dt: (lambda p: (p.__setitem__(slice(None), a), p)[1])(ctx.pinned_array(len(a), dt))
+            runs = flatten_mappability(np.ascontiguousarray(ch.maprows), ch.length) if ch.maprows is not None else np.zeros(0, dtype=MAPRUN_DT)
+            bufs = (pin(ch.reads, READ_DT), pin(ch.gc, np.int8), pin(ch.dels, CNV_DT), pin(ch.dups, CNV_DT), pin(runs, MAPRUN_DT))
+            st, od, ou = ctx.pinned_array(1, STATS_DT), ctx.pinned_array(len(ch.dels), CALL_DT), ctx.pinned_array(len(ch.dups), CALL_DT)
+            jobs.append(chrom_job(ch.index, ch.length, bufs[1], len(bufs[1]), 10, bufs[0], len(bufs[0]), bufs[4], len(bufs[4]), ch.maprows is not None,
+                                  bufs[2], len(bufs[2]), od, bufs[3], len(bufs[3]), ou, st))
+            keep.append(bufs)
+            outs[0].append(st); outs[1].append(od); outs[2].append(ou)
+        ctx.run_chromosomes(np.concatenate(jobs))
+        ctx.sync()
+        check(*outs)
+    finally:
+        ctx.set_async(False)
+
+    # DEVICE mode
+    dev = torch.device("cuda:0")
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).to(dev)
+    ctx.set_pointer_mode(CG_PTR_DEVICE)
+    try:
+        keep, jobs, outs = [], [], ([], [], [])
+        for ch in chroms:
+            runs = flatten_mappability(np.ascontiguousarray(ch.maprows), ch.length) if ch.maprows is not None else np.zeros(0, dtype=MAPRUN_DT)
+            bufs = (up(ch.reads), up(ch.gc), up(ch.dels) if len(ch.dels) else None, up(ch.dups) if len(ch.dups) else None, up(runs) if len(runs) else None)
+            st = torch.zeros(STATS_DT.itemsize, dtype=torch.uint8, device=dev)
+            od = torch.zeros(max(1, len(ch.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)
+            ou = torch.zeros(max(1, len(ch.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)
+            jobs.append(chrom_job(ch.index, ch.length, bufs[1], len(ch.gc), 10, bufs[0], len(ch.reads), bufs[4], len(runs), ch.maprows is not None,
+                                  bufs[2], len(ch.dels), od, bufs[3], len(ch.dups), ou, st))
+            keep.append(bufs)
+            outs[0].append(st); outs[1].append(od); outs[2].append(ou)
+        ctx.run_chromosomes(np.concatenate(jobs))
+        ctx.sync()
+        host = lambda t, dt, n: t.cpu().numpy()[: n * dt.itemsize].view(dt)
+        check([host(t, STATS_DT, 1) for t in outs[0]], [host(t, CALL_DT, len(ch.dels)) for t, ch in zip(outs[1], chroms)],
+              [host(t, CALL_DT, len(ch.dups)) for t, ch in zip(outs[2], chroms)])
+    finally:
+        ctx.set_pointer_mode(CG_PTR_HOST)
