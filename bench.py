@@ -268,11 +268,11 @@ def own_arm(args):
     # A pipelined host: page-locked buffers, asynchronous calls, one cg_sync per step — that is when the
     # results (statistics rows, genotype calls) are valid on the host.
     DEPTH = max(1, env_int("BENCH_E2E_DEPTH", 2))      # samples in flight behind the one being issued, per lane
-    # Issuing a sample costs the host about as much time as the device needs to run it, so a single-GPU host
-    # issues from LANES threads, one context each (a context is driven by one thread at a time; the foreign call
-    # releases the interpreter lock).  Multi-GPU ranks keep one lane: their collective must be issued in one
-    # order on every rank.
-    LANES = max(1, env_int("BENCH_E2E_LANES", 2)) if world == 1 else 1
+    # BENCH_E2E_LANES > 1 issues from that many host threads, one context each (a context is driven by one thread
+    # at a time; the foreign call releases the interpreter lock).  Measured r01h: two lanes give 2.26 against
+    # 2.30 G reads/s with one — the end-to-end leg is not bound by the issuing thread — so one lane is the default.
+    # Multi-GPU ranks always use one: their collective must be issued in one order on every rank.
+    LANES = max(1, env_int("BENCH_E2E_LANES", 1)) if world == 1 else 1
     lanes = [dict(ctx=ctx, ext=ext)]
     for _ in range(LANES - 1):
         cx = Context(local)
