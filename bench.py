@@ -30,7 +30,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "reads/s through the read-depth genotyping hot path (depth + GC + prefix + CNV genotyping)"
+METRIC = "reads/s through the read-depth genotyping hot path (depth + GC bins + per-CNV sums + CNV genotyping)"
 
 
 def env_int(name, default):
@@ -422,7 +422,7 @@ def own_arm(args):
     cnv_ms = k_ms[2] / args.steps
     out = {"metric": METRIC, "value": round(value, 1), "unit": "reads/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
-           "scaling": "strong", "vs_baseline": None, "dtype": "int16/int32 depth+prefix, f32 ordered sum, f64 likelihood",
+           "scaling": "strong", "vs_baseline": None, "dtype": "int16 depth, int32 sums, f32 ordered sum, f64 likelihood",
            "data": "synthetic", "impl": "b200",
            "config": {"workload": wl.name, "chromosomes": n_chrom, "positions": wl.n_positions, "reads": n_reads,
                       "cnvs": n_cnvs, "mappability": has_map, "partition": "chromosomes, LPT by length",
