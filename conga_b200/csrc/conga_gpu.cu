@@ -463,13 +463,18 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         if (rc) return rc;
     }
     /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
-    if (s.used) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_pass, 0));        /* d_reads */
+    /* HOST mode writes the slot's own upload buffers (d_reads, d_gc from the copy stream; d_runs and the staging
+     * arena from both genotype streams); DEVICE mode writes none of them and needs only the slot stream ordered
+     * behind the previous tenant's genotype kernels — 3 waits per chromosome instead of 7 on a host that is the
+     * limit of the resident leg */
+    const bool uploads = c->ptr_mode == CG_PTR_HOST;
+    if (s.used && uploads) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_pass, 0));   /* d_reads */
     for (int t = 0; t < 2; t++) {
         if (!s.geno_queued[t]) continue;
-        CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_geno[t], 0));              /* d_gc */
+        if (uploads) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_geno[t], 0)); /* d_gc */
         CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_depth, d_counts, d_expected */
-        /* d_runs and the staging arena are written from both genotype streams */
-        CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
+        /* d_run_idx is rebuilt on s_geno[0] in either mode: behind the previous tenant's duplication kernel */
+        if (uploads || t == 1) CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
     }
     if (s.wait_reset) { CU(c, cudaStreamWaitEvent(ss, c->ev_reset, 0)); s.wait_reset = false; }
     if (c->profiling && !getenv("CG_PROF_NOCHAIN")) {   /* time kernels alone: chain this slot behind the other one */
