@@ -12,7 +12,7 @@
  *              several-fold under a depth pass that saturates HBM, so the genotype kernels of
  *              up to CG_NSLOT chromosomes are allowed to run side by side.
  *   s_main     cg_stream(): statistics reset, and what cg_join() orders behind everything else
- * Chromosome k lives in slot k&1 (its own records, depth, GC, expected-table, count and
+ * Chromosome k lives in slot k mod CG_NSLOT (its own records, depth, GC, expected-table, count and
  * staging buffers) and nothing of slot 0 depends on slot 1.  So the preparation kernels and the
  * ramp-up of chromosome k+1's depth pass fill the SMs that chromosome k's pass is draining from,
  * the latency-bound genotype kernels of k run underneath the bandwidth-bound pass of k+1, and the
@@ -32,7 +32,7 @@
 
 #define CG_MAX_CHROMS 4096            /* rows of the statistics table */
 #ifndef CG_NSLOT
-#define CG_NSLOT 4
+#define CG_NSLOT 6                    /* measured r01h, C2 resident: 3 slots 1.48 ms per sample, 4 slots 1.22, 6 slots 1.09 (host-issue bound) */
 #endif
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
@@ -117,6 +117,9 @@ struct cg_ctx {
         int chrom_len = 0, mq_threshold = -1;
     } sr;
 
+    /* largest sizes any slot has needed, per buffer kind (see grow()) */
+    size_t hw_gc = 0, hw_reads = 0, hw_runs = 0, hw_run_idx = 0, hw_chunks = 0;
+
     /* cg_gc_profile staging (HOST pointer mode) */
     char* d_gc_bases = nullptr; size_t gc_bases_cap = 0;
     int8_t* d_gc_out = nullptr; size_t gc_out_cap = 0;
@@ -161,10 +164,13 @@ static int sync_all(cg_ctx* c)
 /* Replace a device buffer by a larger one.  Everything queued is drained first (the old
  * buffer may still be read by any stream); growth is rare and amortised. */
 template <typename T>
-static int grow(cg_ctx* c, T** p, size_t* cap, size_t need, size_t keep_elems = 0)
+static int grow(cg_ctx* c, T** p, size_t* cap, size_t need, size_t keep_elems = 0, size_t* high_water = nullptr)
 {
     if (need <= *cap) return CG_OK;
-    const size_t ncap = std::max(need, *cap + *cap / 2);
+    /* chromosomes rotate through the slots, so a slot that has to grow goes straight to the largest size any
+     * slot has needed: every slot reallocates at most once per buffer after the largest chromosome was seen */
+    size_t ncap = std::max(need, *cap + *cap / 2);
+    if (high_water) { ncap = std::max(ncap, *high_water); *high_water = ncap; }
     int rc = sync_all(c);
     if (rc) return rc;
     T* np = nullptr;
@@ -433,33 +439,36 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     cg_slot& s = c->slot[si];
     const int n_chunks = (chrom_len + CG_CHUNK - 1) / CG_CHUNK;
     const size_t n_pos = (size_t)n_chunks * CG_CHUNK;
+    if ((size_t)n_chunks > c->hw_chunks) c->hw_chunks = (size_t)n_chunks;
+    const int a_chunks = (int)c->hw_chunks;               /* what a slot that has to grow is sized for: the largest */
+    const size_t a_pos = (size_t)a_chunks * CG_CHUNK;      /* chromosome any slot has seen (see grow()) */
     if (cgk_counts_words(n_chunks) > s.counts_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
         cudaFree(s.d_counts); s.d_counts = nullptr; s.counts_cap = 0;
-        CU(c, cudaMalloc(&s.d_counts, cgk_counts_words(n_chunks) * sizeof(int32_t)));
-        s.counts_cap = cgk_counts_words(n_chunks);
+        CU(c, cudaMalloc(&s.d_counts, cgk_counts_words(a_chunks) * sizeof(int32_t)));
+        s.counts_cap = cgk_counts_words(a_chunks);
     }
     if (n_pos > s.pos_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
         cudaFree(s.d_depth);
         s.d_depth = nullptr; s.pos_cap = 0;
-        CU(c, cudaMalloc(&s.d_depth, n_pos * sizeof(int16_t)));
-        s.pos_cap = n_pos;
+        CU(c, cudaMalloc(&s.d_depth, a_pos * sizeof(int16_t)));
+        s.pos_cap = a_pos;
     }
     cudaStream_t ss = c->s_slot[si];
     if (n_pos > s.depth32_cap) {
         int rc = sync_all(c);
         if (rc) return rc;
         cudaFree(s.d_depth32); s.d_depth32 = nullptr; s.depth32_cap = 0;
-        CU(c, cudaMalloc(&s.d_depth32, n_pos * sizeof(uint32_t)));
+        CU(c, cudaMalloc(&s.d_depth32, a_pos * sizeof(uint32_t)));
         /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
-        CU(c, cudaMemsetAsync(s.d_depth32, 0, n_pos * sizeof(uint32_t), ss));
-        s.depth32_cap = n_pos;
+        CU(c, cudaMemsetAsync(s.d_depth32, 0, a_pos * sizeof(uint32_t), ss));
+        s.depth32_cap = a_pos;
     }
     if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows);
+        int rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows, 0, &c->hw_gc);
         if (rc) return rc;
     }
     /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
@@ -519,7 +528,7 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
     cg_slot& s = c->slot[c->cur];
     const long long first = c->n_reads;
     if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, (size_t)first);
+        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, (size_t)first, &c->hw_reads);
         if (rc) return rc;
         CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy[c->cur]));
         CU(c, cudaEventRecord(s.ev_copy, c->s_copy[c->cur]));
@@ -529,7 +538,7 @@ int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
         s.reads_ptr = reads;                  /* single device batch: used in place */
     } else {
         const bool external = s.reads_ptr != s.d_reads;
-        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, external ? 0 : (size_t)first);
+        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, external ? 0 : (size_t)first, &c->hw_reads);
         if (rc) return rc;
         if (external) CU(c, cudaMemcpyAsync(s.d_reads, s.reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
         CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
@@ -627,12 +636,12 @@ int cg_set_mappability_runs(cg_ctx* c, const cg_maprun* runs, size_t n, int enab
     s.n_runs = (int)n;
     if (n == 0) { s.runs_ptr = nullptr; return CG_OK; }
     if (!runs) return fail(c, CG_EINVAL, "null runs");
-    int rc = grow(c, &s.d_run_idx, &s.run_idx_cap, (size_t)cgk_run_index_words(s.chrom_len));
+    int rc = grow(c, &s.d_run_idx, &s.run_idx_cap, (size_t)cgk_run_index_words(s.chrom_len), 0, &c->hw_run_idx);
     if (rc) return rc;
     if (c->ptr_mode == CG_PTR_DEVICE) {
         s.runs_ptr = runs;
     } else {
-        rc = grow(c, &s.d_runs, &s.runs_cap, n);
+        rc = grow(c, &s.d_runs, &s.runs_cap, n, 0, &c->hw_runs);
         if (rc) return rc;
         /* on a genotype stream: behind the slot's previous tenant, which may still read d_runs */
         CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, s.s_geno[0]));
