@@ -152,6 +152,9 @@ class DevArr:
 
 # ------------------------------------------------------------------------------------------
 def own_arm(args):
+    # A context drives ~26 streams (6 slots x (upload, slot, 2 genotype) + 2); with the default of 8 hardware
+    # connections streams share queues and kernels of different chromosomes serialise behind each other
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     import torch
     import torch.distributed as dist
     from conga_b200 import multi
