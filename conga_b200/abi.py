@@ -54,6 +54,7 @@ SYMBOLS = {
     "cg_last_error": (C.c_char_p, [_P]),
     "cg_set_pointer_mode": (_I, [_P, _I]),
     "cg_set_async": (_I, [_P, _I]),
+    "cg_set_slots": (_I, [_P, _I]),
     "cg_join": (_I, [_P]),
     "cg_alloc_pinned": (_P, [_P, _Z]),
     "cg_free_pinned": (None, [_P, _P]),
@@ -348,6 +349,10 @@ class Context:
             out = np.empty(need, dtype=np.int8)
         self._ck(self.lib.cg_gc_profile(self.h, _ptr(bases) if n else None, n, _ptr(out) if need else None, need))
         return out
+
+    def set_slots(self, n: int):
+        """cg_set_slots: chromosomes in flight (2..6)."""
+        self._ck(self.lib.cg_set_slots(self.h, int(n)))
 
     def stats_bank(self, bank: int):
         self._ck(self.lib.cg_stats_bank(self.h, int(bank)))

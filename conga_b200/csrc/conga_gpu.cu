@@ -85,6 +85,7 @@ struct cg_ctx {
     char err[512] = {0};
 
     cg_slot slot[CG_NSLOT];
+    int n_slot = CG_NSLOT;                    /* slots in rotation (cg_set_slots); the others stay idle */
     int cur = 0;                              /* slot of the current chromosome */
     long long n_begun = 0;
 
@@ -374,6 +375,18 @@ void* cg_stream(cg_ctx* c) { return c ? (void*)c->s_main : nullptr; }
 int64_t cg_launch_count(cg_ctx* c) { return c ? c->launch_count : 0; }
 
 /* make the main stream (cg_stream) wait for everything queued on the others */
+int cg_set_slots(cg_ctx* c, int n)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (n < 2 || n > CG_NSLOT) return fail(c, CG_EINVAL, "%d slots (2..%d)", n, CG_NSLOT);
+    if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_set_slots inside a chromosome");
+    CU(c, cudaSetDevice(c->device));
+    int rc = sync_all(c);                      /* slots that leave the rotation must be idle: cg_join no longer visits them */
+    if (rc) return rc;
+    c->n_slot = n;
+    return CG_OK;
+}
+
 int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
@@ -381,8 +394,8 @@ int cg_join(cg_ctx* c)
     /* every upload on a copy stream is waited for by a kernel on its slot's stream (cg_push_reads, cg_chrom_finish),
      * so the slot and genotype streams cover the copy streams */
     cudaStream_t all[3 * CG_NSLOT];
-    for (int i = 0; i < CG_NSLOT; i++) { all[3 * i] = c->s_slot[i]; all[1 + 3 * i] = c->slot[i].s_geno[0]; all[2 + 3 * i] = c->slot[i].s_geno[1]; }
-    for (int t = 0; t < 3 * CG_NSLOT; t++) {
+    for (int i = 0; i < c->n_slot; i++) { all[3 * i] = c->s_slot[i]; all[1 + 3 * i] = c->slot[i].s_geno[0]; all[2 + 3 * i] = c->slot[i].s_geno[1]; }
+    for (int t = 0; t < 3 * c->n_slot; t++) {
         CU(c, cudaEventRecord(c->ev_join, all[t]));
         CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
     }
@@ -435,7 +448,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
         return fail(c, CG_EINVAL, "gc_profile needs >= %d windows for length %d (got %d)", need_windows, chrom_len, n_windows);
     CU(c, cudaSetDevice(c->device));
 
-    const int si = (int)(c->n_begun % CG_NSLOT);
+    const int si = (int)(c->n_begun % (unsigned long long)c->n_slot);
     cg_slot& s = c->slot[si];
     const int n_chunks = (chrom_len + CG_CHUNK - 1) / CG_CHUNK;
     const size_t n_pos = (size_t)n_chunks * CG_CHUNK;
@@ -487,7 +500,7 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     }
     if (s.wait_reset) { CU(c, cudaStreamWaitEvent(ss, c->ev_reset, 0)); s.wait_reset = false; }
     if (c->profiling && !getenv("CG_PROF_NOCHAIN")) {   /* time kernels alone: chain this slot behind the other one */
-        cg_slot& o = c->slot[(si + CG_NSLOT - 1) % CG_NSLOT];
+        cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot];
         if (o.used) CU(c, cudaStreamWaitEvent(ss, o.ev_pass, 0));
         for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(ss, o.ev_geno[t], 0));
     }
@@ -571,7 +584,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
          * position (rounds r01a-g) two passes doubled the concurrent write streams and cost HBM efficiency, so
          * they were chained; at 2 bytes per position the overlap hides each launch's ramp and tail instead:
          * C2 sample 1.25 -> 1.20 ms (measured r01h). */
-        cg_slot& o = c->slot[(c->cur + CG_NSLOT - 1) % CG_NSLOT];
+        cg_slot& o = c->slot[(c->cur + c->n_slot - 1) % c->n_slot];
         static const bool overlap = !(getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP")) == 0);
         if (o.used && !overlap) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
     }

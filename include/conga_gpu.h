@@ -110,6 +110,13 @@ int         cg_set_pointer_mode(cg_ctx* ctx, int mode);
  * written by the kernels directly in that page-locked memory, without a copy call. */
 int         cg_set_async(cg_ctx* ctx, int on);
 
+/* Chromosomes in flight: chromosome k of a context occupies slot k mod n (its own streams, depth array,
+ * count and upload buffers) and a slot is reused when its tenant's genotype kernels are done.  Default and
+ * maximum 6 (measured on a 22-chromosome sample: 3 slots 1.48 ms, 4 slots 1.22, 6 slots 1.09); a caller that
+ * owns only two or three chromosomes per sample (one rank of an 8-GPU job) loses nothing with 4 and has a
+ * third fewer streams to order in every cg_join.  Waits for the context to drain; not inside a chromosome. */
+int         cg_set_slots(cg_ctx* ctx, int n);
+
 /* Page-locked host memory for read batches / results (library owns it). */
 void* cg_alloc_pinned(cg_ctx* ctx, size_t bytes);
 void  cg_free_pinned(cg_ctx* ctx, void* p);

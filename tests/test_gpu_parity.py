@@ -476,3 +476,22 @@ def test_run_chromosomes_one_call_per_sample(ctx, oracle):
               [host(t, CALL_DT, len(ch.dups)) for t, ch in zip(outs[2], chroms)])
     finally:
         ctx.set_pointer_mode(CG_PTR_HOST)
+
+
+def test_set_slots_rotation(ctx, oracle):
+    """cg_set_slots: 4, 2 and again 6 chromosomes in flight; seven chromosomes go through each setting, so every
+    slot of the rotation is reused and the ones outside it stay idle."""
+    rng = np.random.default_rng(33)
+    lens = [300_000, 40_000, 450_000, 16_384, 120_000, 64_000, 700_000]
+    chroms = [synth._chrom("t%d" % i, i, L, rng, max(10, L // 35), 6, 3, True, cnv_hi=max(1500, L // 6)) for i, L in enumerate(lens)]
+    try:
+        for n in (4, 2, 6):
+            ctx.set_slots(n)
+            for ch in chroms:
+                check_chromosome_against_oracle(ctx, oracle, ch, 10, True)
+        with pytest.raises(CongaGpuError):
+            ctx.set_slots(1)
+        with pytest.raises(CongaGpuError):
+            ctx.set_slots(7)
+    finally:
+        ctx.set_slots(6)
