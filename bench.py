@@ -183,9 +183,12 @@ def own_arm(args):
     has_map, mq = wl.has_mappability, wl.mq_threshold
 
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
-    # chromosomes in flight: six by default; a rank that owns two or three chromosomes per sample (8 GPUs) gains
-    # nothing from more than four and has a third fewer streams to order in every cg_join
+    # chromosomes in flight: six by default.  With inputs resident, a rank that owns two or three chromosomes per
+    # sample (8 GPUs) gains nothing from more than four and has a third fewer streams to order in every cg_join;
+    # the end-to-end leg keeps six everywhere (uploads of the chromosomes ahead need the depth: 12.5 against 9.9 G
+    # reads/s at 8 GPUs).  DESIGN.md section 6.
     N_SLOTS = env_int("BENCH_SLOTS", 4 if len(mine) <= 3 else 6)
+    N_SLOTS_E2E = env_int("BENCH_SLOTS_E2E", 6)
     ctx.set_slots(N_SLOTS)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     # the statistics table of each of the two banks (cg_stats_bank): consecutive samples alternate, so
@@ -283,9 +286,9 @@ def own_arm(args):
     lanes = [dict(ctx=ctx, ext=ext)]
     for _ in range(LANES - 1):
         cx = Context(local)
-        cx.set_slots(N_SLOTS)
         lanes.append(dict(ctx=cx, ext=torch.cuda.ExternalStream(cx.stream, device=dev)))
     for ln in lanes:
+        ln["ctx"].set_slots(N_SLOTS_E2E)
         ln["ctx"].set_pointer_mode(CG_PTR_HOST)
         ln["ctx"].set_async(True)
     # inputs: one page-locked copy shared by the lanes; results: DEPTH + 1 buffers per lane, so that sample k's
@@ -433,7 +436,7 @@ def own_arm(args):
            "scaling": "strong", "vs_baseline": None, "dtype": "int16 depth, int32 sums, f32 ordered sum, f64 likelihood",
            "data": "synthetic", "impl": "b200",
            "config": {"workload": wl.name, "chromosomes": n_chrom, "positions": wl.n_positions, "reads": n_reads,
-                      "cnvs": n_cnvs, "mappability": has_map, "partition": "chromosomes, LPT by length", "slots": N_SLOTS,
+                      "cnvs": n_cnvs, "mappability": has_map, "partition": "chromosomes, LPT by length", "slots": N_SLOTS, "slots_e2e": N_SLOTS_E2E,
                       "l2": "inputs+outputs per step (%.1f GB) larger than L2" % (wl.algorithmic_bytes_depth_pass() / 1e9)},
            "cnvs_per_s": round(n_cnvs * args.steps / (ms_dev / 1e3), 1),
            "cnvs_per_s_genotype_kernels_rank0": round(sum(len(c.dels) + len(c.dups) for c in mine) / (cnv_ms / 1e3), 1) if cnv_ms > 0 else None,
