@@ -3,17 +3,18 @@
  * genotype.cu.  There is no CPU implementation of any stage in this library:
  * without a CUDA device cg_create fails and nothing else can be called.
  *
- * Execution model.  A context owns two chromosome slots and six streams:
+ * Execution model.  A context owns CG_NSLOT chromosome slots (cg_set_slots puts 2..CG_NSLOT of them in rotation)
+ * and four streams per slot:
  *   s_copy[k]  host->device copies of GC bytes and read batches of slot k (HOST pointer mode); one stream per slot,
  *              so that the few-megabyte copies of consecutive chromosomes overlap their start-up gaps on the copy engines
- *   s_slot[2]  one per slot: chromosome init, batch marking, rare paths, the fused depth pass
+ *   s_slot[k]  one per slot: chromosome init, batch marking, rare paths, the fused depth pass
  *   s_geno[2]  per slot, deletions / duplications: mappability + CNV uploads, the genotype kernel,
  *              downloads.  The genotype kernel is a chain of dependent loads whose latency grows
  *              several-fold under a depth pass that saturates HBM, so the genotype kernels of
  *              up to CG_NSLOT chromosomes are allowed to run side by side.
  *   s_main     cg_stream(): statistics reset, and what cg_join() orders behind everything else
- * Chromosome k lives in slot k mod CG_NSLOT (its own records, depth, GC, expected-table, count and
- * staging buffers) and nothing of slot 0 depends on slot 1.  So the preparation kernels and the
+ * Chromosome k lives in slot k mod n_slot (its own records, depth, GC, expected-table, count and
+ * staging buffers) and no slot depends on another.  So the preparation kernels and the
  * ramp-up of chromosome k+1's depth pass fill the SMs that chromosome k's pass is draining from,
  * the latency-bound genotype kernels of k run underneath the bandwidth-bound pass of k+1, and the
  * copies of k+1 run underneath the pass of k.  Events order the streams per slot; nothing ever
@@ -272,7 +273,6 @@ cg_ctx* cg_create(int device)
         && cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_left[0], cudaEventDisableTiming) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_left[1], cudaEventDisableTiming) == cudaSuccess
-        /* the genotype kernel is small and latency-bound: let its CTAs be placed first */
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
         && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
         && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
@@ -374,7 +374,6 @@ void cg_free_pinned(cg_ctx* c, void* p) { (void)c; if (p) cudaFreeHost(p); }
 void* cg_stream(cg_ctx* c) { return c ? (void*)c->s_main : nullptr; }
 int64_t cg_launch_count(cg_ctx* c) { return c ? c->launch_count : 0; }
 
-/* make the main stream (cg_stream) wait for everything queued on the others */
 int cg_set_slots(cg_ctx* c, int n)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
@@ -384,9 +383,13 @@ int cg_set_slots(cg_ctx* c, int n)
     int rc = sync_all(c);                      /* slots that leave the rotation must be idle: cg_join no longer visits them */
     if (rc) return rc;
     c->n_slot = n;
+    /* the chromosome that was current may sit in a slot that has just left the rotation: it is closed, the next
+     * call that needs a chromosome has to follow a cg_chrom_begin */
+    c->in_chrom = false; c->finished = false;
     return CG_OK;
 }
 
+/* make the main stream (cg_stream) wait for everything queued on the others */
 int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");

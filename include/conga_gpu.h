@@ -114,7 +114,8 @@ int         cg_set_async(cg_ctx* ctx, int on);
  * count and upload buffers) and a slot is reused when its tenant's genotype kernels are done.  Default and
  * maximum 6 (measured on a 22-chromosome sample: 3 slots 1.48 ms, 4 slots 1.22, 6 slots 1.09); a caller that
  * owns only two or three chromosomes per sample (one rank of an 8-GPU job) loses nothing with 4 and has a
- * third fewer streams to order in every cg_join.  Waits for the context to drain; not inside a chromosome. */
+ * third fewer streams to order in every cg_join.  Waits for the context to drain; not between cg_chrom_begin and
+ * cg_chrom_finish; the finished chromosome is closed (no further cg_genotype on it). */
 int         cg_set_slots(cg_ctx* ctx, int n);
 
 /* Page-locked host memory for read batches / results (library owns it). */
