@@ -878,12 +878,15 @@ int cg_sr_reference(cg_ctx* c, const char* ref_seq, int32_t ref_len)
     if (!ref_seq || ref_len < 0) return fail(c, CG_EINVAL, "bad reference sequence");
     CU(c, cudaSetDevice(c->device));
     auto& r = c->sr;
-    if (!r.st) {
-        CU(c, cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
-        CU(c, cudaMalloc(&r.d_lo, sizeof(int) << 20));
-        CU(c, cudaMalloc(&r.d_hi, sizeof(int) << 20));
+    /* each piece on its own test: a call that failed half way (CG_ENOMEM) is completed by the next one */
+    if (!r.st) CU(c, cudaStreamCreateWithFlags(&r.st, cudaStreamNonBlocking));
+    if (!r.d_lo) CU(c, cudaMalloc(&r.d_lo, sizeof(int) << 20));
+    if (!r.d_hi) CU(c, cudaMalloc(&r.d_hi, sizeof(int) << 20));
+    if (!r.d_n_rows) {
         CU(c, cudaMalloc(&r.d_n_rows, 16));
         r.d_n_map = reinterpret_cast<unsigned long long*>(r.d_n_rows + 2);
+    }
+    if (!r.d_rows) {
         CU(c, cudaMalloc(&r.d_rows, sizeof(cg_splitrow) * (size_t)SR_ROWS_CAP));
         r.rows_cap = SR_ROWS_CAP;
     }
