@@ -12,7 +12,8 @@ committed and are what the GPU box and the CPU test-suite replay.  For each case
      BED outputs + conga.log,
   5. parses the SONIC container independently for the GC bytes the reference consumed.
 
-usage: python tests/golden/make_golden.py
+usage: python tests/golden/make_golden.py            (the three base cases)
+       python tests/golden/make_golden.py edge       (ref_edge only; its own seed, the others are not rewritten)
 """
 import gzip
 import os
@@ -124,7 +125,8 @@ def run_case(tag, chroms, rng, n_reads_per_mb, extra_args, with_map, pileup=Fals
         reads, dels, dups, maps = {}, {}, {}, {}
         tsv = []
         for k, (name, L) in enumerate(chroms):
-            n = int(L / 1e6 * n_reads_per_mb)
+            per_mb = n_reads_per_mb[k] if isinstance(n_reads_per_mb, (list, tuple)) else n_reads_per_mb
+            n = int(L / 1e6 * per_mb)
             r = np.zeros(n, dtype=READ_DT)
             r["pos"] = np.sort(rng.integers(0, L - 100, size=n)).astype(np.int32)
             r["len"] = rng.integers(30, 101, size=n)
@@ -227,6 +229,13 @@ def run_case(tag, chroms, rng, n_reads_per_mb, extra_args, with_map, pileup=Fals
 def main():
     if not os.path.exists(os.path.join(REF, "conga_dump")):
         sys.exit("oracle/_ref/conga_dump missing: run `make -C oracle ref` (needs /root/reference)")
+    if sys.argv[1:] == ["edge"]:
+        # a chromosome without a single read (expected table all 0/0 -> 0, lambda 0 -> 0.01, every score -0.00),
+        # a sparse one (most GC bins empty, most CNVs without reads; only mapq 60 passes --min-mapq 37) and a
+        # name with a Y in it (skipped, A4)
+        rng = np.random.default_rng(20221124 + 7)
+        run_case("ref_edge", [("1", 150_000), ("MT", 120_000), ("GL_Y1", 50_000)], rng, [0, 2000, 500], ["--min-mapq", "37"], True)
+        return
     rng = np.random.default_rng(20221124)
     run_case("ref_plain", [("1", 400_000), ("2", 250_000), ("X", 100_000)], rng, 14000, [], False)
     run_case("ref_map_mq20", [("1", 300_000), ("chr2", 200_000)], rng, 60000, ["--min-mapq", "20"], True)
