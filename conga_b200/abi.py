@@ -230,6 +230,13 @@ class Context:
     def chrom_finish(self, out=None, allow_range: bool = False):
         """HOST mode: returns the cg_chrom_stats record.  DEVICE mode: `out` is a device address or None."""
         if self.mode == CG_PTR_HOST:
+            if getattr(self, "is_async", False):
+                # cg_set_async: the pass writes the row into `out` itself, so it has to be page-locked
+                # (Context.pinned_array) and is valid after sync(); a pageable NumPy array would fault
+                if out is None:
+                    raise CongaGpuError(CG_EINVAL, "asynchronous HOST mode: chrom_finish needs a pinned_array(1, STATS_DT) to write to")
+                self._ck(self.lib.cg_chrom_finish(self.h, _ptr(out)))
+                return None
             st = np.zeros(1, dtype=STATS_DT)
             self._ck(self.lib.cg_chrom_finish(self.h, st.ctypes.data), allow=(CG_ERANGE,) if allow_range else ())
             return st[0]

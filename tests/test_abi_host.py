@@ -43,6 +43,15 @@ def test_no_cpu_fallback_without_gpu():
         abi.Context(0)
 
 
+def test_async_host_mode_refuses_a_pageable_statistics_row():
+    """cg_set_async: the pass writes the statistics row into the caller's page-locked memory itself; the Python
+    mirror must not hand it a pageable temporary (checked before any foreign call, so no GPU is needed)."""
+    c = abi.Context.__new__(abi.Context)          # no cg_create: only the wrapper's own argument check runs
+    c.h, c.lib, c.mode, c.is_async = None, None, abi.CG_PTR_HOST, True
+    with pytest.raises(abi.CongaGpuError):
+        c.chrom_finish()
+
+
 def test_product_does_not_touch_the_oracle():
     """Nothing under conga_b200/ may import, link or execute oracle/ (tier rule 3)."""
     for dirpath, _d, files in os.walk(os.path.join(ROOT, "conga_b200")):
