@@ -494,6 +494,8 @@ def reference_arm(args):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+    phases = {}                                   # CPU-seconds per reference function, summed over the processes of the last step
+
     def run_once(subset, base_args):
         t0 = time.perf_counter()
         if kind == "reference":
@@ -503,11 +505,19 @@ def reference_arm(args):
                 wd = os.path.join(tmp, "w%d" % i)
                 os.makedirs(wd, exist_ok=True)
                 procs.append(subprocess.Popen([ref_path] + base_args + ["--first-chr", str(c.index), "--last-chr", str(c.index),
-                                               "--out", os.path.join(wd, "o")], cwd=wd, stdout=subprocess.DEVNULL,
+                                               "--out", os.path.join(wd, "o")], cwd=wd, stdout=subprocess.PIPE,
                                               stderr=subprocess.DEVNULL))
+            phases.clear()
             for p in procs:
-                if p.wait() != 0:
+                line = p.communicate()[0]             # one short JSON line per process: per-phase seconds
+                if p.returncode != 0:
                     raise RuntimeError("ref_path failed")
+                try:
+                    for k, v in json.loads(line.decode().strip().splitlines()[-1]).items():
+                        if k.endswith("_s"):
+                            phases[k] = phases.get(k, 0.0) + float(v)
+                except (ValueError, IndexError):
+                    pass
         else:
             import multiprocessing as mp
             with mp.get_context("fork").Pool(min(ncpu, len(subset))) as pool:
@@ -546,7 +556,10 @@ def reference_arm(args):
                       "reads": wl.n_reads, "cnvs": wl.n_cnvs, "mappability": wl.has_mappability},
            "cnvs_per_s": round(cnvs * args.steps / t, 1),
            "cpu_baseline": {"value": round(value, 1), "unit": "reads/s", "cores": cores, "kind": kind, "sample": sample,
-                            "host_cores_available": ncpu},
+                            "host_cores_available": ncpu,
+                            # where the reference spends its time: init_rd_per_chr / count_reads_bam /
+                            # calc_mean_per_chr / find_SVs, CPU-seconds summed over the processes of the last step
+                            "phase_cpu_seconds_last_step": {k: round(v, 4) for k, v in sorted(phases.items())} or None},
            "e2e": {"value": round(value, 1), "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out), flush=True)
