@@ -134,7 +134,8 @@ struct cg_ctx {
     long long launch_count = 0;
 };
 
-static char g_err[512] = "no error";
+/* what cg_last_error(NULL) returns: per thread, because contexts are driven from one thread each (one per GPU) */
+static thread_local char g_err[512] = "no error";
 
 int cg_fail(cg_ctx* c, int code, const char* fmt, ...)
 {

@@ -95,7 +95,8 @@ typedef struct cg_chrom_stats {
 
 typedef struct cg_ctx cg_ctx;
 
-/* Context on CUDA device `device`.  NULL on failure (cg_last_error(NULL) says why). */
+/* Context on CUDA device `device`.  NULL on failure (cg_last_error(NULL) says why: the last error of the
+ * calling thread). */
 cg_ctx*     cg_create(int device);
 void        cg_destroy(cg_ctx* ctx);
 const char* cg_last_error(cg_ctx* ctx);
