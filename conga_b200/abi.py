@@ -21,6 +21,10 @@ CG_PTR_HOST, CG_PTR_DEVICE = 0, 1
 CG_GC_BINS = 101
 CG_NSLOTS = 4
 CG_TILE = 16384
+CG_CHUNK = 2048
+CG_JMAX = 32
+CG_COMM_ID_BYTES = 128
+CG_JOB_ANNOTATION_RESIDENT = 1
 
 # struct layouts of include/conga_gpu.h as NumPy dtypes
 READ_DT = np.dtype([("pos", "<i4"), ("len", "<u2"), ("mapq", "u1"), ("fl", "u1")])
@@ -37,10 +41,10 @@ SPLITROW_DT = np.dtype([("pos", "<i4"), ("pos_map", "<i4"), ("left_start", "<i4"
                         ("right_end", "<i4"), ("sv_type", "u1"), ("pad", "u1", (7,))])
 # cg_chrom_job: pointers as integers (host or device addresses, whatever the pointer mode says)
 CHROM_JOB_DT = np.dtype([("chr_index", "<i4"), ("chrom_len", "<i4"), ("gc", "<u8"), ("n_windows", "<i4"), ("mq_threshold", "<i4"),
-                         ("reads", "<u8"), ("n_reads", "<u8"), ("runs", "<u8"), ("n_runs", "<u8"), ("use_mappability", "<i4"), ("pad", "<i4"),
+                         ("reads", "<u8"), ("n_reads", "<u8"), ("runs", "<u8"), ("n_runs", "<u8"), ("use_mappability", "<i4"), ("flags", "<i4"),
                          ("dels", "<u8"), ("n_del", "<u8"), ("del_calls", "<u8"), ("dups", "<u8"), ("n_dup", "<u8"), ("dup_calls", "<u8"),
-                         ("stats", "<u8")])
-assert CHROM_JOB_DT.itemsize == 120
+                         ("stats", "<u8"), ("reads_pos", "<u8"), ("reads_mapq", "<u8")])
+assert CHROM_JOB_DT.itemsize == 136
 assert HALF_DT.itemsize == 16 and SPLITROW_DT.itemsize == 32
 assert READ_DT.itemsize == 8 and CNV_DT.itemsize == 8 and MAPIV_DT.itemsize == 16
 assert MAPRUN_DT.itemsize == 16 and CALL_DT.itemsize == 56 and STATS_DT.itemsize == 204 * 8
@@ -60,6 +64,7 @@ SYMBOLS = {
     "cg_free_pinned": (None, [_P, _P]),
     "cg_chrom_begin": (_I, [_P, _I, C.c_int32, _P, C.c_int32, _I]),
     "cg_push_reads": (_I, [_P, _P, _Z]),
+    "cg_push_reads_compact": (_I, [_P, _P, _P, _Z]),
     "cg_chrom_finish": (_I, [_P, _P]),
     "cg_get_expected": (_I, [_P, _P]),
     "cg_set_expected": (_I, [_P, _P]),
@@ -82,6 +87,11 @@ SYMBOLS = {
     "cg_stats_reset": (_I, [_P]),
     "cg_stats_bank": (_I, [_P, _I]),
     "cg_stats_row": (_I, [_P, _I, _P]),
+    "cg_comm_unique_id": (_I, [_P]),
+    "cg_comm_init_rank": (_I, [_P, _I, _I, _P]),
+    "cg_comm_init_all": (_I, [C.POINTER(_P), _I]),
+    "cg_comm_destroy": (_I, [_P]),
+    "cg_stats_allreduce": (_I, [_P, C.c_int32]),
     "cg_set_profiling": (_I, [_P, _I]),
     "cg_kernel_times": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cg_launch_count": (C.c_int64, [_P]),
@@ -227,6 +237,16 @@ class Context:
         assert n is not None
         self._ck(self.lib.cg_push_reads(self.h, _ptr(reads), n))
 
+    def push_reads_compact(self, pos, mapq=None, n: Optional[int] = None):
+        """cg_push_reads_compact: an int32 position plane and a uint8 mapq plane (None: no plane, needs a
+        negative mq_threshold)."""
+        if isinstance(pos, np.ndarray):
+            assert pos.dtype == np.int32 and pos.flags.c_contiguous
+            assert mapq is None or (mapq.dtype == np.uint8 and mapq.flags.c_contiguous and len(mapq) == len(pos))
+            n = len(pos) if n is None else n
+        assert n is not None
+        self._ck(self.lib.cg_push_reads_compact(self.h, _ptr(pos), _ptr(mapq), n))
+
     def chrom_finish(self, out=None, allow_range: bool = False):
         """HOST mode: returns the cg_chrom_stats record.  DEVICE mode: `out` is a device address or None."""
         if self.mode == CG_PTR_HOST:
@@ -364,6 +384,19 @@ class Context:
     def stats_bank(self, bank: int):
         self._ck(self.lib.cg_stats_bank(self.h, int(bank)))
 
+    def comm_init_rank(self, n_ranks: int, rank: int, uid: bytes):
+        """cg_comm_init_rank: join the communicator identified by `uid` (comm_unique_id() of one rank)."""
+        assert len(uid) == CG_COMM_ID_BYTES
+        buf = C.create_string_buffer(uid, CG_COMM_ID_BYTES)
+        self._ck(self.lib.cg_comm_init_rank(self.h, n_ranks, rank, C.cast(buf, C.c_void_p)))
+
+    def comm_destroy(self):
+        self._ck(self.lib.cg_comm_destroy(self.h))
+
+    def stats_allreduce(self, n_rows: int):
+        """cg_stats_allreduce: the path's one collective, queued on cg_stream behind everything queued so far."""
+        self._ck(self.lib.cg_stats_allreduce(self.h, int(n_rows)))
+
     def stats_row(self, chr_index: int):
         st = np.zeros(1, dtype=STATS_DT)
         self._ck(self.lib.cg_stats_row(self.h, chr_index, st.ctypes.data))
@@ -379,12 +412,25 @@ class Context:
         return list(ms), list(n)
 
 
+def comm_unique_id() -> bytes:
+    """cg_comm_unique_id: 128 bytes one rank creates and every rank passes to Context.comm_init_rank."""
+    lib = load_library()
+    buf = C.create_string_buffer(CG_COMM_ID_BYTES)
+    rc = lib.cg_comm_unique_id(C.cast(buf, C.c_void_p))
+    if rc != CG_OK:
+        raise CongaGpuError(rc, lib.cg_last_error(None).decode())
+    return buf.raw
+
+
 def chrom_job(chr_index, chrom_len, gc, n_windows, mq_threshold, reads, n_reads, runs=None, n_runs=0, use_mappability=False,
-              dels=None, n_del=0, del_calls=None, dups=None, n_dup=0, dup_calls=None, stats=None) -> np.ndarray:
-    """One cg_chrom_job record; array arguments may be NumPy arrays, torch tensors or raw addresses."""
+              dels=None, n_del=0, del_calls=None, dups=None, n_dup=0, dup_calls=None, stats=None,
+              reads_pos=None, reads_mapq=None, flags=0) -> np.ndarray:
+    """One cg_chrom_job record; array arguments may be NumPy arrays, torch tensors or raw addresses.
+    reads=None with reads_pos (and optionally reads_mapq) selects the compact record planes."""
     j = np.zeros(1, dtype=CHROM_JOB_DT)
     j["chr_index"], j["chrom_len"], j["gc"], j["n_windows"], j["mq_threshold"] = chr_index, chrom_len, _ptr(gc), n_windows, mq_threshold
     j["reads"], j["n_reads"] = _ptr(reads), n_reads
+    j["reads_pos"], j["reads_mapq"], j["flags"] = _ptr(reads_pos), _ptr(reads_mapq), flags
     j["runs"], j["n_runs"], j["use_mappability"] = _ptr(runs) if n_runs else 0, n_runs, int(bool(use_mappability))
     j["dels"], j["n_del"], j["del_calls"] = _ptr(dels) if n_del else 0, n_del, _ptr(del_calls) if n_del else 0
     j["dups"], j["n_dup"], j["dup_calls"] = _ptr(dups) if n_dup else 0, n_dup, _ptr(dup_calls) if n_dup else 0

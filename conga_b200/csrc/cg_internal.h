@@ -9,47 +9,92 @@
 
 /* ---- geometry of the fused depth pass (K1+K2+K3) -------------------------
  * The unit of work is a CHUNK of 2048 positions, owned by one warp (4 KB of packed u16 bins
- * in shared memory).  Record counts are kept at three levels so that a chunk's scan carry is
- * three short coalesced loads: per chunk, per GROUP of 32 chunks, per SUPER of 32 groups. */
+ * in shared memory).  Depth sums are kept at three levels so that the depth sum in front of a
+ * chunk is three short coalesced loads: per chunk, per GROUP of 32 chunks, per SUPER of 32 groups.
+ *
+ * A SUBMISSION is what one set of kernel launches works on: up to CG_JMAX chromosomes ("jobs").
+ * cg_run_chromosomes hands a whole sample over as one submission (one init, one mark, one pass,
+ * one finalize, one run-index and one genotype launch for all of its chromosomes); the
+ * per-chromosome entry points (cg_chrom_begin ... cg_genotype) are submissions of one job.
+ * The jobs of a submission share the slot's chunk space: job j owns the chunks
+ * [chunk0, chunk0 + n_chunks] of the slot's depth / count arrays, chunk0 a multiple of 1024 so that
+ * groups and supers never straddle two chromosomes. */
 #define CG_CHUNK        2048
 #define CG_CHUNK_SHIFT  11
 #define CG_GROUP_SHIFT  16            /* 32 chunks  = 65,536 positions   */
 #define CG_SUPER_SHIFT  21            /* 32 groups  = 2,097,152 positions */
+#define CG_SUPER_CHUNKS 1024
 #define CG_PASS_THREADS 256
-#define CG_PILEUP_PROBE 16384         /* k_mark_batch looks this many records back for an equal pos */
 #define CG_STATS_WORDS 204            /* int64 words per chromosome row = sizeof(cg_chrom_stats)/8 */
+#define CG_JMAX         32            /* chromosomes one submission carries */
+#define CG_PART_WORDS   (2 * CG_GC_BINS)      /* int32 words one CTA of the pass leaves per job: 101 sums, 101 counts */
 
-/* Device-side error/condition bits, one u32 word per context. */
+/* Device-side condition bits, first control word of a job. */
 #define CG_FLAG_UNSORTED   1u         /* a pushed record had pos < its predecessor */
 #define CG_FLAG_RANGE      2u         /* a record or CNV outside [0, chrom_len) */
-#define CG_FLAG_PILEUP     4u         /* > CG_PILEUP_PROBE records share one pos: int16 wrap possible */
-/* words of the per-context u32 control block (d_flags) */
+/* u32 control words of a job (cg_dev_job::ctl) */
+#define CG_CTL_WORDS 8
 #define CG_W_FLAGS   0
-#define CG_W_TILE    1                /* dynamic chunk counter of the depth pass */
-#define CG_W_DONE    2                /* CTAs of the depth pass that have flushed their statistics */
+#define CG_W_PASSED  2                /* u64 (words 2,3): records with mapq > threshold, bam_data.c:214 */
+/* u32 control words of a slot (cg_sub::sctl) */
+#define CG_SW_TILE   0                /* dynamic work counter of the depth pass */
+#define CG_SW_GENO   1                /* ... of the genotype kernel */
 
-struct cg_counts {                    /* one allocation per slot, see cgk_counts_layout */
-    int32_t* chunk_lo;                /* [n_chunks+1] first record index of each chunk (sorted input) */
-    int32_t* cnt1;                    /* [n_chunks]   sum of the (int16) depths of each chunk */
-    int32_t* cnt2;                    /* [n_groups]   ... of each group of 32 chunks */
-    int32_t* cnt3;                    /* [n_supers]   ... of each super of 32 groups */
+struct cg_counts {                    /* one allocation per slot, see cgk_counts_layout; indices are chunks of the slot's chunk space */
+    int32_t* chunk_lo;                /* [n_space] first record index of each chunk (sorted input) */
+    int32_t* cnt1;                    /* [n_space]   sum of the (int16) depths of each chunk */
+    int32_t* cnt2;                    /* [n_space/32]   ... of each group of 32 chunks */
+    int32_t* cnt3;                    /* [n_space/1024] ... of each super of 32 groups */
 };
 
-struct cg_pass_args {
-    const cg_read* reads;             /* all records of the chromosome, device */
-    long long      n_reads;
+/* One chromosome of a submission, as the kernels see it. */
+struct cg_dev_job {
+    /* records: either 8-byte cg_read records or the compact planes (cg_push_reads_compact) */
+    const cg_read*  reads;
+    const int32_t*  rec_pos;
+    const uint8_t*  rec_mapq;         /* may be NULL with rec_pos when mq_threshold < 0: every record passes */
+    long long       n_reads;          /* records of the chromosome so far */
+    long long       mark_first, mark_n;   /* k_mark: the batch this launch looks at */
+    int32_t         mark_blk0;        /* first 256-record block of this job in the k_mark launch */
+    int32_t         mq_threshold;
+    /* geometry */
+    int32_t         chrom_len, n_chunks;
+    int32_t         chunk0;           /* first chunk in the slot's chunk space, multiple of CG_SUPER_CHUNKS */
+    int32_t         work0;            /* first work index of the pass (prefix of n_chunks over the jobs) */
+    const int8_t*   gc;               /* SONIC GC byte per 100-position window */
+    /* depth-side results */
+    long long*      stats_row;        /* this chromosome's int64[204] row in the statistics bank */
+    long long*      row_out;          /* NULL, or where k_finalize also writes the row: page-locked host memory
+                                         (asynchronous HOST mode) or the caller's device buffer (DEVICE mode) */
+    float*          expected;         /* [128] expected_read_depth[101] */
+    unsigned int*   ctl;              /* CG_W_* words of this job */
+    /* genotype side */
+    const cg_maprun* runs;
+    int32_t*        run_idx;          /* first run per 16384 positions */
+    int32_t         n_runs, has_map;
+    int32_t         run_blk0;         /* first 256-run block of this job in the k_run_index launch */
+    int32_t         chr_index;
+    const cg_cnv*   cnv[2];           /* [0] deletions, [1] duplications */
+    cg_call*        calls[2];
+    int32_t         n_cnv[2];
+    int32_t         cnv0[2];          /* first global CNV index of each kind in the k_genotype launch */
+};
+
+/* What a set of launches works on.  jobs == NULL: a single job travels as the second kernel parameter. */
+struct cg_sub {
+    const cg_dev_job* jobs;
+    int32_t        n_jobs;
+    int32_t        n_work;            /* chunks of all jobs */
+    int32_t        n_space;           /* chunks of the slot's chunk space in use (multiple of CG_SUPER_CHUNKS) */
+    int32_t        n_mark_blocks, n_run_blocks, n_cnv;
     cg_counts      k;
-    const int8_t*  gc;                /* SONIC GC byte per 100-position window */
-    int32_t        chrom_len;
-    int32_t        n_chunks;
-    int            mq_threshold;
-    int16_t*       depth;             /* [n_chunks*CG_CHUNK] */
-    uint32_t*      depth32;           /* unsorted fallback: per-position u32 counts (zero at rest) */
-    unsigned int*  ctl;               /* CG_W_* control words */
-    long long*     stats;             /* this chromosome's int64[204] row */
-    long long*     host_row;          /* NULL, or page-locked host memory the last CTA copies the finished row to */
-    float*         expected;          /* [101] written by the last CTA to finish */
+    int16_t*       depth;             /* [n_space * CG_CHUNK] */
+    uint32_t*      depth32;           /* NULL, or the out-of-order path's per-position u32 counts (zero at rest) */
+    int32_t*       partial;           /* [pass CTAs][n_jobs][CG_PART_WORDS] */
+    int32_t        n_pass_ctas;
+    unsigned int*  sctl;              /* CG_SW_* words of the slot */
     unsigned int*  sticky;            /* context-wide word: CG_FLAG_RANGE is copied here */
+    unsigned int*  h_flags;           /* NULL, or page-locked [n_jobs]: each job's flag word for the host */
 };
 
 #ifdef __cplusplus
@@ -59,28 +104,25 @@ extern "C++" {
 int  cg_fail(cg_ctx* c, int code, const char* fmt, ...);
 void cg_flatten_rows(const cg_mapiv* rows, size_t n, int32_t chrom_len, std::vector<cg_maprun>& out);
 /* depth_pass.cu */
-size_t      cgk_counts_words(int n_chunks);                       /* int32 words one slot's counts need */
-cg_counts   cgk_counts_layout(int32_t* base, int n_chunks);
-cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* counts_base, int n_chunks, long long* stats_row, unsigned int* ctl);
-cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
-                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
-                           unsigned int* ctl, long long* stats_row);
-cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_reads, uint32_t* depth32,
-                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
-                           const unsigned int* ctl, int n_sms);
-cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms);
-cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int n_chunks, int32_t* prefix);
+size_t      cgk_counts_words(int n_space);                        /* int32 words the counts of a chunk space need */
+cg_counts   cgk_counts_layout(int32_t* base, int n_space);
+int         cgk_job_space(int n_chunks);                          /* chunks of chunk space a job of n_chunks occupies */
+int         cgk_pass_grid(int n_work, int n_sms);                 /* CTAs of the pass, = rows of cg_sub::partial */
+cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int32_t* counts_base);
+cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
+cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
+cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
+cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
+cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int chunk0, int n_chunks, int32_t* prefix);
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
-int         cgk_depth_pass_ctas_per_sm(void);
 int         cgk_carveout(void);                                   /* shared-memory carve-out (percent) every kernel asks for */
 cudaError_t cgk_configure_depth(void);                            /* once per process, after the device is selected */
 cudaError_t cgk_configure_genotype(void);
 
 /* genotype.cu */
-cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
-                         const int16_t* depth, const cg_counts& counts, const int8_t* gc, const float* expected,
-                         const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
-                         int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms);
+cudaError_t cgk_genotype(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
+int         cgk_run_index_words(int32_t chrom_len);
+cudaError_t cgk_run_index(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 /* split_read.cu */
 size_t      cgk_sr_sort_temp_bytes(int n);
 cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, unsigned* keys_a, unsigned* keys_b, int* vals_a, int* vals_b,
@@ -95,8 +137,6 @@ cudaError_t cgk_configure_split(void);
 /* gc_profile.cu — SONIC's GC bytes from the bases of one chromosome (sonic/sonic_reference.c:30-106) */
 cudaError_t cgk_gc_profile(cudaStream_t s, const char* bases, long long n_bases, int8_t* out, int n_windows, int n_sms);
 cudaError_t cgk_configure_gc_profile(void);
-int         cgk_run_index_words(int32_t chrom_len);
-cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len);
 }
 #endif
 

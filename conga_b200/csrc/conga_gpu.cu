@@ -3,24 +3,24 @@
  * genotype.cu.  There is no CPU implementation of any stage in this library:
  * without a CUDA device cg_create fails and nothing else can be called.
  *
- * Execution model.  A context owns CG_NSLOT chromosome slots (cg_set_slots puts 2..CG_NSLOT of them in rotation)
- * and four streams per slot:
- *   s_copy[k]  host->device copies of GC bytes and read batches of slot k (HOST pointer mode); one stream per slot,
- *              so that the few-megabyte copies of consecutive chromosomes overlap their start-up gaps on the copy engines
- *   s_slot[k]  one per slot: chromosome init, batch marking, rare paths, the fused depth pass
- *   s_geno[2]  per slot, deletions / duplications: mappability + CNV uploads, the genotype kernel,
- *              downloads.  The genotype kernel is a chain of dependent loads whose latency grows
- *              several-fold under a depth pass that saturates HBM, so the genotype kernels of
- *              up to CG_NSLOT chromosomes are allowed to run side by side.
- *   s_main     cg_stream(): statistics reset, and what cg_join() orders behind everything else
- * Chromosome k lives in slot k mod n_slot (its own records, depth, GC, expected-table, count and
- * staging buffers) and no slot depends on another.  So the preparation kernels and the
- * ramp-up of chromosome k+1's depth pass fill the SMs that chromosome k's pass is draining from,
- * the latency-bound genotype kernels of k run underneath the bandwidth-bound pass of k+1, and the
- * copies of k+1 run underneath the pass of k.  Events order the streams per slot; nothing ever
- * waits on the host unless the caller asked for blocking HOST-mode semantics.  With profiling on
- * (cg_set_profiling) the slots are chained one behind the other so that the event brackets time
- * each kernel alone.
+ * Execution model.  The unit of device work is a SUBMISSION: up to CG_JMAX chromosomes ("jobs") that
+ * every kernel of the path handles in one launch (cg_internal.h).  cg_run_chromosomes hands a whole
+ * sample over as one submission; the per-chromosome entry points are submissions of one job whose
+ * phases (init | record sweep per pushed batch | pass + finalize | genotype) are launched by
+ * cg_chrom_begin | cg_push_reads | cg_chrom_finish | cg_genotype.  A context owns CG_NSLOT slots
+ * (cg_set_slots puts 2..CG_NSLOT of them in rotation); submission k lives in slot k mod n_slot with
+ * its own arrays and streams:
+ *   s_copy     host->device copies of GC bytes, records, mappability runs (HOST pointer mode)
+ *   s_work     job table upload, init, record sweep, depth pass, finalize
+ *   s_geno[2]  mappability index + genotype kernel ([1]: the duplications of a per-chromosome
+ *              cg_genotype call, so that both kinds run side by side).  The genotype kernel is a chain
+ *              of dependent loads whose latency grows several-fold under a depth pass that saturates
+ *              HBM, so it runs on high-priority streams underneath the pass of the next submission.
+ *   s_main     cg_stream(): what cg_join() orders behind everything else; the collective
+ * No slot depends on another.  Events order the streams per slot; nothing ever waits on the host
+ * unless the caller asked for blocking HOST-mode semantics, a slot is reused whose previous
+ * submission has not finished yet, or a buffer has to grow.  With profiling on (cg_set_profiling)
+ * the slots are chained one behind the other so that the event brackets time each kernel alone.
  */
 #include "cg_internal.h"
 
@@ -29,57 +29,79 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
+#include <mutex>
 #include <vector>
 
 #define CG_MAX_CHROMS 4096            /* rows of the statistics table */
 #ifndef CG_NSLOT
-#define CG_NSLOT 6                    /* measured r01h, C2 resident: 3 slots 1.48 ms per sample, 4 slots 1.22, 6 slots 1.09 (host-issue bound) */
+#define CG_NSLOT 6
 #endif
+#define CG_NBANK 2
+#define CG_PASS_GRID_MAX (160 * 3)    /* rows of a slot's partial table: SMs x CTAs per SM the pass may ask for */
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
 
-/* everything one chromosome needs from cg_chrom_begin to its last cg_genotype */
+/* everything one submission needs from its first launch to its last genotype kernel */
 struct cg_slot {
-    /* geometry */
-    int chr_index = -1;
-    int32_t chrom_len = 0;
-    int n_chunks = 0;
-    long long* d_row = nullptr;               /* this chromosome's int64[204] row in the statistics bank it was begun under */
-    /* depth side */
-    cg_read* d_reads = nullptr;       size_t reads_cap = 0;
-    int8_t* d_gc = nullptr;           size_t gc_cap = 0;
-    int32_t* d_counts = nullptr;      size_t counts_cap = 0;      /* chunk bounds + three count levels (cg_counts) */
+    /* the submission */
+    int n_jobs = 0;
+    bool sample = false;                      /* cg_run_chromosomes submission: the job table lives in d_jobs */
+    bool check = false;                       /* ... whose per-job flags the host has not looked at yet */
+    int ptr_mode = CG_PTR_HOST; bool async = false;      /* modes the submission was made under (re-runs) */
+    cg_dev_job hj[CG_JMAX];                   /* host mirror of the job table */
+    cg_sub sub;                               /* what the kernels are launched with */
+    std::vector<cg_chrom_job> src;            /* the caller's jobs (a flagged job is re-run from here) */
+    cg_dev_job* d_jobs = nullptr;             /* [CG_JMAX] */
+    cg_dev_job* h_jobs = nullptr;             /* page-locked staging of the table upload */
+    unsigned int* h_flags = nullptr;          /* page-locked [CG_JMAX]: flag word of every job, written by k_finalize */
+    cudaEvent_t ev_table = nullptr;           /* s_work: the table upload has read h_jobs */
+    /* arrays over the slot's chunk space */
     int16_t* d_depth = nullptr;       size_t pos_cap = 0;
-    float* d_expected = nullptr;              /* [101] (128 allocated) */
-    unsigned int* d_ctl = nullptr;            /* CG_W_* control words */
-    const cg_read* reads_ptr = nullptr;       /* own buffer or the caller's (DEVICE mode) */
-    const int8_t* gc_ptr = nullptr;
-    /* genotype side */
+    int32_t* d_counts = nullptr;      size_t counts_cap = 0;      /* chunk bounds + three count levels (cg_counts) */
+    uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;     /* out-of-order path (per-chromosome entry points); zero at rest */
+    int32_t* d_partial = nullptr;             /* [CG_PASS_GRID_MAX][CG_JMAX][CG_PART_WORDS] */
+    float* d_expected = nullptr;              /* [CG_JMAX][128] */
+    unsigned int* d_ctl = nullptr;            /* [CG_JMAX][CG_CTL_WORDS] + slot words */
+    int32_t* d_run_idx = nullptr;     size_t run_idx_cap = 0;     /* first run per 16384 positions, all jobs */
+    /* staging of the caller's host arrays */
+    cg_read* d_reads = nullptr;       size_t reads_cap = 0;       /* per-chromosome entry points: records appended batch by batch */
+    int32_t* d_pos = nullptr;         size_t rpos_cap = 0;
+    uint8_t* d_mapq = nullptr;        size_t rmapq_cap = 0;
+    int8_t* d_gc = nullptr;           size_t gc_cap = 0;
     cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
-    int32_t* d_run_idx = nullptr;     size_t run_idx_cap = 0;    /* first run per 16384 positions */
-    const cg_maprun* runs_ptr = nullptr; int n_runs = 0; int has_map = 0;
-    char* d_arena = nullptr;          size_t arena_cap = 0, arena_used = 0;   /* CNV + call staging, HOST mode */
+    char* d_in = nullptr;             size_t in_cap = 0;          /* sample submissions: one arena for records, GC bytes, runs */
+    char* d_arena = nullptr;          size_t arena_cap = 0, arena_used = 0;   /* CNV + call staging, blocking HOST mode */
+    int rec_fmt = 0;                          /* per-chromosome pushes: 0 none yet, 1 cg_read, 2 planes, 3 planes without mapq */
     /* ordering */
+    cudaStream_t s_copy = nullptr, s_work = nullptr, s_geno[2] = {nullptr, nullptr};
     cudaEvent_t ev_copy = nullptr;            /* s_copy: last upload for this slot */
-    cudaEvent_t ev_pass = nullptr;            /* slot stream: the pass (and the table) of this slot is done */
-    cudaStream_t s_geno[2] = {nullptr, nullptr};   /* [0] deletions (and uploads), [1] duplications */
+    cudaEvent_t ev_pass = nullptr;            /* s_work: the pass and the finalize of this slot are done */
     cudaEvent_t ev_geno[2] = {nullptr, nullptr};   /* s_geno[t]: last genotype work queued for this slot */
-    cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded */
-    bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false, wait_reset = false;
-    uint32_t* d_depth32 = nullptr;    size_t depth32_cap = 0;    /* out-of-order path only; zero at rest */
+    cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded and indexed */
+    bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false;
+    bool dirty_work = false, dirty_geno[2] = {false, false};     /* work queued since the last cg_join */
+};
+
+/* NCCL, resolved at run time (cg_comm_*): only the five calls the one collective needs */
+typedef struct cg_nccl_comm* cg_nccl_comm_t;
+struct cg_nccl_id { char internal[CG_COMM_ID_BYTES]; };      /* ncclUniqueId: 128 bytes, passed by value */
+struct cg_nccl_api {
+    void* handle = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(cg_nccl_comm_t*, int, cg_nccl_id, int) = nullptr;
+    int (*CommInitAll)(cg_nccl_comm_t*, int, const int*) = nullptr;
+    int (*CommDestroy)(cg_nccl_comm_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, cg_nccl_comm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    int (*GroupStart)(void) = nullptr;
+    int (*GroupEnd)(void) = nullptr;
 };
 
 struct cg_ctx {
     int device = 0;
     int n_sms = 148;
-    cudaStream_t s_copy[CG_NSLOT] = {}, s_main = nullptr;
-    cudaStream_t s_slot[CG_NSLOT] = {};
-    cudaStream_t s_bank = nullptr;            /* clears a statistics bank that is selected again */
-    cudaEvent_t ev_reset = nullptr;           /* the current statistics bank has been cleared */
-    cudaEvent_t ev_left[2] = {nullptr, nullptr};   /* s_main: everything queued when the bank was left (its collective) */
-    bool bank_left[2] = {false, false};
-    int bank = 0;
-    bool dirty = false;                       /* work queued since the last cg_join */
+    cudaStream_t s_main = nullptr;
     cudaEvent_t ev_join = nullptr;
     int ptr_mode = CG_PTR_HOST;
     bool async = false;
@@ -87,16 +109,22 @@ struct cg_ctx {
 
     cg_slot slot[CG_NSLOT];
     int n_slot = CG_NSLOT;                    /* slots in rotation (cg_set_slots); the others stay idle */
-    int cur = 0;                              /* slot of the current chromosome */
+    int cur = 0;                              /* slot of the current chromosome (per-chromosome entry points) */
     long long n_begun = 0;
 
-    /* current chromosome */
+    /* current chromosome (per-chromosome entry points) */
     bool in_chrom = false, finished = false;
-    int mq_threshold = -1;
-    long long n_reads = 0;
     int n_rows = 0;
 
-    long long* d_stats = nullptr;             /* [2 banks][CG_MAX_CHROMS][204] */
+    /* statistics tables: [bank][CG_MAX_CHROMS][204]; d_stats_all only with a communicator */
+    long long* d_stats = nullptr;
+    long long* d_stats_all = nullptr;
+    int bank = 0;
+    cudaEvent_t ev_bank_read[CG_NBANK] = {nullptr, nullptr};     /* s_main: the collective that reads this bank */
+    bool bank_read[CG_NBANK] = {false, false};
+    cg_nccl_comm_t comm = nullptr;
+    int comm_ranks = 0;
+
     unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
 
     /* pinned staging */
@@ -120,7 +148,7 @@ struct cg_ctx {
     } sr;
 
     /* largest sizes any slot has needed, per buffer kind (see grow()) */
-    size_t hw_gc = 0, hw_reads = 0, hw_runs = 0, hw_run_idx = 0, hw_chunks = 0;
+    size_t hw_gc = 0, hw_reads = 0, hw_rpos = 0, hw_rmapq = 0, hw_runs = 0, hw_run_idx = 0, hw_pos = 0, hw_in = 0;
 
     /* cg_gc_profile staging (HOST pointer mode) */
     char* d_gc_bases = nullptr; size_t gc_bases_cap = 0;
@@ -155,12 +183,14 @@ static inline bool blocking(const cg_ctx* c) { return c->ptr_mode == CG_PTR_HOST
 
 static int sync_all(cg_ctx* c)
 {
-    for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_copy[i]));
     CU(c, cudaStreamSynchronize(c->s_main));
-    CU(c, cudaStreamSynchronize(c->s_bank));
     if (c->sr.st) CU(c, cudaStreamSynchronize(c->sr.st));
-    for (int i = 0; i < CG_NSLOT; i++) CU(c, cudaStreamSynchronize(c->s_slot[i]));
-    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(c->slot[i].s_geno[t]));
+    for (int i = 0; i < CG_NSLOT; i++) {
+        cg_slot& s = c->slot[i];
+        CU(c, cudaStreamSynchronize(s.s_copy));
+        CU(c, cudaStreamSynchronize(s.s_work));
+        for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(s.s_geno[t]));
+    }
     return CG_OK;
 }
 
@@ -170,8 +200,8 @@ template <typename T>
 static int grow(cg_ctx* c, T** p, size_t* cap, size_t need, size_t keep_elems = 0, size_t* high_water = nullptr)
 {
     if (need <= *cap) return CG_OK;
-    /* chromosomes rotate through the slots, so a slot that has to grow goes straight to the largest size any
-     * slot has needed: every slot reallocates at most once per buffer after the largest chromosome was seen */
+    /* submissions rotate through the slots, so a slot that has to grow goes straight to the largest size any
+     * slot has needed: every slot reallocates at most once per buffer after the largest submission was seen */
     size_t ncap = std::max(need, *cap + *cap / 2);
     if (high_water) { ncap = std::max(ncap, *high_water); *high_water = ncap; }
     int rc = sync_all(c);
@@ -189,7 +219,6 @@ struct prof_scope {
     cg_ctx* c; cudaStream_t s; cg_evpair ev; bool on;
     prof_scope(cg_ctx* c_, cudaStream_t s_, int slot, int n_launches) : c(c_), s(s_), on(c_->profiling) {
         c->launch_count += n_launches;
-        c->dirty = true;
         if (!on) return;
         if (!c->ev_free.empty()) { ev = c->ev_free.back(); c->ev_free.pop_back(); }
         else { cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); }
@@ -238,6 +267,9 @@ static int sr_grow(cg_ctx* c, T** p, size_t* cap, size_t need)
     return CG_OK;
 }
 
+static int settle_samples(cg_ctx* c);
+static int settle_slot(cg_ctx* c, cg_slot& s);
+
 extern "C" {
 
 int cg_abi_version(void) { return CG_ABI_VERSION; }
@@ -267,41 +299,45 @@ cg_ctx* cg_create(int device)
     c->n_sms = prop.multiProcessorCount;
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
-    bool ok = true;
-    for (int i = 0; ok && i < CG_NSLOT; i++) ok = cudaStreamCreateWithPriority(&c->s_copy[i], cudaStreamNonBlocking, prio_lo) == cudaSuccess;
-    ok = ok && cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
-        && cudaStreamCreateWithPriority(&c->s_bank, cudaStreamNonBlocking, prio_lo) == cudaSuccess
-        && cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming) == cudaSuccess
-        && cudaEventCreateWithFlags(&c->ev_left[0], cudaEventDisableTiming) == cudaSuccess
-        && cudaEventCreateWithFlags(&c->ev_left[1], cudaEventDisableTiming) == cudaSuccess
+    const size_t table_bytes = sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * CG_NBANK;
+    bool ok = cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
-        && cudaMalloc(&c->d_stats, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
-        && cudaMemset(c->d_stats, 0, sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * 2) == cudaSuccess
+        && cudaMalloc(&c->d_stats, table_bytes) == cudaSuccess
+        && cudaMemset(c->d_stats, 0, table_bytes) == cudaSuccess
         && cudaMalloc(&c->d_sticky, 16) == cudaSuccess
         && cudaMemset(c->d_sticky, 0, 16) == cudaSuccess
         && cudaMallocHost(&c->h_stats, sizeof(cg_chrom_stats)) == cudaSuccess
         && cudaMallocHost(&c->h_flags, 16) == cudaSuccess;
+    for (int b = 0; ok && b < CG_NBANK; b++) ok = cudaEventCreateWithFlags(&c->ev_bank_read[b], cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
-        ok = cudaStreamCreateWithPriority(&c->s_slot[i], cudaStreamNonBlocking, prio_lo) == cudaSuccess
+        ok = cudaStreamCreateWithPriority(&s.s_copy, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+            && cudaStreamCreateWithPriority(&s.s_work, cudaStreamNonBlocking, prio_lo) == cudaSuccess
             /* the genotype kernels are small and latency-bound: let their CTAs be placed first */
             && cudaStreamCreateWithPriority(&s.s_geno[0], cudaStreamNonBlocking, prio_hi) == cudaSuccess
             && cudaStreamCreateWithPriority(&s.s_geno[1], cudaStreamNonBlocking, prio_hi) == cudaSuccess
-            && cudaMalloc(&s.d_expected, sizeof(float) * 128) == cudaSuccess
-            && cudaMemset(s.d_expected, 0, sizeof(float) * 128) == cudaSuccess
-            && cudaMalloc(&s.d_ctl, 16) == cudaSuccess
-            && cudaMemset(s.d_ctl, 0, 16) == cudaSuccess
+            && cudaMalloc(&s.d_expected, sizeof(float) * 128 * CG_JMAX) == cudaSuccess
+            && cudaMemset(s.d_expected, 0, sizeof(float) * 128 * CG_JMAX) == cudaSuccess
+            && cudaMalloc(&s.d_ctl, sizeof(unsigned) * (CG_CTL_WORDS * CG_JMAX + 8)) == cudaSuccess
+            && cudaMemset(s.d_ctl, 0, sizeof(unsigned) * (CG_CTL_WORDS * CG_JMAX + 8)) == cudaSuccess
+            && cudaMalloc(&s.d_partial, sizeof(int32_t) * (size_t)CG_PASS_GRID_MAX * CG_JMAX * CG_PART_WORDS) == cudaSuccess
+            && cudaMalloc(&s.d_jobs, sizeof(cg_dev_job) * CG_JMAX) == cudaSuccess
+            && cudaMallocHost(&s.h_jobs, sizeof(cg_dev_job) * CG_JMAX) == cudaSuccess
+            && cudaMallocHost(&s.h_flags, sizeof(unsigned) * CG_JMAX) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_table, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_copy, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_pass, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_geno[0], cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_geno[1], cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_runs, cudaEventDisableTiming) == cudaSuccess;
+        if (ok) memset(s.h_flags, 0, sizeof(unsigned) * CG_JMAX);
     }
     if (!ok) {
         fail(nullptr, CG_ECUDA, "context allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
         cg_destroy(c);
         return nullptr;
     }
+    if (c->n_sms * 3 > CG_PASS_GRID_MAX) { fail(nullptr, CG_ECUDA, "device has %d SMs; the library is sized for <= %d", c->n_sms, CG_PASS_GRID_MAX / 3); cg_destroy(c); return nullptr; }
     snprintf(c->err, sizeof c->err, "no error");
     return c;
 }
@@ -310,25 +346,24 @@ void cg_destroy(cg_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    for (int i = 0; i < CG_NSLOT; i++) if (c->s_copy[i]) cudaStreamSynchronize(c->s_copy[i]);
-    if (c->s_main) cudaStreamSynchronize(c->s_main);
-    if (c->s_bank) cudaStreamSynchronize(c->s_bank);
-    for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamSynchronize(c->s_slot[t]);
-    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamSynchronize(c->slot[i].s_geno[t]);
+    cudaDeviceSynchronize();
+    cg_comm_destroy(c);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (int i = 0; i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
-        cudaFree(s.d_reads); cudaFree(s.d_gc); cudaFree(s.d_counts);
-        cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl);
-        cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32);
-        if (s.ev_copy) cudaEventDestroy(s.ev_copy);
-        if (s.ev_pass) cudaEventDestroy(s.ev_pass);
-        for (int t = 0; t < 2; t++) if (s.ev_geno[t]) cudaEventDestroy(s.ev_geno[t]);
-        if (s.ev_runs) cudaEventDestroy(s.ev_runs);
+        cudaFree(s.d_reads); cudaFree(s.d_pos); cudaFree(s.d_mapq); cudaFree(s.d_gc); cudaFree(s.d_counts);
+        cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl); cudaFree(s.d_partial); cudaFree(s.d_jobs);
+        cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32); cudaFree(s.d_in);
+        if (s.h_jobs) cudaFreeHost(s.h_jobs);
+        if (s.h_flags) cudaFreeHost(s.h_flags);
+        cudaEvent_t evs[] = {s.ev_table, s.ev_copy, s.ev_pass, s.ev_geno[0], s.ev_geno[1], s.ev_runs};
+        for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
+        cudaStream_t sts[] = {s.s_copy, s.s_work, s.s_geno[0], s.s_geno[1]};
+        for (cudaStream_t st : sts) if (st) cudaStreamDestroy(st);
     }
-    cudaFree(c->d_stats); cudaFree(c->d_sticky);
-    if (c->sr.st) { cudaStreamSynchronize(c->sr.st); cudaStreamDestroy(c->sr.st); }
+    cudaFree(c->d_stats); cudaFree(c->d_stats_all); cudaFree(c->d_sticky);
+    if (c->sr.st) cudaStreamDestroy(c->sr.st);
     cudaFree(c->sr.d_ref); cudaFree(c->sr.d_keys_a); cudaFree(c->sr.d_keys_b); cudaFree(c->sr.d_vals_a); cudaFree(c->sr.d_vals_b);
     cudaFree(c->sr.d_temp); cudaFree(c->sr.d_lo); cudaFree(c->sr.d_hi); cudaFree(c->sr.d_halves); cudaFree(c->sr.d_bases);
     cudaFree(c->sr.d_rows); cudaFree(c->sr.d_n_rows); cudaFree(c->sr.d_count);
@@ -336,13 +371,8 @@ void cg_destroy(cg_ctx* c)
     if (c->h_stats) cudaFreeHost(c->h_stats);
     if (c->h_flags) cudaFreeHost(c->h_flags);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
-    for (int i = 0; i < CG_NSLOT; i++) if (c->s_copy[i]) cudaStreamDestroy(c->s_copy[i]);
+    for (int b = 0; b < CG_NBANK; b++) if (c->ev_bank_read[b]) cudaEventDestroy(c->ev_bank_read[b]);
     if (c->s_main) cudaStreamDestroy(c->s_main);
-    if (c->s_bank) cudaStreamDestroy(c->s_bank);
-    for (int b = 0; b < 2; b++) if (c->ev_left[b]) cudaEventDestroy(c->ev_left[b]);
-    for (int t = 0; t < CG_NSLOT; t++) if (c->s_slot[t]) cudaStreamDestroy(c->s_slot[t]);
-    if (c->ev_reset) cudaEventDestroy(c->ev_reset);
-    for (int i = 0; i < CG_NSLOT; i++) for (int t = 0; t < 2; t++) if (c->slot[i].s_geno[t]) cudaStreamDestroy(c->slot[i].s_geno[t]);
     delete c;
 }
 
@@ -383,6 +413,7 @@ int cg_set_slots(cg_ctx* c, int n)
     CU(c, cudaSetDevice(c->device));
     int rc = sync_all(c);                      /* slots that leave the rotation must be idle: cg_join no longer visits them */
     if (rc) return rc;
+    if ((rc = settle_samples(c)) != CG_OK) return rc;
     c->n_slot = n;
     /* the chromosome that was current may sit in a slot that has just left the rotation: it is closed, the next
      * call that needs a chromosome has to follow a cg_chrom_begin */
@@ -390,20 +421,25 @@ int cg_set_slots(cg_ctx* c, int n)
     return CG_OK;
 }
 
-/* make the main stream (cg_stream) wait for everything queued on the others */
+/* make the main stream (cg_stream) wait for everything queued on the others since the last join */
 int cg_join(cg_ctx* c)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     CU(c, cudaSetDevice(c->device));
-    /* every upload on a copy stream is waited for by a kernel on its slot's stream (cg_push_reads, cg_chrom_finish),
-     * so the slot and genotype streams cover the copy streams */
-    cudaStream_t all[3 * CG_NSLOT];
-    for (int i = 0; i < c->n_slot; i++) { all[3 * i] = c->s_slot[i]; all[1 + 3 * i] = c->slot[i].s_geno[0]; all[2 + 3 * i] = c->slot[i].s_geno[1]; }
-    for (int t = 0; t < 3 * c->n_slot; t++) {
-        CU(c, cudaEventRecord(c->ev_join, all[t]));
-        CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
+    /* every upload on a copy stream is waited for by a kernel on its slot's work or genotype stream */
+    for (int i = 0; i < CG_NSLOT; i++) {
+        cg_slot& s = c->slot[i];
+        if (s.dirty_work) {
+            CU(c, cudaEventRecord(c->ev_join, s.s_work));
+            CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
+            s.dirty_work = false;
+        }
+        for (int t = 0; t < 2; t++) if (s.dirty_geno[t]) {
+            CU(c, cudaEventRecord(c->ev_join, s.s_geno[t]));
+            CU(c, cudaStreamWaitEvent(c->s_main, c->ev_join, 0));
+            s.dirty_geno[t] = false;
+        }
     }
-    c->dirty = false;
     return CG_OK;
 }
 
@@ -413,6 +449,7 @@ int cg_sync(cg_ctx* c)
     CU(c, cudaSetDevice(c->device));
     int rc = sync_all(c);
     if (rc) return rc;
+    if ((rc = settle_samples(c)) != CG_OK) return rc;
     prof_collect(c);
     if (c->ptr_mode == CG_PTR_HOST) return report_sticky(c, "cg_sync");
     return CG_OK;
@@ -439,6 +476,97 @@ int cg_kernel_times(cg_ctx* c, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS]
     return CG_OK;
 }
 
+} /* extern "C" */
+
+/* ------------------------------------------------------------------------- */
+/* slots                                                                     */
+
+/* The next slot of the rotation, ordered behind its previous tenant: the streams that will write what the
+ * tenant's kernels may still read wait for its events.  HOST mode writes the slot's upload buffers from the
+ * copy stream; DEVICE mode writes none of them and needs only the work and genotype streams ordered. */
+static int take_slot(cg_ctx* c, int* si_out)
+{
+    int si;
+    for (;;) {
+        si = (int)(c->n_begun % (unsigned long long)c->n_slot);
+        if (!c->slot[si].check) break;
+        int rc = settle_slot(c, c->slot[si]);          /* may re-run a chromosome, which takes slots itself */
+        if (rc) return rc;
+    }
+    cg_slot& s = c->slot[si];
+    const bool uploads = c->ptr_mode == CG_PTR_HOST;
+    if (s.used && uploads) CU(c, cudaStreamWaitEvent(s.s_copy, s.ev_pass, 0));
+    for (int t = 0; t < 2; t++) {
+        if (!s.geno_queued[t]) continue;
+        if (uploads) CU(c, cudaStreamWaitEvent(s.s_copy, s.ev_geno[t], 0));
+        CU(c, cudaStreamWaitEvent(s.s_work, s.ev_geno[t], 0));
+        CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
+    }
+    if (c->profiling && !getenv("CG_PROF_NOCHAIN")) {   /* time kernels alone: chain this slot behind the one before it */
+        cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot];
+        if (o.used) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0));
+        for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_geno[t], 0));
+    }
+    s.used = true; s.geno_queued[0] = s.geno_queued[1] = false; s.runs_uploaded = false;
+    s.arena_used = 0; s.rec_fmt = 0; s.sample = false; s.check = false; s.n_jobs = 0;
+    c->n_begun++;
+    *si_out = si;
+    return CG_OK;
+}
+
+/* depth, counts (and, for the per-chromosome entry points, the out-of-order scratch) for a chunk space */
+static int ensure_space(cg_ctx* c, cg_slot& s, int n_space, bool want_depth32)
+{
+    const size_t n_pos = (size_t)n_space * CG_CHUNK;
+    if (n_pos > c->hw_pos) c->hw_pos = n_pos;
+    const size_t a_pos = c->hw_pos;                       /* the largest chunk space any slot has seen (see grow()) */
+    const size_t a_words = cgk_counts_words((int)(a_pos / CG_CHUNK));
+    if (cgk_counts_words(n_space) > s.counts_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_counts); s.d_counts = nullptr; s.counts_cap = 0;
+        CU(c, cudaMalloc(&s.d_counts, a_words * sizeof(int32_t)));
+        s.counts_cap = a_words;
+    }
+    if (n_pos > s.pos_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_depth); s.d_depth = nullptr; s.pos_cap = 0;
+        CU(c, cudaMalloc(&s.d_depth, a_pos * sizeof(int16_t)));
+        s.pos_cap = a_pos;
+    }
+    if (want_depth32 && n_pos > s.depth32_cap) {
+        int rc = sync_all(c);
+        if (rc) return rc;
+        cudaFree(s.d_depth32); s.d_depth32 = nullptr; s.depth32_cap = 0;
+        CU(c, cudaMalloc(&s.d_depth32, n_pos * sizeof(uint32_t)));
+        /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
+        CU(c, cudaMemsetAsync(s.d_depth32, 0, n_pos * sizeof(uint32_t), s.s_work));
+        s.depth32_cap = n_pos;
+    }
+    return CG_OK;
+}
+
+static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space)
+{
+    cg_sub& S = s.sub;
+    memset(&S, 0, sizeof S);
+    S.n_jobs = n_jobs; S.n_work = n_work; S.n_space = n_space;
+    S.k = cgk_counts_layout(s.d_counts, n_space);
+    S.depth = s.d_depth;
+    S.partial = s.d_partial;
+    S.n_pass_ctas = cgk_pass_grid(n_work, c->n_sms);
+    S.sctl = s.d_ctl + CG_CTL_WORDS * CG_JMAX;
+    S.sticky = c->d_sticky;
+}
+
+static long long* stats_row_of(cg_ctx* c, int chr_index)
+{
+    return c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS;
+}
+
+extern "C" {
+
 /* ------------------------------------------------------------------------- */
 int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc_profile,
                    int32_t n_windows, int mq_threshold)
@@ -446,90 +574,99 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (chr_index < 0 || chr_index >= CG_MAX_CHROMS) return fail(c, CG_EINVAL, "chr_index %d outside 0..%d", chr_index, CG_MAX_CHROMS - 1);
     if (chrom_len <= 0) return fail(c, CG_EINVAL, "chrom_len %d must be positive", chrom_len);
-    if (chrom_len > INT32_MAX - CG_CHUNK) return fail(c, CG_EINVAL, "chrom_len %d too large", chrom_len);
+    if (chrom_len > INT32_MAX - 2 * CG_CHUNK * CG_SUPER_CHUNKS) return fail(c, CG_EINVAL, "chrom_len %d too large", chrom_len);
     const int need_windows = (chrom_len + 99) / 100;
     if (!gc_profile || n_windows < need_windows)
         return fail(c, CG_EINVAL, "gc_profile needs >= %d windows for length %d (got %d)", need_windows, chrom_len, n_windows);
     CU(c, cudaSetDevice(c->device));
 
-    const int si = (int)(c->n_begun % (unsigned long long)c->n_slot);
+    int si, rc;
+    if ((rc = take_slot(c, &si)) != CG_OK) return rc;
     cg_slot& s = c->slot[si];
     const int n_chunks = (chrom_len + CG_CHUNK - 1) / CG_CHUNK;
-    const size_t n_pos = (size_t)n_chunks * CG_CHUNK;
-    if ((size_t)n_chunks > c->hw_chunks) c->hw_chunks = (size_t)n_chunks;
-    const int a_chunks = (int)c->hw_chunks;               /* what a slot that has to grow is sized for: the largest */
-    const size_t a_pos = (size_t)a_chunks * CG_CHUNK;      /* chromosome any slot has seen (see grow()) */
-    if (cgk_counts_words(n_chunks) > s.counts_cap) {
-        int rc = sync_all(c);
-        if (rc) return rc;
-        cudaFree(s.d_counts); s.d_counts = nullptr; s.counts_cap = 0;
-        CU(c, cudaMalloc(&s.d_counts, cgk_counts_words(a_chunks) * sizeof(int32_t)));
-        s.counts_cap = cgk_counts_words(a_chunks);
-    }
-    if (n_pos > s.pos_cap) {
-        int rc = sync_all(c);
-        if (rc) return rc;
-        cudaFree(s.d_depth);
-        s.d_depth = nullptr; s.pos_cap = 0;
-        CU(c, cudaMalloc(&s.d_depth, a_pos * sizeof(int16_t)));
-        s.pos_cap = a_pos;
-    }
-    cudaStream_t ss = c->s_slot[si];
-    if (n_pos > s.depth32_cap) {
-        int rc = sync_all(c);
-        if (rc) return rc;
-        cudaFree(s.d_depth32); s.d_depth32 = nullptr; s.depth32_cap = 0;
-        CU(c, cudaMalloc(&s.d_depth32, a_pos * sizeof(uint32_t)));
-        /* the out-of-order path keeps these counts zero at rest (the pass clears what it consumes) */
-        CU(c, cudaMemsetAsync(s.d_depth32, 0, a_pos * sizeof(uint32_t), ss));
-        s.depth32_cap = a_pos;
-    }
+    const int n_space = cgk_job_space(n_chunks);
+    if ((rc = ensure_space(c, s, n_space, true)) != CG_OK) return rc;
+    cg_dev_job& J = s.hj[0];
+    memset(&J, 0, sizeof J);
     if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows, 0, &c->hw_gc);
-        if (rc) return rc;
-    }
-    /* the slot's previous tenant (two chromosomes ago) must be done with what we overwrite */
-    /* HOST mode writes the slot's own upload buffers (d_reads, d_gc from the copy stream; d_runs and the staging
-     * arena from both genotype streams); DEVICE mode writes none of them and needs only the slot stream ordered
-     * behind the previous tenant's genotype kernels — 3 waits per chromosome instead of 7 on a host that is the
-     * limit of the resident leg */
-    const bool uploads = c->ptr_mode == CG_PTR_HOST;
-    if (s.used && uploads) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_pass, 0));   /* d_reads */
-    for (int t = 0; t < 2; t++) {
-        if (!s.geno_queued[t]) continue;
-        if (uploads) CU(c, cudaStreamWaitEvent(c->s_copy[si], s.ev_geno[t], 0)); /* d_gc */
-        CU(c, cudaStreamWaitEvent(ss, s.ev_geno[t], 0));                         /* d_depth, d_counts, d_expected */
-        /* d_run_idx is rebuilt on s_geno[0] in either mode: behind the previous tenant's duplication kernel */
-        if (uploads || t == 1) CU(c, cudaStreamWaitEvent(s.s_geno[t ^ 1], s.ev_geno[t], 0));
-    }
-    if (s.wait_reset) { CU(c, cudaStreamWaitEvent(ss, c->ev_reset, 0)); s.wait_reset = false; }
-    if (c->profiling && !getenv("CG_PROF_NOCHAIN")) {   /* time kernels alone: chain this slot behind the other one */
-        cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot];
-        if (o.used) CU(c, cudaStreamWaitEvent(ss, o.ev_pass, 0));
-        for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(ss, o.ev_geno[t], 0));
-    }
-    if (c->ptr_mode == CG_PTR_HOST) {
-        CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, c->s_copy[si]));
-        CU(c, cudaEventRecord(s.ev_copy, c->s_copy[si]));
-        s.gc_ptr = s.d_gc;
+        if ((rc = grow(c, &s.d_gc, &s.gc_cap, (size_t)need_windows, 0, &c->hw_gc)) != CG_OK) return rc;
+        CU(c, cudaMemcpyAsync(s.d_gc, gc_profile, (size_t)need_windows, cudaMemcpyHostToDevice, s.s_copy));
+        CU(c, cudaEventRecord(s.ev_copy, s.s_copy));
+        J.gc = s.d_gc;
     } else {
-        s.gc_ptr = gc_profile;
+        J.gc = gc_profile;
     }
-    s.chr_index = chr_index; s.chrom_len = chrom_len; s.n_chunks = n_chunks;
-    s.d_row = c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS;
-    c->dirty = true;
-    s.reads_ptr = s.d_reads;
-    s.n_runs = 0; s.has_map = 0; s.runs_ptr = nullptr;
-    s.arena_used = 0;
-    s.used = true; s.geno_queued[0] = s.geno_queued[1] = false; s.runs_uploaded = false;
-    c->cur = si; c->n_begun++;
-    c->mq_threshold = mq_threshold;
-    c->n_reads = 0;
+    J.chrom_len = chrom_len; J.n_chunks = n_chunks; J.mq_threshold = mq_threshold; J.chr_index = chr_index;
+    J.stats_row = stats_row_of(c, chr_index);
+    J.expected = s.d_expected; J.ctl = s.d_ctl; J.run_idx = nullptr;
+    s.n_jobs = 1;
+    fill_sub(c, s, 1, n_chunks, n_space);
+    s.sub.depth32 = s.d_depth32;
+    c->cur = si;
     c->in_chrom = true; c->finished = false;
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
     {
-        prof_scope ps(c, c->s_slot[c->cur], 0, 1);
-        CU(c, cgk_chrom_init(c->s_slot[c->cur], s.d_counts, n_chunks, s.d_row, s.d_ctl));
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_job_init(s.s_work, s.sub, J, s.d_counts));
+    }
+    s.dirty_work = true;
+    return CG_OK;
+}
+
+/* one batch of records of the current chromosome, either format: staged (HOST), used in place (first DEVICE
+ * batch) or gathered into the slot's own buffers (later DEVICE batches), then looked at by k_mark */
+static int push_records(cg_ctx* c, const cg_read* reads, const int32_t* pos, const uint8_t* mapq, size_t n, const char* who)
+{
+    if (!c->in_chrom || c->finished) return fail(c, CG_EINVAL, "%s outside cg_chrom_begin/cg_chrom_finish", who);
+    if (n == 0) return CG_OK;
+    cg_slot& s = c->slot[c->cur];
+    cg_dev_job& J = s.hj[0];
+    const int fmt = reads ? 1 : (mapq ? 2 : 3);
+    if (fmt == 3 && J.mq_threshold >= 0) return fail(c, CG_EINVAL, "%s: a NULL mapq plane needs a negative mq_threshold (got %d)", who, J.mq_threshold);
+    if (s.rec_fmt && s.rec_fmt != fmt) return fail(c, CG_EINVAL, "%s: a chromosome is pushed in one record format only", who);
+    if ((unsigned long long)J.n_reads + n >= 0x7fffffffull) return fail(c, CG_EINVAL, "more than 2^31-1 records on one chromosome");
+    CU(c, cudaSetDevice(c->device));
+    const size_t first = (size_t)J.n_reads;
+    const cudaMemcpyKind kind = c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    const bool in_place = c->ptr_mode == CG_PTR_DEVICE && first == 0;
+    if (in_place) {
+        J.reads = reads; J.rec_pos = pos; J.rec_mapq = mapq;       /* single device batch: used where it lies */
+    } else {
+        /* the copies run on the copy stream in HOST mode (they overlap the previous slot's kernels) and on the
+         * work stream in DEVICE mode (device-to-device gathers of a caller that pushes in several batches) */
+        cudaStream_t st = c->ptr_mode == CG_PTR_HOST ? s.s_copy : s.s_work;
+        int rc;
+        if (fmt == 1) {
+            const bool external = first && J.reads != s.d_reads;
+            if ((rc = grow(c, &s.d_reads, &s.reads_cap, first + n, external ? 0 : first, &c->hw_reads)) != CG_OK) return rc;
+            if (external) CU(c, cudaMemcpyAsync(s.d_reads, J.reads, first * sizeof(cg_read), cudaMemcpyDeviceToDevice, st));
+            CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), kind, st));
+            J.reads = s.d_reads;
+        } else {
+            const bool external = first && J.rec_pos != s.d_pos;
+            if ((rc = grow(c, &s.d_pos, &s.rpos_cap, first + n, external ? 0 : first, &c->hw_rpos)) != CG_OK) return rc;
+            if (external) CU(c, cudaMemcpyAsync(s.d_pos, J.rec_pos, first * 4, cudaMemcpyDeviceToDevice, st));
+            CU(c, cudaMemcpyAsync(s.d_pos + first, pos, n * 4, kind, st));
+            if (fmt == 2) {
+                if ((rc = grow(c, &s.d_mapq, &s.rmapq_cap, first + n, external ? 0 : first, &c->hw_rmapq)) != CG_OK) return rc;
+                if (external) CU(c, cudaMemcpyAsync(s.d_mapq, J.rec_mapq, first, cudaMemcpyDeviceToDevice, st));
+                CU(c, cudaMemcpyAsync(s.d_mapq + first, mapq, n, kind, st));
+                J.rec_mapq = s.d_mapq;
+            }
+            J.rec_pos = s.d_pos;
+        }
+        if (c->ptr_mode == CG_PTR_HOST) {
+            CU(c, cudaEventRecord(s.ev_copy, s.s_copy));
+            CU(c, cudaStreamWaitEvent(s.s_work, s.ev_copy, 0));
+        }
+    }
+    s.rec_fmt = fmt;
+    J.n_reads = (long long)(first + n);
+    J.mark_first = (long long)first; J.mark_n = (long long)n; J.mark_blk0 = 0;
+    s.sub.n_mark_blocks = (int)((n + 255) / 256);
+    {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_mark(s.s_work, s.sub, J));
     }
     return CG_OK;
 }
@@ -537,37 +674,15 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
 int cg_push_reads(cg_ctx* c, const cg_read* reads, size_t n)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (!c->in_chrom || c->finished) return fail(c, CG_EINVAL, "cg_push_reads outside cg_chrom_begin/cg_chrom_finish");
-    if (n == 0) return CG_OK;
-    if (!reads) return fail(c, CG_EINVAL, "null reads");
-    if ((unsigned long long)c->n_reads + n >= 0x7fffffffull) return fail(c, CG_EINVAL, "more than 2^31-1 records on one chromosome");
-    CU(c, cudaSetDevice(c->device));
-    cg_slot& s = c->slot[c->cur];
-    const long long first = c->n_reads;
-    if (c->ptr_mode == CG_PTR_HOST) {
-        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, (size_t)first, &c->hw_reads);
-        if (rc) return rc;
-        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyHostToDevice, c->s_copy[c->cur]));
-        CU(c, cudaEventRecord(s.ev_copy, c->s_copy[c->cur]));
-        CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));
-        s.reads_ptr = s.d_reads;
-    } else if (first == 0) {
-        s.reads_ptr = reads;                  /* single device batch: used in place */
-    } else {
-        const bool external = s.reads_ptr != s.d_reads;
-        int rc = grow(c, &s.d_reads, &s.reads_cap, (size_t)first + n, external ? 0 : (size_t)first, &c->hw_reads);
-        if (rc) return rc;
-        if (external) CU(c, cudaMemcpyAsync(s.d_reads, s.reads_ptr, (size_t)first * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
-        CU(c, cudaMemcpyAsync(s.d_reads + first, reads, n * sizeof(cg_read), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
-        s.reads_ptr = s.d_reads;
-    }
-    c->n_reads = first + (long long)n;
-    {
-        prof_scope ps(c, c->s_slot[c->cur], 0, 1);
-        CU(c, cgk_mark_batch(c->s_slot[c->cur], s.reads_ptr, first, (long long)n, cgk_counts_layout(s.d_counts, s.n_chunks),
-                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, s.d_row));
-    }
-    return CG_OK;
+    if (n && !reads) return fail(c, CG_EINVAL, "null reads");
+    return push_records(c, reads, nullptr, nullptr, n, "cg_push_reads");
+}
+
+int cg_push_reads_compact(cg_ctx* c, const int32_t* pos, const uint8_t* mapq, size_t n)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (n && !pos) return fail(c, CG_EINVAL, "null pos");
+    return push_records(c, nullptr, pos, mapq, n, "cg_push_reads_compact");
 }
 
 int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
@@ -576,43 +691,37 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     if (!c->in_chrom || c->finished) return fail(c, CG_EINVAL, "cg_chrom_finish without cg_chrom_begin");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    long long* row = s.d_row;
-    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], s.ev_copy, 0));   /* GC bytes */
+    cg_dev_job& J = s.hj[0];
+    if (c->ptr_mode == CG_PTR_HOST) CU(c, cudaStreamWaitEvent(s.s_work, s.ev_copy, 0));   /* GC bytes */
     {
-        prof_scope ps(c, c->s_slot[c->cur], 0, 2);
-        CU(c, cgk_rare_paths(c->s_slot[c->cur], s.reads_ptr, c->n_reads, s.d_depth32, cgk_counts_layout(s.d_counts, s.n_chunks),
-                             s.n_chunks, s.chrom_len, c->mq_threshold, s.d_ctl, c->n_sms));
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_rare_scatter(s.s_work, s.sub, J, c->n_sms));
     }
     {
-        /* Passes of consecutive chromosomes may run side by side (CG_PASS_OVERLAP=0 chains them).  At 6 bytes per
-         * position (rounds r01a-g) two passes doubled the concurrent write streams and cost HBM efficiency, so
-         * they were chained; at 2 bytes per position the overlap hides each launch's ramp and tail instead:
-         * C2 sample 1.25 -> 1.20 ms (measured r01h). */
+        /* Passes of consecutive chromosomes may run side by side (CG_PASS_OVERLAP=0 chains them): at 2 bytes per
+         * position the overlap hides each launch's ramp and tail, C2 sample 1.25 -> 1.20 ms (measured r01h). */
         cg_slot& o = c->slot[(c->cur + c->n_slot - 1) % c->n_slot];
         static const bool overlap = !(getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP")) == 0);
-        if (o.used && !overlap) CU(c, cudaStreamWaitEvent(c->s_slot[c->cur], o.ev_pass, 0));
+        if (o.used && !overlap) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0));
     }
     {
-        prof_scope ps(c, c->s_slot[c->cur], 1, 1);
-        cg_pass_args a;
-        a.reads = s.reads_ptr; a.n_reads = c->n_reads; a.k = cgk_counts_layout(s.d_counts, s.n_chunks);
-        a.gc = s.gc_ptr;
-        a.chrom_len = s.chrom_len; a.n_chunks = s.n_chunks; a.mq_threshold = c->mq_threshold;
-        a.depth = s.d_depth; a.depth32 = s.d_depth32; a.ctl = s.d_ctl;
-        a.stats = row; a.expected = s.d_expected; a.sticky = c->d_sticky;
-        /* asynchronous HOST mode hands over page-locked pointers: the kernel writes the row there itself */
-        a.host_row = (c->ptr_mode == CG_PTR_HOST && c->async && out) ? reinterpret_cast<long long*>(out) : nullptr;
-        CU(c, cgk_depth_pass(c->s_slot[c->cur], a, c->n_sms));
+        prof_scope ps(c, s.s_work, 1, 1);
+        CU(c, cgk_depth_pass(s.s_work, s.sub, J));
     }
-    CU(c, cudaEventRecord(s.ev_pass, c->s_slot[c->cur]));
+    /* a collective that still reads this bank must be through before the row is rewritten */
+    if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(s.s_work, c->ev_bank_read[c->bank], 0));
+    /* asynchronous HOST mode hands over a page-locked pointer, DEVICE mode a device pointer: the kernel writes the row there itself */
+    J.row_out = (out && !blocking(c)) ? reinterpret_cast<long long*>(out) : nullptr;
+    {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_finalize(s.s_work, s.sub, J));
+    }
+    CU(c, cudaEventRecord(s.ev_pass, s.s_work));
+    s.dirty_work = true;
     c->finished = true;
-    if (c->ptr_mode == CG_PTR_DEVICE) {
-        if (out) CU(c, cudaMemcpyAsync(out, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
-        return CG_OK;
-    }
-    if (c->async) return CG_OK;           /* `out` is page-locked, written by the pass, valid after cg_sync */
-    CU(c, cudaMemcpyAsync(c->h_stats, row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
-    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
+    if (!blocking(c)) return CG_OK;
+    CU(c, cudaMemcpyAsync(c->h_stats, J.stats_row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, s.s_work));
+    CU(c, cudaStreamSynchronize(s.s_work));
     if (out) memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
     return report_sticky(c, "cg_chrom_finish");
 }
@@ -623,9 +732,9 @@ int cg_get_expected(cg_ctx* c, float expected[CG_GC_BINS])
     if (!c->finished) return fail(c, CG_EINVAL, "cg_get_expected before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(expected, s.d_expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
-    if (blocking(c)) CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
+    CU(c, cudaMemcpyAsync(expected, s.hj[0].expected, sizeof(float) * CG_GC_BINS,
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, s.s_work));
+    if (blocking(c)) CU(c, cudaStreamSynchronize(s.s_work));
     return CG_OK;
 }
 
@@ -635,9 +744,9 @@ int cg_set_expected(cg_ctx* c, const float expected[CG_GC_BINS])
     if (!c->finished) return fail(c, CG_EINVAL, "cg_set_expected before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(s.d_expected, expected, sizeof(float) * CG_GC_BINS,
-                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, c->s_slot[c->cur]));
-    CU(c, cudaEventRecord(s.ev_pass, c->s_slot[c->cur]));        /* the genotype stream waits for this */
+    CU(c, cudaMemcpyAsync(s.hj[0].expected, expected, sizeof(float) * CG_GC_BINS,
+                          c->ptr_mode == CG_PTR_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, s.s_work));
+    CU(c, cudaEventRecord(s.ev_pass, s.s_work));        /* the genotype stream waits for this */
     return CG_OK;
 }
 
@@ -646,30 +755,36 @@ int cg_set_mappability_runs(cg_ctx* c, const cg_maprun* runs, size_t n, int enab
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (!c->in_chrom) return fail(c, CG_EINVAL, "cg_set_mappability outside a chromosome");
-    if (n > 0x7fffffffull) return fail(c, CG_EINVAL, "too many mappability runs");
+    if (n > 0x7ffffff0ull) return fail(c, CG_EINVAL, "too many mappability runs");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    s.has_map = enabled ? 1 : 0;
-    s.n_runs = (int)n;
-    if (n == 0) { s.runs_ptr = nullptr; return CG_OK; }
+    cg_dev_job& J = s.hj[0];
+    J.has_map = enabled ? 1 : 0;
+    J.n_runs = (int)n;
+    if (n == 0) { J.runs = nullptr; return CG_OK; }
     if (!runs) return fail(c, CG_EINVAL, "null runs");
-    int rc = grow(c, &s.d_run_idx, &s.run_idx_cap, (size_t)cgk_run_index_words(s.chrom_len), 0, &c->hw_run_idx);
+    int rc = grow(c, &s.d_run_idx, &s.run_idx_cap, (size_t)cgk_run_index_words(J.chrom_len), 0, &c->hw_run_idx);
     if (rc) return rc;
+    J.run_idx = s.d_run_idx;
     if (c->ptr_mode == CG_PTR_DEVICE) {
-        s.runs_ptr = runs;
+        J.runs = runs;
     } else {
         rc = grow(c, &s.d_runs, &s.runs_cap, n, 0, &c->hw_runs);
         if (rc) return rc;
         /* on a genotype stream: behind the slot's previous tenant, which may still read d_runs */
         CU(c, cudaMemcpyAsync(s.d_runs, runs, n * sizeof(cg_maprun), cudaMemcpyHostToDevice, s.s_geno[0]));
-        s.runs_ptr = s.d_runs;
+        J.runs = s.d_runs;
     }
+    J.run_blk0 = 0;
+    cg_sub S = s.sub;
+    S.n_run_blocks = (int)((n + 1 + 255) / 256);
     {
         prof_scope ps(c, s.s_geno[0], 2, 1);
-        CU(c, cgk_run_index(s.s_geno[0], s.runs_ptr, (int)n, s.d_run_idx, s.chrom_len));
+        CU(c, cgk_run_index(s.s_geno[0], S, J));
     }
     CU(c, cudaEventRecord(s.ev_runs, s.s_geno[0]));
     s.runs_uploaded = true;
+    s.dirty_geno[0] = true;
     return CG_OK;
 }
 
@@ -679,7 +794,7 @@ int cg_set_mappability(cg_ctx* c, const cg_mapiv* rows, size_t n)
     if (!c->in_chrom) return fail(c, CG_EINVAL, "cg_set_mappability outside a chromosome");
     if (n && !rows) return fail(c, CG_EINVAL, "null rows");
     std::vector<cg_maprun> v;
-    cg_flatten_rows(rows, n, c->slot[c->cur].chrom_len, v);
+    cg_flatten_rows(rows, n, c->slot[c->cur].hj[0].chrom_len, v);
     const int saved = c->ptr_mode;
     c->ptr_mode = CG_PTR_HOST;                                 /* rows are always host memory */
     int rc = cg_set_mappability_runs(c, v.data(), v.size(), n > 0);
@@ -691,8 +806,10 @@ int cg_set_mappability(cg_ctx* c, const cg_mapiv* rows, size_t n)
     return rc;
 }
 
+} /* extern "C" */
+
 /* HOST-mode staging for one cg_genotype call: room for n CNVs and n calls in the slot's arena.
- * The arena is rewound by cg_chrom_begin; when it has to grow, everything queued is drained
+ * The arena is rewound when the slot is taken; when it has to grow, everything queued is drained
  * first, so earlier calls of this chromosome have already delivered their results. */
 static int arena_take(cg_ctx* c, cg_slot& s, size_t n, cg_cnv** d_in, cg_call** d_out)
 {
@@ -711,6 +828,8 @@ static int arena_take(cg_ctx* c, cg_slot& s, size_t n, cg_cnv** d_in, cg_call** 
     return CG_OK;
 }
 
+extern "C" {
+
 int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* out)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
@@ -724,9 +843,8 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     cudaStream_t st = s.s_geno[t];            /* deletions and duplications of one chromosome run side by side */
     const cg_cnv* d_in = cnvs; cg_call* d_out = out;
     /* Asynchronous HOST mode: both arrays are page-locked (cg_set_async), i.e. addressable from the device; the
-     * kernel reads 8 bytes and writes 56 per CNV across PCIe itself, which is cheaper than two copy calls per
-     * launch on a host that issues a chromosome every 50 us. */
-    const bool staged = c->ptr_mode == CG_PTR_HOST && !c->async;
+     * kernel reads 8 bytes and writes 56 per CNV across PCIe itself, which is cheaper than two copy calls per launch. */
+    const bool staged = blocking(c);
     if (staged) {
         cg_cnv* a_in = nullptr;
         int rc = arena_take(c, s, n, &a_in, &d_out);
@@ -736,14 +854,19 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     }
     CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));              /* depth, chunk sums and expected table of this slot */
     if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
+    cg_dev_job J = s.hj[0];                    /* this launch's view of the job: one kind of CNV */
+    J.cnv[t] = d_in; J.calls[t] = d_out; J.n_cnv[t] = (int)n; J.n_cnv[t ^ 1] = 0;
+    J.cnv0[0] = 0; J.cnv0[1] = t ? 0 : (int)n;
+    cg_sub S = s.sub;
+    S.n_cnv = (int)n;
     {
         prof_scope ps(c, st, 2, 1);
-        CU(c, cgk_genotype(st, d_in, (int)n, t, s.d_depth, cgk_counts_layout(s.d_counts, s.n_chunks), s.gc_ptr, s.d_expected, s.runs_ptr, s.d_run_idx, s.n_runs, s.has_map,
-                           s.chrom_len, c->d_sticky, d_out, c->n_sms));
+        CU(c, cgk_genotype(st, S, J, c->n_sms));
     }
     if (staged) CU(c, cudaMemcpyAsync(out, d_out, n * sizeof(cg_call), cudaMemcpyDeviceToHost, st));
     CU(c, cudaEventRecord(s.ev_geno[t], st));
     s.geno_queued[t] = true;
+    s.dirty_geno[t] = true;
     if (blocking(c)) {
         CU(c, cudaStreamSynchronize(st));
         return report_sticky(c, "cg_genotype");
@@ -751,22 +874,237 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     return CG_OK;
 }
 
+} /* extern "C" */
+
+/* ------------------------------------------------------------------------- */
+/* a whole job list as one submission                                         */
+
+static int validate_job(cg_ctx* c, const cg_chrom_job& j, size_t k)
+{
+    if (j.chr_index < 0 || j.chr_index >= CG_MAX_CHROMS) return fail(c, CG_EINVAL, "job %zu: chr_index %d outside 0..%d", k, j.chr_index, CG_MAX_CHROMS - 1);
+    if (j.chrom_len <= 0 || j.chrom_len > INT32_MAX - 2 * CG_CHUNK * CG_SUPER_CHUNKS) return fail(c, CG_EINVAL, "job %zu: chrom_len %d", k, j.chrom_len);
+    if (!j.gc || j.n_windows < (j.chrom_len + 99) / 100) return fail(c, CG_EINVAL, "job %zu: gc_profile needs >= %d windows (got %d)", k, (j.chrom_len + 99) / 100, j.n_windows);
+    if (j.n_reads >= 0x7fffffffull) return fail(c, CG_EINVAL, "job %zu: more than 2^31-1 records on one chromosome", k);
+    if (j.n_reads && !j.reads && !j.reads_pos) return fail(c, CG_EINVAL, "job %zu: null records", k);
+    if (j.n_reads && !j.reads && !j.reads_mapq && j.mq_threshold >= 0) return fail(c, CG_EINVAL, "job %zu: a NULL mapq plane needs a negative mq_threshold", k);
+    if (j.n_runs > 0x7ffffff0ull || (j.n_runs && j.use_mappability && !j.runs)) return fail(c, CG_EINVAL, "job %zu: bad mappability runs", k);
+    if (j.n_del > 0x3fffffffull || j.n_dup > 0x3fffffffull) return fail(c, CG_EINVAL, "job %zu: too many CNVs", k);
+    if ((j.n_del && (!j.dels || !j.del_calls)) || (j.n_dup && (!j.dups || !j.dup_calls))) return fail(c, CG_EINVAL, "job %zu: null CNV argument", k);
+    return CG_OK;
+}
+
+static inline size_t al256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+/* n <= CG_JMAX jobs, DEVICE or asynchronous HOST pointer mode: one launch per kernel for all of them */
+static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
+{
+    int rc;
+    /* geometry of the submission */
+    long long space = 0, work = 0, mark_blocks = 0, run_blocks = 0, n_cnv = 0;
+    size_t in_bytes = 0, ridx_words = 0;
+    const bool host = c->ptr_mode == CG_PTR_HOST;
+    for (int k = 0; k < n; k++) {
+        const cg_chrom_job& j = jobs[k];
+        if ((rc = validate_job(c, j, (size_t)k)) != CG_OK) return rc;
+        const int n_chunks = (j.chrom_len + CG_CHUNK - 1) / CG_CHUNK;
+        space += cgk_job_space(n_chunks); work += n_chunks;
+        mark_blocks += (long long)((j.n_reads + 255) / 256);
+        if (j.use_mappability && j.n_runs) { run_blocks += (long long)((j.n_runs + 1 + 255) / 256); ridx_words += (size_t)cgk_run_index_words(j.chrom_len); }
+        n_cnv += (long long)(j.n_del + j.n_dup);
+        if (host) {
+            in_bytes += j.reads ? al256(j.n_reads * sizeof(cg_read)) : al256(j.n_reads * 4) + (j.reads_mapq ? al256(j.n_reads) : 0);
+            if (!(j.flags & CG_JOB_ANNOTATION_RESIDENT)) {
+                in_bytes += al256((size_t)(j.chrom_len + 99) / 100);
+                if (j.use_mappability) in_bytes += al256(j.n_runs * sizeof(cg_maprun));
+            }
+        }
+    }
+    if (space * CG_CHUNK >= ((long long)1 << 40) || space > 0x7fffffffll || mark_blocks > 0x7fffffffll || run_blocks > 0x7fffffffll || n_cnv > 0x7fffffffll)
+        return fail(c, CG_EINVAL, "submission too large for one launch");
+
+    int si;
+    if ((rc = take_slot(c, &si)) != CG_OK) return rc;
+    cg_slot& s = c->slot[si];
+    if ((rc = ensure_space(c, s, (int)space, false)) != CG_OK) return rc;
+    if (ridx_words && (rc = grow(c, &s.d_run_idx, &s.run_idx_cap, ridx_words, 0, &c->hw_run_idx)) != CG_OK) return rc;
+    if (host && (rc = grow(c, &s.d_in, &s.in_cap, in_bytes, 0, &c->hw_in)) != CG_OK) return rc;
+    /* the staging copy of the table is rewritten below: its previous upload must have read it */
+    CU(c, cudaEventSynchronize(s.ev_table));
+
+    s.sample = true; s.n_jobs = n; s.ptr_mode = c->ptr_mode; s.async = c->async;
+    s.src.assign(jobs, jobs + n);
+    fill_sub(c, s, n, (int)work, (int)space);
+    s.sub.jobs = s.d_jobs;
+    s.sub.n_mark_blocks = (int)mark_blocks; s.sub.n_run_blocks = (int)run_blocks; s.sub.n_cnv = (int)n_cnv;
+    s.sub.h_flags = s.h_flags;
+
+    int chunk0 = 0, work0 = 0, blk0 = 0, rblk0 = 0, cnv0 = 0;
+    size_t in_off = 0, ridx_off = 0;
+    bool any_runs = false;
+    auto stage = [&](const void* src, size_t bytes) -> void* {           /* upload into the slot's arena (HOST mode) */
+        char* dst = s.d_in + in_off;
+        in_off += al256(bytes);
+        if (bytes) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s.s_copy);
+        return dst;
+    };
+    for (int k = 0; k < n; k++) {
+        const cg_chrom_job& j = jobs[k];
+        cg_dev_job& J = s.hj[k];
+        memset(&J, 0, sizeof J);
+        const int n_chunks = (j.chrom_len + CG_CHUNK - 1) / CG_CHUNK;
+        J.chrom_len = j.chrom_len; J.n_chunks = n_chunks; J.chunk0 = chunk0; J.work0 = work0;
+        J.mq_threshold = j.mq_threshold; J.chr_index = j.chr_index;
+        J.n_reads = (long long)j.n_reads; J.mark_first = 0; J.mark_n = (long long)j.n_reads; J.mark_blk0 = blk0;
+        const bool annot_dev = !host || (j.flags & CG_JOB_ANNOTATION_RESIDENT);
+        if (host) {
+            J.gc = annot_dev ? j.gc : static_cast<const int8_t*>(stage(j.gc, (size_t)(j.chrom_len + 99) / 100));
+            if (j.reads) J.reads = static_cast<const cg_read*>(stage(j.reads, j.n_reads * sizeof(cg_read)));
+            else {
+                J.rec_pos = static_cast<const int32_t*>(stage(j.reads_pos, j.n_reads * 4));
+                if (j.reads_mapq) J.rec_mapq = static_cast<const uint8_t*>(stage(j.reads_mapq, j.n_reads));
+            }
+        } else {
+            J.gc = j.gc;
+            if (j.reads) J.reads = j.reads; else { J.rec_pos = j.reads_pos; J.rec_mapq = j.reads_mapq; }
+        }
+        J.stats_row = stats_row_of(c, j.chr_index);
+        J.row_out = reinterpret_cast<long long*>(j.stats);          /* page-locked (asynchronous HOST) or device memory */
+        J.expected = s.d_expected + 128 * k;
+        J.ctl = s.d_ctl + CG_CTL_WORDS * k;
+        J.has_map = j.use_mappability ? 1 : 0;
+        if (j.use_mappability && j.n_runs) {
+            J.runs = annot_dev ? j.runs : static_cast<const cg_maprun*>(stage(j.runs, j.n_runs * sizeof(cg_maprun)));
+            J.n_runs = (int)j.n_runs;
+            J.run_idx = s.d_run_idx + ridx_off; ridx_off += (size_t)cgk_run_index_words(j.chrom_len);
+            J.run_blk0 = rblk0; rblk0 += (int)((j.n_runs + 1 + 255) / 256);
+            any_runs = true;
+        } else {
+            J.run_blk0 = rblk0;
+        }
+        /* CNVs and calls: device memory, or the caller's page-locked arrays read and written across PCIe by the kernel */
+        J.cnv[0] = j.dels; J.calls[0] = j.del_calls; J.n_cnv[0] = (int)j.n_del; J.cnv0[0] = cnv0; cnv0 += (int)j.n_del;
+        J.cnv[1] = j.dups; J.calls[1] = j.dup_calls; J.n_cnv[1] = (int)j.n_dup; J.cnv0[1] = cnv0; cnv0 += (int)j.n_dup;
+        chunk0 += cgk_job_space(n_chunks); work0 += n_chunks; blk0 += (int)((j.n_reads + 255) / 256);
+        if (j.chr_index + 1 > c->n_rows) c->n_rows = j.chr_index + 1;
+    }
+    if (host) {
+        CU(c, cudaGetLastError());
+        CU(c, cudaEventRecord(s.ev_copy, s.s_copy));
+    }
+    memcpy(s.h_jobs, s.hj, sizeof(cg_dev_job) * (size_t)n);
+    CU(c, cudaMemcpyAsync(s.d_jobs, s.h_jobs, sizeof(cg_dev_job) * (size_t)n, cudaMemcpyHostToDevice, s.s_work));
+    CU(c, cudaEventRecord(s.ev_table, s.s_work));
+
+    const cg_dev_job& J0 = s.hj[0];            /* ignored by the kernels: the table is used */
+    {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_job_init(s.s_work, s.sub, J0, s.d_counts));
+    }
+    if (host) CU(c, cudaStreamWaitEvent(s.s_work, s.ev_copy, 0));
+    if (mark_blocks) {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_mark(s.s_work, s.sub, J0));
+    }
+    if (!getenv("CG_PASS_OVERLAP") || atoi(getenv("CG_PASS_OVERLAP")) != 0) { /* passes of consecutive submissions may overlap */ }
+    else { cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot]; if (o.used && &o != &s) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0)); }
+    {
+        prof_scope ps(c, s.s_work, 1, 1);
+        CU(c, cgk_depth_pass(s.s_work, s.sub, J0));
+    }
+    if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(s.s_work, c->ev_bank_read[c->bank], 0));
+    {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_finalize(s.s_work, s.sub, J0));
+    }
+    CU(c, cudaEventRecord(s.ev_pass, s.s_work));
+    s.dirty_work = true;
+    s.check = true;
+
+    if (n_cnv) {
+        cudaStream_t st = s.s_geno[0];
+        CU(c, cudaStreamWaitEvent(st, s.ev_table, 0));
+        if (any_runs) {
+            if (host) CU(c, cudaStreamWaitEvent(st, s.ev_copy, 0));
+            prof_scope ps(c, st, 2, 1);
+            CU(c, cgk_run_index(st, s.sub, J0));
+        }
+        CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));
+        {
+            prof_scope ps(c, st, 2, 1);
+            CU(c, cgk_genotype(st, s.sub, J0, c->n_sms));
+        }
+        CU(c, cudaEventRecord(s.ev_geno[0], st));
+        s.geno_queued[0] = true;
+        s.dirty_geno[0] = true;
+    }
+    c->in_chrom = false; c->finished = false;       /* no current chromosome: the per-chromosome calls need a cg_chrom_begin */
+    return CG_OK;
+}
+
+/* one job through the per-chromosome entry points (blocking HOST mode, and re-runs of flagged jobs) */
+static int run_one_job(cg_ctx* c, const cg_chrom_job& j)
+{
+    int rc;
+    if ((rc = cg_chrom_begin(c, j.chr_index, j.chrom_len, j.gc, j.n_windows, j.mq_threshold)) != CG_OK) return rc;
+    if (j.n_reads) {
+        rc = j.reads ? cg_push_reads(c, j.reads, (size_t)j.n_reads) : cg_push_reads_compact(c, j.reads_pos, j.reads_mapq, (size_t)j.n_reads);
+        if (rc != CG_OK) return rc;
+    }
+    if ((rc = cg_chrom_finish(c, j.stats)) != CG_OK) return rc;
+    if (j.use_mappability && (rc = cg_set_mappability_runs(c, j.runs, (size_t)j.n_runs, 1)) != CG_OK) return rc;
+    if (j.n_del && (rc = cg_genotype(c, j.dels, (size_t)j.n_del, 0, j.del_calls)) != CG_OK) return rc;
+    if (j.n_dup && (rc = cg_genotype(c, j.dups, (size_t)j.n_dup, 1, j.dup_calls)) != CG_OK) return rc;
+    return CG_OK;
+}
+
+/* A sample submission runs the sorted-input path unconditionally.  When it is complete the host looks at the
+ * flag words k_finalize left in page-locked memory: a job whose records were out of order (the reference asks
+ * for coordinate-sorted input, README.md:93, but its result does not depend on the order) is run again through
+ * the per-chromosome entry points, whose out-of-order path gives the reference's result. */
+static int settle_slot(cg_ctx* c, cg_slot& s)
+{
+    if (!s.check) return CG_OK;
+    s.check = false;
+    CU(c, cudaStreamSynchronize(s.s_work));
+    for (int t = 0; t < 2; t++) CU(c, cudaStreamSynchronize(s.s_geno[t]));
+    std::vector<cg_chrom_job> redo;
+    for (int k = 0; k < s.n_jobs; k++) if (s.h_flags[k] & CG_FLAG_UNSORTED) redo.push_back(s.src[(size_t)k]);
+    if (redo.empty()) return CG_OK;
+    const int mode = c->ptr_mode; const bool async = c->async;
+    const bool in_chrom = c->in_chrom, finished = c->finished; const int cur = c->cur;
+    c->ptr_mode = s.ptr_mode; c->async = s.async;
+    int rc = CG_OK;
+    for (const cg_chrom_job& j : redo) if ((rc = run_one_job(c, j)) != CG_OK) break;
+    if (rc == CG_OK) rc = sync_all(c);
+    c->ptr_mode = mode; c->async = async;
+    c->in_chrom = in_chrom; c->finished = finished; c->cur = cur;
+    return rc;
+}
+
+static int settle_samples(cg_ctx* c)
+{
+    for (int i = 0; i < CG_NSLOT; i++) {
+        int rc = settle_slot(c, c->slot[i]);
+        if (rc) return rc;
+    }
+    return CG_OK;
+}
+
+extern "C" {
+
 int cg_run_chromosomes(cg_ctx* c, const cg_chrom_job* jobs, size_t n_jobs)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (n_jobs && !jobs) return fail(c, CG_EINVAL, "null jobs");
-    const size_t BATCH = (size_t)1 << 22;
+    if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_run_chromosomes inside a chromosome");
+    CU(c, cudaSetDevice(c->device));
     int rc;
-    for (size_t k = 0; k < n_jobs; k++) {
-        const cg_chrom_job& j = jobs[k];
-        if ((rc = cg_chrom_begin(c, j.chr_index, j.chrom_len, j.gc, j.n_windows, j.mq_threshold)) != CG_OK) return rc;
-        for (size_t i = 0; i < j.n_reads; i += BATCH)
-            if ((rc = cg_push_reads(c, j.reads + i, j.n_reads - i < BATCH ? (size_t)(j.n_reads - i) : BATCH)) != CG_OK) return rc;
-        if ((rc = cg_chrom_finish(c, j.stats)) != CG_OK) return rc;
-        if (j.use_mappability && (rc = cg_set_mappability_runs(c, j.runs, (size_t)j.n_runs, 1)) != CG_OK) return rc;
-        if (j.n_del && (rc = cg_genotype(c, j.dels, (size_t)j.n_del, 0, j.del_calls)) != CG_OK) return rc;
-        if (j.n_dup && (rc = cg_genotype(c, j.dups, (size_t)j.n_dup, 1, j.dup_calls)) != CG_OK) return rc;
+    if (blocking(c)) {
+        for (size_t k = 0; k < n_jobs; k++) if ((rc = run_one_job(c, jobs[k])) != CG_OK) return rc;
+        return CG_OK;
     }
+    for (size_t k = 0; k < n_jobs; k += CG_JMAX)
+        if ((rc = submit_sample(c, jobs + k, (int)std::min<size_t>(CG_JMAX, n_jobs - k))) != CG_OK) return rc;
     return CG_OK;
 }
 
@@ -777,8 +1115,8 @@ int cg_download_depth(cg_ctx* c, int16_t* out)
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_depth before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    CU(c, cudaMemcpyAsync(out, s.d_depth, (size_t)s.chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, c->s_slot[c->cur]));
-    CU(c, cudaStreamSynchronize(c->s_slot[c->cur]));
+    CU(c, cudaMemcpyAsync(out, s.d_depth, (size_t)s.hj[0].chrom_len * sizeof(int16_t), cudaMemcpyDeviceToHost, s.s_work));
+    CU(c, cudaStreamSynchronize(s.s_work));
     return CG_OK;
 }
 
@@ -788,12 +1126,12 @@ int cg_download_prefix(cg_ctx* c, int32_t* out)
     if (!c->finished) return fail(c, CG_EINVAL, "cg_download_prefix before cg_chrom_finish");
     CU(c, cudaSetDevice(c->device));
     cg_slot& s = c->slot[c->cur];
-    cudaStream_t st = c->s_slot[c->cur];
+    cudaStream_t st = s.s_work;
     /* no prefix array exists on the product path: rebuilt here from the depth array and the chunk sums */
     int32_t* d_prefix = nullptr;
-    CU(c, cudaMalloc(&d_prefix, (size_t)s.n_chunks * CG_CHUNK * sizeof(int32_t)));
-    cudaError_t e = cgk_prefix_from_depth(st, s.d_depth, cgk_counts_layout(s.d_counts, s.n_chunks), s.n_chunks, d_prefix);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_prefix, (size_t)s.chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+    CU(c, cudaMalloc(&d_prefix, (size_t)s.hj[0].n_chunks * CG_CHUNK * sizeof(int32_t)));
+    cudaError_t e = cgk_prefix_from_depth(st, s.d_depth, s.sub.k, 0, s.hj[0].n_chunks, d_prefix);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_prefix, (size_t)s.hj[0].chrom_len * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     cudaFree(d_prefix);
     CU(c, e);
@@ -809,10 +1147,16 @@ int cg_device_arrays(cg_ctx* c, const int16_t** depth, const float** expected)
     return CG_OK;
 }
 
+/* ---- statistics tables and the collective -------------------------------------------------- */
+static long long* table_of(cg_ctx* c, int bank)
+{
+    return (c->comm ? c->d_stats_all : c->d_stats) + (size_t)bank * CG_MAX_CHROMS * CG_STATS_WORDS;
+}
+
 int cg_stats_table(cg_ctx* c, void** device_ptr, int32_t* n_rows)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (device_ptr) *device_ptr = c->d_stats + (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
+    if (device_ptr) *device_ptr = table_of(c, c->bank);
     if (n_rows) *n_rows = c->n_rows;
     return CG_OK;
 }
@@ -823,37 +1167,22 @@ int cg_stats_reset(cg_ctx* c)
     CU(c, cudaSetDevice(c->device));
     int rc = cg_join(c);                      /* rows may still be written or copied by queued work */
     if (rc) return rc;
-    /* the whole bank: an in-place collective also fills the rows of chromosomes this context never saw */
-    CU(c, cudaMemsetAsync(c->d_stats + (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS, 0,
-                          sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS, c->s_main));
-    CU(c, cudaEventRecord(c->ev_reset, c->s_main));
-    for (int i = 0; i < CG_NSLOT; i++) c->slot[i].wait_reset = true;
+    const size_t bytes = sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS, off = (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
+    CU(c, cudaMemsetAsync(c->d_stats + off, 0, bytes, c->s_main));
+    if (c->d_stats_all) CU(c, cudaMemsetAsync(c->d_stats_all + off, 0, bytes, c->s_main));
+    /* chromosomes that write into this bank from now on wait for the clear, like for a collective that reads it */
+    CU(c, cudaEventRecord(c->ev_bank_read[c->bank], c->s_main));
+    c->bank_read[c->bank] = true;
     c->n_rows = 0;
     return CG_OK;
 }
 
-/* Two statistics tables so that the collective over sample k's table (queued on cg_stream after
- * cg_join) can be in flight while the chromosomes of sample k+1 fill the other one.  Selecting a
- * bank clears it on a side stream, ordered behind everything that was queued on cg_stream when the
- * bank was left (the collective that read it); the chromosomes begun afterwards wait for that
- * clear only, never for the other bank's collective. */
 int cg_stats_bank(cg_ctx* c, int bank)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (bank != 0 && bank != 1) return fail(c, CG_EINVAL, "bank %d must be 0 or 1", bank);
+    if (bank < 0 || bank >= CG_NBANK) return fail(c, CG_EINVAL, "bank %d must be 0 or 1", bank);
     if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_stats_bank inside a chromosome");
-    if (bank == c->bank) return CG_OK;
-    CU(c, cudaSetDevice(c->device));
-    if (c->dirty) { int rc = cg_join(c); if (rc) return rc; }      /* the table being left is complete behind this point */
-    CU(c, cudaEventRecord(c->ev_left[c->bank], c->s_main));
-    c->bank_left[c->bank] = true;
-    if (c->bank_left[bank]) CU(c, cudaStreamWaitEvent(c->s_bank, c->ev_left[bank], 0));
-    if (c->bank_left[bank])
-        CU(c, cudaMemsetAsync(c->d_stats + (size_t)bank * CG_MAX_CHROMS * CG_STATS_WORDS, 0,
-                              sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS, c->s_bank));
-    CU(c, cudaEventRecord(c->ev_reset, c->s_bank));
-    for (int i = 0; i < CG_NSLOT; i++) c->slot[i].wait_reset = true;
-    c->bank = bank; c->n_rows = 0;
+    c->bank = bank;
     return CG_OK;
 }
 
@@ -864,10 +1193,127 @@ int cg_stats_row(cg_ctx* c, int chr_index, cg_chrom_stats* out)
     CU(c, cudaSetDevice(c->device));
     int rc = sync_all(c);
     if (rc) return rc;
-    CU(c, cudaMemcpyAsync(c->h_stats, c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS, sizeof(cg_chrom_stats),
+    if ((rc = settle_samples(c)) != CG_OK) return rc;
+    CU(c, cudaMemcpyAsync(c->h_stats, table_of(c, c->bank) + (size_t)chr_index * CG_STATS_WORDS, sizeof(cg_chrom_stats),
                           cudaMemcpyDeviceToHost, c->s_main));
     CU(c, cudaStreamSynchronize(c->s_main));
     memcpy(out, c->h_stats, sizeof(cg_chrom_stats));
+    return CG_OK;
+}
+
+} /* extern "C" */
+
+/* NCCL is looked up at run time: libconga_gpu.so has no link-time dependency on it, and in a process that
+ * already carries one (PyTorch's) the same library is used. */
+static cg_nccl_api g_nccl;
+static std::mutex g_nccl_mutex;
+
+static int nccl_load(cg_ctx* c)
+{
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
+    if (g_nccl.handle) return CG_OK;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(c, CG_ECUDA, "NCCL not found: %s", dlerror());
+    cg_nccl_api a;
+    a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+    a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+    a.CommInitAll = reinterpret_cast<decltype(a.CommInitAll)>(dlsym(h, "ncclCommInitAll"));
+    a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+    a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(dlsym(h, "ncclAllReduce"));
+    a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+    a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(dlsym(h, "ncclGroupStart"));
+    a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(dlsym(h, "ncclGroupEnd"));
+    if (!a.GetUniqueId || !a.CommInitRank || !a.CommInitAll || !a.CommDestroy || !a.AllReduce || !a.GetErrorString || !a.GroupStart || !a.GroupEnd)
+        return fail(c, CG_ECUDA, "NCCL library lacks a required symbol");
+    a.handle = h;
+    g_nccl = a;
+    return CG_OK;
+}
+
+static int comm_tables(cg_ctx* c)
+{
+    if (c->d_stats_all) return CG_OK;
+    const size_t bytes = sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * CG_NBANK;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMalloc(&c->d_stats_all, bytes));
+    CU(c, cudaMemset(c->d_stats_all, 0, bytes));
+    return CG_OK;
+}
+
+extern "C" {
+
+int cg_comm_unique_id(void* id)
+{
+    if (!id) return fail(nullptr, CG_EINVAL, "null id");
+    int rc = nccl_load(nullptr);
+    if (rc) return rc;
+    const int e = g_nccl.GetUniqueId(id);
+    if (e) return fail(nullptr, CG_ECUDA, "ncclGetUniqueId: %s", g_nccl.GetErrorString(e));
+    return CG_OK;
+}
+
+int cg_comm_init_rank(cg_ctx* c, int n_ranks, int rank, const void* id)
+{
+    if (!c || !id) return fail(c, CG_EINVAL, "null argument");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(c, CG_EINVAL, "rank %d of %d", rank, n_ranks);
+    if (c->comm) return fail(c, CG_EINVAL, "the context already has a communicator");
+    int rc = nccl_load(c);
+    if (rc) return rc;
+    CU(c, cudaSetDevice(c->device));
+    if ((rc = sync_all(c)) != CG_OK) return rc;
+    if ((rc = comm_tables(c)) != CG_OK) return rc;
+    cg_nccl_id uid;
+    memcpy(&uid, id, sizeof uid);
+    const int e = g_nccl.CommInitRank(&c->comm, n_ranks, uid, rank);
+    if (e) { c->comm = nullptr; return fail(c, CG_ECUDA, "ncclCommInitRank: %s", g_nccl.GetErrorString(e)); }
+    c->comm_ranks = n_ranks;
+    return CG_OK;
+}
+
+int cg_comm_init_all(cg_ctx** ctxs, int n)
+{
+    if (!ctxs || n < 1) return fail(nullptr, CG_EINVAL, "bad argument");
+    int rc = nccl_load(ctxs[0]);
+    if (rc) return rc;
+    std::vector<int> devs((size_t)n);
+    std::vector<cg_nccl_comm_t> comms((size_t)n, nullptr);
+    for (int i = 0; i < n; i++) {
+        if (!ctxs[i] || ctxs[i]->comm) return fail(ctxs[i], CG_EINVAL, "context %d is null or already has a communicator", i);
+        devs[(size_t)i] = ctxs[i]->device;
+        if ((rc = comm_tables(ctxs[i])) != CG_OK) return rc;
+    }
+    const int e = g_nccl.CommInitAll(comms.data(), n, devs.data());
+    if (e) return fail(ctxs[0], CG_ECUDA, "ncclCommInitAll: %s", g_nccl.GetErrorString(e));
+    for (int i = 0; i < n; i++) { ctxs[i]->comm = comms[(size_t)i]; ctxs[i]->comm_ranks = n; }
+    return CG_OK;
+}
+
+int cg_comm_destroy(cg_ctx* c)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (c->comm && g_nccl.CommDestroy) { cudaSetDevice(c->device); g_nccl.CommDestroy(c->comm); }
+    c->comm = nullptr; c->comm_ranks = 0;
+    return CG_OK;
+}
+
+int cg_stats_allreduce(cg_ctx* c, int32_t n_rows)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (!c->comm) return fail(c, CG_EINVAL, "cg_stats_allreduce without a communicator (cg_comm_init_rank)");
+    if (n_rows < 0 || n_rows > CG_MAX_CHROMS) return fail(c, CG_EINVAL, "n_rows %d", n_rows);
+    if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_stats_allreduce inside a chromosome");
+    CU(c, cudaSetDevice(c->device));
+    int rc = cg_join(c);                       /* cg_stream now waits for every row written so far */
+    if (rc) return rc;
+    if (n_rows == 0) return CG_OK;
+    const size_t off = (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
+    const int e = g_nccl.AllReduce(c->d_stats + off, c->d_stats_all + off, (size_t)n_rows * CG_STATS_WORDS, /* ncclInt64 */ 4, /* ncclSum */ 0,
+                                   c->comm, c->s_main);
+    if (e) return fail(c, CG_ECUDA, "ncclAllReduce: %s", g_nccl.GetErrorString(e));
+    CU(c, cudaEventRecord(c->ev_bank_read[c->bank], c->s_main));
+    c->bank_read[c->bank] = true;
+    c->launch_count += 1;
     return CG_OK;
 }
 
@@ -919,8 +1365,8 @@ int cg_sr_reference(cg_ctx* c, const char* ref_seq, int32_t ref_len)
     CU(c, cudaStreamSynchronize(r.st));            /* ref_seq may be pageable and may die at return */
     r.ref_len = ref_len;
     r.have_ref = true;
-    r.chrom_len = c->slot[c->cur].chrom_len;
-    r.mq_threshold = c->mq_threshold;
+    r.chrom_len = c->slot[c->cur].hj[0].chrom_len;
+    r.mq_threshold = c->slot[c->cur].hj[0].mq_threshold;
     return CG_OK;
 }
 

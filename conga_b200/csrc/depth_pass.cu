@@ -1,40 +1,38 @@
-/* depth_pass.cu — the fused read-depth pass of one chromosome on sm_100a.
+/* depth_pass.cu — the fused read-depth pass on sm_100a, over a SUBMISSION of up to CG_JMAX chromosomes.
  *
- * Replaces, in ONE sweep over the chromosome's positions (no intermediate HBM
+ * Replaces, in ONE sweep over the positions of every chromosome of the submission (no intermediate HBM
  * round trip):
  *   K1  read_depth[pos]++ per passing record        bam_data.c:201-217, read_distribution.c:12-18
  *   K2  chromosome sum + 101 GC-bin sums/counts     read_distribution.c:27-46, :49-73
  *   K3  per-CNV depth sums in O(1): NOT a prefix array — the chunk / group / super depth sums left by the
  *       record sweep plus the depth array itself serve likelihood.c:115-121 (genotype.cu, depth_sum_before)
  *
- * Data layout in HBM (per chromosome slot, reused across chromosomes):
- *   reads      cg_read[N]            8 B records, coordinate sorted
- *   chunk_lo   int32[n_chunks+1]     first record of every 2048-position chunk
+ * Kernels, one launch each per submission (a whole sample through cg_run_chromosomes, or one chromosome
+ * through cg_chrom_begin ... cg_chrom_finish):
+ *   k_job_init     counts of the chunk space zeroed, chunk bounds "behind the last record", control words
+ *   k_mark         one sweep over the records: sortedness / range flags, first record of every chunk,
+ *                  passing records per chunk / group / super and per chromosome
+ *   k_depth_pass   persistent warps pull chunks of ALL chromosomes from one counter (no per-chromosome ramp
+ *                  and tail); shared-memory histogram -> int16 depth vectors; GC-bin sums per CTA and job
+ *   k_finalize     per-CTA partial rows -> cg_chrom_stats row, expected_read_depth[101], flags for the host
+ *   k_rare_scatter out-of-order input (per-chromosome entry points only; a sample submission that meets
+ *                  unsorted records is re-run through them by the host side, conga_gpu.cu)
+ *
+ * Data layout in HBM (per slot; job j owns chunks [chunk0, chunk0 + n_chunks] of the slot's chunk space):
+ *   reads      cg_read[N] or pos int32[N] + mapq u8[N]   coordinate sorted
+ *   chunk_lo   int32[n_space]        first record of every 2048-position chunk
  *   cnt1/2/3   int32[...]            sum of the int16 depths per chunk / 32 chunks / 1024 chunks
- *   depth      int16[n_chunks*2048]  the reference's `short read_depth[]` (wraps mod 2^16)
- *   stats      int64[204]            cg_chrom_stats row
+ *   depth      int16[n_space*2048]   the reference's `short read_depth[]` (wraps mod 2^16)
+ *   partial    int32[CTAs][jobs][202]  what each CTA of the pass saw of each chromosome's GC bins
  *
- * The scan carry never travels between warps.  A chunk's depth sum is the number of
- * passing records that fall in it (every read adds exactly 1) unless a position
- * collects >= 32768 reads and the int16 wraps; k_mark_batch therefore counts records
- * per chunk / group / super while it checks the pushed batch (the records are read
- * once, 8 B each, against 6 B per POSITION for the pass) and k_rare_paths corrects the
- * counts for wrapped pile-ups.  A chunk's carry is then three short coalesced loads:
- * the supers in front of its super, the groups in front of its group inside the super,
- * the chunks in front of it inside the group.  The pass is embarrassingly parallel
- * over chunks: no look-back, no spinning, no block barrier, no separate scan kernel.
+ * A chunk's depth sum is the number of passing records that fall in it (every read adds exactly 1) unless
+ * a position collects >= 32768 reads and the int16 goes negative.  The pass notices that while it bins the
+ * records, takes the sums of such a chunk from a scan of its bins instead, and corrects the three count
+ * levels itself.  The pass is embarrassingly parallel over chunks: no look-back, no spinning, no block
+ * barrier inside the loop, no separate scan kernel, no global atomics except the work counter.
  *
- * Algorithmic bytes per chromosome: 8·N (records) + 2·L (depth, written once) + L/100 (GC bytes); the
- * pass is HBM-write bound.  (SURVEY §8d's plan also wrote a 4·L int32 prefix; rounds r01a-r01g did, at
- * 6 B per position.  It was only ever read at two positions per CNV, see genotype.cu.)
- *
- * Pass kernel shape: persistent warps pulling chunks from a counter; a warp owns 4 KB of
- * packed u16 bins in shared memory.  Per chunk: warp-aggregated shared histogram of the
- * chunk's records -> the eight 256-position rows are summed per lane and their eight
- * warp scans run interleaved (eight independent shuffle chains) -> per row one 16-byte
- * LDS (which is also the 16-byte int16 output vector) and two 16-byte prefix stores,
- * bins zeroed behind -> per-window sums from the prefixes at window ends into 101
- * shared GC accumulators.
+ * Algorithmic bytes per chromosome: 8·N (records; 5·N or 4·N in the compact formats) + 2·L (depth, written
+ * once) + L/100 (GC bytes); the pass is HBM-write bound.
  */
 #include "cg_internal.h"
 #include <cstdlib>
@@ -48,6 +46,8 @@
 
 static_assert(CG_SUPER_SHIFT - CG_GROUP_SHIFT == LVL && LVL == 5, "32 children per level, one per lane");
 static_assert((1 << CG_CHUNK_SHIFT) == CG_CHUNK && ROWS == 8, "chunk geometry");
+static_assert(CG_SUPER_CHUNKS == 1 << (2 * LVL), "a super is 1024 chunks");
+static_assert(CG_JMAX <= 32, "one lane / one thread per job in the set-up code");
 
 __device__ __forceinline__ int sext16(unsigned v) { return (int)(short)(v & 0xffffu); }
 
@@ -61,58 +61,75 @@ __device__ __forceinline__ int warp_incl_scan(int v, int lane)
     return v;
 }
 
-/* streaming stores: depth/prefix are written once and not re-read by this kernel */
+/* streaming stores: depth is written once and not re-read by this kernel */
 __device__ __forceinline__ void st_cs_v4(void* p, unsigned a, unsigned b, unsigned c, unsigned d)
 {
     asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 /* ------------------------------------------------------------------------- */
-static inline int n_groups_of(int n_chunks) { return (n_chunks + 31) >> LVL; }
-static inline int n_supers_of(int n_chunks) { return (n_chunks + 1023) >> (2 * LVL); }
 static inline size_t pad4(size_t n) { return (n + 3) & ~(size_t)3; }
 
-size_t cgk_counts_words(int n_chunks)
+/* chunk space of one job: its chunks plus the bound behind the last one, rounded up to whole supers */
+int cgk_job_space(int n_chunks) { return (n_chunks + 1 + CG_SUPER_CHUNKS - 1) / CG_SUPER_CHUNKS * CG_SUPER_CHUNKS; }
+
+size_t cgk_counts_words(int n_space)
 {
-    return pad4((size_t)n_chunks + 1) + pad4((size_t)n_chunks) + pad4((size_t)n_groups_of(n_chunks)) + pad4((size_t)n_supers_of(n_chunks));
+    return pad4((size_t)n_space) * 2 + pad4((size_t)n_space >> LVL) + pad4((size_t)n_space >> (2 * LVL));
 }
 
-cg_counts cgk_counts_layout(int32_t* base, int n_chunks)
+cg_counts cgk_counts_layout(int32_t* base, int n_space)
 {
     cg_counts k;
     k.cnt1 = base;                                            /* the three zeroed arrays first, chunk_lo last */
-    k.cnt2 = k.cnt1 + pad4((size_t)n_chunks);
-    k.cnt3 = k.cnt2 + pad4((size_t)n_groups_of(n_chunks));
-    k.chunk_lo = k.cnt3 + pad4((size_t)n_supers_of(n_chunks));
+    k.cnt2 = k.cnt1 + pad4((size_t)n_space);
+    k.cnt3 = k.cnt2 + pad4((size_t)n_space >> LVL);
+    k.chunk_lo = k.cnt3 + pad4((size_t)n_space >> (2 * LVL));
     return k;
 }
 
-/* chromosome start: clear the counts, the stats row and the control words; every chunk
- * bound starts "behind the last record" (the pass clamps it to the record count) */
-__global__ void k_chrom_init(int4* base4, int n_zero_vec, int n_vec, long long* stats_row, unsigned int* ctl)
+/* the records of a job, whichever format they came in */
+struct rec_src { const uint2* aos; const int* pos; const unsigned char* mapq; };
+
+__device__ __forceinline__ void load_rec(const rec_src& r, long long i, int& pos, int& mapq)
 {
+    if (r.aos) {
+        const uint2 v = __ldg(r.aos + i);
+        pos = (int)v.x; mapq = (int)((v.y >> 16) & 0xffu);
+    } else {
+        pos = __ldg(r.pos + i);
+        mapq = r.mapq ? (int)__ldg(r.mapq + i) : 255;        /* no mapq plane: the threshold is negative, everything passes */
+    }
+}
+__device__ __forceinline__ int load_pos(const rec_src& r, long long i) { return r.aos ? (int)__ldg(&r.aos[i].x) : __ldg(r.pos + i); }
+
+/* submission start: clear the counts and the control words; every chunk bound starts "behind the last
+ * record" (the pass clamps it to the record count) */
+__global__ void k_job_init(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1, int4* base4, int n_zero_vec, int n_vec)
+{
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
     const int i = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     for (int j = i; j < n_vec; j += stride)
         base4[j] = j < n_zero_vec ? make_int4(0, 0, 0, 0) : make_int4(0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff);
-    if (i < CG_STATS_WORDS) stats_row[i] = 0;
-    if (i < 4) ctl[i] = 0u;
+    if (i < S.n_jobs * CG_CTL_WORDS) jobs[i / CG_CTL_WORDS].ctl[i % CG_CTL_WORDS] = 0u;
+    if (i < 4) S.sctl[i] = 0u;
 }
 
-cudaError_t cgk_chrom_init(cudaStream_t s, int32_t* counts_base, int n_chunks, long long* stats_row, unsigned int* ctl)
+cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int32_t* counts_base)
 {
-    const cg_counts k = cgk_counts_layout(counts_base, n_chunks);
+    const cg_counts k = cgk_counts_layout(counts_base, S.n_space);
     const int n_zero_vec = (int)((k.chunk_lo - counts_base) / 4);
-    const int n_vec = (int)(cgk_counts_words(n_chunks) / 4);
+    const int n_vec = (int)(cgk_counts_words(S.n_space) / 4);
     int blocks = (n_vec + 255) / 256;
-    if (blocks < 1) blocks = 1;
-    if (blocks > 148 * 2) blocks = 148 * 2;
-    k_chrom_init<<<blocks, 256, 0, s>>>(reinterpret_cast<int4*>(counts_base), n_zero_vec, n_vec, stats_row, ctl);
+    if (blocks < 2) blocks = 2;                   /* CG_JMAX * CG_CTL_WORDS = 256 control words fit the first CTA */
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    k_job_init<<<blocks, 256, 0, s>>>(S, J1, reinterpret_cast<int4*>(counts_base), n_zero_vec, n_vec);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
-/* per pushed batch, one sweep over its records: sortedness and range checks,  */
-/* chunk boundaries, passing records per chunk/group/super, pile-up probe      */
+/* one sweep over the records of the submission: sortedness and range checks,  */
+/* chunk boundaries, passing records per chunk/group/super                     */
 __device__ __forceinline__ int chunk_of(int pos, int n_chunks)
 {
     int t = pos >> CG_CHUNK_SHIFT;            /* arithmetic shift: negative pos -> negative chunk */
@@ -132,184 +149,134 @@ __device__ __forceinline__ bool run_leader(int key, int lane, int& cnt)
 }
 
 __global__ void __launch_bounds__(256)
-k_mark_batch(const cg_read* __restrict__ reads, long long first, long long n, cg_counts kk,
-             int n_chunks, int32_t chrom_len, int mq_threshold, unsigned int* ctl, long long* stats_row)
+k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
-    const long long stride = (long long)gridDim.x * blockDim.x;
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
+    __shared__ int s_blk0[CG_JMAX + 1];
+    if (threadIdx.x <= S.n_jobs) s_blk0[threadIdx.x] = threadIdx.x < S.n_jobs ? jobs[threadIdx.x].mark_blk0 : S.n_mark_blocks;
+    __syncthreads();
     const int lane = threadIdx.x & 31;
+    int j = 0, cur = -1;
+    /* what the current job says, in registers */
+    rec_src R = {nullptr, nullptr, nullptr};
+    long long first = 0, n = 0;
+    int n_chunks = 1, chrom_len = 0, mq = -1, chunk0 = 0;
+    unsigned int* ctl = nullptr;
     unsigned f = 0;
     int n_pass = 0;
-    /* whole warps iterate together (k - lane is warp-uniform) so the shuffles below are safe */
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k - lane < n; k += stride) {
+    for (int b = blockIdx.x; b < S.n_mark_blocks; b += gridDim.x) {
+        while (b >= s_blk0[j + 1]) j++;                       /* blocks are visited in ascending order */
+        if (j != cur) {
+            if (cur >= 0) {                                   /* leave the previous job: flags and passing records */
+                if (f) atomicOr(&ctl[CG_W_FLAGS], f);
+                n_pass = __reduce_add_sync(FULL, n_pass);
+                if (lane == 0 && n_pass) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + CG_W_PASSED), (unsigned long long)n_pass);
+            }
+            const cg_dev_job& J = jobs[j];
+            R.aos = reinterpret_cast<const uint2*>(J.reads); R.pos = J.rec_pos; R.mapq = J.rec_mapq;
+            first = J.mark_first; n = J.mark_n;
+            n_chunks = J.n_chunks; chrom_len = J.chrom_len; mq = J.mq_threshold; chunk0 = J.chunk0; ctl = J.ctl;
+            f = 0; n_pass = 0; cur = j;
+        }
+        const long long k = (long long)(b - s_blk0[j]) * 256 + threadIdx.x;
         const bool in = k < n;
         const long long i = first + k;
-        int p = 0, key = -1 - lane;
+        int key = -1 - lane;
         if (in) {
-            const uint2 r = __ldg(reinterpret_cast<const uint2*>(reads) + i);
-            p = (int)r.x;
-            const int mapq = (int)((r.y >> 16) & 0xffu);
+            int p, mapq;
+            load_rec(R, i, p, mapq);
             const int cp = chunk_of(p, n_chunks);
             int cq = -1;
             if (i > 0) {
-                const int q = reads[i - 1].pos;
+                const int q = load_pos(R, i - 1);
                 if (p < q) f |= CG_FLAG_UNSORTED;
                 cq = chunk_of(q, n_chunks);
             }
             const bool inside = p >= 0 && p < chrom_len;
             if (!inside) f |= CG_FLAG_RANGE;
-            for (int t = cq + 1; t <= cp; t++) kk.chunk_lo[t] = (int32_t)i;
-            if (mapq > mq_threshold) {                                   /* bam_data.c:205 */
+            for (int t = cq + 1; t <= cp; t++) S.k.chunk_lo[chunk0 + t] = (int32_t)i;
+            if (mapq > mq) {                                             /* bam_data.c:205 */
                 n_pass++;                                                /* bam_data.c:214 */
-                if (inside) key = cp;
+                if (inside) key = chunk0 + cp;
             }
-            /* a run of >= 32768 equal positions contains two indices that are multiples of the
-             * probe distance, so the later one sees the earlier one */
-            if ((i & (CG_PILEUP_PROBE - 1)) == 0 && i >= CG_PILEUP_PROBE && reads[i - CG_PILEUP_PROBE].pos == p)
-                f |= CG_FLAG_PILEUP;
         }
         /* sorted stream: records of one chunk sit in adjacent lanes -> one atomic per chunk per warp,
          * and the same for the two coarser levels */
         int cnt;
-        if (run_leader(key, lane, cnt) && key >= 0) atomicAdd(&kk.cnt1[key], cnt);
+        if (run_leader(key, lane, cnt) && key >= 0) atomicAdd(&S.k.cnt1[key], cnt);
         const int gkey = key >= 0 ? key >> LVL : key;
-        if (run_leader(gkey, lane, cnt) && gkey >= 0) atomicAdd(&kk.cnt2[gkey], cnt);
+        if (run_leader(gkey, lane, cnt) && gkey >= 0) atomicAdd(&S.k.cnt2[gkey], cnt);
         const int skey = key >= 0 ? key >> (2 * LVL) : key;
-        if (run_leader(skey, lane, cnt) && skey >= 0) atomicAdd(&kk.cnt3[skey], cnt);
+        if (run_leader(skey, lane, cnt) && skey >= 0) atomicAdd(&S.k.cnt3[skey], cnt);
     }
-    if (f) atomicOr(&ctl[CG_W_FLAGS], f);
-    n_pass = __reduce_add_sync(FULL, n_pass);
-    if (lane == 0 && n_pass)
-        atomicAdd((unsigned long long*)&stats_row[2 * CG_GC_BINS + 1], (unsigned long long)n_pass);
+    if (cur >= 0) {
+        if (f) atomicOr(&ctl[CG_W_FLAGS], f);
+        n_pass = __reduce_add_sync(FULL, n_pass);
+        if (lane == 0 && n_pass) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + CG_W_PASSED), (unsigned long long)n_pass);
+    }
 }
 
-cudaError_t cgk_mark_batch(cudaStream_t s, const cg_read* reads, long long first, long long n,
-                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
-                           unsigned int* ctl, long long* stats_row)
+cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 {
-    if (n <= 0) return cudaSuccess;
-    long long blocks = (n + 255) / 256;
+    if (S.n_mark_blocks <= 0) return cudaSuccess;
+    int blocks = S.n_mark_blocks;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_mark_batch<<<(int)blocks, 256, 0, s>>>(reads, first, n, k, n_chunks, chrom_len, mq_threshold, ctl, stats_row);
+    k_mark<<<blocks, 256, 0, s>>>(S, J1);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
-/* rare paths; both kernels return at once for a sorted stream without pile-ups */
-
-/* out-of-order input: global-atomic histogram into u32 words (zero at rest: the
- * pass clears every word it consumes) */
-__global__ void k_rare_scatter(const cg_read* __restrict__ reads, long long n_reads, uint32_t* depth32,
-                               int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
+/* out-of-order input (per-chromosome entry points): global-atomic histogram into u32 words (zero at
+ * rest: the pass clears every word it consumes).  Returns at once for a sorted stream. */
+__global__ void k_rare_scatter(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
-    if (!(ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED)) return;
+    const cg_dev_job& J = S.jobs ? S.jobs[0] : J1;
+    if (!(J.ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED)) return;
+    const rec_src R = {reinterpret_cast<const uint2*>(J.reads), J.rec_pos, J.rec_mapq};
+    uint32_t* d32 = S.depth32 + ((size_t)J.chunk0 << CG_CHUNK_SHIFT);
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_reads; i += stride) {
-        const uint2 r = *reinterpret_cast<const uint2*>(&reads[i]);
-        const int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
-        if (mapq > mq_threshold && pos >= 0 && pos < chrom_len) atomicAdd(&depth32[pos], 1u);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < J.n_reads; i += stride) {
+        int pos, mapq;
+        load_rec(R, i, pos, mapq);
+        if (mapq > J.mq_threshold && pos >= 0 && pos < J.chrom_len) atomicAdd(&d32[pos], 1u);
     }
 }
 
-__device__ __forceinline__ void counts_add(const cg_counts& k, int chunk, int delta)
+cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms)
 {
-    atomicAdd(&k.cnt1[chunk], delta);
-    atomicAdd(&k.cnt2[chunk >> LVL], delta);
-    atomicAdd(&k.cnt3[chunk >> (2 * LVL)], delta);
-}
-
-/* unsorted: chunk sums recomputed from the scattered counts (covers int16 wrap too).
- * sorted with a pile-up flagged: for every run of equal positions longer than the probe
- * distance, count its passing records c and replace the +c by sext16(c). */
-__global__ void __launch_bounds__(256)
-k_rare_totals(const cg_read* __restrict__ reads, long long n_reads, const uint32_t* __restrict__ depth32,
-              cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold, const unsigned int* ctl)
-{
-    const unsigned fl = ctl[CG_W_FLAGS];
-    if (!(fl & (CG_FLAG_UNSORTED | CG_FLAG_PILEUP))) return;
-    const int lane = threadIdx.x & 31;
-    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
-    if (fl & CG_FLAG_UNSORTED) {
-        for (long long c = warp; c < n_chunks; c += n_warps) {
-            const uint4* src = reinterpret_cast<const uint4*>(depth32 + c * CG_CHUNK);
-            int s = 0;
-            for (int q = lane; q < CG_CHUNK / 4; q += 32) {
-                const uint4 v = src[q];
-                s += sext16(v.x) + sext16(v.y) + sext16(v.z) + sext16(v.w);
-            }
-            s = __reduce_add_sync(FULL, s);
-            /* the record count of the chunk is order independent; only a wrap changes it */
-            if (lane == 0) {
-                const int old = k.cnt1[c];
-                if (s != old) counts_add(k, (int)c, s - old);
-            }
-        }
-        return;
-    }
-    const long long n_groups = (n_reads + 31) >> 5;
-    for (long long g = warp; g < n_groups; g += n_warps) {
-        const long long i = (g << 5) + lane;
-        int p = 0;
-        bool start = false;
-        if (i < n_reads) {
-            p = reads[i].pos;
-            start = (i == 0 || reads[i - 1].pos != p) && i + CG_PILEUP_PROBE < n_reads
-                    && reads[i + CG_PILEUP_PROBE].pos == p;
-        }
-        unsigned m = __ballot_sync(FULL, start);
-        while (m) {
-            const int l = __ffs(m) - 1;
-            m &= m - 1;
-            const long long i0 = __shfl_sync(FULL, i, l);
-            const int p0 = __shfl_sync(FULL, p, l);
-            int c = 0;
-            for (long long j = i0;; j += 32) {
-                const long long jj = j + lane;
-                bool inrun = false;
-                if (jj < n_reads) {
-                    const uint2 r = *reinterpret_cast<const uint2*>(&reads[jj]);
-                    inrun = (int)r.x == p0;
-                    if (inrun && (int)((r.y >> 16) & 0xffu) > mq_threshold) c++;
-                }
-                if (!__all_sync(FULL, inrun)) break;
-            }
-            c = __reduce_add_sync(FULL, c);
-            if (lane == 0 && c >= 32768 && p0 >= 0 && p0 < chrom_len)
-                counts_add(k, p0 >> CG_CHUNK_SHIFT, sext16((unsigned)c) - c);
-        }
-    }
-}
-
-cudaError_t cgk_rare_paths(cudaStream_t s, const cg_read* reads, long long n_reads, uint32_t* depth32,
-                           cg_counts k, int n_chunks, int32_t chrom_len, int mq_threshold,
-                           const unsigned int* ctl, int n_sms)
-{
-    k_rare_scatter<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, chrom_len, mq_threshold, ctl);
-    k_rare_totals<<<n_sms * 4, 256, 0, s>>>(reads, n_reads, depth32, k, n_chunks, chrom_len, mq_threshold, ctl);
+    if (!S.depth32) return cudaSuccess;
+    k_rare_scatter<<<n_sms * 4, 256, 0, s>>>(S, J1);
     return cudaGetLastError();
 }
 
 /* ------------------------------------------------------------------------- */
 /* the fused pass                                                            */
-struct __align__(16) pass_smem {
-    uint4 bins4[NWARP][CG_CHUNK / 8];         /* 8 x 4 KB: eight packed u16 counts per vector, one region per warp */
-    int win_end[NWARP][MAXWIN];               /* chunk-local inclusive prefix at each window's last position */
-    /* per-CTA rd_per_gc / window_per_gc.  32-bit is exact here: a CTA's share of the depth sum is
-     * bounded by the record count (< 2^31) and it sweeps < 2^32 positions; native 32-bit shared
-     * atomics instead of the CAS loop a 64-bit shared add compiles to */
-    int gc_rd[CG_GC_BINS];
-    unsigned gc_cnt[CG_GC_BINS];
-    int is_last;
+struct pass_job {                             /* what the pass needs of a job, staged in shared memory */
+    rec_src R;
+    const signed char* gc;
+    int n_reads, chrom_len, mq, chunk0, work0, unsorted;
+    int pad[2];
 };
 
-#define PASS_CTAS_PER_SM 5            /* register/shared-memory budget the kernel is compiled for */
-/* CTAs per SM one launch asks for.  Measured on B200 (C2 chromosomes, pass alone): 1 -> 4.9, 2 -> 6.1,
- * 3 -> 5.6, 4 -> 5.2, 5 -> 5.1 TB/s: more resident warps mean more concurrent write streams and
- * worse HBM efficiency; the rest of the SM stays free for the genotype and preparation kernels. */
+struct __align__(16) pass_smem {
+    uint4 bins4[NWARP][CG_CHUNK / 8];         /* 8 x 4 KB: eight packed u16 counts per vector, one region per warp */
+    int win_end[NWARP][MAXWIN];               /* per GC window of the warp's chunk: records (or, wrapped chunks, depth sum) */
+    pass_job job[CG_JMAX];
+    /* followed by int gcs[n_jobs][CG_PART_WORDS]: per-CTA rd_per_gc / window_per_gc of every job.  32-bit is
+     * exact here: a CTA's share of the depth sum is bounded by the record count (< 2^31) and it sweeps < 2^32
+     * positions; native 32-bit shared atomics instead of the CAS loop a 64-bit shared add compiles to */
+};
+
+#define PASS_MAX_CTAS_PER_SM 3        /* register/shared-memory budget the kernel is compiled for */
+/* CTAs per SM one launch asks for.  Measured on B200 (C2 chromosomes, pass alone, r01h): 1 -> 4.9, 2 -> 6.1,
+ * 3 -> 5.6 TB/s: more resident warps mean more concurrent write streams and worse HBM efficiency; the
+ * rest of the SM stays free for the genotype and preparation kernels. */
 #define PASS_GRID_CTAS_PER_SM 2
 #ifndef PASS_BATCH
 #define PASS_BATCH 4                  /* chunks per visit to the work counter */
 #endif
+#define PASS_PRE 2                    /* 32-record groups of a chunk asked for one chunk ahead */
+static_assert(PASS_BATCH >= 3 && PASS_BATCH <= 32, "the bounds of batch n+1 are asked for at chunk 1 and used after chunk PASS_BATCH-1");
 
 /* expected_read_depth[101], read_distribution.c:75-83:
  *   expected[0] = 0; expected[i] = (float)rd_per_gc[i] / window_per_gc[i]; NaN / Inf -> 0.
@@ -328,223 +295,364 @@ __device__ __forceinline__ float expected_of(long long rd, long long cnt, int i)
 /* sum of the two sign-extended 16-bit halves of w, added to acc (one IDP.2A) */
 __device__ __forceinline__ int add_halves(unsigned w, int acc) { return __dp2a_lo((int)w, 0x0101, acc); }
 
-__global__ void __launch_bounds__(NT, PASS_CTAS_PER_SM)
-k_depth_pass(const cg_pass_args a)
+/* 32 records (one per lane) into the warp's packed bins and window counters.  Warp aggregation: the stream
+ * is sorted, so equal positions sit in adjacent lanes and one lane adds for all of them. */
+__device__ __forceinline__ void bin32(bool in, int pos, int mapq, int base, int w0, int mq, int chrom_len,
+                                      unsigned* bins, int* wend, int lane, bool& big)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    pass_smem& sm = *reinterpret_cast<pass_smem*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint4* my4 = sm.bins4[warp];
-    unsigned* bins = reinterpret_cast<unsigned*>(my4);                 /* word = positions 2k (low), 2k+1 (high) */
-    int* wend = sm.win_end[warp];
-    const bool unsorted = (a.ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED) != 0;
-    const int n_reads = (int)a.n_reads;
-
-    for (int i = lane; i < CG_CHUNK / 8; i += 32) my4[i] = make_uint4(0, 0, 0, 0);
-    if (lane < MAXWIN) wend[lane] = 0;
-    for (int i = tid; i < CG_GC_BINS; i += NT) { sm.gc_rd[i] = 0; sm.gc_cnt[i] = 0u; }
-    __syncthreads();
-
-    /* Chunks are handed out PASS_BATCH at a time from one counter: at 2 B per position the pass needs
-     * 1.5 G chunks/s to saturate HBM, more than one address takes atomics (measured 0.9 G/s, r01g) */
-    unsigned cur = 0u;
-    if (lane == 0) cur = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
-    int c = (int)__shfl_sync(FULL, cur, 0);
-    int left = PASS_BATCH;                            /* chunks of the current batch not yet done, this one included */
-    unsigned nxt = 0u;
-    int blo = 0;
-
-    while (c < a.n_chunks) {
-        /* the batch after this one: asked for at the batch's first chunk, looked at after its last */
-        if (left == PASS_BATCH) {
-            if (lane == 0) nxt = atomicAdd(&a.ctl[CG_W_TILE], (unsigned)PASS_BATCH);
-            /* record bounds of the whole batch in one coalesced load: lane j holds chunk_lo[c + j] */
-            blo = lane <= PASS_BATCH ? min(__ldg(&a.k.chunk_lo[min(c + lane, a.n_chunks)]), n_reads) : 0;
-        }
-        const int base = c << CG_CHUNK_SHIFT;
-        const int w0 = base / 100;                    /* first GC window overlapping the chunk */
-        /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
-         * went negative (32768 or more records on one position): counted while the records are binned.
-         * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
-        bool big = false;
-        /* the GC byte of this lane's window: asked for now, used after the stores */
-        const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
-        const int chunk_end = min(base + CG_CHUNK, a.chrom_len);
-        const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(chunk_end, 100 * (w0 + lane) + 100);
-        int gbin = 0;
-        if (lane < nwin && gw_e > gw_s) gbin = (int)a.gc[w0 + lane];              /* sonic_interval.c:263-272 */
-
-        /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
-        if (!unsorted) {
-            const int lo = __shfl_sync(FULL, blo, PASS_BATCH - left), hi = __shfl_sync(FULL, blo, PASS_BATCH - left + 1);
-            for (int i0 = lo; i0 < hi; i0 += 32) {
-                const int i = i0 + lane;
-                const bool in = i < hi;
-                uint2 r = make_uint2(0u, 0u);
-                if (in) r = __ldg(reinterpret_cast<const uint2*>(a.reads) + i);
-                const int pos = (int)r.x, mapq = (int)((r.y >> 16) & 0xffu);
-                const unsigned off = (unsigned)(pos - base);
-                const bool ok = in && mapq > a.mq_threshold                       /* bam_data.c:205 */
-                                && off < (unsigned)CG_CHUNK && pos < a.chrom_len;
-                /* warp aggregation: the stream is sorted, so equal positions sit in adjacent lanes */
-                int cnt;
-                const bool leader = run_leader(ok ? (int)off : -1 - lane, lane, cnt);
-                if (ok && leader) {
-                    unsigned now;                                                 /* the position's count so far, unwrapped */
-                    if (off & 1u) {
-                        now = (atomicAdd(&bins[off >> 1], (unsigned)cnt << 16) >> 16) + (unsigned)cnt;   /* bam_data.c:213; carry-out = wrap */
-                    } else {
-                        now = (atomicAdd(&bins[off >> 1], (unsigned)cnt) & 0xffffu) + (unsigned)cnt;
-                        /* the low half wrapped into its neighbour's count: take the carry back out */
-                        if (now > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
-                    }
-                    big |= now >= 0x8000u;
-                    atomicAdd(&wend[pos / 100 - w0], cnt);
-                }
-            }
+    const unsigned off = (unsigned)(pos - base);
+    const bool ok = in && mapq > mq                                              /* bam_data.c:205 */
+                    && off < (unsigned)CG_CHUNK && pos < chrom_len;
+    int cnt;
+    const bool leader = run_leader(ok ? (int)off : -1 - lane, lane, cnt);
+    if (ok && leader) {
+        unsigned now;                                                            /* the position's count so far, unwrapped */
+        if (off & 1u) {
+            now = (atomicAdd(&bins[off >> 1], (unsigned)cnt << 16) >> 16) + (unsigned)cnt;   /* bam_data.c:213; carry-out = wrap */
         } else {
-            uint4* src = reinterpret_cast<uint4*>(a.depth32 + (size_t)base);
-            for (int q = lane; q < CG_CHUNK / 8; q += 32) {
-                const uint4 x = src[2 * q], y = src[2 * q + 1];
-                my4[q] = make_uint4((x.x & 0xffffu) | (x.y << 16), (x.z & 0xffffu) | (x.w << 16),
-                                    (y.x & 0xffffu) | (y.y << 16), (y.z & 0xffffu) | (y.w << 16));
-                src[2 * q] = make_uint4(0, 0, 0, 0);                              /* zero at rest */
-                src[2 * q + 1] = make_uint4(0, 0, 0, 0);
-            }
-            big = true;
+            now = (atomicAdd(&bins[off >> 1], (unsigned)cnt) & 0xffffu) + (unsigned)cnt;
+            /* the low half wrapped into its neighbour's count: take the carry back out */
+            if (now > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
         }
-        const bool wrapped = __any_sync(FULL, big);
-        __syncwarp();
-
-        if (!wrapped) {
-            /* ---- rows -> depth stores: the packed bins ARE the int16 output vectors ---- */
-            char* dp = reinterpret_cast<char*>(a.depth) + ((size_t)base + lane * 8) * 2;
-#pragma unroll
-            for (int r = 0; r < ROWS; r++) {
-                const uint4 v = my4[r * 32 + lane];
-                my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
-                st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
-            }
-        } else {
-            if (lane < MAXWIN) wend[lane] = 0;                        /* the scan below writes window-END sums */
-            __syncwarp();
-            /* ---- eight row scans at once: lane sums, then eight independent shuffle chains ---- */
-            int ex[ROWS];                                 /* -> prefix in front of this lane's 8 positions, per row */
-            {
-                int tot[ROWS];
-    #pragma unroll
-                for (int r = 0; r < ROWS; r++) {
-                    const uint4 v = my4[r * 32 + lane];
-                    tot[r] = add_halves(v.w, add_halves(v.z, add_halves(v.y, add_halves(v.x, 0))));
-                    ex[r] = tot[r];
-                }
-    #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-    #pragma unroll
-                    for (int r = 0; r < ROWS; r++) {
-                        const int o = __shfl_up_sync(FULL, ex[r], d);
-                        if (lane >= d) ex[r] += o;
-                    }
-                }
-                int run = 0;                                /* sums are relative to the chunk's first position */
-    #pragma unroll
-                for (int r = 0; r < ROWS; r++) {
-                    const int row_total = __shfl_sync(FULL, ex[r], 31);
-                    ex[r] = run + ex[r] - tot[r];
-                    run += row_total;
-                }
-            }
-
-            /* ---- rows -> depth stores, window-end sums ---- */
-            {
-                const int cpos = base + lane * 8;         /* this lane's first position in row 0 */
-                int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
-                char* dp = reinterpret_cast<char*>(a.depth) + (size_t)cpos * 2;
-    #pragma unroll
-                for (int r = 0; r < ROWS; r++) {
-                    const uint4 v = my4[r * 32 + lane];
-                    my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
-                    const int b = ex[r];
-                    const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
-                    const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
-                    const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
-                    const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
-                    st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
-                    /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
-                    if (wm >= 92) {
-                        const int k = 99 - wm;
-                        const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
-                                     : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
-                        wend[wq - w0] = b + sk;
-                    }
-                    if (r == ROWS - 1 && lane == 31)                      /* the chunk's last position closes a partial window */
-                        wend[(base + CG_CHUNK - 1) / 100 - w0] = b + s7;
-                    wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
-                    if (wm >= 100) { wm -= 100; wq++; }
-                }
-            }
-            __syncwarp();
-
-            /* window-end sums -> per-window sums */
-            const int nw = (base + CG_CHUNK - 1) / 100 - w0 + 1;
-            const int d = lane < nw ? wend[lane] - (lane ? wend[lane - 1] : 0) : 0;
-            __syncwarp();
-            if (lane < nw) wend[lane] = d;
-        }
-        __syncwarp();
-
-        /* ---- GC-bin sums from the per-window depth sums (read_distribution.c:63-73) ---- */
-        if (lane < nwin && gw_e > gw_s) {
-            const int bin = (unsigned)gbin > 100u ? 0 : gbin;
-            const int sum = wend[lane];
-            if (sum) atomicAdd(&sm.gc_rd[bin], sum);
-            atomicAdd(&sm.gc_cnt[bin], (unsigned)(gw_e - gw_s));
-        }
-        if (lane < MAXWIN) wend[lane] = 0;                            /* clean for the next chunk */
-        __syncwarp();
-        if (--left) c++;
-        else { c = (int)__shfl_sync(FULL, nxt, 0); left = PASS_BATCH; }
-    }
-
-    /* ---- CTA epilogue: flush the per-CTA statistics; the last CTA derives the table ---- */
-    __syncthreads();
-    for (int b = tid; b < CG_GC_BINS; b += NT) {
-        if (sm.gc_rd[b])  atomicAdd((unsigned long long*)&a.stats[b], (unsigned long long)(long long)sm.gc_rd[b]);
-        if (sm.gc_cnt[b]) atomicAdd((unsigned long long*)&a.stats[CG_GC_BINS + b], (unsigned long long)sm.gc_cnt[b]);
-    }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) sm.is_last = atomicAdd(&a.ctl[CG_W_DONE], 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (sm.is_last) {
-        __threadfence();
-        if (tid < CG_GC_BINS) {
-            const long long rd = __ldcg(&a.stats[tid]), cnt = __ldcg(&a.stats[CG_GC_BINS + tid]);
-            a.expected[tid] = expected_of(rd, cnt, tid);
-        }
-        if (warp == NWARP - 1) {
-            /* calc_mu_per_chr, read_distribution.c:35: |sum| <= number of records < 2^31 */
-            int tot = 0;
-            const int n_supers = (a.n_chunks + 1023) >> (2 * LVL);
-            for (int j = lane; j < n_supers; j += 32) tot += a.k.cnt3[j];
-            tot = __reduce_add_sync(FULL, tot);
-            if (lane == 0) {
-                a.stats[2 * CG_GC_BINS] = (long long)tot;
-                if (a.ctl[CG_W_FLAGS] & CG_FLAG_RANGE) atomicOr(a.sticky, CG_FLAG_RANGE);
-            }
-        }
-        if (a.host_row) {                     /* asynchronous HOST mode: the row goes straight to page-locked host memory */
-            __syncthreads();
-            if (tid < CG_STATS_WORDS) a.host_row[tid] = __ldcg(&a.stats[tid]);
-        }
+        big |= now >= 0x8000u;
+        atomicAdd(&wend[pos / 100 - w0], cnt);
     }
 }
 
-int cgk_depth_pass_ctas_per_sm(void) { return PASS_CTAS_PER_SM; }
+__global__ void __launch_bounds__(NT, PASS_MAX_CTAS_PER_SM)
+k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    pass_smem& sm = *reinterpret_cast<pass_smem*>(smem_raw);
+    int* gcs = reinterpret_cast<int*>(smem_raw + sizeof(pass_smem));
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_jobs = S.n_jobs;
+    uint4* my4 = sm.bins4[warp];
+    unsigned* bins = reinterpret_cast<unsigned*>(my4);                 /* word = positions 2k (low), 2k+1 (high) */
+    int* wend = sm.win_end[warp];
+
+    if (tid < n_jobs) {
+        const cg_dev_job& J = jobs[tid];
+        pass_job& P = sm.job[tid];
+        P.R.aos = reinterpret_cast<const uint2*>(J.reads); P.R.pos = J.rec_pos; P.R.mapq = J.rec_mapq;
+        P.gc = reinterpret_cast<const signed char*>(J.gc);
+        P.n_reads = (int)J.n_reads; P.chrom_len = J.chrom_len; P.mq = J.mq_threshold; P.chunk0 = J.chunk0; P.work0 = J.work0;
+        P.unsorted = (S.depth32 != nullptr && (J.ctl[CG_W_FLAGS] & CG_FLAG_UNSORTED)) ? 1 : 0;
+    }
+    for (int i = lane; i < CG_CHUNK / 8; i += 32) my4[i] = make_uint4(0, 0, 0, 0);
+    if (lane < MAXWIN) wend[lane] = 0;
+    for (int i = tid; i < n_jobs * CG_PART_WORDS; i += NT) gcs[i] = 0;
+    __syncthreads();
+
+    const unsigned n_work = (unsigned)S.n_work;
+
+    /* lanes 0..PASS_BATCH-1: job, chunk within the job and record bounds of the chunks of one batch */
+    auto load_batch = [&](unsigned wfirst, int jhint, int& job, int& lc, int& lo, int& hi) {
+        job = -1; lc = 0; lo = 0; hi = 0;
+        const unsigned wq = wfirst + (unsigned)lane;
+        if (lane < PASS_BATCH && wq < n_work) {
+            int j = jhint;
+            while (j + 1 < n_jobs && wq >= (unsigned)sm.job[j + 1].work0) j++;
+            job = j; lc = (int)(wq - (unsigned)sm.job[j].work0);
+            const int g = sm.job[j].chunk0 + lc, nr = sm.job[j].n_reads;
+            lo = min(__ldg(&S.k.chunk_lo[g]), nr);
+            hi = min(__ldg(&S.k.chunk_lo[g + 1]), nr);
+        }
+    };
+    /* what a chunk needs from HBM, asked for one chunk ahead of use: its first 32*PASS_PRE records
+     * and the GC byte of this lane's window */
+    auto prefetch = [&](int job, int lc, int lo, int hi, int (&pos)[PASS_PRE], int (&mq)[PASS_PRE], int& gcb) {
+#pragma unroll
+        for (int u = 0; u < PASS_PRE; u++) { pos[u] = 0; mq[u] = 0; }
+        gcb = 0;
+        if (job < 0) return;
+        const pass_job& P = sm.job[job];
+        if (!P.unsorted) {
+            const rec_src R = P.R;
+#pragma unroll
+            for (int u = 0; u < PASS_PRE; u++) {
+                const int i = lo + 32 * u + lane;
+                if (i < hi) load_rec(R, i, pos[u], mq[u]);
+            }
+        }
+        const int base = lc << CG_CHUNK_SHIFT, w0 = base / 100;
+        const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
+        const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(min(base + CG_CHUNK, P.chrom_len), 100 * (w0 + lane) + 100);
+        if (lane < nwin && gw_e > gw_s) gcb = (int)P.gc[w0 + lane];               /* sonic_interval.c:263-272 */
+    };
+
+    /* Chunks are handed out PASS_BATCH at a time from one counter: at 2 B per position the pass needs
+     * 1.5 G chunks/s to saturate HBM, more than one address takes atomics (measured 0.9 G/s, r01g).
+     * Every global load of the loop is issued at least one chunk ahead of its use: the counter value of
+     * batch n+1 at chunk 0 of batch n, its chunk bounds at chunk 1, the records and GC bytes of a chunk
+     * while the chunk before it is binned and stored. */
+    unsigned wcur = 0u, wnext = 0u;
+    if (lane == 0) wcur = atomicAdd(&S.sctl[CG_SW_TILE], (unsigned)PASS_BATCH);
+    wcur = __shfl_sync(FULL, wcur, 0);
+    int b_job, b_lc, b_lo, b_hi;
+    load_batch(wcur, 0, b_job, b_lc, b_lo, b_hi);
+    int n_job = -1, n_lc = 0, n_lo = 0, n_hi = 0;
+    int p_pos[PASS_PRE], p_mq[PASS_PRE], p_gc;
+    prefetch(__shfl_sync(FULL, b_job, 0), __shfl_sync(FULL, b_lc, 0), __shfl_sync(FULL, b_lo, 0), __shfl_sync(FULL, b_hi, 0), p_pos, p_mq, p_gc);
+    int q = 0;
+
+    while (wcur < n_work) {
+        if (q == 0 && lane == 0) wnext = atomicAdd(&S.sctl[CG_SW_TILE], (unsigned)PASS_BATCH);
+        if (q == 1) {
+            wnext = __shfl_sync(FULL, wnext, 0);
+            load_batch(wnext, max(0, __shfl_sync(FULL, b_job, 0)), n_job, n_lc, n_lo, n_hi);
+        }
+        const int cjob = __shfl_sync(FULL, b_job, q), clc = __shfl_sync(FULL, b_lc, q);
+        const int lo = __shfl_sync(FULL, b_lo, q), hi = __shfl_sync(FULL, b_hi, q);
+        /* the chunk after this one: the next of the batch, or the first of the next batch */
+        const bool last = q == PASS_BATCH - 1;
+        const int xs = last ? 0 : q + 1;
+        const int xjob = __shfl_sync(FULL, last ? n_job : b_job, xs), xlc = __shfl_sync(FULL, last ? n_lc : b_lc, xs);
+        const int xlo = __shfl_sync(FULL, last ? n_lo : b_lo, xs), xhi = __shfl_sync(FULL, last ? n_hi : b_hi, xs);
+        int x_pos[PASS_PRE], x_mq[PASS_PRE], x_gc;
+        prefetch(xjob, xlc, xlo, xhi, x_pos, x_mq, x_gc);
+
+        if (cjob >= 0) {
+            const pass_job& P = sm.job[cjob];
+            const int chrom_len = P.chrom_len, mq = P.mq;
+            const int base = clc << CG_CHUNK_SHIFT;
+            const int w0 = base / 100;                    /* first GC window overlapping the chunk */
+            const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
+            const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(min(base + CG_CHUNK, chrom_len), 100 * (w0 + lane) + 100);
+            const size_t gpos = (size_t)(P.chunk0 + clc) << CG_CHUNK_SHIFT;          /* the chunk in the slot's depth array */
+            /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
+             * went negative (32768 or more records on one position): counted while the records are binned.
+             * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
+            bool big = false;
+
+            /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
+            if (!P.unsorted) {
+                const rec_src R = P.R;
+                int c_pos[PASS_PRE], c_mq[PASS_PRE];
+#pragma unroll
+                for (int u = 0; u < PASS_PRE; u++) { c_pos[u] = p_pos[u]; c_mq[u] = p_mq[u]; }
+                for (int i0 = lo; i0 < hi; i0 += 32 * PASS_PRE) {
+                    int f_pos[PASS_PRE], f_mq[PASS_PRE];          /* the group after this one */
+#pragma unroll
+                    for (int u = 0; u < PASS_PRE; u++) {
+                        f_pos[u] = 0; f_mq[u] = 0;
+                        const int i = i0 + 32 * (PASS_PRE + u) + lane;
+                        if (i < hi) load_rec(R, i, f_pos[u], f_mq[u]);
+                    }
+#pragma unroll
+                    for (int u = 0; u < PASS_PRE; u++)
+                        if (i0 + 32 * u < hi)
+                            bin32(i0 + 32 * u + lane < hi, c_pos[u], c_mq[u], base, w0, mq, chrom_len, bins, wend, lane, big);
+#pragma unroll
+                    for (int u = 0; u < PASS_PRE; u++) { c_pos[u] = f_pos[u]; c_mq[u] = f_mq[u]; }
+                }
+            } else {
+                uint4* src = reinterpret_cast<uint4*>(S.depth32 + gpos);
+                for (int v = lane; v < CG_CHUNK / 8; v += 32) {
+                    const uint4 x = src[2 * v], y = src[2 * v + 1];
+                    my4[v] = make_uint4((x.x & 0xffffu) | (x.y << 16), (x.z & 0xffffu) | (x.w << 16),
+                                        (y.x & 0xffffu) | (y.y << 16), (y.z & 0xffffu) | (y.w << 16));
+                    src[2 * v] = make_uint4(0, 0, 0, 0);                              /* zero at rest */
+                    src[2 * v + 1] = make_uint4(0, 0, 0, 0);
+                }
+                big = true;
+            }
+            const bool wrapped = __any_sync(FULL, big);
+            __syncwarp();
+
+            if (!wrapped) {
+                /* ---- rows -> depth stores: the packed bins ARE the int16 output vectors ---- */
+                char* dp = reinterpret_cast<char*>(S.depth) + (gpos + (size_t)lane * 8) * 2;
+#pragma unroll
+                for (int r = 0; r < ROWS; r++) {
+                    const uint4 v = my4[r * 32 + lane];
+                    my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
+                    st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
+                }
+            } else {
+                if (lane < MAXWIN) wend[lane] = 0;                        /* the scan below writes window-END sums */
+                __syncwarp();
+                /* ---- eight row scans at once: lane sums, then eight independent shuffle chains ---- */
+                int ex[ROWS];                                 /* -> prefix in front of this lane's 8 positions, per row */
+                int chunk_total = 0;
+                {
+                    int tot[ROWS];
+#pragma unroll
+                    for (int r = 0; r < ROWS; r++) {
+                        const uint4 v = my4[r * 32 + lane];
+                        tot[r] = add_halves(v.w, add_halves(v.z, add_halves(v.y, add_halves(v.x, 0))));
+                        ex[r] = tot[r];
+                    }
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+                        for (int r = 0; r < ROWS; r++) {
+                            const int o = __shfl_up_sync(FULL, ex[r], d);
+                            if (lane >= d) ex[r] += o;
+                        }
+                    }
+                    int run = 0;                                /* sums are relative to the chunk's first position */
+#pragma unroll
+                    for (int r = 0; r < ROWS; r++) {
+                        const int row_total = __shfl_sync(FULL, ex[r], 31);
+                        ex[r] = run + ex[r] - tot[r];
+                        run += row_total;
+                    }
+                    chunk_total = run;
+                }
+                /* the count levels hold the number of records; a wrapped int16 changes the chunk's depth sum */
+                if (lane == 0) {
+                    const int g = P.chunk0 + clc;
+                    const int old = S.k.cnt1[g];
+                    if (old != chunk_total) {
+                        S.k.cnt1[g] = chunk_total;
+                        atomicAdd(&S.k.cnt2[g >> LVL], chunk_total - old);
+                        atomicAdd(&S.k.cnt3[g >> (2 * LVL)], chunk_total - old);
+                    }
+                }
+
+                /* ---- rows -> depth stores, window-end sums ---- */
+                {
+                    const int cpos = base + lane * 8;         /* this lane's first position in row 0 */
+                    int wq = cpos / 100, wm = cpos - wq * 100;                /* its GC window and offset within it */
+                    char* dp = reinterpret_cast<char*>(S.depth) + (gpos + (size_t)lane * 8) * 2;
+#pragma unroll
+                    for (int r = 0; r < ROWS; r++) {
+                        const uint4 v = my4[r * 32 + lane];
+                        my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
+                        const int b = ex[r];
+                        const int s0 = sext16(v.x), s1 = add_halves(v.x, 0);
+                        const int s2 = s1 + sext16(v.y), s3 = add_halves(v.y, s1);
+                        const int s4 = s3 + sext16(v.z), s5 = add_halves(v.z, s3);
+                        const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
+                        st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
+                        /* the lane whose 8 positions contain a window's last position (== 99 mod 100) */
+                        if (wm >= 92) {
+                            const int k = 99 - wm;
+                            const int sk = k == 0 ? s0 : k == 1 ? s1 : k == 2 ? s2 : k == 3 ? s3
+                                         : k == 4 ? s4 : k == 5 ? s5 : k == 6 ? s6 : s7;
+                            wend[wq - w0] = b + sk;
+                        }
+                        if (r == ROWS - 1 && lane == 31)                      /* the chunk's last position closes a partial window */
+                            wend[(base + CG_CHUNK - 1) / 100 - w0] = b + s7;
+                        wm += 56; wq += 2;                                    /* 256 = 2*100 + 56 */
+                        if (wm >= 100) { wm -= 100; wq++; }
+                    }
+                }
+                __syncwarp();
+
+                /* window-end sums -> per-window sums */
+                const int d = lane < nwin ? wend[lane] - (lane ? wend[lane - 1] : 0) : 0;
+                __syncwarp();
+                if (lane < nwin) wend[lane] = d;
+            }
+            __syncwarp();
+
+            /* ---- GC-bin sums from the per-window depth sums (read_distribution.c:63-73) ---- */
+            if (lane < nwin && gw_e > gw_s) {
+                const int bin = (unsigned)p_gc > 100u ? 0 : p_gc;
+                int* acc = gcs + cjob * CG_PART_WORDS;
+                const int sum = wend[lane];
+                if (sum) atomicAdd(&acc[bin], sum);
+                atomicAdd(reinterpret_cast<unsigned*>(&acc[CG_GC_BINS + bin]), (unsigned)(gw_e - gw_s));
+            }
+            if (lane < MAXWIN) wend[lane] = 0;                            /* clean for the next chunk */
+            __syncwarp();
+        }
+
+#pragma unroll
+        for (int u = 0; u < PASS_PRE; u++) { p_pos[u] = x_pos[u]; p_mq[u] = x_mq[u]; }
+        p_gc = x_gc;
+        if (++q == PASS_BATCH) {
+            q = 0;
+            wcur = wnext;
+            b_job = n_job; b_lc = n_lc; b_lo = n_lo; b_hi = n_hi;
+        }
+    }
+
+    /* ---- CTA epilogue: what this CTA saw of every job's GC bins, plain coalesced stores ---- */
+    __syncthreads();
+    int* out = S.partial + (size_t)blockIdx.x * n_jobs * CG_PART_WORDS;
+    for (int i = tid; i < n_jobs * CG_PART_WORDS; i += NT) out[i] = gcs[i];
+}
+
+static int pass_ctas_per_sm(void)
+{
+    static int ctas_per_sm = 0;               /* CG_PASS_CTAS: CTAs per SM one launch asks for (tuning) */
+    if (!ctas_per_sm) {
+        const char* e = getenv("CG_PASS_CTAS");
+        ctas_per_sm = e ? atoi(e) : PASS_GRID_CTAS_PER_SM;
+        if (ctas_per_sm < 1 || ctas_per_sm > PASS_MAX_CTAS_PER_SM) ctas_per_sm = PASS_MAX_CTAS_PER_SM;
+    }
+    return ctas_per_sm;
+}
+
+int cgk_pass_grid(int n_work, int n_sms)
+{
+    int grid = n_sms * pass_ctas_per_sm();
+    const int want = (n_work + NWARP * PASS_BATCH - 1) / (NWARP * PASS_BATCH);
+    if (grid > want) grid = want;
+    return grid < 1 ? 1 : grid;
+}
+
+static size_t pass_smem_bytes(int n_jobs) { return sizeof(pass_smem) + (size_t)n_jobs * CG_PART_WORDS * sizeof(int); }
+
+cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
+{
+    k_depth_pass<<<S.n_pass_ctas, NT, pass_smem_bytes(S.n_jobs), s>>>(S, J1);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------------------- */
+/* per job: the partial rows of the pass -> the cg_chrom_stats row (read_distribution.c:27-73), the
+ * expected table (:75-83), the chromosome's flags */
+__global__ void __launch_bounds__(256)
+k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
+{
+    const cg_dev_job& J = S.jobs ? S.jobs[blockIdx.x] : J1;
+    __shared__ long long row[CG_STATS_WORDS];
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < CG_PART_WORDS) {
+        const int32_t* p = S.partial + (size_t)blockIdx.x * CG_PART_WORDS + tid;
+        const size_t stride = (size_t)S.n_jobs * CG_PART_WORDS;
+        long long s = 0;
+        if (tid < CG_GC_BINS) { for (int c = 0; c < S.n_pass_ctas; c++) s += (long long)p[c * stride]; }
+        else                  { for (int c = 0; c < S.n_pass_ctas; c++) s += (long long)(unsigned)p[c * stride]; }
+        row[tid] = s;
+    } else if (tid >= 224) {
+        /* calc_mu_per_chr, read_distribution.c:35: |sum| <= number of records < 2^31 */
+        int tot = 0;
+        const int s0 = J.chunk0 >> (2 * LVL), s1 = (J.chunk0 + J.n_chunks + CG_SUPER_CHUNKS - 1) >> (2 * LVL);
+        for (int j = s0 + lane; j < s1; j += 32) tot += S.k.cnt3[j];
+        tot = __reduce_add_sync(FULL, tot);
+        if (lane == 0) {
+            row[2 * CG_GC_BINS] = (long long)tot;
+            row[2 * CG_GC_BINS + 1] = (long long)*reinterpret_cast<const unsigned long long*>(J.ctl + CG_W_PASSED);
+        }
+    }
+    __syncthreads();
+    if (tid < CG_STATS_WORDS) {
+        J.stats_row[tid] = row[tid];
+        if (J.row_out) J.row_out[tid] = row[tid];
+    }
+    if (tid < CG_GC_BINS) J.expected[tid] = expected_of(row[tid], row[CG_GC_BINS + tid], tid);
+    if (tid == 0) {
+        const unsigned fl = J.ctl[CG_W_FLAGS];
+        if (fl & CG_FLAG_RANGE) atomicOr(S.sticky, CG_FLAG_RANGE);
+        if (S.h_flags) S.h_flags[blockIdx.x] = fl;
+    }
+}
+
+cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
+{
+    k_finalize<<<S.n_jobs, 256, 0, s>>>(S, J1);
+    return cudaGetLastError();
+}
 
 /* Two kernels share an SM only if they ask for the same L1/shared-memory split; otherwise the
  * CTAs of the second wait until the SM has drained.  Every kernel of the library therefore
- * states the same carve-out, so that the preparation and genotype kernels of one chromosome
+ * states the same carve-out, so that the preparation and genotype kernels of one submission
  * really run on the SMs a neighbour's depth pass occupies. */
 int cgk_carveout(void)
 {
@@ -561,31 +669,32 @@ cudaError_t cgk_configure_depth(void)
 {
     const int pct = cgk_carveout();
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pass_smem))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem_bytes(CG_JMAX))) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_chrom_init, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_mark_batch, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_job_init, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_mark, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_rare_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_rare_totals, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_finalize, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
-/* Diagnostic (cg_download_prefix): the int32 inclusive prefix of the depth array, P[i] = sum of depth[0..i]
+/* Diagnostic (cg_download_prefix): the int32 inclusive prefix of a job's depth array, P[i] = sum of depth[0..i]
  * mod 2^32, rebuilt from the depth array and the chunk / group / super sums.  One warp per chunk. */
 __global__ void __launch_bounds__(256)
-k_prefix_from_depth(const int16_t* __restrict__ depth, cg_counts k, int n_chunks, int32_t* __restrict__ prefix)
+k_prefix_from_depth(const int16_t* __restrict__ depth, cg_counts k, int chunk0, int n_chunks, int32_t* __restrict__ prefix)
 {
     const int lane = threadIdx.x & 31;
     const int n_warps = gridDim.x * (blockDim.x >> 5);
-    for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < n_chunks; c += n_warps) {
+    for (int lc = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); lc < n_chunks; lc += n_warps) {
+        const int c = chunk0 + lc;
         int part = 0;
         const int g = c >> LVL, sp = c >> (2 * LVL);
         const int i1 = (g << LVL) + lane, i2 = (sp << LVL) + lane;
         if (i1 < c) part += k.cnt1[i1];
         if (i2 < g) part += k.cnt2[i2];
-        for (int j = lane; j < sp; j += 32) part += k.cnt3[j];
+        for (int j = (chunk0 >> (2 * LVL)) + lane; j < sp; j += 32) part += k.cnt3[j];
         int run = __reduce_add_sync(FULL, part);
-        const size_t base = (size_t)c << CG_CHUNK_SHIFT;
+        const size_t base = (size_t)c << CG_CHUNK_SHIFT, obase = (size_t)lc << CG_CHUNK_SHIFT;
         const uint4* src = reinterpret_cast<const uint4*>(depth + base);
         for (int r = 0; r < ROWS; r++) {
             const uint4 v = src[r * 32 + lane];
@@ -595,7 +704,7 @@ k_prefix_from_depth(const int16_t* __restrict__ depth, cg_counts k, int n_chunks
             const int s6 = s5 + sext16(v.w), s7 = add_halves(v.w, s5);
             const int incl = warp_incl_scan(s7, lane);
             const int b = run + incl - s7;
-            int4* dst = reinterpret_cast<int4*>(prefix + base + (size_t)(r * 32 + lane) * 8);
+            int4* dst = reinterpret_cast<int4*>(prefix + obase + (size_t)(r * 32 + lane) * 8);
             dst[0] = make_int4(b + s0, b + s1, b + s2, b + s3);
             dst[1] = make_int4(b + s4, b + s5, b + s6, b + s7);
             run += __shfl_sync(FULL, incl, 31);
@@ -603,29 +712,12 @@ k_prefix_from_depth(const int16_t* __restrict__ depth, cg_counts k, int n_chunks
     }
 }
 
-cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int n_chunks, int32_t* prefix)
+cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int chunk0, int n_chunks, int32_t* prefix)
 {
     if (n_chunks <= 0) return cudaSuccess;
     int blocks = (n_chunks + 7) / 8;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_prefix_from_depth<<<blocks, 256, 0, s>>>(depth, k, n_chunks, prefix);
-    return cudaGetLastError();
-}
-
-cudaError_t cgk_depth_pass(cudaStream_t s, const cg_pass_args& a, int n_sms)
-{
-    const int smem = (int)sizeof(pass_smem);           /* opted in by cgk_configure_depth */
-    static int ctas_per_sm = 0;               /* CG_PASS_CTAS: CTAs per SM one launch asks for (tuning) */
-    if (!ctas_per_sm) {
-        const char* e = getenv("CG_PASS_CTAS");
-        ctas_per_sm = e ? atoi(e) : PASS_GRID_CTAS_PER_SM;
-        if (ctas_per_sm < 1 || ctas_per_sm > PASS_CTAS_PER_SM) ctas_per_sm = PASS_CTAS_PER_SM;
-    }
-    int grid = n_sms * ctas_per_sm;
-    const int want = (a.n_chunks + NWARP - 1) / NWARP;
-    if (grid > want) grid = want;
-    if (grid < 1) grid = 1;
-    k_depth_pass<<<grid, NT, smem, s>>>(a);
+    k_prefix_from_depth<<<blocks, 256, 0, s>>>(depth, k, chunk0, n_chunks, prefix);
     return cudaGetLastError();
 }
 

@@ -302,46 +302,59 @@ __device__ __forceinline__ cg_cnv make_cnv(int a, int b) { cg_cnv v; v.start = a
 #define GENO_WARPS 4                        /* warps per CTA */
 #define GENO_RAMP 32                        /* windows of the expected chain walked lane-serially */
 #define RUN_BUCKET_SHIFT 14                 /* run_idx[b] = first run whose end lies beyond position b << 14 */
+__device__ __forceinline__ int cgk_run_index_words_dev(int32_t chrom_len) { return ((chrom_len + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT) + 2; }
 
-/* index of the flattened mappability track: one entry per 16384 positions */
-__global__ void k_run_index(const cg_maprun* __restrict__ runs, int n_runs, int32_t* run_idx, int n_buckets)
+/* index of the flattened mappability tracks of a submission: per job one entry per 16384 positions */
+__global__ void __launch_bounds__(256)
+k_run_index(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
-    const int stride = gridDim.x * blockDim.x;
-    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r <= n_runs; r += stride) {
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
+    __shared__ int s_blk0[CG_JMAX + 1];
+    if (threadIdx.x <= S.n_jobs) s_blk0[threadIdx.x] = threadIdx.x < S.n_jobs ? jobs[threadIdx.x].run_blk0 : S.n_run_blocks;
+    __syncthreads();
+    int j = 0;
+    for (int b = blockIdx.x; b < S.n_run_blocks; b += gridDim.x) {
+        while (b >= s_blk0[j + 1]) j++;
+        const cg_dev_job& J = jobs[j];
+        const cg_maprun* __restrict__ runs = J.runs;
+        const int n_runs = J.n_runs, n_buckets = cgk_run_index_words_dev(J.chrom_len) - 1;
+        const int r = (b - s_blk0[j]) * 256 + threadIdx.x;
+        if (r > n_runs) continue;
         const long long prev_end = r ? runs[r - 1].end : 0;
         const long long end = r < n_runs ? runs[r].end : ((long long)n_buckets << RUN_BUCKET_SHIFT) + 1;
         /* buckets whose first position p satisfies prev_end <= p < end: run r is the first one ending beyond p */
-        for (long long b = (prev_end + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT; b <= n_buckets && (b << RUN_BUCKET_SHIFT) < end; b++)
-            run_idx[b] = r;
+        for (long long q = (prev_end + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT; q <= n_buckets && (q << RUN_BUCKET_SHIFT) < end; q++)
+            J.run_idx[q] = r;
     }
 }
 
 int cgk_run_index_words(int32_t chrom_len) { return ((chrom_len + (1 << RUN_BUCKET_SHIFT) - 1) >> RUN_BUCKET_SHIFT) + 2; }
 
-cudaError_t cgk_run_index(cudaStream_t s, const cg_maprun* runs, int n_runs, int32_t* run_idx, int32_t chrom_len)
+cudaError_t cgk_run_index(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 {
-    const int n_buckets = cgk_run_index_words(chrom_len) - 1;
-    int blocks = (n_runs + 256) / 256;
-    if (blocks > 148 * 4) blocks = 148 * 4;
-    k_run_index<<<blocks, 256, 0, s>>>(runs, n_runs, run_idx, n_buckets);
+    if (S.n_run_blocks <= 0) return cudaSuccess;
+    int blocks = S.n_run_blocks;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_run_index<<<blocks, 256, 0, s>>>(S, J1);
     return cudaGetLastError();
 }
 
 /* D(p) = sum of depth[0, p) mod 2^32, by one warp (every lane gets the result).  Chunk boundary: the supers
  * in front of p's super, the groups in front of its group, the chunks in front of its chunk (one lane each,
  * the carry of the depth pass's first version).  Inside the chunk: 16-byte loads of eight int16 depths. */
-__device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ depth, const cg_counts& k, int p, int lane)
+__device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ depth, const cg_counts& k, int chunk0, int p, int lane)
 {
-    const int c = p >> CG_CHUNK_SHIFT;
+    /* depth points at the job's first position; the count arrays are indexed by chunk of the slot's chunk space */
+    const int c = chunk0 + (p >> CG_CHUNK_SHIFT);
     const int g = c >> 5, sp = c >> 10;
     int part = 0;
     {
         const int i1 = (g << 5) + lane, i2 = (sp << 5) + lane;
         if (i1 < c) part += __ldg(&k.cnt1[i1]);
         if (i2 < g) part += __ldg(&k.cnt2[i2]);
-        for (int j = lane; j < sp; j += 32) part += __ldg(&k.cnt3[j]);
+        for (int j = (chunk0 >> 10) + lane; j < sp; j += 32) part += __ldg(&k.cnt3[j]);
     }
-    const int base = c << CG_CHUNK_SHIFT;
+    const int base = (p >> CG_CHUNK_SHIFT) << CG_CHUNK_SHIFT;
     const uint4* row = reinterpret_cast<const uint4*>(depth + base);
     for (int q0 = 0; base + q0 * 8 < p; q0 += 32) {
         const int q = q0 + lane, first = base + q * 8;                 /* this lane's eight positions */
@@ -363,36 +376,63 @@ __device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ dept
     return __reduce_add_sync(FULL, part);
 }
 
-template <int G>
+/* One CNV per warp (measured on B200, C2, every kernel on one shared-memory carve-out so that they really
+ * share SMs with the depth pass: 8 CNVs per warp 7.7 ms of genotype kernels per sample, 4 -> 5.4, 2 -> 4.1,
+ * 1 -> 2.9: the GPU is otherwise idle under the bandwidth-bound pass, so latency wins over lane efficiency).
+ * The launch covers every CNV of the submission: global index -> (job, kind) through the cnv0 prefix. */
 __global__ void __launch_bounds__(GENO_WARPS * 32)
-k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int16_t* __restrict__ depth, const cg_counts counts,
-           const int8_t* __restrict__ gc, const float* __restrict__ expected,
-           const cg_maprun* __restrict__ runs, const int32_t* __restrict__ run_idx, int n_runs, int has_map,
-           int32_t chrom_len, unsigned int* flags, cg_call* out)
+k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
-    __shared__ unsigned s_expb[CG_GC_BINS];             /* bit patterns of expected_read_depth[] */
-    for (int i = threadIdx.x; i < CG_GC_BINS; i += blockDim.x) s_expb[i] = __float_as_uint(expected[i]);
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
+    __shared__ unsigned s_expb_all[GENO_WARPS][CG_GC_BINS + 3];   /* bit patterns of the warp's job's expected_read_depth[] */
+    __shared__ int s_seg0[2 * CG_JMAX + 1];                       /* first global CNV index of (job, kind) = segment 2*job + kind */
+    for (int i = threadIdx.x; i <= 2 * S.n_jobs; i += blockDim.x)
+        s_seg0[i] = i < 2 * S.n_jobs ? jobs[i >> 1].cnv0[i & 1] : S.n_cnv;
     __syncthreads();
     const int lane = threadIdx.x & 31;
+    unsigned* s_expb = s_expb_all[threadIdx.x >> 5];
     const int n_warps = gridDim.x * GENO_WARPS;
-    const int n_windows = (chrom_len + 99) / 100;
-    const bool use_map = has_map && n_runs > 0;
-    const int n_groups = (n + G - 1) / G;
+    int seg = 0, cur_job = -1, cur_seg = -1;
+    /* what the current segment says, in registers */
+    const cg_cnv* __restrict__ cnvs = nullptr; cg_call* out = nullptr;
+    const int16_t* __restrict__ depth = nullptr; const int8_t* __restrict__ gc = nullptr;
+    const cg_maprun* __restrict__ runs = nullptr; const int32_t* __restrict__ run_idx = nullptr;
+    int n_runs = 0, has_map = 0, chrom_len = 0, chunk0 = 0, is_dup = 0, n_windows = 0;
+    bool use_map = false;
+    const cg_counts counts = S.k;
 
-    for (int grp = blockIdx.x * GENO_WARPS + (threadIdx.x >> 5); grp < n_groups; grp += n_warps) {
-        /* ---- phase 0: lane = CNV ---- */
-        const int c = grp * G + lane;
-        const bool valid = lane < G && c < n;
+    for (int gi = blockIdx.x * GENO_WARPS + (threadIdx.x >> 5); gi < S.n_cnv; gi += n_warps) {
+        while (gi >= s_seg0[seg + 1]) seg++;                     /* a warp's indices ascend */
+        if (seg != cur_seg) {
+            const cg_dev_job& J = jobs[seg >> 1];
+            is_dup = seg & 1;
+            cnvs = J.cnv[is_dup]; out = J.calls[is_dup];
+            if ((seg >> 1) != cur_job) {
+                depth = S.depth + ((size_t)J.chunk0 << CG_CHUNK_SHIFT); gc = J.gc;
+                runs = J.runs; run_idx = J.run_idx; n_runs = J.n_runs; has_map = J.has_map;
+                chrom_len = J.chrom_len; chunk0 = J.chunk0;
+                n_windows = (chrom_len + 99) / 100;
+                use_map = has_map && n_runs > 0;
+                __syncwarp();
+                for (int i = lane; i < CG_GC_BINS; i += 32) s_expb[i] = __float_as_uint(J.expected[i]);
+                __syncwarp();
+                cur_job = seg >> 1;
+            }
+            cur_seg = seg;
+        }
+        /* ---- phase 0: lane 0 = the CNV ---- */
+        const int c = gi - s_seg0[seg];
+        const bool valid = lane == 0;
         cg_cnv v = make_cnv(0, 0);
         if (valid) v = cnvs[c];
         int s = v.start, e = v.end;
-        if (valid && (s < 0 || e > chrom_len)) { atomicOr(flags, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
+        if (valid && (s < 0 || e > chrom_len)) { atomicOr(S.sticky, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
         const bool any = valid && e > s;
         int obs = 0;                                    /* likelihood.c:120, the warp sums for one CNV at a time */
         for (unsigned todo = __ballot_sync(FULL, any); todo; todo &= todo - 1) {
             const int L = __ffs(todo) - 1;
             const int cs = __shfl_sync(FULL, s, L), ce = __shfl_sync(FULL, e, L);
-            const int d = depth_sum_before(depth, counts, ce, lane) - depth_sum_before(depth, counts, cs, lane);
+            const int d = depth_sum_before(depth, counts, chunk0, ce, lane) - depth_sum_before(depth, counts, chunk0, cs, lane);
             if (lane == L) obs = d;
         }
         const int w_last = any ? (e - 1) / 100 : -1;
@@ -581,32 +621,19 @@ k_genotype(const cg_cnv* __restrict__ cnvs, int n, int is_dup, const int16_t* __
     }
 }
 
-#ifndef GENO_G
-/* CNVs per warp.  Measured on B200, C2, all kernels with one shared-memory carve-out (so that they
- * really share SMs with the depth pass): genotype kernels alone 8 -> 7.7, 4 -> 5.4, 2 -> 4.1,
- * 1 -> 2.9 ms per sample; whole step 8 -> 3.14, 4 -> 3.05, 2 -> 3.02, 1 -> 3.01 ms.  The GPU is
- * otherwise idle under the bandwidth-bound pass, so latency wins over lane efficiency. */
-#define GENO_G 1
-#endif
-
 cudaError_t cgk_configure_genotype(void)
 {
     const int pct = cgk_carveout();                       /* see cgk_configure_depth */
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_genotype<GENO_G>, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_genotype, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_run_index, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
 }
 
-cudaError_t cgk_genotype(cudaStream_t s, const cg_cnv* cnvs, int n, int is_dup,
-                         const int16_t* depth, const cg_counts& counts, const int8_t* gc, const float* expected,
-                         const cg_maprun* runs, const int32_t* run_idx, int n_runs, int has_map,
-                         int32_t chrom_len, unsigned int* flags, cg_call* out, int n_sms)
+cudaError_t cgk_genotype(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms)
 {
-    if (n <= 0) return cudaSuccess;
-    const int n_groups = (n + GENO_G - 1) / GENO_G;
-    int blocks = (n_groups + GENO_WARPS - 1) / GENO_WARPS;
-    if (blocks > n_sms * 8) blocks = n_sms * 8;
-    k_genotype<GENO_G><<<blocks, GENO_WARPS * 32, 0, s>>>(cnvs, n, is_dup, depth, counts, gc, expected, runs, run_idx, n_runs,
-                                                          has_map, chrom_len, flags, out);
+    if (S.n_cnv <= 0) return cudaSuccess;
+    int blocks = (S.n_cnv + GENO_WARPS - 1) / GENO_WARPS;
+    if (blocks > n_sms * 12) blocks = n_sms * 12;
+    k_genotype<<<blocks, GENO_WARPS * 32, 0, s>>>(S, J1);
     return cudaGetLastError();
 }

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CG_ABI_VERSION 1
+#define CG_ABI_VERSION 2
 
 enum {
     CG_OK = 0,
@@ -136,6 +136,12 @@ int cg_chrom_begin(cg_ctx* ctx, int chr_index, int32_t chrom_len,
  * and handled by the global-atomic path with identical results. */
 int cg_push_reads(cg_ctx* ctx, const cg_read* reads, size_t n);
 
+/* The same records as two planes — all that bam_data.c:205,213 reads of a record: pos[i] = core.pos and
+ * mapq[i] = core.qual.  5 bytes per record across PCIe instead of 8; mapq may be NULL when the chromosome's
+ * mq_threshold is negative (the default, cmdline.c:188-194: every record passes and the plane would never
+ * decide anything), which makes it 4.  A chromosome is pushed in one format only. */
+int cg_push_reads_compact(cg_ctx* ctx, const int32_t* pos, const uint8_t* mapq, size_t n);
+
 /* Close the chromosome: depth (int16, wraps mod 2^16 like the reference's `short`),
  * chromosome sum and the 101 GC-bin sums/counts, and the
  * expected_read_depth[101] table computed with the reference's exact expression
@@ -212,23 +218,38 @@ int cg_sr_rows(cg_ctx* ctx, cg_splitrow* out, size_t cap, size_t* n_rows, uint64
 int cg_sr_count(cg_ctx* ctx, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
                 const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp);
 
-/* ---- One call for the loop body of read_bam (bam_data.c:304-338) over several chromosomes ----
- * Job k is exactly: cg_chrom_begin(chr_index, chrom_len, gc, n_windows, mq_threshold);
- * cg_push_reads(reads, n_reads) in batches of 2^22 records; cg_chrom_finish(stats);
- * cg_set_mappability_runs(runs, n_runs, 1) when use_mappability != 0; cg_genotype(dels, n_del, 0, del_calls)
- * when n_del > 0; cg_genotype(dups, n_dup, 1, dup_calls) when n_dup > 0 — same pointer mode, same
- * blocking / asynchronous behaviour, same errors (the first failing call's code is returned and the jobs
- * after it are not started).  It exists for callers that drive the library through a foreign-function
- * interface with a per-call cost (ctypes, cgo, JNI): one crossing per sample instead of six per chromosome. */
+/* ---- The loop body of read_bam (bam_data.c:304-338) over several chromosomes as ONE submission ----
+ * Job k means exactly: cg_chrom_begin(chr_index, chrom_len, gc, n_windows, mq_threshold); cg_push_reads(reads,
+ * n_reads) (or cg_push_reads_compact(reads_pos, reads_mapq, n_reads) when reads == NULL); cg_chrom_finish(stats);
+ * cg_set_mappability_runs(runs, n_runs, 1) when use_mappability != 0; cg_genotype(dels, n_del, 0, del_calls);
+ * cg_genotype(dups, n_dup, 1, dup_calls) — same pointer mode, same results.
+ *
+ * In DEVICE pointer mode and in asynchronous HOST mode the jobs are NOT run one after the other: the whole
+ * list (in groups of 32) is handed to the device as one job table and each kernel of the path is launched
+ * once for all chromosomes of the group — one init, one record sweep, one depth pass whose warps pull the
+ * chunks of every chromosome from one counter, one finalize, one mappability index, one genotype launch over
+ * all CNVs.  A sample is six launches instead of eight per chromosome, and the pass has one ramp and one tail
+ * per sample.  Consecutive calls rotate through the context's slots, so sample k+1's uploads and pass overlap
+ * sample k's genotype kernel.  Results are valid after cg_sync() (or after an event recorded on cg_stream
+ * behind cg_join()).  A job whose records turn out not to be coordinate-sorted (the reference requires sorted
+ * input, README.md:93) is detected on the device and re-run through the per-chromosome entry points inside
+ * cg_sync() / when its slot is reused, with identical results; its statistics row is final only then.
+ * In blocking HOST mode the call is the plain loop over the per-chromosome entry points. */
 typedef struct cg_chrom_job {
     int32_t chr_index, chrom_len;
     const int8_t* gc;          int32_t n_windows; int32_t mq_threshold;
-    const cg_read* reads;      uint64_t n_reads;
-    const cg_maprun* runs;     uint64_t n_runs;   int32_t use_mappability; int32_t pad;
+    const cg_read* reads;      uint64_t n_reads;  /* reads == NULL: the compact planes below */
+    const cg_maprun* runs;     uint64_t n_runs;   int32_t use_mappability; int32_t flags;   /* CG_JOB_* */
     const cg_cnv* dels;        uint64_t n_del;    cg_call* del_calls;
     const cg_cnv* dups;        uint64_t n_dup;    cg_call* dup_calls;
     cg_chrom_stats* stats;     /* may be NULL */
+    const int32_t* reads_pos;  const uint8_t* reads_mapq;    /* see cg_push_reads_compact */
 } cg_chrom_job;
+/* flags.  CG_JOB_ANNOTATION_RESIDENT: HOST pointer mode only, submissions only (DEVICE and asynchronous HOST
+ * mode) — gc, runs, dels and dups are DEVICE pointers although the records and the results are host memory:
+ * what a batch driver does with the inputs that are the same for every sample (SONIC's GC bytes, the CNV set,
+ * the flattened mappability track).  Only the records cross PCIe. */
+#define CG_JOB_ANNOTATION_RESIDENT 1
 int cg_run_chromosomes(cg_ctx* ctx, const cg_chrom_job* jobs, size_t n_jobs);
 
 /* ---- SONIC's GC profile from the bases of a chromosome ----
@@ -258,27 +279,45 @@ int cg_download_prefix(cg_ctx* ctx, int32_t* out /* chrom_len */);
  * cg_chrom_begin): int16 depth, float expected[101]. */
 int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const float** expected);
 
-/* Device address of the int64[n_rows][204] statistics table, one row per
- * chr_index seen since cg_stats_reset (layout = cg_chrom_stats).  A multi-GPU
- * driver all-reduces it (NCCL sum) so every rank holds every chromosome's row. */
+/* Device address of the int64[n_rows][204] statistics table of the current bank, one row per
+ * chr_index seen since cg_stats_reset (layout = cg_chrom_stats).  With a communicator (cg_comm_init_*)
+ * this is the table cg_stats_allreduce fills: every rank holds every chromosome's row. */
 int cg_stats_table(cg_ctx* ctx, void** device_ptr, int32_t* n_rows);
 int cg_stats_reset(cg_ctx* ctx);
 /* Two tables ("banks", 0 and 1; 0 at creation).  The chromosomes begun after cg_stats_bank write
- * their rows to `bank`, and cg_stats_table / cg_stats_row refer to it.  A driver that processes
- * sample after sample alternates banks: the collective over sample k's table — queued on cg_stream
- * after cg_join — is then in flight while sample k+1's chromosomes already fill the other bank.
- * A bank that is selected again is cleared first (all rows, so an in-place all-reduce is fine),
- * ordered behind whatever was queued on cg_stream when it was left; nothing waits on the host. */
+ * their rows to `bank`, and cg_stats_table / cg_stats_row / cg_stats_allreduce refer to it.  A driver that
+ * processes sample after sample alternates banks: the collective over sample k's table is then in flight
+ * while sample k+1's chromosomes already fill the other bank.  Selecting a bank clears nothing: a row holds
+ * what the last chromosome with that chr_index left there (cg_stats_reset zeroes the current bank); a
+ * chromosome that writes into a bank a collective is still reading waits for that collective on the device. */
 int cg_stats_bank(cg_ctx* ctx, int bank);
 int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
+
+/* ---- the path's one collective: every rank receives every chromosome's statistics row ----
+ * One context per GPU; the contexts of a job form a communicator (NCCL over NVLink, loaded with dlopen when
+ * the first of these calls is made: a single-GPU user needs no NCCL).  cg_comm_unique_id fills 128 bytes on
+ * one rank, which the caller hands to every rank (any out-of-band channel); cg_comm_init_rank is then called
+ * by all ranks (one process or thread per GPU).  cg_comm_init_all is the single-process form for n contexts
+ * driven by one process.  cg_stats_allreduce orders cg_stream behind everything queued on the context
+ * (cg_join) and queues ONE ncclAllReduce(int64, sum) of rows [0, n_rows) of the current bank on it: out of
+ * place, from the table this context's chromosomes wrote (rows of other ranks' chromosomes stay zero there)
+ * into the table cg_stats_table / cg_stats_row then refer to.  Nothing blocks; every rank must pass the same
+ * n_rows.  The reduced rows are bookkeeping (conga.log, read_distribution.c:41): no genotype of any
+ * chromosome depends on another chromosome's row (read_distribution.c:49-84 rebuilds the table per chromosome). */
+#define CG_COMM_ID_BYTES 128
+int cg_comm_unique_id(void* id /* CG_COMM_ID_BYTES */);
+int cg_comm_init_rank(cg_ctx* ctx, int n_ranks, int rank, const void* id);
+int cg_comm_init_all(cg_ctx** ctxs, int n);
+int cg_comm_destroy(cg_ctx* ctx);
+int cg_stats_allreduce(cg_ctx* ctx, int32_t n_rows);
 
 /* Device time of this context's kernels, from CUDA events recorded on its stream
  * around every launch group while profiling is on.  cg_kernel_times waits for the
  * stream, returns the milliseconds and launch counts accumulated since the last
- * call, and clears them.  Slots: 0 = chromosome init + batch marking + rare paths
- * + tile scan, 1 = the fused depth/GC pass (it also derives the expected table),
- * 2 = CNV sums + likelihoods (runs on the genotype stream, overlapping slot 1 of the next
- * chromosome), 3 = the split-read kernels (k-mer index, re-mapping, overlap counts). */
+ * call, and clears them.  Slots: 0 = submission init + record sweep + out-of-order scatter + finalize,
+ * 1 = the fused depth/GC pass, 2 = mappability index + CNV sums + likelihoods (on the genotype stream,
+ * overlapping slot 1 of the next submission), 3 = the split-read kernels (k-mer index, re-mapping,
+ * overlap counts). */
 #define CG_NSLOTS 4
 int cg_set_profiling(cg_ctx* ctx, int on);
 int cg_kernel_times(cg_ctx* ctx, double ms[CG_NSLOTS], int64_t launches[CG_NSLOTS]);

@@ -27,12 +27,13 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/conga_gpu.h but not exported"
     assert set(names) == set(abi.SYMBOLS), set(names) ^ set(abi.SYMBOLS)
-    assert lib.cg_abi_version() == 1
+    assert lib.cg_abi_version() == 2
 
 
 def test_struct_sizes_match_header():
     assert abi.READ_DT.itemsize == 8 and abi.CNV_DT.itemsize == 8 and abi.MAPIV_DT.itemsize == 16
     assert abi.MAPRUN_DT.itemsize == 16 and abi.CALL_DT.itemsize == 56 and abi.STATS_DT.itemsize == 1632
+    assert abi.CHROM_JOB_DT.itemsize == 136          # cg_chrom_job, ABI 2: + reads_pos, reads_mapq
 
 
 def test_no_cpu_fallback_without_gpu():

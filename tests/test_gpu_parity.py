@@ -385,34 +385,40 @@ def test_async_host_mode_pipelines_chromosomes_without_mixing_them_up(ctx, oracl
 
 
 def test_statistics_banks(ctx, oracle):
-    """cg_stats_bank: rows go to the selected bank; a bank that is selected again starts cleared (all rows,
-    including ones an in-place all-reduce would have filled for other ranks' chromosomes)."""
+    """cg_stats_bank: rows go to the selected bank and stay there (a row holds what the last chromosome with
+    that chr_index left); cg_stats_reset zeroes the current bank."""
     rng = np.random.default_rng(5)
     a = synth._chrom("a", 3, 300_000, rng, 5000, 4, 2, False, cnv_hi=20_000)
     b = synth._chrom("b", 7, 200_000, rng, 3000, 4, 2, False, cnv_hi=20_000)
     st_a = oracle.chromosome(a, -1, False)[1]
     st_b = oracle.chromosome(b, -1, False)[1]
     same = lambda got, want: all(np.array_equal(got[f], want[f]) for f in ("rd_per_gc", "window_per_gc", "rd_cnt", "reads_passed"))
-    ctx.stats_bank(0)
-    ctx.stats_reset()
+    for bank in (0, 1):
+        ctx.stats_bank(bank)
+        ctx.stats_reset()
     try:
+        ctx.stats_bank(0)
         hotpath.run_chromosome(ctx, a)
         assert same(ctx.stats_row(3), st_a)
         ctx.stats_bank(1)
         hotpath.run_chromosome(ctx, b)
         assert same(ctx.stats_row(7), st_b)
         assert int(ctx.stats_row(3)["window_per_gc"].sum()) == 0          # bank 1 never saw chromosome a
-        p0 = ctx.stats_table()[0]
-        ctx.stats_bank(0)                                                  # selected again: cleared
-        assert ctx.stats_table()[0] != p0
-        assert int(ctx.stats_row(3)["window_per_gc"].sum()) == 0
-        hotpath.run_chromosome(ctx, b)
-        assert same(ctx.stats_row(7), st_b)
-        ctx.stats_bank(1)
-        assert int(ctx.stats_row(7)["window_per_gc"].sum()) == 0
-    finally:
+        p1 = ctx.stats_table()[0]
         ctx.stats_bank(0)
+        assert ctx.stats_table()[0] != p1
+        assert same(ctx.stats_row(3), st_a)                                # still there
+        assert int(ctx.stats_row(7)["window_per_gc"].sum()) == 0
+        hotpath.run_chromosome(ctx, b)
+        assert same(ctx.stats_row(7), st_b) and same(ctx.stats_row(3), st_a)
         ctx.stats_reset()
+        assert int(ctx.stats_row(7)["window_per_gc"].sum()) == 0 and int(ctx.stats_row(3)["rd_cnt"]) == 0
+        ctx.stats_bank(1)
+        assert same(ctx.stats_row(7), st_b)                                # the other bank is untouched
+    finally:
+        for bank in (1, 0):
+            ctx.stats_bank(bank)
+            ctx.stats_reset()
 
 
 def test_run_chromosomes_one_call_per_sample(ctx, oracle):
