@@ -55,7 +55,7 @@ struct cg_dev_job {
     const uint8_t*  rec_mapq;         /* may be NULL with rec_pos when mq_threshold < 0: every record passes */
     long long       n_reads;          /* records of the chromosome so far */
     long long       mark_first, mark_n;   /* k_mark: the batch this launch looks at */
-    int32_t         mark_blk0;        /* first 256-record block of this job in the k_mark launch */
+    int32_t         mark_blk0;        /* first block visit of this job in the k_mark launch (cgk_mark_blocks) */
     int32_t         mq_threshold;
     /* geometry */
     int32_t         chrom_len, n_chunks;
@@ -77,7 +77,7 @@ struct cg_dev_job {
     const cg_cnv*   cnv[2];           /* [0] deletions, [1] duplications */
     cg_call*        calls[2];
     int32_t         n_cnv[2];
-    int32_t         cnv0[2];          /* first global CNV index of each kind in the k_genotype launch */
+    int32_t         cnv0[2];          /* first group (cgk_geno_groups) of each kind in the k_genotype launch */
 };
 
 /* What a set of launches works on.  jobs == NULL: a single job travels as the second kernel parameter. */
@@ -86,7 +86,7 @@ struct cg_sub {
     int32_t        n_jobs;
     int32_t        n_work;            /* chunks of all jobs */
     int32_t        n_space;           /* chunks of the slot's chunk space in use (multiple of CG_SUPER_CHUNKS) */
-    int32_t        n_mark_blocks, n_run_blocks, n_cnv;
+    int32_t        n_mark_blocks, n_run_blocks, n_cnv;   /* n_cnv: CNV groups of the launch */
     cg_counts      k;
     int16_t*       depth;             /* [n_space * CG_CHUNK] */
     uint32_t*      depth32;           /* NULL, or the out-of-order path's per-position u32 counts (zero at rest) */
@@ -109,6 +109,7 @@ cg_counts   cgk_counts_layout(int32_t* base, int n_space);
 int         cgk_job_space(int n_chunks);                          /* chunks of chunk space a job of n_chunks occupies */
 int         cgk_pass_grid(int n_work, int n_sms);                 /* CTAs of the pass, = rows of cg_sub::partial */
 cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int32_t* counts_base);
+int         cgk_mark_blocks(unsigned long long n_records);        /* block visits of k_mark for a batch of records */
 cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
@@ -120,6 +121,7 @@ cudaError_t cgk_configure_depth(void);                            /* once per pr
 cudaError_t cgk_configure_genotype(void);
 
 /* genotype.cu */
+int         cgk_geno_groups(unsigned long long n_cnv);            /* warps' worth of work n CNVs of one (job, kind) are */
 cudaError_t cgk_genotype(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
 int         cgk_run_index_words(int32_t chrom_len);
 cudaError_t cgk_run_index(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);

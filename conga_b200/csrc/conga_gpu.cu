@@ -77,6 +77,7 @@ struct cg_slot {
     cudaStream_t s_copy = nullptr, s_work = nullptr, s_geno[2] = {nullptr, nullptr};
     cudaEvent_t ev_copy = nullptr;            /* s_copy: last upload for this slot */
     cudaEvent_t ev_pass = nullptr;            /* s_work: the pass and the finalize of this slot are done */
+    cudaEvent_t ev_passk = nullptr;           /* s_work: the pass kernel alone is done (the next submission's pass is chained on it) */
     cudaEvent_t ev_geno[2] = {nullptr, nullptr};   /* s_geno[t]: last genotype work queued for this slot */
     cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded and indexed */
     bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false;
@@ -327,6 +328,7 @@ cg_ctx* cg_create(int device)
             && cudaEventCreateWithFlags(&s.ev_table, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_copy, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_pass, cudaEventDisableTiming) == cudaSuccess
+            && cudaEventCreateWithFlags(&s.ev_passk, cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_geno[0], cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_geno[1], cudaEventDisableTiming) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_runs, cudaEventDisableTiming) == cudaSuccess;
@@ -357,7 +359,7 @@ void cg_destroy(cg_ctx* c)
         cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32); cudaFree(s.d_in);
         if (s.h_jobs) cudaFreeHost(s.h_jobs);
         if (s.h_flags) cudaFreeHost(s.h_flags);
-        cudaEvent_t evs[] = {s.ev_table, s.ev_copy, s.ev_pass, s.ev_geno[0], s.ev_geno[1], s.ev_runs};
+        cudaEvent_t evs[] = {s.ev_table, s.ev_copy, s.ev_pass, s.ev_passk, s.ev_geno[0], s.ev_geno[1], s.ev_runs};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
         cudaStream_t sts[] = {s.s_copy, s.s_work, s.s_geno[0], s.s_geno[1]};
         for (cudaStream_t st : sts) if (st) cudaStreamDestroy(st);
@@ -560,6 +562,19 @@ static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space)
     S.sticky = c->d_sticky;
 }
 
+/* The pass of a submission starts when the pass of the submission before it has ended (CG_PASS_OVERLAP=1 lets
+ * them overlap).  Two passes at once double the concurrent write streams and cost HBM efficiency, and the
+ * genotype kernel and record sweep of the neighbours already fill the pass's ramp and tail; measured r02b on C3:
+ * the pass alone 1.10 ms per sample, the pipelined step with free overlap 1.63 ms. */
+static int chain_pass(cg_ctx* c, int si)
+{
+    static const bool overlap = getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP")) != 0;
+    cg_slot& s = c->slot[si];
+    cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot];
+    if (!overlap && o.used && &o != &s) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_passk, 0));
+    return CG_OK;
+}
+
 static long long* stats_row_of(cg_ctx* c, int chr_index)
 {
     return c->d_stats + ((size_t)c->bank * CG_MAX_CHROMS + (size_t)chr_index) * CG_STATS_WORDS;
@@ -663,7 +678,7 @@ static int push_records(cg_ctx* c, const cg_read* reads, const int32_t* pos, con
     s.rec_fmt = fmt;
     J.n_reads = (long long)(first + n);
     J.mark_first = (long long)first; J.mark_n = (long long)n; J.mark_blk0 = 0;
-    s.sub.n_mark_blocks = (int)((n + 255) / 256);
+    s.sub.n_mark_blocks = cgk_mark_blocks(n);
     {
         prof_scope ps(c, s.s_work, 0, 1);
         CU(c, cgk_mark(s.s_work, s.sub, J));
@@ -697,17 +712,12 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
         prof_scope ps(c, s.s_work, 0, 1);
         CU(c, cgk_rare_scatter(s.s_work, s.sub, J, c->n_sms));
     }
-    {
-        /* Passes of consecutive chromosomes may run side by side (CG_PASS_OVERLAP=0 chains them): at 2 bytes per
-         * position the overlap hides each launch's ramp and tail, C2 sample 1.25 -> 1.20 ms (measured r01h). */
-        cg_slot& o = c->slot[(c->cur + c->n_slot - 1) % c->n_slot];
-        static const bool overlap = !(getenv("CG_PASS_OVERLAP") && atoi(getenv("CG_PASS_OVERLAP")) == 0);
-        if (o.used && !overlap) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0));
-    }
+    { int rc = chain_pass(c, c->cur); if (rc) return rc; }
     {
         prof_scope ps(c, s.s_work, 1, 1);
         CU(c, cgk_depth_pass(s.s_work, s.sub, J));
     }
+    CU(c, cudaEventRecord(s.ev_passk, s.s_work));
     /* a collective that still reads this bank must be through before the row is rewritten */
     if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(s.s_work, c->ev_bank_read[c->bank], 0));
     /* asynchronous HOST mode hands over a page-locked pointer, DEVICE mode a device pointer: the kernel writes the row there itself */
@@ -856,9 +866,9 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
     cg_dev_job J = s.hj[0];                    /* this launch's view of the job: one kind of CNV */
     J.cnv[t] = d_in; J.calls[t] = d_out; J.n_cnv[t] = (int)n; J.n_cnv[t ^ 1] = 0;
-    J.cnv0[0] = 0; J.cnv0[1] = t ? 0 : (int)n;
+    J.cnv0[0] = 0; J.cnv0[1] = t ? 0 : cgk_geno_groups(n);
     cg_sub S = s.sub;
-    S.n_cnv = (int)n;
+    S.n_cnv = cgk_geno_groups(n);
     {
         prof_scope ps(c, st, 2, 1);
         CU(c, cgk_genotype(st, S, J, c->n_sms));
@@ -908,9 +918,9 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         if ((rc = validate_job(c, j, (size_t)k)) != CG_OK) return rc;
         const int n_chunks = (j.chrom_len + CG_CHUNK - 1) / CG_CHUNK;
         space += cgk_job_space(n_chunks); work += n_chunks;
-        mark_blocks += (long long)((j.n_reads + 255) / 256);
+        mark_blocks += (long long)cgk_mark_blocks(j.n_reads);
         if (j.use_mappability && j.n_runs) { run_blocks += (long long)((j.n_runs + 1 + 255) / 256); ridx_words += (size_t)cgk_run_index_words(j.chrom_len); }
-        n_cnv += (long long)(j.n_del + j.n_dup);
+        n_cnv += (long long)cgk_geno_groups(j.n_del) + cgk_geno_groups(j.n_dup);
         if (host) {
             in_bytes += j.reads ? al256(j.n_reads * sizeof(cg_read)) : al256(j.n_reads * 4) + (j.reads_mapq ? al256(j.n_reads) : 0);
             if (!(j.flags & CG_JOB_ANNOTATION_RESIDENT)) {
@@ -982,9 +992,9 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
             J.run_blk0 = rblk0;
         }
         /* CNVs and calls: device memory, or the caller's page-locked arrays read and written across PCIe by the kernel */
-        J.cnv[0] = j.dels; J.calls[0] = j.del_calls; J.n_cnv[0] = (int)j.n_del; J.cnv0[0] = cnv0; cnv0 += (int)j.n_del;
-        J.cnv[1] = j.dups; J.calls[1] = j.dup_calls; J.n_cnv[1] = (int)j.n_dup; J.cnv0[1] = cnv0; cnv0 += (int)j.n_dup;
-        chunk0 += cgk_job_space(n_chunks); work0 += n_chunks; blk0 += (int)((j.n_reads + 255) / 256);
+        J.cnv[0] = j.dels; J.calls[0] = j.del_calls; J.n_cnv[0] = (int)j.n_del; J.cnv0[0] = cnv0; cnv0 += cgk_geno_groups(j.n_del);
+        J.cnv[1] = j.dups; J.calls[1] = j.dup_calls; J.n_cnv[1] = (int)j.n_dup; J.cnv0[1] = cnv0; cnv0 += cgk_geno_groups(j.n_dup);
+        chunk0 += cgk_job_space(n_chunks); work0 += n_chunks; blk0 += cgk_mark_blocks(j.n_reads);
         if (j.chr_index + 1 > c->n_rows) c->n_rows = j.chr_index + 1;
     }
     if (host) {
@@ -1005,12 +1015,12 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         prof_scope ps(c, s.s_work, 0, 1);
         CU(c, cgk_mark(s.s_work, s.sub, J0));
     }
-    if (!getenv("CG_PASS_OVERLAP") || atoi(getenv("CG_PASS_OVERLAP")) != 0) { /* passes of consecutive submissions may overlap */ }
-    else { cg_slot& o = c->slot[(si + c->n_slot - 1) % c->n_slot]; if (o.used && &o != &s) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0)); }
+    if ((rc = chain_pass(c, si)) != CG_OK) return rc;
     {
         prof_scope ps(c, s.s_work, 1, 1);
         CU(c, cgk_depth_pass(s.s_work, s.sub, J0));
     }
+    CU(c, cudaEventRecord(s.ev_passk, s.s_work));
     if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(s.s_work, c->ev_bank_read[c->bank], 0));
     {
         prof_scope ps(c, s.s_work, 0, 1);

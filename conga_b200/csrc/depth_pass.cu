@@ -129,7 +129,7 @@ cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, 
 
 /* ------------------------------------------------------------------------- */
 /* one sweep over the records of the submission: sortedness and range checks,  */
-/* chunk boundaries, passing records per chunk/group/super                     */
+/* first record of every chunk, records that pass the mapq threshold           */
 __device__ __forceinline__ int chunk_of(int pos, int n_chunks)
 {
     int t = pos >> CG_CHUNK_SHIFT;            /* arithmetic shift: negative pos -> negative chunk */
@@ -147,6 +147,9 @@ __device__ __forceinline__ bool run_leader(int key, int lane, int& cnt)
     cnt = (above ? __ffs(above) - 1 : 32) - lane;
     return leader;
 }
+
+#define MARK_U 4                      /* records per thread and block visit: MARK_U independent loads in flight */
+#define MARK_BLOCK (256 * MARK_U)     /* records per block visit = the unit of cg_dev_job::mark_blk0 */
 
 __global__ void __launch_bounds__(256)
 k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
@@ -178,36 +181,41 @@ k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
             n_chunks = J.n_chunks; chrom_len = J.chrom_len; mq = J.mq_threshold; chunk0 = J.chunk0; ctl = J.ctl;
             f = 0; n_pass = 0; cur = j;
         }
-        const long long k = (long long)(b - s_blk0[j]) * 256 + threadIdx.x;
-        const bool in = k < n;
-        const long long i = first + k;
-        int key = -1 - lane;
-        if (in) {
-            int p, mapq;
-            load_rec(R, i, p, mapq);
-            const int cp = chunk_of(p, n_chunks);
-            int cq = -1;
-            if (i > 0) {
-                const int q = load_pos(R, i - 1);
-                if (p < q) f |= CG_FLAG_UNSORTED;
-                cq = chunk_of(q, n_chunks);
-            }
-            const bool inside = p >= 0 && p < chrom_len;
-            if (!inside) f |= CG_FLAG_RANGE;
-            for (int t = cq + 1; t <= cp; t++) S.k.chunk_lo[chunk0 + t] = (int32_t)i;
-            if (mapq > mq) {                                             /* bam_data.c:205 */
-                n_pass++;                                                /* bam_data.c:214 */
-                if (inside) key = chunk0 + cp;
+        /* the sweep is a chain load -> compare -> store per record, so its speed is the number of loads in
+         * flight and the instructions per record: MARK_U records per thread (256 apart, coalesced per warp) are
+         * asked for before any is looked at; the record in front of a warp's 32 comes from the lane below (one
+         * extra load for lane 0); only a lane whose record opens a new chunk does more than a dozen instructions */
+        const int k0 = (b - s_blk0[j]) * MARK_BLOCK + (int)threadIdx.x;       /* batches hold < 2^31 records */
+        const int n32 = (int)n;
+        int p[MARK_U], mapq[MARK_U], prev0[MARK_U];
+#pragma unroll
+        for (int u = 0; u < MARK_U; u++) {
+            const int k = k0 + 256 * u;
+            p[u] = 0; mapq[u] = 0; prev0[u] = 0;
+            if (k < n32) {
+                load_rec(R, first + k, p[u], mapq[u]);
+                if (lane == 0 && first + k > 0) prev0[u] = load_pos(R, first + k - 1);
             }
         }
-        /* sorted stream: records of one chunk sit in adjacent lanes -> one atomic per chunk per warp,
-         * and the same for the two coarser levels */
-        int cnt;
-        if (run_leader(key, lane, cnt) && key >= 0) atomicAdd(&S.k.cnt1[key], cnt);
-        const int gkey = key >= 0 ? key >> LVL : key;
-        if (run_leader(gkey, lane, cnt) && gkey >= 0) atomicAdd(&S.k.cnt2[gkey], cnt);
-        const int skey = key >= 0 ? key >> (2 * LVL) : key;
-        if (run_leader(skey, lane, cnt) && skey >= 0) atomicAdd(&S.k.cnt3[skey], cnt);
+#pragma unroll
+        for (int u = 0; u < MARK_U; u++) {
+            const int k = k0 + 256 * u;
+            const int cp = chunk_of(p[u], n_chunks);
+            int q = __shfl_up_sync(FULL, p[u], 1);            /* the record in front (valid whenever this one is) */
+            int cq = __shfl_up_sync(FULL, cp, 1);
+            if (lane == 0) { q = prev0[u]; cq = chunk_of(q, n_chunks); }
+            if (k < n32) {
+                const bool has_prev = first + k > 0;
+                if (has_prev && p[u] < q) f |= CG_FLAG_UNSORTED;
+                if ((unsigned)p[u] >= (unsigned)chrom_len) f |= CG_FLAG_RANGE;
+                n_pass += mapq[u] > mq;                                  /* bam_data.c:205, :214 */
+                if (!has_prev) cq = -1;
+                if (cp > cq) {
+                    const int i = (int)(first + k);
+                    for (int t = cq + 1; t <= cp; t++) S.k.chunk_lo[chunk0 + t] = i;
+                }
+            }
+        }
     }
     if (cur >= 0) {
         if (f) atomicOr(&ctl[CG_W_FLAGS], f);
@@ -215,6 +223,8 @@ k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
         if (lane == 0 && n_pass) atomicAdd(reinterpret_cast<unsigned long long*>(ctl + CG_W_PASSED), (unsigned long long)n_pass);
     }
 }
+
+int cgk_mark_blocks(unsigned long long n_records) { return (int)((n_records + MARK_BLOCK - 1) / MARK_BLOCK); }
 
 cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 {
@@ -268,10 +278,10 @@ struct __align__(16) pass_smem {
 };
 
 #define PASS_MAX_CTAS_PER_SM 3        /* register/shared-memory budget the kernel is compiled for */
-/* CTAs per SM one launch asks for.  Measured on B200 (C2 chromosomes, pass alone, r01h): 1 -> 4.9, 2 -> 6.1,
- * 3 -> 5.6 TB/s: more resident warps mean more concurrent write streams and worse HBM efficiency; the
- * rest of the SM stays free for the genotype and preparation kernels. */
-#define PASS_GRID_CTAS_PER_SM 2
+/* CTAs per SM one launch asks for.  Measured on B200 with one launch per sample (r02b, pass alone): C3 1 -> 2.38 ms,
+ * 2 -> 1.40, 3 -> 1.12 (0.85 of the copy peak); C2 2 -> 1.06, 3 -> 0.99 (0.91): the loop waits on record loads that
+ * are asked for one chunk ahead, and under a saturated HBM a chunk-time of 16 warps is shorter than that latency. */
+#define PASS_GRID_CTAS_PER_SM 3
 #ifndef PASS_BATCH
 #define PASS_BATCH 4                  /* chunks per visit to the work counter */
 #endif
@@ -462,6 +472,9 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             __syncwarp();
 
             if (!wrapped) {
+                /* the chunk's depth sum = its records (k_finalize sums the group and super levels from these) */
+                const int chunk_total = __reduce_add_sync(FULL, lane < nwin ? wend[lane] : 0);
+                if (lane == 0) S.k.cnt1[P.chunk0 + clc] = chunk_total;
                 /* ---- rows -> depth stores: the packed bins ARE the int16 output vectors ---- */
                 char* dp = reinterpret_cast<char*>(S.depth) + (gpos + (size_t)lane * 8) * 2;
 #pragma unroll
@@ -501,16 +514,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
                     }
                     chunk_total = run;
                 }
-                /* the count levels hold the number of records; a wrapped int16 changes the chunk's depth sum */
-                if (lane == 0) {
-                    const int g = P.chunk0 + clc;
-                    const int old = S.k.cnt1[g];
-                    if (old != chunk_total) {
-                        S.k.cnt1[g] = chunk_total;
-                        atomicAdd(&S.k.cnt2[g >> LVL], chunk_total - old);
-                        atomicAdd(&S.k.cnt3[g >> (2 * LVL)], chunk_total - old);
-                    }
-                }
+                if (lane == 0) S.k.cnt1[P.chunk0 + clc] = chunk_total;     /* depth sum of the chunk, wrapped int16s included */
 
                 /* ---- rows -> depth stores, window-end sums ---- */
                 {
@@ -606,28 +610,75 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1
 
 /* ------------------------------------------------------------------------- */
 /* per job: the partial rows of the pass -> the cg_chrom_stats row (read_distribution.c:27-73), the
- * expected table (:75-83), the chromosome's flags */
-__global__ void __launch_bounds__(256)
+ * expected table (:75-83), the chromosome's flags; and the group / super levels of the depth sums from the
+ * chunk level (what depth_sum_before in genotype.cu reads).  grid = (jobs, FIN_Y): the CTAs of a job share
+ * its supers, CTA (j, 0) also writes the row. */
+#define FIN_Y 4
+#define FIN_T 1024
+#define FIN_PARTS (FIN_T / 256)       /* slices of the pass's CTAs summed side by side: 4 x 256 threads, 202 of each busy */
+__global__ void __launch_bounds__(FIN_T)
 k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
     const cg_dev_job& J = S.jobs ? S.jobs[blockIdx.x] : J1;
+    __shared__ long long part[FIN_PARTS][CG_PART_WORDS];
     __shared__ long long row[CG_STATS_WORDS];
-    const int tid = threadIdx.x, lane = tid & 31;
-    if (tid < CG_PART_WORDS) {
-        const int32_t* p = S.partial + (size_t)blockIdx.x * CG_PART_WORDS + tid;
-        const size_t stride = (size_t)S.n_jobs * CG_PART_WORDS;
-        long long s = 0;
-        if (tid < CG_GC_BINS) { for (int c = 0; c < S.n_pass_ctas; c++) s += (long long)p[c * stride]; }
-        else                  { for (int c = 0; c < S.n_pass_ctas; c++) s += (long long)(unsigned)p[c * stride]; }
-        row[tid] = s;
-    } else if (tid >= 224) {
-        /* calc_mu_per_chr, read_distribution.c:35: |sum| <= number of records < 2^31 */
-        int tot = 0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    /* ---- depth sums per group of 32 chunks and per super of 32 groups, from the chunk level the pass wrote ---- */
+    {
         const int s0 = J.chunk0 >> (2 * LVL), s1 = (J.chunk0 + J.n_chunks + CG_SUPER_CHUNKS - 1) >> (2 * LVL);
-        for (int j = s0 + lane; j < s1; j += 32) tot += S.k.cnt3[j];
-        tot = __reduce_add_sync(FULL, tot);
+        for (int sp = s0 + (int)blockIdx.y * (FIN_T / 32) + warp; sp < s1; sp += (FIN_T / 32) * FIN_Y) {
+            const int32_t* c1 = S.k.cnt1 + ((size_t)sp << (2 * LVL));
+            int v[32];
+#pragma unroll
+            for (int g = 0; g < 32; g++) v[g] = c1[(g << LVL) + lane];       /* 32 independent coalesced loads */
+            int mine = 0;                                     /* lane g ends up with the sum of group g */
+#pragma unroll
+            for (int g = 0; g < 32; g++) {
+                const int t = __reduce_add_sync(FULL, v[g]);
+                if (lane == g) mine = t;
+            }
+            S.k.cnt2[((size_t)sp << LVL) + lane] = mine;
+            const int tot = __reduce_add_sync(FULL, mine);
+            if (lane == 0) S.k.cnt3[sp] = tot;
+        }
+    }
+    if (blockIdx.y != 0) return;
+
+    /* ---- the statistics row: word w of every CTA's partial row, FIN_PARTS slices of the CTAs at a time ---- */
+    {
+        const int w = tid & 255, sl = tid >> 8;
+        if (w < CG_PART_WORDS) {
+            const int32_t* p = S.partial + (size_t)blockIdx.x * CG_PART_WORDS + w;
+            const size_t stride = (size_t)S.n_jobs * CG_PART_WORDS;
+            long long s = 0;
+            if (w < CG_GC_BINS) {
+#pragma unroll 8
+                for (int c = sl; c < S.n_pass_ctas; c += FIN_PARTS) s += (long long)p[c * stride];
+            } else {
+#pragma unroll 8
+                for (int c = sl; c < S.n_pass_ctas; c += FIN_PARTS) s += (long long)(unsigned)p[c * stride];
+            }
+            part[sl][w] = s;
+        }
+    }
+    __syncthreads();
+    if (tid < CG_PART_WORDS) {
+        long long s = 0;
+#pragma unroll
+        for (int k = 0; k < FIN_PARTS; k++) s += part[k][tid];
+        row[tid] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        /* calc_mu_per_chr, read_distribution.c:33-37: the sum of every depth = the sum over the GC bins, each
+         * position belonging to exactly one bin (:70-71) */
+        long long tot = 0;
+        for (int b = lane; b < CG_GC_BINS; b += 32) tot += row[b];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(FULL, tot, d);
         if (lane == 0) {
-            row[2 * CG_GC_BINS] = (long long)tot;
+            row[2 * CG_GC_BINS] = tot;
             row[2 * CG_GC_BINS + 1] = (long long)*reinterpret_cast<const unsigned long long*>(J.ctl + CG_W_PASSED);
         }
     }
@@ -646,7 +697,7 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
 
 cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 {
-    k_finalize<<<S.n_jobs, 256, 0, s>>>(S, J1);
+    k_finalize<<<dim3((unsigned)S.n_jobs, FIN_Y), FIN_T, 0, s>>>(S, J1);
     return cudaGetLastError();
 }
 

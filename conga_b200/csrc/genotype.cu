@@ -376,10 +376,16 @@ __device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ dept
     return __reduce_add_sync(FULL, part);
 }
 
-/* One CNV per warp (measured on B200, C2, every kernel on one shared-memory carve-out so that they really
- * share SMs with the depth pass: 8 CNVs per warp 7.7 ms of genotype kernels per sample, 4 -> 5.4, 2 -> 4.1,
- * 1 -> 2.9: the GPU is otherwise idle under the bandwidth-bound pass, so latency wins over lane efficiency).
- * The launch covers every CNV of the submission: global index -> (job, kind) through the cnv0 prefix. */
+/* GENO_G CNVs per warp, one per lane in the lane = CNV phases.  The launch covers every CNV of the submission:
+ * the CNVs of a (job, kind) segment are cut into groups of GENO_G, global group index -> segment through the
+ * cnv0 prefix (in groups).  With one launch per chromosome (round 1) one CNV per warp was best: the launches were
+ * small and latency-bound.  One launch per sample carries 15-40 k CNVs and is bound by issue slots instead (r02b,
+ * G = 1: 1.9 IPC at 9.8 active threads per warp, every short CNV a serial walk on a single lane). */
+#ifndef GENO_G
+#define GENO_G 8
+#endif
+int cgk_geno_groups(unsigned long long n_cnv) { return (int)((n_cnv + GENO_G - 1) / GENO_G); }
+
 __global__ void __launch_bounds__(GENO_WARPS * 32)
 k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
@@ -397,7 +403,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
     const cg_cnv* __restrict__ cnvs = nullptr; cg_call* out = nullptr;
     const int16_t* __restrict__ depth = nullptr; const int8_t* __restrict__ gc = nullptr;
     const cg_maprun* __restrict__ runs = nullptr; const int32_t* __restrict__ run_idx = nullptr;
-    int n_runs = 0, has_map = 0, chrom_len = 0, chunk0 = 0, is_dup = 0, n_windows = 0;
+    int n_runs = 0, has_map = 0, chrom_len = 0, chunk0 = 0, is_dup = 0, n_windows = 0, n_seg = 0;
     bool use_map = false;
     const cg_counts counts = S.k;
 
@@ -406,7 +412,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         if (seg != cur_seg) {
             const cg_dev_job& J = jobs[seg >> 1];
             is_dup = seg & 1;
-            cnvs = J.cnv[is_dup]; out = J.calls[is_dup];
+            cnvs = J.cnv[is_dup]; out = J.calls[is_dup]; n_seg = J.n_cnv[is_dup];
             if ((seg >> 1) != cur_job) {
                 depth = S.depth + ((size_t)J.chunk0 << CG_CHUNK_SHIFT); gc = J.gc;
                 runs = J.runs; run_idx = J.run_idx; n_runs = J.n_runs; has_map = J.has_map;
@@ -420,9 +426,9 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             }
             cur_seg = seg;
         }
-        /* ---- phase 0: lane 0 = the CNV ---- */
-        const int c = gi - s_seg0[seg];
-        const bool valid = lane == 0;
+        /* ---- phase 0: lane = CNV ---- */
+        const int c = (gi - s_seg0[seg]) * GENO_G + lane;
+        const bool valid = lane < GENO_G && c < n_seg;
         cg_cnv v = make_cnv(0, 0);
         if (valid) v = cnvs[c];
         int s = v.start, e = v.end;

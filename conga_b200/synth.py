@@ -43,6 +43,13 @@ class Workload:
     chroms: List[Chromosome] = field(default_factory=list)
     mq_threshold: int = -1
     has_mappability: bool = False
+    # a batch (config 5): sample_pos[s][i] = sorted int32 start positions of sample s on chromosome i; sample 0 is
+    # what chroms[i].reads holds.  None: one sample.
+    sample_pos: Optional[List[List[np.ndarray]]] = None
+
+    @property
+    def n_samples(self) -> int:
+        return len(self.sample_pos) if self.sample_pos is not None else 1
 
     @property
     def n_reads(self) -> int:
@@ -218,6 +225,38 @@ def config3(scale: float = 1.0, seed: int = SEED0 + 3) -> Workload:
     """C3: whole genome 1x, 1000G-Phase-3-shaped call sets (~33k dels median 3 kb, ~6k dups median 35 kb)."""
     return genome("c3: GRCh37-shaped, 1x, ~40k CNVs", 1.0, 33_000, 6_000, False, seed, scale=scale,
                   lognormal=((3000, 1.3, 1_000_000), (35000, 1.2, 1_000_000)))
+
+
+def sorted_uniform_positions(length: int, n: int, rng: np.random.Generator) -> np.ndarray:
+    """n start positions, uniform on [1, length - 100), already sorted: normalised partial sums of exponential
+    gaps (the order statistics of a uniform sample) — no sort, so a 64-sample batch is generated in seconds."""
+    if n == 0:
+        return np.zeros(0, dtype=np.int32)
+    g = rng.standard_exponential(n + 1)
+    c = np.cumsum(g)
+    pos = 1 + (c[:-1] / c[-1]) * max(1, length - 101)
+    return np.minimum(pos.astype(np.int64), length - 1).astype(np.int32)
+
+
+def config4(scale: float = 1.0, seed: int = SEED0 + 4) -> Workload:
+    """C4's depth / genotype side: whole genome 5x of 70-bp reads, --min-mapq 20, the C3-shaped call sets.  (The
+    --rp side of config 4 needs bases and a reference sequence: tests/cli_inputs.py builds those for the whole-
+    program runs; this workload is what the four hot-path seams see.)"""
+    wl = genome("c4: GRCh37-shaped, 5x, ~40k CNVs, --min-mapq 20 (depth + genotype seams)", 5.0, 33_000, 6_000, False, seed,
+                scale=scale, mq_threshold=20, lognormal=((3000, 1.3, 1_000_000), (35000, 1.2, 1_000_000)))
+    return wl
+
+
+def config5(n_samples: int = 64, scale: float = 1.0, seed: int = SEED0 + 5) -> Workload:
+    """C5: a batch of n_samples 0.5x samples genotyped against ONE shared C3-shaped CNV set.  GC bytes and CNVs
+    are those of chroms[]; the samples differ in their reads (seed + sample)."""
+    wl = genome("c5: batch of %d GRCh37-shaped 0.5x samples against one ~40k-CNV set" % n_samples, 0.5, 33_000, 6_000, False, seed,
+                scale=scale, lognormal=((3000, 1.3, 1_000_000), (35000, 1.2, 1_000_000)))
+    wl.sample_pos = [[np.ascontiguousarray(c.reads["pos"]) for c in wl.chroms]]
+    for sidx in range(1, n_samples):
+        rng = np.random.default_rng(seed + 1000 * sidx)
+        wl.sample_pos.append([sorted_uniform_positions(c.length, int(round(c.length * 0.5 / 70)), rng) for c in wl.chroms])
+    return wl
 
 
 def lpt_partition(lengths: List[int], n_parts: int) -> List[List[int]]:
