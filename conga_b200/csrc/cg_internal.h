@@ -87,12 +87,15 @@ struct cg_sub {
     int32_t        n_work;            /* chunks of all jobs */
     int32_t        n_space;           /* chunks of the slot's chunk space in use (multiple of CG_SUPER_CHUNKS) */
     int32_t        n_mark_blocks, n_run_blocks, n_cnv;   /* n_cnv: CNV groups of the launch */
+    int32_t        geno_g;            /* CNVs per group = per warp of k_genotype */
     cg_counts      k;
     int16_t*       depth;             /* [n_space * CG_CHUNK] */
     uint32_t*      depth32;           /* NULL, or the out-of-order path's per-position u32 counts (zero at rest) */
     int32_t*       partial;           /* [pass CTAs][n_jobs][CG_PART_WORDS] */
     int32_t        n_pass_ctas;
-    unsigned int*  sctl;              /* CG_SW_* words of the slot */
+    unsigned int*  sctl;              /* CG_SW_* words of the slot (zero at rest) */
+    long long*     fin_acc;           /* [CG_JMAX][256] k_finalize's scratch rows (zero at rest) */
+    unsigned int*  fin_cnt;           /* [CG_JMAX] CTAs of k_finalize that have added their share (zero at rest) */
     unsigned int*  sticky;            /* context-wide word: CG_FLAG_RANGE is copied here */
     unsigned int*  h_flags;           /* NULL, or page-locked [n_jobs]: each job's flag word for the host */
 };
@@ -107,8 +110,7 @@ void cg_flatten_rows(const cg_mapiv* rows, size_t n, int32_t chrom_len, std::vec
 size_t      cgk_counts_words(int n_space);                        /* int32 words the counts of a chunk space need */
 cg_counts   cgk_counts_layout(int32_t* base, int n_space);
 int         cgk_job_space(int n_chunks);                          /* chunks of chunk space a job of n_chunks occupies */
-int         cgk_pass_grid(int n_work, int n_sms);                 /* CTAs of the pass, = rows of cg_sub::partial */
-cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int32_t* counts_base);
+int         cgk_pass_grid(int n_work, long long n_records, int n_sms);   /* CTAs of the pass, = rows of cg_sub::partial */
 int         cgk_mark_blocks(unsigned long long n_records);        /* block visits of k_mark for a batch of records */
 cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
@@ -121,7 +123,8 @@ cudaError_t cgk_configure_depth(void);                            /* once per pr
 cudaError_t cgk_configure_genotype(void);
 
 /* genotype.cu */
-int         cgk_geno_groups(unsigned long long n_cnv);            /* warps' worth of work n CNVs of one (job, kind) are */
+int         cgk_geno_g(unsigned long long n_cnv, int n_sms);      /* CNVs per warp for a launch over n_cnv CNVs */
+int         cgk_geno_groups(unsigned long long n_cnv, int g);     /* warps' worth of work n CNVs of one (job, kind) are */
 cudaError_t cgk_genotype(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
 int         cgk_run_index_words(int32_t chrom_len);
 cudaError_t cgk_run_index(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);

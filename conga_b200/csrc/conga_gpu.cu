@@ -38,7 +38,7 @@
 #define CG_NSLOT 6
 #endif
 #define CG_NBANK 2
-#define CG_PASS_GRID_MAX (160 * 3)    /* rows of a slot's partial table: SMs x CTAs per SM the pass may ask for */
+#define CG_PASS_GRID_MAX (160 * 4)    /* rows of a slot's partial table: SMs x CTAs per SM the pass may ask for */
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
 
@@ -81,6 +81,8 @@ struct cg_slot {
     cudaEvent_t ev_geno[2] = {nullptr, nullptr};   /* s_geno[t]: last genotype work queued for this slot */
     cudaEvent_t ev_runs = nullptr;            /* s_geno[0]: mappability runs uploaded and indexed */
     bool used = false, geno_queued[2] = {false, false}, runs_uploaded = false;
+    bool open = false;                        /* a chromosome was begun here and not finished: the control words are not at rest */
+    long long* d_fin = nullptr;               /* [CG_JMAX][256] scratch rows + CG_JMAX counters of k_finalize (zero at rest) */
     bool dirty_work = false, dirty_geno[2] = {false, false};     /* work queued since the last cg_join */
 };
 
@@ -323,6 +325,8 @@ cg_ctx* cg_create(int device)
             && cudaMemset(s.d_ctl, 0, sizeof(unsigned) * (CG_CTL_WORDS * CG_JMAX + 8)) == cudaSuccess
             && cudaMalloc(&s.d_partial, sizeof(int32_t) * (size_t)CG_PASS_GRID_MAX * CG_JMAX * CG_PART_WORDS) == cudaSuccess
             && cudaMalloc(&s.d_jobs, sizeof(cg_dev_job) * CG_JMAX) == cudaSuccess
+            && cudaMalloc(&s.d_fin, sizeof(long long) * (CG_JMAX * 256 + CG_JMAX)) == cudaSuccess
+            && cudaMemset(s.d_fin, 0, sizeof(long long) * (CG_JMAX * 256 + CG_JMAX)) == cudaSuccess
             && cudaMallocHost(&s.h_jobs, sizeof(cg_dev_job) * CG_JMAX) == cudaSuccess
             && cudaMallocHost(&s.h_flags, sizeof(unsigned) * CG_JMAX) == cudaSuccess
             && cudaEventCreateWithFlags(&s.ev_table, cudaEventDisableTiming) == cudaSuccess
@@ -339,7 +343,7 @@ cg_ctx* cg_create(int device)
         cg_destroy(c);
         return nullptr;
     }
-    if (c->n_sms * 3 > CG_PASS_GRID_MAX) { fail(nullptr, CG_ECUDA, "device has %d SMs; the library is sized for <= %d", c->n_sms, CG_PASS_GRID_MAX / 3); cg_destroy(c); return nullptr; }
+    if (c->n_sms * 4 > CG_PASS_GRID_MAX) { fail(nullptr, CG_ECUDA, "device has %d SMs; the library is sized for <= %d", c->n_sms, CG_PASS_GRID_MAX / 4); cg_destroy(c); return nullptr; }
     snprintf(c->err, sizeof c->err, "no error");
     return c;
 }
@@ -355,7 +359,7 @@ void cg_destroy(cg_ctx* c)
     for (int i = 0; i < CG_NSLOT; i++) {
         cg_slot& s = c->slot[i];
         cudaFree(s.d_reads); cudaFree(s.d_pos); cudaFree(s.d_mapq); cudaFree(s.d_gc); cudaFree(s.d_counts);
-        cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl); cudaFree(s.d_partial); cudaFree(s.d_jobs);
+        cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl); cudaFree(s.d_partial); cudaFree(s.d_jobs); cudaFree(s.d_fin);
         cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32); cudaFree(s.d_in);
         if (s.h_jobs) cudaFreeHost(s.h_jobs);
         if (s.h_flags) cudaFreeHost(s.h_flags);
@@ -509,6 +513,10 @@ static int take_slot(cg_ctx* c, int* si_out)
         if (o.used) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_pass, 0));
         for (int t = 0; t < 2; t++) if (o.geno_queued[t]) CU(c, cudaStreamWaitEvent(s.s_work, o.ev_geno[t], 0));
     }
+    if (s.open) {       /* begun, records pushed, never finished: no finalize has put the control words back to rest */
+        CU(c, cudaMemsetAsync(s.d_ctl, 0, sizeof(unsigned) * (CG_CTL_WORDS * CG_JMAX + 8), s.s_work));
+        s.open = false;
+    }
     s.used = true; s.geno_queued[0] = s.geno_queued[1] = false; s.runs_uploaded = false;
     s.arena_used = 0; s.rec_fmt = 0; s.sample = false; s.check = false; s.n_jobs = 0;
     c->n_begun++;
@@ -549,7 +557,7 @@ static int ensure_space(cg_ctx* c, cg_slot& s, int n_space, bool want_depth32)
     return CG_OK;
 }
 
-static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space)
+static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space, long long n_records)
 {
     cg_sub& S = s.sub;
     memset(&S, 0, sizeof S);
@@ -557,8 +565,10 @@ static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space)
     S.k = cgk_counts_layout(s.d_counts, n_space);
     S.depth = s.d_depth;
     S.partial = s.d_partial;
-    S.n_pass_ctas = cgk_pass_grid(n_work, c->n_sms);
+    S.n_pass_ctas = cgk_pass_grid(n_work, n_records, c->n_sms);
     S.sctl = s.d_ctl + CG_CTL_WORDS * CG_JMAX;
+    S.fin_acc = s.d_fin;
+    S.fin_cnt = reinterpret_cast<unsigned int*>(s.d_fin + CG_JMAX * 256);
     S.sticky = c->d_sticky;
 }
 
@@ -615,15 +625,12 @@ int cg_chrom_begin(cg_ctx* c, int chr_index, int32_t chrom_len, const int8_t* gc
     J.stats_row = stats_row_of(c, chr_index);
     J.expected = s.d_expected; J.ctl = s.d_ctl; J.run_idx = nullptr;
     s.n_jobs = 1;
-    fill_sub(c, s, 1, n_chunks, n_space);
+    fill_sub(c, s, 1, n_chunks, n_space, 0);
     s.sub.depth32 = s.d_depth32;
     c->cur = si;
     c->in_chrom = true; c->finished = false;
     if (chr_index + 1 > c->n_rows) c->n_rows = chr_index + 1;
-    {
-        prof_scope ps(c, s.s_work, 0, 1);
-        CU(c, cgk_job_init(s.s_work, s.sub, J, s.d_counts));
-    }
+    s.open = true;                            /* until cg_chrom_finish: its finalize leaves the control words zero again */
     s.dirty_work = true;
     return CG_OK;
 }
@@ -712,6 +719,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
         prof_scope ps(c, s.s_work, 0, 1);
         CU(c, cgk_rare_scatter(s.s_work, s.sub, J, c->n_sms));
     }
+    s.sub.n_pass_ctas = cgk_pass_grid(s.sub.n_work, J.n_reads, c->n_sms);
     { int rc = chain_pass(c, c->cur); if (rc) return rc; }
     {
         prof_scope ps(c, s.s_work, 1, 1);
@@ -728,6 +736,7 @@ int cg_chrom_finish(cg_ctx* c, cg_chrom_stats* out)
     }
     CU(c, cudaEventRecord(s.ev_pass, s.s_work));
     s.dirty_work = true;
+    s.open = false;
     c->finished = true;
     if (!blocking(c)) return CG_OK;
     CU(c, cudaMemcpyAsync(c->h_stats, J.stats_row, sizeof(cg_chrom_stats), cudaMemcpyDeviceToHost, s.s_work));
@@ -866,9 +875,10 @@ int cg_genotype(cg_ctx* c, const cg_cnv* cnvs, size_t n, int is_dup, cg_call* ou
     if (t == 1 && s.runs_uploaded) CU(c, cudaStreamWaitEvent(st, s.ev_runs, 0));
     cg_dev_job J = s.hj[0];                    /* this launch's view of the job: one kind of CNV */
     J.cnv[t] = d_in; J.calls[t] = d_out; J.n_cnv[t] = (int)n; J.n_cnv[t ^ 1] = 0;
-    J.cnv0[0] = 0; J.cnv0[1] = t ? 0 : cgk_geno_groups(n);
     cg_sub S = s.sub;
-    S.n_cnv = cgk_geno_groups(n);
+    S.geno_g = cgk_geno_g(n, c->n_sms);
+    S.n_cnv = cgk_geno_groups(n, S.geno_g);
+    J.cnv0[0] = 0; J.cnv0[1] = t ? 0 : S.n_cnv;
     {
         prof_scope ps(c, st, 2, 1);
         CU(c, cgk_genotype(st, S, J, c->n_sms));
@@ -911,6 +921,10 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
     int rc;
     /* geometry of the submission */
     long long space = 0, work = 0, mark_blocks = 0, run_blocks = 0, n_cnv = 0;
+    unsigned long long all_cnvs = 0;
+    unsigned long long all_records = 0;
+    for (int k = 0; k < n; k++) { all_cnvs += jobs[k].n_del + jobs[k].n_dup; all_records += jobs[k].n_reads; }
+    const int G = cgk_geno_g(all_cnvs, c->n_sms);
     size_t in_bytes = 0, ridx_words = 0;
     const bool host = c->ptr_mode == CG_PTR_HOST;
     for (int k = 0; k < n; k++) {
@@ -920,7 +934,7 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         space += cgk_job_space(n_chunks); work += n_chunks;
         mark_blocks += (long long)cgk_mark_blocks(j.n_reads);
         if (j.use_mappability && j.n_runs) { run_blocks += (long long)((j.n_runs + 1 + 255) / 256); ridx_words += (size_t)cgk_run_index_words(j.chrom_len); }
-        n_cnv += (long long)cgk_geno_groups(j.n_del) + cgk_geno_groups(j.n_dup);
+        n_cnv += (long long)cgk_geno_groups(j.n_del, G) + cgk_geno_groups(j.n_dup, G);
         if (host) {
             in_bytes += j.reads ? al256(j.n_reads * sizeof(cg_read)) : al256(j.n_reads * 4) + (j.reads_mapq ? al256(j.n_reads) : 0);
             if (!(j.flags & CG_JOB_ANNOTATION_RESIDENT)) {
@@ -943,10 +957,11 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
 
     s.sample = true; s.n_jobs = n; s.ptr_mode = c->ptr_mode; s.async = c->async;
     s.src.assign(jobs, jobs + n);
-    fill_sub(c, s, n, (int)work, (int)space);
+    fill_sub(c, s, n, (int)work, (int)space, (long long)all_records);
     s.sub.jobs = s.d_jobs;
     s.sub.n_mark_blocks = (int)mark_blocks; s.sub.n_run_blocks = (int)run_blocks; s.sub.n_cnv = (int)n_cnv;
     s.sub.h_flags = s.h_flags;
+    s.sub.geno_g = G;
 
     int chunk0 = 0, work0 = 0, blk0 = 0, rblk0 = 0, cnv0 = 0;
     size_t in_off = 0, ridx_off = 0;
@@ -992,8 +1007,8 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
             J.run_blk0 = rblk0;
         }
         /* CNVs and calls: device memory, or the caller's page-locked arrays read and written across PCIe by the kernel */
-        J.cnv[0] = j.dels; J.calls[0] = j.del_calls; J.n_cnv[0] = (int)j.n_del; J.cnv0[0] = cnv0; cnv0 += cgk_geno_groups(j.n_del);
-        J.cnv[1] = j.dups; J.calls[1] = j.dup_calls; J.n_cnv[1] = (int)j.n_dup; J.cnv0[1] = cnv0; cnv0 += cgk_geno_groups(j.n_dup);
+        J.cnv[0] = j.dels; J.calls[0] = j.del_calls; J.n_cnv[0] = (int)j.n_del; J.cnv0[0] = cnv0; cnv0 += cgk_geno_groups(j.n_del, G);
+        J.cnv[1] = j.dups; J.calls[1] = j.dup_calls; J.n_cnv[1] = (int)j.n_dup; J.cnv0[1] = cnv0; cnv0 += cgk_geno_groups(j.n_dup, G);
         chunk0 += cgk_job_space(n_chunks); work0 += n_chunks; blk0 += cgk_mark_blocks(j.n_reads);
         if (j.chr_index + 1 > c->n_rows) c->n_rows = j.chr_index + 1;
     }
@@ -1006,10 +1021,6 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
     CU(c, cudaEventRecord(s.ev_table, s.s_work));
 
     const cg_dev_job& J0 = s.hj[0];            /* ignored by the kernels: the table is used */
-    {
-        prof_scope ps(c, s.s_work, 0, 1);
-        CU(c, cgk_job_init(s.s_work, s.sub, J0, s.d_counts));
-    }
     if (host) CU(c, cudaStreamWaitEvent(s.s_work, s.ev_copy, 0));
     if (mark_blocks) {
         prof_scope ps(c, s.s_work, 0, 1);

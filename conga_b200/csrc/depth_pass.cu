@@ -9,7 +9,6 @@
  *
  * Kernels, one launch each per submission (a whole sample through cg_run_chromosomes, or one chromosome
  * through cg_chrom_begin ... cg_chrom_finish):
- *   k_job_init     counts of the chunk space zeroed, chunk bounds "behind the last record", control words
  *   k_mark         one sweep over the records: sortedness / range flags, first record of every chunk,
  *                  passing records per chunk / group / super and per chromosome
  *   k_depth_pass   persistent warps pull chunks of ALL chromosomes from one counter (no per-chromosome ramp
@@ -101,31 +100,30 @@ __device__ __forceinline__ void load_rec(const rec_src& r, long long i, int& pos
         mapq = r.mapq ? (int)__ldg(r.mapq + i) : 255;        /* no mapq plane: the threshold is negative, everything passes */
     }
 }
+/* The same in two steps for software pipelining: load_raw only ISSUES the loads (nothing reads the result, so an
+ * in-order warp does not wait), unpack_raw is called where the record is used.  A load whose result is shifted or
+ * masked on the spot is not a prefetch: the warp stalls at the shift until the data is there. */
+__device__ __forceinline__ uint2 load_raw(const rec_src& r, long long i)
+{
+    if (r.aos) return __ldg(r.aos + i);
+    uint2 v;
+    v.x = (unsigned)__ldg(r.pos + i);
+    v.y = r.mapq ? (unsigned)__ldg(r.mapq + i) : 255u;
+    return v;
+}
+__device__ __forceinline__ void unpack_raw(bool aos, uint2 v, int& pos, int& mapq)
+{
+    pos = (int)v.x;
+    mapq = aos ? (int)((v.y >> 16) & 0xffu) : (int)v.y;
+}
+
 __device__ __forceinline__ int load_pos(const rec_src& r, long long i) { return r.aos ? (int)__ldg(&r.aos[i].x) : __ldg(r.pos + i); }
 
-/* submission start: clear the counts and the control words; every chunk bound starts "behind the last
- * record" (the pass clamps it to the record count) */
-__global__ void k_job_init(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1, int4* base4, int n_zero_vec, int n_vec)
-{
-    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
-    for (int j = i; j < n_vec; j += stride)
-        base4[j] = j < n_zero_vec ? make_int4(0, 0, 0, 0) : make_int4(0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff);
-    if (i < S.n_jobs * CG_CTL_WORDS) jobs[i / CG_CTL_WORDS].ctl[i % CG_CTL_WORDS] = 0u;
-    if (i < 4) S.sctl[i] = 0u;
-}
-
-cudaError_t cgk_job_init(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int32_t* counts_base)
-{
-    const cg_counts k = cgk_counts_layout(counts_base, S.n_space);
-    const int n_zero_vec = (int)((k.chunk_lo - counts_base) / 4);
-    const int n_vec = (int)(cgk_counts_words(S.n_space) / 4);
-    int blocks = (n_vec + 255) / 256;
-    if (blocks < 2) blocks = 2;                   /* CG_JMAX * CG_CTL_WORDS = 256 control words fit the first CTA */
-    if (blocks > 148 * 4) blocks = 148 * 4;
-    k_job_init<<<blocks, 256, 0, s>>>(S, J1, reinterpret_cast<int4*>(counts_base), n_zero_vec, n_vec);
-    return cudaGetLastError();
-}
+/* No kernel prepares a submission.  Every array the kernels accumulate into is ZERO AT REST: the work counters
+ * and the per-job control words are cleared by k_finalize when it has read them, its scratch rows likewise; the
+ * chunk depth sums are written for every chunk by the pass; the chunk bounds are written for every chunk by the
+ * record sweep (the chromosome's last record also closes the chunks behind it) and a chromosome without records
+ * has its bounds clamped to [0, 0] by the pass. */
 
 /* ------------------------------------------------------------------------- */
 /* one sweep over the records of the submission: sortedness and range checks,  */
@@ -181,40 +179,55 @@ k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
             n_chunks = J.n_chunks; chrom_len = J.chrom_len; mq = J.mq_threshold; chunk0 = J.chunk0; ctl = J.ctl;
             f = 0; n_pass = 0; cur = j;
         }
-        /* the sweep is a chain load -> compare -> store per record, so its speed is the number of loads in
-         * flight and the instructions per record: MARK_U records per thread (256 apart, coalesced per warp) are
-         * asked for before any is looked at; the record in front of a warp's 32 comes from the lane below (one
-         * extra load for lane 0); only a lane whose record opens a new chunk does more than a dozen instructions */
-        const int k0 = (b - s_blk0[j]) * MARK_BLOCK + (int)threadIdx.x;       /* batches hold < 2^31 records */
+        /* The sweep is a chain load -> compare -> store per record, so its speed is the number of loads in flight and
+         * the instructions per record.  A thread takes MARK_U CONSECUTIVE records: all their loads are issued before any
+         * is looked at (load_raw), and every record's predecessor sits in the same thread except the first one's, which
+         * comes from the lane below (one extra load for lane 0).  Only a record that opens a new chunk does more than a
+         * dozen instructions.  (r02d: one record per thread and step, 100 instructions per 32 records, 0.2 ms per 43 M.) */
+        const int k0 = (b - s_blk0[j]) * MARK_BLOCK + (int)threadIdx.x * MARK_U;      /* batches hold < 2^31 records */
         const int n32 = (int)n;
-        int p[MARK_U], mapq[MARK_U], prev0[MARK_U];
+        const bool aos = R.aos != nullptr;
+        uint2 raw[MARK_U];
+        int prev0 = 0;
 #pragma unroll
         for (int u = 0; u < MARK_U; u++) {
-            const int k = k0 + 256 * u;
-            p[u] = 0; mapq[u] = 0; prev0[u] = 0;
-            if (k < n32) {
-                load_rec(R, first + k, p[u], mapq[u]);
-                if (lane == 0 && first + k > 0) prev0[u] = load_pos(R, first + k - 1);
-            }
+            raw[u] = make_uint2(0u, 0u);
+            if (k0 + u < n32) raw[u] = load_raw(R, first + k0 + u);
         }
+        if (lane == 0 && k0 < n32 && first + k0 > 0) prev0 = load_pos(R, first + k0 - 1);
+        int p[MARK_U], cp[MARK_U], mapq[MARK_U];
+#pragma unroll
+        for (int u = 0; u < MARK_U; u++) { unpack_raw(aos, raw[u], p[u], mapq[u]); cp[u] = chunk_of(p[u], n_chunks); }
+        int q = __shfl_up_sync(FULL, p[MARK_U - 1], 1), cq = __shfl_up_sync(FULL, cp[MARK_U - 1], 1);
+        if (lane == 0) { q = prev0; cq = chunk_of(prev0, n_chunks); }
+        if (first + k0 == 0) cq = -1;                         /* the chromosome's first record opens every chunk up to its own */
+        int32_t* lo = S.k.chunk_lo + chunk0;
 #pragma unroll
         for (int u = 0; u < MARK_U; u++) {
-            const int k = k0 + 256 * u;
-            const int cp = chunk_of(p[u], n_chunks);
-            int q = __shfl_up_sync(FULL, p[u], 1);            /* the record in front (valid whenever this one is) */
-            int cq = __shfl_up_sync(FULL, cp, 1);
-            if (lane == 0) { q = prev0[u]; cq = chunk_of(q, n_chunks); }
-            if (k < n32) {
-                const bool has_prev = first + k > 0;
-                if (has_prev && p[u] < q) f |= CG_FLAG_UNSORTED;
+            if (k0 + u < n32) {
+                if (p[u] < q && first + k0 + u > 0) f |= CG_FLAG_UNSORTED;
                 if ((unsigned)p[u] >= (unsigned)chrom_len) f |= CG_FLAG_RANGE;
                 n_pass += mapq[u] > mq;                                  /* bam_data.c:205, :214 */
-                if (!has_prev) cq = -1;
-                if (cp > cq) {
-                    const int i = (int)(first + k);
-                    for (int t = cq + 1; t <= cp; t++) S.k.chunk_lo[chunk0 + t] = i;
+                if (cp[u] > cq) {                                        /* this record opens chunk cp (and the empty ones before it) */
+                    const int i = (int)first + k0 + u;
+                    lo[cp[u]] = i;
+#pragma unroll 1
+                    for (int t = cq + 1; t < cp[u]; t++) lo[t] = i;
                 }
             }
+            q = p[u]; cq = cp[u];
+        }
+        /* the last record pushed so far closes every chunk behind its own, the bound behind the last chunk included
+         * (a later batch's first record rewrites the ones it opens); the warp that holds it does that together */
+        const int last_u = n32 - 1 - k0;
+        const unsigned last_m = __ballot_sync(FULL, last_u >= 0 && last_u < MARK_U);
+        if (last_m) {
+            int mine = 0;
+#pragma unroll
+            for (int u = 0; u < MARK_U; u++) if (u == last_u) mine = cp[u];
+            const int cpl = __shfl_sync(FULL, mine, __ffs(last_m) - 1);
+            const int end = (int)first + n32;
+            for (int t = cpl + 1 + lane; t <= n_chunks; t += 32) lo[t] = end;
         }
     }
     if (cur >= 0) {
@@ -277,11 +290,13 @@ struct __align__(16) pass_smem {
      * positions; native 32-bit shared atomics instead of the CAS loop a 64-bit shared add compiles to */
 };
 
-#define PASS_MAX_CTAS_PER_SM 3        /* register/shared-memory budget the kernel is compiled for */
+#define PASS_MAX_CTAS_PER_SM 4        /* register budget the kernel is compiled for: 64 per thread, so that three CTAs leave
+                                         a quarter of the register file to the record sweep and the genotype kernel of the
+                                         neighbouring submissions */
 /* CTAs per SM one launch asks for.  Measured on B200 with one launch per sample (r02b, pass alone): C3 1 -> 2.38 ms,
  * 2 -> 1.40, 3 -> 1.12 (0.85 of the copy peak); C2 2 -> 1.06, 3 -> 0.99 (0.91): the loop waits on record loads that
  * are asked for one chunk ahead, and under a saturated HBM a chunk-time of 16 warps is shorter than that latency. */
-#define PASS_GRID_CTAS_PER_SM 3
+#define PASS_GRID_CTAS_PER_SM 3       /* upper value; cgk_pass_grid picks 2 or 3 by record density */
 #ifndef PASS_BATCH
 #define PASS_BATCH 4                  /* chunks per visit to the work counter */
 #endif
@@ -357,7 +372,8 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
 
     const unsigned n_work = (unsigned)S.n_work;
 
-    /* lanes 0..PASS_BATCH-1: job, chunk within the job and record bounds of the chunks of one batch */
+    /* lanes 0..PASS_BATCH-1: job, chunk within the job and record bounds of the chunks of one batch.  The two bounds
+     * are only ASKED for here (clamped to the job's record count where they are used, see load_raw) */
     auto load_batch = [&](unsigned wfirst, int jhint, int& job, int& lc, int& lo, int& hi) {
         job = -1; lc = 0; lo = 0; hi = 0;
         const unsigned wq = wfirst + (unsigned)lane;
@@ -365,16 +381,16 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             int j = jhint;
             while (j + 1 < n_jobs && wq >= (unsigned)sm.job[j + 1].work0) j++;
             job = j; lc = (int)(wq - (unsigned)sm.job[j].work0);
-            const int g = sm.job[j].chunk0 + lc, nr = sm.job[j].n_reads;
-            lo = min(__ldg(&S.k.chunk_lo[g]), nr);
-            hi = min(__ldg(&S.k.chunk_lo[g + 1]), nr);
+            const int g = sm.job[j].chunk0 + lc;
+            lo = __ldg(&S.k.chunk_lo[g]);
+            hi = __ldg(&S.k.chunk_lo[g + 1]);
         }
     };
     /* what a chunk needs from HBM, asked for one chunk ahead of use: its first 32*PASS_PRE records
      * and the GC byte of this lane's window */
-    auto prefetch = [&](int job, int lc, int lo, int hi, int (&pos)[PASS_PRE], int (&mq)[PASS_PRE], int& gcb) {
+    auto prefetch = [&](int job, int lc, int lo, int hi, uint2 (&raw)[PASS_PRE], int& gcb) {
 #pragma unroll
-        for (int u = 0; u < PASS_PRE; u++) { pos[u] = 0; mq[u] = 0; }
+        for (int u = 0; u < PASS_PRE; u++) raw[u] = make_uint2(0u, 0u);
         gcb = 0;
         if (job < 0) return;
         const pass_job& P = sm.job[job];
@@ -383,7 +399,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
 #pragma unroll
             for (int u = 0; u < PASS_PRE; u++) {
                 const int i = lo + 32 * u + lane;
-                if (i < hi) load_rec(R, i, pos[u], mq[u]);
+                if (i < hi) raw[u] = load_raw(R, i);           /* issued here, unpacked when the chunk is binned */
             }
         }
         const int base = lc << CG_CHUNK_SHIFT, w0 = base / 100;
@@ -403,8 +419,12 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
     int b_job, b_lc, b_lo, b_hi;
     load_batch(wcur, 0, b_job, b_lc, b_lo, b_hi);
     int n_job = -1, n_lc = 0, n_lo = 0, n_hi = 0;
-    int p_pos[PASS_PRE], p_mq[PASS_PRE], p_gc;
-    prefetch(__shfl_sync(FULL, b_job, 0), __shfl_sync(FULL, b_lc, 0), __shfl_sync(FULL, b_lo, 0), __shfl_sync(FULL, b_hi, 0), p_pos, p_mq, p_gc);
+    uint2 p_raw[PASS_PRE];
+    int p_gc;
+    {
+        const int j0 = __shfl_sync(FULL, b_job, 0), nr0 = j0 >= 0 ? sm.job[j0].n_reads : 0;
+        prefetch(j0, __shfl_sync(FULL, b_lc, 0), max(0, min(__shfl_sync(FULL, b_lo, 0), nr0)), max(0, min(__shfl_sync(FULL, b_hi, 0), nr0)), p_raw, p_gc);
+    }
     int q = 0;
 
     while (wcur < n_work) {
@@ -414,14 +434,17 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             load_batch(wnext, max(0, __shfl_sync(FULL, b_job, 0)), n_job, n_lc, n_lo, n_hi);
         }
         const int cjob = __shfl_sync(FULL, b_job, q), clc = __shfl_sync(FULL, b_lc, q);
-        const int lo = __shfl_sync(FULL, b_lo, q), hi = __shfl_sync(FULL, b_hi, q);
+        const int c_nr = cjob >= 0 ? sm.job[cjob].n_reads : 0;
+        const int lo = max(0, min(__shfl_sync(FULL, b_lo, q), c_nr)), hi = max(0, min(__shfl_sync(FULL, b_hi, q), c_nr));
         /* the chunk after this one: the next of the batch, or the first of the next batch */
         const bool last = q == PASS_BATCH - 1;
         const int xs = last ? 0 : q + 1;
         const int xjob = __shfl_sync(FULL, last ? n_job : b_job, xs), xlc = __shfl_sync(FULL, last ? n_lc : b_lc, xs);
-        const int xlo = __shfl_sync(FULL, last ? n_lo : b_lo, xs), xhi = __shfl_sync(FULL, last ? n_hi : b_hi, xs);
-        int x_pos[PASS_PRE], x_mq[PASS_PRE], x_gc;
-        prefetch(xjob, xlc, xlo, xhi, x_pos, x_mq, x_gc);
+        const int x_nr = xjob >= 0 ? sm.job[xjob].n_reads : 0;
+        const int xlo = max(0, min(__shfl_sync(FULL, last ? n_lo : b_lo, xs), x_nr)), xhi = max(0, min(__shfl_sync(FULL, last ? n_hi : b_hi, xs), x_nr));
+        uint2 x_raw[PASS_PRE];
+        int x_gc;
+        prefetch(xjob, xlc, xlo, xhi, x_raw, x_gc);
 
         if (cjob >= 0) {
             const pass_job& P = sm.job[cjob];
@@ -439,23 +462,27 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
             if (!P.unsorted) {
                 const rec_src R = P.R;
-                int c_pos[PASS_PRE], c_mq[PASS_PRE];
+                const bool aos = R.aos != nullptr;
+                uint2 c_raw[PASS_PRE];
 #pragma unroll
-                for (int u = 0; u < PASS_PRE; u++) { c_pos[u] = p_pos[u]; c_mq[u] = p_mq[u]; }
+                for (int u = 0; u < PASS_PRE; u++) c_raw[u] = p_raw[u];
                 for (int i0 = lo; i0 < hi; i0 += 32 * PASS_PRE) {
-                    int f_pos[PASS_PRE], f_mq[PASS_PRE];          /* the group after this one */
+                    uint2 f_raw[PASS_PRE];                        /* the group after this one */
 #pragma unroll
                     for (int u = 0; u < PASS_PRE; u++) {
-                        f_pos[u] = 0; f_mq[u] = 0;
+                        f_raw[u] = make_uint2(0u, 0u);
                         const int i = i0 + 32 * (PASS_PRE + u) + lane;
-                        if (i < hi) load_rec(R, i, f_pos[u], f_mq[u]);
+                        if (i < hi) f_raw[u] = load_raw(R, i);
                     }
 #pragma unroll
                     for (int u = 0; u < PASS_PRE; u++)
-                        if (i0 + 32 * u < hi)
-                            bin32(i0 + 32 * u + lane < hi, c_pos[u], c_mq[u], base, w0, mq, chrom_len, bins, wend, lane, big);
+                        if (i0 + 32 * u < hi) {
+                            int r_pos, r_mq;
+                            unpack_raw(aos, c_raw[u], r_pos, r_mq);
+                            bin32(i0 + 32 * u + lane < hi, r_pos, r_mq, base, w0, mq, chrom_len, bins, wend, lane, big);
+                        }
 #pragma unroll
-                    for (int u = 0; u < PASS_PRE; u++) { c_pos[u] = f_pos[u]; c_mq[u] = f_mq[u]; }
+                    for (int u = 0; u < PASS_PRE; u++) c_raw[u] = f_raw[u];
                 }
             } else {
                 uint4* src = reinterpret_cast<uint4*>(S.depth32 + gpos);
@@ -566,7 +593,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
         }
 
 #pragma unroll
-        for (int u = 0; u < PASS_PRE; u++) { p_pos[u] = x_pos[u]; p_mq[u] = x_mq[u]; }
+        for (int u = 0; u < PASS_PRE; u++) p_raw[u] = x_raw[u];
         p_gc = x_gc;
         if (++q == PASS_BATCH) {
             q = 0;
@@ -592,9 +619,15 @@ static int pass_ctas_per_sm(void)
     return ctas_per_sm;
 }
 
-int cgk_pass_grid(int n_work, int n_sms)
+int cgk_pass_grid(int n_work, long long n_records, int n_sms)
 {
-    int grid = n_sms * pass_ctas_per_sm();
+    /* Three CTAs per SM.  Alone, a sparse record stream (C2: 3 per chunk) is a pure write stream and runs faster with
+     * two (1.00 against 1.14 ms per sample, r02d) — but in the pipeline of samples two CTAs leave so much of the SM to
+     * the neighbours' record sweep and genotype kernel that their traffic breaks the write stream (1.47 ms per step
+     * against 1.09); the dense stream (C3: 29 per chunk) needs the third CTA for its record loads either way. */
+    (void)n_records;
+    int per_sm = pass_ctas_per_sm();
+    int grid = n_sms * per_sm;
     const int want = (n_work + NWARP * PASS_BATCH - 1) / (NWARP * PASS_BATCH);
     if (grid > want) grid = want;
     return grid < 1 ? 1 : grid;
@@ -615,23 +648,28 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1
  * its supers, CTA (j, 0) also writes the row. */
 #define FIN_Y 4
 #define FIN_T 1024
-#define FIN_PARTS (FIN_T / 256)       /* slices of the pass's CTAs summed side by side: 4 x 256 threads, 202 of each busy */
+#define FIN_PARTS (FIN_T / 256)       /* slices of a CTA's share of the pass's CTAs summed side by side */
 __global__ void __launch_bounds__(FIN_T)
 k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
-    const cg_dev_job& J = S.jobs ? S.jobs[blockIdx.x] : J1;
+    const int j = blockIdx.x;
+    const cg_dev_job& J = S.jobs ? S.jobs[j] : J1;
     __shared__ long long part[FIN_PARTS][CG_PART_WORDS];
     __shared__ long long row[CG_STATS_WORDS];
+    __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    /* ---- depth sums per group of 32 chunks and per super of 32 groups, from the chunk level the pass wrote ---- */
+    /* ---- depth sums per group of 32 chunks and per super of 32 groups, from the chunk level the pass wrote
+     *      (chunks behind the chromosome's last one count as zero: nobody ever writes them) ---- */
     {
         const int s0 = J.chunk0 >> (2 * LVL), s1 = (J.chunk0 + J.n_chunks + CG_SUPER_CHUNKS - 1) >> (2 * LVL);
+        const int c_end = J.chunk0 + J.n_chunks;
         for (int sp = s0 + (int)blockIdx.y * (FIN_T / 32) + warp; sp < s1; sp += (FIN_T / 32) * FIN_Y) {
-            const int32_t* c1 = S.k.cnt1 + ((size_t)sp << (2 * LVL));
+            const int cb = sp << (2 * LVL);
+            const int32_t* c1 = S.k.cnt1 + cb;
             int v[32];
 #pragma unroll
-            for (int g = 0; g < 32; g++) v[g] = c1[(g << LVL) + lane];       /* 32 independent coalesced loads */
+            for (int g = 0; g < 32; g++) { const int ci = (g << LVL) + lane; v[g] = cb + ci < c_end ? c1[ci] : 0; }   /* 32 independent coalesced loads */
             int mine = 0;                                     /* lane g ends up with the sum of group g */
 #pragma unroll
             for (int g = 0; g < 32; g++) {
@@ -643,21 +681,22 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             if (lane == 0) S.k.cnt3[sp] = tot;
         }
     }
-    if (blockIdx.y != 0) return;
 
-    /* ---- the statistics row: word w of every CTA's partial row, FIN_PARTS slices of the CTAs at a time ---- */
+    /* ---- the statistics row: CTA (j, y) adds word w of every FIN_Y-th pass CTA's partial row into the job's scratch
+     *      row (zero at rest); the last of the job's CTAs to arrive finishes the row ---- */
+    long long* acc = S.fin_acc + (size_t)j * 256;
     {
         const int w = tid & 255, sl = tid >> 8;
         if (w < CG_PART_WORDS) {
-            const int32_t* p = S.partial + (size_t)blockIdx.x * CG_PART_WORDS + w;
+            const int32_t* p = S.partial + (size_t)j * CG_PART_WORDS + w;
             const size_t stride = (size_t)S.n_jobs * CG_PART_WORDS;
             long long s = 0;
             if (w < CG_GC_BINS) {
 #pragma unroll 8
-                for (int c = sl; c < S.n_pass_ctas; c += FIN_PARTS) s += (long long)p[c * stride];
+                for (int c = (int)blockIdx.y + FIN_Y * sl; c < S.n_pass_ctas; c += FIN_Y * FIN_PARTS) s += (long long)p[c * stride];
             } else {
 #pragma unroll 8
-                for (int c = sl; c < S.n_pass_ctas; c += FIN_PARTS) s += (long long)(unsigned)p[c * stride];
+                for (int c = (int)blockIdx.y + FIN_Y * sl; c < S.n_pass_ctas; c += FIN_Y * FIN_PARTS) s += (long long)(unsigned)p[c * stride];
             }
             part[sl][w] = s;
         }
@@ -667,8 +706,16 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         long long s = 0;
 #pragma unroll
         for (int k = 0; k < FIN_PARTS; k++) s += part[k][tid];
-        row[tid] = s;
+        if (s) atomicAdd(reinterpret_cast<unsigned long long*>(acc + tid), (unsigned long long)s);
     }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(&S.fin_cnt[j], 1u) == FIN_Y - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (tid < CG_PART_WORDS) { row[tid] = __ldcg(acc + tid); acc[tid] = 0; }        /* scratch row zero at rest again */
+    if (tid == 0) S.fin_cnt[j] = 0u;
     __syncthreads();
     if (warp == 0) {
         /* calc_mu_per_chr, read_distribution.c:33-37: the sum of every depth = the sum over the GC bins, each
@@ -691,8 +738,13 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
     if (tid == 0) {
         const unsigned fl = J.ctl[CG_W_FLAGS];
         if (fl & CG_FLAG_RANGE) atomicOr(S.sticky, CG_FLAG_RANGE);
-        if (S.h_flags) S.h_flags[blockIdx.x] = fl;
+        if (S.h_flags) S.h_flags[j] = fl;
     }
+    __syncthreads();
+    /* zero at rest: this job's control words, and (once per submission) the slot's work counters — the record sweep
+     * and the pass that used them are behind this kernel in stream order */
+    if (tid < CG_CTL_WORDS) J.ctl[tid] = 0u;
+    if (j == 0 && tid < 4) S.sctl[tid] = 0u;
 }
 
 cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
@@ -722,7 +774,6 @@ cudaError_t cgk_configure_depth(void)
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem_bytes(CG_JMAX))) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_job_init, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_mark, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_rare_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_finalize, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;

@@ -282,6 +282,33 @@ __device__ __forceinline__ unsigned load_gc4(const int8_t* __restrict__ gc, int 
 
 __device__ __forceinline__ cg_cnv make_cnv(int a, int b) { cg_cnv v; v.start = a; v.end = b; return v; }
 
+/* Sum of depth[s, e) by one warp straight from the depth array: for a CNV of a few thousand positions this is one
+ * round of independent 16-byte loads (<= GENO_DIRECT/256 + 1 per lane) instead of two endpoint sums with three
+ * count levels each.  Positions outside [s, e) inside the first and last vector are masked out. */
+#define GENO_DIRECT 8192
+__device__ __forceinline__ int depth_sum_direct(const int16_t* __restrict__ depth, int s, int e, int lane)
+{
+    const int v0 = s >> 3, v1 = (e + 7) >> 3;                       /* vectors of eight positions */
+    const uint4* row = reinterpret_cast<const uint4*>(depth);
+    int part = 0;
+    for (int q = v0 + lane; q < v1; q += 32) {
+        uint4 v = __ldg(row + q);
+        const int first = q << 3;
+        if (first < s || first + 8 > e) {
+            unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int p0 = first + 2 * j, p1 = p0 + 1;
+                const unsigned keep = ((p0 >= s && p0 < e) ? 0xffffu : 0u) | ((p1 >= s && p1 < e) ? 0xffff0000u : 0u);
+                w[j] &= keep;
+            }
+            v = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        part = __dp2a_lo((int)v.w, 0x0101, __dp2a_lo((int)v.z, 0x0101, __dp2a_lo((int)v.y, 0x0101, __dp2a_lo((int)v.x, 0x0101, part))));
+    }
+    return __reduce_add_sync(FULL, part);
+}
+
 /* ---- G CNVs per warp ---------------------------------------------------------
  * The work per CNV is irregular (a few windows to several thousand) and the exact fp32 chain
  * has a serial, branchy ramp-up: while E is small every addition changes its exponent.  A warp
@@ -381,12 +408,21 @@ __device__ __forceinline__ int depth_sum_before(const int16_t* __restrict__ dept
  * cnv0 prefix (in groups).  With one launch per chromosome (round 1) one CNV per warp was best: the launches were
  * small and latency-bound.  One launch per sample carries 15-40 k CNVs and is bound by issue slots instead (r02b,
  * G = 1: 1.9 IPC at 9.8 active threads per warp, every short CNV a serial walk on a single lane). */
-#ifndef GENO_G
-#define GENO_G 8
-#endif
-int cgk_geno_groups(unsigned long long n_cnv) { return (int)((n_cnv + GENO_G - 1) / GENO_G); }
+#define GENO_G_MAX 8
+/* CNVs per warp for a launch over n CNVs: one per warp while the warps fit the GPU at once (48 per SM) — then the
+ * launch lasts as long as its longest CNV — and up to GENO_G_MAX when there are more (then lane efficiency counts) */
+int cgk_geno_g(unsigned long long n_cnv, int n_sms)
+{
+    static int forced = -1;
+    if (forced < 0) { const char* e = getenv("CG_GENO_G"); forced = e ? atoi(e) : 0; }     /* tuning only */
+    if (forced >= 1 && forced <= 32) return forced;
+    const unsigned long long cap = (unsigned long long)n_sms * 48;
+    unsigned long long g = (n_cnv + cap - 1) / cap;
+    return g < 1 ? 1 : g > GENO_G_MAX ? GENO_G_MAX : (int)g;
+}
+int cgk_geno_groups(unsigned long long n_cnv, int g) { return (int)((n_cnv + (unsigned)g - 1) / (unsigned)g); }
 
-__global__ void __launch_bounds__(GENO_WARPS * 32)
+__global__ void __launch_bounds__(GENO_WARPS * 32, 8)
 k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
 {
     const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
@@ -395,7 +431,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
     for (int i = threadIdx.x; i <= 2 * S.n_jobs; i += blockDim.x)
         s_seg0[i] = i < 2 * S.n_jobs ? jobs[i >> 1].cnv0[i & 1] : S.n_cnv;
     __syncthreads();
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, G = S.geno_g;
     unsigned* s_expb = s_expb_all[threadIdx.x >> 5];
     const int n_warps = gridDim.x * GENO_WARPS;
     int seg = 0, cur_job = -1, cur_seg = -1;
@@ -427,8 +463,8 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             cur_seg = seg;
         }
         /* ---- phase 0: lane = CNV ---- */
-        const int c = (gi - s_seg0[seg]) * GENO_G + lane;
-        const bool valid = lane < GENO_G && c < n_seg;
+        const int c = (gi - s_seg0[seg]) * G + lane;
+        const bool valid = lane < G && c < n_seg;
         cg_cnv v = make_cnv(0, 0);
         if (valid) v = cnvs[c];
         int s = v.start, e = v.end;
@@ -438,7 +474,9 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         for (unsigned todo = __ballot_sync(FULL, any); todo; todo &= todo - 1) {
             const int L = __ffs(todo) - 1;
             const int cs = __shfl_sync(FULL, s, L), ce = __shfl_sync(FULL, e, L);
-            const int d = depth_sum_before(depth, counts, chunk0, ce, lane) - depth_sum_before(depth, counts, chunk0, cs, lane);
+            int d;
+            if (ce - cs <= GENO_DIRECT) d = depth_sum_direct(depth, cs, ce, lane);
+            else d = depth_sum_before(depth, counts, chunk0, ce, lane) - depth_sum_before(depth, counts, chunk0, cs, lane);
             if (lane == L) obs = d;
         }
         const int w_last = any ? (e - 1) / 100 : -1;
