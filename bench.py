@@ -199,6 +199,11 @@ def own_arm(args):
     n_chrom, S = len(wl.chroms), wl.n_samples
     parts = multi.lpt_partition([c.length for c in wl.chroms], world)
     mine = [wl.chroms[i] for i in parts[rank]]
+    if args.emulate_rank and world == 1:
+        # tuning only: rank R's share of an N-rank job alone on one GPU (no collective) -- what one rank of the
+        # scaling run executes per step, measurable without holding N GPUs
+        r_, n_ = (int(x) for x in args.emulate_rank.split("/"))
+        mine = [wl.chroms[i] for i in multi.lpt_partition([c.length for c in wl.chroms], n_)[r_]]
     has_map, mq = wl.has_mappability, wl.mq_threshold
 
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
@@ -397,7 +402,8 @@ def own_arm(args):
                 assert int(ctx.stats_row(c.index)["window_per_gc"].sum()) == c.length, "statistics row %d wrong after the all-reduce" % c.index
         parity["allreduced_rows_on_every_rank"] = True
     # (3) the N-rank calls, gathered in SONIC order, against ONE GPU running the whole sample alone (rank 0)
-    gathered = multi.gather_calls(dev_calls, n_chrom, group=cpu_group) if world > 1 else [dev_calls[i] for i in range(n_chrom)]
+    empty_calls = (np.zeros(0, dtype=CALL_DT), np.zeros(0, dtype=CALL_DT))
+    gathered = multi.gather_calls(dev_calls, n_chrom, group=cpu_group) if world > 1 else [dev_calls.get(i, empty_calls) for i in range(n_chrom)]
     if rank == 0:
         digest = calls_digest(gathered)
         parity["calls_sha256_16"] = digest
@@ -662,6 +668,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (debugging only; 1.0 = the named config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--emulate-rank", default="", help="R/N: run rank R's share of an N-rank partition alone on one GPU (tuning only)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -1032,32 +1032,34 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         CU(c, cgk_depth_pass(s.s_work, s.sub, J0));
     }
     CU(c, cudaEventRecord(s.ev_passk, s.s_work));
-    if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(s.s_work, c->ev_bank_read[c->bank], 0));
-    {
-        prof_scope ps(c, s.s_work, 0, 1);
-        CU(c, cgk_finalize(s.s_work, s.sub, J0));
-    }
-    CU(c, cudaEventRecord(s.ev_pass, s.s_work));
     s.dirty_work = true;
     s.check = true;
 
-    if (n_cnv) {
-        cudaStream_t st = s.s_geno[0];
-        CU(c, cudaStreamWaitEvent(st, s.ev_table, 0));
-        if (any_runs) {
-            if (host) CU(c, cudaStreamWaitEvent(st, s.ev_copy, 0));
-            prof_scope ps(c, st, 2, 1);
-            CU(c, cgk_run_index(st, s.sub, J0));
-        }
-        CU(c, cudaStreamWaitEvent(st, s.ev_pass, 0));
-        {
-            prof_scope ps(c, st, 2, 1);
-            CU(c, cgk_genotype(st, s.sub, J0, c->n_sms));
-        }
-        CU(c, cudaEventRecord(s.ev_geno[0], st));
-        s.geno_queued[0] = true;
-        s.dirty_geno[0] = true;
+    /* finalize, mappability index and genotype kernel on the slot's high-priority stream: when the pass ends, the pass
+     * of the next submission (chained on ev_passk, low priority) and this finalize become runnable together, and the
+     * small kernel should be placed first */
+    cudaStream_t st = s.s_geno[0];
+    CU(c, cudaStreamWaitEvent(st, s.ev_table, 0));
+    if (n_cnv && any_runs) {
+        if (host) CU(c, cudaStreamWaitEvent(st, s.ev_copy, 0));
+        prof_scope ps(c, st, 2, 1);
+        CU(c, cgk_run_index(st, s.sub, J0));
     }
+    CU(c, cudaStreamWaitEvent(st, s.ev_passk, 0));
+    /* a collective that still reads this bank must be through before the rows are rewritten */
+    if (c->bank_read[c->bank]) CU(c, cudaStreamWaitEvent(st, c->ev_bank_read[c->bank], 0));
+    {
+        prof_scope ps(c, st, 0, 1);
+        CU(c, cgk_finalize(st, s.sub, J0));
+    }
+    CU(c, cudaEventRecord(s.ev_pass, st));
+    if (n_cnv) {
+        prof_scope ps(c, st, 2, 1);
+        CU(c, cgk_genotype(st, s.sub, J0, c->n_sms));
+    }
+    CU(c, cudaEventRecord(s.ev_geno[0], st));
+    s.geno_queued[0] = true;
+    s.dirty_geno[0] = true;
     c->in_chrom = false; c->finished = false;       /* no current chromosome: the per-chromosome calls need a cg_chrom_begin */
     return CG_OK;
 }

@@ -646,8 +646,10 @@ cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1
  * expected table (:75-83), the chromosome's flags; and the group / super levels of the depth sums from the
  * chunk level (what depth_sum_before in genotype.cu reads).  grid = (jobs, FIN_Y): the CTAs of a job share
  * its supers, CTA (j, 0) also writes the row. */
-#define FIN_Y 4
-#define FIN_T 1024
+/* 16 CTAs of 256 threads per job rather than a few large ones: a CTA of this size fits beside three CTAs of the pass
+ * on an SM, so the finalize of submission k does not have to wait for a gap in the pass of submission k+1 */
+#define FIN_Y 16
+#define FIN_T 256
 #define FIN_PARTS (FIN_T / 256)       /* slices of a CTA's share of the pass's CTAs summed side by side */
 __global__ void __launch_bounds__(FIN_T)
 k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
