@@ -259,7 +259,9 @@ int cg_run_chromosomes(cg_ctx* ctx, const cg_chrom_job* jobs, size_t n_jobs);
  * [100w - 1, 100w + 99) (window 0: [0, 99) — char_count starts at 1, :82), the value the builder writes
  * as (char)(100.0 * gc / 100) (:96) and sonic_read_gc_profile (:139-159) hands to CONGA.  n_windows: capacity
  * of out_gc.  Pointers follow the pointer mode; in HOST mode the call blocks, in DEVICE mode it is queued
- * on cg_stream.  Needs no chromosome to be open. */
+ * on cg_stream.  Needs no chromosome to be open.  DEVICE mode: the kernel's bulk copies start at `bases` rounded
+ * down to 16 bytes and end at `bases + n_bases` rounded up, so the buffer needs up to 15 addressable bytes on either
+ * side (any cudaMalloc block has them; a pointer at the very end of a mapping has not). */
 int cg_gc_profile(cg_ctx* ctx, const char* bases, int64_t n_bases, int8_t* out_gc, int32_t n_windows);
 
 /* Wait for everything queued on the context (all of its streams).  In HOST pointer mode it
