@@ -92,6 +92,7 @@ SYMBOLS = {
     "cg_comm_init_all": (_I, [C.POINTER(_P), _I]),
     "cg_comm_destroy": (_I, [_P]),
     "cg_stats_allreduce": (_I, [_P, C.c_int32]),
+    "cg_stats_allreduce_all": (_I, [C.POINTER(_P), _I, C.c_int32]),
     "cg_set_profiling": (_I, [_P, _I]),
     "cg_kernel_times": (_I, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cg_launch_count": (C.c_int64, [_P]),

@@ -1320,7 +1320,7 @@ int cg_comm_destroy(cg_ctx* c)
     return CG_OK;
 }
 
-int cg_stats_allreduce(cg_ctx* c, int32_t n_rows)
+static int allreduce_one(cg_ctx* c, int32_t n_rows)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
     if (!c->comm) return fail(c, CG_EINVAL, "cg_stats_allreduce without a communicator (cg_comm_init_rank)");
@@ -1338,6 +1338,20 @@ int cg_stats_allreduce(cg_ctx* c, int32_t n_rows)
     c->bank_read[c->bank] = true;
     c->launch_count += 1;
     return CG_OK;
+}
+
+int cg_stats_allreduce(cg_ctx* c, int32_t n_rows) { return allreduce_one(c, n_rows); }
+
+int cg_stats_allreduce_all(cg_ctx** ctxs, int n, int32_t n_rows)
+{
+    if (!ctxs || n < 1) return fail(nullptr, CG_EINVAL, "bad argument");
+    int rc = nccl_load(ctxs[0]);
+    if (rc) return rc;
+    g_nccl.GroupStart();                       /* one thread issuing for several communicators */
+    for (int i = 0; i < n && rc == CG_OK; i++) rc = allreduce_one(ctxs[i], n_rows);
+    const int e = g_nccl.GroupEnd();
+    if (rc == CG_OK && e) rc = fail(ctxs[0], CG_ECUDA, "ncclGroupEnd: %s", g_nccl.GetErrorString(e));
+    return rc;
 }
 
 /* ---- split reads (--rp) ----------------------------------------------------------------- */

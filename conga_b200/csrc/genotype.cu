@@ -235,9 +235,101 @@ __device__ __forceinline__ int c_double_to_int(double x)
 __device__ __forceinline__ bool near_integer(double x)
 {
     const double a = fabs(x), d = fabs(a - rint(a));
-    return d <= 1e-7 * fmax(1.0, a);
+    return d <= 1e-9 * fmax(1.0, a);
 }
 
+
+/* ---- double-double evaluation of a Poisson log-likelihood, for the decisions only ----------------
+ * likelihood.c takes discontinuous decisions on the three likelihoods: `(int)lhomo`, `(int)lhetero` inside the
+ * int-truncating max (:138, :160, common.c:262-268) and `lhomo > lhetero` (:164).  The device's fp64 log / lgamma
+ * and glibc's agree to ~1e-13 relative, which is enough for every printed digit unless a likelihood sits on an
+ * integer, or the two on each other, closer than that.  A CNV whose likelihoods come within 1e-9 relative of such a
+ * boundary (margin_flags) has the three of them evaluated again here in double-double arithmetic (~31 significant
+ * digits): k*log(lambda) - lambda - log(k!), log by atanh series after exact range reduction, log(k!) by
+ * Stirling's series above 40 with an exact shift below it.  The truncation and the comparison then follow the
+ * real-number values; no libm, neither CUDA's nor glibc's, decides.  (If the real value lies within glibc's own
+ * rounding error of the boundary, the reference's answer is a property of its libm build, not of its algorithm.) */
+struct dd { double hi, lo; };
+__device__ __forceinline__ dd dd_quick(double a, double b) { const double s = a + b; dd r; r.hi = s; r.lo = b - (s - a); return r; }
+__device__ __forceinline__ dd dd_two_sum(double a, double b) { const double s = a + b, bb = s - a; dd r; r.hi = s; r.lo = (a - (s - bb)) + (b - bb); return r; }
+__device__ __forceinline__ dd dd_two_prod(double a, double b) { const double p = a * b; dd r; r.hi = p; r.lo = __fma_rn(a, b, -p); return r; }
+__device__ __forceinline__ dd dd_add(dd x, dd y) { dd s = dd_two_sum(x.hi, y.hi); s.lo += x.lo + y.lo; return dd_quick(s.hi, s.lo); }
+__device__ __forceinline__ dd dd_neg(dd x) { dd r; r.hi = -x.hi; r.lo = -x.lo; return r; }
+__device__ __forceinline__ dd dd_sub(dd x, dd y) { return dd_add(x, dd_neg(y)); }
+__device__ __forceinline__ dd dd_mul(dd x, dd y) { dd p = dd_two_prod(x.hi, y.hi); p.lo += x.hi * y.lo + x.lo * y.hi; return dd_quick(p.hi, p.lo); }
+__device__ __forceinline__ dd dd_from(double a) { dd r; r.hi = a; r.lo = 0.0; return r; }
+__device__ __forceinline__ dd dd_div(dd x, dd y)
+{
+    const double q1 = x.hi / y.hi;
+    dd r = dd_sub(x, dd_mul(y, dd_from(q1)));
+    const double q2 = r.hi / y.hi;
+    r = dd_sub(r, dd_mul(y, dd_from(q2)));
+    const double q3 = r.hi / y.hi;
+    dd q = dd_quick(q1, q2);
+    return dd_add(q, dd_from(q3));
+}
+
+/* log(x) for a finite double x > 0 */
+__device__ __noinline__ dd dd_log(double x)
+{
+    int e;
+    double m = frexp(x, &e);                          /* x = m * 2^e, m in [0.5, 1) */
+    if (m < 0.70710678118654752) { m *= 2.0; e -= 1; }            /* m in [sqrt(1/2), sqrt(2)): exact */
+    const dd num = dd_from(m - 1.0);                  /* exact for m in [0.5, 2] */
+    const dd den = dd_two_sum(m, 1.0);
+    const dd t = dd_div(num, den);                    /* |t| <= 0.1716 */
+    const dd t2 = dd_mul(t, t);
+    dd sum = dd_div(dd_from(1.0), dd_from(47.0));     /* sum_k t^(2k) / (2k+1), k = 23 .. 0: (0.0295)^24 < 2e-37 */
+    for (int k = 22; k >= 0; k--) sum = dd_add(dd_mul(sum, t2), dd_div(dd_from(1.0), dd_from((double)(2 * k + 1))));
+    dd lm = dd_mul(t, sum);
+    lm.hi *= 2.0; lm.lo *= 2.0;
+    dd ln2; ln2.hi = 0x1.62e42fefa39efp-1; ln2.lo = 0x1.abc9e3b39803fp-56;
+    return dd_add(dd_mul(ln2, dd_from((double)e)), lm);
+}
+
+/* log(k!) = lgamma(k + 1) for an integer k >= 0 */
+__device__ __noinline__ dd dd_log_factorial(int k)
+{
+    if (k <= 1) return dd_from(0.0);
+    double z = (double)k + 1.0;                       /* lgamma's argument */
+    dd prod = dd_from(1.0);                           /* lgamma(z) = lgamma(z + m) - log(z (z+1) ... (z+m-1)) */
+    while (z < 40.0) { prod = dd_mul(prod, dd_from(z)); z += 1.0; }
+    const dd lz = dd_log(z);
+    const dd zi = dd_div(dd_from(1.0), dd_from(z)), zi2 = dd_mul(zi, zi);
+    /* B_2n / (2n (2n-1)), n = 10 .. 1, as exact integer ratios; the first omitted term is below 4e-33 for z >= 40 */
+    const double cn[10] = {1.0, -1.0, 1.0, -1.0, 1.0, -691.0, 1.0, -3617.0, 43867.0, -174611.0};
+    const double cd[10] = {12.0, 360.0, 1260.0, 1680.0, 1188.0, 360360.0, 156.0, 122400.0, 244188.0, 125400.0};
+    dd ser = dd_from(0.0);
+    for (int n = 9; n >= 0; n--) ser = dd_add(dd_mul(ser, zi2), dd_div(dd_from(cn[n]), dd_from(cd[n])));
+    ser = dd_mul(ser, zi);
+    dd hl2pi; hl2pi.hi = 0x1.d67f1c864beb5p-1; hl2pi.lo = -0x1.65b5a1b7ff5dfp-55;
+    dd r = dd_mul(dd_sub(dd_from(z), dd_from(0.5)), lz);
+    r = dd_add(dd_sub(r, dd_from(z)), dd_add(hl2pi, ser));
+    if (prod.hi != 1.0) {
+        dd lp = dd_log(prod.hi);                      /* log(hi + lo) = log(hi) + lo/hi - ...: (lo/hi)^2 < 2e-32 */
+        lp = dd_add(lp, dd_from(prod.lo / prod.hi));
+        r = dd_sub(r, lp);
+    }
+    return r;
+}
+
+/* lpoisson (likelihood.c:96-105) in double-double; lambda is an exact double (0 already replaced by 0.01) */
+__device__ __noinline__ dd dd_lpoisson(int k, double lambda, dd logfact)
+{
+    return dd_sub(dd_sub(dd_mul(dd_log(lambda), dd_from((double)k)), dd_from(lambda)), logfact);
+}
+
+/* (int)x of the real number x = hi + lo as C truncates a double that holds it: toward zero; out of int range as cvttsd2si */
+__device__ __forceinline__ int dd_trunc_to_int(dd x)
+{
+    if (!(x.hi > -2147483649.0 && x.hi < 2147483648.0)) return (int)0x80000000;
+    double t = trunc(x.hi);
+    if (t == x.hi) {                                  /* hi is an integer: lo decides on which side the value lies */
+        if (x.hi > 0.0 && x.lo < 0.0) t -= 1.0;
+        else if (x.hi < 0.0 && x.lo > 0.0) t += 1.0;
+    }
+    return __double2int_rz(t);
+}
 
 /* fp64 twin of step_delta_f32: significand increment of one rounded addition of v while the
  * running sum has biased exponent e. */
@@ -647,7 +739,19 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             const double lhomo = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_homo)), lam_homo), lg);
             const double lhetero = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_het)), lam_het), lg);
             const double lnone = __dsub_rn(__dsub_rn(__dmul_rn(k, log(lam_none)), lam_none), lg);
-            const int ih = c_double_to_int(lhomo), it = c_double_to_int(lhetero);
+            int ih = c_double_to_int(lhomo), it = c_double_to_int(lhetero);
+            bool homo_gt_het = lhomo > lhetero;
+            /* a decision within 1e-9 relative of its boundary is taken from the double-double values (see dd_lpoisson);
+             * bit-identical likelihoods (E = 0: all three lambdas are 0.01) are equal in any arithmetic */
+            unsigned mf = 0;
+            if (near_integer(lhomo) || near_integer(lhetero)) mf |= 1u;
+            if (lhomo != lhetero && fabs(lhomo - lhetero) <= 1e-9 * fmax(fabs(lhomo), fabs(lhetero))) mf |= 2u;
+            if (mf) {
+                const dd lf = dd_log_factorial(obs);
+                const dd h = dd_lpoisson(obs, lam_homo, lf), t = dd_lpoisson(obs, lam_het, lf);
+                ih = dd_trunc_to_int(h); it = dd_trunc_to_int(t);
+                homo_gt_het = lam_homo == lam_het ? false : (h.hi > t.hi || (h.hi == t.hi && h.lo > t.lo));
+            }
             cg_call o;
             o.observed = obs;
             o.expected = E;
@@ -655,10 +759,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             o.lhomo = lhomo; o.lhetero = lhetero; o.lnone = lnone;
             o.score = (double)(ih < it ? it : ih) / lnone;                         /* :138 / :160 */
             if (!is_dup) o.copy_number = (__int2float_rn(obs) < __fdiv_rn(E, 4.0f)) ? 2 : 1;   /* :146-149 */
-            else         o.copy_number = (lhomo > lhetero) ? 2 : 1;                           /* :164-167 */
-            unsigned mf = 0;
-            if (near_integer(lhomo) || near_integer(lhetero)) mf |= 1u;
-            if (fabs(lhomo - lhetero) <= 1e-7 * fmax(fabs(lhomo), fabs(lhetero))) mf |= 2u;
+            else         o.copy_number = homo_gt_het ? 2 : 1;                                 /* :164-167 */
             o.margin_flags = mf;
             out[c] = o;
         }

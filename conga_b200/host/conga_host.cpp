@@ -58,7 +58,6 @@
 #include "sonic.h"
 
 #include <cuda_runtime.h>
-#include <nccl.h>
 
 #include "conga_gpu.h"
 
@@ -718,7 +717,6 @@ struct Gpus {
     int first_dev = 0;
     std::vector<cg_ctx*> ctx;
     std::vector<std::thread> threads;
-    std::vector<ncclComm_t> comms;
     void start()
     {
         first_dev = getenv("CONGA_GPU_DEVICE") ? atoi(getenv("CONGA_GPU_DEVICE")) : 0;
@@ -741,34 +739,22 @@ struct Gpus {
         for (cg_ctx* c : ctx)
             if (!c) die("Error: %s (conga-b200 has no CPU implementation of the genotyping path)", cg_last_error(nullptr));
     }
-    /* ncclAllReduce(int64, sum) of the statistics tables, one communicator per GPU of this process */
+    /* the path's one collective, issued by the library: ncclAllReduce(int64, sum) of the statistics tables, one
+     * communicator per GPU of this process (cg_comm_init_all on first use, kept for the following samples of a batch) */
+    bool have_comm = false;
     void allreduce(int n_rows)
     {
         const int n = (int)ctx.size();
-        ncclResult_t rc;
-        if (comms.empty()) {
-            std::vector<int> devs(n);
-            for (int g = 0; g < n; g++) devs[g] = first_dev + g;
-            comms.resize(n);
-            if ((rc = ncclCommInitAll(comms.data(), n, devs.data())) != ncclSuccess) die("Error: ncclCommInitAll: %s", ncclGetErrorString(rc));
+        if (!have_comm) {
+            if (cg_comm_init_all(ctx.data(), n) != CG_OK) die("Error: %s", cg_last_error(ctx[0]));
+            have_comm = true;
         }
-        std::vector<void*> tables(n);
-        for (int g = 0; g < n; g++) {
-            int32_t rows = 0;
-            if (cg_stats_table(ctx[g], &tables[g], &rows) != CG_OK || cg_join(ctx[g]) != CG_OK) die("Error: %s", cg_last_error(ctx[g]));
-        }
-        ncclGroupStart();
-        for (int g = 0; g < n; g++)
-            if ((rc = ncclAllReduce(tables[g], tables[g], (size_t)n_rows * 204, ncclInt64, ncclSum, comms[g], (cudaStream_t)cg_stream(ctx[g]))) != ncclSuccess)
-                die("Error: ncclAllReduce: %s", ncclGetErrorString(rc));
-        if ((rc = ncclGroupEnd()) != ncclSuccess) die("Error: ncclGroupEnd: %s", ncclGetErrorString(rc));
+        if (cg_stats_allreduce_all(ctx.data(), n, n_rows) != CG_OK) die("Error: %s", cg_last_error(ctx[0]));
         for (int g = 0; g < n; g++) if (cg_sync(ctx[g]) != CG_OK) die("Error: cg_sync: %s", cg_last_error(ctx[g]));
     }
     void shutdown()
     {
-        for (ncclComm_t c : comms) ncclCommDestroy(c);
-        comms.clear();
-        for (cg_ctx* c : ctx) cg_destroy(c);
+        for (cg_ctx* c : ctx) cg_destroy(c);                 /* destroys the context's communicator too */
         ctx.clear();
     }
 };

@@ -79,8 +79,9 @@ typedef struct cg_call {
     double   lhomo, lhetero, lnone;   /* likelihood.c:133-135 / :155-157 */
     double   score;         /* likelihood_score likelihood.c:138,160 (int-truncating max) */
     int32_t  copy_number;   /* likelihood.c:146-149 / :164-167 */
-    uint32_t margin_flags;  /* diagnostics only: bit0 (int) truncation of lhomo/lhetero within
-                               1e-7 of an integer, bit1 |lhomo-lhetero| within 1e-7 relative */
+    uint32_t margin_flags;  /* bit0: lhomo or lhetero within 1e-9 relative of an integer, bit1: of each other.  For a
+                               flagged CNV the (int) truncations in `score` and the lhomo > lhetero test in
+                               `copy_number` were taken from a double-double evaluation of the likelihoods */
 } cg_call;
 
 #define CG_GC_BINS 101
@@ -312,6 +313,8 @@ int cg_comm_init_rank(cg_ctx* ctx, int n_ranks, int rank, const void* id);
 int cg_comm_init_all(cg_ctx** ctxs, int n);
 int cg_comm_destroy(cg_ctx* ctx);
 int cg_stats_allreduce(cg_ctx* ctx, int32_t n_rows);
+/* the same for the n contexts of cg_comm_init_all, issued by one thread (inside one NCCL group) */
+int cg_stats_allreduce_all(cg_ctx** ctxs, int n, int32_t n_rows);
 
 /* Device time of this context's kernels, from CUDA events recorded on its stream
  * around every launch group while profiling is on.  cg_kernel_times waits for the
