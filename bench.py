@@ -197,13 +197,13 @@ def own_arm(args):
 
     wl = build_workload(args.workload, args.scale, args.samples)
     n_chrom, S = len(wl.chroms), wl.n_samples
-    parts = multi.lpt_partition([c.length for c in wl.chroms], world)
+    parts = multi.balanced_partition([c.length for c in wl.chroms], world)
     mine = [wl.chroms[i] for i in parts[rank]]
     if args.emulate_rank and world == 1:
         # tuning only: rank R's share of an N-rank job alone on one GPU (no collective) -- what one rank of the
         # scaling run executes per step, measurable without holding N GPUs
         r_, n_ = (int(x) for x in args.emulate_rank.split("/"))
-        mine = [wl.chroms[i] for i in multi.lpt_partition([c.length for c in wl.chroms], n_)[r_]]
+        mine = [wl.chroms[i] for i in multi.balanced_partition([c.length for c in wl.chroms], n_)[r_]]
     has_map, mq = wl.has_mappability, wl.mq_threshold
 
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
@@ -475,7 +475,7 @@ def own_arm(args):
            "config": {"workload": wl.name, "chromosomes": n_chrom, "positions": wl.n_positions, "reads": int(round(n_reads)),
                       "cnvs": n_cnvs, "mappability": has_map, "min_mapq": mq, "samples": S,
                       "l2": "inputs+outputs per step (%.1f GB) larger than L2" % (wl.algorithmic_bytes_depth_pass() / 1e9)},
-           "run": {"partition": "chromosomes over ranks, LPT by length; one submission per rank and sample", "slots": ctx_slots(ctx),
+           "run": {"partition": "chromosomes over ranks, balanced by length (LPT + seeded local search: %.4f of ideal); one submission per rank and sample" % multi.balance([c.length for c in wl.chroms], parts), "slots": ctx_slots(ctx),
                    "repeats": args.repeats, "ms_per_step_spread": spread(dev_ms), "host_issue_ms_per_step": round(issue_ms_dev / args.steps, 4),
                    "resident_record_bytes": rec_bytes},
            "cnvs_per_s": round(n_cnvs * args.steps / (ms_dev / 1e3), 1),

@@ -117,3 +117,14 @@ def test_lpt_partition_balance():
         assert sorted(sum(parts, [])) == list(range(22))
         loads = [sum(GRCH37[i] for i in p) for p in parts]
         assert sum(GRCH37) / n / max(loads) >= bound
+
+
+def test_balanced_partition_beats_lpt_and_is_deterministic():
+    from conga_b200 import multi
+    from conga_b200.synth import GRCH37
+    for n, bound in ((2, 0.9999), (4, 0.999), (8, 0.99)):
+        parts = multi.balanced_partition(GRCH37, n)
+        assert sorted(sum(parts, [])) == list(range(22))
+        assert multi.balance(GRCH37, parts) >= bound >= 0 and multi.balance(GRCH37, parts) >= multi.balance(GRCH37, multi.lpt_partition(GRCH37, n))
+        assert parts == multi.balanced_partition(list(GRCH37), n)          # every rank computes the same partition
+    assert multi.balanced_partition([5, 3], 4) == multi.lpt_partition([5, 3], 4)
