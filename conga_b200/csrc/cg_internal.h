@@ -129,10 +129,8 @@ cudaError_t cgk_genotype(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, 
 int         cgk_run_index_words(int32_t chrom_len);
 cudaError_t cgk_run_index(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 /* split_read.cu */
-size_t      cgk_sr_sort_temp_bytes(int n);
-cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, unsigned* keys_a, unsigned* keys_b, int* vals_a, int* vals_b,
-                         void* temp, size_t temp_bytes, int* lo, int* hi, int n_sms);
-cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len, const int* pos_sorted, const int* lo, const int* hi,
+cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, int* cnt, int* pos_list, int* lo, int* hi, int n_sms);
+cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len, const int* pos_list, const int* lo, const int* hi,
                           const cg_half* halves, long long n_halves, const unsigned char* bases, int chrom_len, int mq_threshold,
                           cg_splitrow* rows, unsigned* n_rows, unsigned cap, unsigned long long* n_mappings, int n_sms);
 cudaError_t cgk_sr_count(cudaStream_t s, const cg_splitrow* rows, int n_rows, const cg_cnv* dels, int n_del, const cg_cnv* dups, int n_dup,

@@ -138,11 +138,12 @@ struct cg_ctx {
     struct {
         cudaStream_t st = nullptr;
         unsigned char* d_ref = nullptr; size_t ref_cap = 0; int ref_len = 0;
-        unsigned *d_keys_a = nullptr, *d_keys_b = nullptr; int *d_vals_a = nullptr, *d_vals_b = nullptr; size_t idx_cap = 0;
-        void* d_temp = nullptr; size_t temp_cap = 0;
+        int* d_pos_list = nullptr; size_t idx_cap = 0;      /* positions grouped by k-mer value */
+        int* d_cnt = nullptr;                               /* [2^20] positions per value, then slot counters */
         int *d_lo = nullptr, *d_hi = nullptr;
-        cg_half* d_halves = nullptr; size_t halves_cap = 0;
-        unsigned char* d_bases = nullptr; size_t bases_cap = 0;
+        cg_half* d_halves[2] = {nullptr, nullptr}; size_t halves_cap[2] = {0, 0};      /* two staging sets: batch k+1 is copied while batch k is searched */
+        unsigned char* d_bases[2] = {nullptr, nullptr}; size_t bases_cap[2] = {0, 0};
+        cudaEvent_t ev_buf[2] = {nullptr, nullptr}; unsigned n_push = 0;
         cg_splitrow* d_rows = nullptr; unsigned rows_cap = 0;
         unsigned* d_n_rows = nullptr; unsigned long long* d_n_map = nullptr;     /* one 16-byte block */
         char* d_count = nullptr; size_t count_cap = 0;
@@ -370,8 +371,9 @@ void cg_destroy(cg_ctx* c)
     }
     cudaFree(c->d_stats); cudaFree(c->d_stats_all); cudaFree(c->d_sticky);
     if (c->sr.st) cudaStreamDestroy(c->sr.st);
-    cudaFree(c->sr.d_ref); cudaFree(c->sr.d_keys_a); cudaFree(c->sr.d_keys_b); cudaFree(c->sr.d_vals_a); cudaFree(c->sr.d_vals_b);
-    cudaFree(c->sr.d_temp); cudaFree(c->sr.d_lo); cudaFree(c->sr.d_hi); cudaFree(c->sr.d_halves); cudaFree(c->sr.d_bases);
+    cudaFree(c->sr.d_ref); cudaFree(c->sr.d_pos_list); cudaFree(c->sr.d_cnt);
+    cudaFree(c->sr.d_lo); cudaFree(c->sr.d_hi);
+    for (int b = 0; b < 2; b++) { cudaFree(c->sr.d_halves[b]); cudaFree(c->sr.d_bases[b]); if (c->sr.ev_buf[b]) cudaEventDestroy(c->sr.ev_buf[b]); }
     cudaFree(c->sr.d_rows); cudaFree(c->sr.d_n_rows); cudaFree(c->sr.d_count);
     cudaFree(c->d_gc_bases); cudaFree(c->d_gc_out);
     if (c->h_stats) cudaFreeHost(c->h_stats);
@@ -1376,28 +1378,20 @@ int cg_sr_reference(cg_ctx* c, const char* ref_seq, int32_t ref_len)
     }
     int rc;
     if ((rc = sr_grow(c, &r.d_ref, &r.ref_cap, (size_t)ref_len + 1))) return rc;
+    if (!r.d_cnt) CU(c, cudaMalloc(&r.d_cnt, sizeof(int) << 20));
     if ((size_t)ref_len > r.idx_cap) {
         CU(c, cudaStreamSynchronize(r.st));
-        cudaFree(r.d_keys_a); cudaFree(r.d_keys_b); cudaFree(r.d_vals_a); cudaFree(r.d_vals_b);
-        r.d_keys_a = r.d_keys_b = nullptr; r.d_vals_a = r.d_vals_b = nullptr; r.idx_cap = 0;
+        cudaFree(r.d_pos_list); r.d_pos_list = nullptr; r.idx_cap = 0;
         const size_t n = (size_t)ref_len + 1024;
-        CU(c, cudaMalloc(&r.d_keys_a, n * 4)); CU(c, cudaMalloc(&r.d_keys_b, n * 4));
-        CU(c, cudaMalloc(&r.d_vals_a, n * 4)); CU(c, cudaMalloc(&r.d_vals_b, n * 4));
+        CU(c, cudaMalloc(&r.d_pos_list, n * 4));
         r.idx_cap = n;
-    }
-    const size_t temp = cgk_sr_sort_temp_bytes(ref_len > 0 ? ref_len : 1);
-    if (temp > r.temp_cap) {
-        CU(c, cudaStreamSynchronize(r.st));
-        cudaFree(r.d_temp); r.d_temp = nullptr; r.temp_cap = 0;
-        CU(c, cudaMalloc(&r.d_temp, temp + 1024));
-        r.temp_cap = temp + 1024;
     }
     CU(c, cudaMemcpyAsync(r.d_ref, ref_seq, (size_t)ref_len, cudaMemcpyHostToDevice, r.st));
     CU(c, cudaMemsetAsync(r.d_ref + ref_len, 0, 1, r.st));
     CU(c, cudaMemsetAsync(r.d_n_rows, 0, 16, r.st));
     {
-        prof_scope ps(c, r.st, 3, 2);
-        CU(c, cgk_sr_index(r.st, r.d_ref, ref_len, r.d_keys_a, r.d_keys_b, r.d_vals_a, r.d_vals_b, r.d_temp, r.temp_cap, r.d_lo, r.d_hi, c->n_sms));
+        prof_scope ps(c, r.st, 3, 3);
+        CU(c, cgk_sr_index(r.st, r.d_ref, ref_len, r.d_cnt, r.d_pos_list, r.d_lo, r.d_hi, c->n_sms));
     }
     CU(c, cudaStreamSynchronize(r.st));            /* ref_seq may be pageable and may die at return */
     r.ref_len = ref_len;
@@ -1417,16 +1411,22 @@ int cg_sr_push(cg_ctx* c, const cg_half* halves, size_t n, const char* bases, si
     CU(c, cudaSetDevice(c->device));
     auto& r = c->sr;
     int rc;
-    if ((rc = sr_grow(c, &r.d_halves, &r.halves_cap, n))) return rc;
-    if ((rc = sr_grow(c, &r.d_bases, &r.bases_cap, n_bases + 1))) return rc;
-    CU(c, cudaMemcpyAsync(r.d_halves, halves, n * sizeof(cg_half), cudaMemcpyHostToDevice, r.st));
-    CU(c, cudaMemcpyAsync(r.d_bases, bases, n_bases, cudaMemcpyHostToDevice, r.st));
+    /* two staging sets in rotation: this batch's copies and search are queued behind the previous batch's without the
+     * host waiting for either; a set is written again only when the search that read it is done (a pageable host
+     * buffer is consumed by cudaMemcpyAsync before it returns, so the caller may reuse it at once) */
+    const int b = (int)(r.n_push++ & 1u);
+    if (!r.ev_buf[b]) CU(c, cudaEventCreateWithFlags(&r.ev_buf[b], cudaEventDisableTiming));
+    CU(c, cudaEventSynchronize(r.ev_buf[b]));
+    if ((rc = sr_grow(c, &r.d_halves[b], &r.halves_cap[b], n))) return rc;
+    if ((rc = sr_grow(c, &r.d_bases[b], &r.bases_cap[b], n_bases + 1))) return rc;
+    CU(c, cudaMemcpyAsync(r.d_halves[b], halves, n * sizeof(cg_half), cudaMemcpyHostToDevice, r.st));
+    CU(c, cudaMemcpyAsync(r.d_bases[b], bases, n_bases, cudaMemcpyHostToDevice, r.st));
     {
         prof_scope ps(c, r.st, 3, 1);
-        CU(c, cgk_sr_search(r.st, r.d_ref, r.ref_len, r.d_vals_b, r.d_lo, r.d_hi, r.d_halves, (long long)n, r.d_bases, r.chrom_len,
+        CU(c, cgk_sr_search(r.st, r.d_ref, r.ref_len, r.d_pos_list, r.d_lo, r.d_hi, r.d_halves[b], (long long)n, r.d_bases[b], r.chrom_len,
                             r.mq_threshold, r.d_rows, r.d_n_rows, r.rows_cap, r.d_n_map, c->n_sms));
     }
-    CU(c, cudaStreamSynchronize(r.st));            /* the staging buffers are reused by the next batch */
+    CU(c, cudaEventRecord(r.ev_buf[b], r.st));
     return CG_OK;
 }
 

@@ -10,13 +10,15 @@
  * come back.
  *
  * Index.  The reference chains, for every k-mer value, the positions where it starts, and drops
- * values with >= MAX_SR_HIT (50000) positions.  Here: one 21-bit key per position (the 20-bit k-mer
- * code of split_read.c:36-50, or a sentinel where ref[i..i+9] is not all ACGT or runs past the
- * sequence), a stable radix sort of (key, position) — positions stay ascending inside a k-mer — and
- * two int32[2^20] arrays with each k-mer's span in the sorted position list.
+ * values with >= MAX_SR_HIT (50000) positions.  Here: a counting sort by the 20-bit k-mer code of
+ * split_read.c:36-50 (positions whose ten bases are not all ACGT, or run past the sequence, have no
+ * k-mer): k_sr_hist counts the positions of every value, k_sr_scan turns the 2^20 counts into each
+ * value's span [lo, hi) of one position list, k_sr_scatter writes every position into its value's span
+ * (one atomic slot counter per value; the order inside a span is arbitrary, which nothing below minds).
+ * Hand-written; round 1 sorted (key, position) pairs with cub::DeviceRadixSort.
  *
- * Search.  One warp per read half.  The window test |hit - pos| < 100000 (split_read.c:120,172) is a
- * binary search into the k-mer's ascending positions; for each candidate the lanes compare the bases
+ * Search.  One warp per read half.  The lanes walk the seed's span 32 positions at a time and test the
+ * window |hit - pos| < 100000 (split_read.c:120,172); for each candidate inside it the lanes compare the bases
  * (hammingDistance, common.c:277-287) and the warp sums mismatches; forward hits are kept (at most 99
  * matter: with >= MAX_MAPPING hits the reference keeps none), reverse-complement hits are only
  * counted — they lower mapq = 60 / n but can never make a row (determine_SvType only pairs
@@ -24,7 +26,6 @@
  * list equals the reference's linked list as a multiset, which is all count_ReadPairs looks at.
  */
 #include "cg_internal.h"
-#include <cub/device/device_radix_sort.cuh>
 
 #define FULL 0xffffffffu
 #define SR_K 10                       /* HASHKMERLEN  split_read.h:18 */
@@ -40,43 +41,75 @@ __device__ __forceinline__ int base_code(unsigned char c)        /* (c & 0x6) >>
     return (c == 'A' || c == 'C' || c == 'G' || c == 'T') ? ((c & 0x6) >> 1) : -1;
 }
 
-/* key of every position: the k-mer starting there, if all ten bases are ACGT and inside the sequence */
-__global__ void k_sr_keys(const unsigned char* __restrict__ ref, int n, unsigned* keys, int* vals)
+/* the k-mer starting at position i, or -1 if its ten bases are not all ACGT or run past the sequence */
+__device__ __forceinline__ int kmer_at(const unsigned char* __restrict__ ref, int i, int n)
+{
+    if (i + SR_K > n) return -1;
+    unsigned v = 0;
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < SR_K; j++) {
+        const int c = base_code(ref[i + j]);
+        ok = ok && c >= 0;
+        v = (v << 2) | (unsigned)(c & 3);
+    }
+    return ok ? (int)v : -1;
+}
+
+/* positions per k-mer value */
+__global__ void k_sr_hist(const unsigned char* __restrict__ ref, int n, int* cnt)
 {
     const int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        unsigned key = SR_SENTINEL;
-        if (i + SR_K <= n) {
-            unsigned v = 0;
-            bool ok = true;
-#pragma unroll
-            for (int j = 0; j < SR_K; j++) {
-                const int c = base_code(ref[i + j]);
-                ok = ok && c >= 0;
-                v = (v << 2) | (unsigned)(c & 3);
-            }
-            if (ok) key = v;
-        }
-        keys[i] = key;
-        vals[i] = i;
+        const int k = kmer_at(ref, i, n);
+        if (k >= 0) atomicAdd(&cnt[k], 1);
     }
 }
 
-/* span of every k-mer value in the sorted list */
-__global__ void k_sr_bounds(const unsigned* __restrict__ keys, int n, int* lo, int* hi)
+/* exclusive scan of the 2^20 counts by ONE CTA of 32 warps: a warp owns 32768 consecutive values and walks them 32 at
+ * a time with a shuffle scan and a running carry; the warps' totals are scanned in shared memory.  lo[k] = first slot
+ * of value k in the position list, hi[k] = lo[k] + its count; the counts are cleared for k_sr_scatter's slot counters */
+__global__ void __launch_bounds__(1024)
+k_sr_scan(int* cnt, int* lo, int* hi)
+{
+    __shared__ int s_tot[32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int per_warp = SR_BUCKETS / 32, base = w * per_warp;
+    int carry = 0;
+    for (int i = 0; i < per_warp; i += 32) {
+        const int v = cnt[base + i + lane];
+        int x = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, x, d); if (lane >= d) x += o; }
+        lo[base + i + lane] = carry + x - v;                  /* relative to the warp's first value for now */
+        carry += __shfl_sync(FULL, x, 31);
+    }
+    if (lane == 0) s_tot[w] = carry;
+    __syncthreads();
+    int off = 0;
+    for (int k = 0; k < w; k++) off += s_tot[k];
+    for (int i = 0; i < per_warp; i += 32) {
+        const int k = base + i + lane;
+        const int l = lo[k] + off;
+        lo[k] = l;
+        hi[k] = l + cnt[k];
+        cnt[k] = 0;
+    }
+}
+
+/* every position into its value's span */
+__global__ void k_sr_scatter(const unsigned char* __restrict__ ref, int n, const int* __restrict__ lo, int* fill, int* pos_list)
 {
     const int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const unsigned k = keys[i];
-        if (k >= SR_SENTINEL) continue;
-        if (i == 0 || keys[i - 1] != k) lo[k] = i;
-        if (i == n - 1 || keys[i + 1] != k) hi[k] = i + 1;
+        const int k = kmer_at(ref, i, n);
+        if (k >= 0) pos_list[lo[k] + atomicAdd(&fill[k], 1)] = i;
     }
 }
 
 struct sr_search_args {
     const unsigned char* ref; int ref_len;          /* ref_seq and bp_cnt (ref[bp_cnt] is the terminator) */
-    const int* pos_sorted; const int* lo; const int* hi;
+    const int* pos_list; const int* lo; const int* hi;     /* positions grouped by k-mer value, span of every value */
     const cg_half* halves; long long n_halves;
     const unsigned char* bases;
     int chrom_len, mq_threshold;
@@ -119,28 +152,32 @@ k_sr_search(const sr_search_args a)
                 if (rev && n_fwd >= SR_MAX_MAPPING) break;                    /* split_read.c:133 */
                 const int seed = seed_of(str, len, rev != 0);
                 if (seed < 0) continue;
-                int lo = a.lo[seed], hi = a.hi[seed];
+                const int lo = a.lo[seed], hi = a.hi[seed];
                 if (hi - lo >= SR_MAX_HIT) continue;                          /* init_hash_table, split_read.c:440-448 */
-                /* first position > pos - SR_LOOKAHEAD */
-                const int want = hf.pos - SR_LOOKAHEAD;
-                int l = lo, r = hi;
-                while (l < r) { const int m = (l + r) >> 1; if (a.pos_sorted[m] > want) r = m; else l = m + 1; }
-                for (int c = l; c < hi; c++) {
-                    const int hit = a.pos_sorted[c];
-                    if (hit >= hf.pos + SR_LOOKAHEAD) break;                  /* abs(hit - pos) < SR_LOOKAHEAD */
-                    int d = 0;
-                    for (int i = lane; i < len; i += 32) {
-                        unsigned char q = rev ? str[len - 1 - i] : str[i];
-                        if (rev) q = q == 'A' ? 'T' : q == 'T' ? 'A' : q == 'G' ? 'C' : q == 'C' ? 'G' : q;
-                        /* the reference compares against ref_seq[hit + i]; at and beyond the terminator nothing equals a base */
-                        const unsigned char t = hit + i < a.ref_len ? a.ref[hit + i] : (unsigned char)0;
-                        d += t != q;
-                    }
-                    d = __reduce_add_sync(FULL, d);
-                    if (d <= dist_max) {
-                        if (!rev) { if (n_fwd < SR_MAX_MAPPING && lane == 0) s_hits[w][n_fwd] = hit; n_fwd++; }
-                        n_all++;
-                        if (n_all > SR_MAX_MAPPING + 1) break;                /* already rejected: >= MAX_MAPPING mappings keep none */
+                bool done = false;
+                for (int c0 = lo; c0 < hi && !done; c0 += 32) {
+                    /* 32 positions of the span at a time; the ones inside the window abs(hit - pos) < SR_LOOKAHEAD are candidates */
+                    const int mine = c0 + lane < hi ? a.pos_list[c0 + lane] : 0x7fffffff;
+                    const long long dlt = (long long)mine - (long long)hf.pos;
+                    unsigned cand = __ballot_sync(FULL, c0 + lane < hi && dlt > -(long long)SR_LOOKAHEAD && dlt < (long long)SR_LOOKAHEAD);
+                    while (cand) {
+                        const int src = __ffs(cand) - 1;
+                        cand &= cand - 1;
+                        const int hit = __shfl_sync(FULL, mine, src);
+                        int d = 0;
+                        for (int i = lane; i < len; i += 32) {
+                            unsigned char q = rev ? str[len - 1 - i] : str[i];
+                            if (rev) q = q == 'A' ? 'T' : q == 'T' ? 'A' : q == 'G' ? 'C' : q == 'C' ? 'G' : q;
+                            /* the reference compares against ref_seq[hit + i]; at and beyond the terminator nothing equals a base */
+                            const unsigned char t = hit + i < a.ref_len ? a.ref[hit + i] : (unsigned char)0;
+                            d += t != q;
+                        }
+                        d = __reduce_add_sync(FULL, d);
+                        if (d <= dist_max) {
+                            if (!rev) { if (n_fwd < SR_MAX_MAPPING && lane == 0) s_hits[w][n_fwd] = hit; n_fwd++; }
+                            n_all++;
+                            if (n_all > SR_MAX_MAPPING + 1) { done = true; break; }   /* already rejected: >= MAX_MAPPING mappings keep none */
+                        }
                     }
                 }
             }
@@ -205,33 +242,23 @@ __global__ void k_sr_count(const cg_splitrow* __restrict__ rows, int n_rows, con
 }
 
 /* ---- launchers ------------------------------------------------------------------------ */
-size_t cgk_sr_sort_temp_bytes(int n)
-{
-    size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const unsigned*)nullptr, (unsigned*)nullptr, (const int*)nullptr, (int*)nullptr, n, 0, 2 * SR_K + 1);
-    return bytes;
-}
-
-cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, unsigned* keys_a, unsigned* keys_b, int* vals_a, int* vals_b,
-                         void* temp, size_t temp_bytes, int* lo, int* hi, int n_sms)
+cudaError_t cgk_sr_index(cudaStream_t s, const unsigned char* ref, int n, int* cnt, int* pos_list, int* lo, int* hi, int n_sms)
 {
     cudaError_t e;
-    if ((e = cudaMemsetAsync(lo, 0, sizeof(int) * SR_BUCKETS, s)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(hi, 0, sizeof(int) * SR_BUCKETS, s)) != cudaSuccess) return e;
-    if (n <= 0) return cudaSuccess;
-    k_sr_keys<<<n_sms * 8, 256, 0, s>>>(ref, n, keys_a, vals_a);
-    if ((e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_a, keys_b, vals_a, vals_b, n, 0, 2 * SR_K + 1, s)) != cudaSuccess) return e;
-    k_sr_bounds<<<n_sms * 8, 256, 0, s>>>(keys_b, n, lo, hi);
+    if ((e = cudaMemsetAsync(cnt, 0, sizeof(int) * SR_BUCKETS, s)) != cudaSuccess) return e;
+    if (n > 0) k_sr_hist<<<n_sms * 8, 256, 0, s>>>(ref, n, cnt);
+    k_sr_scan<<<1, 1024, 0, s>>>(cnt, lo, hi);
+    if (n > 0) k_sr_scatter<<<n_sms * 8, 256, 0, s>>>(ref, n, lo, cnt, pos_list);
     return cudaGetLastError();
 }
 
-cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len, const int* pos_sorted, const int* lo, const int* hi,
+cudaError_t cgk_sr_search(cudaStream_t s, const unsigned char* ref, int ref_len, const int* pos_list, const int* lo, const int* hi,
                           const cg_half* halves, long long n_halves, const unsigned char* bases, int chrom_len, int mq_threshold,
                           cg_splitrow* rows, unsigned* n_rows, unsigned cap, unsigned long long* n_mappings, int n_sms)
 {
     if (n_halves <= 0) return cudaSuccess;
     sr_search_args a;
-    a.ref = ref; a.ref_len = ref_len; a.pos_sorted = pos_sorted; a.lo = lo; a.hi = hi;
+    a.ref = ref; a.ref_len = ref_len; a.pos_list = pos_list; a.lo = lo; a.hi = hi;
     a.halves = halves; a.n_halves = n_halves; a.bases = bases; a.chrom_len = chrom_len; a.mq_threshold = mq_threshold;
     a.rows = rows; a.n_rows = n_rows; a.cap = cap; a.n_mappings = n_mappings;
     long long blocks = (n_halves + SR_WARPS - 1) / SR_WARPS;
@@ -254,8 +281,9 @@ cudaError_t cgk_configure_split(void)
 {
     const int pct = cgk_carveout();
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_sr_keys, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_sr_bounds, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_sr_hist, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_sr_scan, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_sr_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_sr_search, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     return cudaFuncSetAttribute(k_sr_count, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
 }
