@@ -100,6 +100,16 @@ struct cg_sub {
     unsigned int*  h_flags;           /* NULL, or page-locked [n_jobs]: each job's flag word for the host */
 };
 
+/* Checked build (-DCG_CHECKED, scripts/build_checked.sh): every index the kernels form is asserted against the extent of
+ * the array it goes into; a violation traps the kernel and the next CUDA call fails.  compute-sanitizer is not available on
+ * the B200 pool this was developed on, so the parity suite is run once against this build instead. */
+#ifdef CG_CHECKED
+#include <assert.h>
+#define CG_CHECK(cond) assert(cond)
+#else
+#define CG_CHECK(cond) ((void)0)
+#endif
+
 #ifdef __cplusplus
 #include <vector>
 extern "C++" {

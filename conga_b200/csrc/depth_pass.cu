@@ -197,7 +197,8 @@ k_mark(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
         if (lane == 0 && k0 < n32 && first + k0 > 0) prev0 = load_pos(R, first + k0 - 1);
         int p[MARK_U], cp[MARK_U], mapq[MARK_U];
 #pragma unroll
-        for (int u = 0; u < MARK_U; u++) { unpack_raw(aos, raw[u], p[u], mapq[u]); cp[u] = chunk_of(p[u], n_chunks); }
+        for (int u = 0; u < MARK_U; u++) { unpack_raw(aos, raw[u], p[u], mapq[u]); cp[u] = chunk_of(p[u], n_chunks); CG_CHECK(cp[u] >= 0 && cp[u] < n_chunks); }
+        CG_CHECK(chunk0 >= 0 && chunk0 + n_chunks < S.n_space);
         int q = __shfl_up_sync(FULL, p[MARK_U - 1], 1), cq = __shfl_up_sync(FULL, cp[MARK_U - 1], 1);
         if (lane == 0) { q = prev0; cq = chunk_of(prev0, n_chunks); }
         if (first + k0 == 0) cq = -1;                         /* the chromosome's first record opens every chunk up to its own */
@@ -340,6 +341,7 @@ __device__ __forceinline__ void bin32(bool in, int pos, int mapq, int base, int 
             if (now > 0xffffu) atomicSub(&bins[off >> 1], 0x10000u);
         }
         big |= now >= 0x8000u;
+        CG_CHECK((off >> 1) < (unsigned)(CG_CHUNK / 2) && pos / 100 - w0 >= 0 && pos / 100 - w0 < MAXWIN);
         atomicAdd(&wend[pos / 100 - w0], cnt);
     }
 }
@@ -382,6 +384,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             while (j + 1 < n_jobs && wq >= (unsigned)sm.job[j + 1].work0) j++;
             job = j; lc = (int)(wq - (unsigned)sm.job[j].work0);
             const int g = sm.job[j].chunk0 + lc;
+            CG_CHECK(g >= 0 && g + 1 < S.n_space);
             lo = __ldg(&S.k.chunk_lo[g]);
             hi = __ldg(&S.k.chunk_lo[g + 1]);
         }
@@ -399,12 +402,14 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
 #pragma unroll
             for (int u = 0; u < PASS_PRE; u++) {
                 const int i = lo + 32 * u + lane;
+                CG_CHECK(i < hi ? (i >= 0 && i < P.n_reads) : true);
                 if (i < hi) raw[u] = load_raw(R, i);           /* issued here, unpacked when the chunk is binned */
             }
         }
         const int base = lc << CG_CHUNK_SHIFT, w0 = base / 100;
         const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
         const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(min(base + CG_CHUNK, P.chrom_len), 100 * (w0 + lane) + 100);
+        CG_CHECK(!(lane < nwin && gw_e > gw_s) || (w0 + lane) * 100 < P.chrom_len);
         if (lane < nwin && gw_e > gw_s) gcb = (int)P.gc[w0 + lane];               /* sonic_interval.c:263-272 */
     };
 
@@ -454,6 +459,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
             const int nwin = (base + CG_CHUNK - 1) / 100 - w0 + 1;
             const int gw_s = max(base, 100 * (w0 + lane)), gw_e = min(min(base + CG_CHUNK, chrom_len), 100 * (w0 + lane) + 100);
             const size_t gpos = (size_t)(P.chunk0 + clc) << CG_CHUNK_SHIFT;          /* the chunk in the slot's depth array */
+            CG_CHECK(P.chunk0 + clc >= 0 && P.chunk0 + clc < S.n_space && nwin <= MAXWIN && cjob < n_jobs);
             /* A window's depth sum is the number of records that fell into it as long as no int16 of the chunk
              * went negative (32768 or more records on one position): counted while the records are binned.
              * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
@@ -472,6 +478,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
                     for (int u = 0; u < PASS_PRE; u++) {
                         f_raw[u] = make_uint2(0u, 0u);
                         const int i = i0 + 32 * (PASS_PRE + u) + lane;
+                        CG_CHECK(i < hi ? (i >= 0 && i < P.n_reads) : true);
                         if (i < hi) f_raw[u] = load_raw(R, i);
                     }
 #pragma unroll
@@ -604,6 +611,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
 
     /* ---- CTA epilogue: what this CTA saw of every job's GC bins, plain coalesced stores ---- */
     __syncthreads();
+    CG_CHECK((int)blockIdx.x < S.n_pass_ctas);
     int* out = S.partial + (size_t)blockIdx.x * n_jobs * CG_PART_WORDS;
     for (int i = tid; i < n_jobs * CG_PART_WORDS; i += NT) out[i] = gcs[i];
 }
@@ -668,6 +676,7 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         const int c_end = J.chunk0 + J.n_chunks;
         for (int sp = s0 + (int)blockIdx.y * (FIN_T / 32) + warp; sp < s1; sp += (FIN_T / 32) * FIN_Y) {
             const int cb = sp << (2 * LVL);
+            CG_CHECK(cb >= 0 && cb + CG_SUPER_CHUNKS <= S.n_space);
             const int32_t* c1 = S.k.cnt1 + cb;
             int v[32];
 #pragma unroll

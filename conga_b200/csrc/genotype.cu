@@ -383,6 +383,7 @@ __device__ __forceinline__ int depth_sum_direct(const int16_t* __restrict__ dept
     const int v0 = s >> 3, v1 = (e + 7) >> 3;                       /* vectors of eight positions */
     const uint4* row = reinterpret_cast<const uint4*>(depth);
     int part = 0;
+    CG_CHECK(s >= 0 && e >= s);
     for (int q = v0 + lane; q < v1; q += 32) {
         uint4 v = __ldg(row + q);
         const int first = q << 3;
@@ -558,6 +559,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         const int c = (gi - s_seg0[seg]) * G + lane;
         const bool valid = lane < G && c < n_seg;
         cg_cnv v = make_cnv(0, 0);
+        CG_CHECK(!valid || (c >= 0 && c < n_seg));
         if (valid) v = cnvs[c];
         int s = v.start, e = v.end;
         if (valid && (s < 0 || e > chrom_len)) { atomicOr(S.sticky, CG_FLAG_RANGE); s = max(s, 0); e = min(e, chrom_len); }
@@ -575,6 +577,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         int w = any ? s / 100 : 0;                      /* next window of the expected chain */
         int r_lo = 0, r_hi = 0;                         /* the first run ending beyond s lies in [r_lo, r_hi] */
         if (use_map && any) {
+            CG_CHECK((s >> RUN_BUCKET_SHIFT) + 1 < cgk_run_index_words_dev(chrom_len));
             r_lo = __ldg(&run_idx[s >> RUN_BUCKET_SHIFT]);
             r_hi = __ldg(&run_idx[(s >> RUN_BUCKET_SHIFT) + 1]);
         }
@@ -582,6 +585,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         /* ---- phase 1: expected_rd ramp-up (likelihood.c:115-119), window by window ---- */
         float E = 0.0f;
         for (int i = 0; i < GENO_RAMP && w <= w_last; i++, w++) {
+            CG_CHECK(w >= 0 && w < n_windows);
             int bin = (int)__ldg(&gc[w]);                                          /* sonic_interval.c:263-272 */
             if ((unsigned)bin > 100u) bin = 0;
             E = add_run_f32(E, __uint_as_float(s_expb[bin]), min(e, 100 * w + 100) - max(s, 100 * w));
@@ -591,6 +595,7 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
         if (use_map && any) {
             while (r_hi - r_lo > 8) {
                 const int mid = (r_lo + r_hi) >> 1;
+                CG_CHECK(mid >= 0 && mid < n_runs);
                 if (__ldg(&runs[mid].end) > s) r_hi = mid; else r_lo = mid + 1;
             }
         }

@@ -103,7 +103,11 @@ __global__ void k_sr_scatter(const unsigned char* __restrict__ ref, int n, const
     const int stride = gridDim.x * blockDim.x;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const int k = kmer_at(ref, i, n);
-        if (k >= 0) pos_list[lo[k] + atomicAdd(&fill[k], 1)] = i;
+        if (k >= 0) {
+            const int slot = lo[k] + atomicAdd(&fill[k], 1);
+            CG_CHECK(slot >= 0 && slot < n);
+            pos_list[slot] = i;
+        }
     }
 }
 
@@ -152,7 +156,9 @@ k_sr_search(const sr_search_args a)
                 if (rev && n_fwd >= SR_MAX_MAPPING) break;                    /* split_read.c:133 */
                 const int seed = seed_of(str, len, rev != 0);
                 if (seed < 0) continue;
+                CG_CHECK(seed >= 0 && seed < SR_BUCKETS);
                 const int lo = a.lo[seed], hi = a.hi[seed];
+                CG_CHECK(lo >= 0 && hi >= lo && hi <= a.ref_len);
                 if (hi - lo >= SR_MAX_HIT) continue;                          /* init_hash_table, split_read.c:440-448 */
                 bool done = false;
                 for (int c0 = lo; c0 < hi && !done; c0 += 32) {

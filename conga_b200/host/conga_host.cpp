@@ -341,7 +341,14 @@ struct Decoder {
         const int l = c.l_qseq;
         if (!(l > p.min_read_length)) return;
         if ((c.flag & (BAM_FSECONDARY | BAM_FSUPPLEMENTARY | BAM_FDUP | BAM_FQCFAIL)) != 0) return;         /* is_proper, common.c:317-323 */
-        if (sonic_is_satellite(p.this_sonic, p.this_sonic->chromosome_names[ct.chr_index], (int)c.pos, (int)c.pos + 20) != 0) return;
+        /* libsonic caches the chromosome it looked at last inside the sonic struct (sonic_refind_chromosome_index writes
+         * this_sonic->last_chromosome_index, sonic_reference.c:124-131) and this runs on up to 16 decode threads over parts
+         * of different chromosomes: every thread asks through its own shallow copy of the struct (the tables behind the
+         * pointers are read-only), so no thread can return the index another one has just stored */
+        static thread_local sonic local_sonic;
+        static thread_local const sonic* local_of = nullptr;
+        if (local_of != p.this_sonic) { local_sonic = *p.this_sonic; local_of = p.this_sonic; }
+        if (sonic_is_satellite(&local_sonic, local_sonic.chromosome_names[ct.chr_index], (int)c.pos, (int)c.pos + 20) != 0) return;
         if (c.pos == 0) return;                                                                               /* split_read.c:215-216 */
         const uint8_t* q = bam_get_qual(b);
         const uint8_t* sq = bam_get_seq(b);
