@@ -482,7 +482,12 @@ struct Decoder {
 };
 
 /* ---- output_SVs, likelihood.c:172-288 ---------------------------------------------------- */
-struct Totals { int dels = 0, dups = 0; };
+struct Totals {
+    int dels = 0, dups = 0;
+    /* CONGA_STATS side file */
+    long long reads = 0, positions = 0, cnvs = 0, split_rows = 0;
+    int chromosomes = 0, samples = 0;
+};
 
 void write_rows(const Params& p, const char* chr, const std::vector<cg_cnv>& dels, const std::vector<cg_call>& dcall,
                 const std::vector<cg_cnv>& dups, const std::vector<cg_call>& ucall, const std::vector<int32_t>& del_border_rp,
@@ -684,6 +689,8 @@ void emit_chromosome(const Params& p, const std::string& sample, const char* son
         return;
     }
     const char* chr = r.chr.c_str();
+    tot.reads += (long long)r.st.reads_passed; tot.positions += (long long)r.length; tot.chromosomes++;
+    tot.cnvs += (long long)(r.dels.size() + r.dups.size()); tot.split_rows += r.n_paired;
     fprintf(stderr, "\nReading BAM [%s] - Chromosome: %s", sample.c_str(), chr);
     fprintf(stderr, "\n-->counting reads");
     fprintf(stderr, " (%d reads, %ld split-reads)\n", (int)r.st.reads_passed, r.n_split);
@@ -999,7 +1006,10 @@ int main(int argc, char** argv)
     tick("BEDs parsed");
     gpus.wait();
     tick("CUDA contexts up");
-    if (getenv("CONGA_TIMING")) for (cg_ctx* c : gpus.ctx) cg_set_profiling(c, 1);
+    /* CONGA_STATS=<file>: an opt-in machine-readable summary of the run (metrics); nothing else changes */
+    const char* stats_path = getenv("CONGA_STATS");
+    const auto t_work0 = std::chrono::steady_clock::now();
+    if (getenv("CONGA_TIMING") || stats_path) for (cg_ctx* c : gpus.ctx) cg_set_profiling(c, 1);
     FILE* main_log = g_log;
     for (size_t i = 0; i < samples.size(); i++) {
         Sample* next = i + 1 < samples.size() ? new Sample(samples[i + 1], (int)gpus.ctx.size()) : nullptr;   /* decoded under sample i */
@@ -1018,15 +1028,40 @@ int main(int argc, char** argv)
         if (batch) { fclose(g_log); g_log = main_log; fprintf(g_log, "sample %zu: %s -> %s%s\n", i, cur->p.bam_file.c_str(), cur->p.outdir.c_str(), cur->p.outprefix.c_str()); }
         delete cur;
         cur = next;
+        tot.samples++;
         tick("sample done");
     }
-    if (getenv("CONGA_TIMING"))
+    if (getenv("CONGA_TIMING") && !stats_path)             /* with CONGA_STATS the kernel times go into the side file */
         for (cg_ctx* c : gpus.ctx) {
             double ms[CG_NSLOTS]; int64_t n[CG_NSLOTS];
             if (cg_kernel_times(c, ms, n) == CG_OK)
                 fprintf(stderr, "[timing] kernels: prep %.3f ms (%ld), depth pass %.3f ms (%ld), genotype %.3f ms (%ld), split reads %.3f ms (%ld)\n",
                         ms[0], (long)n[0], ms[1], (long)n[1], ms[2], (long)n[2], ms[3], (long)n[3]);
         }
+    if (stats_path) {
+        double ms[CG_NSLOTS] = {0, 0, 0, 0}; int64_t n[CG_NSLOTS] = {0, 0, 0, 0};
+        for (cg_ctx* c : gpus.ctx) {
+            double m[CG_NSLOTS]; int64_t k[CG_NSLOTS];
+            if (cg_kernel_times(c, m, k) == CG_OK) for (int i = 0; i < CG_NSLOTS; i++) { ms[i] += m[i]; n[i] += k[i]; }
+        }
+        const double work_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_work0).count();
+        const double total_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - g_t0).count();
+        /* bytes the depth pass moves by construction: 8 per record, 2 per position, 1 per 100 positions */
+        const double pass_bytes = 8.0 * (double)tot.reads + 2.01 * (double)tot.positions;
+        FILE* f = fopen(stats_path, "w");
+        if (f) {
+            fprintf(f, "{\"samples\": %d, \"gpus\": %zu, \"chromosomes\": %d, \"positions\": %lld, \"reads\": %lld, \"cnvs\": %lld, \"split_read_rows\": %lld,\n"
+                       " \"seconds_total\": %.4f, \"seconds_after_contexts_up\": %.4f, \"reads_per_s\": %.1f, \"cnvs_per_s\": %.1f,\n"
+                       " \"kernel_ms\": {\"prep\": %.4f, \"depth_pass\": %.4f, \"genotype\": %.4f, \"split_reads\": %.4f},\n"
+                       " \"kernel_launches\": {\"prep\": %ld, \"depth_pass\": %ld, \"genotype\": %ld, \"split_reads\": %ld},\n"
+                       " \"depth_pass_gb_per_s\": %.1f, \"genotype_cnvs_per_s\": %.1f}\n",
+                    tot.samples, gpus.ctx.size(), tot.chromosomes, tot.positions, tot.reads, tot.cnvs, tot.split_rows,
+                    total_s, work_s, work_s > 0 ? (double)tot.reads / work_s : 0.0, work_s > 0 ? (double)tot.cnvs / work_s : 0.0,
+                    ms[0], ms[1], ms[2], ms[3], (long)n[0], (long)n[1], (long)n[2], (long)n[3],
+                    ms[1] > 0 ? pass_bytes / (ms[1] * 1e-3) / 1e9 : 0.0, ms[2] > 0 ? (double)tot.cnvs / (ms[2] * 1e-3) : 0.0);
+            fclose(f);
+        }
+    }
     gpus.shutdown();
     tick("contexts destroyed");
     for (auto& kv : in.runs) cg_free_runs(kv.second.first);

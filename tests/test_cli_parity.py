@@ -66,13 +66,19 @@ def test_plain_dels_and_dups(tools):
 
 
 def test_mappability_min_mapq_c_score(tools):
+    """... and CONGA_STATS=<file>: the opt-in machine-readable summary leaves every output as it is."""
+    import json
     tmp = tempfile.mkdtemp(prefix="cli_")
     try:
         rng = np.random.default_rng(102)
         paths = cli_inputs.build_inputs(tmp, [("1", 300_000), ("chr2", 200_000)], rng, reads_per_mb=60000, with_map=True)
+        stats = os.path.join(tmp, "stats.json")
         outs = run_both(tmp, paths, ["--dels", paths["dels"], "--dups", paths["dups"], "--mappability", paths["map"],
-                                     "--min-mapq", "20", "--c-score", "0.3", "--min-sv-size", "1200"])
+                                     "--min-mapq", "20", "--c-score", "0.3", "--min-sv-size", "1200"], env={"CONGA_STATS": stats})
         assert_same(outs)
+        st = json.load(open(stats))
+        assert st["chromosomes"] == 2 and st["positions"] == 500_000 and st["reads"] > 0 and st["cnvs"] > 0
+        assert st["kernel_launches"]["depth_pass"] == 2 and st["kernel_ms"]["depth_pass"] > 0 and st["depth_pass_gb_per_s"] > 0
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
