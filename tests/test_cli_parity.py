@@ -14,7 +14,7 @@ import cli_inputs
 
 pytestmark = pytest.mark.gpu
 ROOT = cli_inputs.ROOT
-HOST = os.path.join(ROOT, "conga_b200", "host", "conga-b200")
+HOST = os.environ.get("CONGA_HOST_BIN") or os.path.join(ROOT, "conga_b200", "host", "conga-b200")   # CONGA_HOST_BIN: the sanitizer build (scripts/gpu_asan.sh)
 REF_CONGA = os.path.join(cli_inputs.REF, "conga")
 
 
