@@ -178,7 +178,7 @@ def own_arm(args):
     from conga_b200 import multi
     from conga_b200 import (CALL_DT, CG_PTR_DEVICE, CG_PTR_HOST, CHROM_JOB_DT, CNV_DT, MAPRUN_DT, READ_DT, STATS_DT, Context,
                             chrom_job, comm_unique_id, flatten_mappability)
-    from conga_b200.abi import CG_JOB_ANNOTATION_RESIDENT
+    from conga_b200.abi import ANCHOR_DT, CG_JOB_ANNOTATION_RESIDENT, encode_positions_delta
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     # stdout carries the JSON line and nothing else: libraries that print there (NCCL's version banner)
@@ -324,10 +324,12 @@ def own_arm(args):
     # where those are the same for all samples and stay resident (CG_JOB_ANNOTATION_RESIDENT).
     ctx.set_pointer_mode(CG_PTR_HOST)
     ctx.set_async(True)
+    if args.e2e_format == "auto":              # a sparse sample (C2: one read per 600 bases) escapes almost every delta: 5 bytes per read
+        args.e2e_format = "delta" if wl.n_reads * 200 > wl.n_positions else "planes"
     NBUF = 8                                   # result buffers in rotation: more than the six submissions in flight
     annot_resident = planes
     with_mapq = mq >= 0
-    h2d = d2h = 0
+    h2d = d2h = rec_h2d = 0
     inputs = []
     for k, c in enumerate(mine):
         r = res[k]
@@ -335,11 +337,23 @@ def own_arm(args):
         for s in range(S):
             rec = sample_records(k, s)
             pos = rec if planes else np.ascontiguousarray(rec["pos"])
-            pp = ctx.pinned_array(len(pos), np.int32); pp[:] = pos
-            pm = None
+            if args.e2e_format == "delta":
+                d_, big_, anc_ = encode_positions_delta(pos)
+                pd_ = ctx.pinned_array(len(d_), np.uint8); pd_[:] = d_
+                pb_ = ctx.pinned_array(len(big_), np.int32); pb_[:] = big_
+                pa_ = ctx.pinned_array(len(anc_), ANCHOR_DT); pa_[:] = anc_
+                recs = dict(n=len(pos), reads_delta=pd_, reads_big=pb_, n_big=len(big_), reads_anchor=pa_)
+                nbytes = pd_.nbytes + pb_.nbytes + pa_.nbytes
+            else:
+                pp = ctx.pinned_array(len(pos), np.int32); pp[:] = pos
+                recs = dict(n=len(pos), reads_pos=pp)
+                nbytes = pp.nbytes
             if with_mapq:
                 pm = ctx.pinned_array(len(pos), np.uint8); pm[:] = rec["mapq"]
-            per_sample.append((pp, pm))
+                recs["reads_mapq"] = pm
+                nbytes += pm.nbytes
+            recs["nbytes"] = nbytes
+            per_sample.append(recs)
         if annot_resident:
             ann = (r["gc"], r["dels"], r["dups"], r["runs"])
         else:
@@ -350,7 +364,8 @@ def own_arm(args):
             prn = ctx.pinned_array(len(fr), MAPRUN_DT); prn[:] = fr
             ann = (pg, pd, pu, prn)
             h2d += pg.nbytes + pd.nbytes + pu.nbytes + prn.nbytes
-        h2d += per_sample[0][0].nbytes + (per_sample[0][1].nbytes if with_mapq else 0)
+        h2d += per_sample[0]["nbytes"]
+        rec_h2d += per_sample[0]["nbytes"]
         d2h += (len(c.dels) + len(c.dups)) * CALL_DT.itemsize + STATS_DT.itemsize
         inputs.append((c, per_sample, ann))
     outs = [[(ctx.pinned_array(len(c.dels), CALL_DT), ctx.pinned_array(len(c.dups), CALL_DT), ctx.pinned_array(1, STATS_DT))
@@ -359,9 +374,10 @@ def own_arm(args):
     def host_jobs(s, buf):
         if not inputs:
             return np.zeros(0, dtype=CHROM_JOB_DT)
-        return np.concatenate([chrom_job(c.index, c.length, ann[0], len(c.gc), mq, None, len(ps[s][0]), ann[3], r["n_runs"], has_map,
-                                         ann[1], len(c.dels), od, ann[2], len(c.dups), ou, st, reads_pos=ps[s][0], reads_mapq=ps[s][1],
-                                         flags=CG_JOB_ANNOTATION_RESIDENT if annot_resident else 0)
+        return np.concatenate([chrom_job(c.index, c.length, ann[0], len(c.gc), mq, None, ps[s]["n"], ann[3], r["n_runs"], has_map,
+                                         ann[1], len(c.dels), od, ann[2], len(c.dups), ou, st,
+                                         flags=CG_JOB_ANNOTATION_RESIDENT if annot_resident else 0,
+                                         **{k_: v_ for k_, v_ in ps[s].items() if k_ not in ("n", "nbytes")})
                                for (c, ps, ann), r, (od, ou, st) in zip(inputs, res, outs[buf])])
     cycle = int(np.lcm(S, NBUF))              # step k uses sample k % S and result buffers k % NBUF
     jobs_host = {(k % S, k % NBUF): host_jobs(k % S, k % NBUF) for k in range(cycle)} if cycle <= 256 else None
@@ -433,9 +449,10 @@ def own_arm(args):
 
     n_reads = float(np.mean(reads_of_sample)) if S > 1 else float(reads_of_sample[0])
     if world > 1:
-        t = torch.tensor([n_reads, h2d, d2h, launches], dtype=torch.float64, device=dev)
+        t = torch.tensor([n_reads, h2d, d2h, launches, rec_h2d], dtype=torch.float64, device=dev)
         dist.all_reduce(t)
-        n_reads, h2d, d2h, launches = float(t[0].item()), int(t[1].item()), int(t[2].item()), int(t[3].item())
+        n_reads, h2d, d2h, launches, rec_h2d = float(t[0].item()), int(t[1].item()), int(t[2].item()), int(t[3].item()), int(t[4].item())
+    rec_h2d_all = float(rec_h2d)
     n_cnvs = wl.n_cnvs
     value = n_reads * args.steps / (ms_dev / 1e3)
     e2e = n_reads * args.steps / (ms_e2e / 1e3)
@@ -482,7 +499,9 @@ def own_arm(args):
            "cnvs_per_s_genotype_kernel_alone_rank0": round(sum(len(c.dels) + len(c.dups) for c in mine) / (cnv_ms / 1e3), 1) if cnv_ms > 0 else None,
            "e2e": {"value": round(e2e, 1), "unit": "reads/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                    "ms_per_step_spread": spread(e2e_ms_sorted), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                   "bytes_per_read": 5 if with_mapq else 4, "annotation_resident": annot_resident,
+                   "record_format": ("delta-coded positions (cg_encode_positions_delta)" if args.e2e_format == "delta" else "int32 position plane")
+                                    + (" + uint8 mapq plane" if with_mapq else ""),
+                   "bytes_per_read": round(rec_h2d_all / max(1.0, n_reads), 3), "annotation_resident": annot_resident,
                    "cnvs_per_s": round(n_cnvs * args.steps / (ms_e2e / 1e3), 1)},
            "gpu_launches": int(launches), "gpu_launches_per_step": round(launches / args.steps, 2),
            "roofline": roofline, "parity": parity, "clocks": clocks}
@@ -667,6 +686,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (debugging only; 1.0 = the named config)")
+    ap.add_argument("--e2e-format", default="auto", choices=["auto", "delta", "planes"],
+                    help="record stream of the end-to-end leg: delta-coded positions (1 byte per read and 4 more per gap >= 255) or an "
+                         "int32 position plane (4); auto = delta when the mean gap between reads is below 200 bases")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--emulate-rank", default="", help="R/N: run rank R's share of an N-rank partition alone on one GPU (tuning only)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)

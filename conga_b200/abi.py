@@ -43,8 +43,11 @@ SPLITROW_DT = np.dtype([("pos", "<i4"), ("pos_map", "<i4"), ("left_start", "<i4"
 CHROM_JOB_DT = np.dtype([("chr_index", "<i4"), ("chrom_len", "<i4"), ("gc", "<u8"), ("n_windows", "<i4"), ("mq_threshold", "<i4"),
                          ("reads", "<u8"), ("n_reads", "<u8"), ("runs", "<u8"), ("n_runs", "<u8"), ("use_mappability", "<i4"), ("flags", "<i4"),
                          ("dels", "<u8"), ("n_del", "<u8"), ("del_calls", "<u8"), ("dups", "<u8"), ("n_dup", "<u8"), ("dup_calls", "<u8"),
-                         ("stats", "<u8"), ("reads_pos", "<u8"), ("reads_mapq", "<u8")])
-assert CHROM_JOB_DT.itemsize == 136
+                         ("stats", "<u8"), ("reads_pos", "<u8"), ("reads_mapq", "<u8"),
+                         ("reads_delta", "<u8"), ("reads_big", "<u8"), ("n_big", "<u8"), ("reads_anchor", "<u8")])
+assert CHROM_JOB_DT.itemsize == 168
+ANCHOR_DT = np.dtype([("pos_before", "<i4"), ("big_before", "<u4")])
+CG_DELTA_BLOCK = 1024
 assert HALF_DT.itemsize == 16 and SPLITROW_DT.itemsize == 32
 assert READ_DT.itemsize == 8 and CNV_DT.itemsize == 8 and MAPIV_DT.itemsize == 16
 assert MAPRUN_DT.itemsize == 16 and CALL_DT.itemsize == 56 and STATS_DT.itemsize == 204 * 8
@@ -79,6 +82,7 @@ SYMBOLS = {
     "cg_sr_count": (_I, [_P, _P, _Z, _P, _Z, _P, _Z, _P, _P]),
     "cg_gc_profile": (_I, [_P, _P, C.c_int64, _P, C.c_int32]),
     "cg_run_chromosomes": (_I, [_P, _P, _Z]),
+    "cg_encode_positions_delta": (_I, [_P, _Z, _P, _P, _Z, C.POINTER(_Z), _P]),
     "cg_sync": (_I, [_P]),
     "cg_download_depth": (_I, [_P, _P]),
     "cg_download_prefix": (_I, [_P, _P]),
@@ -413,6 +417,39 @@ class Context:
         return list(ms), list(n)
 
 
+def encode_positions_delta(pos: np.ndarray):
+    """cg_encode_positions_delta: sorted int32 positions -> (uint8 deltas, int32 side array, ANCHOR_DT anchors)."""
+    lib = load_library()
+    pos = np.ascontiguousarray(pos, dtype=np.int32)
+    n = len(pos)
+    delta = np.empty(n, dtype=np.uint8)
+    anchors = np.zeros((n + CG_DELTA_BLOCK - 1) // CG_DELTA_BLOCK, dtype=ANCHOR_DT)
+    big = np.empty(max(16, n // 16), dtype=np.int32)
+    nb = C.c_size_t(0)
+    for _ in range(2):
+        rc = lib.cg_encode_positions_delta(pos.ctypes.data, n, delta.ctypes.data, big.ctypes.data, len(big), C.byref(nb), anchors.ctypes.data)
+        if rc != CG_ERANGE:
+            break
+        big = np.empty(nb.value, dtype=np.int32)
+    if rc != CG_OK:
+        raise CongaGpuError(rc, lib.cg_last_error(None).decode())
+    return delta, big[:nb.value].copy(), anchors
+
+
+def decode_positions_delta(delta: np.ndarray, big: np.ndarray, anchors: np.ndarray) -> np.ndarray:
+    """What k_decode_delta computes, in NumPy (tests): the int32 positions of a delta-coded stream."""
+    gaps = delta.astype(np.int64)
+    gaps[delta == 255] = big
+    pos = np.cumsum(gaps).astype(np.int32)
+    if len(pos):
+        blk = np.arange(len(anchors)) * CG_DELTA_BLOCK
+        before = np.concatenate([[0], pos[blk[1:] - 1]]) if len(blk) > 1 else np.zeros(1, dtype=np.int64)
+        assert np.array_equal(anchors["pos_before"], before.astype(np.int32))
+        esc = np.concatenate([[0], np.cumsum(delta == 255)])
+        assert np.array_equal(anchors["big_before"], esc[blk].astype(np.uint32))
+    return pos
+
+
 def comm_unique_id() -> bytes:
     """cg_comm_unique_id: 128 bytes one rank creates and every rank passes to Context.comm_init_rank."""
     lib = load_library()
@@ -425,13 +462,14 @@ def comm_unique_id() -> bytes:
 
 def chrom_job(chr_index, chrom_len, gc, n_windows, mq_threshold, reads, n_reads, runs=None, n_runs=0, use_mappability=False,
               dels=None, n_del=0, del_calls=None, dups=None, n_dup=0, dup_calls=None, stats=None,
-              reads_pos=None, reads_mapq=None, flags=0) -> np.ndarray:
+              reads_pos=None, reads_mapq=None, flags=0, reads_delta=None, reads_big=None, n_big=0, reads_anchor=None) -> np.ndarray:
     """One cg_chrom_job record; array arguments may be NumPy arrays, torch tensors or raw addresses.
     reads=None with reads_pos (and optionally reads_mapq) selects the compact record planes."""
     j = np.zeros(1, dtype=CHROM_JOB_DT)
     j["chr_index"], j["chrom_len"], j["gc"], j["n_windows"], j["mq_threshold"] = chr_index, chrom_len, _ptr(gc), n_windows, mq_threshold
     j["reads"], j["n_reads"] = _ptr(reads), n_reads
     j["reads_pos"], j["reads_mapq"], j["flags"] = _ptr(reads_pos), _ptr(reads_mapq), flags
+    j["reads_delta"], j["reads_big"], j["n_big"], j["reads_anchor"] = _ptr(reads_delta), _ptr(reads_big) if n_big else 0, n_big, _ptr(reads_anchor)
     j["runs"], j["n_runs"], j["use_mappability"] = _ptr(runs) if n_runs else 0, n_runs, int(bool(use_mappability))
     j["dels"], j["n_del"], j["del_calls"] = _ptr(dels) if n_del else 0, n_del, _ptr(del_calls) if n_del else 0
     j["dups"], j["n_dup"], j["dup_calls"] = _ptr(dups) if n_dup else 0, n_dup, _ptr(dup_calls) if n_dup else 0

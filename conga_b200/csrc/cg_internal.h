@@ -53,6 +53,10 @@ struct cg_dev_job {
     const cg_read*  reads;
     const int32_t*  rec_pos;
     const uint8_t*  rec_mapq;         /* may be NULL with rec_pos when mq_threshold < 0: every record passes */
+    const uint8_t*  rec_delta;        /* delta-coded positions (cg_encode_positions_delta) that k_decode_delta turns into ... */
+    const int32_t*  rec_big;
+    const cg_delta_anchor* rec_anchor;
+    int32_t*        rec_pos_out;      /* ... this position plane (= rec_pos), or NULL */
     long long       n_reads;          /* records of the chromosome so far */
     long long       mark_first, mark_n;   /* k_mark: the batch this launch looks at */
     int32_t         mark_blk0;        /* first block visit of this job in the k_mark launch (cgk_mark_blocks) */
@@ -123,6 +127,7 @@ int         cgk_job_space(int n_chunks);                          /* chunks of c
 int         cgk_pass_grid(int n_work, long long n_records, int n_sms);   /* CTAs of the pass, = rows of cg_sub::partial */
 int         cgk_mark_blocks(unsigned long long n_records);        /* block visits of k_mark for a batch of records */
 cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
+cudaError_t cgk_decode_delta(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);

@@ -71,6 +71,7 @@ struct cg_slot {
     int8_t* d_gc = nullptr;           size_t gc_cap = 0;
     cg_maprun* d_runs = nullptr;      size_t runs_cap = 0;
     char* d_in = nullptr;             size_t in_cap = 0;          /* sample submissions: one arena for records, GC bytes, runs */
+    int32_t* d_dec = nullptr;         size_t dec_cap = 0;         /* DEVICE mode: position planes decoded from delta streams */
     char* d_arena = nullptr;          size_t arena_cap = 0, arena_used = 0;   /* CNV + call staging, blocking HOST mode */
     int rec_fmt = 0;                          /* per-chromosome pushes: 0 none yet, 1 cg_read, 2 planes, 3 planes without mapq */
     /* ordering */
@@ -152,7 +153,7 @@ struct cg_ctx {
     } sr;
 
     /* largest sizes any slot has needed, per buffer kind (see grow()) */
-    size_t hw_gc = 0, hw_reads = 0, hw_rpos = 0, hw_rmapq = 0, hw_runs = 0, hw_run_idx = 0, hw_pos = 0, hw_in = 0;
+    size_t hw_gc = 0, hw_reads = 0, hw_rpos = 0, hw_rmapq = 0, hw_runs = 0, hw_run_idx = 0, hw_pos = 0, hw_in = 0, hw_dec = 0;
 
     /* cg_gc_profile staging (HOST pointer mode) */
     char* d_gc_bases = nullptr; size_t gc_bases_cap = 0;
@@ -361,7 +362,7 @@ void cg_destroy(cg_ctx* c)
         cg_slot& s = c->slot[i];
         cudaFree(s.d_reads); cudaFree(s.d_pos); cudaFree(s.d_mapq); cudaFree(s.d_gc); cudaFree(s.d_counts);
         cudaFree(s.d_depth); cudaFree(s.d_expected); cudaFree(s.d_ctl); cudaFree(s.d_partial); cudaFree(s.d_jobs); cudaFree(s.d_fin);
-        cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32); cudaFree(s.d_in);
+        cudaFree(s.d_runs); cudaFree(s.d_run_idx); cudaFree(s.d_arena); cudaFree(s.d_depth32); cudaFree(s.d_in); cudaFree(s.d_dec);
         if (s.h_jobs) cudaFreeHost(s.h_jobs);
         if (s.h_flags) cudaFreeHost(s.h_flags);
         cudaEvent_t evs[] = {s.ev_table, s.ev_copy, s.ev_pass, s.ev_passk, s.ev_geno[0], s.ev_geno[1], s.ev_runs};
@@ -907,7 +908,9 @@ static int validate_job(cg_ctx* c, const cg_chrom_job& j, size_t k)
     if (j.chrom_len <= 0 || j.chrom_len > INT32_MAX - 2 * CG_CHUNK * CG_SUPER_CHUNKS) return fail(c, CG_EINVAL, "job %zu: chrom_len %d", k, j.chrom_len);
     if (!j.gc || j.n_windows < (j.chrom_len + 99) / 100) return fail(c, CG_EINVAL, "job %zu: gc_profile needs >= %d windows (got %d)", k, (j.chrom_len + 99) / 100, j.n_windows);
     if (j.n_reads >= 0x7fffffffull) return fail(c, CG_EINVAL, "job %zu: more than 2^31-1 records on one chromosome", k);
-    if (j.n_reads && !j.reads && !j.reads_pos) return fail(c, CG_EINVAL, "job %zu: null records", k);
+    if (j.n_reads && !j.reads && !j.reads_pos && !j.reads_delta) return fail(c, CG_EINVAL, "job %zu: null records", k);
+    if (j.n_reads && !j.reads && !j.reads_pos && (!j.reads_anchor || (j.n_big && !j.reads_big) || j.n_big > j.n_reads))
+        return fail(c, CG_EINVAL, "job %zu: a delta-coded stream needs its anchors and its side array", k);
     if (j.n_reads && !j.reads && !j.reads_mapq && j.mq_threshold >= 0) return fail(c, CG_EINVAL, "job %zu: a NULL mapq plane needs a negative mq_threshold", k);
     if (j.n_runs > 0x7ffffff0ull || (j.n_runs && j.use_mappability && !j.runs)) return fail(c, CG_EINVAL, "job %zu: bad mappability runs", k);
     if (j.n_del > 0x3fffffffull || j.n_dup > 0x3fffffffull) return fail(c, CG_EINVAL, "job %zu: too many CNVs", k);
@@ -927,7 +930,7 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
     unsigned long long all_records = 0;
     for (int k = 0; k < n; k++) { all_cnvs += jobs[k].n_del + jobs[k].n_dup; all_records += jobs[k].n_reads; }
     const int G = cgk_geno_g(all_cnvs, c->n_sms);
-    size_t in_bytes = 0, ridx_words = 0;
+    size_t in_bytes = 0, ridx_words = 0, dec_words = 0;
     const bool host = c->ptr_mode == CG_PTR_HOST;
     for (int k = 0; k < n; k++) {
         const cg_chrom_job& j = jobs[k];
@@ -937,8 +940,11 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         mark_blocks += (long long)cgk_mark_blocks(j.n_reads);
         if (j.use_mappability && j.n_runs) { run_blocks += (long long)((j.n_runs + 1 + 255) / 256); ridx_words += (size_t)cgk_run_index_words(j.chrom_len); }
         n_cnv += (long long)cgk_geno_groups(j.n_del, G) + cgk_geno_groups(j.n_dup, G);
+        if (!host && !j.reads && !j.reads_pos) dec_words += (size_t)((j.n_reads + 63) & ~(uint64_t)63);   /* DEVICE mode: the plane a delta stream decodes into */
         if (host) {
             in_bytes += j.reads ? al256(j.n_reads * sizeof(cg_read)) : al256(j.n_reads * 4) + (j.reads_mapq ? al256(j.n_reads) : 0);
+            if (!j.reads && !j.reads_pos)          /* delta stream: the bytes, the side array, the anchors; the plane above is what they decode into */
+                in_bytes += al256(j.n_reads) + al256(j.n_big * 4) + al256((size_t)cgk_mark_blocks(j.n_reads) * sizeof(cg_delta_anchor));
             if (!(j.flags & CG_JOB_ANNOTATION_RESIDENT)) {
                 in_bytes += al256((size_t)(j.chrom_len + 99) / 100);
                 if (j.use_mappability) in_bytes += al256(j.n_runs * sizeof(cg_maprun));
@@ -954,6 +960,7 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
     if ((rc = ensure_space(c, s, (int)space, false)) != CG_OK) return rc;
     if (ridx_words && (rc = grow(c, &s.d_run_idx, &s.run_idx_cap, ridx_words, 0, &c->hw_run_idx)) != CG_OK) return rc;
     if (host && (rc = grow(c, &s.d_in, &s.in_cap, in_bytes, 0, &c->hw_in)) != CG_OK) return rc;
+    if (!host && dec_words && (rc = grow(c, &s.d_dec, &s.dec_cap, dec_words, 0, &c->hw_dec)) != CG_OK) return rc;
     /* the staging copy of the table is rewritten below: its previous upload must have read it */
     CU(c, cudaEventSynchronize(s.ev_table));
 
@@ -967,11 +974,12 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
 
     int chunk0 = 0, work0 = 0, blk0 = 0, rblk0 = 0, cnv0 = 0;
     size_t in_off = 0, ridx_off = 0;
-    bool any_runs = false;
+    bool any_runs = false, any_delta = false;
+    size_t dec_off = 0;
     auto stage = [&](const void* src, size_t bytes) -> void* {           /* upload into the slot's arena (HOST mode) */
         char* dst = s.d_in + in_off;
         in_off += al256(bytes);
-        if (bytes) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s.s_copy);
+        if (bytes && src) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s.s_copy);     /* no source: room only */
         return dst;
     };
     for (int k = 0; k < n; k++) {
@@ -983,16 +991,32 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
         J.mq_threshold = j.mq_threshold; J.chr_index = j.chr_index;
         J.n_reads = (long long)j.n_reads; J.mark_first = 0; J.mark_n = (long long)j.n_reads; J.mark_blk0 = blk0;
         const bool annot_dev = !host || (j.flags & CG_JOB_ANNOTATION_RESIDENT);
+        const bool delta = !j.reads && !j.reads_pos && j.n_reads;
         if (host) {
             J.gc = annot_dev ? j.gc : static_cast<const int8_t*>(stage(j.gc, (size_t)(j.chrom_len + 99) / 100));
             if (j.reads) J.reads = static_cast<const cg_read*>(stage(j.reads, j.n_reads * sizeof(cg_read)));
+            else if (!delta) J.rec_pos = static_cast<const int32_t*>(stage(j.reads_pos, j.n_reads * 4));
             else {
-                J.rec_pos = static_cast<const int32_t*>(stage(j.reads_pos, j.n_reads * 4));
-                if (j.reads_mapq) J.rec_mapq = static_cast<const uint8_t*>(stage(j.reads_mapq, j.n_reads));
+                /* the delta bytes, the side array and the anchors are uploaded; the position plane is only reserved:
+                 * k_decode_delta fills it on the device */
+                J.rec_delta = static_cast<const uint8_t*>(stage(j.reads_delta, j.n_reads));
+                J.rec_big = static_cast<const int32_t*>(stage(j.reads_big, j.n_big * 4));
+                J.rec_anchor = static_cast<const cg_delta_anchor*>(stage(j.reads_anchor, (size_t)cgk_mark_blocks(j.n_reads) * sizeof(cg_delta_anchor)));
+                J.rec_pos_out = static_cast<int32_t*>(stage(nullptr, j.n_reads * 4));
+                J.rec_pos = J.rec_pos_out;
+                any_delta = true;
             }
+            if (!j.reads && j.reads_mapq) J.rec_mapq = static_cast<const uint8_t*>(stage(j.reads_mapq, j.n_reads));
         } else {
             J.gc = j.gc;
-            if (j.reads) J.reads = j.reads; else { J.rec_pos = j.reads_pos; J.rec_mapq = j.reads_mapq; }
+            if (j.reads) J.reads = j.reads;
+            else if (!delta) { J.rec_pos = j.reads_pos; J.rec_mapq = j.reads_mapq; }
+            else {
+                J.rec_delta = j.reads_delta; J.rec_big = j.reads_big; J.rec_anchor = j.reads_anchor; J.rec_mapq = j.reads_mapq;
+                J.rec_pos_out = s.d_dec + dec_off; dec_off += (size_t)((j.n_reads + 63) & ~(uint64_t)63);
+                J.rec_pos = J.rec_pos_out;
+                any_delta = true;
+            }
         }
         J.stats_row = stats_row_of(c, j.chr_index);
         J.row_out = reinterpret_cast<long long*>(j.stats);          /* page-locked (asynchronous HOST) or device memory */
@@ -1024,6 +1048,10 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
 
     const cg_dev_job& J0 = s.hj[0];            /* ignored by the kernels: the table is used */
     if (host) CU(c, cudaStreamWaitEvent(s.s_work, s.ev_copy, 0));
+    if (mark_blocks && any_delta) {
+        prof_scope ps(c, s.s_work, 0, 1);
+        CU(c, cgk_decode_delta(s.s_work, s.sub, J0));
+    }
     if (mark_blocks) {
         prof_scope ps(c, s.s_work, 0, 1);
         CU(c, cgk_mark(s.s_work, s.sub, J0));
@@ -1070,6 +1098,8 @@ static int submit_sample(cg_ctx* c, const cg_chrom_job* jobs, int n)
 static int run_one_job(cg_ctx* c, const cg_chrom_job& j)
 {
     int rc;
+    if (j.n_reads && !j.reads && !j.reads_pos)             /* before anything is begun */
+        return fail(c, CG_EINVAL, "a delta-coded record stream is taken by submissions only (DEVICE or asynchronous HOST mode)");
     if ((rc = cg_chrom_begin(c, j.chr_index, j.chrom_len, j.gc, j.n_windows, j.mq_threshold)) != CG_OK) return rc;
     if (j.n_reads) {
         rc = j.reads ? cg_push_reads(c, j.reads, (size_t)j.n_reads) : cg_push_reads_compact(c, j.reads_pos, j.reads_mapq, (size_t)j.n_reads);
@@ -1116,6 +1146,36 @@ static int settle_samples(cg_ctx* c)
 }
 
 extern "C" {
+
+/* host-side input preparation: positions -> delta bytes + side array + anchors (include/conga_gpu.h) */
+int cg_encode_positions_delta(const int32_t* pos, size_t n, uint8_t* delta, int32_t* big, size_t big_cap, size_t* n_big,
+                              cg_delta_anchor* anchors)
+{
+    if ((n && (!pos || !delta || !anchors)) || !n_big) return fail(nullptr, CG_EINVAL, "null argument");
+    size_t nb = 0;
+    int32_t prev = 0;
+    bool fits = true;
+    for (size_t i = 0; i < n; i++) {
+        if ((i % CG_DELTA_BLOCK) == 0) {
+            anchors[i / CG_DELTA_BLOCK].pos_before = prev;
+            anchors[i / CG_DELTA_BLOCK].big_before = (uint32_t)nb;
+        }
+        const int32_t p = pos[i];
+        if (p < prev) return fail(nullptr, CG_EINVAL, "record %zu: position %d behind %d — a delta-coded stream needs non-negative, non-decreasing positions", i, p, prev);
+        const int64_t d = (int64_t)p - (int64_t)prev;
+        if (d >= 255) {
+            delta[i] = 255;
+            if (nb < big_cap && big) big[nb] = (int32_t)d; else fits = false;
+            nb++;
+        } else {
+            delta[i] = (uint8_t)d;
+        }
+        prev = p;
+    }
+    *n_big = nb;
+    if (!fits) return fail(nullptr, CG_ERANGE, "the side array needs %zu entries (%zu given)", nb, big_cap);
+    return CG_OK;
+}
 
 int cg_run_chromosomes(cg_ctx* c, const cg_chrom_job* jobs, size_t n_jobs)
 {

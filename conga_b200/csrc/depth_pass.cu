@@ -250,6 +250,77 @@ cudaError_t cgk_mark(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 }
 
 /* ------------------------------------------------------------------------- */
+/* delta-coded positions -> int32 position plane (include/conga_gpu.h, cg_encode_positions_delta).  One CTA per block
+ * of CG_DELTA_BLOCK = MARK_BLOCK records (the block partition of k_mark), four records per thread: the four delta
+ * bytes are one 32-bit load; escapes (255) take their gap from the side array at anchor.big_before + (escapes in
+ * front inside the block); positions are anchor.pos_before + inclusive block scan of the gaps.  ~1 byte read and 4
+ * written per record: HBM time a twentieth of what the bytes saved on PCIe cost. */
+static_assert(MARK_BLOCK == CG_DELTA_BLOCK && MARK_U == 4, "k_decode_delta shares k_mark's block partition");
+__global__ void __launch_bounds__(256)
+k_decode_delta(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
+{
+    const cg_dev_job* jobs = S.jobs ? S.jobs : &J1;
+    __shared__ int s_blk0[CG_JMAX + 1];
+    __shared__ int s_wsum[8], s_wesc[8];
+    if (threadIdx.x <= S.n_jobs) s_blk0[threadIdx.x] = threadIdx.x < S.n_jobs ? jobs[threadIdx.x].mark_blk0 : S.n_mark_blocks;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int j = 0;
+    for (int b = blockIdx.x; b < S.n_mark_blocks; b += gridDim.x) {
+        while (b >= s_blk0[j + 1]) j++;
+        const cg_dev_job& J = jobs[j];
+        if (!J.rec_delta) continue;                           /* block-uniform */
+        const int lb = b - s_blk0[j], n = (int)J.n_reads;
+        const int k0 = lb * CG_DELTA_BLOCK + (int)threadIdx.x * 4;
+        const cg_delta_anchor an = J.rec_anchor[lb];
+        unsigned d4 = 0u;
+        if (k0 + 3 < n && (reinterpret_cast<uintptr_t>(J.rec_delta) & 3u) == 0u)
+            d4 = __ldg(reinterpret_cast<const unsigned*>(J.rec_delta + k0));                    /* k0 is a multiple of 4 */
+        else for (int u = 0; u < 4; u++) if (k0 + u < n) d4 |= (unsigned)__ldg(J.rec_delta + k0 + u) << (8 * u);
+        int g[4], esc = 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) { g[u] = (int)((d4 >> (8 * u)) & 0xffu); esc += (k0 + u < n && g[u] == 255); }
+        /* escapes in front of this thread inside the block */
+        int e_incl = esc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, e_incl, d); if (lane >= d) e_incl += o; }
+        if (lane == 31) s_wesc[warp] = e_incl;
+        __syncthreads();
+        int e_before = e_incl - esc;
+        for (int w = 0; w < warp; w++) e_before += s_wesc[w];
+        int bi = (int)an.big_before + e_before;
+#pragma unroll
+        for (int u = 0; u < 4; u++) if (k0 + u < n && g[u] == 255) g[u] = __ldg(J.rec_big + bi++);
+        /* positions: inclusive scan of the gaps */
+        int tsum = 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) { if (k0 + u >= n) g[u] = 0; tsum += g[u]; }
+        int s_incl = tsum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, s_incl, d); if (lane >= d) s_incl += o; }
+        if (lane == 31) s_wsum[warp] = s_incl;
+        __syncthreads();
+        int p = an.pos_before + s_incl - tsum;
+        for (int w = 0; w < warp; w++) p += s_wsum[w];
+        int out[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { p += g[u]; out[u] = p; }
+        if (k0 + 3 < n) *reinterpret_cast<int4*>(J.rec_pos_out + k0) = make_int4(out[0], out[1], out[2], out[3]);
+        else for (int u = 0; u < 4; u++) if (k0 + u < n) J.rec_pos_out[k0 + u] = out[u];
+        __syncthreads();                                      /* s_wsum / s_wesc are reused by the next block */
+    }
+}
+
+cudaError_t cgk_decode_delta(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
+{
+    if (S.n_mark_blocks <= 0) return cudaSuccess;
+    int blocks = S.n_mark_blocks;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_decode_delta<<<blocks, 256, 0, s>>>(S, J1);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------------------- */
 /* out-of-order input (per-chromosome entry points): global-atomic histogram into u32 words (zero at
  * rest: the pass clears every word it consumes).  Returns at once for a sorted stream. */
 __global__ void k_rare_scatter(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job J1)
@@ -786,6 +857,7 @@ cudaError_t cgk_configure_depth(void)
     if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pass_smem_bytes(CG_JMAX))) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_depth_pass, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_mark, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_decode_delta, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_rare_scatter, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(k_finalize, cudaFuncAttributePreferredSharedMemoryCarveout, pct)) != cudaSuccess) return e;
     return cudaSuccess;

@@ -319,6 +319,9 @@ __device__ __noinline__ dd dd_lpoisson(int k, double lambda, dd logfact)
     return dd_sub(dd_sub(dd_mul(dd_log(lambda), dd_from((double)k)), dd_from(lambda)), logfact);
 }
 
+struct dd_decision { int ih, it, homo_gt_het; };
+__device__ dd_decision dd_decide(int obs, double lam_homo, double lam_het);
+
 /* (int)x of the real number x = hi + lo as C truncates a double that holds it: toward zero; out of int range as cvttsd2si */
 __device__ __forceinline__ int dd_trunc_to_int(dd x)
 {
@@ -329,6 +332,18 @@ __device__ __forceinline__ int dd_trunc_to_int(dd x)
         else if (x.hi < 0.0 && x.lo > 0.0) t += 1.0;
     }
     return __double2int_rz(t);
+}
+
+/* the three decisions of a flagged CNV in one out-of-line call (one call site keeps the spills around it out of the
+ * common path of k_genotype) */
+__device__ __noinline__ dd_decision dd_decide(int obs, double lam_homo, double lam_het)
+{
+    const dd lf = dd_log_factorial(obs);
+    const dd h = dd_lpoisson(obs, lam_homo, lf), t = dd_lpoisson(obs, lam_het, lf);
+    dd_decision r;
+    r.ih = dd_trunc_to_int(h); r.it = dd_trunc_to_int(t);
+    r.homo_gt_het = lam_homo == lam_het ? 0 : (h.hi > t.hi || (h.hi == t.hi && h.lo > t.lo)) ? 1 : 0;
+    return r;
 }
 
 /* fp64 twin of step_delta_f32: significand increment of one rounded addition of v while the
@@ -752,10 +767,8 @@ k_genotype(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
             if (near_integer(lhomo) || near_integer(lhetero)) mf |= 1u;
             if (lhomo != lhetero && fabs(lhomo - lhetero) <= 1e-9 * fmax(fabs(lhomo), fabs(lhetero))) mf |= 2u;
             if (mf) {
-                const dd lf = dd_log_factorial(obs);
-                const dd h = dd_lpoisson(obs, lam_homo, lf), t = dd_lpoisson(obs, lam_het, lf);
-                ih = dd_trunc_to_int(h); it = dd_trunc_to_int(t);
-                homo_gt_het = lam_homo == lam_het ? false : (h.hi > t.hi || (h.hi == t.hi && h.lo > t.lo));
+                const dd_decision dcs = dd_decide(obs, lam_homo, lam_het);
+                ih = dcs.ih; it = dcs.it; homo_gt_het = dcs.homo_gt_het != 0;
             }
             cg_call o;
             o.observed = obs;

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define CG_ABI_VERSION 2
+#define CG_ABI_VERSION 3
 
 enum {
     CG_OK = 0,
@@ -219,6 +219,22 @@ int cg_sr_rows(cg_ctx* ctx, cg_splitrow* out, size_t cap, size_t* n_rows, uint64
 int cg_sr_count(cg_ctx* ctx, const cg_splitrow* rows, size_t n, const cg_cnv* dels, size_t n_del,
                 const cg_cnv* dups, size_t n_dup, int32_t* border_rp, int32_t* rp);
 
+/* ---- Delta-coded positions: the record stream at one byte per read ----
+ * A coordinate-sorted BAM (README.md:93) hands out non-decreasing positions, a few dozen bases apart at the
+ * coverages CONGA is meant for, and all bam_data.c:205,213 reads of a record is pos and qual.  So the host may
+ * send, instead of pos[i], delta[i] = min(pos[i] - pos[i-1], 255) as one byte (pos[-1] = 0), the gaps of 255 and
+ * more in a side array `big` in stream order, and one anchor per block of CG_DELTA_BLOCK records (the position in
+ * front of the block and the number of side-array entries in front of it) so that the device decodes every block
+ * on its own: k_decode_delta rebuilds the int32 position plane in HBM with a block scan, and the path continues
+ * as for cg_push_reads_compact.  4.0 -> 1.0 bytes per record across PCIe (C3: 201 -> 72 MB per sample).
+ * cg_encode_positions_delta is host code for callers that produce positions (it is input preparation, like building
+ * cg_read records from bam1_t): returns CG_EINVAL if the positions decrease or are negative (such a stream travels
+ * as cg_read records or planes), CG_ERANGE if `big` is too small (*n_big says how many entries are needed). */
+#define CG_DELTA_BLOCK 1024
+typedef struct cg_delta_anchor { int32_t pos_before; uint32_t big_before; } cg_delta_anchor;
+int cg_encode_positions_delta(const int32_t* pos, size_t n, uint8_t* delta /* n */, int32_t* big, size_t big_cap, size_t* n_big,
+                              cg_delta_anchor* anchors /* ceil(n / CG_DELTA_BLOCK) */);
+
 /* ---- The loop body of read_bam (bam_data.c:304-338) over several chromosomes as ONE submission ----
  * Job k means exactly: cg_chrom_begin(chr_index, chrom_len, gc, n_windows, mq_threshold); cg_push_reads(reads,
  * n_reads) (or cg_push_reads_compact(reads_pos, reads_mapq, n_reads) when reads == NULL); cg_chrom_finish(stats);
@@ -245,6 +261,9 @@ typedef struct cg_chrom_job {
     const cg_cnv* dups;        uint64_t n_dup;    cg_call* dup_calls;
     cg_chrom_stats* stats;     /* may be NULL */
     const int32_t* reads_pos;  const uint8_t* reads_mapq;    /* see cg_push_reads_compact */
+    /* reads == NULL and reads_pos == NULL: the positions as a delta-coded stream (cg_encode_positions_delta);
+     * reads_mapq goes with it as with reads_pos.  Submissions only (DEVICE and asynchronous HOST mode). */
+    const uint8_t* reads_delta; const int32_t* reads_big; uint64_t n_big; const struct cg_delta_anchor* reads_anchor;
 } cg_chrom_job;
 /* flags.  CG_JOB_ANNOTATION_RESIDENT: HOST pointer mode only, submissions only (DEVICE and asynchronous HOST
  * mode) — gc, runs, dels and dups are DEVICE pointers although the records and the results are host memory:

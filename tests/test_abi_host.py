@@ -27,13 +27,13 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/conga_gpu.h but not exported"
     assert set(names) == set(abi.SYMBOLS), set(names) ^ set(abi.SYMBOLS)
-    assert lib.cg_abi_version() == 2
+    assert lib.cg_abi_version() == 3
 
 
 def test_struct_sizes_match_header():
     assert abi.READ_DT.itemsize == 8 and abi.CNV_DT.itemsize == 8 and abi.MAPIV_DT.itemsize == 16
     assert abi.MAPRUN_DT.itemsize == 16 and abi.CALL_DT.itemsize == 56 and abi.STATS_DT.itemsize == 1632
-    assert abi.CHROM_JOB_DT.itemsize == 136          # cg_chrom_job, ABI 2: + reads_pos, reads_mapq
+    assert abi.CHROM_JOB_DT.itemsize == 168          # cg_chrom_job, ABI 3: + reads_pos, reads_mapq, the delta-coded stream
 
 
 def test_no_cpu_fallback_without_gpu():
@@ -128,3 +128,22 @@ def test_balanced_partition_beats_lpt_and_is_deterministic():
         assert multi.balance(GRCH37, parts) >= bound >= 0 and multi.balance(GRCH37, parts) >= multi.balance(GRCH37, multi.lpt_partition(GRCH37, n))
         assert parts == multi.balanced_partition(list(GRCH37), n)          # every rank computes the same partition
     assert multi.balanced_partition([5, 3], 4) == multi.lpt_partition([5, 3], 4)
+
+
+def test_delta_coded_positions_round_trip():
+    """cg_encode_positions_delta (host code of the library) against the NumPy statement of what k_decode_delta computes."""
+    rng = np.random.default_rng(3)
+    for n in (0, 1, 2, 1023, 1024, 1025, 4096, 50_001):
+        pos = np.sort(rng.integers(0, max(1, n) * 60 + 9, size=n)).astype(np.int32)
+        if n > 10:
+            pos[n // 3:] += 1_000_000                      # one gap far above 255, equal positions elsewhere
+            pos[5:8] = pos[5]
+            pos = np.sort(pos)
+        d, big, anc = abi.encode_positions_delta(pos)
+        assert d.dtype == np.uint8 and len(d) == n and len(anc) == (n + 1023) // 1024
+        assert int((d == 255).sum()) == len(big) and (len(big) == 0 or big.min() >= 255)
+        assert np.array_equal(abi.decode_positions_delta(d, big, anc), pos)
+    with pytest.raises(abi.CongaGpuError):
+        abi.encode_positions_delta(np.array([10, 9], dtype=np.int32))
+    with pytest.raises(abi.CongaGpuError):
+        abi.encode_positions_delta(np.array([-1, 9], dtype=np.int32))

@@ -36,8 +36,15 @@ class DeviceSample:
             runs = runs_of(ch)
             b = dict(gc=up(ch.gc), dels=up(ch.dels) if len(ch.dels) else None, dups=up(ch.dups) if len(ch.dups) else None,
                      runs=up(runs) if len(runs) else None)
+            extra = {}
             if fmt == "aos":
                 b["reads"] = up(ch.reads) if len(ch.reads) else None
+            elif fmt.startswith("delta"):
+                from conga_b200 import encode_positions_delta
+                d, big, anc = encode_positions_delta(ch.reads["pos"])
+                b["delta"], b["big"], b["anc"] = (up(d) if len(d) else None), (up(big) if len(big) else None), (up(anc) if len(anc) else None)
+                b["mapq"] = up(np.ascontiguousarray(ch.reads["mapq"])) if len(ch.reads) and fmt == "delta" else None
+                extra = dict(reads_delta=b["delta"], reads_big=b["big"], n_big=len(big), reads_anchor=b["anc"])
             else:
                 b["pos"] = up(np.ascontiguousarray(ch.reads["pos"])) if len(ch.reads) else None
                 b["mapq"] = up(np.ascontiguousarray(ch.reads["mapq"])) if len(ch.reads) and fmt == "planes" else None
@@ -46,7 +53,7 @@ class DeviceSample:
             ou = torch.zeros(max(1, len(ch.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev)
             self.jobs.append(chrom_job(ch.index, ch.length, b["gc"], len(ch.gc), mq, b.get("reads"), len(ch.reads), b["runs"], len(runs),
                                        ch.maprows is not None, b["dels"], len(ch.dels), od, b["dups"], len(ch.dups), ou, st,
-                                       reads_pos=b.get("pos"), reads_mapq=b.get("mapq")))
+                                       reads_pos=b.get("pos"), reads_mapq=b.get("mapq"), **extra))
             self.keep.append(b)
             self.out.append((st, od, ou))
         self.jobs = np.concatenate(self.jobs)
@@ -101,7 +108,7 @@ def test_sample_of_40_chromosomes_device_mode(ctx, oracle):
     check_against_oracle(oracle, chroms, s.results(), 10)
 
 
-@pytest.mark.parametrize("fmt,mq", [("planes", 20), ("pos_only", -1), ("aos", -1)])
+@pytest.mark.parametrize("fmt,mq", [("planes", 20), ("pos_only", -1), ("aos", -1), ("delta", 20), ("delta_pos_only", -1)])
 def test_sample_record_formats_device_mode(ctx, oracle, fmt, mq):
     chroms = mixed_chromosomes(9, seed=5, big=600_000)
     s = DeviceSample(chroms, mq, fmt)
@@ -138,6 +145,45 @@ def test_sample_compact_planes_asynchronous_host_mode(ctx, oracle):
         ctx.sync()
         for outs in samples:
             check_against_oracle(oracle, chroms, [(st[0], od, ou) for st, od, ou in outs], 10)
+    finally:
+        ctx.set_async(False)
+
+
+def test_sample_delta_coded_stream_asynchronous_host_mode(ctx, oracle):
+    """Positions as one byte per record (cg_encode_positions_delta) from page-locked host memory; the chromosomes
+    include gaps far above 255 (sparse ones), blocks that end inside the stream, a chromosome without a record, and a
+    pile-up of equal positions (delta 0)."""
+    from conga_b200 import encode_positions_delta
+    from conga_b200.abi import ANCHOR_DT
+    chroms = mixed_chromosomes(10, seed=18, big=1_000_000)
+    rng = np.random.default_rng(4)
+    sparse = synth._chrom("sp", 10, 3_000_000, rng, 900, 6, 3, False, cnv_hi=200_000)          # mean gap 3300: almost every delta escapes
+    pile = tiny_chrom(50_000, sorted([(1234, 60)] * 3000 + [(int(p), 30) for p in rng.integers(0, 50_000, size=5000)]), dels=[(0, 50_000), (1000, 2500)])
+    pile.index = 11
+    chroms = chroms + [sparse, pile]
+    pin = lambda a, dt: (lambda p: (p.__setitem__(slice(None), a), p)[1])(ctx.pinned_array(len(a), dt))
+    ctx.set_pointer_mode(CG_PTR_HOST)
+    ctx.set_async(True)
+    try:
+        jobs, outs, keep = [], [], []
+        for ch in chroms:
+            runs = runs_of(ch)
+            d, big, anc = encode_positions_delta(ch.reads["pos"])
+            bufs = (pin(d, np.uint8), pin(big, np.int32), pin(anc, ANCHOR_DT), pin(np.ascontiguousarray(ch.reads["mapq"]), np.uint8),
+                    pin(ch.gc, np.int8), pin(ch.dels, CNV_DT), pin(ch.dups, CNV_DT), pin(runs, MAPRUN_DT))
+            st, od, ou = ctx.pinned_array(1, STATS_DT), ctx.pinned_array(len(ch.dels), CALL_DT), ctx.pinned_array(len(ch.dups), CALL_DT)
+            jobs.append(chrom_job(ch.index, ch.length, bufs[4], len(ch.gc), 10, None, len(ch.reads), bufs[7], len(runs), ch.maprows is not None,
+                                  bufs[5], len(ch.dels), od, bufs[6], len(ch.dups), ou, st, reads_mapq=bufs[3],
+                                  reads_delta=bufs[0], reads_big=bufs[1], n_big=len(big), reads_anchor=bufs[2]))
+            keep.append(bufs)
+            outs.append((st, od, ou))
+        for _ in range(2):
+            ctx.run_chromosomes(np.concatenate(jobs))
+        ctx.sync()
+        check_against_oracle(oracle, chroms, [(st[0], od, ou) for st, od, ou in outs], 10)
+        ctx.set_async(False)                             # blocking mode runs chromosome by chromosome: no delta streams there
+        with pytest.raises(Exception):
+            ctx.run_chromosomes(np.concatenate(jobs))
     finally:
         ctx.set_async(False)
 
