@@ -206,15 +206,24 @@ def own_arm(args):
         mine = [wl.chroms[i] for i in multi.balanced_partition([c.length for c in wl.chroms], n_)[r_]]
     has_map, mq = wl.has_mappability, wl.mq_threshold
 
+    collective = os.environ.get("BENCH_COLLECTIVE", "peer")       # "nccl": the library's ncclAllReduce instead (the checked baseline)
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
     ctx.set_slots(env_int("BENCH_SLOTS", 6))
     if world > 1:
         # the path's one collective runs inside the library (cg_stats_allreduce -> ncclAllReduce on cg_stream)
-        box = [comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0, group=cpu_group)
-        ctx.comm_init_rank(world, rank, box[0])
+        if collective == "nccl":
+            box = [comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=cpu_group)
+            ctx.comm_init_rank(world, rank, box[0])
+        else:
+            # fused: k_finalize stores every finished row into every rank's table over NVLink (CUDA IPC peer memory);
+            # cg_stats_allreduce is then a one-warp flag exchange on cg_stream
+            handles = [None] * world
+            dist.all_gather_object(handles, ctx.peer_export(), group=cpu_group)
+            ctx.peer_connect(world, rank, handles)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     step_no = [0]
+    no_coll = bool(os.environ.get("BENCH_DEBUG_NO_COLLECTIVE"))       # tuning only: what the collective costs a step (the row check below then fails)
 
     def barrier():
         if world > 1:
@@ -237,8 +246,11 @@ def own_arm(args):
 
     # ---- leg 1: inputs resident in HBM (CG_PTR_DEVICE) ------------------------------------
     res = []
+    flatten_s = 0.0
     for k, c in enumerate(mine):
+        t_fl = time.perf_counter()
         runs = flatten_mappability(c.maprows, c.length) if (has_map and c.maprows is not None) else None
+        flatten_s += time.perf_counter() - t_fl
         res.append(dict(c=c, gc=to_dev(c.gc), dels=to_dev(c.dels), dups=to_dev(c.dups),
                         runs=to_dev(runs) if runs is not None and len(runs) else None,
                         n_runs=0 if runs is None else len(runs), runs_host=runs,
@@ -262,9 +274,9 @@ def own_arm(args):
         k = step_no[0]
         step_no[0] += 1
         if world > 1:
-            ctx.stats_bank(k & 1)             # the all-reduce of sample k is in flight while sample k+1 fills the other bank
+            ctx.stats_bank(k & 3)             # the all-reduce of sample k is in flight while the next three samples fill the other banks
         ctx.run_chromosomes(jobs_dev[k % S])  # ONE submission: every kernel of the path once for all chromosomes of this rank
-        if world > 1:
+        if world > 1 and not no_coll:
             ctx.stats_allreduce(n_chrom)
 
     def timed(step_fn, k, finish=None):
@@ -387,7 +399,7 @@ def own_arm(args):
         k = e2e_no[0]
         e2e_no[0] += 1
         if world > 1:
-            ctx.stats_bank(k & 1)
+            ctx.stats_bank(k & 3)
         s, b = k % S, k % NBUF
         ctx.run_chromosomes(jobs_host[(s, b)] if jobs_host is not None else host_jobs(s, b))
         if world > 1:
@@ -398,6 +410,7 @@ def own_arm(args):
     ctx.sync()
     regions_e2e = [timed(step_e2e, args.steps) for _ in range(max(3, args.repeats // 2))]
     ms_e2e = float(np.median([r[0] for r in regions_e2e]))
+    issue_ms_e2e = float(np.median([r[1] for r in regions_e2e]))
     e2e_ms_sorted = sorted(r[0] for r in regions_e2e)
     last_e2e = e2e_no[0] - 1
     ctx.set_async(False)
@@ -412,7 +425,7 @@ def own_arm(args):
         parity["host_mode_equals_device_mode"] = True
     # (2) every rank holds every chromosome's statistics row after the all-reduce
     if world > 1:
-        for b in (0, 1):
+        for b in (0, 1, 2, 3):
             ctx.stats_bank(b)
             for c in wl.chroms:
                 assert int(ctx.stats_row(c.index)["window_per_gc"].sum()) == c.length, "statistics row %d wrong after the all-reduce" % c.index
@@ -493,12 +506,18 @@ def own_arm(args):
                       "cnvs": n_cnvs, "mappability": has_map, "min_mapq": mq, "samples": S,
                       "l2": "inputs+outputs per step (%.1f GB) larger than L2" % (wl.algorithmic_bytes_depth_pass() / 1e9)},
            "run": {"partition": "chromosomes over ranks, balanced by length (LPT + seeded local search: %.4f of ideal); one submission per rank and sample" % multi.balance([c.length for c in wl.chroms], parts), "slots": ctx_slots(ctx),
+                   "collective": None if world == 1 else ("rows stored into every rank's table by k_finalize over NVLink peer memory + one-warp flag exchange (cg_peer_*)"
+                                                         if collective != "nccl" else "ncclAllReduce(int64, sum) of the statistics table, issued by the library"),
                    "repeats": args.repeats, "ms_per_step_spread": spread(dev_ms), "host_issue_ms_per_step": round(issue_ms_dev / args.steps, 4),
-                   "resident_record_bytes": rec_bytes},
+                   "resident_record_bytes": rec_bytes,
+                   # host-side input preparation outside every timed region, once per BED file (the reference re-parses and re-paints
+                   # the BED per chromosome inside its find_SVs, svs.c:317-377): BED rows -> disjoint runs, this rank's chromosomes
+                   "mappability_flatten_ms_once": round(flatten_s * 1e3, 2) if has_map else None},
            "cnvs_per_s": round(n_cnvs * args.steps / (ms_dev / 1e3), 1),
            "cnvs_per_s_genotype_kernel_alone_rank0": round(sum(len(c.dels) + len(c.dups) for c in mine) / (cnv_ms / 1e3), 1) if cnv_ms > 0 else None,
            "e2e": {"value": round(e2e, 1), "unit": "reads/s", "ms_per_step": round(ms_e2e / args.steps, 4),
-                   "ms_per_step_spread": spread(e2e_ms_sorted), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "ms_per_step_spread": spread(e2e_ms_sorted), "host_issue_ms_per_step": round(issue_ms_e2e / args.steps, 4),
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "record_format": ("delta-coded positions (cg_encode_positions_delta)" if args.e2e_format == "delta" else "int32 position plane")
                                     + (" + uint8 mapq plane" if with_mapq else ""),
                    "bytes_per_read": round(rec_h2d_all / max(1.0, n_reads), 3), "annotation_resident": annot_resident,

@@ -24,6 +24,7 @@ CG_TILE = 16384
 CG_CHUNK = 2048
 CG_JMAX = 32
 CG_COMM_ID_BYTES = 128
+CG_PEER_HANDLE_BYTES = 64
 CG_JOB_ANNOTATION_RESIDENT = 1
 
 # struct layouts of include/conga_gpu.h as NumPy dtypes
@@ -91,6 +92,10 @@ SYMBOLS = {
     "cg_stats_reset": (_I, [_P]),
     "cg_stats_bank": (_I, [_P, _I]),
     "cg_stats_row": (_I, [_P, _I, _P]),
+    "cg_peer_export": (_I, [_P, _P]),
+    "cg_peer_connect": (_I, [_P, _I, _I, _P]),
+    "cg_peer_connect_local": (_I, [C.POINTER(_P), _I]),
+    "cg_peer_disconnect": (_I, [_P]),
     "cg_comm_unique_id": (_I, [_P]),
     "cg_comm_init_rank": (_I, [_P, _I, _I, _P]),
     "cg_comm_init_all": (_I, [C.POINTER(_P), _I]),
@@ -395,6 +400,22 @@ class Context:
         buf = C.create_string_buffer(uid, CG_COMM_ID_BYTES)
         self._ck(self.lib.cg_comm_init_rank(self.h, n_ranks, rank, C.cast(buf, C.c_void_p)))
 
+    def peer_export(self) -> bytes:
+        """cg_peer_export: the CUDA IPC handle of this context's reduced statistics tables (64 bytes)."""
+        buf = C.create_string_buffer(CG_PEER_HANDLE_BYTES)
+        self._ck(self.lib.cg_peer_export(self.h, C.cast(buf, C.c_void_p)))
+        return buf.raw
+
+    def peer_connect(self, n_ranks: int, rank: int, handles):
+        """cg_peer_connect: `handles` = peer_export() of every rank, in rank order (one process per GPU)."""
+        blob = b"".join(handles)
+        assert len(blob) == n_ranks * CG_PEER_HANDLE_BYTES
+        buf = C.create_string_buffer(blob, len(blob))
+        self._ck(self.lib.cg_peer_connect(self.h, n_ranks, rank, C.cast(buf, C.c_void_p)))
+
+    def peer_disconnect(self):
+        self._ck(self.lib.cg_peer_disconnect(self.h))
+
     def comm_destroy(self):
         self._ck(self.lib.cg_comm_destroy(self.h))
 
@@ -448,6 +469,15 @@ def decode_positions_delta(delta: np.ndarray, big: np.ndarray, anchors: np.ndarr
         esc = np.concatenate([[0], np.cumsum(delta == 255)])
         assert np.array_equal(anchors["big_before"], esc[blk].astype(np.uint32))
     return pos
+
+
+def peer_connect_local(contexts):
+    """cg_peer_connect_local: the contexts of ONE process become each other's peers (rank = position)."""
+    lib = load_library()
+    arr = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    rc = lib.cg_peer_connect_local(arr, len(contexts))
+    if rc != CG_OK:
+        raise CongaGpuError(rc, lib.cg_last_error(contexts[0].h).decode())
 
 
 def comm_unique_id() -> bytes:

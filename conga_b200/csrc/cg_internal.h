@@ -32,6 +32,7 @@
 /* Device-side condition bits, first control word of a job. */
 #define CG_FLAG_UNSORTED   1u         /* a pushed record had pos < its predecessor */
 #define CG_FLAG_RANGE      2u         /* a record or CNV outside [0, chrom_len) */
+#define CG_FLAG_PEER_TIMEOUT 8u       /* a peer's word did not arrive within the exchange kernel's patience */
 /* u32 control words of a job (cg_dev_job::ctl) */
 #define CG_CTL_WORDS 8
 #define CG_W_FLAGS   0
@@ -102,6 +103,8 @@ struct cg_sub {
     unsigned int*  fin_cnt;           /* [CG_JMAX] CTAs of k_finalize that have added their share (zero at rest) */
     unsigned int*  sticky;            /* context-wide word: CG_FLAG_RANGE is copied here */
     unsigned int*  h_flags;           /* NULL, or page-locked [n_jobs]: each job's flag word for the host */
+    int32_t        n_peer_rows;       /* 0, or ranks whose tables k_finalize stores a finished row into (this rank included) */
+    long long*     peer_rows[CG_MAX_PEERS];   /* row 0 of every rank's table for the current bank (peer memory over NVLink) */
 };
 
 /* Checked build (-DCG_CHECKED, scripts/build_checked.sh): every index the kernels form is asserted against the extent of
@@ -131,6 +134,8 @@ cudaError_t cgk_decode_delta(cudaStream_t s, const cg_sub& S, const cg_dev_job& 
 cudaError_t cgk_rare_scatter(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1, int n_sms);
 cudaError_t cgk_depth_pass(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
 cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1);
+struct cg_peer_flags { unsigned int* theirs[CG_MAX_PEERS]; unsigned int* mine; int n, rank; unsigned epoch; unsigned int* sticky; };
+cudaError_t cgk_peer_exchange(cudaStream_t s, const cg_peer_flags& f);
 cudaError_t cgk_prefix_from_depth(cudaStream_t s, const int16_t* depth, cg_counts k, int chunk0, int n_chunks, int32_t* prefix);
 cudaError_t cgk_expected_table(cudaStream_t s, const long long* stats_row, float* expected);
 int         cgk_carveout(void);                                   /* shared-memory carve-out (percent) every kernel asks for */

@@ -37,7 +37,7 @@
 #ifndef CG_NSLOT
 #define CG_NSLOT 6
 #endif
-#define CG_NBANK 2
+#define CG_NBANK 4
 #define CG_PASS_GRID_MAX (160 * 4)    /* rows of a slot's partial table: SMs x CTAs per SM the pass may ask for */
 
 struct cg_evpair { cudaEvent_t a, b; int slot; };
@@ -124,10 +124,15 @@ struct cg_ctx {
     long long* d_stats = nullptr;
     long long* d_stats_all = nullptr;
     int bank = 0;
-    cudaEvent_t ev_bank_read[CG_NBANK] = {nullptr, nullptr};     /* s_main: the collective that reads this bank */
-    bool bank_read[CG_NBANK] = {false, false};
+    cudaEvent_t ev_bank_read[CG_NBANK] = {};                     /* s_main: the collective that reads this bank */
+    bool bank_read[CG_NBANK] = {};
     cg_nccl_comm_t comm = nullptr;
     int comm_ranks = 0;
+    /* peer exchange (cg_peer_*): every rank's reduced tables and arrival words, mapped into this context's address space */
+    int n_peers = 0, peer_rank = 0;
+    long long* peer_base[CG_MAX_PEERS] = {};
+    bool peer_ipc[CG_MAX_PEERS] = {};         /* opened with cudaIpcOpenMemHandle: closed by cg_peer_disconnect */
+    unsigned int epoch[CG_NBANK] = {};
 
     unsigned int* d_sticky = nullptr;         /* [0] CG_FLAG_RANGE seen since the last report */
 
@@ -305,7 +310,8 @@ cg_ctx* cg_create(int device)
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);     /* hi is the numerically smaller one */
     const size_t table_bytes = sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * CG_NBANK;
-    bool ok = cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_lo) == cudaSuccess
+    /* cg_stream carries the collective: high priority, so that its kernel is placed in the first gap the passes leave */
+    bool ok = cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_hi) == cudaSuccess
         && cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) == cudaSuccess
         && cudaMalloc(&c->d_stats, table_bytes) == cudaSuccess
         && cudaMemset(c->d_stats, 0, table_bytes) == cudaSuccess
@@ -355,6 +361,7 @@ void cg_destroy(cg_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+    cg_peer_disconnect(c);
     cg_comm_destroy(c);
     for (auto& ev : c->ev_live) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
     for (auto& ev : c->ev_free) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
@@ -460,6 +467,11 @@ int cg_sync(cg_ctx* c)
     if (rc) return rc;
     if ((rc = settle_samples(c)) != CG_OK) return rc;
     prof_collect(c);
+    if (c->n_peers) {                          /* a peer's arrival word that never came (k_peer_exchange gave up) */
+        CU(c, cudaMemcpyAsync(c->h_flags, c->d_sticky, 4, cudaMemcpyDeviceToHost, c->s_main));
+        CU(c, cudaStreamSynchronize(c->s_main));
+        if (c->h_flags[0] & CG_FLAG_PEER_TIMEOUT) return fail(c, CG_ECUDA, "cg_sync: the peer exchange timed out: a rank did not deliver its rows");
+    }
     if (c->ptr_mode == CG_PTR_HOST) return report_sticky(c, "cg_sync");
     return CG_OK;
 }
@@ -572,6 +584,8 @@ static void fill_sub(cg_ctx* c, cg_slot& s, int n_jobs, int n_work, int n_space,
     S.sctl = s.d_ctl + CG_CTL_WORDS * CG_JMAX;
     S.fin_acc = s.d_fin;
     S.fin_cnt = reinterpret_cast<unsigned int*>(s.d_fin + CG_JMAX * 256);
+    S.n_peer_rows = c->n_peers;
+    for (int r = 0; r < c->n_peers; r++) S.peer_rows[r] = c->peer_base[r] + (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
     S.sticky = c->d_sticky;
 }
 
@@ -1235,7 +1249,7 @@ int cg_device_arrays(cg_ctx* c, const int16_t** depth, const float** expected)
 /* ---- statistics tables and the collective -------------------------------------------------- */
 static long long* table_of(cg_ctx* c, int bank)
 {
-    return (c->comm ? c->d_stats_all : c->d_stats) + (size_t)bank * CG_MAX_CHROMS * CG_STATS_WORDS;
+    return ((c->comm || c->n_peers) ? c->d_stats_all : c->d_stats) + (size_t)bank * CG_MAX_CHROMS * CG_STATS_WORDS;
 }
 
 int cg_stats_table(cg_ctx* c, void** device_ptr, int32_t* n_rows)
@@ -1265,7 +1279,7 @@ int cg_stats_reset(cg_ctx* c)
 int cg_stats_bank(cg_ctx* c, int bank)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (bank < 0 || bank >= CG_NBANK) return fail(c, CG_EINVAL, "bank %d must be 0 or 1", bank);
+    if (bank < 0 || bank >= CG_NBANK) return fail(c, CG_EINVAL, "bank %d must be 0..%d", bank, CG_NBANK - 1);
     if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_stats_bank inside a chromosome");
     c->bank = bank;
     return CG_OK;
@@ -1316,10 +1330,14 @@ static int nccl_load(cg_ctx* c)
     return CG_OK;
 }
 
+#define CG_TABLE_WORDS ((size_t)CG_STATS_WORDS * CG_MAX_CHROMS * CG_NBANK)       /* int64 words of the tables of all banks */
+static inline unsigned int* arrival_words(long long* tables) { return reinterpret_cast<unsigned int*>(tables + CG_TABLE_WORDS); }
+
 static int comm_tables(cg_ctx* c)
 {
     if (c->d_stats_all) return CG_OK;
-    const size_t bytes = sizeof(long long) * CG_STATS_WORDS * CG_MAX_CHROMS * CG_NBANK;
+    /* the reduced tables, and behind them the peers' arrival words [bank][rank] of the peer exchange */
+    const size_t bytes = sizeof(long long) * CG_TABLE_WORDS + sizeof(unsigned int) * CG_NBANK * CG_MAX_PEERS;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMalloc(&c->d_stats_all, bytes));
     CU(c, cudaMemset(c->d_stats_all, 0, bytes));
@@ -1327,6 +1345,86 @@ static int comm_tables(cg_ctx* c)
 }
 
 extern "C" {
+
+int cg_peer_export(cg_ctx* c, void* handle)
+{
+    if (!c || !handle) return fail(c, CG_EINVAL, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= CG_PEER_HANDLE_BYTES, "IPC handle size");
+    int rc = comm_tables(c);
+    if (rc) return rc;
+    cudaIpcMemHandle_t h;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaIpcGetMemHandle(&h, c->d_stats_all));
+    memset(handle, 0, CG_PEER_HANDLE_BYTES);
+    memcpy(handle, &h, sizeof h);
+    return CG_OK;
+}
+
+static int peer_ready(cg_ctx* c, int n_ranks, int rank)
+{
+    if (n_ranks < 1 || n_ranks > CG_MAX_PEERS || rank < 0 || rank >= n_ranks) return fail(c, CG_EINVAL, "rank %d of %d (at most %d)", rank, n_ranks, CG_MAX_PEERS);
+    if (c->n_peers || c->comm) return fail(c, CG_EINVAL, "the context already has peers or a communicator");
+    if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_peer_connect inside a chromosome");
+    CU(c, cudaSetDevice(c->device));
+    int rc = sync_all(c);
+    if (rc) return rc;
+    return comm_tables(c);
+}
+
+int cg_peer_connect(cg_ctx* c, int n_ranks, int rank, const void* handles)
+{
+    if (!c || !handles) return fail(c, CG_EINVAL, "null argument");
+    int rc = peer_ready(c, n_ranks, rank);
+    if (rc) return rc;
+    for (int r = 0; r < n_ranks; r++) {
+        if (r == rank) { c->peer_base[r] = c->d_stats_all; c->peer_ipc[r] = false; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char*>(handles) + (size_t)r * CG_PEER_HANDLE_BYTES, sizeof h);
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            for (int q = 0; q < r; q++) if (c->peer_ipc[q]) { cudaIpcCloseMemHandle(c->peer_base[q]); c->peer_ipc[q] = false; }
+            return fail(c, CG_ECUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+        }
+        c->peer_base[r] = static_cast<long long*>(p); c->peer_ipc[r] = true;
+    }
+    c->n_peers = n_ranks; c->peer_rank = rank;
+    return CG_OK;
+}
+
+int cg_peer_connect_local(cg_ctx** ctxs, int n)
+{
+    if (!ctxs || n < 1 || n > CG_MAX_PEERS) return fail(nullptr, CG_EINVAL, "bad argument");
+    int rc;
+    for (int i = 0; i < n; i++) {
+        if (!ctxs[i]) return fail(nullptr, CG_EINVAL, "context %d is null", i);
+        if ((rc = peer_ready(ctxs[i], n, i)) != CG_OK) return rc;
+    }
+    for (int i = 0; i < n; i++) {
+        cudaSetDevice(ctxs[i]->device);
+        for (int r = 0; r < n; r++) {
+            if (ctxs[r]->device != ctxs[i]->device) {
+                const cudaError_t e = cudaDeviceEnablePeerAccess(ctxs[r]->device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(ctxs[i], CG_ECUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", ctxs[i]->device, ctxs[r]->device, cudaGetErrorString(e));
+                cudaGetLastError();
+            }
+            ctxs[i]->peer_base[r] = ctxs[r]->d_stats_all; ctxs[i]->peer_ipc[r] = false;
+        }
+        ctxs[i]->n_peers = n; ctxs[i]->peer_rank = i;
+    }
+    return CG_OK;
+}
+
+int cg_peer_disconnect(cg_ctx* c)
+{
+    if (!c) return fail(nullptr, CG_EINVAL, "null context");
+    if (!c->n_peers) return CG_OK;
+    cudaSetDevice(c->device);
+    sync_all(c);
+    for (int r = 0; r < c->n_peers; r++) if (c->peer_ipc[r]) { cudaIpcCloseMemHandle(c->peer_base[r]); c->peer_ipc[r] = false; }
+    c->n_peers = 0;
+    return CG_OK;
+}
 
 int cg_comm_unique_id(void* id)
 {
@@ -1385,12 +1483,25 @@ int cg_comm_destroy(cg_ctx* c)
 static int allreduce_one(cg_ctx* c, int32_t n_rows)
 {
     if (!c) return fail(nullptr, CG_EINVAL, "null context");
-    if (!c->comm) return fail(c, CG_EINVAL, "cg_stats_allreduce without a communicator (cg_comm_init_rank)");
+    if (!c->comm && !c->n_peers) return fail(c, CG_EINVAL, "cg_stats_allreduce without a communicator (cg_comm_init_rank) or peers (cg_peer_connect)");
     if (n_rows < 0 || n_rows > CG_MAX_CHROMS) return fail(c, CG_EINVAL, "n_rows %d", n_rows);
     if (c->in_chrom && !c->finished) return fail(c, CG_EINVAL, "cg_stats_allreduce inside a chromosome");
     CU(c, cudaSetDevice(c->device));
     int rc = cg_join(c);                       /* cg_stream now waits for every row written so far */
     if (rc) return rc;
+    if (c->n_peers) {
+        /* the rows are already in every rank's table (k_finalize stored them there): tell the peers, wait for theirs */
+        cg_peer_flags f;
+        memset(&f, 0, sizeof f);
+        for (int r = 0; r < c->n_peers; r++) f.theirs[r] = arrival_words(c->peer_base[r]) + (size_t)c->bank * CG_MAX_PEERS;
+        f.mine = arrival_words(c->d_stats_all) + (size_t)c->bank * CG_MAX_PEERS;
+        f.n = c->n_peers; f.rank = c->peer_rank; f.epoch = ++c->epoch[c->bank]; f.sticky = c->d_sticky;
+        CU(c, cgk_peer_exchange(c->s_main, f));
+        CU(c, cudaEventRecord(c->ev_bank_read[c->bank], c->s_main));
+        c->bank_read[c->bank] = true;
+        c->launch_count += 1;
+        return CG_OK;
+    }
     if (n_rows == 0) return CG_OK;
     const size_t off = (size_t)c->bank * CG_MAX_CHROMS * CG_STATS_WORDS;
     const int e = g_nccl.AllReduce(c->d_stats + off, c->d_stats_all + off, (size_t)n_rows * CG_STATS_WORDS, /* ncclInt64 */ 4, /* ncclSum */ 0,

@@ -815,6 +815,10 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
     if (tid < CG_STATS_WORDS) {
         J.stats_row[tid] = row[tid];
         if (J.row_out) J.row_out[tid] = row[tid];
+        /* the collective, fused: the finished row goes straight into every rank's table (peer memory over NVLink;
+         * rows are disjoint per rank, so there is nothing to reduce) */
+        for (int p = 0; p < S.n_peer_rows; p++) S.peer_rows[p][(size_t)J.chr_index * CG_STATS_WORDS + tid] = row[tid];
+        if (S.n_peer_rows) __threadfence_system();
     }
     if (tid < CG_GC_BINS) J.expected[tid] = expected_of(row[tid], row[CG_GC_BINS + tid], tid);
     if (tid == 0) {
@@ -832,6 +836,36 @@ k_finalize(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_job 
 cudaError_t cgk_finalize(cudaStream_t s, const cg_sub& S, const cg_dev_job& J1)
 {
     k_finalize<<<dim3((unsigned)S.n_jobs, FIN_Y), FIN_T, 0, s>>>(S, J1);
+    return cudaGetLastError();
+}
+
+/* What is left of the collective when k_finalize stores the rows into the peers' tables itself: one warp tells every
+ * peer "my rows of this sample are in your table" (flags[bank][my rank] = epoch in the peer's memory) and waits for
+ * the same word from every peer.  Runs on cg_stream behind cg_join, i.e. behind every finalize of the sample. */
+__global__ void k_peer_exchange(const __grid_constant__ cg_peer_flags f)
+{
+    const int t = threadIdx.x;
+    if (t >= f.n) return;
+    __threadfence_system();
+    if (t != f.rank) {
+        volatile unsigned int* dst = f.theirs[t] + f.rank;
+        *dst = f.epoch;
+    }
+    __threadfence_system();
+    if (t != f.rank) {
+        volatile unsigned int* src = f.mine + t;
+        const long long t0 = clock64();
+        while ((int)(*src - f.epoch) < 0) {
+            if (clock64() - t0 > 20000000000ll) { atomicOr(f.sticky, CG_FLAG_PEER_TIMEOUT); break; }     /* ~10 s: a peer is gone */
+            __nanosleep(200);
+        }
+    }
+    __threadfence_system();
+}
+
+cudaError_t cgk_peer_exchange(cudaStream_t s, const cg_peer_flags& f)
+{
+    k_peer_exchange<<<1, 32, 0, s>>>(f);
     return cudaGetLastError();
 }
 

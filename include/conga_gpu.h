@@ -306,10 +306,10 @@ int cg_device_arrays(cg_ctx* ctx, const int16_t** depth, const float** expected)
  * this is the table cg_stats_allreduce fills: every rank holds every chromosome's row. */
 int cg_stats_table(cg_ctx* ctx, void** device_ptr, int32_t* n_rows);
 int cg_stats_reset(cg_ctx* ctx);
-/* Two tables ("banks", 0 and 1; 0 at creation).  The chromosomes begun after cg_stats_bank write
+/* Four tables ("banks", 0..3; 0 at creation).  The chromosomes begun after cg_stats_bank write
  * their rows to `bank`, and cg_stats_table / cg_stats_row / cg_stats_allreduce refer to it.  A driver that
- * processes sample after sample alternates banks: the collective over sample k's table is then in flight
- * while sample k+1's chromosomes already fill the other bank.  Selecting a bank clears nothing: a row holds
+ * processes sample after sample rotates through the banks (k mod 4): the collective over sample k's table is then in
+ * flight while the chromosomes of the next three samples already fill the other banks.  Selecting a bank clears nothing: a row holds
  * what the last chromosome with that chr_index left there (cg_stats_reset zeroes the current bank); a
  * chromosome that writes into a bank a collective is still reading waits for that collective on the device. */
 int cg_stats_bank(cg_ctx* ctx, int bank);
@@ -326,6 +326,26 @@ int cg_stats_row(cg_ctx* ctx, int chr_index, cg_chrom_stats* out);
  * into the table cg_stats_table / cg_stats_row then refer to.  Nothing blocks; every rank must pass the same
  * n_rows.  The reduced rows are bookkeeping (conga.log, read_distribution.c:41): no genotype of any
  * chromosome depends on another chromosome's row (read_distribution.c:49-84 rebuilds the table per chromosome). */
+/* ---- the same exchange fused into the path's own kernel: peer stores over NVLink instead of a collective kernel ----
+ * The rows are disjoint per rank (a chromosome is owned by one rank), so nothing has to be reduced: with peer
+ * memory connected, k_finalize — which has just built a chromosome's row — stores it straight into the table of
+ * EVERY rank (its own included), 1632 bytes per peer over NVLink / NVSwitch, and cg_stats_allreduce shrinks to a
+ * one-warp kernel on cg_stream that tells every peer "my rows of this sample are in your table" and waits for
+ * the same word from all of them.  cg_stats_table / cg_stats_row read the table the peers write.  Measured on
+ * B200: the NCCL all-reduce of the 36 KB table costs a step 29 us (it needs an empty SM under a persistent pass);
+ * the flag exchange does not.  NCCL stays available (cg_comm_*) and is what the two are checked against.
+ *   one process per GPU:  cg_peer_export fills CG_PEER_HANDLE_BYTES (a CUDA IPC handle) on every rank; the
+ *                         handles of all ranks, in rank order, go to cg_peer_connect on every rank;
+ *   one process, n GPUs:  cg_peer_connect_local(ctxs, n), rank = position in ctxs.
+ * A bank's rows are overwritten by a peer as soon as that peer starts the sample that uses the bank again (four
+ * samples later): a driver that reads rows on the host does so before it lets any rank go that far. */
+#define CG_PEER_HANDLE_BYTES 64
+#define CG_MAX_PEERS 16
+int cg_peer_export(cg_ctx* ctx, void* handle /* CG_PEER_HANDLE_BYTES */);
+int cg_peer_connect(cg_ctx* ctx, int n_ranks, int rank, const void* handles /* n_ranks x CG_PEER_HANDLE_BYTES */);
+int cg_peer_connect_local(cg_ctx** ctxs, int n);
+int cg_peer_disconnect(cg_ctx* ctx);
+
 #define CG_COMM_ID_BYTES 128
 int cg_comm_unique_id(void* id /* CG_COMM_ID_BYTES */);
 int cg_comm_init_rank(cg_ctx* ctx, int n_ranks, int rank, const void* id);

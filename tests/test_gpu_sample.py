@@ -275,3 +275,46 @@ def test_push_reads_compact_per_chromosome(ctx, oracle):
         assert np.array_equal(ctx.download_depth(), depth)
     finally:
         ctx.set_pointer_mode(CG_PTR_HOST)
+
+
+def test_peer_exchange_two_contexts(ctx, oracle):
+    """The fused collective (cg_peer_*): k_finalize stores a finished row into every rank's table, cg_stats_allreduce is
+    a flag exchange.  Two contexts of this process are each other's peers (cg_peer_connect_local; on one GPU here, over
+    NVLink between GPUs of a box); each runs its own chromosomes of two samples through alternating banks, and afterwards
+    BOTH hold every chromosome's row of both samples."""
+    from conga_b200 import Context, peer_connect_local
+    rng = np.random.default_rng(31)
+    chroms = [synth._chrom("p%d" % i, i, L, rng, max(10, L // 40), 5, 2, False, cnv_hi=max(1500, L // 8))
+              for i, L in enumerate([400_000, 90_000, 250_000, 30_000, 120_000])]
+    want = [oracle.chromosome(ch, -1, False)[1] for ch in chroms]
+    other = Context(0)
+    try:
+        ranks = [ctx, other]
+        peer_connect_local(ranks)
+        mine = [[chroms[0], chroms[3]], [chroms[1], chroms[2], chroms[4]]]
+        samples = [[DeviceSample(m, -1) for m in mine] for _ in range(2)]
+        for c in ranks:
+            c.set_pointer_mode(CG_PTR_DEVICE)
+        for k, smp in enumerate(samples):
+            for c, s in zip(ranks, smp):
+                c.stats_bank(k)
+                c.run_chromosomes(s.jobs)
+                c.stats_allreduce(len(chroms))           # nothing blocks: the other rank's exchange is issued right behind
+        for c in ranks:
+            c.sync()
+        for c in ranks:
+            for bank in (0, 1):
+                c.stats_bank(bank)
+                for ch, st_ref in zip(chroms, want):
+                    got = c.stats_row(ch.index)
+                    for f in ("rd_per_gc", "window_per_gc", "rd_cnt", "reads_passed"):
+                        assert np.array_equal(got[f], st_ref[f]), (bank, ch.name, f)
+        for smp in samples:                              # and the calls are what a single rank computes
+            for m, s in zip(mine, smp):
+                check_against_oracle(oracle, m, s.results(), -1)
+    finally:
+        for c in (ctx, other):
+            c.set_pointer_mode(CG_PTR_HOST)
+            c.stats_bank(0)
+        ctx.lib.cg_peer_disconnect(ctx.h)
+        other.close()
