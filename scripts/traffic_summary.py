@@ -14,6 +14,8 @@ wr = sum(d["dram__bytes_write.sum"] for d in per.values())
 t = sum(d["gpu__time_duration.sum"] for d in per.values())
 out = {"kernel": "k_depth_pass", "launches": n, "dram_bytes_read_per_launch": rd / n, "dram_bytes_write_per_launch": wr / n,
        "traffic_bytes_per_launch": (rd + wr) / n, "ncu_time_s_per_launch": t / n,
-       "source": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none, 22 launches of one C2 sample (%s)" % tag}
+       "workload": sys.argv[3] if len(sys.argv) > 3 else "c3",
+       "source": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none, %d launches of k_depth_pass, one per sample (%s); "
+                 "bytes still dirty in the 126 MB L2 when a launch ends are not counted" % (n, tag)}
 json.dump(out, open("profiles/traffic.json", "w"), indent=1)
 print(json.dumps(out))
