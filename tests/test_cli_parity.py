@@ -213,10 +213,11 @@ def test_rp_without_dups_changes_nothing(tools):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
-@pytest.mark.parametrize("workload", ["c1", "c2"])
+@pytest.mark.parametrize("workload", ["c1", "c2", "c3"])
 def test_baseline_configs_at_full_size_whole_program(tools, workload):
-    """BASELINE.json configs[0] and configs[1] at their full sizes (C2: 22 GRCh37-length chromosomes, 4.8 M reads,
-    10 k deletions + 5 k duplications, mappability BED): every byte of the three BED files and every conga.log
+    """BASELINE.json configs[0], configs[1] and configs[2] at their full sizes (C2: 22 GRCh37-length chromosomes, 4.8 M
+    reads, 10 k deletions + 5 k duplications, mappability BED; C3: 43 M reads at 1x, 33 k deletions + 6 k duplications —
+    about 75 s, half of it building the BAM): every byte of the three BED files and every conga.log
     chromosome line equals what the unmodified reference program writes from the same BAM."""
     import json
     import sys
