@@ -30,7 +30,7 @@ def _rank_main(rank, world, port, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         chroms = _workload()
-        parts = multi.lpt_partition([c.length for c in chroms], world)
+        parts = multi.balanced_partition([c.length for c in chroms], world, iters=20_000, seeds=2)      # what bench.py shards by
         orc = oracle_py.load()
         table = torch.zeros((N_CHROM, multi.STATS_WORDS), dtype=torch.int64)
         local = {}

@@ -38,7 +38,8 @@ def test_oracle_matches_reference_dump(path, oracle):
             if g.with_map:
                 assert out["mappability"].tobytes() == ref["mappability"].tobytes()
             for f in ("lhomo", "lhetero", "lnone", "score"):
-                np.testing.assert_allclose(out[f], ref[f], rtol=1e-13, atol=0, equal_nan=True)
+                # same expression, same glibc as the reference dump: every bit of every double (the sign of -0.0 included)
+                assert np.ascontiguousarray(out[f]).tobytes() == np.ascontiguousarray(ref[f]).tobytes(), f
 
 
 def test_reference_sorted_and_filtered_cnvs():
