@@ -217,10 +217,28 @@ def own_arm(args):
             ctx.comm_init_rank(world, rank, box[0])
         else:
             # fused: k_finalize stores every finished row into every rank's table over NVLink (CUDA IPC peer memory);
-            # cg_stats_allreduce is then a one-warp flag exchange on cg_stream
+            # cg_stats_allreduce is then a one-warp flag exchange on cg_stream.  Should peer memory not be available on a
+            # box (IPC handles refused), every rank falls back to the NCCL form together, and the line says so.
             handles = [None] * world
-            dist.all_gather_object(handles, ctx.peer_export(), group=cpu_group)
-            ctx.peer_connect(world, rank, handles)
+            try:
+                mine_h = ctx.peer_export()
+            except Exception:
+                mine_h = None
+            dist.all_gather_object(handles, mine_h, group=cpu_group)
+            ok = all(h is not None for h in handles)
+            if ok:
+                try:
+                    ctx.peer_connect(world, rank, handles)
+                except Exception:
+                    ok = False
+            oks = [None] * world
+            dist.all_gather_object(oks, ok, group=cpu_group)
+            if not all(oks):
+                ctx.peer_disconnect()
+                collective = "nccl (peer memory unavailable)"
+                box = [comm_unique_id() if rank == 0 else None]
+                dist.broadcast_object_list(box, src=0, group=cpu_group)
+                ctx.comm_init_rank(world, rank, box[0])
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     step_no = [0]
     no_coll = bool(os.environ.get("BENCH_DEBUG_NO_COLLECTIVE"))       # tuning only: what the collective costs a step (the row check below then fails)
@@ -507,7 +525,7 @@ def own_arm(args):
                       "l2": "inputs+outputs per step (%.1f GB) larger than L2" % (wl.algorithmic_bytes_depth_pass() / 1e9)},
            "run": {"partition": "chromosomes over ranks, balanced by length (LPT + seeded local search: %.4f of ideal); one submission per rank and sample" % multi.balance([c.length for c in wl.chroms], parts), "slots": ctx_slots(ctx),
                    "collective": None if world == 1 else ("rows stored into every rank's table by k_finalize over NVLink peer memory + one-warp flag exchange (cg_peer_*)"
-                                                         if collective != "nccl" else "ncclAllReduce(int64, sum) of the statistics table, issued by the library"),
+                                                         if not collective.startswith("nccl") else "ncclAllReduce(int64, sum) of the statistics table, issued by the library [%s]" % collective),
                    "repeats": args.repeats, "ms_per_step_spread": spread(dev_ms), "host_issue_ms_per_step": round(issue_ms_dev / args.steps, 4),
                    "resident_record_bytes": rec_bytes,
                    # host-side input preparation outside every timed region, once per BED file (the reference re-parses and re-paints
