@@ -205,6 +205,16 @@ def own_arm(args):
         r_, n_ = (int(x) for x in args.emulate_rank.split("/"))
         mine = [wl.chroms[i] for i in multi.balanced_partition([c.length for c in wl.chroms], n_)[r_]]
     has_map, mq = wl.has_mappability, wl.mq_threshold
+    # A rank of an N-GPU job holds 22/N chromosomes: a sample is then a small submission (C3 at N = 8: 0.15 ms of
+    # pass per sample) and the fixed cost of a set of launches shows.  A submission carries up to 32 jobs, so the
+    # resident leg hands over several consecutive samples per cg_run_chromosomes call: the rows of the g-th sample of a
+    # submission live at chr_index + g * n_chrom of the bank, results in buffers of their own.
+    KSUB = args.samples_per_submission
+    jobs_max = max(1, max(len(p) for p in (multi.balanced_partition([c.length for c in wl.chroms], int(args.emulate_rank.split("/")[1]))
+                                             if (args.emulate_rank and world == 1) else parts)))      # the same on every rank: the exchange is per submission
+    if KSUB <= 0:
+        KSUB = min(8, 32 // jobs_max) if (world > 1 or args.emulate_rank) else 1
+    KSUB = max(1, min(KSUB, 32 // jobs_max))
 
     collective = os.environ.get("BENCH_COLLECTIVE", "peer")       # "nccl": the library's ncclAllReduce instead (the checked baseline)
     ctx = Context(local)                      # raises if libconga_gpu.so or the GPU is missing
@@ -272,32 +282,47 @@ def own_arm(args):
         res.append(dict(c=c, gc=to_dev(c.gc), dels=to_dev(c.dels), dups=to_dev(c.dups),
                         runs=to_dev(runs) if runs is not None and len(runs) else None,
                         n_runs=0 if runs is None else len(runs), runs_host=runs,
-                        out_del=torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev),
-                        out_dup=torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev),
-                        stats=torch.zeros(STATS_DT.itemsize, dtype=torch.uint8, device=dev),
+                        out_del=[torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
+                        out_dup=[torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
+                        stats=[torch.zeros(STATS_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
                         reads=[to_dev(sample_records(k, s)) for s in range(S)], n_reads=[len(sample_records(k, s)) for s in range(S)]))
     torch.cuda.synchronize()
 
-    def device_jobs(s):
+    def device_jobs(s, g):
+        """the jobs of sample s as the g-th sample of a submission"""
         if not res:
             return np.zeros(0, dtype=CHROM_JOB_DT)
-        return np.concatenate([chrom_job(r["c"].index, r["c"].length, r["gc"], len(r["c"].gc), mq,
+        return np.concatenate([chrom_job(r["c"].index + g * n_chrom, r["c"].length, r["gc"], len(r["c"].gc), mq,
                                          None if planes else r["reads"][s], r["n_reads"][s], r["runs"], r["n_runs"], has_map,
-                                         r["dels"], len(r["c"].dels), r["out_del"], r["dups"], len(r["c"].dups), r["out_dup"], r["stats"],
+                                         r["dels"], len(r["c"].dels), r["out_del"][g], r["dups"], len(r["c"].dups), r["out_dup"][g], r["stats"][g],
                                          reads_pos=r["reads"][s] if planes else None) for r in res])
-    jobs_dev = [device_jobs(s) for s in range(S)]
+    jobs_dev = {}
+
+    def group_jobs(s0, n):
+        """one submission: samples s0 .. s0 + n - 1 (mod S)"""
+        key = (s0 % S, n)
+        if key not in jobs_dev:
+            jobs_dev[key] = np.concatenate([device_jobs((s0 + g) % S, g) for g in range(n)])
+        return jobs_dev[key]
     reads_of_sample = [sum(len(sample_records(k, s)) for k in range(len(mine))) for s in range(S)]
+    last_group = [0]
 
-    def step_device():
-        k = step_no[0]
-        step_no[0] += 1
-        if world > 1:
-            ctx.stats_bank(k & 3)             # the all-reduce of sample k is in flight while the next three samples fill the other banks
-        ctx.run_chromosomes(jobs_dev[k % S])  # ONE submission: every kernel of the path once for all chromosomes of this rank
-        if world > 1 and not no_coll:
-            ctx.stats_allreduce(n_chrom)
+    def steps_device(k_steps):
+        """k_steps samples, KSUB per submission"""
+        done = 0
+        while done < k_steps:
+            n = min(KSUB, k_steps - done)
+            k = step_no[0]
+            step_no[0] += n
+            done += n
+            if world > 1:
+                ctx.stats_bank((k // KSUB) & 3)   # the exchange of a submission's rows is in flight while the next three fill the other banks
+            ctx.run_chromosomes(group_jobs(k, n)) # ONE submission: every kernel of the path once for all chromosomes of this rank
+            last_group[0] = n
+            if world > 1 and not no_coll:
+                ctx.stats_allreduce(n_chrom * n)
 
-    def timed(step_fn, k, finish=None):
+    def timed(steps_fn, k, finish=None):
         """K steps bracketed by barrier + synchronize; device time by CUDA events on cg_stream (which cg_join orders
         behind every stream of the context), max over ranks; also the host time spent issuing the K steps."""
         barrier()
@@ -307,8 +332,7 @@ def own_arm(args):
         with torch.cuda.stream(ext):
             e0.record()
         t0 = time.perf_counter()
-        for _ in range(k):
-            step_fn()
+        steps_fn(k)
         ctx.join()
         issue_ms = (time.perf_counter() - t0) * 1e3
         with torch.cuda.stream(ext):
@@ -321,27 +345,27 @@ def own_arm(args):
         return max_over_ranks([e0.elapsed_time(e1), issue_ms])
 
     ctx.set_pointer_mode(CG_PTR_DEVICE)
-    for _ in range(max(3, args.warmup)):
-        step_device()
+    steps_device(max(3, args.warmup) * KSUB)
     ctx.sync()
     sampler = make_sampler(local)
     if rank == 0:
         sampler.start()
     launches0 = ctx.launch_count
-    regions = [timed(step_device, args.steps) for _ in range(args.repeats)]
+    regions = [timed(steps_device, args.steps) for _ in range(args.repeats)]
     launches = (ctx.launch_count - launches0) // args.repeats
     last_sample_dev = (step_no[0] - 1) % S
     dev_ms = sorted(r[0] for r in regions)
     ms_dev = float(np.median(dev_ms))
     issue_ms_dev = float(np.median([r[1] for r in regions]))
     # the calls of the resident leg's last step, for the parity checks below
-    dev_calls = {r["c"].index: (r["out_del"].cpu().numpy()[: len(r["c"].dels) * CALL_DT.itemsize].view(CALL_DT).copy(),
-                                r["out_dup"].cpu().numpy()[: len(r["c"].dups) * CALL_DT.itemsize].view(CALL_DT).copy()) for r in res}
+    g_last = last_group[0] - 1                 # ... which was the g_last-th sample of its submission
+    dev_calls = {r["c"].index: (r["out_del"][g_last].cpu().numpy()[: len(r["c"].dels) * CALL_DT.itemsize].view(CALL_DT).copy(),
+                                r["out_dup"][g_last].cpu().numpy()[: len(r["c"].dups) * CALL_DT.itemsize].view(CALL_DT).copy()) for r in res}
     # same K steps again with per-launch CUDA events on the context's streams -> roofline of the depth pass.  The
     # slots are chained while profiling (kernels timed alone), so this leg is NOT the one `value` comes from.
     ctx.set_profiling(True)
     ctx.kernel_times()
-    timed(step_device, args.steps)
+    timed(steps_device, args.steps)
     k_ms, k_n = ctx.kernel_times()
     ctx.set_profiling(False)
     clocks = sampler.stop() if rank == 0 else None
@@ -423,10 +447,13 @@ def own_arm(args):
         if world > 1:
             ctx.stats_allreduce(n_chrom)
 
-    for _ in range(max(3, args.warmup)):      # submissions rotate through the slots: their upload buffers settle within a few samples
-        step_e2e()
+    def steps_e2e(k_steps):
+        for _ in range(k_steps):
+            step_e2e()
+
+    steps_e2e(max(3, args.warmup))            # submissions rotate through the slots: their upload buffers settle within a few samples
     ctx.sync()
-    regions_e2e = [timed(step_e2e, args.steps) for _ in range(max(3, args.repeats // 2))]
+    regions_e2e = [timed(steps_e2e, args.steps) for _ in range(max(3, args.repeats // 2))]
     ms_e2e = float(np.median([r[0] for r in regions_e2e]))
     issue_ms_e2e = float(np.median([r[1] for r in regions_e2e]))
     e2e_ms_sorted = sorted(r[0] for r in regions_e2e)
@@ -497,7 +524,7 @@ def own_arm(args):
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     pass_ms, pass_n = k_ms[1], max(1, k_n[1])
-    achieved = alg * pass_n / (pass_ms / 1e3) / 1e9 if pass_ms > 0 else 0.0
+    achieved = alg * args.steps / (pass_ms / 1e3) / 1e9 if pass_ms > 0 else 0.0      # a launch carries KSUB samples' worth of alg
     # DRAM bytes per launch from the committed ncu capture of this command (profiles/traffic.json, written by
     # scripts/traffic_summary.py from scripts/gpu_traffic.sh); only meaningful for the workload it was taken on
     traffic, traffic_src = None, None
@@ -510,7 +537,7 @@ def own_arm(args):
                 "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "timed": "profiling leg: per-launch CUDA events on the launching stream, slots chained so that the pass runs alone; "
                          "`value` comes from the pipelined leg where consecutive samples overlap",
-                "algorithmic_bytes_per_launch": int(alg), "launches": int(pass_n), "avg_launch_ms": round(pass_ms / pass_n, 4),
+                "algorithmic_bytes_per_launch": int(alg * args.steps / pass_n), "launches": int(pass_n), "avg_launch_ms": round(pass_ms / pass_n, 4),
                 "frac_whole_step": round(alg / (ms_dev / args.steps / 1e3) / 1e9 / peak, 4),
                 "kernel_ms_per_step": {"init+mark+finalize": round(k_ms[0] / args.steps, 4), "depth_pass": round(k_ms[1] / args.steps, 4),
                                        "run_index+genotype": round(k_ms[2] / args.steps, 4)}}
@@ -523,7 +550,8 @@ def own_arm(args):
            "config": {"workload": wl.name, "chromosomes": n_chrom, "positions": wl.n_positions, "reads": int(round(n_reads)),
                       "cnvs": n_cnvs, "mappability": has_map, "min_mapq": mq, "samples": S,
                       "l2": "inputs+outputs per step (%.1f GB) larger than L2" % (wl.algorithmic_bytes_depth_pass() / 1e9)},
-           "run": {"partition": "chromosomes over ranks, balanced by length (LPT + seeded local search: %.4f of ideal); one submission per rank and sample" % multi.balance([c.length for c in wl.chroms], parts), "slots": ctx_slots(ctx),
+           "run": {"partition": "chromosomes over ranks, balanced by length (LPT + seeded local search: %.4f of ideal); one submission per rank and %s" % (multi.balance([c.length for c in wl.chroms], parts), "sample" if KSUB == 1 else "%d consecutive samples (resident leg)" % KSUB),
+                   "samples_per_submission": KSUB, "slots": ctx_slots(ctx),
                    "collective": None if world == 1 else ("rows stored into every rank's table by k_finalize over NVLink peer memory + one-warp flag exchange (cg_peer_*)"
                                                          if not collective.startswith("nccl") else "ncclAllReduce(int64, sum) of the statistics table, issued by the library [%s]" % collective),
                    "repeats": args.repeats, "ms_per_step_spread": spread(dev_ms), "host_issue_ms_per_step": round(issue_ms_dev / args.steps, 4),
@@ -728,6 +756,9 @@ def main():
                          "int32 position plane (4); auto = delta when the mean gap between reads is below 200 bases")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--emulate-rank", default="", help="R/N: run rank R's share of an N-rank partition alone on one GPU (tuning only)")
+    ap.add_argument("--samples-per-submission", type=int, default=0,
+                    help="samples one cg_run_chromosomes call carries in the resident leg (0 = auto: as many as fit the 32 jobs of a "
+                         "submission, at most 8, when the chromosomes are shared among ranks; 1 on one GPU)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     if args.impl == "reference":
