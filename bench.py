@@ -273,6 +273,7 @@ def own_arm(args):
         return wl.sample_pos[s][c.index] if planes else c.reads
 
     # ---- leg 1: inputs resident in HBM (CG_PTR_DEVICE) ------------------------------------
+    NOUT = 8
     res = []
     flatten_s = 0.0
     for k, c in enumerate(mine):
@@ -282,30 +283,33 @@ def own_arm(args):
         res.append(dict(c=c, gc=to_dev(c.gc), dels=to_dev(c.dels), dups=to_dev(c.dups),
                         runs=to_dev(runs) if runs is not None and len(runs) else None,
                         n_runs=0 if runs is None else len(runs), runs_host=runs,
-                        out_del=[torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
-                        out_dup=[torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
-                        stats=[torch.zeros(STATS_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)],
+                        # result buffers: per position in a submission, NOUT sets in rotation (more than the six submissions in
+                        # flight: the genotype kernels of two submissions may finish in either order)
+                        out_del=[[torch.empty(max(1, len(c.dels)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)] for _ in range(NOUT)],
+                        out_dup=[[torch.empty(max(1, len(c.dups)) * CALL_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)] for _ in range(NOUT)],
+                        stats=[[torch.zeros(STATS_DT.itemsize, dtype=torch.uint8, device=dev) for _ in range(KSUB)] for _ in range(NOUT)],
                         reads=[to_dev(sample_records(k, s)) for s in range(S)], n_reads=[len(sample_records(k, s)) for s in range(S)]))
     torch.cuda.synchronize()
 
-    def device_jobs(s, g):
-        """the jobs of sample s as the g-th sample of a submission"""
+    def device_jobs(s, g, ob):
+        """the jobs of sample s as the g-th sample of a submission, results into buffer set ob"""
         if not res:
             return np.zeros(0, dtype=CHROM_JOB_DT)
         return np.concatenate([chrom_job(r["c"].index + g * n_chrom, r["c"].length, r["gc"], len(r["c"].gc), mq,
                                          None if planes else r["reads"][s], r["n_reads"][s], r["runs"], r["n_runs"], has_map,
-                                         r["dels"], len(r["c"].dels), r["out_del"][g], r["dups"], len(r["c"].dups), r["out_dup"][g], r["stats"][g],
+                                         r["dels"], len(r["c"].dels), r["out_del"][ob][g], r["dups"], len(r["c"].dups), r["out_dup"][ob][g], r["stats"][ob][g],
                                          reads_pos=r["reads"][s] if planes else None) for r in res])
     jobs_dev = {}
 
-    def group_jobs(s0, n):
+    def group_jobs(s0, n, ob):
         """one submission: samples s0 .. s0 + n - 1 (mod S)"""
-        key = (s0 % S, n)
+        key = (s0 % S, n, ob)
         if key not in jobs_dev:
-            jobs_dev[key] = np.concatenate([device_jobs((s0 + g) % S, g) for g in range(n)])
+            jobs_dev[key] = np.concatenate([device_jobs((s0 + g) % S, g, ob) for g in range(n)])
         return jobs_dev[key]
     reads_of_sample = [sum(len(sample_records(k, s)) for k in range(len(mine))) for s in range(S)]
-    last_group = [0]
+    last_group = [0, 0]                        # samples and buffer set of the last submission
+    group_no = [0]
 
     def steps_device(k_steps):
         """k_steps samples, KSUB per submission"""
@@ -317,8 +321,10 @@ def own_arm(args):
             done += n
             if world > 1:
                 ctx.stats_bank((k // KSUB) & 3)   # the exchange of a submission's rows is in flight while the next three fill the other banks
-            ctx.run_chromosomes(group_jobs(k, n)) # ONE submission: every kernel of the path once for all chromosomes of this rank
-            last_group[0] = n
+            ob = group_no[0] % NOUT
+            group_no[0] += 1
+            ctx.run_chromosomes(group_jobs(k, n, ob))     # ONE submission: every kernel of the path once for all chromosomes of this rank
+            last_group[0], last_group[1] = n, ob
             if world > 1 and not no_coll:
                 ctx.stats_allreduce(n_chrom * n)
 
@@ -359,8 +365,9 @@ def own_arm(args):
     issue_ms_dev = float(np.median([r[1] for r in regions]))
     # the calls of the resident leg's last step, for the parity checks below
     g_last = last_group[0] - 1                 # ... which was the g_last-th sample of its submission
-    dev_calls = {r["c"].index: (r["out_del"][g_last].cpu().numpy()[: len(r["c"].dels) * CALL_DT.itemsize].view(CALL_DT).copy(),
-                                r["out_dup"][g_last].cpu().numpy()[: len(r["c"].dups) * CALL_DT.itemsize].view(CALL_DT).copy()) for r in res}
+    ob_last = last_group[1]
+    dev_calls = {r["c"].index: (r["out_del"][ob_last][g_last].cpu().numpy()[: len(r["c"].dels) * CALL_DT.itemsize].view(CALL_DT).copy(),
+                                r["out_dup"][ob_last][g_last].cpu().numpy()[: len(r["c"].dups) * CALL_DT.itemsize].view(CALL_DT).copy()) for r in res}
     # same K steps again with per-launch CUDA events on the context's streams -> roofline of the depth pass.  The
     # slots are chained while profiling (kernels timed alone), so this leg is NOT the one `value` comes from.
     ctx.set_profiling(True)
