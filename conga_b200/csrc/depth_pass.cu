@@ -370,7 +370,10 @@ struct __align__(16) pass_smem {
  * are asked for one chunk ahead, and under a saturated HBM a chunk-time of 16 warps is shorter than that latency. */
 #define PASS_GRID_CTAS_PER_SM 3       /* upper value; cgk_pass_grid picks 2 or 3 by record density */
 #ifndef PASS_BATCH
-#define PASS_BATCH 4                  /* chunks per visit to the work counter */
+#define PASS_BATCH 8                  /* chunks per visit to the work counter.  r02j, pass alone / step, ms per sample:
+                                       * 4: C3 1.002 / 1.198, C2 1.175 / 1.113;  6: 0.989 / 1.189, 0.899 / 0.977;  8: 0.985 / 1.185,
+                                       * 0.902 / 0.987 (C4 and a rank's eighth of C3 unchanged): with a batch a warp writes 32 KB of
+                                       * consecutive depth before it moves on, and the sparse stream of C2 is all writes */
 #endif
 #define PASS_PRE 2                    /* 32-record groups of a chunk asked for one chunk ahead */
 static_assert(PASS_BATCH >= 3 && PASS_BATCH <= 32, "the bounds of batch n+1 are asked for at chunk 1 and used after chunk PASS_BATCH-1");
