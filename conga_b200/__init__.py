@@ -6,7 +6,7 @@ of the reference's call seams (`hotpath`) and the synthetic-input generator (`sy
 Nothing here computes any stage of the path on the CPU.
 """
 from .abi import (CALL_DT, CHROM_JOB_DT, chrom_job, CNV_DT, HALF_DT, SPLITROW_DT, MAPIV_DT, MAPRUN_DT, READ_DT, STATS_DT, CG_PTR_DEVICE, CG_PTR_HOST,
-                  CongaGpuError, Context, comm_unique_id, encode_positions_delta, flatten_mappability, load_library, peer_connect_local)
+                  CongaGpuError, Context, comm_unique_id, depth_stats_noalloc, encode_positions_delta, flatten_mappability, load_library, peer_connect_local)
 
 __all__ = ["CALL_DT", "CHROM_JOB_DT", "chrom_job", "CNV_DT", "HALF_DT", "SPLITROW_DT", "MAPIV_DT", "MAPRUN_DT", "READ_DT", "STATS_DT", "CG_PTR_DEVICE",
-           "CG_PTR_HOST", "CongaGpuError", "Context", "comm_unique_id", "encode_positions_delta", "peer_connect_local", "flatten_mappability", "load_library"]
+           "CG_PTR_HOST", "CongaGpuError", "Context", "comm_unique_id", "depth_stats_noalloc", "encode_positions_delta", "peer_connect_local", "flatten_mappability", "load_library"]

@@ -82,6 +82,7 @@ SYMBOLS = {
     "cg_sr_rows": (_I, [_P, _P, _Z, C.POINTER(_Z), C.POINTER(C.c_uint64)]),
     "cg_sr_count": (_I, [_P, _P, _Z, _P, _Z, _P, _Z, _P, _P]),
     "cg_gc_profile": (_I, [_P, _P, C.c_int64, _P, C.c_int32]),
+    "cg_depth_stats_noalloc": (_I, [_I, _P, _P, _P, C.c_size_t, _I, C.c_int32, _P, C.c_int32, _P, _P, _P, _P]),
     "cg_run_chromosomes": (_I, [_P, _P, _Z]),
     "cg_encode_positions_delta": (_I, [_P, _Z, _P, _P, _Z, C.POINTER(_Z), _P]),
     "cg_sync": (_I, [_P]),
@@ -478,6 +479,20 @@ def peer_connect_local(contexts):
     rc = lib.cg_peer_connect_local(arr, len(contexts))
     if rc != CG_OK:
         raise CongaGpuError(rc, lib.cg_last_error(contexts[0].h).decode())
+
+
+CG_NOALLOC_MAX_LEN = 8386560
+
+
+def depth_stats_noalloc(device: int, stream, pos, mapq, n_reads: int, mq_threshold: int, chrom_len: int, gc, n_windows: int,
+                        depth_out=None, stats_out=None, expected_out=None, flags_out=None) -> None:
+    """cg_depth_stats_noalloc: the depth side of one chromosome out of the library's fixed scratch array.  Every
+    pointer is a device address (torch tensor, int or None); `stream` is a cudaStream_t as an int (0: default)."""
+    lib = load_library()
+    rc = lib.cg_depth_stats_noalloc(device, int(stream or 0), _ptr(pos), _ptr(mapq), n_reads, mq_threshold, chrom_len,
+                                    _ptr(gc), n_windows, _ptr(depth_out), _ptr(stats_out), _ptr(expected_out), _ptr(flags_out))
+    if rc != CG_OK:
+        raise CongaGpuError(rc, lib.cg_last_error(None).decode())
 
 
 def comm_unique_id() -> bytes:

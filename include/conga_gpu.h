@@ -355,6 +355,32 @@ int cg_stats_allreduce(cg_ctx* ctx, int32_t n_rows);
 /* the same for the n contexts of cg_comm_init_all, issued by one thread (inside one NCCL group) */
 int cg_stats_allreduce_all(cg_ctx** ctxs, int n, int32_t n_rows);
 
+/* ---- the depth side of one chromosome without any allocation ----
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and
+ * same results as cg_chrom_begin + cg_push_reads_compact + cg_chrom_finish (+ cg_get_expected, cg_download_depth)
+ * in DEVICE pointer mode, but needs no context: every scratch array of the kernels, the int16 depth array
+ * included, lives in one fixed 17.4 MB __device__ array of the library (held by every GPU that loads the library
+ * until the process exits).  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine)
+ * and does not block: three kernels, one clearing memset and the copy of the depth array are queued on `stream`
+ * (a cudaStream_t; NULL = the default stream) of GPU `device`.
+ *   pos, mapq      device: the records' int32 positions, NON-DECREASING, and their uint8 mapq plane (NULL iff
+ *                  mq_threshold < 0: every record passes), n_reads of each.  There is no out-of-order path here:
+ *                  for unsorted records bit 1 (unsorted) is set in *flags_out and the outputs are undefined.
+ *   chrom_len      1 .. CG_NOALLOC_MAX_LEN; anything larger is rejected with CG_EINVAL (use a context then).
+ *   gc_profile     device: SONIC GC byte per 100-position window, n_windows >= ceil(chrom_len / 100).
+ *   depth_out      device int16[chrom_len] (read_depth[], bam_data.c:205-215) or NULL.
+ *   stats_out      device cg_chrom_stats or NULL;  expected_out: device float[CG_GC_BINS] or NULL.
+ *   flags_out      device uint32 or NULL: 0, or bit 1 = a record was out of order, bit 2 = a record outside
+ *                  [0, chrom_len).
+ * All calls share the one array, which keeps the previous call's contents (what must start at zero is cleared at
+ * the head of every call): calls queued on ONE stream are ordered and safe; calls that overlap on a GPU — two
+ * streams, two threads — race on it.  Errors: cg_last_error(NULL). */
+#define CG_NOALLOC_MAX_LEN 8386560          /* 4095 chunks of 2048 positions */
+int cg_depth_stats_noalloc(int device, void* stream, const int32_t* pos, const uint8_t* mapq, size_t n_reads,
+                           int mq_threshold, int32_t chrom_len, const int8_t* gc_profile, int32_t n_windows,
+                           int16_t* depth_out, cg_chrom_stats* stats_out, float* expected_out, uint32_t* flags_out);
+
 /* Device time of this context's kernels, from CUDA events recorded on its stream
  * around every launch group while profiling is on.  cg_kernel_times waits for the
  * stream, returns the milliseconds and launch counts accumulated since the last
