@@ -375,7 +375,9 @@ struct __align__(16) pass_smem {
                                        * 0.902 / 0.987 (C4 and a rank's eighth of C3 unchanged): with a batch a warp writes 32 KB of
                                        * consecutive depth before it moves on, and the sparse stream of C2 is all writes */
 #endif
+#ifndef PASS_PRE
 #define PASS_PRE 2                    /* 32-record groups of a chunk asked for one chunk ahead */
+#endif
 static_assert(PASS_BATCH >= 3 && PASS_BATCH <= 32, "the bounds of batch n+1 are asked for at chunk 1 and used after chunk PASS_BATCH-1");
 
 /* expected_read_depth[101], read_distribution.c:75-83:
