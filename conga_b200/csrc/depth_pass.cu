@@ -37,6 +37,19 @@
 #include <cstdlib>
 
 #define FULL 0xffffffffu
+/* How a finished chunk leaves shared memory.  Default: ONE bulk copy shared -> global of the warp's 4 KB region
+ * (cp.async.bulk.global.shared::cta, SASS UBLKCP.G.S), issued by one lane, with an L2 evict-first policy — the depth
+ * array is a 5.8 GB write stream nobody reads before the genotype kernel.  The warp's eight LDS.128 + eight STG.128 per
+ * lane and chunk become one instruction, and the copy engine writes whole 4 KB lines.  r02k on B200, pass alone /
+ * step, ms per sample:   per-lane st.global.cs.v4 (-DPASS_NO_BULK_STORE): C3 0.993 / 1.193, C2 0.911 / 0.999, C4 1.561 / 2.055;
+ * bulk copy without the policy: C3 0.976 / 1.154, C2 0.915 / 0.994, C4 1.529 / 1.997;  with it: C3 0.961 / 1.145, C2 0.899 / 0.977.
+ * Two regions per warp (-DPASS_BULK_BUFS=2: bin one while the other is read) need 64 KB per CTA, only two CTAs fit an SM,
+ * and C3 falls to 1.168 / 1.378: with one region the warp waits for the copy engine to have READ the region (not for
+ * the write) before it clears it, which costs nothing measurable beside 23 other warps. */
+#ifndef PASS_NO_BULK_STORE
+#define PASS_BULK_STORE
+#define PASS_BULK_HINT
+#endif
 #define NT   CG_PASS_THREADS
 #define NWARP (NT / 32)
 #define ROWS (CG_CHUNK / 256)         /* rows of 256 positions per chunk */
@@ -354,7 +367,14 @@ struct pass_job {                             /* what the pass needs of a job, s
 };
 
 struct __align__(16) pass_smem {
+#ifdef PASS_BULK_STORE
+#ifndef PASS_BULK_BUFS
+#define PASS_BULK_BUFS 1                      /* 2: one region is binned while the bulk store of the other is read (only two CTAs fit an SM then) */
+#endif
+    uint4 bins4[NWARP][PASS_BULK_BUFS * (CG_CHUNK / 8)];
+#else
     uint4 bins4[NWARP][CG_CHUNK / 8];         /* 8 x 4 KB: eight packed u16 counts per vector, one region per warp */
+#endif
     int win_end[NWARP][MAXWIN];               /* per GC window of the warp's chunk: records (or, wrapped chunks, depth sum) */
     pass_job job[CG_JMAX];
     /* followed by int gcs[n_jobs][CG_PART_WORDS]: per-CTA rd_per_gc / window_per_gc of every job.  32-bit is
@@ -433,6 +453,13 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
     const int n_jobs = S.n_jobs;
     uint4* my4 = sm.bins4[warp];
     unsigned* bins = reinterpret_cast<unsigned*>(my4);                 /* word = positions 2k (low), 2k+1 (high) */
+#ifdef PASS_BULK_STORE
+    int bulk_buf = 0;
+#ifdef PASS_BULK_HINT
+    unsigned long long bulk_policy;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(bulk_policy));
+#endif
+#endif
     int* wend = sm.win_end[warp];
 
     if (tid < n_jobs) {
@@ -540,6 +567,19 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
              * went negative (32768 or more records on one position): counted while the records are binned.
              * `wrapped` chunks (and the out-of-order path) take the sums from a scan of the bins instead. */
             bool big = false;
+#ifdef PASS_BULK_STORE
+            /* this chunk's region: the other one may still be read by the bulk store of the chunk before; the store
+             * that read THIS region (two chunks ago) has to be through before the region is cleared */
+            my4 = sm.bins4[warp] + bulk_buf * (CG_CHUNK / 8);
+            bins = reinterpret_cast<unsigned*>(my4);
+            if (lane == 0) {
+                if (PASS_BULK_BUFS == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            }
+            __syncwarp();
+            for (int i = lane; i < CG_CHUNK / 8; i += 32) my4[i] = make_uint4(0, 0, 0, 0);
+            __syncwarp();
+#endif
 
             /* ---- phase A: the chunk's records -> packed shared-memory histogram, records per window ---- */
             if (!P.unsorted) {
@@ -586,6 +626,23 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
                 const int chunk_total = __reduce_add_sync(FULL, lane < nwin ? wend[lane] : 0);
                 if (lane == 0) S.k.cnt1[P.chunk0 + clc] = chunk_total;
                 /* ---- rows -> depth stores: the packed bins ARE the int16 output vectors ---- */
+#ifdef PASS_BULK_STORE
+                /* one bulk copy shared -> global of the whole 4 KB region, issued by one lane */
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    const unsigned src = (unsigned)__cvta_generic_to_shared(my4);
+                    int16_t* dst = S.depth + gpos;
+#ifdef PASS_BULK_HINT
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+                                 :: "l"(dst), "r"(src), "r"(CG_CHUNK * 2), "l"(bulk_policy) : "memory");
+#else
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(dst), "r"(src), "r"(CG_CHUNK * 2) : "memory");
+#endif
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                bulk_buf ^= PASS_BULK_BUFS - 1;
+#else
                 char* dp = reinterpret_cast<char*>(S.depth) + (gpos + (size_t)lane * 8) * 2;
 #pragma unroll
                 for (int r = 0; r < ROWS; r++) {
@@ -593,6 +650,7 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
                     my4[r * 32 + lane] = make_uint4(0, 0, 0, 0);          /* clean bins for the next chunk */
                     st_cs_v4(dp + r * 512, v.x, v.y, v.z, v.w);
                 }
+#endif
             } else {
                 if (lane < MAXWIN) wend[lane] = 0;                        /* the scan below writes window-END sums */
                 __syncwarp();
@@ -685,6 +743,9 @@ k_depth_pass(const __grid_constant__ cg_sub S, const __grid_constant__ cg_dev_jo
         }
     }
 
+#ifdef PASS_BULK_STORE
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      /* shared memory is read until then */
+#endif
     /* ---- CTA epilogue: what this CTA saw of every job's GC bins, plain coalesced stores ---- */
     __syncthreads();
     CG_CHECK((int)blockIdx.x < S.n_pass_ctas);
