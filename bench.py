@@ -320,7 +320,7 @@ def own_arm(args):
             step_no[0] += n
             done += n
             if world > 1:
-                ctx.stats_bank((k // KSUB) & 3)   # the exchange of a submission's rows is in flight while the next three fill the other banks
+                ctx.stats_bank(group_no[0] & 3)   # the exchange of a submission's rows is in flight while the next three fill the other banks
             ob = group_no[0] % NOUT
             group_no[0] += 1
             ctx.run_chromosomes(group_jobs(k, n, ob))     # ONE submission: every kernel of the path once for all chromosomes of this rank

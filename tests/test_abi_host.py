@@ -44,6 +44,20 @@ def test_no_cpu_fallback_without_gpu():
         abi.Context(0)
 
 
+def test_no_alloc_entry_point_refuses_sizes_beyond_its_scratch():
+    """cg_depth_stats_noalloc checks its arguments before the first CUDA call: a chromosome longer than the fixed
+    scratch array is refused with a clear error (no GPU needed, nothing is computed)."""
+    with pytest.raises(abi.CongaGpuError) as ei:
+        abi.depth_stats_noalloc(0, 0, None, None, 0, -1, abi.CG_NOALLOC_MAX_LEN + 1, 1 << 20, 1 << 30)
+    assert ei.value.code == abi.CG_EINVAL and "CG_NOALLOC_MAX_LEN" in str(ei.value)
+    with pytest.raises(abi.CongaGpuError) as ei:            # a NULL mapq plane with a threshold that could reject a record
+        abi.depth_stats_noalloc(0, 0, 1 << 20, None, 10, 20, 1000, 1 << 20, 10)
+    assert ei.value.code == abi.CG_EINVAL
+    import re
+    hdr = open(os.path.join(ROOT, "include", "conga_gpu.h")).read()
+    assert int(re.search(r"#define CG_NOALLOC_MAX_LEN (\d+)", hdr).group(1)) == abi.CG_NOALLOC_MAX_LEN
+
+
 def test_async_host_mode_refuses_a_pageable_statistics_row():
     """cg_set_async: the pass writes the statistics row into the caller's page-locked memory itself; the Python
     mirror must not hand it a pageable temporary (checked before any foreign call, so no GPU is needed)."""
